@@ -1,0 +1,86 @@
+/* C ABI of the B200 Predictive Sampling rollout engine.
+ *
+ * Drop-in boundary for mjpc::SamplingPlanner (reference: mjpc/planners/sampling/planner.h:41-165,
+ * interface mjpc/planners/planner.h:32-102).  A host-side planner class keeps the reference's
+ * Initialize/Allocate/Reset/SetState/OptimizePolicy/ActionFromPolicy methods and forwards the
+ * planning iteration to these entry points.  All pointers are HOST pointers owned by the caller;
+ * every call is synchronous.  Return value: 0 = ok, <0 = error (text in ps_last_error()).
+ * There is no CPU fallback: without a CUDA device ps_create() fails.
+ */
+#ifndef PS_ENGINE_H_
+#define PS_ENGINE_H_
+#include "ps_model.h"
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define PS_MAX_COST_TERMS 128     /* kMaxCostTerms, mjpc/task.h:32 */
+#define PS_MAX_TASK_PARAMS 64
+#define PS_MAX_TASK_AUX 128
+
+/* residual functions implemented on device (Task::Name() of the reference task) */
+enum { PS_TASK_PARTICLE = 0,      /* mjpc/tasks/particle/particle.cc:50-56 (time-varying goal) */
+       PS_TASK_PARTICLE_FIXED,    /* particle.cc:73-78 (mocap goal) */
+       PS_TASK_PARTICLE_TEST,     /* mjpc/test/testdata/particle_residual.h:33-43 */
+       PS_TASK_CARTPOLE,          /* mjpc/tasks/cartpole/cartpole.cc:36-49 */
+       PS_TASK_ACROBOT,           /* mjpc/tasks/acrobot/acrobot.cc:36-49 */
+       PS_TASK_SWIMMER,           /* mjpc/tasks/swimmer/swimmer.cc:33-45 */
+       PS_TASK_WALKER,            /* mjpc/tasks/walker/walker.cc:38-69 */
+       PS_TASK_QUADRUPED,         /* mjpc/tasks/quadruped/quadruped.cc:33-221 */
+       PS_NUM_TASKS };
+
+enum { PS_SPLINE_ZERO = 0, PS_SPLINE_LINEAR = 1, PS_SPLINE_CUBIC = 2 }; /* spline.h SplineInterpolation */
+
+/* Cost specification + residual snapshot: what Task::Residual()/BaseResidualFn::Update()
+ * (mjpc/task.cc:112-128) hands the planner each iteration, flattened to a POD. */
+typedef struct PsTask_ {
+  int task_id;
+  int num_residual, num_term, num_trace, num_parameters;
+  int dim_norm_residual[PS_MAX_COST_TERMS];
+  int num_norm_parameter[PS_MAX_COST_TERMS];
+  int norm[PS_MAX_COST_TERMS];                 /* mjpc::NormType, mjpc/norm.h:24-35 */
+  double weight[PS_MAX_COST_TERMS];
+  double norm_parameter[2 * PS_MAX_COST_TERMS];
+  double risk;
+  double parameters[PS_MAX_TASK_PARAMS];       /* Task::parameters (residual_* numerics) */
+  double aux[PS_MAX_TASK_AUX];                 /* task-specific residual state (quadruped gait/mode) */
+  int trace_sensor[4];                         /* sensor ids of trace0.. (GetTraces, utilities.cc:250) */
+} PsTask;
+
+typedef struct PsEngine_ PsEngine;
+
+const char* ps_last_error(void);
+/* device_ordinal: CUDA device; rank/world: sample sharding (global sample i lives on rank i*world/N) */
+PsEngine* ps_create(int device_ordinal);
+void ps_destroy(PsEngine* e);
+int ps_set_model(PsEngine* e, const PsModel* m);
+int ps_set_task(PsEngine* e, const PsTask* t);
+/* SamplingPlanner::SetState, planner.cc:146-149 */
+int ps_set_state(PsEngine* e, const double* state, const double* mocap, const double* userdata, double time);
+/* nominal plan (policy.plan): P knot times, knots[P][nu] */
+int ps_set_nominal(PsEngine* e, const double* times, const double* knots, int P, int interpolation);
+/* optional injected standard-normal noise z[N][P][nu] and per-sample second-std flags (parity
+ * runs); pass NULL to use the on-device counter-based generator seeded by ps_set_seed */
+int ps_set_noise(PsEngine* e, const double* z, const unsigned char* use_std2, int N);
+int ps_set_seed(PsEngine* e, unsigned long long seed);
+/* K1+K2+K3: perturb (sample_offset..sample_offset+N of a global batch), roll out H steps,
+ * reduce.  Outputs: local winner index (lowest index on ties), its return, nominal return. */
+int ps_rollouts(PsEngine* e, int N, int H, double sigma0, double sigma1, int sample_offset,
+                int* winner, double* winner_return, double* nominal_return);
+int ps_get_returns(PsEngine* e, double* total_return /*[N]*/, unsigned char* failure /*[N] or NULL*/);
+int ps_get_knots(PsEngine* e, int sample, double* knots /*[P][nu]*/);
+/* full trajectory of one sample (re-rolled with writeback): states[H][nq+nv+na], actions[H][nu],
+ * times[H], residual[H][nr], costs[H], trace[H][3*num_trace]; any pointer may be NULL */
+int ps_get_trajectory(PsEngine* e, int sample, double* states, double* actions, double* times,
+                      double* residual, double* costs, double* trace, double* total_return, int* failure);
+/* writeback of ALL samples for parity tests: states[N][H][ns], residual[N][H][nr] (may be NULL) */
+int ps_get_all_trajectories(PsEngine* e, double* states, double* actions, double* residual, double* costs);
+/* device time of the last ps_rollouts kernels in milliseconds (CUDA events) */
+int ps_last_kernel_ms(PsEngine* e, float* perturb_ms, float* rollout_ms, float* reduce_ms);
+int ps_kernel_launch_count(PsEngine* e, long long* launches);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* PS_ENGINE_H_ */

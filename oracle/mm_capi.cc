@@ -1,0 +1,114 @@
+// ORACLE (test infrastructure).  ctypes-facing C entry points over the CPU restatement.  Used only
+// by tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs.
+#include <cstring>
+#include <string>
+#include "mm_planner.h"
+#include "mm_math.h"
+
+namespace mm {
+void optimizePolicy(Planner* pl, int N, int horizon, const double* z, const unsigned char* use_std2, int nthread);
+}
+using namespace mm;
+
+struct Handle { Planner pl; Data d; };
+
+static void cb(const Model* m, Data* d, void* user) { residual(m, d, (const PsTask*)user, d->sensordata.data()); }
+
+extern "C" {
+
+void* mmo_create(const PsModel* m, const PsTask* t) {
+  Handle* h = new Handle;
+  h->pl.model = m; h->pl.task = *t;
+  makeData(m, &h->d);
+  h->pl.state.assign(m->nq + m->nv + m->na, 0); h->pl.mocap.assign(7 * m->nmocap, 0); h->pl.userdata.assign(m->nuserdata, 0);
+  for (int i = 0; i < m->nmocap; i++) { copy(&h->pl.mocap[7 * i], &h->d.mocap_pos[3 * i], 3); copy(&h->pl.mocap[7 * i + 3], &h->d.mocap_quat[4 * i], 4); }
+  return h;
+}
+void mmo_destroy(void* hp) { delete (Handle*)hp; }
+void mmo_set_task(void* hp, const PsTask* t) { ((Handle*)hp)->pl.task = *t; }
+
+static std::vector<double>* field(Data* d, const std::string& f) {
+#define F(n) if (f == #n) return &d->n;
+  F(qpos) F(qvel) F(act) F(ctrl) F(qacc) F(qacc_warmstart) F(mocap_pos) F(mocap_quat) F(sensordata)
+  F(xpos) F(xquat) F(xmat) F(xipos) F(ximat) F(geom_xpos) F(geom_xmat) F(site_xpos) F(subtree_com) F(cdof) F(cinert)
+  F(qM) F(qLD) F(cvel) F(qfrc_bias) F(qfrc_passive) F(qfrc_fluid) F(qfrc_actuator) F(qfrc_smooth) F(qacc_smooth)
+  F(qfrc_constraint) F(actuator_force) F(efc_J) F(efc_pos) F(efc_D) F(efc_R) F(efc_aref) F(efc_force) F(efc_vel)
+  F(qDeriv) F(subtree_linvel) F(subtree_angmom) F(act_dot)
+#undef F
+  return nullptr;
+}
+int mmo_set(void* hp, const char* f, const double* v, int n) {
+  Handle* h = (Handle*)hp;
+  if (!std::strcmp(f, "time")) { h->d.time = v[0]; return 1; }
+  auto* x = field(&h->d, f); if (!x || (int)x->size() < n) return -1;
+  copy(x->data(), v, n); return n;
+}
+int mmo_get(void* hp, const char* f, double* out, int cap) {
+  Handle* h = (Handle*)hp;
+  if (!std::strcmp(f, "time")) { out[0] = h->d.time; return 1; }
+  if (!std::strcmp(f, "nefc")) { out[0] = h->d.nefc; return 1; }
+  if (!std::strcmp(f, "ncon")) { out[0] = h->d.ncon; return 1; }
+  if (!std::strcmp(f, "solver_iter")) { out[0] = h->d.solver_iter; return 1; }
+  if (!std::strcmp(f, "warnings")) { double s = 0; for (int i = 0; i < N_WARN; i++) s += h->d.warning[i]; out[0] = s; return 1; }
+  if (!std::strcmp(f, "contact")) {  // [dist, pos3, frame9, dim, geom1, geom2] per contact
+    int n = 0; for (auto& c : h->d.contact) { if (n + 16 > cap) break; out[n] = c.dist; copy(out + n + 1, c.pos, 3); copy(out + n + 4, c.frame, 9); out[n + 13] = c.dim; out[n + 14] = c.geom1; out[n + 15] = c.geom2; n += 16; }
+    return n;
+  }
+  auto* x = field(&h->d, f); if (!x) return -1;
+  int n = std::min<int>(cap, (int)x->size()); copy(out, x->data(), n); return (int)x->size();
+}
+void mmo_reset_data(void* hp) { Handle* h = (Handle*)hp; resetData(h->pl.model, &h->d); }
+void mmo_forward(void* hp) { Handle* h = (Handle*)hp; forward(h->pl.model, &h->d, cb, &h->pl.task); }
+void mmo_step(void* hp) { Handle* h = (Handle*)hp; step(h->pl.model, &h->d, cb, &h->pl.task); }
+double mmo_cost(void* hp, const double* res) { return costValue(&((Handle*)hp)->pl.task, res); }
+void mmo_cost_terms(void* hp, const double* res, double* terms) { costTerms(&((Handle*)hp)->pl.task, res, terms, true); }
+double mmo_norm(const double* x, const double* params, int n, int type) { return normValue(x, params, n, type); }
+void mmo_spline_sample(const double* times, const double* knots, int P, int dim, int interp, double t, double* out) { splineSample(times, knots, P, dim, interp, t, out); }
+
+// ---- planner level
+void mmo_planner_config(void* hp, int num_spline_points, int interpolation, double s0, double s1) {
+  Planner& p = ((Handle*)hp)->pl; p.num_spline_points = num_spline_points; p.interpolation = interpolation;
+  p.noise_exploration[0] = s0; p.noise_exploration[1] = s1;
+}
+void mmo_set_state(void* hp, const double* state, const double* mocap, const double* userdata, double time) {
+  Planner& p = ((Handle*)hp)->pl;
+  copy(p.state.data(), state, (int)p.state.size());
+  if (mocap) copy(p.mocap.data(), mocap, (int)p.mocap.size());
+  if (userdata) copy(p.userdata.data(), userdata, (int)p.userdata.size());
+  p.time = time;
+}
+void mmo_set_policy(void* hp, const double* times, const double* knots, int P, int interp) {
+  Planner& p = ((Handle*)hp)->pl; int nu = p.model->nu;
+  p.policy.times.assign(times, times + P); p.policy.knots.assign(knots, knots + P * nu); p.policy.interp = interp;
+  p.previous_policy = p.policy; p.candidate.clear(); p.winner = 0;
+}
+void mmo_optimize(void* hp, int N, int H, const double* z, const unsigned char* use_std2, int nthread) {
+  optimizePolicy(&((Handle*)hp)->pl, N, H, z, use_std2, nthread);
+}
+int mmo_winner(void* hp) { return ((Handle*)hp)->pl.winner; }
+double mmo_improvement(void* hp) { return ((Handle*)hp)->pl.improvement; }
+int mmo_get_policy(void* hp, int which /*0 policy,1 previous,2+i candidate i*/, double* times, double* knots) {
+  Planner& p = ((Handle*)hp)->pl; const Policy& q = which == 0 ? p.policy : which == 1 ? p.previous_policy : p.candidate[which - 2];
+  copy(times, q.times.data(), q.P()); copy(knots, q.knots.data(), (int)q.knots.size()); return q.P();
+}
+void mmo_action(void* hp, double t, int use_previous, double* action) {
+  Planner& p = ((Handle*)hp)->pl; policyAction(p.model, use_previous ? p.previous_policy : p.policy, t, action);
+}
+void mmo_get_returns(void* hp, double* ret, unsigned char* fail) {
+  Planner& p = ((Handle*)hp)->pl;
+  for (size_t i = 0; i < p.trajectory.size(); i++) { ret[i] = p.trajectory[i].total_return; if (fail) fail[i] = p.trajectory[i].failure; }
+}
+void mmo_get_trajectory(void* hp, int i, double* states, double* actions, double* times, double* res, double* costs,
+                        double* trace, double* total_return, int* failure) {
+  const Trajectory& t = ((Handle*)hp)->pl.trajectory[i];
+  if (states) copy(states, t.states.data(), (int)t.states.size());
+  if (actions) copy(actions, t.actions.data(), (int)t.actions.size());
+  if (times) copy(times, t.times.data(), (int)t.times.size());
+  if (res) copy(res, t.residual.data(), (int)t.residual.size());
+  if (costs) copy(costs, t.costs.data(), (int)t.costs.size());
+  if (trace) copy(trace, t.trace.data(), (int)t.trace.size());
+  if (total_return) *total_return = t.total_return;
+  if (failure) *failure = t.failure;
+}
+
+}  // extern "C"

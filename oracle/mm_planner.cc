@@ -1,0 +1,116 @@
+// ORACLE (test infrastructure).  Restates Trajectory::NoisyRollout (mjpc/trajectory.cc:100-210),
+// Trajectory::UpdateReturn (:312-326), SamplingPolicy::Action (planners/sampling/policy.cc:52-59)
+// and SamplingPlanner::{UpdateNominalPolicy,AddNoiseToPolicy,Rollouts,OptimizePolicy}
+// (planners/sampling/planner.cc:190-208,236-380,525-534) with injected noise.
+#include <algorithm>
+#include <thread>
+#include "mm_planner.h"
+#include "mm_math.h"
+
+namespace mm {
+
+void policyAction(const Model* m, const Policy& p, double t, double* action) {
+  splineSample(p.times.data(), p.knots.data(), p.P(), m->nu, p.interp, t, action);
+  for (int i = 0; i < m->nu; i++) action[i] = clip(action[i], m->actuator_ctrlrange[2 * i], m->actuator_ctrlrange[2 * i + 1]);
+}
+
+struct CbUser { const PsTask* task; };
+static void residualCallback(const Model* m, Data* d, void* user) {
+  residual(m, d, ((CbUser*)user)->task, d->sensordata.data());
+}
+
+static bool checkWarnings(Data* d) {
+  bool f = false;
+  for (int i = 0; i < N_WARN; i++) if (d->warning[i] > 0) { d->warning[i] = 0; f = true; }
+  return f;
+}
+
+static void getTraces(const Model* m, const Data* d, const PsTask* t, double* out) {
+  for (int i = 0; i < t->num_trace; i++) copy(out + 3 * i, &d->sensordata[m->sensor_adr[t->trace_sensor[i]]], 3);
+}
+
+void rollout(const Model* m, const PsTask* task, Data* d, const Policy& p, const double* state, double time,
+             const double* mocap, const double* userdata, int steps, Trajectory* tr) {
+  int nq = m->nq, nv = m->nv, na = m->na, nu = m->nu, ns = nq + nv + na, nr = task->num_residual, ntr = 3 * task->num_trace;
+  tr->failure = false; tr->horizon = steps;
+  tr->states.assign(ns * steps, 0); tr->actions.assign(nu * steps, 0); tr->times.assign(steps, 0);
+  tr->residual.assign(nr * steps, 0); tr->costs.assign(steps, 0); tr->trace.assign(ntr * steps, 0);
+  for (int i = 0; i < m->nmocap; i++) { copy(&d->mocap_pos[3 * i], mocap + 7 * i, 3); copy(&d->mocap_quat[4 * i], mocap + 7 * i + 3, 4); }
+  copy(d->userdata.data(), userdata, m->nuserdata);
+  copy(tr->states.data(), state, ns);
+  copy(d->qpos.data(), state, nq); copy(d->qvel.data(), state + nq, nv); copy(d->act.data(), state + nq + nv, na);
+  tr->times[0] = time; d->time = time;
+  // deterministic warm start (the reference inherits qacc_warmstart from whatever rollout last
+  // used this worker's mjData; see DESIGN.md "deviations")
+  zero(d->qacc_warmstart.data(), nv);
+  for (int i = 0; i < N_WARN; i++) d->warning[i] = 0;
+  CbUser cu{task};
+  for (int t = 0; t < steps - 1; t++) {
+    policyAction(m, p, d->time, &tr->actions[t * nu]);
+    copy(d->ctrl.data(), &tr->actions[t * nu], nu);
+    step(m, d, residualCallback, &cu);
+    copy(&tr->residual[t * nr], d->sensordata.data(), nr);
+    getTraces(m, d, task, &tr->trace[t * ntr]);
+    if ((tr->failure |= checkWarnings(d))) { tr->total_return = 1.0e6; return; }
+    copy(&tr->states[(t + 1) * ns], d->qpos.data(), nq); copy(&tr->states[(t + 1) * ns + nq], d->qvel.data(), nv);
+    copy(&tr->states[(t + 1) * ns + nq + nv], d->act.data(), na);
+    tr->times[t + 1] = d->time;
+  }
+  if (steps > 1) copy(&tr->actions[(steps - 1) * nu], &tr->actions[(steps - 2) * nu], nu);
+  forward(m, d, residualCallback, &cu);
+  copy(&tr->residual[(steps - 1) * nr], d->sensordata.data(), nr);
+  getTraces(m, d, task, &tr->trace[(steps - 1) * ntr]);
+  tr->total_return = 0;
+  for (int t = 0; t < steps; t++) { tr->costs[t] = costValue(task, &tr->residual[t * nr]); tr->total_return += tr->costs[t]; }
+  tr->total_return /= std::max(steps, 1);
+}
+
+// SamplingPlanner::UpdateNominalPolicy, non-sliding branch (planner.cc:282-309)
+static void updateNominal(Planner* pl, int horizon) {
+  const Model* m = pl->model;
+  const Policy& src = pl->candidate.empty() ? pl->policy : pl->candidate[pl->winner];
+  int P = pl->num_spline_points, nu = m->nu;
+  double t = pl->time, th = (horizon - 1) * m->opt_timestep;
+  double shift = pl->interpolation == PS_SPLINE_ZERO ? std::fmax(th / P, 1.0e-5) : std::fmax(th / (P - 1), 1.0e-5);
+  Policy np; np.interp = pl->interpolation; np.times.resize(P); np.knots.resize(P * nu);
+  for (int k = 0; k < P; k++) { np.times[k] = t; policyAction(m, src, t, &np.knots[k * nu]); t += shift; }
+  pl->policy = np;
+}
+
+// OptimizePolicy with injected noise z[N][P][nu] (sample-major, node, actuator: the draw order of
+// planner.cc:327-333) and per-sample use_std2 flags (the Bernoulli draw of :323)
+void optimizePolicy(Planner* pl, int N, int horizon, const double* z, const unsigned char* use_std2, int nthread) {
+  const Model* m = pl->model; int nu = m->nu;
+  updateNominal(pl, horizon);
+  pl->policy.interp = pl->interpolation;
+  int P = pl->policy.P();
+  pl->candidate.assign(N, pl->policy);
+  pl->trajectory.resize(N);
+  for (int i = 1; i < N; i++) {
+    double sd = pl->noise_exploration[0];
+    if (pl->noise_exploration[1] > 0 && use_std2 && use_std2[i]) sd = pl->noise_exploration[1];
+    Policy& c = pl->candidate[i];
+    for (int k = 0; k < P; k++) {
+      for (int a = 0; a < nu; a++) {
+        double scale = 0.5 * (m->actuator_ctrlrange[2 * a + 1] - m->actuator_ctrlrange[2 * a]);
+        c.knots[k * nu + a] += (scale * sd) * z[((size_t)i * P + k) * nu + a];
+      }
+      for (int a = 0; a < nu; a++) c.knots[k * nu + a] = clip(c.knots[k * nu + a], m->actuator_ctrlrange[2 * a], m->actuator_ctrlrange[2 * a + 1]);
+    }
+  }
+  nthread = std::max(1, nthread);
+  if ((int)pl->data.size() < nthread) { size_t old = pl->data.size(); pl->data.resize(nthread); for (size_t k = old; k < pl->data.size(); k++) makeData(m, &pl->data[k]); }
+  auto work = [&](int tid) {
+    for (int i = tid; i < N; i += nthread)
+      rollout(m, &pl->task, &pl->data[tid], pl->candidate[i], pl->state.data(), pl->time, pl->mocap.data(), pl->userdata.data(), horizon, &pl->trajectory[i]);
+  };
+  if (nthread == 1) work(0);
+  else { std::vector<std::thread> th; for (int k = 0; k < nthread; k++) th.emplace_back(work, k); for (auto& x : th) x.join(); }
+  int best = 0;
+  for (int i = 1; i < N; i++) if (pl->trajectory[i].total_return < pl->trajectory[best].total_return) best = i;
+  pl->winner = best;
+  pl->previous_policy = pl->policy; pl->policy = pl->candidate[best];
+  pl->improvement = std::fmax(pl->trajectory[0].total_return - pl->trajectory[best].total_return, 0.0);
+}
+
+}  // namespace mm

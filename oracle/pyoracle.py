@@ -1,0 +1,136 @@
+"""ORACLE (test infrastructure, not product): ctypes wrapper over oracle/libmm_oracle.so.
+
+Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs import this.
+"""
+import ctypes
+import os
+import subprocess
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_LIB = None
+_dp = ctypes.POINTER(ctypes.c_double)
+
+
+def build():
+    subprocess.check_call(["make", "-s", "-C", _HERE])
+
+
+def lib():
+    global _LIB
+    if _LIB is None:
+        path = os.path.join(_HERE, "libmm_oracle.so")
+        if not os.path.exists(path):
+            build()
+        L = ctypes.CDLL(path)
+        L.mmo_create.restype = ctypes.c_void_p
+        L.mmo_cost.restype = ctypes.c_double
+        L.mmo_norm.restype = ctypes.c_double
+        L.mmo_improvement.restype = ctypes.c_double
+        _LIB = L
+    return _LIB
+
+
+def _p(a):
+    return a.ctypes.data_as(_dp) if a is not None else None
+
+
+def _arr(x):
+    return np.ascontiguousarray(np.asarray(x, dtype=np.float64))
+
+
+def norm(x, params, ntype):
+    x = _arr(x); p = _arr(list(params) + [0.0, 0.0])
+    return lib().mmo_norm(_p(x), _p(p), ctypes.c_int(x.size), ctypes.c_int(ntype))
+
+
+def spline_sample(times, knots, interp, t):
+    times = _arr(times); knots = _arr(knots).reshape(len(times), -1)
+    out = np.zeros(knots.shape[1] if len(times) else 1)
+    lib().mmo_spline_sample(_p(times), _p(knots), len(times), out.size, interp, ctypes.c_double(t), _p(out))
+    return out
+
+
+class Oracle:
+    def __init__(self, model, task):
+        self.model, self.task = model, task
+        self.L = lib()
+        self.h = ctypes.c_void_p(self.L.mmo_create(ctypes.byref(model.c_struct()), ctypes.byref(task)))
+        self.ns = model.nq + model.nv + model.na
+
+    def __del__(self):
+        try:
+            self.L.mmo_destroy(self.h)
+        except Exception:
+            pass
+
+    # ---- engine level
+    def set(self, name, v):
+        v = _arr(np.atleast_1d(v))
+        r = self.L.mmo_set(self.h, name.encode(), _p(v), v.size)
+        assert r >= 0, name
+
+    def get(self, name, cap=65536):
+        out = np.zeros(cap)
+        n = self.L.mmo_get(self.h, name.encode(), _p(out), cap)
+        assert n >= 0, name
+        return out[:n].copy()
+
+    def set_task(self, task):
+        self.task = task; self.L.mmo_set_task(self.h, ctypes.byref(task))
+
+    def reset_data(self): self.L.mmo_reset_data(self.h)
+    def forward(self): self.L.mmo_forward(self.h)
+    def step(self): self.L.mmo_step(self.h)
+
+    def cost(self, residual):
+        r = _arr(residual); return self.L.mmo_cost(self.h, _p(r))
+
+    def cost_terms(self, residual):
+        r = _arr(residual); out = np.zeros(self.task.num_term)
+        self.L.mmo_cost_terms(self.h, _p(r), _p(out)); return out
+
+    # ---- planner level
+    def configure(self, num_spline_points, interpolation, sigma0, sigma1=0.0):
+        self.P = num_spline_points
+        self.L.mmo_planner_config(self.h, num_spline_points, interpolation, ctypes.c_double(sigma0), ctypes.c_double(sigma1))
+
+    def set_state(self, state, time, mocap=None, userdata=None):
+        s = _arr(state); mo = _arr(mocap) if mocap is not None else None
+        ud = _arr(userdata) if userdata is not None else None
+        self.L.mmo_set_state(self.h, _p(s), _p(mo), _p(ud), ctypes.c_double(time))
+
+    def set_policy(self, times, knots, interp):
+        t = _arr(times); k = _arr(knots)
+        self.L.mmo_set_policy(self.h, _p(t), _p(k), len(t), interp)
+
+    def optimize(self, N, H, z, use_std2=None, nthread=1):
+        z = _arr(z)
+        u = np.ascontiguousarray(use_std2, dtype=np.uint8) if use_std2 is not None else None
+        self.N, self.H = N, H
+        self.L.mmo_optimize(self.h, N, H, _p(z), u.ctypes.data_as(ctypes.c_char_p) if u is not None else None, nthread)
+        return self.L.mmo_winner(self.h)
+
+    def policy(self, which=0):
+        nu = self.model.nu
+        t = np.zeros(64); k = np.zeros(64 * max(nu, 1))
+        P = self.L.mmo_get_policy(self.h, which, _p(t), _p(k))
+        return t[:P].copy(), k[:P * nu].reshape(P, nu).copy()
+
+    def action(self, t, use_previous=False):
+        out = np.zeros(max(self.model.nu, 1))
+        self.L.mmo_action(self.h, ctypes.c_double(t), int(use_previous), _p(out)); return out[:self.model.nu]
+
+    def returns(self):
+        r = np.zeros(self.N); f = np.zeros(self.N, dtype=np.uint8)
+        self.L.mmo_get_returns(self.h, _p(r), f.ctypes.data_as(ctypes.c_char_p)); return r, f
+
+    def improvement(self): return self.L.mmo_improvement(self.h)
+
+    def trajectory(self, i):
+        H, m, t = self.H, self.model, self.task
+        st = np.zeros((H, self.ns)); ac = np.zeros((H, m.nu)); tm = np.zeros(H)
+        rs = np.zeros((H, t.num_residual)); cs = np.zeros(H); tr = np.zeros((H, 3 * t.num_trace))
+        ret = ctypes.c_double(); fail = ctypes.c_int()
+        self.L.mmo_get_trajectory(self.h, i, _p(st), _p(ac), _p(tm), _p(rs), _p(cs), _p(tr), ctypes.byref(ret), ctypes.byref(fail))
+        return dict(states=st, actions=ac, times=tm, residual=rs, costs=cs, trace=tr, total_return=ret.value, failure=bool(fail.value))
