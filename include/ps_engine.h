@@ -46,6 +46,8 @@ typedef struct PsTask_ {
   double parameters[PS_MAX_TASK_PARAMS];       /* Task::parameters (residual_* numerics) */
   double aux[PS_MAX_TASK_AUX];                 /* task-specific residual state (quadruped gait/mode) */
   int trace_sensor[4];                         /* sensor ids of trace0.. (GetTraces, utilities.cc:250) */
+  int sensor_id[16];                           /* SensorByName lookups resolved once on the host (utilities.cc:166-175) */
+  int iaux[16];                                /* task-specific integer state (body / geom ids, modes) */
 } PsTask;
 
 typedef struct PsEngine_ PsEngine;
@@ -55,6 +57,8 @@ const char* ps_last_error(void);
 PsEngine* ps_create(int device_ordinal);
 void ps_destroy(PsEngine* e);
 int ps_set_model(PsEngine* e, const PsModel* m);
+/* Agent::PlanIteration overrides (agent.cc:275-276): model->opt.timestep / opt.integrator */
+int ps_set_options(PsEngine* e, double timestep, int integrator);
 int ps_set_task(PsEngine* e, const PsTask* t);
 /* SamplingPlanner::SetState, planner.cc:146-149 */
 int ps_set_state(PsEngine* e, const double* state, const double* mocap, const double* userdata, double time);
@@ -79,6 +83,15 @@ int ps_get_all_trajectories(PsEngine* e, double* states, double* actions, double
 /* device time of the last ps_rollouts kernels in milliseconds (CUDA events) */
 int ps_last_kernel_ms(PsEngine* e, float* perturb_ms, float* rollout_ms, float* reduce_ms);
 int ps_kernel_launch_count(PsEngine* e, long long* launches);
+/* Device-resident winner record of the last ps_rollouts: [return, global index, nominal return,
+ * knots[P*nu]] as doubles.  Exposed so a multi-GPU host can feed it to an NCCL all-gather
+ * (min-loc over ranks) without a host round trip.  *count = 3 + P*nu. */
+int ps_winner_record_device(PsEngine* e, void** device_ptr, int* count);
+/* CUDA stream (cudaStream_t) all engine work is issued on */
+int ps_stream(PsEngine* e, void** stream);
+/* ps_rollouts without the final device->host read: results stay in the winner record */
+int ps_rollouts_async(PsEngine* e, int N, int H, double sigma0, double sigma1, int sample_offset);
+int ps_name(char* out, int cap);
 
 #ifdef __cplusplus
 }

@@ -1,0 +1,517 @@
+// C ABI of the B200 Predictive Sampling rollout engine (include/ps_engine.h): host-side staging,
+// kernel launches and read-back.  No CPU fallback exists: every entry point drives the CUDA
+// kernels in ps_kernels.cuh, and ps_create() fails without a device.
+//
+// Boundary it replaces: the body of SamplingPlanner::OptimizePolicyCandidates / Rollouts
+// (mjpc/planners/sampling/planner.cc:151-187,342-380) -- N ThreadPool closures each calling
+// Trajectory::Rollout on a per-thread mjData -- becomes K1 + K2 + K3 on one stream.
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+#include "../../include/ps_engine.h"
+#include "ps_kernels.cuh"
+
+using namespace ps;
+
+static thread_local std::string g_error;
+static int fail(const std::string& s) { g_error = s; return -1; }
+#define CU(call)                                                                                   \
+  do { cudaError_t e_ = (call); if (e_ != cudaSuccess) return fail(std::string(#call) + ": " + cudaGetErrorString(e_)); } while (0)
+
+// ---------------------------------------------------------------- engine instantiations
+//                        NQ NV NU NA NBODY NJNT NGEOM NSITE NMOCAP NPAIR MAXCON MAXEFC NSENSOR ELLIPTIC
+typedef Traits<2, 2, 2, 0, 4, 2, 8, 2, 1, 0, 0, 4, 12, false> TinyT;          // particle, cartpole, acrobot
+typedef Traits<9, 9, 6, 5, 9, 9, 12, 4, 1, 12, 10, 48, 16, false> PlanarT;    // swimmer, walker
+typedef Traits<19, 18, 12, 0, 16, 13, 40, 24, 2, 48, 16, 96, 24, true> LeggedT;  // quadruped (free joint, elliptic cones)
+
+struct PairList { std::vector<int> g1, g2; int unsupported = 0; };
+
+static int weld_body(const PsModel* m, int b) { while (b > 0 && m->body_dofnum[b] == 0) b = m->body_parentid[b]; return b; }
+
+static bool pair_supported(int t1, int t2) {
+  if (t1 == PS_GEOM_PLANE) return t2 == PS_GEOM_SPHERE || t2 == PS_GEOM_CAPSULE || t2 == PS_GEOM_CYLINDER || t2 == PS_GEOM_BOX;
+  if (t1 == PS_GEOM_SPHERE) return t2 == PS_GEOM_SPHERE || t2 == PS_GEOM_CAPSULE;
+  return t1 == PS_GEOM_CAPSULE && t2 == PS_GEOM_CAPSULE;
+}
+
+// static part of the collision filter (contype/conaffinity, same/welded body, parent-child)
+static PairList static_pairs(const PsModel* m) {
+  PairList pl;
+  if (m->opt_disableflags & (PS_DSBL_CONTACT | PS_DSBL_CONSTRAINT)) return pl;
+  for (int ga = 0; ga < m->ngeom; ga++)
+    for (int gb = ga + 1; gb < m->ngeom; gb++) {
+      const int b1 = m->geom_bodyid[ga], b2 = m->geom_bodyid[gb];
+      if (b1 == b2) continue;
+      if (!((m->geom_contype[ga] & m->geom_conaffinity[gb]) || (m->geom_contype[gb] & m->geom_conaffinity[ga]))) continue;
+      const int w1 = weld_body(m, b1), w2 = weld_body(m, b2);
+      if (w1 == w2) continue;
+      if (!(m->opt_disableflags & PS_DSBL_FILTERPARENT) && w1 != 0 && w2 != 0)
+        if (weld_body(m, m->body_parentid[w1]) == w2 || weld_body(m, m->body_parentid[w2]) == w1) continue;
+      int g1 = ga, g2 = gb;
+      if (m->geom_type[g1] > m->geom_type[g2]) { int t = g1; g1 = g2; g2 = t; }
+      if (m->geom_type[g1] == PS_GEOM_PLANE && m->geom_type[g2] == PS_GEOM_PLANE) continue;
+      if (!pair_supported(m->geom_type[g1], m->geom_type[g2])) { pl.unsupported++; continue; }
+      pl.g1.push_back(g1); pl.g2.push_back(g2);
+    }
+  return pl;
+}
+
+template <class T>
+static int fill_model(const PsModel* s, const PairList& pl, void* out, std::string* why) {
+  DevModel<T>& m = reinterpret_cast<Constants<T>*>(out)->m;
+  std::memset(&m, 0, sizeof(m));
+#define CAP(field, cap) if (s->field > cap) { *why = std::string(#field) + " exceeds capacity"; return -1; }
+  CAP(nq, T::NQ) CAP(nv, T::NV) CAP(nu, T::NU) CAP(na, T::NA) CAP(nbody, T::NBODY) CAP(njnt, T::NJNT) CAP(ngeom, T::NGEOM)
+  CAP(nsite, T::NSITE) CAP(nmocap, T::NMOCAP) CAP(nsensor, T::NSENSOR)
+#undef CAP
+  if ((int)pl.g1.size() > T::NPAIR) { *why = "collision pairs exceed capacity"; return -1; }
+  if (s->opt_cone == PS_CONE_ELLIPTIC && !T::ELLIPTIC && !pl.g1.empty()) { *why = "elliptic cones not in this instantiation"; return -1; }
+  m.timestep = s->opt_timestep; m.impratio = s->opt_impratio; m.tolerance = s->opt_tolerance; m.ls_tolerance = s->opt_ls_tolerance;
+  m.density = s->opt_density; m.viscosity = s->opt_viscosity; m.meaninertia = s->stat_meaninertia;
+  for (int k = 0; k < 3; k++) { m.gravity[k] = s->opt_gravity[k]; m.wind[k] = s->opt_wind[k]; }
+  m.integrator = s->opt_integrator; m.cone = s->opt_cone; m.iterations = s->opt_iterations; m.ls_iterations = s->opt_ls_iterations;
+  m.disableflags = s->opt_disableflags;
+  m.nq = s->nq; m.nv = s->nv; m.nu = s->nu; m.na = s->na; m.nbody = s->nbody; m.njnt = s->njnt; m.ngeom = s->ngeom;
+  m.nsite = s->nsite; m.nmocap = s->nmocap; m.nsensor = s->nsensor; m.npair = (int)pl.g1.size();
+#define CPY(dst, src, n) for (int i_ = 0; i_ < (n); i_++) m.dst[i_] = s->src[i_];
+  CPY(qpos0, qpos0, s->nq) CPY(qpos_spring, qpos_spring, s->nq)
+  CPY(body_parentid, body_parentid, s->nbody) CPY(body_rootid, body_rootid, s->nbody) CPY(body_jntnum, body_jntnum, s->nbody)
+  CPY(body_jntadr, body_jntadr, s->nbody) CPY(body_dofnum, body_dofnum, s->nbody) CPY(body_dofadr, body_dofadr, s->nbody)
+  CPY(body_mocapid, body_mocapid, s->nbody)
+  for (int b = 0; b < s->nbody; b++) m.body_weldid[b] = weld_body(s, b);
+  CPY(body_pos, body_pos, 3 * s->nbody) CPY(body_quat, body_quat, 4 * s->nbody) CPY(body_ipos, body_ipos, 3 * s->nbody)
+  CPY(body_iquat, body_iquat, 4 * s->nbody) CPY(body_mass, body_mass, s->nbody) CPY(body_subtreemass, body_subtreemass, s->nbody)
+  CPY(body_inertia, body_inertia, 3 * s->nbody) CPY(body_invweight0, body_invweight0, 2 * s->nbody)
+  CPY(jnt_type, jnt_type, s->njnt) CPY(jnt_qposadr, jnt_qposadr, s->njnt) CPY(jnt_dofadr, jnt_dofadr, s->njnt)
+  CPY(jnt_bodyid, jnt_bodyid, s->njnt) CPY(jnt_limited, jnt_limited, s->njnt) CPY(jnt_pos, jnt_pos, 3 * s->njnt)
+  CPY(jnt_axis, jnt_axis, 3 * s->njnt) CPY(jnt_stiffness, jnt_stiffness, s->njnt) CPY(jnt_range, jnt_range, 2 * s->njnt)
+  CPY(jnt_margin, jnt_margin, s->njnt) CPY(jnt_solref, jnt_solref, 2 * s->njnt) CPY(jnt_solimp, jnt_solimp, 5 * s->njnt)
+  CPY(dof_bodyid, dof_bodyid, s->nv) CPY(dof_jntid, dof_jntid, s->nv) CPY(dof_parentid, dof_parentid, s->nv)
+  CPY(dof_armature, dof_armature, s->nv) CPY(dof_damping, dof_damping, s->nv) CPY(dof_frictionloss, dof_frictionloss, s->nv)
+  CPY(dof_solref, dof_solref, 2 * s->nv) CPY(dof_solimp, dof_solimp, 5 * s->nv) CPY(dof_invweight0, dof_invweight0, s->nv)
+  CPY(geom_type, geom_type, s->ngeom) CPY(geom_condim, geom_condim, s->ngeom) CPY(geom_bodyid, geom_bodyid, s->ngeom)
+  CPY(geom_priority, geom_priority, s->ngeom) CPY(geom_group, geom_group, s->ngeom)
+  CPY(geom_size, geom_size, 3 * s->ngeom) CPY(geom_pos, geom_pos, 3 * s->ngeom) CPY(geom_quat, geom_quat, 4 * s->ngeom)
+  CPY(geom_friction, geom_friction, 3 * s->ngeom) CPY(geom_solmix, geom_solmix, s->ngeom) CPY(geom_solref, geom_solref, 2 * s->ngeom)
+  CPY(geom_solimp, geom_solimp, 5 * s->ngeom) CPY(geom_margin, geom_margin, s->ngeom) CPY(geom_gap, geom_gap, s->ngeom)
+  CPY(geom_rbound, geom_rbound, s->ngeom)
+  CPY(site_bodyid, site_bodyid, s->nsite) CPY(site_pos, site_pos, 3 * s->nsite) CPY(site_quat, site_quat, 4 * s->nsite)
+  CPY(act_dyntype, actuator_dyntype, s->nu) CPY(act_gaintype, actuator_gaintype, s->nu) CPY(act_biastype, actuator_biastype, s->nu)
+  CPY(act_actadr, actuator_actadr, s->nu) CPY(act_ctrllimited, actuator_ctrllimited, s->nu)
+  CPY(act_forcelimited, actuator_forcelimited, s->nu) CPY(act_actlimited, actuator_actlimited, s->nu)
+  CPY(act_dynprm, actuator_dynprm, 3 * s->nu) CPY(act_gainprm, actuator_gainprm, 3 * s->nu) CPY(act_biasprm, actuator_biasprm, 3 * s->nu)
+  CPY(act_ctrlrange, actuator_ctrlrange, 2 * s->nu) CPY(act_forcerange, actuator_forcerange, 2 * s->nu)
+  CPY(act_actrange, actuator_actrange, 2 * s->nu) CPY(act_gear, actuator_gear, s->nu)
+  CPY(sensor_type, sensor_type, s->nsensor) CPY(sensor_objtype, sensor_objtype, s->nsensor) CPY(sensor_objid, sensor_objid, s->nsensor)
+#undef CPY
+  for (int i = 0; i < s->nu; i++) {
+    if (s->actuator_trntype[i] != PS_TRN_JOINT) { *why = "only joint transmissions are supported"; return -1; }
+    m.act_jntid[i] = s->actuator_trnid[2 * i];
+  }
+  for (int i = 0; i < s->nv; i++) if (s->dof_damping[i] > 0) m.any_damping = 1;
+  for (int p = 0; p < m.npair; p++) { m.pair_geom1[p] = pl.g1[p]; m.pair_geom2[p] = pl.g2[p]; m.geom_used[pl.g1[p]] = 1; m.geom_used[pl.g2[p]] = 1; }
+  for (int i = 0; i < s->nsensor; i++) if (s->sensor_objtype[i] == PS_OBJ_GEOM && s->sensor_objid[i] >= 0) m.geom_used[s->sensor_objid[i]] = 1;
+  if (T::ELLIPTIC) for (int g = 0; g < s->ngeom; g++) m.geom_used[g] = 1;   // legged residual reads geom frames directly
+  return 0;
+}
+
+template <class T>
+static void set_options(void* c, double timestep, int integrator) {
+  DevModel<T>& m = reinterpret_cast<Constants<T>*>(c)->m; m.timestep = timestep; m.integrator = integrator;
+}
+
+template <class T>
+static void set_task(void* c, const DevTask& t, int need_subtreevel) {
+  Constants<T>* k = reinterpret_cast<Constants<T>*>(c); k->t = t; k->m.need_subtreevel = need_subtreevel;
+}
+
+template <class T>
+static int set_plan(void* c, const double* state, int ns, const double* mocap, int nmocap, double time, const double* times,
+                    int P, int interp, int H) {
+  DevPlan<T>& p = reinterpret_cast<Constants<T>*>(c)->p;
+  if (P > 36) return -1;
+  if (state) for (int i = 0; i < ns; i++) p.state[i] = state[i];
+  if (mocap) for (int i = 0; i < 7 * nmocap; i++) p.mocap[i] = mocap[i];
+  if (time == time) p.time = time;
+  if (times) { for (int i = 0; i < P; i++) p.spline_times[i] = times[i]; p.num_spline_points = P; p.interpolation = interp; }
+  if (H > 0) p.horizon = H;
+  return 0;
+}
+
+template <class T, int BLOCK>
+static void launch_rollout(cudaStream_t st, const void* dconst, const double* knots, int stride, int first, int n,
+                           long long offset, double* returns, unsigned char* failure, MinLoc* block_min, Writeback wb, bool writeback) {
+  const int grid = (n + BLOCK - 1) / BLOCK;
+  const Constants<T>* c = reinterpret_cast<const Constants<T>*>(dconst);
+  if (writeback) rollout_kernel<T, BLOCK, true><<<grid, BLOCK, 0, st>>>(c, knots, stride, first, n, offset, returns, failure, block_min, wb);
+  else rollout_kernel<T, BLOCK, false><<<grid, BLOCK, 0, st>>>(c, knots, stride, first, n, offset, returns, failure, block_min, wb);
+}
+
+struct Variant {
+  const char* name; size_t const_bytes; int block;
+  int (*fill)(const PsModel*, const PairList&, void*, std::string*);
+  void (*options)(void*, double, int);
+  void (*task)(void*, const DevTask&, int);
+  int (*plan)(void*, const double*, int, const double*, int, double, const double*, int, int, int);
+  void (*launch)(cudaStream_t, const void*, const double*, int, int, int, long long, double*, unsigned char*, MinLoc*, Writeback, bool);
+};
+template <class T, int BLOCK>
+static Variant make_variant(const char* name) {
+  return Variant{name, sizeof(Constants<T>), BLOCK, fill_model<T>, set_options<T>, set_task<T>, set_plan<T>, launch_rollout<T, BLOCK>};
+}
+static const Variant kVariants[] = {make_variant<TinyT, 128>("tiny"), make_variant<PlanarT, 64>("planar"),
+                                    make_variant<LeggedT, 64>("legged")};
+
+// ---------------------------------------------------------------- engine object
+struct PsEngine_ {
+  int device = 0; cudaStream_t stream = nullptr;
+  const Variant* var = nullptr;
+  void* h_const = nullptr; void* d_const = nullptr;             // pinned host mirror + device copy
+  int nq = 0, nv = 0, nu = 0, na = 0, nmocap = 0, nsensor = 0, ns = 0;
+  std::vector<int> sensor_type;
+  std::vector<double> ctrlrange;
+  DevTask task{}; bool have_task = false, have_model = false;
+  int P = 0, interp = 0, H = 0, N = 0, cap = 0, stride = 0, nelem = 0, nblocks = 0;
+  long long offset = 0;
+  double *d_nominal = nullptr, *d_ctrlrange = nullptr, *d_knots = nullptr, *d_returns = nullptr, *d_record = nullptr, *d_z = nullptr;
+  unsigned char *d_failure = nullptr, *d_std2 = nullptr; MinLoc* d_blockmin = nullptr;
+  double* h_record = nullptr;                                     // pinned
+  size_t knots_cap = 0, z_cap = 0; bool have_noise = false;
+  unsigned long long seed = 1234, iteration = 0;
+  // writeback buffers (parity / BestTrajectory), sized on demand
+  Writeback wb{}; size_t wb_cap[6] = {0, 0, 0, 0, 0, 0}; int wb_N = 0, wb_H = 0; bool wb_valid = false;
+  double sigma0 = 0, sigma1 = 0;
+  cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
+  long long launches = 0;
+  double* d_scratch = nullptr; size_t scratch_cap = 0;
+};
+
+static int ensure(double** p, size_t* cap, size_t need) {
+  if (*cap >= need) return 0;
+  if (*p) cudaFree(*p);
+  *p = nullptr; *cap = 0;
+  CU(cudaMalloc(p, need * sizeof(double)));
+  *cap = need; return 0;
+}
+
+extern "C" {
+
+const char* ps_last_error(void) { return g_error.c_str(); }
+int ps_name(char* out, int cap) { std::snprintf(out, cap, "mujoco_mpc_b200 predictive-sampling engine (sm_100a)"); return 0; }
+
+PsEngine* ps_create(int device_ordinal) {
+  int ndev = 0;
+  if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev <= device_ordinal) {
+    g_error = "ps_create: no CUDA device " + std::to_string(device_ordinal) + " (this engine has no CPU path)"; return nullptr;
+  }
+  if (cudaSetDevice(device_ordinal) != cudaSuccess) { g_error = "cudaSetDevice failed"; return nullptr; }
+  PsEngine* e = new PsEngine_;
+  e->device = device_ordinal;
+  if (cudaStreamCreateWithFlags(&e->stream, cudaStreamNonBlocking) != cudaSuccess) { g_error = "cudaStreamCreate failed"; delete e; return nullptr; }
+  for (auto& ev : e->ev) cudaEventCreate(&ev);
+  cudaMallocHost(&e->h_record, (3 + 36 * 32) * sizeof(double));
+  cudaMalloc(&e->d_record, (3 + 36 * 32) * sizeof(double));
+  return e;
+}
+
+void ps_destroy(PsEngine* e) {
+  if (!e) return;
+  cudaSetDevice(e->device);
+  cudaStreamSynchronize(e->stream);
+  void* bufs[] = {e->d_const, e->d_nominal, e->d_ctrlrange, e->d_knots, e->d_returns, e->d_record, e->d_z, e->d_failure, e->d_std2,
+                  e->d_blockmin, e->wb.states, e->wb.actions, e->wb.residual, e->wb.costs, e->wb.times, e->wb.trace, e->d_scratch};
+  for (void* b : bufs) if (b) cudaFree(b);
+  if (e->h_const) cudaFreeHost(e->h_const);
+  if (e->h_record) cudaFreeHost(e->h_record);
+  for (auto& ev : e->ev) if (ev) cudaEventDestroy(ev);
+  cudaStreamDestroy(e->stream);
+  delete e;
+}
+
+int ps_set_model(PsEngine* e, const PsModel* m) {
+  if (!e || !m) return fail("ps_set_model: null argument");
+  CU(cudaSetDevice(e->device));
+  PairList pl = static_pairs(m);
+  std::string why, all;
+  const Variant* chosen = nullptr; void* host = nullptr;
+  for (const Variant& v : kVariants) {
+    void* h = nullptr; CU(cudaMallocHost(&h, v.const_bytes)); std::memset(h, 0, v.const_bytes);
+    if (v.fill(m, pl, h, &why) == 0) { chosen = &v; host = h; break; }
+    all += std::string(v.name) + ": " + why + "; "; cudaFreeHost(h);
+  }
+  if (!chosen) return fail("ps_set_model: model outside the supported class (" + all + ")");
+  if (e->h_const) cudaFreeHost(e->h_const);
+  if (e->d_const) cudaFree(e->d_const);
+  e->var = chosen; e->h_const = host;
+  CU(cudaMalloc(&e->d_const, chosen->const_bytes));
+  e->nq = m->nq; e->nv = m->nv; e->nu = m->nu; e->na = m->na; e->nmocap = m->nmocap; e->nsensor = m->nsensor; e->ns = m->nq + m->nv + m->na;
+  e->sensor_type.assign(m->sensor_type, m->sensor_type + m->nsensor);
+  e->ctrlrange.assign(m->actuator_ctrlrange, m->actuator_ctrlrange + 2 * m->nu);
+  for (int i = 0; i < m->nu; i++) if (!m->actuator_ctrllimited[i]) { e->ctrlrange[2 * i] = -1e300; e->ctrlrange[2 * i + 1] = 1e300; }
+  if (e->d_ctrlrange) cudaFree(e->d_ctrlrange);
+  CU(cudaMalloc(&e->d_ctrlrange, sizeof(double) * 2 * (m->nu > 0 ? m->nu : 1)));
+  CU(cudaMemcpy(e->d_ctrlrange, e->ctrlrange.data(), sizeof(double) * 2 * m->nu, cudaMemcpyHostToDevice));
+  // default mocap poses = body pos/quat (mj_resetData)
+  std::vector<double> mocap(7 * (m->nmocap > 0 ? m->nmocap : 1), 0.0);
+  for (int b = 0; b < m->nbody; b++) if (m->body_mocapid[b] >= 0) {
+    const int id = m->body_mocapid[b];
+    for (int k = 0; k < 3; k++) mocap[7 * id + k] = m->body_pos[3 * b + k];
+    for (int k = 0; k < 4; k++) mocap[7 * id + 3 + k] = m->body_quat[4 * b + k];
+  }
+  std::vector<double> st(e->ns, 0.0); for (int i = 0; i < m->nq; i++) st[i] = m->qpos0[i];
+  chosen->plan(e->h_const, st.data(), e->ns, mocap.data(), m->nmocap, 0.0, nullptr, 0, 0, 0);
+  e->have_model = true; e->have_task = false; e->wb_valid = false;
+  return 0;
+}
+
+int ps_set_options(PsEngine* e, double timestep, int integrator) {
+  if (!e || !e->have_model) return fail("ps_set_options: no model");
+  e->var->options(e->h_const, timestep, integrator); return 0;
+}
+
+int ps_set_task(PsEngine* e, const PsTask* t) {
+  if (!e || !e->have_model) return fail("ps_set_task: set the model first");
+  if (t->num_term > kMaxTerms) return fail("ps_set_task: more cost terms than the device carries");
+  if (t->num_residual > kMaxResidual) return fail("ps_set_task: residual too long");
+  if (t->num_parameters > kMaxTaskParam) return fail("ps_set_task: too many task parameters");
+  DevTask d; std::memset(&d, 0, sizeof(d));
+  d.task_id = t->task_id; d.num_residual = t->num_residual; d.num_term = t->num_term; d.num_trace = t->num_trace > 4 ? 4 : t->num_trace;
+  int np = 0;
+  for (int k = 0; k < t->num_term; k++) {
+    d.dim_norm_residual[k] = t->dim_norm_residual[k]; d.num_norm_parameter[k] = t->num_norm_parameter[k]; d.norm[k] = t->norm[k];
+    d.weight[k] = t->weight[k]; np += t->num_norm_parameter[k];
+  }
+  for (int k = 0; k < np && k < 2 * kMaxTerms; k++) d.norm_parameter[k] = t->norm_parameter[k];
+  d.risk = t->risk;
+  for (int k = 0; k < t->num_parameters; k++) d.parameters[k] = t->parameters[k];
+  for (int k = 0; k < kMaxTaskAux; k++) d.aux[k] = t->aux[k];
+  int need_sub = 0;
+  for (int k = 0; k < 16; k++) {
+    d.sensor_id[k] = t->sensor_id[k]; d.iaux[k] = t->iaux[k];
+    const int s = t->sensor_id[k];
+    if (s < 0 || s >= e->nsensor) { if (s >= e->nsensor) return fail("ps_set_task: sensor id out of range"); continue; }
+    if (e->sensor_type[s] == PS_SENS_SUBTREELINVEL || e->sensor_type[s] == PS_SENS_SUBTREEANGMOM) need_sub = 1;
+  }
+  for (int k = 0; k < 4; k++) d.trace_sensor[k] = t->trace_sensor[k];
+  e->task = d; e->have_task = true;
+  e->var->task(e->h_const, d, need_sub);
+  return 0;
+}
+
+int ps_set_state(PsEngine* e, const double* state, const double* mocap, const double* userdata, double time) {
+  (void)userdata;   // none of the supported tasks read userdata on the planning path
+  if (!e || !e->have_model) return fail("ps_set_state: no model");
+  e->var->plan(e->h_const, state, e->ns, mocap, e->nmocap, time, nullptr, 0, 0, 0);
+  return 0;
+}
+
+int ps_set_nominal(PsEngine* e, const double* times, const double* knots, int P, int interpolation) {
+  if (!e || !e->have_model) return fail("ps_set_nominal: no model");
+  if (P < 1 || P > 36) return fail("ps_set_nominal: spline points must be in [1, 36]");
+  CU(cudaSetDevice(e->device));
+  const double nan = std::nan("");
+  e->var->plan(e->h_const, nullptr, 0, nullptr, 0, nan, times, P, interpolation, 0);
+  e->P = P; e->interp = interpolation; e->nelem = P * e->nu;
+  if (!e->d_nominal) CU(cudaMalloc(&e->d_nominal, sizeof(double) * 36 * 32));
+  CU(cudaMemcpyAsync(e->d_nominal, knots, sizeof(double) * e->nelem, cudaMemcpyHostToDevice, e->stream));
+  CU(cudaStreamSynchronize(e->stream));     // knots is caller-owned pageable memory
+  return 0;
+}
+
+int ps_set_noise(PsEngine* e, const double* z, const unsigned char* use_std2, int N) {
+  if (!e || !e->have_model) return fail("ps_set_noise: no model");
+  CU(cudaSetDevice(e->device));
+  if (!z) { e->have_noise = false; return 0; }
+  if (e->P <= 0) return fail("ps_set_noise: set the nominal plan first");
+  const size_t need = (size_t)N * e->nelem;
+  if (ensure(&e->d_z, &e->z_cap, need)) return -1;
+  CU(cudaMemcpy(e->d_z, z, need * sizeof(double), cudaMemcpyHostToDevice));
+  if (e->d_std2) { cudaFree(e->d_std2); e->d_std2 = nullptr; }
+  if (use_std2) { CU(cudaMalloc(&e->d_std2, N)); CU(cudaMemcpy(e->d_std2, use_std2, N, cudaMemcpyHostToDevice)); }
+  e->have_noise = true;
+  return 0;
+}
+
+int ps_set_seed(PsEngine* e, unsigned long long seed) { if (!e) return fail("null engine"); e->seed = seed; e->iteration = 0; return 0; }
+
+static int alloc_samples(PsEngine* e, int N) {
+  const int stride = (N + 31) & ~31;
+  if (stride > e->cap) {
+    if (e->d_returns) cudaFree(e->d_returns); if (e->d_failure) cudaFree(e->d_failure); if (e->d_blockmin) cudaFree(e->d_blockmin);
+    e->d_returns = nullptr; e->d_failure = nullptr; e->d_blockmin = nullptr; e->cap = 0;
+    CU(cudaMalloc(&e->d_returns, sizeof(double) * stride));
+    CU(cudaMalloc(&e->d_failure, stride));
+    CU(cudaMalloc(&e->d_blockmin, sizeof(MinLoc) * (stride / 32 + 1)));
+    e->cap = stride;
+  }
+  if (ensure(&e->d_knots, &e->knots_cap, (size_t)stride * e->nelem)) return -1;
+  e->stride = stride;
+  return 0;
+}
+
+static int run_iteration(PsEngine* e, int N, int H, double sigma0, double sigma1, int sample_offset, bool writeback) {
+  if (!e || !e->have_model || !e->have_task) return fail("ps_rollouts: model and task must be set");
+  if (e->P <= 0) return fail("ps_rollouts: nominal plan not set");
+  if (N < 1 || H < 1) return fail("ps_rollouts: N and H must be positive");
+  if (H > 512) return fail("ps_rollouts: horizon exceeds kMaxTrajectoryHorizon (512)");
+  CU(cudaSetDevice(e->device));
+  if (alloc_samples(e, N)) return -1;
+  e->N = N; e->H = H; e->offset = sample_offset; e->sigma0 = sigma0; e->sigma1 = sigma1;
+  e->var->plan(e->h_const, nullptr, 0, nullptr, 0, std::nan(""), nullptr, 0, 0, H);
+  CU(cudaMemcpyAsync(e->d_const, e->h_const, e->var->const_bytes, cudaMemcpyHostToDevice, e->stream));
+  const int stride = e->stride, nelem = e->nelem;
+  if (writeback) {
+    const size_t ns = e->ns, nr = e->task.num_residual, nt = 3 * (size_t)e->task.num_trace;
+    double** ptr[6] = {&e->wb.states, &e->wb.actions, &e->wb.residual, &e->wb.costs, &e->wb.times, &e->wb.trace};
+    const size_t need[6] = {H * ns * stride, (size_t)H * e->nu * stride, H * nr * stride, (size_t)H * stride, (size_t)H * stride, H * (nt ? nt : 1) * stride};
+    for (int k = 0; k < 6; k++) { if (ensure(ptr[k], &e->wb_cap[k], need[k])) return -1; CU(cudaMemsetAsync(*ptr[k], 0, need[k] * sizeof(double), e->stream)); }
+  }
+  CU(cudaEventRecord(e->ev[0], e->stream));
+  dim3 pg((N + 255) / 256, nelem);
+  perturb_kernel<<<pg, 256, 0, e->stream>>>(e->d_nominal, e->d_ctrlrange, N, nelem, e->nu, sigma0, sigma1, e->seed, e->iteration,
+                                            (long long)sample_offset, e->have_noise ? e->d_z : nullptr,
+                                            e->have_noise ? e->d_std2 : nullptr, e->d_knots, stride);
+  CU(cudaEventRecord(e->ev[1], e->stream));
+  e->nblocks = (N + e->var->block - 1) / e->var->block;
+  e->var->launch(e->stream, e->d_const, e->d_knots, stride, 0, N, (long long)sample_offset, e->d_returns, e->d_failure, e->d_blockmin, e->wb, writeback);
+  CU(cudaEventRecord(e->ev[2], e->stream));
+  argmin_kernel<<<1, 256, 0, e->stream>>>(e->d_blockmin, e->nblocks, e->d_returns, e->d_knots, stride, nelem, (long long)sample_offset, e->d_record);
+  CU(cudaEventRecord(e->ev[3], e->stream));
+  CU(cudaGetLastError());
+  e->launches += 3; e->iteration++;
+  e->wb_valid = writeback; e->wb_N = N; e->wb_H = H;
+  return 0;
+}
+
+int ps_rollouts_async(PsEngine* e, int N, int H, double sigma0, double sigma1, int sample_offset) {
+  return run_iteration(e, N, H, sigma0, sigma1, sample_offset, false);
+}
+
+static int fetch_record(PsEngine* e, int* winner, double* winner_return, double* nominal_return) {
+  CU(cudaMemcpyAsync(e->h_record, e->d_record, sizeof(double) * (3 + e->nelem), cudaMemcpyDeviceToHost, e->stream));
+  CU(cudaStreamSynchronize(e->stream));
+  if (winner) *winner = (int)((long long)e->h_record[1] - e->offset);
+  if (winner_return) *winner_return = e->h_record[0];
+  if (nominal_return) *nominal_return = e->h_record[2];
+  return 0;
+}
+
+int ps_rollouts(PsEngine* e, int N, int H, double sigma0, double sigma1, int sample_offset, int* winner, double* winner_return,
+                double* nominal_return) {
+  if (run_iteration(e, N, H, sigma0, sigma1, sample_offset, false)) return -1;
+  return fetch_record(e, winner, winner_return, nominal_return);
+}
+
+/* same as ps_rollouts but with full trajectory writeback of every sample (parity tests, traces) */
+int ps_rollouts_writeback(PsEngine* e, int N, int H, double sigma0, double sigma1, int sample_offset, int* winner,
+                          double* winner_return, double* nominal_return) {
+  if (run_iteration(e, N, H, sigma0, sigma1, sample_offset, true)) return -1;
+  return fetch_record(e, winner, winner_return, nominal_return);
+}
+
+int ps_get_returns(PsEngine* e, double* total_return, unsigned char* failure) {
+  if (!e || e->N <= 0) return fail("ps_get_returns: nothing rolled out");
+  CU(cudaSetDevice(e->device));
+  CU(cudaStreamSynchronize(e->stream));
+  if (total_return) CU(cudaMemcpy(total_return, e->d_returns, sizeof(double) * e->N, cudaMemcpyDeviceToHost));
+  if (failure) CU(cudaMemcpy(failure, e->d_failure, e->N, cudaMemcpyDeviceToHost));
+  return 0;
+}
+
+static int gather_column(PsEngine* e, const double* src, int rows, int i, double* out) {
+  if (!out || rows == 0) return 0;
+  if (ensure(&e->d_scratch, &e->scratch_cap, rows)) return -1;
+  gather_column_kernel<<<(rows + 127) / 128, 128, 0, e->stream>>>(src, rows, e->stride, i, e->d_scratch);
+  e->launches++;
+  CU(cudaMemcpyAsync(out, e->d_scratch, sizeof(double) * rows, cudaMemcpyDeviceToHost, e->stream));
+  CU(cudaStreamSynchronize(e->stream));
+  return 0;
+}
+
+int ps_get_knots(PsEngine* e, int sample, double* knots) {
+  if (!e || e->N <= 0 || sample < 0 || sample >= e->N) return fail("ps_get_knots: bad sample");
+  CU(cudaSetDevice(e->device));
+  return gather_column(e, e->d_knots, e->nelem, sample, knots);
+}
+
+int ps_get_trajectory(PsEngine* e, int sample, double* states, double* actions, double* times, double* residual, double* costs,
+                      double* trace, double* total_return, int* failure) {
+  if (!e || e->N <= 0 || sample < 0 || sample >= e->N) return fail("ps_get_trajectory: bad sample");
+  CU(cudaSetDevice(e->device));
+  const int H = e->H, stride = e->stride;
+  if (!e->wb_valid) {
+    // re-roll just this sample with writeback (candidate knots are still resident)
+    const size_t ns = e->ns, nr = e->task.num_residual, nt = 3 * (size_t)e->task.num_trace;
+    double** ptr[6] = {&e->wb.states, &e->wb.actions, &e->wb.residual, &e->wb.costs, &e->wb.times, &e->wb.trace};
+    const size_t need[6] = {H * ns * stride, (size_t)H * e->nu * stride, H * nr * stride, (size_t)H * stride, (size_t)H * stride, H * (nt ? nt : 1) * stride};
+    for (int k = 0; k < 6; k++) if (ensure(ptr[k], &e->wb_cap[k], need[k])) return -1;
+    // zero this sample's column lazily: a failed rollout leaves later steps untouched, so clear all
+    for (int k = 0; k < 6; k++) CU(cudaMemsetAsync(*ptr[k], 0, need[k] * sizeof(double), e->stream));
+    MinLoc* tmp = e->d_blockmin + (e->cap / 32);   // spare slot
+    e->var->launch(e->stream, e->d_const, e->d_knots, stride, sample, 1, e->offset, e->d_returns, e->d_failure, tmp, e->wb, true);
+    e->launches++;
+    CU(cudaGetLastError());
+  }
+  const int ns = e->ns, nr = e->task.num_residual, nt = 3 * e->task.num_trace;
+  if (gather_column(e, e->wb.states, H * ns, sample, states)) return -1;
+  if (gather_column(e, e->wb.actions, H * e->nu, sample, actions)) return -1;
+  if (gather_column(e, e->wb.times, H, sample, times)) return -1;
+  if (gather_column(e, e->wb.residual, H * nr, sample, residual)) return -1;
+  if (gather_column(e, e->wb.costs, H, sample, costs)) return -1;
+  if (nt && gather_column(e, e->wb.trace, H * nt, sample, trace)) return -1;
+  CU(cudaStreamSynchronize(e->stream));
+  if (total_return) CU(cudaMemcpy(total_return, e->d_returns + sample, sizeof(double), cudaMemcpyDeviceToHost));
+  if (failure) { unsigned char f = 0; CU(cudaMemcpy(&f, e->d_failure + sample, 1, cudaMemcpyDeviceToHost)); *failure = f & 1; }
+  return 0;
+}
+
+static int transpose_out(PsEngine* e, const double* src, int rows, double* out) {
+  if (!out || rows == 0) return 0;
+  const size_t total = (size_t)rows * e->N;
+  if (ensure(&e->d_scratch, &e->scratch_cap, total)) return -1;
+  dim3 grid((e->N + 31) / 32, (rows + 31) / 32), block(32, 8);
+  transpose_kernel<<<grid, block, 0, e->stream>>>(src, rows, e->stride, e->N, e->d_scratch);
+  e->launches++;
+  CU(cudaMemcpyAsync(out, e->d_scratch, total * sizeof(double), cudaMemcpyDeviceToHost, e->stream));
+  CU(cudaStreamSynchronize(e->stream));
+  return 0;
+}
+
+int ps_get_all_trajectories(PsEngine* e, double* states, double* actions, double* residual, double* costs) {
+  if (!e || !e->wb_valid) return fail("ps_get_all_trajectories: call ps_rollouts_writeback first");
+  CU(cudaSetDevice(e->device));
+  const int H = e->H;
+  if (transpose_out(e, e->wb.states, H * e->ns, states)) return -1;
+  if (transpose_out(e, e->wb.actions, H * e->nu, actions)) return -1;
+  if (transpose_out(e, e->wb.residual, H * e->task.num_residual, residual)) return -1;
+  if (transpose_out(e, e->wb.costs, H, costs)) return -1;
+  return 0;
+}
+
+int ps_last_kernel_ms(PsEngine* e, float* perturb_ms, float* rollout_ms, float* reduce_ms) {
+  if (!e) return fail("null engine");
+  CU(cudaSetDevice(e->device));
+  CU(cudaEventSynchronize(e->ev[3]));
+  if (perturb_ms) CU(cudaEventElapsedTime(perturb_ms, e->ev[0], e->ev[1]));
+  if (rollout_ms) CU(cudaEventElapsedTime(rollout_ms, e->ev[1], e->ev[2]));
+  if (reduce_ms) CU(cudaEventElapsedTime(reduce_ms, e->ev[2], e->ev[3]));
+  return 0;
+}
+
+int ps_kernel_launch_count(PsEngine* e, long long* launches) { if (!e) return fail("null engine"); *launches = e->launches; return 0; }
+
+int ps_winner_record_device(PsEngine* e, void** device_ptr, int* count) {
+  if (!e) return fail("null engine");
+  if (device_ptr) *device_ptr = e->d_record;
+  if (count) *count = 3 + e->nelem;
+  return 0;
+}
+
+int ps_stream(PsEngine* e, void** stream) { if (!e) return fail("null engine"); *stream = (void*)e->stream; return 0; }
+
+int ps_variant(PsEngine* e, char* out, int cap) {
+  if (!e || !e->var) return fail("no model"); std::snprintf(out, cap, "%s", e->var->name); return 0;
+}
+
+}  // extern "C"

@@ -1,0 +1,169 @@
+// Device-side model / per-rollout data layout of the B200 Predictive Sampling rollout engine.
+//
+// The reference planner hands MuJoCo an mjModel + one mjData per worker thread
+// (mjpc/planners/planner.cc:23-33, mjpc/planners/sampling/planner.cc:151-187).  Here the model
+// constants live in ONE fixed-capacity POD (DevModel<T>) that every thread block pulls into
+// shared memory with a single TMA bulk copy, and the per-rollout working set (RolloutData<T>) is a
+// fixed-capacity struct private to the thread that owns the rollout.  Capacities are compile
+// time (Traits) so every array has a constant stride; actual sizes are runtime fields.
+#pragma once
+#include <cmath>
+#include <cstdint>
+
+#if defined(__CUDACC__)
+#define PS_HD __host__ __device__ __forceinline__
+#define PS_FN __host__ __device__
+#else
+#define PS_HD inline
+#define PS_FN inline
+#endif
+
+namespace ps {
+
+constexpr double kMinVal = 1e-15;   // mjMINVAL
+constexpr double kMaxVal = 1e10;    // mjMAXVAL
+constexpr double kPi = 3.14159265358979323846;
+constexpr int kMaxTerms = 16;       // cost terms carried on device (the six tasks use <= 9)
+constexpr int kMaxResidual = 48;    // quadruped: 42
+constexpr int kMaxTaskParam = 16;
+constexpr int kMaxTaskAux = 96;
+
+// compile-time capacities of one engine instantiation
+template <int NQ_, int NV_, int NU_, int NA_, int NBODY_, int NJNT_, int NGEOM_, int NSITE_,
+          int NMOCAP_, int NPAIR_, int MAXCON_, int MAXEFC_, int NSENSOR_, bool ELLIPTIC_>
+struct Traits {
+  static constexpr int NQ = NQ_, NV = NV_, NU = NU_, NA = (NA_ > 0 ? NA_ : 1), NBODY = NBODY_,
+                       NJNT = NJNT_, NGEOM = NGEOM_, NSITE = (NSITE_ > 0 ? NSITE_ : 1),
+                       NMOCAP = (NMOCAP_ > 0 ? NMOCAP_ : 1), NPAIR = (NPAIR_ > 0 ? NPAIR_ : 1),
+                       MAXCON = (MAXCON_ > 0 ? MAXCON_ : 1), MAXEFC = (MAXEFC_ > 0 ? MAXEFC_ : 1),
+                       NSENSOR = (NSENSOR_ > 0 ? NSENSOR_ : 1);
+  static constexpr bool ELLIPTIC = ELLIPTIC_;
+  static constexpr int NCONEH = ELLIPTIC_ ? MAXCON : 1;
+};
+
+enum { JNT_FREE = 0, JNT_BALL = 1, JNT_SLIDE = 2, JNT_HINGE = 3 };
+enum { GEOM_PLANE = 0, GEOM_SPHERE = 2, GEOM_CAPSULE = 3, GEOM_CYLINDER = 5, GEOM_BOX = 6 };
+enum { INT_EULER = 0, INT_RK4 = 1, INT_IMPLICIT = 2, INT_IMPLICITFAST = 3 };
+enum { CONE_PYRAMIDAL = 0, CONE_ELLIPTIC = 1 };
+enum { DSBL_CONSTRAINT = 1, DSBL_FRICTIONLOSS = 4, DSBL_LIMIT = 8, DSBL_CONTACT = 16, DSBL_PASSIVE = 32,
+       DSBL_GRAVITY = 64, DSBL_CLAMPCTRL = 128, DSBL_WARMSTART = 256, DSBL_FILTERPARENT = 512,
+       DSBL_ACTUATION = 1024, DSBL_REFSAFE = 2048, DSBL_EULERDAMP = 16384 };
+enum { DYN_NONE = 0, DYN_INTEGRATOR = 1, DYN_FILTER = 2, DYN_FILTEREXACT = 3 };
+enum { SENS_JOINTPOS = 8, SENS_JOINTVEL = 9, SENS_FRAMEPOS = 25, SENS_FRAMEXAXIS = 27, SENS_FRAMEYAXIS = 28,
+       SENS_FRAMEZAXIS = 29, SENS_FRAMELINVEL = 30, SENS_FRAMEANGVEL = 31, SENS_SUBTREECOM = 34,
+       SENS_SUBTREELINVEL = 35, SENS_SUBTREEANGMOM = 36 };
+enum { OBJ_BODY = 1, OBJ_XBODY = 2, OBJ_GEOM = 5, OBJ_SITE = 6 };
+enum { EFC_FRICTION_DOF = 0, EFC_LIMIT_JOINT, EFC_CONTACT_FRICTIONLESS, EFC_CONTACT_PYRAMIDAL, EFC_CONTACT_ELLIPTIC };
+enum { ST_SATISFIED = 0, ST_QUADRATIC, ST_LINEARNEG, ST_LINEARPOS, ST_CONE };
+enum { SPLINE_ZERO = 0, SPLINE_LINEAR = 1, SPLINE_CUBIC = 2 };
+
+// ------------------------------------------------------------------------------------------
+// Model constants (shared memory resident).  16-byte aligned, size a multiple of 16 so it can be
+// moved with cp.async.bulk.
+template <class T>
+struct alignas(16) DevModel {
+  // options
+  double timestep, impratio, tolerance, ls_tolerance, density, viscosity, meaninertia;
+  double gravity[3], wind[3];
+  int integrator, cone, iterations, ls_iterations, disableflags;
+  int nq, nv, nu, na, nbody, njnt, ngeom, nsite, nmocap, nsensor, npair;
+  int any_damping;     // some dof has damping > 0 (Euler implicit-damping branch)
+  int need_subtreevel; // a subtreelinvel / subtreeangmom sensor is read by the task
+  int pad_;
+  double qpos0[T::NQ], qpos_spring[T::NQ];
+  // bodies
+  int body_parentid[T::NBODY], body_rootid[T::NBODY], body_jntnum[T::NBODY], body_jntadr[T::NBODY],
+      body_dofnum[T::NBODY], body_dofadr[T::NBODY], body_mocapid[T::NBODY], body_weldid[T::NBODY];
+  double body_pos[T::NBODY * 3], body_quat[T::NBODY * 4], body_ipos[T::NBODY * 3], body_iquat[T::NBODY * 4],
+      body_mass[T::NBODY], body_subtreemass[T::NBODY], body_inertia[T::NBODY * 3], body_invweight0[T::NBODY * 2];
+  // joints
+  int jnt_type[T::NJNT], jnt_qposadr[T::NJNT], jnt_dofadr[T::NJNT], jnt_bodyid[T::NJNT], jnt_limited[T::NJNT];
+  double jnt_pos[T::NJNT * 3], jnt_axis[T::NJNT * 3], jnt_stiffness[T::NJNT], jnt_range[T::NJNT * 2],
+      jnt_margin[T::NJNT], jnt_solref[T::NJNT * 2], jnt_solimp[T::NJNT * 5];
+  // dofs
+  int dof_bodyid[T::NV], dof_jntid[T::NV], dof_parentid[T::NV];
+  double dof_armature[T::NV], dof_damping[T::NV], dof_frictionloss[T::NV], dof_solref[T::NV * 2],
+      dof_solimp[T::NV * 5], dof_invweight0[T::NV];
+  // geoms
+  int geom_type[T::NGEOM], geom_condim[T::NGEOM], geom_bodyid[T::NGEOM], geom_priority[T::NGEOM],
+      geom_group[T::NGEOM], geom_used[T::NGEOM];
+  double geom_size[T::NGEOM * 3], geom_pos[T::NGEOM * 3], geom_quat[T::NGEOM * 4], geom_friction[T::NGEOM * 3],
+      geom_solmix[T::NGEOM], geom_solref[T::NGEOM * 2], geom_solimp[T::NGEOM * 5], geom_margin[T::NGEOM],
+      geom_gap[T::NGEOM], geom_rbound[T::NGEOM];
+  // statically filtered collision candidates, in the order mj_collision would visit them
+  int pair_geom1[T::NPAIR], pair_geom2[T::NPAIR];
+  // sites
+  int site_bodyid[T::NSITE];
+  double site_pos[T::NSITE * 3], site_quat[T::NSITE * 4];
+  // actuators (joint transmission)
+  int act_dyntype[T::NU], act_gaintype[T::NU], act_biastype[T::NU], act_jntid[T::NU], act_actadr[T::NU],
+      act_ctrllimited[T::NU], act_forcelimited[T::NU], act_actlimited[T::NU];
+  double act_dynprm[T::NU * 3], act_gainprm[T::NU * 3], act_biasprm[T::NU * 3], act_ctrlrange[T::NU * 2],
+      act_forcerange[T::NU * 2], act_actrange[T::NU * 2], act_gear[T::NU];
+  // sensors the residuals may read
+  int sensor_type[T::NSENSOR], sensor_objtype[T::NSENSOR], sensor_objid[T::NSENSOR];
+};
+
+// Cost specification + residual snapshot (what Task::Residual()/BaseResidualFn::Update hands the
+// planner every iteration, mjpc/task.cc:112-128), trimmed to device capacities.
+struct alignas(16) DevTask {
+  int task_id, num_residual, num_term, num_trace;
+  int dim_norm_residual[kMaxTerms], num_norm_parameter[kMaxTerms], norm[kMaxTerms];
+  int sensor_id[16];     // SensorByName resolved on the host (mjpc/utilities.cc:166-175)
+  int trace_sensor[4];
+  int iaux[16];
+  double weight[kMaxTerms], norm_parameter[2 * kMaxTerms];
+  double risk;
+  double parameters[kMaxTaskParam];
+  double aux[kMaxTaskAux];
+};
+
+// Per-iteration inputs shared by all rollouts.
+template <class T>
+struct alignas(16) DevPlan {
+  double state[T::NQ + T::NV + T::NA];
+  double mocap[7 * T::NMOCAP];
+  double time;
+  double spline_times[36];   // kMaxSplinePoints-ish cap of the reference GUI (sampling/planner.h:36)
+  int num_spline_points, interpolation, horizon, pad_;
+};
+
+struct Contact {
+  double dist, pos[3], frame[9], includemargin, friction[5], solref[2], solimp[5], mu;
+  int dim, geom1, geom2, efc_address;
+};
+
+// Working set of ONE rollout (thread-private).
+template <class T>
+struct RolloutData {
+  double time;
+  double qpos[T::NQ], qvel[T::NV], act[T::NA], ctrl[T::NU], qacc[T::NV], qacc_warmstart[T::NV], act_dot[T::NA];
+  double mocap_pos[3 * T::NMOCAP], mocap_quat[4 * T::NMOCAP];
+  // position stage
+  double xpos[3 * T::NBODY], xquat[4 * T::NBODY], xmat[9 * T::NBODY], xipos[3 * T::NBODY], ximat[9 * T::NBODY];
+  double xanchor[3 * T::NJNT], xaxis[3 * T::NJNT];
+  double geom_xpos[3 * T::NGEOM], geom_xmat[9 * T::NGEOM];
+  double site_xpos[3 * T::NSITE], site_xmat[9 * T::NSITE];
+  double subtree_com[3 * T::NBODY], cinert[10 * T::NBODY], crb[10 * T::NBODY], cdof[6 * T::NV];
+  double qM[T::NV * T::NV], qLD[T::NV * T::NV], qLDiagInv[T::NV];
+  double actuator_length[T::NU], actuator_velocity[T::NU], actuator_force[T::NU];
+  // velocity stage
+  double cvel[6 * T::NBODY], cdof_dot[6 * T::NV];
+  double qfrc_bias[T::NV], qfrc_passive[T::NV], qfrc_actuator[T::NV], qfrc_smooth[T::NV], qacc_smooth[T::NV],
+      qfrc_constraint[T::NV];
+  double subtree_linvel[3 * T::NBODY], subtree_angmom[3 * T::NBODY];
+  // constraints
+  int ncon, nefc, solver_iter, warning;
+  Contact contact[T::MAXCON];
+  double coneH[T::NCONEH * 36];
+  int efc_type[T::MAXEFC], efc_id[T::MAXEFC], efc_state[T::MAXEFC];
+  double efc_J[T::MAXEFC * T::NV], efc_pos[T::MAXEFC], efc_margin[T::MAXEFC], efc_frictionloss[T::MAXEFC],
+      efc_D[T::MAXEFC], efc_R[T::MAXEFC], efc_aref[T::MAXEFC], efc_force[T::MAXEFC], efc_KBI[3 * T::MAXEFC];
+  // solver scratch
+  double sv_Ma[T::NV], sv_grad[T::NV], sv_search[T::NV], sv_Mv[T::NV], sv_H[T::NV * T::NV];
+  double sv_Jaref[T::MAXEFC], sv_Jv[T::MAXEFC];
+};
+
+enum { WARN_BADQPOS = 1, WARN_BADQVEL = 2, WARN_BADQACC = 4, WARN_BADCTRL = 8, WARN_CAPACITY = 16 };
+
+}  // namespace ps
