@@ -92,6 +92,13 @@ int ps_stream(PsEngine* e, void** stream);
 /* ps_rollouts without the final device->host read: results stay in the winner record */
 int ps_rollouts_async(PsEngine* e, int N, int H, double sigma0, double sigma1, int sample_offset);
 int ps_name(char* out, int cap);
+/* engine instantiation chosen for the model ("tiny" / "planar" / "legged") */
+int ps_variant(PsEngine* e, char* out, int cap);
+/* ps_rollouts with full per-step writeback of every sample (parity tests, traces) */
+int ps_rollouts_writeback(PsEngine* e, int N, int H, double sigma0, double sigma1, int sample_offset,
+                          int* winner, double* winner_return, double* nominal_return);
+/* measured FP64 FMA throughput of the device (TFLOP/s): roofline denominator of the rollout kernel */
+int ps_fp64_peak(PsEngine* e, int reps, double* tflops);
 
 #ifdef __cplusplus
 }

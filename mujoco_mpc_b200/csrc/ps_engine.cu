@@ -10,7 +10,8 @@
 #include <string>
 #include <vector>
 #include "../../include/ps_engine.h"
-#include "ps_kernels.cuh"
+#include "ps_variant.h"
+#include "ps_kernels_aux.cuh"
 
 using namespace ps;
 
@@ -19,149 +20,7 @@ static int fail(const std::string& s) { g_error = s; return -1; }
 #define CU(call)                                                                                   \
   do { cudaError_t e_ = (call); if (e_ != cudaSuccess) return fail(std::string(#call) + ": " + cudaGetErrorString(e_)); } while (0)
 
-// ---------------------------------------------------------------- engine instantiations
-//                        NQ NV NU NA NBODY NJNT NGEOM NSITE NMOCAP NPAIR MAXCON MAXEFC NSENSOR ELLIPTIC
-typedef Traits<2, 2, 2, 0, 4, 2, 8, 2, 1, 0, 0, 4, 12, false> TinyT;          // particle, cartpole, acrobot
-typedef Traits<9, 9, 6, 5, 9, 9, 12, 4, 1, 12, 10, 48, 16, false> PlanarT;    // swimmer, walker
-typedef Traits<19, 18, 12, 0, 16, 13, 40, 24, 2, 48, 16, 96, 24, true> LeggedT;  // quadruped (free joint, elliptic cones)
-
-struct PairList { std::vector<int> g1, g2; int unsupported = 0; };
-
-static int weld_body(const PsModel* m, int b) { while (b > 0 && m->body_dofnum[b] == 0) b = m->body_parentid[b]; return b; }
-
-static bool pair_supported(int t1, int t2) {
-  if (t1 == PS_GEOM_PLANE) return t2 == PS_GEOM_SPHERE || t2 == PS_GEOM_CAPSULE || t2 == PS_GEOM_CYLINDER || t2 == PS_GEOM_BOX;
-  if (t1 == PS_GEOM_SPHERE) return t2 == PS_GEOM_SPHERE || t2 == PS_GEOM_CAPSULE;
-  return t1 == PS_GEOM_CAPSULE && t2 == PS_GEOM_CAPSULE;
-}
-
-// static part of the collision filter (contype/conaffinity, same/welded body, parent-child)
-static PairList static_pairs(const PsModel* m) {
-  PairList pl;
-  if (m->opt_disableflags & (PS_DSBL_CONTACT | PS_DSBL_CONSTRAINT)) return pl;
-  for (int ga = 0; ga < m->ngeom; ga++)
-    for (int gb = ga + 1; gb < m->ngeom; gb++) {
-      const int b1 = m->geom_bodyid[ga], b2 = m->geom_bodyid[gb];
-      if (b1 == b2) continue;
-      if (!((m->geom_contype[ga] & m->geom_conaffinity[gb]) || (m->geom_contype[gb] & m->geom_conaffinity[ga]))) continue;
-      const int w1 = weld_body(m, b1), w2 = weld_body(m, b2);
-      if (w1 == w2) continue;
-      if (!(m->opt_disableflags & PS_DSBL_FILTERPARENT) && w1 != 0 && w2 != 0)
-        if (weld_body(m, m->body_parentid[w1]) == w2 || weld_body(m, m->body_parentid[w2]) == w1) continue;
-      int g1 = ga, g2 = gb;
-      if (m->geom_type[g1] > m->geom_type[g2]) { int t = g1; g1 = g2; g2 = t; }
-      if (m->geom_type[g1] == PS_GEOM_PLANE && m->geom_type[g2] == PS_GEOM_PLANE) continue;
-      if (!pair_supported(m->geom_type[g1], m->geom_type[g2])) { pl.unsupported++; continue; }
-      pl.g1.push_back(g1); pl.g2.push_back(g2);
-    }
-  return pl;
-}
-
-template <class T>
-static int fill_model(const PsModel* s, const PairList& pl, void* out, std::string* why) {
-  DevModel<T>& m = reinterpret_cast<Constants<T>*>(out)->m;
-  std::memset(&m, 0, sizeof(m));
-#define CAP(field, cap) if (s->field > cap) { *why = std::string(#field) + " exceeds capacity"; return -1; }
-  CAP(nq, T::NQ) CAP(nv, T::NV) CAP(nu, T::NU) CAP(na, T::NA) CAP(nbody, T::NBODY) CAP(njnt, T::NJNT) CAP(ngeom, T::NGEOM)
-  CAP(nsite, T::NSITE) CAP(nmocap, T::NMOCAP) CAP(nsensor, T::NSENSOR)
-#undef CAP
-  if ((int)pl.g1.size() > T::NPAIR) { *why = "collision pairs exceed capacity"; return -1; }
-  if (s->opt_cone == PS_CONE_ELLIPTIC && !T::ELLIPTIC && !pl.g1.empty()) { *why = "elliptic cones not in this instantiation"; return -1; }
-  m.timestep = s->opt_timestep; m.impratio = s->opt_impratio; m.tolerance = s->opt_tolerance; m.ls_tolerance = s->opt_ls_tolerance;
-  m.density = s->opt_density; m.viscosity = s->opt_viscosity; m.meaninertia = s->stat_meaninertia;
-  for (int k = 0; k < 3; k++) { m.gravity[k] = s->opt_gravity[k]; m.wind[k] = s->opt_wind[k]; }
-  m.integrator = s->opt_integrator; m.cone = s->opt_cone; m.iterations = s->opt_iterations; m.ls_iterations = s->opt_ls_iterations;
-  m.disableflags = s->opt_disableflags;
-  m.nq = s->nq; m.nv = s->nv; m.nu = s->nu; m.na = s->na; m.nbody = s->nbody; m.njnt = s->njnt; m.ngeom = s->ngeom;
-  m.nsite = s->nsite; m.nmocap = s->nmocap; m.nsensor = s->nsensor; m.npair = (int)pl.g1.size();
-#define CPY(dst, src, n) for (int i_ = 0; i_ < (n); i_++) m.dst[i_] = s->src[i_];
-  CPY(qpos0, qpos0, s->nq) CPY(qpos_spring, qpos_spring, s->nq)
-  CPY(body_parentid, body_parentid, s->nbody) CPY(body_rootid, body_rootid, s->nbody) CPY(body_jntnum, body_jntnum, s->nbody)
-  CPY(body_jntadr, body_jntadr, s->nbody) CPY(body_dofnum, body_dofnum, s->nbody) CPY(body_dofadr, body_dofadr, s->nbody)
-  CPY(body_mocapid, body_mocapid, s->nbody)
-  for (int b = 0; b < s->nbody; b++) m.body_weldid[b] = weld_body(s, b);
-  CPY(body_pos, body_pos, 3 * s->nbody) CPY(body_quat, body_quat, 4 * s->nbody) CPY(body_ipos, body_ipos, 3 * s->nbody)
-  CPY(body_iquat, body_iquat, 4 * s->nbody) CPY(body_mass, body_mass, s->nbody) CPY(body_subtreemass, body_subtreemass, s->nbody)
-  CPY(body_inertia, body_inertia, 3 * s->nbody) CPY(body_invweight0, body_invweight0, 2 * s->nbody)
-  CPY(jnt_type, jnt_type, s->njnt) CPY(jnt_qposadr, jnt_qposadr, s->njnt) CPY(jnt_dofadr, jnt_dofadr, s->njnt)
-  CPY(jnt_bodyid, jnt_bodyid, s->njnt) CPY(jnt_limited, jnt_limited, s->njnt) CPY(jnt_pos, jnt_pos, 3 * s->njnt)
-  CPY(jnt_axis, jnt_axis, 3 * s->njnt) CPY(jnt_stiffness, jnt_stiffness, s->njnt) CPY(jnt_range, jnt_range, 2 * s->njnt)
-  CPY(jnt_margin, jnt_margin, s->njnt) CPY(jnt_solref, jnt_solref, 2 * s->njnt) CPY(jnt_solimp, jnt_solimp, 5 * s->njnt)
-  CPY(dof_bodyid, dof_bodyid, s->nv) CPY(dof_jntid, dof_jntid, s->nv) CPY(dof_parentid, dof_parentid, s->nv)
-  CPY(dof_armature, dof_armature, s->nv) CPY(dof_damping, dof_damping, s->nv) CPY(dof_frictionloss, dof_frictionloss, s->nv)
-  CPY(dof_solref, dof_solref, 2 * s->nv) CPY(dof_solimp, dof_solimp, 5 * s->nv) CPY(dof_invweight0, dof_invweight0, s->nv)
-  CPY(geom_type, geom_type, s->ngeom) CPY(geom_condim, geom_condim, s->ngeom) CPY(geom_bodyid, geom_bodyid, s->ngeom)
-  CPY(geom_priority, geom_priority, s->ngeom) CPY(geom_group, geom_group, s->ngeom)
-  CPY(geom_size, geom_size, 3 * s->ngeom) CPY(geom_pos, geom_pos, 3 * s->ngeom) CPY(geom_quat, geom_quat, 4 * s->ngeom)
-  CPY(geom_friction, geom_friction, 3 * s->ngeom) CPY(geom_solmix, geom_solmix, s->ngeom) CPY(geom_solref, geom_solref, 2 * s->ngeom)
-  CPY(geom_solimp, geom_solimp, 5 * s->ngeom) CPY(geom_margin, geom_margin, s->ngeom) CPY(geom_gap, geom_gap, s->ngeom)
-  CPY(geom_rbound, geom_rbound, s->ngeom)
-  CPY(site_bodyid, site_bodyid, s->nsite) CPY(site_pos, site_pos, 3 * s->nsite) CPY(site_quat, site_quat, 4 * s->nsite)
-  CPY(act_dyntype, actuator_dyntype, s->nu) CPY(act_gaintype, actuator_gaintype, s->nu) CPY(act_biastype, actuator_biastype, s->nu)
-  CPY(act_actadr, actuator_actadr, s->nu) CPY(act_ctrllimited, actuator_ctrllimited, s->nu)
-  CPY(act_forcelimited, actuator_forcelimited, s->nu) CPY(act_actlimited, actuator_actlimited, s->nu)
-  CPY(act_dynprm, actuator_dynprm, 3 * s->nu) CPY(act_gainprm, actuator_gainprm, 3 * s->nu) CPY(act_biasprm, actuator_biasprm, 3 * s->nu)
-  CPY(act_ctrlrange, actuator_ctrlrange, 2 * s->nu) CPY(act_forcerange, actuator_forcerange, 2 * s->nu)
-  CPY(act_actrange, actuator_actrange, 2 * s->nu) CPY(act_gear, actuator_gear, s->nu)
-  CPY(sensor_type, sensor_type, s->nsensor) CPY(sensor_objtype, sensor_objtype, s->nsensor) CPY(sensor_objid, sensor_objid, s->nsensor)
-#undef CPY
-  for (int i = 0; i < s->nu; i++) {
-    if (s->actuator_trntype[i] != PS_TRN_JOINT) { *why = "only joint transmissions are supported"; return -1; }
-    m.act_jntid[i] = s->actuator_trnid[2 * i];
-  }
-  for (int i = 0; i < s->nv; i++) if (s->dof_damping[i] > 0) m.any_damping = 1;
-  for (int p = 0; p < m.npair; p++) { m.pair_geom1[p] = pl.g1[p]; m.pair_geom2[p] = pl.g2[p]; m.geom_used[pl.g1[p]] = 1; m.geom_used[pl.g2[p]] = 1; }
-  for (int i = 0; i < s->nsensor; i++) if (s->sensor_objtype[i] == PS_OBJ_GEOM && s->sensor_objid[i] >= 0) m.geom_used[s->sensor_objid[i]] = 1;
-  if (T::ELLIPTIC) for (int g = 0; g < s->ngeom; g++) m.geom_used[g] = 1;   // legged residual reads geom frames directly
-  return 0;
-}
-
-template <class T>
-static void set_options(void* c, double timestep, int integrator) {
-  DevModel<T>& m = reinterpret_cast<Constants<T>*>(c)->m; m.timestep = timestep; m.integrator = integrator;
-}
-
-template <class T>
-static void set_task(void* c, const DevTask& t, int need_subtreevel) {
-  Constants<T>* k = reinterpret_cast<Constants<T>*>(c); k->t = t; k->m.need_subtreevel = need_subtreevel;
-}
-
-template <class T>
-static int set_plan(void* c, const double* state, int ns, const double* mocap, int nmocap, double time, const double* times,
-                    int P, int interp, int H) {
-  DevPlan<T>& p = reinterpret_cast<Constants<T>*>(c)->p;
-  if (P > 36) return -1;
-  if (state) for (int i = 0; i < ns; i++) p.state[i] = state[i];
-  if (mocap) for (int i = 0; i < 7 * nmocap; i++) p.mocap[i] = mocap[i];
-  if (time == time) p.time = time;
-  if (times) { for (int i = 0; i < P; i++) p.spline_times[i] = times[i]; p.num_spline_points = P; p.interpolation = interp; }
-  if (H > 0) p.horizon = H;
-  return 0;
-}
-
-template <class T, int BLOCK>
-static void launch_rollout(cudaStream_t st, const void* dconst, const double* knots, int stride, int first, int n,
-                           long long offset, double* returns, unsigned char* failure, MinLoc* block_min, Writeback wb, bool writeback) {
-  const int grid = (n + BLOCK - 1) / BLOCK;
-  const Constants<T>* c = reinterpret_cast<const Constants<T>*>(dconst);
-  if (writeback) rollout_kernel<T, BLOCK, true><<<grid, BLOCK, 0, st>>>(c, knots, stride, first, n, offset, returns, failure, block_min, wb);
-  else rollout_kernel<T, BLOCK, false><<<grid, BLOCK, 0, st>>>(c, knots, stride, first, n, offset, returns, failure, block_min, wb);
-}
-
-struct Variant {
-  const char* name; size_t const_bytes; int block;
-  int (*fill)(const PsModel*, const PairList&, void*, std::string*);
-  void (*options)(void*, double, int);
-  void (*task)(void*, const DevTask&, int);
-  int (*plan)(void*, const double*, int, const double*, int, double, const double*, int, int, int);
-  void (*launch)(cudaStream_t, const void*, const double*, int, int, int, long long, double*, unsigned char*, MinLoc*, Writeback, bool);
-};
-template <class T, int BLOCK>
-static Variant make_variant(const char* name) {
-  return Variant{name, sizeof(Constants<T>), BLOCK, fill_model<T>, set_options<T>, set_task<T>, set_plan<T>, launch_rollout<T, BLOCK>};
-}
-static const Variant kVariants[] = {make_variant<TinyT, 128>("tiny"), make_variant<PlanarT, 64>("planar"),
-                                    make_variant<LeggedT, 64>("legged")};
+static const Variant* const kVariants[] = {variant_tiny(), variant_planar(), variant_legged()};
 
 // ---------------------------------------------------------------- engine object
 struct PsEngine_ {
@@ -235,7 +94,8 @@ int ps_set_model(PsEngine* e, const PsModel* m) {
   PairList pl = static_pairs(m);
   std::string why, all;
   const Variant* chosen = nullptr; void* host = nullptr;
-  for (const Variant& v : kVariants) {
+  for (const Variant* vp : kVariants) {
+    const Variant& v = *vp;
     void* h = nullptr; CU(cudaMallocHost(&h, v.const_bytes)); std::memset(h, 0, v.const_bytes);
     if (v.fill(m, pl, h, &why) == 0) { chosen = &v; host = h; break; }
     all += std::string(v.name) + ": " + why + "; "; cudaFreeHost(h);
@@ -248,7 +108,6 @@ int ps_set_model(PsEngine* e, const PsModel* m) {
   e->nq = m->nq; e->nv = m->nv; e->nu = m->nu; e->na = m->na; e->nmocap = m->nmocap; e->nsensor = m->nsensor; e->ns = m->nq + m->nv + m->na;
   e->sensor_type.assign(m->sensor_type, m->sensor_type + m->nsensor);
   e->ctrlrange.assign(m->actuator_ctrlrange, m->actuator_ctrlrange + 2 * m->nu);
-  for (int i = 0; i < m->nu; i++) if (!m->actuator_ctrllimited[i]) { e->ctrlrange[2 * i] = -1e300; e->ctrlrange[2 * i + 1] = 1e300; }
   if (e->d_ctrlrange) cudaFree(e->d_ctrlrange);
   CU(cudaMalloc(&e->d_ctrlrange, sizeof(double) * 2 * (m->nu > 0 ? m->nu : 1)));
   CU(cudaMemcpy(e->d_ctrlrange, e->ctrlrange.data(), sizeof(double) * 2 * m->nu, cudaMemcpyHostToDevice));
@@ -272,28 +131,8 @@ int ps_set_options(PsEngine* e, double timestep, int integrator) {
 
 int ps_set_task(PsEngine* e, const PsTask* t) {
   if (!e || !e->have_model) return fail("ps_set_task: set the model first");
-  if (t->num_term > kMaxTerms) return fail("ps_set_task: more cost terms than the device carries");
-  if (t->num_residual > kMaxResidual) return fail("ps_set_task: residual too long");
-  if (t->num_parameters > kMaxTaskParam) return fail("ps_set_task: too many task parameters");
-  DevTask d; std::memset(&d, 0, sizeof(d));
-  d.task_id = t->task_id; d.num_residual = t->num_residual; d.num_term = t->num_term; d.num_trace = t->num_trace > 4 ? 4 : t->num_trace;
-  int np = 0;
-  for (int k = 0; k < t->num_term; k++) {
-    d.dim_norm_residual[k] = t->dim_norm_residual[k]; d.num_norm_parameter[k] = t->num_norm_parameter[k]; d.norm[k] = t->norm[k];
-    d.weight[k] = t->weight[k]; np += t->num_norm_parameter[k];
-  }
-  for (int k = 0; k < np && k < 2 * kMaxTerms; k++) d.norm_parameter[k] = t->norm_parameter[k];
-  d.risk = t->risk;
-  for (int k = 0; k < t->num_parameters; k++) d.parameters[k] = t->parameters[k];
-  for (int k = 0; k < kMaxTaskAux; k++) d.aux[k] = t->aux[k];
-  int need_sub = 0;
-  for (int k = 0; k < 16; k++) {
-    d.sensor_id[k] = t->sensor_id[k]; d.iaux[k] = t->iaux[k];
-    const int s = t->sensor_id[k];
-    if (s < 0 || s >= e->nsensor) { if (s >= e->nsensor) return fail("ps_set_task: sensor id out of range"); continue; }
-    if (e->sensor_type[s] == PS_SENS_SUBTREELINVEL || e->sensor_type[s] == PS_SENS_SUBTREEANGMOM) need_sub = 1;
-  }
-  for (int k = 0; k < 4; k++) d.trace_sensor[k] = t->trace_sensor[k];
+  DevTask d; int need_sub = 0; std::string why;
+  if (convert_task(t, e->sensor_type.data(), e->nsensor, &d, &need_sub, &why)) return fail("ps_set_task: " + why);
   e->task = d; e->have_task = true;
   e->var->task(e->h_const, d, need_sub);
   return 0;
@@ -505,6 +344,29 @@ int ps_winner_record_device(PsEngine* e, void** device_ptr, int* count) {
   if (!e) return fail("null engine");
   if (device_ptr) *device_ptr = e->d_record;
   if (count) *count = 3 + e->nelem;
+  return 0;
+}
+
+/* measured DFMA throughput of the device in TFLOP/s (best of `reps` launches) */
+int ps_fp64_peak(PsEngine* e, int reps, double* tflops) {
+  if (!e) return fail("null engine");
+  CU(cudaSetDevice(e->device));
+  int sms = 0; CU(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, e->device));
+  const int blocks = sms * 8, threads = 256, iters = 1 << 16;
+  double* out = nullptr; CU(cudaMalloc(&out, sizeof(double) * blocks * threads));
+  cudaEvent_t a, b; cudaEventCreate(&a); cudaEventCreate(&b);
+  double best = 0;
+  for (int r = 0; r < reps + 1; r++) {
+    cudaEventRecord(a, e->stream);
+    dfma_probe_kernel<<<blocks, threads, 0, e->stream>>>(out, iters, 0.999999, 1e-6);
+    cudaEventRecord(b, e->stream);
+    CU(cudaEventSynchronize(b));
+    float ms = 0; cudaEventElapsedTime(&ms, a, b);
+    const double tf = 2.0 * 8 * (double)iters * blocks * threads / (ms * 1e-3) / 1e12;
+    if (r > 0 && tf > best) best = tf;
+  }
+  cudaEventDestroy(a); cudaEventDestroy(b); cudaFree(out);
+  *tflops = best; e->launches += reps + 1;
   return 0;
 }
 

@@ -1,0 +1,134 @@
+// Non-template kernels of the planning iteration (compiled once, in ps_engine.cu): K1 knot-noise
+// perturbation, K3 grid-level min-loc + winner record, and the SoA read-back helpers.
+#pragma once
+#include "ps_kernels.cuh"
+
+namespace ps {
+
+// ---------------------------------------------------------------- counter-based RNG (Philox4x32-10)
+__device__ __forceinline__ void philox_round(uint32_t (&c)[4], uint32_t k0, uint32_t k1) {
+  const uint32_t hi0 = __umulhi(0xD2511F53u, c[0]), lo0 = 0xD2511F53u * c[0];
+  const uint32_t hi1 = __umulhi(0xCD9E8D57u, c[2]), lo1 = 0xCD9E8D57u * c[2];
+  const uint32_t n0 = hi1 ^ c[1] ^ k0, n1 = lo1, n2 = hi0 ^ c[3] ^ k1, n3 = lo0;
+  c[0] = n0; c[1] = n1; c[2] = n2; c[3] = n3;
+}
+__device__ __forceinline__ void philox4x32(uint32_t (&c)[4], uint32_t k0, uint32_t k1) {
+#pragma unroll
+  for (int i = 0; i < 10; i++) { philox_round(c, k0, k1); k0 += 0x9E3779B9u; k1 += 0xBB67AE85u; }
+}
+__device__ __forceinline__ double u01_open(uint32_t hi, uint32_t lo) {   // (0, 1), 53 bits
+  const unsigned long long x = ((unsigned long long)hi << 32) | lo;
+  return ((double)(x >> 11) + 0.5) * (1.0 / 9007199254740992.0);
+}
+
+// ---------------------------------------------------------------- K1
+// grid: (ceil(n / block), P*nu); knots[(e) * stride + i] for local sample i, element e = p*nu + a
+__global__ void perturb_kernel(const double* __restrict__ nominal, const double* __restrict__ ctrlrange, int n, int nelem, int nu,
+                               double sigma0, double sigma1, unsigned long long seed, unsigned long long iteration,
+                               long long sample_offset, const double* __restrict__ z_injected,
+                               const unsigned char* __restrict__ std2_injected, double* __restrict__ knots, int stride) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  const int e = blockIdx.y;
+  if (i >= n) return;
+  const long long gi = sample_offset + i;          // global sample index (rank-independent noise)
+  const int a = e % nu;
+  const double lo = ctrlrange[2 * a], hi = ctrlrange[2 * a + 1];
+  double v = nominal[e];
+  if (gi != 0) {
+    double sd = sigma0, z;
+    if (z_injected) {
+      z = z_injected[(size_t)i * nelem + e];
+      if (sigma1 > 0 && std2_injected && std2_injected[i]) sd = sigma1;
+    } else {
+      const uint32_t k0 = (uint32_t)seed, k1 = (uint32_t)(seed >> 32);
+      if (sigma1 > 0) {
+        uint32_t c[4] = {(uint32_t)gi, (uint32_t)(gi >> 32), 0xFFFFFFFFu, (uint32_t)iteration};
+        philox4x32(c, k0, k1);
+        if (u01_open(c[0], c[1]) < 0.2) sd = sigma1;     // absl::Bernoulli(gen, 0.2), planner.cc:323
+      }
+      uint32_t c[4] = {(uint32_t)gi, (uint32_t)(gi >> 32), (uint32_t)e, (uint32_t)iteration};
+      philox4x32(c, k0, k1);
+      const double u1 = u01_open(c[0], c[1]), u2 = u01_open(c[2], c[3]);
+      z = sqrt(-2.0 * log(u1)) * cospi(2.0 * u2);        // Box-Muller
+    }
+    const double scale = 0.5 * (hi - lo);
+    v += (scale * sd) * z;
+    v = clampd(v, lo, hi);
+  }
+  knots[(size_t)e * stride + i] = v;
+}
+
+// ---------------------------------------------------------------- K3
+// record = [winner_cost, winner_global_index, nominal_cost (local sample 0), knots[nelem]...]
+__global__ void argmin_kernel(const MinLoc* __restrict__ block_min, int nblocks, const double* __restrict__ returns,
+                              const double* __restrict__ knots, int stride, int nelem, long long sample_offset,
+                              double* __restrict__ record) {
+  __shared__ MinLoc wm[32];
+  __shared__ long long win;
+  double c = 1.0e300; long long gi = 0x7fffffffffffffffLL;
+  for (int b = threadIdx.x; b < nblocks; b += blockDim.x) {
+    const MinLoc v = block_min[b];
+    if (better(v.cost, v.index, c, gi)) { c = v.cost; gi = v.index; }
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    const double oc = __shfl_down_sync(0xffffffffu, c, o);
+    const long long oi = __shfl_down_sync(0xffffffffu, gi, o);
+    if (better(oc, oi, c, gi)) { c = oc; gi = oi; }
+  }
+  if ((threadIdx.x & 31) == 0) { wm[threadIdx.x >> 5].cost = c; wm[threadIdx.x >> 5].index = gi; }
+  __syncthreads();
+  if (threadIdx.x < 32) {
+    const int nw = (blockDim.x + 31) / 32;
+    c = threadIdx.x < nw ? wm[threadIdx.x].cost : 1.0e300;
+    gi = threadIdx.x < nw ? wm[threadIdx.x].index : 0x7fffffffffffffffLL;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      const double oc = __shfl_down_sync(0xffffffffu, c, o);
+      const long long oi = __shfl_down_sync(0xffffffffu, gi, o);
+      if (better(oc, oi, c, gi)) { c = oc; gi = oi; }
+    }
+    if (threadIdx.x == 0) {
+      if (gi == 0x7fffffffffffffffLL) gi = sample_offset;     // all NaN: fall back to the first sample
+      record[0] = c; record[1] = (double)gi; record[2] = returns[0]; win = gi - sample_offset;
+    }
+  }
+  __syncthreads();
+  const long long w = win;
+  for (int e = threadIdx.x; e < nelem; e += blockDim.x) record[3 + e] = knots[(size_t)e * stride + w];
+}
+
+// gather one sample's SoA column into a dense host-order array: out[r] = src[r * stride + i]
+__global__ void gather_column_kernel(const double* __restrict__ src, int rows, int stride, int i, double* __restrict__ out) {
+  const int r = blockIdx.x * blockDim.x + threadIdx.x;
+  if (r < rows) out[r] = src[(size_t)r * stride + i];
+}
+
+// transpose SoA [rows][stride] -> [n][rows] (parity read-back of all samples)
+__global__ void transpose_kernel(const double* __restrict__ src, int rows, int stride, int n, double* __restrict__ out) {
+  __shared__ double tile[32][33];
+  const int x = blockIdx.x * 32 + threadIdx.x;   // sample
+  for (int ry = threadIdx.y; ry < 32; ry += blockDim.y) {
+    const int r = blockIdx.y * 32 + ry;
+    tile[ry][threadIdx.x] = (r < rows && x < n) ? src[(size_t)r * stride + x] : 0.0;
+  }
+  __syncthreads();
+  const int r2 = blockIdx.y * 32 + threadIdx.x;  // row
+  for (int sy = threadIdx.y; sy < 32; sy += blockDim.y) {
+    const int s = blockIdx.x * 32 + sy;
+    if (s < n && r2 < rows) out[(size_t)s * rows + r2] = tile[threadIdx.x][sy];
+  }
+}
+
+// FP64 FMA throughput probe: the roofline denominator for the rollout kernel.
+// 8 independent dependency chains per thread, 2 flops per DFMA.
+__global__ void dfma_probe_kernel(double* out, int iters, double a, double b) {
+  double x0 = threadIdx.x, x1 = x0 + 1, x2 = x0 + 2, x3 = x0 + 3, x4 = x0 + 4, x5 = x0 + 5, x6 = x0 + 6, x7 = x0 + 7;
+  for (int i = 0; i < iters; i++) {
+    x0 = fma(x0, a, b); x1 = fma(x1, a, b); x2 = fma(x2, a, b); x3 = fma(x3, a, b);
+    x4 = fma(x4, a, b); x5 = fma(x5, a, b); x6 = fma(x6, a, b); x7 = fma(x7, a, b);
+  }
+  out[blockIdx.x * blockDim.x + threadIdx.x] = x0 + x1 + x2 + x3 + x4 + x5 + x6 + x7;
+}
+
+}  // namespace ps

@@ -1,0 +1,87 @@
+// The time recursion of ONE candidate rollout: policy -> forward pass -> residual -> cost ->
+// integrate, H-1 times, then the terminal forward pass.  Mirrors Trajectory::NoisyRollout +
+// UpdateReturn (mjpc/trajectory.cc:100-210,312-326): residual[t] = r(x_t, u_t), states[t+1] is the
+// post-integration state, the terminal residual is r(x_{H-1}, u_{H-2}), the return is the mean of
+// the per-step costs, and a diverged rollout scores 1e6 (trajectory.cc:169-173).
+#pragma once
+#include "ps_cost.cuh"
+
+namespace ps {
+
+template <class T>
+struct alignas(128) Constants { DevModel<T> m; DevTask t; DevPlan<T> p; };
+
+// optional full-trajectory outputs, SoA [t][field][stride] with the sample index fastest
+struct Writeback {
+  double* states; double* actions; double* residual; double* costs; double* times; double* trace;
+};
+
+// knots: SoA [P*nu][stride]; i = this rollout's column.  flags: bit0 failure, bit1 capacity overflow
+template <class T, bool WB>
+PS_FN double rollout_sample(const DevModel<T>& m, const DevTask& task, const DevPlan<T>& plan, const double* knots,
+                            int stride, int i, const Writeback& wb, int* flags) {
+  RolloutData<T> d;
+  const int nq = m.nq, nv = m.nv, na = m.na, nu = m.nu, ns = nq + nv + na, nr = task.num_residual;
+  const int H = plan.horizon, P = plan.num_spline_points, ntr = 3 * task.num_trace;
+  for (int k = 0; k < nq; k++) d.qpos[k] = plan.state[k];
+  for (int k = 0; k < nv; k++) { d.qvel[k] = plan.state[nq + k]; d.qacc_warmstart[k] = 0; d.qacc[k] = 0; }
+  for (int k = 0; k < na; k++) d.act[k] = plan.state[nq + nv + k];
+  for (int k = 0; k < nu; k++) d.ctrl[k] = 0;
+  for (int k = 0; k < m.nmocap; k++) { vcopy(d.mocap_pos + 3 * k, plan.mocap + 7 * k, 3); vcopy(d.mocap_quat + 4 * k, plan.mocap + 7 * k + 3, 4); }
+  d.time = plan.time; d.warning = 0; d.ncon = 0; d.nefc = 0; d.solver_iter = 0;
+  const double* kcol = knots + i;
+  auto kn = [&](int p, int a) { return kcol[(size_t)(p * nu + a) * stride]; };
+  double residual[kMaxResidual];
+  double sum = 0; bool failed = false;
+  if (WB) { for (int k = 0; k < ns; k++) wb.states[(size_t)k * stride + i] = plan.state[k]; wb.times[i] = d.time; }
+
+  for (int t = 0; t < H - 1; t++) {
+    spline_sample(plan.spline_times, P, nu, plan.interpolation, d.time, kn, d.ctrl);
+    for (int a = 0; a < nu; a++) d.ctrl[a] = clampd(d.ctrl[a], m.act_ctrlrange[2 * a], m.act_ctrlrange[2 * a + 1]);
+    if (WB) for (int a = 0; a < nu; a++) wb.actions[((size_t)t * nu + a) * stride + i] = d.ctrl[a];
+    if (state_is_bad(m, d)) { failed = true; break; }
+    forward_pass(m, d);
+    task_residual(m, d, task, residual);
+    const double c = cost_value(task, residual);
+    if (WB) {
+      for (int k = 0; k < nr; k++) wb.residual[((size_t)t * nr + k) * stride + i] = residual[k];
+      wb.costs[(size_t)t * stride + i] = c;
+      for (int k = 0; k < task.num_trace; k++) {
+        double tr[3]; read_sensor(m, d, task.trace_sensor[k], tr);
+        for (int x = 0; x < 3; x++) wb.trace[((size_t)t * ntr + 3 * k + x) * stride + i] = tr[x];
+      }
+    }
+    if (acc_is_bad(m, d) || (d.warning & (WARN_BADQPOS | WARN_BADQVEL | WARN_BADQACC | WARN_BADCTRL))) { failed = true; break; }
+    sum += c;
+    integrate(m, d);
+    if (WB) {
+      double* s = wb.states + ((size_t)(t + 1) * ns) * stride + i;
+      for (int k = 0; k < nq; k++) s[(size_t)k * stride] = d.qpos[k];
+      for (int k = 0; k < nv; k++) s[(size_t)(nq + k) * stride] = d.qvel[k];
+      for (int k = 0; k < na; k++) s[(size_t)(nq + nv + k) * stride] = d.act[k];
+      wb.times[(size_t)(t + 1) * stride + i] = d.time;
+    }
+  }
+  double total;
+  if (!failed) {
+    // terminal: ctrl is NOT rewritten before the final forward pass (trajectory.cc:190-198)
+    if (WB && H > 1) for (int a = 0; a < nu; a++) wb.actions[((size_t)(H - 1) * nu + a) * stride + i] = d.ctrl[a];
+    forward_pass(m, d);
+    task_residual(m, d, task, residual);
+    const double c = cost_value(task, residual);
+    if (WB) {
+      for (int k = 0; k < nr; k++) wb.residual[((size_t)(H - 1) * nr + k) * stride + i] = residual[k];
+      wb.costs[(size_t)(H - 1) * stride + i] = c;
+      for (int k = 0; k < task.num_trace; k++) {
+        double tr[3]; read_sensor(m, d, task.trace_sensor[k], tr);
+        for (int x = 0; x < 3; x++) wb.trace[((size_t)(H - 1) * ntr + 3 * k + x) * stride + i] = tr[x];
+      }
+    }
+    sum += c;
+    total = sum / (H > 1 ? H : 1);
+  } else total = 1.0e6;
+  *flags = (failed ? 1 : 0) | ((d.warning & WARN_CAPACITY) ? 2 : 0);
+  return total;
+}
+
+}  // namespace ps

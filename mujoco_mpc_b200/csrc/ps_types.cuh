@@ -12,7 +12,7 @@
 
 #if defined(__CUDACC__)
 #define PS_HD __host__ __device__ __forceinline__
-#define PS_FN __host__ __device__
+#define PS_FN __host__ __device__ inline
 #else
 #define PS_HD inline
 #define PS_FN inline

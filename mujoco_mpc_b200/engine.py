@@ -1,0 +1,176 @@
+"""ctypes binding of the C-ABI engine library (include/ps_engine.h -> libps_engine.so).
+
+This is plumbing for tests and the benchmark; the product is the shared library.  There is no
+CPU fallback: if the library is missing or no CUDA device is present, construction raises.
+"""
+import ctypes
+import os
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libps_engine.so")
+_dp = ctypes.POINTER(ctypes.c_double)
+_LIB = None
+
+EXPORTS = ["ps_last_error", "ps_create", "ps_destroy", "ps_set_model", "ps_set_options", "ps_set_task", "ps_set_state",
+           "ps_set_nominal", "ps_set_noise", "ps_set_seed", "ps_rollouts", "ps_rollouts_async", "ps_rollouts_writeback",
+           "ps_get_returns", "ps_get_knots", "ps_get_trajectory", "ps_get_all_trajectories", "ps_last_kernel_ms",
+           "ps_kernel_launch_count", "ps_winner_record_device", "ps_stream", "ps_name", "ps_variant", "ps_fp64_peak"]
+
+
+class EngineError(RuntimeError):
+    pass
+
+
+def lib():
+    global _LIB
+    if _LIB is None:
+        if not os.path.exists(LIB_PATH):
+            raise EngineError(f"{LIB_PATH} not built (run python mujoco_mpc_b200/build.py); there is no CPU fallback")
+        L = ctypes.CDLL(LIB_PATH)
+        L.ps_last_error.restype = ctypes.c_char_p
+        L.ps_create.restype = ctypes.c_void_p
+        L.ps_create.argtypes = [ctypes.c_int]
+        L.ps_destroy.argtypes = [ctypes.c_void_p]
+        _LIB = L
+    return _LIB
+
+
+def _p(a):
+    return a.ctypes.data_as(_dp) if a is not None else None
+
+
+def _arr(x):
+    return np.ascontiguousarray(np.asarray(x, dtype=np.float64))
+
+
+class Engine:
+    """One engine handle on one CUDA device."""
+
+    def __init__(self, model, task, device=0):
+        self.L = lib()
+        h = self.L.ps_create(device)
+        if not h:
+            raise EngineError(self.L.ps_last_error().decode())
+        self.h = ctypes.c_void_p(h)
+        self.model, self.task = model, task
+        self._ck(self.L.ps_set_model(self.h, ctypes.byref(model.c_struct())))
+        self._ck(self.L.ps_set_task(self.h, ctypes.byref(task)))
+        self.ns = model.nq + model.nv + model.na
+        self.N = self.H = self.P = 0
+
+    def _ck(self, r):
+        if r != 0:
+            raise EngineError(self.L.ps_last_error().decode())
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.L.ps_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def variant(self):
+        b = ctypes.create_string_buffer(64)
+        self._ck(self.L.ps_variant(self.h, b, 64))
+        return b.value.decode()
+
+    def set_task(self, task):
+        self.task = task
+        self._ck(self.L.ps_set_task(self.h, ctypes.byref(task)))
+
+    def set_options(self, timestep, integrator):
+        self._ck(self.L.ps_set_options(self.h, ctypes.c_double(timestep), int(integrator)))
+
+    def set_state(self, state, time, mocap=None):
+        s = _arr(state)
+        mo = _arr(mocap) if mocap is not None else None
+        self._ck(self.L.ps_set_state(self.h, _p(s), _p(mo), None, ctypes.c_double(time)))
+
+    def set_nominal(self, times, knots, interp):
+        t = _arr(times)
+        k = _arr(knots)
+        self.P = len(t)
+        self._ck(self.L.ps_set_nominal(self.h, _p(t), _p(k), len(t), int(interp)))
+
+    def set_noise(self, z, use_std2=None):
+        if z is None:
+            self._ck(self.L.ps_set_noise(self.h, None, None, 0))
+            return
+        z = _arr(z)
+        u = np.ascontiguousarray(use_std2, dtype=np.uint8) if use_std2 is not None else None
+        self._ck(self.L.ps_set_noise(self.h, _p(z), u.ctypes.data_as(ctypes.POINTER(ctypes.c_ubyte)) if u is not None else None,
+                                     z.shape[0]))
+
+    def set_seed(self, seed):
+        self._ck(self.L.ps_set_seed(self.h, ctypes.c_ulonglong(seed)))
+
+    def rollouts(self, N, H, sigma0, sigma1=0.0, sample_offset=0, writeback=False):
+        w = ctypes.c_int()
+        wr = ctypes.c_double()
+        nr = ctypes.c_double()
+        fn = self.L.ps_rollouts_writeback if writeback else self.L.ps_rollouts
+        self._ck(fn(self.h, N, H, ctypes.c_double(sigma0), ctypes.c_double(sigma1), sample_offset, ctypes.byref(w),
+                    ctypes.byref(wr), ctypes.byref(nr)))
+        self.N, self.H = N, H
+        return w.value, wr.value, nr.value
+
+    def rollouts_async(self, N, H, sigma0, sigma1=0.0, sample_offset=0):
+        self._ck(self.L.ps_rollouts_async(self.h, N, H, ctypes.c_double(sigma0), ctypes.c_double(sigma1), sample_offset))
+        self.N, self.H = N, H
+
+    def returns(self):
+        r = np.zeros(self.N)
+        f = np.zeros(self.N, dtype=np.uint8)
+        self._ck(self.L.ps_get_returns(self.h, _p(r), f.ctypes.data_as(ctypes.POINTER(ctypes.c_ubyte))))
+        return r, f
+
+    def knots(self, sample):
+        k = np.zeros((self.P, self.model.nu))
+        self._ck(self.L.ps_get_knots(self.h, sample, _p(k)))
+        return k
+
+    def trajectory(self, i):
+        H, m, t = self.H, self.model, self.task
+        st = np.zeros((H, self.ns)); ac = np.zeros((H, m.nu)); tm = np.zeros(H)
+        rs = np.zeros((H, t.num_residual)); cs = np.zeros(H); tr = np.zeros((H, max(1, 3 * t.num_trace)))
+        ret = ctypes.c_double(); fail = ctypes.c_int()
+        self._ck(self.L.ps_get_trajectory(self.h, i, _p(st), _p(ac), _p(tm), _p(rs), _p(cs), _p(tr), ctypes.byref(ret),
+                                          ctypes.byref(fail)))
+        return dict(states=st, actions=ac, times=tm, residual=rs, costs=cs, trace=tr[:, :3 * t.num_trace],
+                    total_return=ret.value, failure=bool(fail.value))
+
+    def all_trajectories(self):
+        N, H, m, t = self.N, self.H, self.model, self.task
+        st = np.zeros((N, H, self.ns)); ac = np.zeros((N, H, m.nu)); rs = np.zeros((N, H, t.num_residual)); cs = np.zeros((N, H))
+        self._ck(self.L.ps_get_all_trajectories(self.h, _p(st), _p(ac), _p(rs), _p(cs)))
+        return dict(states=st, actions=ac, residual=rs, costs=cs)
+
+    def kernel_ms(self):
+        a, b, c = ctypes.c_float(), ctypes.c_float(), ctypes.c_float()
+        self._ck(self.L.ps_last_kernel_ms(self.h, ctypes.byref(a), ctypes.byref(b), ctypes.byref(c)))
+        return a.value, b.value, c.value
+
+    def launches(self):
+        n = ctypes.c_longlong()
+        self._ck(self.L.ps_kernel_launch_count(self.h, ctypes.byref(n)))
+        return n.value
+
+    def winner_record_ptr(self):
+        p = ctypes.c_void_p(); n = ctypes.c_int()
+        self._ck(self.L.ps_winner_record_device(self.h, ctypes.byref(p), ctypes.byref(n)))
+        return p.value, n.value
+
+    def fp64_peak(self, reps=5):
+        v = ctypes.c_double()
+        self._ck(self.L.ps_fp64_peak(self.h, reps, ctypes.byref(v)))
+        return v.value
+
+    def stream(self):
+        p = ctypes.c_void_p()
+        self._ck(self.L.ps_stream(self.h, ctypes.byref(p)))
+        return p.value

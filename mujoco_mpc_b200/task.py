@@ -26,7 +26,14 @@ class PsTaskC(ctypes.Structure):
                 ("risk", ctypes.c_double),
                 ("parameters", ctypes.c_double * MAX_TASK_PARAMS),
                 ("aux", ctypes.c_double * MAX_TASK_AUX),
-                ("trace_sensor", ctypes.c_int * 4)]
+                ("trace_sensor", ctypes.c_int * 4),
+                ("sensor_id", ctypes.c_int * 16),
+                ("iaux", ctypes.c_int * 16)]
+
+# sensors each task's residual reads by name (SensorByName call sites in mjpc/tasks/<task>/<task>.cc)
+TASK_SENSORS = {"Particle": ["position", "velocity"], "ParticleFixed": ["position", "velocity"],
+                "Swimmer": ["nose", "target"],
+                "Walker": ["torso_position", "torso_zaxis", "torso_subtreelinvel"]}
 
 
 def make_task(model, name: str) -> PsTaskC:
@@ -76,4 +83,11 @@ def make_task(model, name: str) -> PsTaskC:
         elif nm.startswith("residual_"):
             t.parameters[k] = float(model.numeric_data[model.numeric_adr[i]]); k += 1
     t.num_parameters = k
+    for j in range(16):
+        t.sensor_id[j] = -1
+    for j, nm in enumerate(TASK_SENSORS.get(name, [])):
+        sid = model.name2id("sensor", nm)
+        if sid < 0:
+            raise ValueError(f"task {name}: sensor '{nm}' not found in the model")
+        t.sensor_id[j] = sid
     return t

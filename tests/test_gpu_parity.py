@@ -1,0 +1,113 @@
+"""GPU parity: the CUDA engine (through the C ABI) against the CPU oracle under the SAME injected
+knot noise.  Tolerances are the north_star's: per-step qpos/qvel 1e-9 relative, total trajectory
+cost 1e-8 relative, identical best-sample index."""
+import numpy as np
+import pytest
+from mujoco_mpc_b200 import registry
+from mujoco_mpc_b200.engine import Engine
+from tests.common import synthetic_state, oracle_iteration
+
+pytestmark = pytest.mark.gpu
+
+STATE_RTOL, COST_RTOL = 1e-9, 1e-8
+
+
+def rel_err(a, b):
+    return np.abs(a - b).max() / max(1.0, np.abs(b).max())
+
+
+def run_case(name, N, interp, H=None, seed=2024, sigma=None, time=0.37, warm=True):
+    model, task, s = registry.load(name)
+    H = H or s["steps"]
+    P = min(s["num_spline_points"], 36)
+    sigma = s["exploration"] if sigma is None else sigma
+    rng = np.random.default_rng(seed)
+    z = rng.standard_normal((N, P, model.nu))
+    state = synthetic_state(model)
+    nominal = None
+    if warm:   # steady state: a non-trivial previous plan, offset in time so resampling matters
+        nt = time - 0.013 + np.linspace(0, (H - 1) * s["timestep"], P)
+        nk = rng.uniform(-0.6, 0.6, (P, model.nu)) * 0.5 * (model.actuator_ctrlrange[:, 1] - model.actuator_ctrlrange[:, 0])
+        nominal = (nt, nk)
+    o, nt, nk, w = oracle_iteration(model, task, s, state, time, N, H, P, interp, sigma, z, nominal=nominal)
+    e = Engine(model, task)
+    e.set_state(state, time)
+    e.set_nominal(nt, nk, interp)
+    e.set_noise(z)
+    gw, gwr, gnr = e.rollouts(N, H, sigma, writeback=True)
+    oret, ofail = o.returns()
+    gret, gfail = e.returns()
+    assert np.array_equal(ofail.astype(bool), (gfail & 1).astype(bool))
+    ok = ~ofail.astype(bool)
+    assert np.abs(gret[ok] - oret[ok]).max() <= COST_RTOL * max(1.0, np.abs(oret[ok]).max()), (name, np.abs(gret - oret).max())
+    assert gw == w, (name, gw, w, gret[gw], oret[w])
+    assert abs(gwr - oret[w]) <= COST_RTOL * max(1.0, abs(oret[w]))
+    assert abs(gnr - oret[0]) <= COST_RTOL * max(1.0, abs(oret[0]))
+    # every step of every sample
+    tr = e.all_trajectories()
+    worst_s = worst_r = 0.0
+    for i in range(N):
+        ot = o.trajectory(i)
+        if ot["failure"]:
+            continue
+        worst_s = max(worst_s, rel_err(tr["states"][i], ot["states"]))
+        worst_r = max(worst_r, rel_err(tr["residual"][i], ot["residual"]))
+        assert np.allclose(tr["actions"][i], ot["actions"], rtol=0, atol=1e-12)
+    assert worst_s <= STATE_RTOL, (name, worst_s)
+    assert worst_r <= 1e-8, (name, worst_r)
+    # candidate knots and single-trajectory read-back
+    pt, pk = o.policy(2 + w)
+    assert np.allclose(e.knots(w), pk, rtol=0, atol=1e-14)
+    e.close()
+    return worst_s, worst_r
+
+
+@pytest.mark.parametrize("name", ["Particle", "Cartpole", "Acrobot"])
+@pytest.mark.parametrize("interp", [0, 1, 2])
+def test_parity_small_models(oracle_lib, name, interp):
+    run_case(name, N=256, interp=interp)
+
+
+def test_parity_config2_sizes(oracle_lib):
+    # BASELINE config 2: Acrobot + Particle, 4,096 samples, cubic
+    run_case("Acrobot", N=4096, interp=2, H=101)
+    run_case("Particle", N=4096, interp=2)
+
+
+def test_first_iteration_zero_nominal(oracle_lib):
+    run_case("Cartpole", N=128, interp=0, warm=False)
+
+
+def test_reroll_single_trajectory(oracle_lib):
+    model, task, s = registry.load("Cartpole")
+    N, H, P = 64, 51, 10
+    z = np.random.default_rng(1).standard_normal((N, P, model.nu))
+    state = synthetic_state(model)
+    o, nt, nk, w = oracle_iteration(model, task, s, state, 0.0, N, H, P, 2, 0.5, z)
+    e = Engine(model, task)
+    e.set_state(state, 0.0); e.set_nominal(nt, nk, 2); e.set_noise(z)
+    gw, _, _ = e.rollouts(N, H, 0.5)             # cost-only mode
+    assert gw == w
+    g = e.trajectory(w); ot = o.trajectory(w)     # re-rolled with writeback
+    assert rel_err(g["states"], ot["states"]) <= STATE_RTOL
+    assert rel_err(g["trace"], ot["trace"]) <= 1e-9
+    assert abs(g["total_return"] - ot["total_return"]) <= COST_RTOL * max(1, abs(ot["total_return"]))
+    assert np.allclose(g["times"], ot["times"], rtol=0, atol=1e-12)
+    e.close()
+
+
+def test_device_rng_statistics():
+    model, task, s = registry.load("Particle")
+    e = Engine(model, task)
+    N, P = 65536, 5
+    e.set_state(registry.home_state(model), 0.0)
+    e.set_nominal(np.linspace(0, 0.5, P), np.zeros((P, model.nu)), 2)
+    e.set_seed(7)
+    e.rollouts(N, 3, 0.1)
+    k = np.stack([e.knots(i) for i in range(0, 4096)])
+    assert np.all(k[0] == 0)                        # sample 0 is the un-noised nominal
+    zs = k[1:].ravel() / 0.1                        # ctrlrange +-1 => scale 1
+    assert abs(zs.mean()) < 0.02 and abs(zs.std() - 1) < 0.02
+    e.set_seed(7); e.rollouts(N, 3, 0.1)
+    assert np.array_equal(e.knots(17), k[17])       # counter-based: reproducible
+    e.close()
