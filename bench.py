@@ -83,7 +83,7 @@ class ClockSampler(threading.Thread):
 
 def make_cases(workload, rank, world):
     from mujoco_mpc_b200 import registry
-    from tests.common import synthetic_state
+    from mujoco_mpc_b200.registry import synthetic_state
     cases = []
     for name, N, interp, H in WORKLOADS[workload]:
         model, task, s = registry.load(name)

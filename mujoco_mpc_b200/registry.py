@@ -51,3 +51,16 @@ def home_state(model):
     k = model.name2id("key", "home")
     st[:model.nq] = model.key_qpos[k] if k >= 0 else model.qpos0
     return st
+
+
+def synthetic_state(model, seed=1234, pos=0.05, vel=0.1):
+    import numpy as np
+    rng = np.random.default_rng(seed)
+    st = home_state(model)
+    st[:model.nq] += rng.uniform(-pos, pos, model.nq)
+    st[model.nq:model.nq + model.nv] += rng.uniform(-vel, vel, model.nv)
+    for j in range(model.njnt):        # renormalise free-joint quaternions
+        if model.jnt_type[j] == 0:
+            a = model.jnt_qposadr[j] + 3
+            st[a:a + 4] /= np.linalg.norm(st[a:a + 4])
+    return st

@@ -5,16 +5,7 @@ from mujoco_mpc_b200 import registry
 from oracle import pyoracle
 
 
-def synthetic_state(model, seed=1234, pos=0.05, vel=0.1):
-    rng = np.random.default_rng(seed)
-    st = registry.home_state(model)
-    st[:model.nq] += rng.uniform(-pos, pos, model.nq)
-    st[model.nq:model.nq + model.nv] += rng.uniform(-vel, vel, model.nv)
-    for j in range(model.njnt):        # renormalise free-joint quaternions
-        if model.jnt_type[j] == 0:
-            a = model.jnt_qposadr[j] + 3
-            st[a:a + 4] /= np.linalg.norm(st[a:a + 4])
-    return st
+from mujoco_mpc_b200.registry import synthetic_state  # noqa: F401
 
 
 def oracle_iteration(model, task, settings, state, time, N, H, P, interp, sigma, z, nominal=None, mocap=None, nthread=1):
