@@ -15,7 +15,7 @@ namespace ps {
 // ---------------------------------------------------------------- engine instantiations
 //                        NQ NV NU NA NBODY NJNT NGEOM NSITE NMOCAP NPAIR MAXCON MAXEFC NSENSOR ELLIPTIC
 typedef Traits<2, 2, 2, 0, 4, 2, 8, 2, 1, 0, 0, 4, 12, false> TinyT;          // particle, cartpole, acrobot
-typedef Traits<9, 9, 6, 5, 9, 9, 12, 4, 1, 12, 10, 48, 16, false> PlanarT;    // swimmer, walker
+typedef Traits<9, 9, 6, 5, 9, 9, 18, 6, 1, 8, 14, 64, 20, false> PlanarT;    // swimmer, walker
 typedef Traits<19, 18, 12, 0, 16, 13, 40, 24, 2, 48, 16, 96, 24, true> LeggedT;  // quadruped (free joint, elliptic cones)
 
 struct PairList { std::vector<int> g1, g2; int unsupported = 0; };

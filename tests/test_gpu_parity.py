@@ -74,6 +74,13 @@ def test_parity_config2_sizes(oracle_lib):
     run_case("Particle", N=4096, interp=2)
 
 
+@pytest.mark.parametrize("name,N", [("Swimmer", 512), ("Walker", 1024)])
+def test_parity_planar_models(oracle_lib, name, N):
+    # Swimmer: implicit integrator + fluid forces + activation states + joint limits;
+    # Walker: capsule-plane contacts, pyramidal cones, Newton solver
+    run_case(name, N=N, interp=2)
+
+
 def test_first_iteration_zero_nominal(oracle_lib):
     run_case("Cartpole", N=128, interp=0, warm=False)
 
