@@ -10,7 +10,12 @@ CSRC = os.path.join(HERE, "csrc")
 OUT = os.path.join(HERE, "libps_engine.so")
 UNITS = ["ps_engine.cu", "ps_variant_tiny.cu", "ps_variant_planar.cu", "ps_variant_legged.cu"]
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
+# -fmad=false: FP64 multiply-adds are NOT contracted, so the device arithmetic is operation-for-operation
+# the IEEE sequence the oracle executes (-ffp-contract=off).  Contact-rich rollouts amplify rounding
+# differences by many orders of magnitude, so this is what keeps the 1e-9 / 1e-8 parity bars robust.
 FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17", "-Xcompiler", "-fPIC"]
+if os.environ.get("PS_FMAD", "0") != "1":
+    FLAGS.append("-fmad=false")
 
 
 def _stale(target, deps):

@@ -231,6 +231,14 @@ PS_HD void sanitize_sol(double timestep, int disableflags, const double* sr, con
   solimp[4] = fmax(1.0, solimp[4]);
 }
 
+// x^p; the integer powers models actually use (solimp power 1..3) are exact IEEE products
+PS_HD double pow_small(double x, double p) {
+  if (p == 1) return x;
+  if (p == 2) return x * x;
+  if (p == 3) return x * x * x;
+  return pow(x, p);
+}
+
 PS_HD double impedance_at(const double* si, double pos, double margin) {
   if (si[0] == si[1] || si[2] <= kMinVal) return 0.5 * (si[0] + si[1]);
   const double x = fabs((pos - margin) / si[2]);
@@ -238,8 +246,8 @@ PS_HD double impedance_at(const double* si, double pos, double margin) {
   if (x <= 0) return si[0];
   double y;
   if (si[4] == 1) y = x;
-  else if (x <= si[3]) y = pow(x, si[4]) / pow(si[3], si[4] - 1);
-  else y = 1 - pow(1 - x, si[4]) / pow(1 - si[3], si[4] - 1);
+  else if (x <= si[3]) y = pow_small(x, si[4]) / pow_small(si[3], si[4] - 1);
+  else y = 1 - pow_small(1 - x, si[4]) / pow_small(1 - si[3], si[4] - 1);
   return si[0] + y * (si[1] - si[0]);
 }
 

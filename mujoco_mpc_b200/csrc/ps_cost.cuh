@@ -86,7 +86,7 @@ PS_FN void task_residual(const DevModel<T>& m, const RolloutData<T>& d, const De
     case TASK_PARTICLE: case TASK_PARTICLE_FIXED: {
       // particle.cc:36-56 (time-varying goal) / :73-78 (mocap goal); sensor_id = {position, velocity}
       double goal[2];
-      if (t.task_id == TASK_PARTICLE) { goal[0] = 0.25 * sin(d.time); goal[1] = 0.25 * cos(d.time / kPi); }
+      if (t.task_id == TASK_PARTICLE) { goal[0] = 0.25 * sin_det(d.time); goal[1] = 0.25 * cos_det(d.time / kPi); }
       else { goal[0] = d.mocap_pos[0]; goal[1] = d.mocap_pos[1]; }
       read_sensor(m, d, t.sensor_id[0], s0); read_sensor(m, d, t.sensor_id[1], s1);
       r[0] = s0[0] - goal[0]; r[1] = s0[1] - goal[1]; r[2] = s1[0]; r[3] = s1[1];
@@ -98,7 +98,7 @@ PS_FN void task_residual(const DevModel<T>& m, const RolloutData<T>& d, const De
       break;
     case TASK_CARTPOLE:
       // cartpole.cc:36-49
-      r[0] = cos(d.qpos[1]) - 1; r[1] = d.qpos[0] - t.parameters[0]; r[2] = d.qvel[1]; r[3] = d.ctrl[0];
+      r[0] = cos_det(d.qpos[1]) - 1; r[1] = d.qpos[0] - t.parameters[0]; r[2] = d.qvel[1]; r[3] = d.ctrl[0];
       break;
     case TASK_ACROBOT:
       // acrobot.cc:36-49: tip (site 0) to target (site 1), z then x

@@ -56,10 +56,46 @@ PS_HD void quat_to_mat(double* m, const double* q) {
 PS_HD void quat_rotate(double* r, const double* v, const double* q) {
   double m[9]; quat_to_mat(m, q); mat_vec3(r, m, v);
 }
+// sin and cos from IEEE +,-,* only (two-term Cody-Waite reduction by pi/2 carried to ~118 bits, then
+// the classic minimax kernels on [-pi/4, pi/4]; error < 1 ulp).  Vendor libm sin/cos differ from
+// one another in the last bit for a few percent of arguments, and contact-rich rollouts amplify
+// a one-ulp difference by ten orders of magnitude; evaluating the pair this way makes the
+// rollout independent of the math library underneath it.
+PS_HD void sincos_det(double x, double* sn, double* cs) {
+  if (!(fabs(x) < 1.0e6)) { *sn = sin(x); *cs = cos(x); return; }   // out of the reduction's range (never an angle)
+  const double fn = floor(x * 6.36619772367581382433e-01 + 0.5);
+  const double t = x - fn * 1.57079632673412561417e+00;
+  double w = fn * 6.07710050630396597660e-11;
+  const double r = t - w;
+  w = fn * 2.02226624879595063154e-21 - ((t - r) - w);
+  const double y0 = r - w, y1 = (r - y0) - w;
+  const double z = y0 * y0;
+  // sine kernel
+  const double v = z * y0;
+  const double rs = 8.33333333332248946124e-03 + z * (-1.98412698298579493134e-04 + z * (2.75573137070700676789e-06 +
+                    z * (-2.50507602534068634195e-08 + z * 1.58969099521155010221e-10)));
+  const double ks = y0 - ((z * (0.5 * y1 - v * rs) - y1) - v * -1.66666666666666324348e-01);
+  // cosine kernel
+  const double ww = z * z;
+  const double rc = z * (4.16666666666666019037e-02 + z * (-1.38888888888741095749e-03 + z * 2.48015872894767294178e-05)) +
+                    (ww * ww) * (-2.75573143513906633035e-07 + z * (2.08757232129817482790e-09 + z * -1.13596475577881948265e-11));
+  const double hz = 0.5 * z, wc = 1.0 - hz;
+  const double kc = wc + (((1.0 - wc) - hz) + (z * rc - y0 * y1));
+  const long long n = (long long)fn;
+  switch ((int)(n & 3)) {
+    case 0: *sn = ks; *cs = kc; break;
+    case 1: *sn = kc; *cs = -ks; break;
+    case 2: *sn = -ks; *cs = -kc; break;
+    default: *sn = -kc; *cs = ks; break;
+  }
+}
+PS_HD double sin_det(double x) { double s, c; sincos_det(x, &s, &c); return s; }
+PS_HD double cos_det(double x) { double s, c; sincos_det(x, &s, &c); return c; }
+
 PS_HD void axis_angle_quat(double* q, const double* axis, double angle) {
   if (angle == 0) { q[0] = 1; q[1] = 0; q[2] = 0; q[3] = 0; return; }
-  double s = sin(angle * 0.5);
-  q[0] = cos(angle * 0.5); q[1] = axis[0] * s; q[2] = axis[1] * s; q[3] = axis[2] * s;
+  double s, c; sincos_det(angle * 0.5, &s, &c);
+  q[0] = c; q[1] = axis[0] * s; q[2] = axis[1] * s; q[3] = axis[2] * s;
 }
 // q <- q * exp(dt * w / 2), w in the body frame (free / ball joint position update)
 PS_HD void quat_integrate(double* q, const double* w, double dt) {

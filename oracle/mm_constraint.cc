@@ -27,6 +27,15 @@ static void sanitizeSol(const Model* m, const double* sr, const double* si, doub
   solimp[4] = std::fmax(1.0, solimp[4]);
 }
 
+// x^p with the integer powers MuJoCo models actually use (solimp power 1 or 2) evaluated by exact
+// IEEE multiplication, so the result does not depend on the libm at hand
+static double powi(double x, double p) {
+  if (p == 1) return x;
+  if (p == 2) return x * x;
+  if (p == 3) return x * x * x;
+  return std::pow(x, p);
+}
+
 static double impedance(const double* si, double pos, double margin) {
   if (si[0] == si[1] || si[2] <= kMinVal) return 0.5 * (si[0] + si[1]);
   double x = std::fabs((pos - margin) / si[2]);
@@ -34,8 +43,8 @@ static double impedance(const double* si, double pos, double margin) {
   if (x <= 0) return si[0];
   double y;
   if (si[4] == 1) y = x;
-  else if (x <= si[3]) y = std::pow(x, si[4]) / std::pow(si[3], si[4] - 1);
-  else y = 1 - std::pow(1 - x, si[4]) / std::pow(1 - si[3], si[4] - 1);
+  else if (x <= si[3]) y = powi(x, si[4]) / powi(si[3], si[4] - 1);
+  else y = 1 - powi(1 - x, si[4]) / powi(1 - si[3], si[4] - 1);
   return si[0] + y * (si[1] - si[0]);
 }
 

@@ -81,7 +81,7 @@ void residual(const Model* m, const Data* d, const PsTask* t, double* r) {
   switch (t->task_id) {
     case PS_TASK_PARTICLE: case PS_TASK_PARTICLE_FIXED: {
       double goal[2];
-      if (t->task_id == PS_TASK_PARTICLE) { goal[0] = 0.25 * std::sin(d->time); goal[1] = 0.25 * std::cos(d->time / kPi); }
+      if (t->task_id == PS_TASK_PARTICLE) { goal[0] = 0.25 * sinDet(d->time); goal[1] = 0.25 * cosDet(d->time / kPi); }
       else { goal[0] = d->mocap_pos[0]; goal[1] = d->mocap_pos[1]; }
       const double* pos = sensorByName(m, d, "position"); const double* vel = sensorByName(m, d, "velocity");
       for (int i = 0; i < m->nq; i++) r[i] = pos[i] - goal[i];
@@ -94,7 +94,7 @@ void residual(const Model* m, const Data* d, const PsTask* t, double* r) {
       for (int i = 0; i < m->nv; i++) r[2 + i] = d->qvel[i];
       break;
     case PS_TASK_CARTPOLE:
-      r[0] = std::cos(d->qpos[1]) - 1; r[1] = d->qpos[0] - t->parameters[0]; r[2] = d->qvel[1]; r[3] = d->ctrl[0];
+      r[0] = cosDet(d->qpos[1]) - 1; r[1] = d->qpos[0] - t->parameters[0]; r[2] = d->qvel[1]; r[3] = d->ctrl[0];
       break;
     case PS_TASK_ACROBOT:
       r[0] = d->site_xpos[2] - d->site_xpos[5]; r[1] = d->site_xpos[0] - d->site_xpos[3];

@@ -62,10 +62,47 @@ inline void quat2Mat(double* m, const double* q) {
 inline void rotVecQuat(double* r, const double* v, const double* q) {
   double m[9]; quat2Mat(m, q); double t[3]; mulMatVec3(t, m, v); copy(r, t, 3);
 }
+// sin/cos restated with IEEE +,-,* only (fdlibm-style: Cody-Waite reduction by pi/2 with the
+// hi/mid/lo split of pi/2, then the k_sin / k_cos minimax kernels; < 1 ulp).  The reference calls
+// libm's sin/cos (via MuJoCo's mju_sin/mju_cos); libm implementations disagree with each other in
+// the last bit for a few percent of arguments, so the oracle pins one published algorithm instead
+// of whatever libm the host has.  DEVIATION from the reference: <= 1 ulp per call.
+inline void sincosDet(double x, double* sn, double* cs) {
+  if (!(std::fabs(x) < 1.0e6)) { *sn = std::sin(x); *cs = std::cos(x); return; }
+  static const double invpio2 = 6.36619772367581382433e-01, pio2_1 = 1.57079632673412561417e+00,
+                      pio2_2 = 6.07710050630396597660e-11, pio2_2t = 2.02226624879595063154e-21;
+  static const double S1 = -1.66666666666666324348e-01, S2 = 8.33333333332248946124e-03, S3 = -1.98412698298579493134e-04,
+                      S4 = 2.75573137070700676789e-06, S5 = -2.50507602534068634195e-08, S6 = 1.58969099521155010221e-10;
+  static const double C1 = 4.16666666666666019037e-02, C2 = -1.38888888888741095749e-03, C3 = 2.48015872894767294178e-05,
+                      C4 = -2.75573143513906633035e-07, C5 = 2.08757232129817482790e-09, C6 = -1.13596475577881948265e-11;
+  double fn = std::floor(x * invpio2 + 0.5);
+  double t = x - fn * pio2_1;
+  double w = fn * pio2_2;
+  double r = t - w;
+  w = fn * pio2_2t - ((t - r) - w);
+  double y0 = r - w, y1 = (r - y0) - w;
+  double z = y0 * y0;
+  double v = z * y0;
+  double rs = S2 + z * (S3 + z * (S4 + z * (S5 + z * S6)));
+  double ks = y0 - ((z * (0.5 * y1 - v * rs) - y1) - v * S1);
+  double ww = z * z;
+  double rc = z * (C1 + z * (C2 + z * C3)) + (ww * ww) * (C4 + z * (C5 + z * C6));
+  double hz = 0.5 * z, wc = 1.0 - hz;
+  double kc = wc + (((1.0 - wc) - hz) + (z * rc - y0 * y1));
+  long long n = (long long)fn;
+  switch ((int)(n & 3)) {
+    case 0: *sn = ks; *cs = kc; break;
+    case 1: *sn = kc; *cs = -ks; break;
+    case 2: *sn = -ks; *cs = -kc; break;
+    default: *sn = -kc; *cs = ks; break;
+  }
+}
+inline double sinDet(double x) { double s, c; sincosDet(x, &s, &c); return s; }
+inline double cosDet(double x) { double s, c; sincosDet(x, &s, &c); return c; }
 inline void axisAngle2Quat(double* q, const double* axis, double angle) {
   if (angle == 0) { q[0] = 1; q[1] = q[2] = q[3] = 0; return; }
-  double s = std::sin(angle * 0.5);
-  q[0] = std::cos(angle * 0.5); q[1] = axis[0] * s; q[2] = axis[1] * s; q[3] = axis[2] * s;
+  double s, c; sincosDet(angle * 0.5, &s, &c);
+  q[0] = c; q[1] = axis[0] * s; q[2] = axis[1] * s; q[3] = axis[2] * s;
 }
 // integrate quaternion by angular velocity (body frame) * dt   (mju_quatIntegrate)
 inline void quatIntegrate(double* q, const double* vel, double dt) {
