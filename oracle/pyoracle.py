@@ -13,7 +13,33 @@ _dp = ctypes.POINTER(ctypes.c_double)
 
 
 def build():
-    subprocess.check_call(["make", "-s", "-C", _HERE])
+    subprocess.check_call(["make", "-s", "-C", _HERE, "all"], stdout=subprocess.DEVNULL)
+
+
+_REF = None
+
+
+def ref_lib():
+    """The reference's own norm.cc / spline.cc compiled unmodified (oracle/_ref); None when absent."""
+    global _REF
+    path = os.path.join(_HERE, "_ref", "libmjpc_ref.so")
+    if _REF is None and os.path.exists(path):
+        L = ctypes.CDLL(path)
+        L.ref_norm.restype = ctypes.c_double
+        _REF = L
+    return _REF
+
+
+def ref_norm(x, params, ntype):
+    x = _arr(x); p = _arr(list(params) + [0.0, 0.0, 0.0])
+    return ref_lib().ref_norm(_p(x), _p(p), ctypes.c_int(x.size), ctypes.c_int(ntype))
+
+
+def ref_spline_sample(times, knots, interp, t):
+    times = _arr(times); knots = _arr(knots).reshape(len(times), -1)
+    out = np.zeros(knots.shape[1])
+    ref_lib().ref_spline_sample(_p(times), _p(knots), len(times), out.size, interp, ctypes.c_double(t), _p(out))
+    return out
 
 
 def lib():
@@ -45,7 +71,7 @@ def norm(x, params, ntype):
 
 
 def spline_sample(times, knots, interp, t):
-    times = _arr(times); knots = _arr(knots).reshape(len(times), -1)
+    times = _arr(times); knots = _arr(knots).reshape(len(times), -1) if len(times) else np.zeros((0, 1))
     out = np.zeros(knots.shape[1] if len(times) else 1)
     lib().mmo_spline_sample(_p(times), _p(knots), len(times), out.size, interp, ctypes.c_double(t), _p(out))
     return out
