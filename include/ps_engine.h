@@ -87,6 +87,8 @@ int ps_kernel_launch_count(PsEngine* e, long long* launches);
  * knots[P*nu]] as doubles.  Exposed so a multi-GPU host can feed it to an NCCL all-gather
  * (min-loc over ranks) without a host round trip.  *count = 3 + P*nu. */
 int ps_winner_record_device(PsEngine* e, void** device_ptr, int* count);
+/* host copy of the same record as fetched by the last ps_rollouts / ps_rollouts_writeback */
+int ps_get_winner_record(PsEngine* e, double* out, int cap);
 /* CUDA stream (cudaStream_t) all engine work is issued on */
 int ps_stream(PsEngine* e, void** stream);
 /* ps_rollouts without the final device->host read: results stay in the winner record */

@@ -370,6 +370,15 @@ int ps_fp64_peak(PsEngine* e, int reps, double* tflops) {
   return 0;
 }
 
+/* host copy of the winner record fetched by the last ps_rollouts: [return, global index, nominal return, knots[P*nu]] */
+int ps_get_winner_record(PsEngine* e, double* out, int cap) {
+  if (!e || e->N <= 0) return fail("ps_get_winner_record: nothing rolled out");
+  const int n = 3 + e->nelem;
+  if (cap < n) return fail("ps_get_winner_record: buffer too small");
+  for (int i = 0; i < n; i++) out[i] = e->h_record[i];
+  return 0;
+}
+
 int ps_stream(PsEngine* e, void** stream) { if (!e) return fail("null engine"); *stream = (void*)e->stream; return 0; }
 
 int ps_variant(PsEngine* e, char* out, int cap) {

@@ -1,0 +1,85 @@
+// extern "C" surface over CudaSamplingPlanner for language bindings (tests/, bench.py use it via
+// ctypes).  House style follows the reference's own C plugin ABI, mjpc/interface.cc:77-115.
+#include <cstring>
+#include "cuda_sampling_planner.h"
+
+using mjpc_b200::CudaSamplingPlanner;
+
+extern "C" {
+
+// pure host logic of the cross-rank min-loc (lowest return, ties -> lowest global sample index);
+// records are [world][count] with record = [return, global index, nominal return, knots...]
+int psp_select_winner(const double* all, int world, int count) {
+  int best = 0;
+  for (int r = 1; r < world; r++) {
+    const double c = all[(size_t)r * count], bc = all[(size_t)best * count];
+    if (c < bc || (c == bc && all[(size_t)r * count + 1] < all[(size_t)best * count + 1])) best = r;
+  }
+  return best;
+}
+
+void* psp_create(const PsModel* model, const PsTask* task, int device) {
+  CudaSamplingPlanner* p = new CudaSamplingPlanner;
+  p->Initialize(model, task, device); p->Allocate(); p->Reset(mjpc_b200::kMaxTrajectoryHorizon);
+  return p;
+}
+void psp_destroy(void* h) { delete (CudaSamplingPlanner*)h; }
+void psp_reset(void* h, int horizon, const double* initial_repeated_action) { ((CudaSamplingPlanner*)h)->Reset(horizon, initial_repeated_action); }
+void psp_set_state(void* h, const double* state, const double* mocap, const double* userdata, double time) {
+  ((CudaSamplingPlanner*)h)->SetState(state, mocap, userdata, time);
+}
+void psp_set_task(void* h, const PsTask* t) { ((CudaSamplingPlanner*)h)->SetTask(t); }
+void psp_configure(void* h, int num_trajectory, int interpolation, int num_spline_points, double sigma0, double sigma1, int sliding) {
+  CudaSamplingPlanner* p = (CudaSamplingPlanner*)h;
+  if (num_trajectory > 0) p->num_trajectory_ = num_trajectory;
+  if (interpolation >= 0) p->interpolation_ = interpolation;
+  if (num_spline_points > 0) { p->policy.num_spline_points = num_spline_points; p->previous_policy.num_spline_points = num_spline_points; }
+  if (sigma0 >= 0) p->noise_exploration[0] = sigma0;
+  if (sigma1 >= 0) p->noise_exploration[1] = sigma1;
+  if (sliding >= 0) p->sliding_plan_ = sliding;
+}
+void psp_set_noise(void* h, const double* z, const unsigned char* use_std2, int N) { ((CudaSamplingPlanner*)h)->SetNoise(z, use_std2, N); }
+void psp_set_seed(void* h, unsigned long long seed) { ((CudaSamplingPlanner*)h)->SetSeed(seed); }
+void psp_set_sharding(void* h, int rank, int world, mjpc_b200::AllGatherFn fn, void* ctx) { ((CudaSamplingPlanner*)h)->SetSharding(rank, world, fn, ctx); }
+void psp_optimize_policy(void* h, int horizon) { ((CudaSamplingPlanner*)h)->OptimizePolicy(horizon); }
+int psp_optimize_policy_candidates(void* h, int ncandidates, int horizon) { return ((CudaSamplingPlanner*)h)->OptimizePolicyCandidates(ncandidates, horizon); }
+double psp_candidate_score(void* h, int c) { return ((CudaSamplingPlanner*)h)->CandidateScore(c); }
+void psp_action_from_candidate_policy(void* h, double* action, int c, double time) { ((CudaSamplingPlanner*)h)->ActionFromCandidatePolicy(action, c, nullptr, time); }
+void psp_copy_candidate_to_policy(void* h, int c) { ((CudaSamplingPlanner*)h)->CopyCandidateToPolicy(c); }
+void psp_nominal_trajectory(void* h, int horizon) { ((CudaSamplingPlanner*)h)->NominalTrajectory(horizon); }
+void psp_action_from_policy(void* h, double* action, double time, int use_previous) {
+  ((CudaSamplingPlanner*)h)->ActionFromPolicy(action, nullptr, time, use_previous != 0);
+}
+int psp_winner(void* h) { return ((CudaSamplingPlanner*)h)->winner; }
+double psp_improvement(void* h) { return ((CudaSamplingPlanner*)h)->improvement; }
+int psp_num_parameters(void* h) { return ((CudaSamplingPlanner*)h)->NumParameters(); }
+// which: 0 policy, 1 previous_policy.  Returns the number of spline points written.
+int psp_get_policy(void* h, int which, double* times, double* knots) {
+  CudaSamplingPlanner* p = (CudaSamplingPlanner*)h;
+  const mjpc_b200::TimeSpline& s = which ? p->previous_policy.plan : p->policy.plan;
+  std::memcpy(times, s.times().data(), sizeof(double) * s.times().size());
+  std::memcpy(knots, s.values().data(), sizeof(double) * s.values().size());
+  return s.Size();
+}
+void psp_timers(void* h, double* noise_us, double* rollouts_us, double* policy_update_us) {
+  CudaSamplingPlanner* p = (CudaSamplingPlanner*)h;
+  *noise_us = p->noise_compute_time; *rollouts_us = p->rollouts_compute_time; *policy_update_us = p->policy_update_compute_time;
+}
+// BestTrajectory(): returns horizon (0 if none); any pointer may be NULL
+int psp_best_trajectory(void* h, double* states, double* actions, double* times, double* residual, double* costs, double* trace,
+                        double* total_return, int* failure) {
+  const mjpc_b200::Trajectory* t = ((CudaSamplingPlanner*)h)->BestTrajectory();
+  if (!t) return 0;
+  if (states) std::memcpy(states, t->states.data(), sizeof(double) * t->states.size());
+  if (actions) std::memcpy(actions, t->actions.data(), sizeof(double) * t->actions.size());
+  if (times) std::memcpy(times, t->times.data(), sizeof(double) * t->times.size());
+  if (residual) std::memcpy(residual, t->residual.data(), sizeof(double) * t->residual.size());
+  if (costs) std::memcpy(costs, t->costs.data(), sizeof(double) * t->costs.size());
+  if (trace && t->dim_trace) std::memcpy(trace, t->trace.data(), sizeof(double) * (size_t)t->horizon * t->dim_trace);
+  if (total_return) *total_return = t->total_return;
+  if (failure) *failure = t->failure;
+  return t->horizon;
+}
+void* psp_engine(void* h) { return ((CudaSamplingPlanner*)h)->engine(); }
+
+}  // extern "C"

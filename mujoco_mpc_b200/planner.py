@@ -1,0 +1,157 @@
+"""ctypes binding of the host-side planner library (libps_planner.so: CudaSamplingPlanner, the
+C++ drop-in for mjpc::SamplingPlanner).  Method names follow the reference's Planner interface."""
+import ctypes
+import os
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libps_planner.so")
+_dp = ctypes.POINTER(ctypes.c_double)
+_LIB = None
+ALLGATHER = ctypes.CFUNCTYPE(ctypes.c_int, ctypes.c_void_p, _dp, _dp, ctypes.c_int)
+
+
+def lib():
+    global _LIB
+    if _LIB is None:
+        if not os.path.exists(LIB_PATH):
+            raise RuntimeError(f"{LIB_PATH} not built (python -c 'from mujoco_mpc_b200 import build; build.build(); build.build_host()')")
+        ctypes.CDLL(os.path.join(_HERE, "libps_engine.so"), mode=ctypes.RTLD_GLOBAL)
+        L = ctypes.CDLL(LIB_PATH)
+        L.psp_create.restype = ctypes.c_void_p
+        L.psp_engine.restype = ctypes.c_void_p
+        L.psp_candidate_score.restype = ctypes.c_double
+        L.psp_improvement.restype = ctypes.c_double
+        _LIB = L
+    return _LIB
+
+
+def _p(a):
+    return a.ctypes.data_as(_dp) if a is not None else None
+
+
+def _arr(x):
+    return np.ascontiguousarray(np.asarray(x, dtype=np.float64))
+
+
+def select_winner(records):
+    """Cross-rank min-loc over winner records [world][3 + P*nu] (host logic, no GPU needed)."""
+    r = _arr(records)
+    return lib().psp_select_winner(_p(r), r.shape[0], r.shape[1])
+
+
+class CudaSamplingPlanner:
+    def __init__(self, model, task, device=0):
+        self.L = lib()
+        self.model, self.task = model, task
+        self.h = ctypes.c_void_p(self.L.psp_create(ctypes.byref(model.c_struct()), ctypes.byref(task), device))
+        self.ns = model.nq + model.nv + model.na
+        self._cb = None
+        self.horizon = 0
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.L.psp_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def Reset(self, horizon, initial_repeated_action=None):
+        a = _arr(initial_repeated_action) if initial_repeated_action is not None else None
+        self.L.psp_reset(self.h, horizon, _p(a))
+
+    def configure(self, num_trajectory=-1, interpolation=-1, num_spline_points=-1, sigma0=-1.0, sigma1=-1.0, sliding=-1):
+        self.L.psp_configure(self.h, num_trajectory, interpolation, num_spline_points, ctypes.c_double(sigma0),
+                             ctypes.c_double(sigma1), sliding)
+
+    def SetState(self, state, time, mocap=None, userdata=None):
+        s = _arr(state); mo = _arr(mocap) if mocap is not None else None; ud = _arr(userdata) if userdata is not None else None
+        self.L.psp_set_state(self.h, _p(s), _p(mo), _p(ud), ctypes.c_double(time))
+
+    def SetTask(self, task):
+        self.task = task
+        self.L.psp_set_task(self.h, ctypes.byref(task))
+
+    def SetNoise(self, z, use_std2=None):
+        if z is None:
+            self.L.psp_set_noise(self.h, None, None, 0); return
+        z = _arr(z)
+        u = np.ascontiguousarray(use_std2, dtype=np.uint8) if use_std2 is not None else None
+        self.L.psp_set_noise(self.h, _p(z), u.ctypes.data_as(ctypes.POINTER(ctypes.c_ubyte)) if u is not None else None, z.shape[0])
+
+    def SetSeed(self, seed):
+        self.L.psp_set_seed(self.h, ctypes.c_ulonglong(seed))
+
+    def SetSharding(self, rank, world, gather):
+        """gather(mine: np.ndarray[count]) -> np.ndarray[world, count]"""
+        def cb(ctx, mine, all_, count):
+            try:
+                m = np.ctypeslib.as_array(mine, shape=(count,)).copy()
+                out = _arr(gather(m)).reshape(-1)
+                ctypes.memmove(all_, out.ctypes.data, out.size * 8)
+                return 0
+            except Exception:
+                return -1
+        self._cb = ALLGATHER(cb)
+        self.L.psp_set_sharding(self.h, rank, world, self._cb, None)
+
+    def OptimizePolicy(self, horizon):
+        self.horizon = horizon
+        self.L.psp_optimize_policy(self.h, horizon)
+
+    def OptimizePolicyCandidates(self, ncandidates, horizon):
+        self.horizon = horizon
+        return self.L.psp_optimize_policy_candidates(self.h, ncandidates, horizon)
+
+    def CandidateScore(self, c):
+        return self.L.psp_candidate_score(self.h, c)
+
+    def ActionFromCandidatePolicy(self, c, time):
+        a = np.zeros(max(self.model.nu, 1)); self.L.psp_action_from_candidate_policy(self.h, _p(a), c, ctypes.c_double(time))
+        return a[:self.model.nu]
+
+    def CopyCandidateToPolicy(self, c):
+        self.L.psp_copy_candidate_to_policy(self.h, c)
+
+    def NominalTrajectory(self, horizon):
+        self.horizon = horizon
+        self.L.psp_nominal_trajectory(self.h, horizon)
+
+    def ActionFromPolicy(self, time, use_previous=False):
+        a = np.zeros(max(self.model.nu, 1)); self.L.psp_action_from_policy(self.h, _p(a), ctypes.c_double(time), int(use_previous))
+        return a[:self.model.nu]
+
+    @property
+    def winner(self):
+        return self.L.psp_winner(self.h)
+
+    @property
+    def improvement(self):
+        return self.L.psp_improvement(self.h)
+
+    def NumParameters(self):
+        return self.L.psp_num_parameters(self.h)
+
+    def policy(self, previous=False):
+        t = np.zeros(64); k = np.zeros(64 * max(self.model.nu, 1))
+        P = self.L.psp_get_policy(self.h, int(previous), _p(t), _p(k))
+        return t[:P].copy(), k[:P * self.model.nu].reshape(P, self.model.nu).copy()
+
+    def timers(self):
+        a, b, c = ctypes.c_double(), ctypes.c_double(), ctypes.c_double()
+        self.L.psp_timers(self.h, ctypes.byref(a), ctypes.byref(b), ctypes.byref(c))
+        return dict(noise_us=a.value, rollouts_us=b.value, policy_update_us=c.value)
+
+    def BestTrajectory(self):
+        H, m, t = self.horizon, self.model, self.task
+        st = np.zeros((H, self.ns)); ac = np.zeros((H, m.nu)); tm = np.zeros(H); rs = np.zeros((H, t.num_residual)); cs = np.zeros(H)
+        tr = np.zeros((H, max(1, 3 * t.num_trace))); ret = ctypes.c_double(); fail = ctypes.c_int()
+        h = self.L.psp_best_trajectory(self.h, _p(st), _p(ac), _p(tm), _p(rs), _p(cs), _p(tr), ctypes.byref(ret), ctypes.byref(fail))
+        if h == 0:
+            return None
+        return dict(states=st, actions=ac, times=tm, residual=rs, costs=cs, trace=tr[:, :3 * t.num_trace], total_return=ret.value,
+                    failure=bool(fail.value))
