@@ -102,8 +102,15 @@ void CudaSamplingPlanner::SetTask(const PsTask* task) {
   if (ps_set_task(engine_, task)) Fail("ps_set_task");
 }
 
+// The tensor is [N][P][nu]; P is only fixed once the nominal has been resampled, so the upload is
+// deferred to the next OptimizePolicyCandidates (after ps_set_nominal).
 void CudaSamplingPlanner::SetNoise(const double* z, const unsigned char* use_std2, int N) {
-  if (ps_set_noise(engine_, z, use_std2, N)) Fail("ps_set_noise");
+  noise_pending_ = true; noise_n_ = z ? N : 0;
+  noise_z_.clear(); noise_std2_.clear();
+  if (z) {
+    noise_z_.assign(z, z + (size_t)N * policy.num_spline_points * model_->nu);
+    if (use_std2) noise_std2_.assign(use_std2, use_std2 + N);
+  }
 }
 void CudaSamplingPlanner::SetSeed(unsigned long long seed) { ps_set_seed(engine_, seed); }
 void CudaSamplingPlanner::SetSharding(int rank, int world, AllGatherFn fn, void* ctx) {
@@ -157,6 +164,10 @@ int CudaSamplingPlanner::OptimizePolicyCandidates(int ncandidates, int horizon) 
   if (ps_set_options(engine_, model_->opt_timestep, model_->opt_integrator)) Fail("ps_set_options");   // agent.cc:275-276
   if (ps_set_state(engine_, state.data(), mocap.data(), userdata.data(), time)) Fail("ps_set_state");
   if (ps_set_nominal(engine_, policy.plan.times().data(), policy.plan.values().data(), P, interpolation_)) Fail("ps_set_nominal");
+  if (noise_pending_) {
+    if (ps_set_noise(engine_, noise_n_ ? noise_z_.data() : nullptr, noise_std2_.empty() ? nullptr : noise_std2_.data(), noise_n_)) Fail("ps_set_noise");
+    noise_pending_ = false;
+  }
   int local_winner = 0; double wret = 0, nret = 0;
   if (ps_rollouts(engine_, num_trajectory, horizon, noise_exploration[0], noise_exploration[1], rank_ * num_trajectory,
                   &local_winner, &wret, &nret)) Fail("ps_rollouts");

@@ -89,6 +89,7 @@ class CudaSamplingPlanner {
   double nominal_return_ = 0, winner_return_ = 0;
   int rank_ = 0, world_ = 1; AllGatherFn gather_ = nullptr; void* gather_ctx_ = nullptr;
   bool winner_is_local_ = true; int local_winner_ = 0;
+  std::vector<double> noise_z_; std::vector<unsigned char> noise_std2_; int noise_n_ = 0; bool noise_pending_ = false;
   mutable std::shared_mutex mtx_;
 };
 

@@ -40,28 +40,53 @@ def test_closed_loop_iterations_match_oracle(oracle_lib, name, interp):
     pl.close()
 
 
+def load_particle_fixture(timestep=None):
+    import os
+    from mujoco_mpc_b200 import mjcf, task as T
+    m = mjcf.load(os.path.join(os.path.dirname(__file__), "fixtures", "particle_task.xml"))
+    if timestep:
+        m.v["opt_timestep"] = timestep; m._c = None
+    return m, T.make_task(m, "ParticleTest")
+
+
 def test_random_search_reaches_goal():
-    # sampling_planner_test.cc:44-113 on the in-tree particle model (fixed mocap goal variant),
-    # with device-generated noise: final state within 1e-1 of the goal, actions within ctrlrange
-    model, task, s = registry.load("Particle")
-    from mujoco_mpc_b200 import task as T
-    task.task_id = T.TASK_IDS["ParticleFixed"]
-    pl = CudaSamplingPlanner(model, task); pl.configure(num_trajectory=128, interpolation=0, num_spline_points=11, sigma0=0.05)
+    # sampling_planner_test.cc:44-113, same fixture and settings: particle_task.xml, dt 0.1, 26 steps,
+    # 10 samples, noise_exploration[0] = 0.01, 1000 OptimizePolicy iterations from the same state;
+    # final best-trajectory state within 1e-1 of (goal, 0 velocity); actions inside ctrlrange
+    model, task = load_particle_fixture(timestep=0.1)
+    pl = CudaSamplingPlanner(model, task)
+    pl.configure(sigma0=0.01)
     pl.SetSeed(3)
-    state = np.zeros(4); goal = np.array([0.1, 0.1])
-    mocap = np.array([goal[0], goal[1], 0.01, 1, 0, 0, 0.0])
-    H = 26
-    for _ in range(150):
-        pl.SetState(state, 0.0, mocap=mocap); pl.OptimizePolicy(H)
+    steps = int(max(min(2.5 / 0.1 + 1, 512), 1))
+    mocap = np.array([0.25, 0, 0.01, 1, 0, 0, 0.0])
+    pl.SetState(np.zeros(4), 0.0, mocap=mocap)
+    for _ in range(1000):
+        pl.OptimizePolicy(steps)
     bt = pl.BestTrajectory()
-    assert np.linalg.norm(bt["states"][-1][:2] - goal) < 1e-1
-    assert np.all(bt["actions"] >= -1 - 1e-12) and np.all(bt["actions"] <= 1 + 1e-12)
+    final = bt["states"][steps - 1]
+    assert abs(final[0] - 0.25) < 1e-1 and abs(final[1] - 0.0) < 1e-1 and abs(final[2]) < 1e-1 and abs(final[3]) < 1e-1
+    assert np.all(bt["actions"][:steps - 1] <= 1.0) and np.all(bt["actions"][:steps - 1] >= -1.0)
+    pl.close()
+
+
+def test_rollout_residual_state_alignment():
+    # rollout_test.cc:127-144: for the copy-residual task, residual[t] == states[t] (minus the goal in
+    # the position block) -- pins that the residual is evaluated at the PRE-step state
+    model, task = load_particle_fixture()
+    pl = CudaSamplingPlanner(model, task)
+    pl.configure(num_trajectory=4, sigma0=0.3)
+    pl.SetSeed(1)
+    st = np.array([0.05, -0.02, 0.3, -0.1]); mocap = np.array([0.1, 0.2, 0.01, 1, 0, 0, 0.0])
+    pl.SetState(st, 0.0, mocap=mocap); pl.OptimizePolicy(100)
+    bt = pl.BestTrajectory()
+    expect = bt["states"].copy(); expect[:, 0] -= 0.1; expect[:, 1] -= 0.2
+    assert np.abs(expect - bt["residual"]).sum() < 1e-5
     pl.close()
 
 
 def test_previous_policy_is_bit_exact():
     # agent_test.cc:204-262: ActionFromPolicy(use_previous=true) returns the pre-iteration policy exactly
-    model, task, s = registry.load("Particle")
+    model, task = load_particle_fixture(timestep=0.1)
     pl = CudaSamplingPlanner(model, task); pl.configure(num_trajectory=128)
     pl.SetSeed(5)
     pl.SetState(np.zeros(4), 0.0); pl.OptimizePolicy(51)
