@@ -32,6 +32,7 @@ WORKLOADS = {
 }
 DEFAULT_WORKLOAD = "acrobot+particle_4096_cubic"
 METRIC = "rollout sample-steps/sec"
+CONST_BYTES = {"tiny": 6144, "planar": 11264, "legged": 30720}   # sizeof(Constants<T>) rounded up
 # FP64 flops per sample-step (FMA = 2), from the ncu instruction counts of the rollout kernel
 # (profiles/flops_per_sample_step.json, see DESIGN.md "Measurement")
 FLOPS_FILE = os.path.join(ROOT, "profiles", "flops_per_sample_step.json")
@@ -197,19 +198,39 @@ def main():
                 if world > 1:
                     dist.all_gather_into_tensor(gathered[k], rec_views[k])   # min-loc over ranks (cost, index, knots)
                     g = gathered[k].view(world, -1)
-                    best = torch.argmin(g[:, 0] + 0.0)            # ties -> lowest rank == lowest global index
+                    tie = g[:, 0] == g[:, 0].min()                # lowest return, ties -> lowest global index
+                    best = torch.where(tie, g[:, 1], torch.full_like(g[:, 1], float("inf"))).argmin()
                     _ = g[best]
                 b.record(st)
             b.synchronize()
             ms += a.elapsed_time(b)
         return ms
 
+    # end-to-end arm: the drop-in host planner (CudaSamplingPlanner), host buffers in and out
+    from mujoco_mpc_b200.planner import CudaSamplingPlanner
+    planners = []
+    for c in cases:
+        pl = CudaSamplingPlanner(c["model"], c["task"], device=local)
+        pl.configure(num_trajectory=c["N"], interpolation=c["interp"], num_spline_points=c["P"], sigma0=c["sigma"], sigma1=0.0)
+        pl.SetSeed(2024)
+        if world > 1:
+            cnt = 3 + c["P"] * c["model"].nu
+            dev_in = torch.empty(cnt, dtype=torch.float64, device=f"cuda:{local}")
+            dev_out = torch.empty(world * cnt, dtype=torch.float64, device=f"cuda:{local}")
+            def gather(mine, dev_in=dev_in, dev_out=dev_out):
+                dev_in.copy_(torch.from_numpy(mine)); dist.all_gather_into_tensor(dev_out, dev_in)
+                return dev_out.cpu().numpy()
+            pl.SetSharding(rank, world, gather)
+        planners.append(pl)
+    e2e_time = [0.0]
+
     def e2e_step():
-        """public host-buffer path: state + nominal in (H2D), winner out (D2H)"""
-        for e, c in zip(engines, cases):
-            e.set_state(c["state"], 0.0)
-            e.set_nominal(c["times"], c["knots"], c["interp"])
-            e.rollouts(c["N"], c["H"], c["sigma"], 0.0, c["offset"])
+        """public API: SetState (host state) -> OptimizePolicy (resample, H2D, K1-K3, D2H winner) -> ActionFromPolicy"""
+        for pl, c in zip(planners, cases):
+            pl.SetState(c["state"], e2e_time[0])
+            pl.OptimizePolicy(c["H"])
+            pl.ActionFromPolicy(e2e_time[0])
+        e2e_time[0] += 0.01
 
     def barrier():
         if world > 1:
@@ -247,7 +268,8 @@ def main():
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     e2e_value = units / float(t.item())
-    h2d = sum(8 * (c["state"].size + 1 + c["P"] + c["P"] * c["model"].nu) + 0 for c in cases)
+    # per iteration: the whole Constants block (model + task + plan, pinned) + nominal knots go up, the winner record comes back
+    h2d = sum(CONST_BYTES.get(e.variant(), 0) + 8 * c["P"] * c["model"].nu for e, c in zip(engines, cases))
     d2h = sum(8 * (3 + c["P"] * c["model"].nu) for c in cases)
 
     if rank == 0:
@@ -285,6 +307,8 @@ def main():
         print(json.dumps(line))
     for e in engines:
         e.close()
+    for pl in planners:
+        pl.close()
     if world > 1:
         dist.destroy_process_group()
 

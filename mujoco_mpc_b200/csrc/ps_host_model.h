@@ -59,6 +59,9 @@ inline int fill_model(const PsModel* s, const PairList& pl, void* out, std::stri
   CAP(nsite, T::NSITE) CAP(nmocap, T::NMOCAP) CAP(nsensor, T::NSENSOR)
 #undef CAP
   if ((int)pl.g1.size() > T::NPAIR) { *why = "collision pairs exceed capacity"; return -1; }
+  if (s->opt_integrator == PS_INT_RK4) { *why = "RK4 integrator is not supported (Euler / implicit / implicitfast)"; return -1; }
+  if (s->opt_solver != PS_SOL_NEWTON && !(s->opt_disableflags & PS_DSBL_CONSTRAINT)) { *why = "only the Newton solver is supported"; return -1; }
+  if (pl.unsupported) { *why = "model has colliding geom pairs outside the supported narrow-phase set"; return -1; }
   if (s->opt_cone == PS_CONE_ELLIPTIC && !T::ELLIPTIC && !pl.g1.empty()) { *why = "elliptic cones not in this instantiation"; return -1; }
   m.timestep = s->opt_timestep; m.impratio = s->opt_impratio; m.tolerance = s->opt_tolerance; m.ls_tolerance = s->opt_ls_tolerance;
   m.density = s->opt_density; m.viscosity = s->opt_viscosity; m.meaninertia = s->stat_meaninertia;
