@@ -32,7 +32,7 @@ WORKLOADS = {
 }
 DEFAULT_WORKLOAD = "acrobot+particle_4096_cubic"
 METRIC = "rollout sample-steps/sec"
-CONST_BYTES = {"tiny": 6144, "planar": 11264, "legged": 30720}   # sizeof(Constants<T>) rounded up
+CONST_BYTES = {"tiny": 6144, "planar": 11264, "legged": 23552}   # sizeof(Constants<T>) rounded up
 # FP64 flops per sample-step (FMA = 2), from the ncu instruction counts of the rollout kernel
 # (profiles/flops_per_sample_step.json, see DESIGN.md "Measurement")
 FLOPS_FILE = os.path.join(ROOT, "profiles", "flops_per_sample_step.json")
@@ -88,6 +88,9 @@ def make_cases(workload, rank, world):
     cases = []
     for name, N, interp, H in WORKLOADS[workload]:
         model, task, s = registry.load(name)
+        if name == "Quadruped Flat":   # planning state of a trotting robot heading for the goal
+            from mujoco_mpc_b200 import task as _task
+            _task.quadruped_snapshot(model, task, mode="Quadruped", gait="Trot", time=0.0)
         H = H or s["steps"]
         P = min(s["num_spline_points"], 36)
         state = synthetic_state(model)

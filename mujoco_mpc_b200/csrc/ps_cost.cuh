@@ -7,6 +7,7 @@
 // path), mjpc/task.cc:71-110 (CostTerms / CostValue), mjpc/tasks/<task>/<task>.cc (Residual).
 #pragma once
 #include "ps_step.cuh"
+#include "ps_quadruped.cuh"
 
 namespace ps {
 
@@ -77,9 +78,6 @@ enum { TASK_PARTICLE = 0, TASK_PARTICLE_FIXED, TASK_PARTICLE_TEST, TASK_CARTPOLE
        TASK_WALKER, TASK_QUADRUPED };
 
 template <class T>
-PS_FN void quadruped_residual(const DevModel<T>& m, const RolloutData<T>& d, const DevTask& t, double* r);
-
-template <class T>
 PS_FN void task_residual(const DevModel<T>& m, const RolloutData<T>& d, const DevTask& t, double* r) {
   double s0[3], s1[3];
   switch (t.task_id) {
@@ -121,11 +119,6 @@ PS_FN void task_residual(const DevModel<T>& m, const RolloutData<T>& d, const De
     case TASK_QUADRUPED: quadruped_residual(m, d, t, r); break;
     default: break;
   }
-}
-
-template <class T>
-PS_FN void quadruped_residual(const DevModel<T>& m, const RolloutData<T>& d, const DevTask& t, double* r) {
-  for (int i = 0; i < t.num_residual; i++) r[i] = 0;   // filled in by the quadruped row
 }
 
 }  // namespace ps

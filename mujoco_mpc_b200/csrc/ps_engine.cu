@@ -28,7 +28,7 @@ struct PsEngine_ {
   const Variant* var = nullptr;
   void* h_const = nullptr; void* d_const = nullptr;             // pinned host mirror + device copy
   int nq = 0, nv = 0, nu = 0, na = 0, nmocap = 0, nsensor = 0, ns = 0;
-  std::vector<int> sensor_type;
+  std::vector<int> sensor_type; bool ray_ok = false;
   std::vector<double> ctrlrange;
   DevTask task{}; bool have_task = false, have_model = false;
   int P = 0, interp = 0, H = 0, N = 0, cap = 0, stride = 0, nelem = 0, nblocks = 0;
@@ -107,6 +107,7 @@ int ps_set_model(PsEngine* e, const PsModel* m) {
   CU(cudaMalloc(&e->d_const, chosen->const_bytes));
   e->nq = m->nq; e->nv = m->nv; e->nu = m->nu; e->na = m->na; e->nmocap = m->nmocap; e->nsensor = m->nsensor; e->ns = m->nq + m->nv + m->na;
   e->sensor_type.assign(m->sensor_type, m->sensor_type + m->nsensor);
+  e->ray_ok = ray_scenery_ok(m);
   e->ctrlrange.assign(m->actuator_ctrlrange, m->actuator_ctrlrange + 2 * m->nu);
   if (e->d_ctrlrange) cudaFree(e->d_ctrlrange);
   CU(cudaMalloc(&e->d_ctrlrange, sizeof(double) * 2 * (m->nu > 0 ? m->nu : 1)));
@@ -133,6 +134,11 @@ int ps_set_task(PsEngine* e, const PsTask* t) {
   if (!e || !e->have_model) return fail("ps_set_task: set the model first");
   DevTask d; int need_sub = 0; std::string why;
   if (convert_task(t, e->sensor_type.data(), e->nsensor, &d, &need_sub, &why)) return fail("ps_set_task: " + why);
+  if (d.task_id == TASK_QUADRUPED) {
+    if (!e->ray_ok) return fail("ps_set_task: Quadruped needs static plane/sphere/box group-0 scenery for its ground ray casts");
+    if (e->nq != 19 || e->nu != 12) return fail("ps_set_task: Quadruped expects a free joint + 12 actuated joints");
+    for (int k = 0; k < 3; k++) if (t->sensor_id[k] < 0) return fail("ps_set_task: Quadruped sensor ids (subtreecom, subtreelinvel, angmom) missing");
+  }
   e->task = d; e->have_task = true;
   e->var->task(e->h_const, d, need_sub);
   return 0;

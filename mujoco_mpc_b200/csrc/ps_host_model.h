@@ -16,7 +16,7 @@ namespace ps {
 //                        NQ NV NU NA NBODY NJNT NGEOM NSITE NMOCAP NPAIR MAXCON MAXEFC NSENSOR ELLIPTIC
 typedef Traits<2, 2, 2, 0, 4, 2, 8, 2, 1, 0, 0, 4, 12, false> TinyT;          // particle, cartpole, acrobot
 typedef Traits<9, 9, 6, 5, 9, 9, 18, 6, 1, 8, 14, 64, 20, false> PlanarT;    // swimmer, walker
-typedef Traits<19, 18, 12, 0, 16, 13, 40, 24, 2, 48, 16, 96, 24, true> LeggedT;  // quadruped (free joint, elliptic cones)
+typedef Traits<19, 18, 12, 0, 16, 13, 44, 8, 2, 40, 16, 96, 16, true> LeggedT;  // quadruped (free joint, elliptic cones)
 
 struct PairList { std::vector<int> g1, g2; int unsupported = 0; };
 
@@ -48,6 +48,19 @@ inline PairList static_pairs(const PsModel* m) {
       pl.g1.push_back(g1); pl.g2.push_back(g2);
     }
   return pl;
+}
+
+// Ground() (utilities.cc:538-556) ray-casts against every group-0 geom.  The device carries static
+// plane / sphere / box scenery; this reports whether that covers the model's whole group 0.
+inline bool ray_scenery_ok(const PsModel* s) {
+  int n = 0;
+  for (int g = 0; g < s->ngeom; g++) {
+    if (s->geom_group[g] != 0) continue;
+    const int tp = s->geom_type[g];
+    if (weld_body(s, s->geom_bodyid[g]) != 0 || !(tp == PS_GEOM_PLANE || tp == PS_GEOM_SPHERE || tp == PS_GEOM_BOX)) return false;
+    if (++n > kMaxRayGeom) return false;
+  }
+  return n > 0;
 }
 
 template <class T>
@@ -108,7 +121,14 @@ inline int fill_model(const PsModel* s, const PairList& pl, void* out, std::stri
   for (int i = 0; i < s->nv; i++) if (s->dof_damping[i] > 0) m.any_damping = 1;
   for (int p = 0; p < m.npair; p++) { m.pair_geom1[p] = pl.g1[p]; m.pair_geom2[p] = pl.g2[p]; m.geom_used[pl.g1[p]] = 1; m.geom_used[pl.g2[p]] = 1; }
   for (int i = 0; i < s->nsensor; i++) if (s->sensor_objtype[i] == PS_OBJ_GEOM && s->sensor_objid[i] >= 0) m.geom_used[s->sensor_objid[i]] = 1;
-  if (T::ELLIPTIC) for (int g = 0; g < s->ngeom; g++) m.geom_used[g] = 1;   // legged residual reads geom frames directly
+  // Ground() ray candidates: group-0 geoms; the device carries static plane / sphere / box scenery only
+  m.ray_complete = 1;
+  for (int g = 0; g < s->ngeom; g++) {
+    if (s->geom_group[g] != 0) continue;
+    const int tp = s->geom_type[g];
+    const bool ok = weld_body(s, s->geom_bodyid[g]) == 0 && (tp == PS_GEOM_PLANE || tp == PS_GEOM_SPHERE || tp == PS_GEOM_BOX);
+    if (ok && m.nray < kMaxRayGeom) { m.ray_geom[m.nray++] = g; m.geom_used[g] = 1; } else m.ray_complete = 0;
+  }
   return 0;
 }
 

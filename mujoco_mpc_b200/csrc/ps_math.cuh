@@ -18,13 +18,13 @@ PS_HD void cross3(double* r, const double* a, const double* b) {
 PS_HD double norm3(const double* a) { return sqrt(dot3(a, a)); }
 PS_HD double unit3(double* a) {
   double n = norm3(a);
-  if (n < kMinVal) { a[0] = 1; a[1] = 0; a[2] = 0; } else { a[0] /= n; a[1] /= n; a[2] /= n; }
+  if (n < kMinVal) { a[0] = 1; a[1] = 0; a[2] = 0; } else { const double inv = 1 / n; a[0] *= inv; a[1] *= inv; a[2] *= inv; }
   return n;
 }
 PS_HD void unit4(double* q) {
   double n = sqrt(q[0] * q[0] + q[1] * q[1] + q[2] * q[2] + q[3] * q[3]);
   if (n < kMinVal) { q[0] = 1; q[1] = 0; q[2] = 0; q[3] = 0; }
-  else if (fabs(n - 1) > kMinVal) { q[0] /= n; q[1] /= n; q[2] /= n; q[3] /= n; }
+  else if (fabs(n - 1) > kMinVal) { const double inv = 1 / n; q[0] *= inv; q[1] *= inv; q[2] *= inv; q[3] *= inv; }
 }
 PS_HD void mat_vec3(double* r, const double* M, const double* v) {
   double x = M[0] * v[0] + M[1] * v[1] + M[2] * v[2];

@@ -27,6 +27,7 @@ constexpr int kMaxTerms = 16;       // cost terms carried on device (the six tas
 constexpr int kMaxResidual = 48;    // quadruped: 42
 constexpr int kMaxTaskParam = 16;
 constexpr int kMaxTaskAux = 96;
+constexpr int kMaxRayGeom = 8;
 
 // compile-time capacities of one engine instantiation
 template <int NQ_, int NV_, int NU_, int NA_, int NBODY_, int NJNT_, int NGEOM_, int NSITE_,
@@ -69,6 +70,9 @@ struct alignas(16) DevModel {
   int nq, nv, nu, na, nbody, njnt, ngeom, nsite, nmocap, nsensor, npair;
   int any_damping;     // some dof has damping > 0 (Euler implicit-damping branch)
   int need_subtreevel; // a subtreelinvel / subtreeangmom sensor is read by the task
+  int nray;            // group-0 scenery the Ground() ray cast visits (utilities.cc:538-556)
+  int ray_geom[kMaxRayGeom];
+  int ray_complete;    // every group-0 geom is static plane/sphere/box scenery and fits ray_geom
   int pad_;
   double qpos0[T::NQ], qpos_spring[T::NQ];
   // bodies

@@ -22,13 +22,13 @@ inline void cross(double* r, const double* a, const double* b) {
 inline double norm3(const double* a) { return std::sqrt(dot3(a, a)); }
 inline double normalize3(double* a) {
   double n = norm3(a);
-  if (n < kMinVal) { a[0] = 1; a[1] = 0; a[2] = 0; } else { a[0] /= n; a[1] /= n; a[2] /= n; }
+  if (n < kMinVal) { a[0] = 1; a[1] = 0; a[2] = 0; } else { const double inv = 1 / n; a[0] *= inv; a[1] *= inv; a[2] *= inv; }
   return n;
 }
 inline double normalize4(double* q) {
   double n = std::sqrt(q[0] * q[0] + q[1] * q[1] + q[2] * q[2] + q[3] * q[3]);
   if (n < kMinVal) { q[0] = 1; q[1] = q[2] = q[3] = 0; }
-  else if (std::fabs(n - 1) > kMinVal) { for (int i = 0; i < 4; i++) q[i] /= n; }
+  else if (std::fabs(n - 1) > kMinVal) { const double inv = 1 / n; for (int i = 0; i < 4; i++) q[i] *= inv; }
   return n;
 }
 // r = M * v (M row-major 3x3)

@@ -1,0 +1,46 @@
+"""TEST INFRASTRUCTURE: ctypes driver for tests/hostsim/hostsim.cc (the engine's kernel-source
+headers compiled with g++).  Used by the CPU test-suite and by hand to diff the device code path
+against the oracle in the GPU-less container.  Not imported by the product."""
+import ctypes
+import os
+import subprocess
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_LIB = os.path.join(_HERE, "libhostsim.so")
+_CSRC = os.path.join(_HERE, "..", "..", "mujoco_mpc_b200", "csrc")
+
+
+def build(force=False):
+    src = os.path.join(_HERE, "hostsim.cc")
+    deps = [src] + [os.path.join(_CSRC, f) for f in os.listdir(_CSRC) if f.endswith((".cuh", ".h"))]
+    if not force and os.path.exists(_LIB) and all(os.path.getmtime(_LIB) >= os.path.getmtime(d) for d in deps):
+        return _LIB
+    cmd = ["g++", "-std=c++17", "-O2", "-ffp-contract=off", "-fPIC", "-shared", "-x", "c++", src, "-o", _LIB]
+    subprocess.run(cmd, check=True)
+    return _LIB
+
+
+def _p(a):
+    return a.ctypes.data_as(ctypes.POINTER(ctypes.c_double))
+
+
+def rollout(model, task, state, time, times, knots, interp, H, timestep, integrator, mocap=None):
+    """One rollout of the device code path on the host.  knots: [P][nu].  Returns a dict with
+    states [H][ns], actions [H][nu], residual [H][nr], costs [H], total, flags, variant."""
+    L = ctypes.CDLL(build())
+    ns, nu, nr = model.nq + model.nv + model.na, model.nu, task.num_residual
+    state = np.ascontiguousarray(state, dtype=np.float64)
+    times = np.ascontiguousarray(times, dtype=np.float64)
+    knots = np.ascontiguousarray(knots, dtype=np.float64).reshape(len(times), nu)
+    states = np.zeros((H, ns)); actions = np.zeros((H, nu)); residual = np.zeros((H, nr)); costs = np.zeros(H)
+    total = ctypes.c_double(0); flags = ctypes.c_int(0); variant = ctypes.create_string_buffer(256)
+    mo = None if mocap is None else np.ascontiguousarray(mocap, dtype=np.float64)
+    rc = L.hs_rollout(ctypes.byref(model.c_struct()), ctypes.byref(task), _p(state), None if mo is None else _p(mo),
+                      ctypes.c_double(time), _p(times), _p(knots), len(times), int(interp), int(H), ctypes.c_double(timestep),
+                      int(integrator), _p(states), _p(actions), _p(residual), _p(costs), ctypes.byref(total),
+                      ctypes.byref(flags), variant, 256)
+    if rc != 0:
+        raise RuntimeError(f"hs_rollout failed ({rc}): {variant.value.decode()}")
+    return dict(states=states, actions=actions, residual=residual, costs=costs, total=total.value, flags=flags.value,
+                variant=variant.value.decode())

@@ -16,8 +16,10 @@ def rel_err(a, b):
     return np.abs(a - b).max() / max(1.0, np.abs(b).max())
 
 
-def run_case(name, N, interp, H=None, seed=2024, sigma=None, time=0.37, warm=True):
+def run_case(name, N, interp, H=None, seed=2024, sigma=None, time=0.37, warm=True, prep=None):
     model, task, s = registry.load(name)
+    if prep is not None:
+        prep(model, task)
     H = H or s["steps"]
     P = min(s["num_spline_points"], 36)
     sigma = s["exploration"] if sigma is None else sigma
@@ -79,6 +81,31 @@ def test_parity_planar_models(oracle_lib, name, N):
     # Swimmer: implicit integrator + fluid forces + activation states + joint limits;
     # Walker: capsule-plane contacts, pyramidal cones, Newton solver
     run_case(name, N=N, interp=2)
+
+
+QUAD_CASES = [  # mode, gait, walk angvel: every branch of quadruped.cc:33-221
+    ("Quadruped", "Trot", 0.0), ("Quadruped", "Stand", 0.0), ("Biped", "Trot", 0.0), ("Walk", "Walk", 0.0),
+    ("Walk", "Canter", 0.5), ("Scramble", "Gallop", 0.0), ("Flip", "Stand", 0.0)]
+
+
+@pytest.mark.parametrize("mode,gait,angvel", QUAD_CASES)
+def test_parity_quadruped(oracle_lib, mode, gait, angvel):
+    # free joint, 12 torque actuators, elliptic cones with condim-6 feet, frictionloss + joint limits,
+    # ground ray casts in the gait residual
+    from mujoco_mpc_b200 import task as T
+
+    def prep(model, task):
+        T.quadruped_snapshot(model, task, mode=mode, gait=gait, time=0.3, position=(0.1, 0.2), heading=(0.5, 0.1),
+                             speed=0.5, angvel=angvel)
+    ws, wr = run_case("Quadruped Flat", N=192, interp=2, prep=prep)
+    assert ws <= STATE_RTOL
+
+
+def test_parity_quadruped_one_second_horizon(oracle_lib):
+    # BASELINE config 4 geometry: 1 s horizon at the task's 10 ms agent timestep
+    from mujoco_mpc_b200 import task as T
+    run_case("Quadruped Flat", N=512, interp=2, H=101,
+             prep=lambda m, t: T.quadruped_snapshot(m, t, mode="Quadruped", gait="Trot", time=0.37))
 
 
 def test_first_iteration_zero_nominal(oracle_lib):
