@@ -156,8 +156,8 @@ PS_HD void complete_frame(double* f) {
   cross3(f + 6, f, f + 3);
 }
 
-template <class T>
-PS_FN void mix_contact_params(const DevModel<T>& m, int g1, int g2, Contact* con) {
+template <class T, class C>
+PS_FN void mix_contact_params(const DevModel<T>& m, int g1, int g2, C* con) {
   const int p1 = m.geom_priority[g1], p2 = m.geom_priority[g2];
   double fri[3];
   if (p1 != p2) {
@@ -481,12 +481,15 @@ PS_FN void newton_direction(const DevModel<T>& m, RolloutData<T>& d) {
       const double D = d.efc_D[r]; const double* J = d.efc_J + r * S;
       for (int i = 0; i < nv; i++) { if (J[i] == 0) continue; const double s = D * J[i]; for (int j = 0; j <= i; j++) H[i * S + j] += s * J[j]; }
     } else if (T::ELLIPTIC && st == ST_CONE && d.efc_type[r] == EFC_CONTACT_ELLIPTIC) {
+      // cone block J_c' (Hc J_c): T = Hc J_c first, then the symmetric update, one add per cone row
       const int ci = d.efc_id[r]; const int dim = d.contact[ci].dim; const double* CH = d.coneH + 36 * ci;
-      for (int a = 0; a < dim; a++) for (int b = 0; b < dim; b++) {
-        const double h = CH[a * dim + b]; if (h == 0) continue;
-        const double* Ja = d.efc_J + (r + a) * S; const double* Jb = d.efc_J + (r + b) * S;
-        for (int i = 0; i < nv; i++) { const double s = h * Ja[i]; if (s == 0) continue; for (int j = 0; j <= i; j++) H[i * S + j] += s * Jb[j]; }
+      double Tm[6 * S];
+      for (int a = 0; a < dim; a++) for (int j = 0; j < nv; j++) {
+        double t = 0; for (int b = 0; b < dim; b++) t += CH[a * dim + b] * d.efc_J[(r + b) * S + j];
+        Tm[a * S + j] = t;
       }
+      for (int i = 0; i < nv; i++) for (int j = 0; j <= i; j++)
+        for (int a = 0; a < dim; a++) H[i * S + j] += d.efc_J[(r + a) * S + i] * Tm[a * S + j];
       r += dim - 1;
     }
   }
@@ -498,7 +501,7 @@ PS_FN void newton_direction(const DevModel<T>& m, RolloutData<T>& d) {
     }
   double* x = d.sv_search;
   for (int i = 0; i < nv; i++) { double s = d.sv_grad[i]; for (int k = 0; k < i; k++) s -= H[i * S + k] * x[k]; x[i] = s / H[i * S + i]; }
-  for (int i = nv - 1; i >= 0; i--) { double s = x[i]; for (int k = i + 1; k < nv; k++) s -= H[k * S + i] * x[k]; x[i] = s / H[i * S + i]; }
+  for (int i = nv - 1; i >= 0; i--) { double s = x[i]; for (int k = nv - 1; k > i; k--) s -= H[k * S + i] * x[k]; x[i] = s / H[i * S + i]; }
   for (int i = 0; i < nv; i++) x[i] = -x[i];
 }
 

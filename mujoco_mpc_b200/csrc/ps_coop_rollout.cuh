@@ -1,0 +1,204 @@
+// Warp-cooperative rollout: forward pass, Euler integration (implicit joint damping), the
+// Trajectory::NoisyRollout time recursion (mjpc/trajectory.cc:100-210,312-326) and, on the device,
+// the persistent kernel that hands rollouts to warps.
+#pragma once
+#include "ps_coop_solver.cuh"
+#include "ps_cost.cuh"
+#include "ps_rollout.cuh"
+#ifdef __CUDACC__
+#include "ps_kernels.cuh"
+#endif
+
+namespace ps {
+
+// lanes a stage runs on: all of them, or (diagnostics) a single working lane
+PS_HD Lanes stage_lanes(const Lanes& L, int debug_serial, int stage) {
+#ifdef __CUDA_ARCH__
+  if ((debug_serial >> stage) & 1) { Lanes S; S.lane = L.lane == 0 ? 0 : (1 << 28); S.width = 1; return S; }
+#endif
+  return L;
+}
+
+template <class T>
+PS_FN void co_forward_pass(const Lanes& L, const DevModel<T>& m, CoopData<T>& d) {
+  const int dbg = m.debug_serial;
+  co_position_smooth(stage_lanes(L, dbg, 0), m, d);
+  co_make_constraints(stage_lanes(L, dbg, 1), m, d);
+  co_velocity_stage(stage_lanes(L, dbg, 2), m, d);
+  co_reference_acceleration(stage_lanes(L, dbg, 3), m, d);
+  if (m.need_subtreevel) co_subtree_velocity(stage_lanes(L, dbg, 4), m, d);
+  co_actuation_stage(stage_lanes(L, dbg, 5), m, d);
+  co_acceleration_stage(stage_lanes(L, dbg, 6), m, d);
+  co_constraint_stage(stage_lanes(L, dbg, 7), m, d);
+}
+
+// semi-implicit Euler with implicit joint damping (mj_Euler); other integrators stay with the
+// thread-per-rollout engine
+template <class T>
+PS_FN void co_integrate(const Lanes& L, const DevModel<T>& m, CoopData<T>& d) {
+  constexpr int S = T::NV; const int nv = m.nv; const double dt = m.timestep;
+  double* qacc = d.sv_x;
+  if (!m.any_damping || (m.disableflags & DSBL_EULERDAMP)) { CO_FOR(i, nv) qacc[i] = d.qacc[i]; L.sync(); }
+  else {
+    double* A = d.qH;
+    CO_FOR(w, nv * S) A[w] = d.qM[w];
+    L.sync();
+    CO_FOR(i, nv) { A[i * S + i] += dt * m.dof_damping[i]; qacc[i] = d.qfrc_smooth[i] + d.qfrc_constraint[i]; }
+    L.sync();
+    co_factor_tree(L, m, A, d.qLDiagInv);
+    co_solve_tree(L, m, qacc, A, d.qLDiagInv);
+  }
+  if (m.na && !(m.disableflags & DSBL_ACTUATION)) {
+    CO_FOR(i, m.nu) {
+      if (m.act_dyntype[i] == DYN_NONE) continue;
+      const int a = m.act_actadr[i];
+      double act = d.act[a];
+      if (m.act_dyntype[i] == DYN_FILTEREXACT) {
+        const double tau = fmax(kMinVal, m.act_dynprm[3 * i]);
+        act = act + d.act_dot[a] * tau * (1 - exp(-dt / tau));
+      } else act = act + d.act_dot[a] * dt;
+      if (m.act_actlimited[i]) act = clampd(act, m.act_actrange[2 * i], m.act_actrange[2 * i + 1]);
+      d.act[a] = act;
+    }
+  }
+  CO_FOR(i, nv) d.qvel[i] += qacc[i] * dt;
+  L.sync();
+  CO_FOR(j, m.njnt) {
+    const int qa = m.jnt_qposadr[j], da = m.jnt_dofadr[j], jt = m.jnt_type[j];
+    if (jt == JNT_FREE) {
+      for (int k = 0; k < 3; k++) d.qpos[qa + k] += dt * d.qvel[da + k];
+      quat_integrate(d.qpos + qa + 3, d.qvel + da + 3, dt);
+    } else if (jt == JNT_BALL) quat_integrate(d.qpos + qa, d.qvel + da, dt);
+    else d.qpos[qa] += dt * d.qvel[da];
+  }
+  if (L.lane == 0) d.time += dt;
+  L.sync();
+}
+
+// knots: SoA [P*nu][stride]; i = this rollout's column.  flags: bit0 failure, bit1 capacity overflow
+template <class T, bool WB>
+PS_FN double co_rollout(const Lanes& L, const DevModel<T>& m, const DevTask& task, const DevPlan<T>& plan, const double* knots,
+                        int stride, int i, const Writeback& wb, CoopData<T>& d, int* flags) {
+  const int nq = m.nq, nv = m.nv, na = m.na, nu = m.nu, ns = nq + nv + na, nr = task.num_residual;
+  const int H = plan.horizon, P = plan.num_spline_points, ntr = 3 * task.num_trace;
+  CO_FOR(k, nq) d.qpos[k] = plan.state[k];
+  CO_FOR(k, nv) { d.qvel[k] = plan.state[nq + k]; d.qacc_warmstart[k] = 0; d.qacc[k] = 0; }
+  CO_FOR(k, na) d.act[k] = plan.state[nq + nv + k];
+  CO_FOR(k, nu) d.ctrl[k] = 0;
+  CO_FOR(k, m.nmocap) { vcopy(d.mocap_pos + 3 * k, plan.mocap + 7 * k, 3); vcopy(d.mocap_quat + 4 * k, plan.mocap + 7 * k + 3, 4); }
+  if (L.lane == 0) { d.time = plan.time; d.warning = 0; d.ncon = 0; d.nefc = 0; d.nlimit = 0; d.solver_iter = 0; }
+  if (WB) { CO_FOR(k, ns) wb.states[(size_t)k * stride + i] = plan.state[k]; if (L.lane == 0) wb.times[i] = plan.time; }
+  L.sync();
+  const double* kcol = knots + i;
+  double sum = 0; bool failed = false;
+
+  for (int t = 0; t < H; t++) {
+    const bool terminal = t == H - 1;
+    if (!terminal) {
+      // policy: spline sample + clamp, one lane per actuator
+      const double time = d.time;
+      CO_FOR(a, nu) {
+        auto kn = [&](int p, int) { return kcol[(size_t)(p * nu + a) * stride]; };
+        double u; spline_sample(plan.spline_times, P, 1, plan.interpolation, time, kn, &u);
+        d.ctrl[a] = clampd(u, m.act_ctrlrange[2 * a], m.act_ctrlrange[2 * a + 1]);
+      }
+      bool bad = false;
+      CO_FOR(k, nq) bad = bad || bad_number(d.qpos[k]);
+      CO_FOR(k, nv) bad = bad || bad_number(d.qvel[k]);
+      L.sync();
+      if (L.any(bad)) { failed = true; if (WB) { CO_FOR(a, nu) wb.actions[((size_t)t * nu + a) * stride + i] = d.ctrl[a]; } break; }
+    }
+    if (WB && (!terminal || H > 1)) CO_FOR(a, nu) wb.actions[((size_t)t * nu + a) * stride + i] = d.ctrl[a];
+    co_forward_pass(L, m, d);
+    if (L.lane == 0) {
+      task_residual(m, d, task, d.residual);
+      d.sc_cost = cost_value(task, d.residual);
+    }
+    L.sync();
+    const double c = d.sc_cost;
+    if (WB) {
+      CO_FOR(k, nr) wb.residual[((size_t)t * nr + k) * stride + i] = d.residual[k];
+      if (L.lane == 0) {
+        wb.costs[(size_t)t * stride + i] = c;
+        for (int k = 0; k < task.num_trace; k++) {
+          double tr[3]; read_sensor(m, d, task.trace_sensor[k], tr);
+          for (int x = 0; x < 3; x++) wb.trace[((size_t)t * ntr + 3 * k + x) * stride + i] = tr[x];
+        }
+      }
+    }
+    if (terminal) { sum += c; break; }
+    bool badacc = false;
+    CO_FOR(k, nv) badacc = badacc || bad_number(d.qacc[k]);
+    if (L.any(badacc) || (d.warning & (WARN_BADQPOS | WARN_BADQVEL | WARN_BADQACC | WARN_BADCTRL))) { failed = true; break; }
+    sum += c;
+    co_integrate(stage_lanes(L, m.debug_serial, 8), m, d);
+    if (WB) {
+      double* s = wb.states + ((size_t)(t + 1) * ns) * stride + i;
+      CO_FOR(k, nq) s[(size_t)k * stride] = d.qpos[k];
+      CO_FOR(k, nv) s[(size_t)(nq + k) * stride] = d.qvel[k];
+      CO_FOR(k, na) s[(size_t)(nq + nv + k) * stride] = d.act[k];
+      if (L.lane == 0) wb.times[(size_t)(t + 1) * stride + i] = d.time;
+    }
+  }
+  const double total = failed ? 1.0e6 : sum / (H > 1 ? H : 1);
+  *flags = (failed ? 1 : 0) | ((d.warning & WARN_CAPACITY) ? 2 : 0);
+  L.sync();
+  return total;
+}
+
+#ifdef __CUDACC__
+// ---------------------------------------------------------------- persistent kernel: one warp per rollout
+// Each warp owns a CoopData slot in dynamic shared memory and pulls rollout indices from a global
+// counter until the batch is exhausted, so long (contact-rich) and short rollouts balance across
+// the grid.  Constants arrive once per block by TMA bulk copy.
+template <class T, int WARPS, bool WB>
+__global__ void __launch_bounds__(WARPS * 32)
+coop_rollout_kernel(const Constants<T>* __restrict__ gconst, const double* __restrict__ knots, int stride, int first, int n,
+                    long long sample_offset, double* __restrict__ returns, unsigned char* __restrict__ failure,
+                    MinLoc* __restrict__ block_min, Writeback wb, int* __restrict__ counter) {
+  extern __shared__ __align__(128) unsigned char smem[];
+  Constants<T>& sc = *reinterpret_cast<Constants<T>*>(smem);
+  constexpr size_t kConst = (sizeof(Constants<T>) + 127) / 128 * 128;
+  constexpr size_t kData = (sizeof(CoopData<T>) + 127) / 128 * 128;
+  __shared__ alignas(8) uint64_t bar;
+  __shared__ MinLoc warp_min[WARPS];
+
+  if (threadIdx.x == 0) { mbar_init(&bar, 1); asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    constexpr uint32_t total = (uint32_t)sizeof(Constants<T>);
+    mbar_expect_tx(&bar, total);
+    const char* src = reinterpret_cast<const char*>(gconst); char* dst = reinterpret_cast<char*>(&sc);
+    for (uint32_t off = 0; off < total; off += 32768u) {
+      const uint32_t sz = total - off < 32768u ? total - off : 32768u;
+      tma_bulk_g2s(dst + off, src + off, sz, &bar);
+    }
+  }
+  mbar_wait(&bar, 0);
+
+  const int warp = threadIdx.x >> 5;
+  Lanes L; L.lane = threadIdx.x & 31; L.width = 32;
+  CoopData<T>& d = *reinterpret_cast<CoopData<T>*>(smem + kConst + warp * kData);
+  double best = 1.0e300; long long best_i = 0x7fffffffffffffffLL;
+  for (;;) {
+    int k = 0;
+    if (L.lane == 0) k = atomicAdd(counter, 1);
+    k = __shfl_sync(0xffffffffu, k, 0);
+    if (k >= n) break;
+    const int i = first + k;
+    int flags = 0;
+    double total = co_rollout<T, WB>(L, sc.m, sc.t, sc.p, knots, stride, i, wb, d, &flags);
+    if (L.lane == 0) { returns[i] = total; failure[i] = (unsigned char)flags; }
+    if (!(total == total)) total = 1.0e300;              // NaN never wins
+    if (better(total, sample_offset + i, best, best_i)) { best = total; best_i = sample_offset + i; }
+  }
+  if (L.lane == 0) { warp_min[warp].cost = best; warp_min[warp].index = best_i; }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    for (int w = 1; w < WARPS; w++) if (better(warp_min[w].cost, warp_min[w].index, best, best_i)) { best = warp_min[w].cost; best_i = warp_min[w].index; }
+    block_min[blockIdx.x].cost = best; block_min[blockIdx.x].index = best_i;
+  }
+}
+#endif
+
+}  // namespace ps

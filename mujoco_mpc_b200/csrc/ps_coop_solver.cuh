@@ -1,0 +1,323 @@
+// Warp-cooperative primal Newton solver with exact line search (mj_solNewton semantics as restated
+// in ps_constraint.cuh): per-row work is spread over the lanes, every scalar (costs, step length,
+// stopping tests) is recomputed redundantly by all lanes from shared memory in row order, so control
+// flow stays warp-uniform and sums keep the sequential order.
+#pragma once
+#include "ps_coop_constraint.cuh"
+
+namespace ps {
+
+// state, force and cost term of every row for jar = J a - aref; returns the summed cost
+template <class T>
+PS_FN double co_update_rows(const Lanes& L, const DevModel<T>& m, CoopData<T>& d, const double* jar) {
+  const int nefc = d.nefc;
+  CO_FOR(i, nefc) {
+    const int tp = d.efc_type[i];
+    const double D = d.efc_D[i], R = d.efc_R[i], x = jar[i];
+    if (tp == EFC_FRICTION_DOF) {
+      const double f = m.dof_frictionloss[d.efc_id[i]];
+      if (x <= -R * f) { d.efc_state[i] = ST_LINEARNEG; d.efc_force[i] = f; d.sv_tmp[i] = -0.5 * R * f * f - f * x; }
+      else if (x >= R * f) { d.efc_state[i] = ST_LINEARPOS; d.efc_force[i] = -f; d.sv_tmp[i] = -0.5 * R * f * f + f * x; }
+      else { d.efc_state[i] = ST_QUADRATIC; d.efc_force[i] = -D * x; d.sv_tmp[i] = 0.5 * D * x * x; }
+    } else if (tp != EFC_CONTACT_ELLIPTIC) {
+      if (x < 0) { d.efc_state[i] = ST_QUADRATIC; d.efc_force[i] = -D * x; d.sv_tmp[i] = 0.5 * D * x * x; }
+      else { d.efc_state[i] = ST_SATISFIED; d.efc_force[i] = 0; d.sv_tmp[i] = 0; }
+    } else {
+      const CoopContact& con = d.contact[d.efc_id[i]];
+      if (i != con.efc_address) continue;              // the contact's first row does the whole cone
+      const int dim = con.dim; const double mu = con.mu; const double* fr = con.friction;
+      double U[6]; U[0] = jar[i] * mu;
+      for (int j = 1; j < dim; j++) U[j] = jar[i + j] * fr[j - 1];
+      const double N = U[0]; double TT = 0;
+      for (int j = 1; j < dim; j++) TT += U[j] * U[j];
+      const double Tn = sqrt(TT);
+      int st;
+      if (N >= mu * Tn || (Tn <= 0 && N >= 0)) {
+        st = ST_SATISFIED; for (int j = 0; j < dim; j++) { d.efc_force[i + j] = 0; d.sv_tmp[i + j] = 0; }
+      } else if (mu * N + Tn <= 0 || (Tn <= 0 && N < 0)) {
+        st = ST_QUADRATIC;
+        for (int j = 0; j < dim; j++) { d.efc_force[i + j] = -d.efc_D[i + j] * jar[i + j]; d.sv_tmp[i + j] = 0.5 * d.efc_D[i + j] * jar[i + j] * jar[i + j]; }
+      } else {
+        st = ST_CONE;
+        const double Dm = d.efc_D[i] / (mu * mu * (1 + mu * mu));
+        const double NT = N - mu * Tn;
+        d.sv_tmp[i] = 0.5 * Dm * NT * NT;
+        d.efc_force[i] = -Dm * NT * mu;
+        for (int j = 1; j < dim; j++) { d.efc_force[i + j] = -d.efc_force[i] / Tn * U[j] * fr[j - 1]; d.sv_tmp[i + j] = 0; }
+      }
+      for (int j = 0; j < dim; j++) d.efc_state[i + j] = (unsigned char)st;
+    }
+  }
+  L.sync();
+  double cost = 0;
+  for (int i = 0; i < nefc; i++) cost += d.sv_tmp[i];
+  return cost;
+}
+
+struct CoSolverScalars { double cost, gauss, prev_cost; };
+
+template <class T>
+PS_FN void co_update_cost(const Lanes& L, const DevModel<T>& m, CoopData<T>& d, CoSolverScalars& c) {
+  const int nv = m.nv;
+  const double cc = co_update_rows(L, m, d, d.sv_Jaref);
+  double g = 0;
+  for (int i = 0; i < nv; i++) g += 0.5 * (d.sv_Ma[i] - d.qfrc_smooth[i]) * (d.qacc[i] - d.qacc_smooth[i]);
+  c.gauss = g; c.prev_cost = c.cost; c.cost = g + cc;
+  // qfrc_constraint = J' f, one lane per dof, rows in order
+  const int nf = (m.disableflags & DSBL_FRICTIONLOSS) ? 0 : m.nfrictionrow;
+  const int nl = d.nlimit, ncon = d.ncon;
+  CO_FOR(i, nv) {
+    double s = 0;
+    const int fr = nf ? m.dof_frictionrow[i] : -1;
+    if (fr >= 0) { const double f = d.efc_force[fr]; if (f != 0) s += f; }
+    for (int r = nf; r < nf + nl; r++) {
+      const double f = d.efc_force[r];
+      if (f != 0 && m.jnt_dofadr[d.efc_id[r]] == i) s += (double)d.efc_jrow[r] * f;
+    }
+    for (int ci = 0; ci < ncon; ci++) {
+      const CoopContact& con = d.contact[ci];
+      const int k = d.con_slot[ci * T::NV + i];
+      if (con.efc_address < 0 || k < 0) continue;
+      for (int q = 0; q < con.nrow; q++) {
+        const double f = d.efc_force[con.efc_address + q];
+        if (f != 0) s += d.jpool[(con.jadr + q) * T::NCH + k] * f;
+      }
+    }
+    d.qfrc_constraint[i] = s;
+  }
+  L.sync();
+}
+
+// H = M + J' D_active J (+ cone blocks) -> Cholesky -> search = -H^-1 grad
+template <class T>
+PS_FN void co_newton_direction(const Lanes& L, const DevModel<T>& m, CoopData<T>& d) {
+  constexpr int S = T::NV, NCH = T::NCH; const int nv = m.nv;
+  double* H = d.qH;
+  CO_FOR(i, nv) d.sv_grad[i] = d.sv_Ma[i] - d.qfrc_smooth[i] - d.qfrc_constraint[i];
+  CO_FOR(w, nv * S) H[w] = d.qM[w];
+  L.sync();
+  // unit rows: friction rows hit distinct diagonal entries; limit rows go through one lane, in order
+  const int nf = (m.disableflags & DSBL_FRICTIONLOSS) ? 0 : m.nfrictionrow;
+  CO_FOR(k, nf) if (d.efc_state[k] == ST_QUADRATIC) { const int i = d.efc_id[k]; H[i * S + i] += d.efc_D[k]; }
+  L.sync();
+  if (L.lane == 0)
+    for (int r = nf; r < nf + d.nlimit; r++) if (d.efc_state[r] == ST_QUADRATIC) { const int i = m.jnt_dofadr[d.efc_id[r]]; H[i * S + i] += d.efc_D[r]; }
+  L.sync();
+  // contacts one after the other; lanes own (dof slot, dof slot) pairs of the contact's block
+  for (int ci = 0; ci < d.ncon; ci++) {
+    const CoopContact& con = d.contact[ci];
+    const int adr = con.efc_address;
+    if (adr < 0) continue;
+    const int n = con.ndof, npair = n * (n + 1) / 2, nrow = con.nrow;
+    const signed char* dof = d.con_dof + ci * NCH;
+    const double* J = d.jpool + con.jadr * NCH;
+    const bool cone = d.efc_type[adr] == EFC_CONTACT_ELLIPTIC && d.efc_state[adr] == ST_CONE;
+    if (cone) {
+      const int dim = con.dim; const double mu = con.mu; const double* fr = con.friction;
+      // local cone Hessian (dim x dim), recomputed from the row residuals
+      double U[6]; U[0] = d.sv_Jaref[adr] * mu;
+      for (int j = 1; j < dim; j++) U[j] = d.sv_Jaref[adr + j] * fr[j - 1];
+      const double N = U[0]; double TT = 0;
+      for (int j = 1; j < dim; j++) TT += U[j] * U[j];
+      const double Tn = sqrt(TT);
+      const double Dm = d.efc_D[adr] / (mu * mu * (1 + mu * mu));
+      const double s1 = mu * N / (Tn * Tn * Tn), s2 = mu * mu - mu * N / Tn;
+      CO_FOR(w, dim * dim) {
+        const int k = w / dim, j = w % dim;
+        double h;
+        if (k == 0 && j == 0) h = 1;
+        else if (k == 0 || j == 0) h = -mu * U[k + j] / Tn;
+        else h = s1 * U[j] * U[k] + (k == j ? s2 : 0.0);
+        d.sv_coneH[w] = h * (Dm * (k == 0 ? mu : fr[k - 1]) * (j == 0 ? mu : fr[j - 1]));
+      }
+      L.sync();
+      CO_FOR(w, dim * n) {
+        const int a = w / n, k = w % n;
+        double t = 0;
+        for (int b = 0; b < dim; b++) t += d.sv_coneH[a * dim + b] * J[b * NCH + k];
+        d.sv_T[a * NCH + k] = t;
+      }
+      L.sync();
+    }
+    CO_FOR(w, npair) {
+      // w -> (ki >= kj)
+      int ki = 0; while ((ki + 1) * (ki + 2) / 2 <= w) ki++;
+      const int kj = w - ki * (ki + 1) / 2;
+      double* h = H + dof[ki] * S + dof[kj];
+      double acc = *h;
+      if (cone) { for (int a = 0; a < con.dim; a++) acc += J[a * NCH + ki] * d.sv_T[a * NCH + kj]; }
+      else for (int q = 0; q < nrow; q++) if (d.efc_state[adr + q] == ST_QUADRATIC) acc += d.efc_D[adr + q] * J[q * NCH + ki] * J[q * NCH + kj];
+      *h = acc;
+    }
+    L.sync();
+  }
+  // Cholesky by columns: entry (i, j) = (H_ij - sum_{k<j} L_ik L_jk) / L_jj
+  for (int j = 0; j < nv; j++) {
+    double dg = 0;
+    for (int base = j; base < nv; base += L.width) {
+      const int i = base + L.lane;
+      double s = 0;
+      if (i < nv) { s = H[i * S + j]; for (int k = 0; k < j; k++) s -= H[i * S + k] * H[j * S + k]; }
+      if (base == j) {
+        dg = L.bcast(sqrt(fmax(s, kMinVal)), 0);
+        if (i == j) H[j * S + j] = dg; else if (i < nv) H[i * S + j] = s / dg;
+      } else if (i < nv) H[i * S + j] = s / dg;
+    }
+    L.sync();
+  }
+  // forward / backward substitution by columns
+  double* x = d.sv_x;
+  CO_FOR(i, nv) x[i] = d.sv_grad[i];
+  L.sync();
+  for (int k = 0; k < nv; k++) {
+    const double xk = x[k] / H[k * S + k];
+    L.sync();
+    if (L.lane == 0) x[k] = xk;
+    for (int base = k + 1; base < nv; base += L.width) { const int i = base + L.lane; if (i < nv) x[i] -= H[i * S + k] * xk; }
+    L.sync();
+  }
+  for (int k = nv - 1; k >= 0; k--) {
+    const double xk = x[k] / H[k * S + k];
+    L.sync();
+    if (L.lane == 0) x[k] = xk;
+    CO_FOR(i, k) x[i] -= H[k * S + i] * xk;
+    L.sync();
+  }
+  CO_FOR(i, nv) d.sv_search[i] = -x[i];
+  L.sync();
+}
+
+// value, slope and curvature of the total cost along the search direction at step alpha
+template <class T>
+PS_FN void co_line_eval(const Lanes& L, const DevModel<T>& m, CoopData<T>& d, const double* qg, double alpha,
+                        double* cost, double* d1, double* d2) {
+  const int nefc = d.nefc;
+  double* tf = d.sv_tmp; double* tg = d.efc_force; double* th = d.efc_aref;     // both dead during the line search
+  CO_FOR(i, nefc) {
+    const int tp = d.efc_type[i];
+    const double D = d.efc_D[i], R = d.efc_R[i];
+    const double x = d.sv_Jaref[i] + alpha * d.sv_Jv[i], v = d.sv_Jv[i];
+    if (tp == EFC_FRICTION_DOF) {
+      const double fl = m.dof_frictionloss[d.efc_id[i]];
+      if (x <= -R * fl) { tf[i] = -0.5 * R * fl * fl - fl * x; tg[i] = -fl * v; th[i] = 0; }
+      else if (x >= R * fl) { tf[i] = -0.5 * R * fl * fl + fl * x; tg[i] = fl * v; th[i] = 0; }
+      else { tf[i] = 0.5 * D * x * x; tg[i] = D * x * v; th[i] = D * v * v; }
+    } else if (tp != EFC_CONTACT_ELLIPTIC) {
+      if (x < 0) { tf[i] = 0.5 * D * x * x; tg[i] = D * x * v; th[i] = D * v * v; }
+      else { tf[i] = 0; tg[i] = 0; th[i] = 0; }
+    } else {
+      const CoopContact& con = d.contact[d.efc_id[i]];
+      if (i != con.efc_address) continue;
+      const int dim = con.dim; const double mu = con.mu; const double* fr = con.friction;
+      const double N = x * mu, Np = v * mu; double TT = 0, UV = 0, VV = 0;
+      for (int j = 1; j < dim; j++) {
+        const double u = (d.sv_Jaref[i + j] + alpha * d.sv_Jv[i + j]) * fr[j - 1], w = d.sv_Jv[i + j] * fr[j - 1];
+        TT += u * u; UV += u * w; VV += w * w;
+      }
+      const double Tn = sqrt(TT);
+      for (int j = 0; j < dim; j++) { tf[i + j] = 0; tg[i + j] = 0; th[i + j] = 0; }
+      if (N >= mu * Tn || (Tn <= 0 && N >= 0)) {
+      } else if (mu * N + Tn <= 0 || (Tn <= 0 && N < 0)) {
+        for (int j = 0; j < dim; j++) {
+          const double xj = d.sv_Jaref[i + j] + alpha * d.sv_Jv[i + j], vj = d.sv_Jv[i + j], Dj = d.efc_D[i + j];
+          tf[i + j] = 0.5 * Dj * xj * xj; tg[i + j] = Dj * xj * vj; th[i + j] = Dj * vj * vj;
+        }
+      } else {
+        const double Dm = D / (mu * mu * (1 + mu * mu));
+        const double Tp = UV / Tn, Tpp = VV / Tn - UV * UV / (Tn * Tn * Tn);
+        const double NT = N - mu * Tn, NTp = Np - mu * Tp;
+        tf[i] = 0.5 * Dm * NT * NT; tg[i] = Dm * NT * NTp; th[i] = Dm * (NTp * NTp + NT * (-mu * Tpp));
+      }
+    }
+  }
+  L.sync();
+  double f = qg[0] + alpha * qg[1] + alpha * alpha * qg[2];
+  double g = qg[1] + 2 * alpha * qg[2];
+  double h = 2 * qg[2];
+  for (int i = 0; i < nefc; i++) { f += tf[i]; g += tg[i]; h += th[i]; }
+  L.sync();
+  *cost = f; *d1 = g; *d2 = h;
+}
+
+template <class T>
+PS_FN double co_line_search(const Lanes& L, const DevModel<T>& m, CoopData<T>& d, const CoSolverScalars& c) {
+  const int nv = m.nv, nefc = d.nefc;
+  const double snorm = sqrt(vdot(d.sv_search, d.sv_search, nv));
+  if (snorm < kMinVal) return 0;
+  const double scale = 1.0 / (m.meaninertia * (nv > 1 ? nv : 1));
+  const double gtol = m.tolerance * m.ls_tolerance * snorm / scale;
+  co_mul_M(L, m, d, d.sv_Mv, d.sv_search);
+  CO_FOR(r, nefc) d.sv_Jv[r] = co_row_dot(m, d, r, d.sv_search);
+  L.sync();
+  double qg[3] = {c.gauss, 0, 0};
+  for (int i = 0; i < nv; i++) { qg[1] += d.sv_search[i] * (d.sv_Ma[i] - d.qfrc_smooth[i]); qg[2] += 0.5 * d.sv_search[i] * d.sv_Mv[i]; }
+  double c0, d0, h0; co_line_eval(L, m, d, qg, 0, &c0, &d0, &h0);
+  if (!(h0 > 0) || d0 >= 0) return 0;
+  double lo = 0, hi = -1;
+  double alpha = -d0 / h0, cc, dd, hh;
+  co_line_eval(L, m, d, qg, alpha, &cc, &dd, &hh);
+  for (int it = 0; it < m.ls_iterations && fabs(dd) >= gtol; it++) {
+    if (dd < 0) lo = alpha; else hi = alpha;
+    double an = hh > 0 ? alpha - dd / hh : -1;
+    if (hi < 0) { if (!(an > lo)) an = 2 * alpha; }
+    else if (!(an > lo && an < hi)) an = 0.5 * (lo + hi);
+    alpha = an;
+    co_line_eval(L, m, d, qg, alpha, &cc, &dd, &hh);
+  }
+  if (!(cc < c0)) return 0;
+  return alpha;
+}
+
+template <class T>
+PS_FN void co_constraint_stage(const Lanes& L, const DevModel<T>& m, CoopData<T>& d) {
+  const int nv = m.nv, nefc = d.nefc;
+  if (!nefc) {
+    CO_FOR(i, nv) { d.qacc[i] = d.qacc_smooth[i]; d.qacc_warmstart[i] = d.qacc_smooth[i]; d.qfrc_constraint[i] = 0; }
+    if (L.lane == 0) d.solver_iter = 0;
+    L.sync();
+    return;
+  }
+  CoSolverScalars c; c.cost = 0; c.prev_cost = 0; c.gauss = 0;
+  if (!(m.disableflags & DSBL_WARMSTART)) {
+    // keep the warm start only if it beats the unconstrained acceleration
+    CO_FOR(i, nv) d.qacc[i] = d.qacc_warmstart[i];
+    L.sync();
+    co_mul_M(L, m, d, d.sv_Ma, d.qacc);
+    CO_FOR(r, nefc) d.sv_Jaref[r] = co_row_dot(m, d, r, d.qacc) - d.efc_aref[r];
+    L.sync();
+    double cw = co_update_rows(L, m, d, d.sv_Jaref);
+    for (int i = 0; i < nv; i++) cw += 0.5 * (d.sv_Ma[i] - d.qfrc_smooth[i]) * (d.qacc[i] - d.qacc_smooth[i]);
+    L.sync();
+    CO_FOR(r, nefc) d.sv_Jv[r] = co_row_dot(m, d, r, d.qacc_smooth) - d.efc_aref[r];
+    L.sync();
+    const double cs = co_update_rows(L, m, d, d.sv_Jv);
+    L.sync();
+    if (cw > cs) { CO_FOR(i, nv) d.qacc[i] = d.qacc_smooth[i]; }
+    L.sync();
+  } else { CO_FOR(i, nv) d.qacc[i] = d.qacc_smooth[i]; L.sync(); }
+  co_mul_M(L, m, d, d.sv_Ma, d.qacc);
+  CO_FOR(r, nefc) d.sv_Jaref[r] = co_row_dot(m, d, r, d.qacc) - d.efc_aref[r];
+  L.sync();
+  co_update_cost(L, m, d, c);
+  co_newton_direction(L, m, d);
+  const double scale = 1.0 / (m.meaninertia * (nv > 1 ? nv : 1));
+  int iter = 0;
+  while (iter < m.iterations) {
+    const double alpha = co_line_search(L, m, d, c);
+    if (alpha == 0) break;
+    CO_FOR(i, nv) { d.qacc[i] += alpha * d.sv_search[i]; d.sv_Ma[i] += alpha * d.sv_Mv[i]; }
+    CO_FOR(r, nefc) d.sv_Jaref[r] += alpha * d.sv_Jv[r];
+    L.sync();
+    co_update_cost(L, m, d, c);
+    co_newton_direction(L, m, d);
+    iter++;
+    const double improvement = scale * (c.prev_cost - c.cost);
+    const double gradient = scale * sqrt(vdot(d.sv_grad, d.sv_grad, nv));
+    if (improvement < m.tolerance || gradient < m.tolerance) break;
+  }
+  CO_FOR(i, nv) d.qacc_warmstart[i] = d.qacc[i];
+  if (L.lane == 0) d.solver_iter = iter;
+  L.sync();
+}
+
+}  // namespace ps

@@ -77,8 +77,8 @@ PS_FN double cost_value(const DevTask& t, const double* residual) {
 enum { TASK_PARTICLE = 0, TASK_PARTICLE_FIXED, TASK_PARTICLE_TEST, TASK_CARTPOLE, TASK_ACROBOT, TASK_SWIMMER,
        TASK_WALKER, TASK_QUADRUPED };
 
-template <class T>
-PS_FN void task_residual(const DevModel<T>& m, const RolloutData<T>& d, const DevTask& t, double* r) {
+template <class T, class D>
+PS_FN void task_residual(const DevModel<T>& m, const D& d, const DevTask& t, double* r) {
   double s0[3], s1[3];
   switch (t.task_id) {
     case TASK_PARTICLE: case TASK_PARTICLE_FIXED: {

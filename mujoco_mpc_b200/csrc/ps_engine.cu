@@ -6,6 +6,7 @@
 // (mjpc/planners/sampling/planner.cc:151-187,342-380) -- N ThreadPool closures each calling
 // Trajectory::Rollout on a per-thread mjData -- becomes K1 + K2 + K3 on one stream.
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <string>
 #include <vector>
@@ -20,7 +21,15 @@ static int fail(const std::string& s) { g_error = s; return -1; }
 #define CU(call)                                                                                   \
   do { cudaError_t e_ = (call); if (e_ != cudaSuccess) return fail(std::string(#call) + ": " + cudaGetErrorString(e_)); } while (0)
 
-static const Variant* const kVariants[] = {variant_tiny(), variant_planar(), variant_legged()};
+// tried in order; the warp-per-rollout instantiations come before their thread-per-rollout fallbacks
+static const Variant* const kVariants[] = {variant_tiny(), variant_planar_coop(), variant_planar(), variant_legged_coop(), variant_legged()};
+
+// the cooperative engine carries semi-implicit Euler and no fluid forces
+static bool coop_supported(const PsModel* m, std::string* why) {
+  if (m->opt_integrator != PS_INT_EULER) { *why = "integrator is not Euler"; return false; }
+  if (m->opt_density > 0 || m->opt_viscosity > 0) { *why = "fluid forces"; return false; }
+  return true;
+}
 
 // ---------------------------------------------------------------- engine object
 struct PsEngine_ {
@@ -28,7 +37,7 @@ struct PsEngine_ {
   const Variant* var = nullptr;
   void* h_const = nullptr; void* d_const = nullptr;             // pinned host mirror + device copy
   int nq = 0, nv = 0, nu = 0, na = 0, nmocap = 0, nsensor = 0, ns = 0;
-  std::vector<int> sensor_type; bool ray_ok = false;
+  std::vector<int> sensor_type; bool ray_ok = false; bool force_thread_variant = false; int* d_counter = nullptr;
   std::vector<double> ctrlrange;
   DevTask task{}; bool have_task = false, have_model = false;
   int P = 0, interp = 0, H = 0, N = 0, cap = 0, stride = 0, nelem = 0, nblocks = 0;
@@ -71,6 +80,9 @@ PsEngine* ps_create(int device_ordinal) {
   for (auto& ev : e->ev) cudaEventCreate(&ev);
   cudaMallocHost(&e->h_record, (3 + 36 * 32) * sizeof(double));
   cudaMalloc(&e->d_record, (3 + 36 * 32) * sizeof(double));
+  cudaMalloc(&e->d_counter, sizeof(int));
+  const char* env = std::getenv("PS_THREAD_PER_ROLLOUT");       // diagnostics: keep the warp-per-rollout engine out
+  e->force_thread_variant = env && env[0] == '1';
   return e;
 }
 
@@ -79,7 +91,7 @@ void ps_destroy(PsEngine* e) {
   cudaSetDevice(e->device);
   cudaStreamSynchronize(e->stream);
   void* bufs[] = {e->d_const, e->d_nominal, e->d_ctrlrange, e->d_knots, e->d_returns, e->d_record, e->d_z, e->d_failure, e->d_std2,
-                  e->d_blockmin, e->wb.states, e->wb.actions, e->wb.residual, e->wb.costs, e->wb.times, e->wb.trace, e->d_scratch};
+                  e->d_blockmin, e->d_counter, e->wb.states, e->wb.actions, e->wb.residual, e->wb.costs, e->wb.times, e->wb.trace, e->d_scratch};
   for (void* b : bufs) if (b) cudaFree(b);
   if (e->h_const) cudaFreeHost(e->h_const);
   if (e->h_record) cudaFreeHost(e->h_record);
@@ -96,6 +108,7 @@ int ps_set_model(PsEngine* e, const PsModel* m) {
   const Variant* chosen = nullptr; void* host = nullptr;
   for (const Variant* vp : kVariants) {
     const Variant& v = *vp;
+    if (v.coop && (e->force_thread_variant || !coop_supported(m, &why))) { all += std::string(v.name) + ": " + (e->force_thread_variant ? "disabled" : why) + "; "; continue; }
     void* h = nullptr; CU(cudaMallocHost(&h, v.const_bytes)); std::memset(h, 0, v.const_bytes);
     if (v.fill(m, pl, h, &why) == 0) { chosen = &v; host = h; break; }
     all += std::string(v.name) + ": " + why + "; "; cudaFreeHost(h);
@@ -121,12 +134,16 @@ int ps_set_model(PsEngine* e, const PsModel* m) {
   }
   std::vector<double> st(e->ns, 0.0); for (int i = 0; i < m->nq; i++) st[i] = m->qpos0[i];
   chosen->plan(e->h_const, st.data(), e->ns, mocap.data(), m->nmocap, 0.0, nullptr, 0, 0, 0);
+  if (const char* dbg = std::getenv("PS_COOP_SERIAL")) chosen->debug(e->h_const, std::atoi(dbg));
   e->have_model = true; e->have_task = false; e->wb_valid = false;
   return 0;
 }
 
 int ps_set_options(PsEngine* e, double timestep, int integrator) {
   if (!e || !e->have_model) return fail("ps_set_options: no model");
+  if (e->var->coop && integrator != PS_INT_EULER)
+    return fail("ps_set_options: this model runs on the warp-per-rollout engine (Euler); call ps_set_model with the new integrator");
+  if (integrator == PS_INT_RK4) return fail("ps_set_options: RK4 integrator is not supported");
   e->var->options(e->h_const, timestep, integrator); return 0;
 }
 
@@ -187,7 +204,7 @@ static int alloc_samples(PsEngine* e, int N) {
     e->d_returns = nullptr; e->d_failure = nullptr; e->d_blockmin = nullptr; e->cap = 0;
     CU(cudaMalloc(&e->d_returns, sizeof(double) * stride));
     CU(cudaMalloc(&e->d_failure, stride));
-    CU(cudaMalloc(&e->d_blockmin, sizeof(MinLoc) * (stride / 32 + 1)));
+    CU(cudaMalloc(&e->d_blockmin, sizeof(MinLoc) * (stride + 1)));   // one entry per block (a block is >= 1 rollout) + a spare
     e->cap = stride;
   }
   if (ensure(&e->d_knots, &e->knots_cap, (size_t)stride * e->nelem)) return -1;
@@ -218,8 +235,7 @@ static int run_iteration(PsEngine* e, int N, int H, double sigma0, double sigma1
                                             (long long)sample_offset, e->have_noise ? e->d_z : nullptr,
                                             e->have_noise ? e->d_std2 : nullptr, e->d_knots, stride);
   CU(cudaEventRecord(e->ev[1], e->stream));
-  e->nblocks = (N + e->var->block - 1) / e->var->block;
-  e->var->launch(e->stream, e->d_const, e->d_knots, stride, 0, N, (long long)sample_offset, e->d_returns, e->d_failure, e->d_blockmin, e->wb, writeback);
+  e->nblocks = e->var->launch(e->stream, e->d_const, e->d_knots, stride, 0, N, (long long)sample_offset, e->d_returns, e->d_failure, e->d_blockmin, e->wb, writeback, e->d_counter);
   CU(cudaEventRecord(e->ev[2], e->stream));
   argmin_kernel<<<1, 256, 0, e->stream>>>(e->d_blockmin, e->nblocks, e->d_returns, e->d_knots, stride, nelem, (long long)sample_offset, e->d_record);
   CU(cudaEventRecord(e->ev[3], e->stream));
@@ -293,8 +309,8 @@ int ps_get_trajectory(PsEngine* e, int sample, double* states, double* actions, 
     for (int k = 0; k < 6; k++) if (ensure(ptr[k], &e->wb_cap[k], need[k])) return -1;
     // zero this sample's column lazily: a failed rollout leaves later steps untouched, so clear all
     for (int k = 0; k < 6; k++) CU(cudaMemsetAsync(*ptr[k], 0, need[k] * sizeof(double), e->stream));
-    MinLoc* tmp = e->d_blockmin + (e->cap / 32);   // spare slot
-    e->var->launch(e->stream, e->d_const, e->d_knots, stride, sample, 1, e->offset, e->d_returns, e->d_failure, tmp, e->wb, true);
+    MinLoc* tmp = e->d_blockmin + e->cap;   // spare slot
+    e->var->launch(e->stream, e->d_const, e->d_knots, stride, sample, 1, e->offset, e->d_returns, e->d_failure, tmp, e->wb, true, e->d_counter);
     e->launches++;
     CU(cudaGetLastError());
   }

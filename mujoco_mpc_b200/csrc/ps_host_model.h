@@ -18,6 +18,10 @@ typedef Traits<2, 2, 2, 0, 4, 2, 8, 2, 1, 0, 0, 4, 12, false> TinyT;          //
 typedef Traits<9, 9, 6, 5, 9, 9, 18, 6, 1, 8, 14, 64, 20, false> PlanarT;    // swimmer, walker
 typedef Traits<19, 18, 12, 0, 16, 13, 44, 8, 2, 40, 16, 96, 16, true> LeggedT;  // quadruped (free joint, elliptic cones)
 
+// warp-per-rollout instantiations: + NCH (dofs one contact touches), NJROW (compressed Jacobian rows)
+typedef Traits<9, 9, 6, 5, 9, 9, 18, 6, 1, 8, 14, 64, 20, false, 9, 52> PlanarCoopT;
+typedef Traits<19, 18, 12, 0, 16, 13, 44, 8, 2, 40, 24, 120, 16, true, 12, 84> LeggedCoopT;
+
 struct PairList { std::vector<int> g1, g2; int unsupported = 0; };
 
 inline int weld_body(const PsModel* m, int b) { while (b > 0 && m->body_dofnum[b] == 0) b = m->body_parentid[b]; return b; }
@@ -61,6 +65,59 @@ inline bool ray_scenery_ok(const PsModel* s) {
     if (++n > kMaxRayGeom) return false;
   }
   return n > 0;
+}
+
+template <class T>
+inline bool track_geom(DevModel<T>& m, int g) {
+  if (g < 0 || g >= m.ngeom) return false;
+  if (m.geom_trackslot[g] >= 0) return true;
+  if (m.ntrack >= kMaxTrackGeom) return false;
+  m.geom_trackslot[g] = (short)m.ntrack; m.track_geom[m.ntrack++] = (short)g;
+  return true;
+}
+
+// Schedules of the warp-cooperative engine: every table lists independent work items of one phase in
+// the order that reproduces the sequential recursions of the thread-per-rollout code bit for bit.
+template <class T>
+inline int build_schedules(const PsModel* s, DevModel<T>& m, std::string* why) {
+  const int nb = s->nbody, nv = s->nv;
+  std::vector<int> depth(nb, 0);
+  int maxd = 0;
+  for (int b = 1; b < nb; b++) { depth[b] = depth[s->body_parentid[b]] + 1; if (depth[b] > maxd) maxd = depth[b]; }
+  m.nlevel = maxd + 1;
+  int at = 0;
+  for (int l = 0; l <= maxd; l++) { m.level_adr[l] = (short)at; for (int b = 0; b < nb; b++) if (depth[b] == l) m.level_body[at++] = (short)b; }
+  m.level_adr[maxd + 1] = (short)at;
+  at = 0;
+  for (int p = 0; p < nb; p++) { m.child_adr[p] = (short)at; for (int c = nb - 1; c > 0; c--) if (s->body_parentid[c] == p) m.child_list[at++] = (short)c; }
+  m.child_adr[nb] = (short)at;
+  std::vector<int> dd(nv > 0 ? nv : 1, 0); int maxdd = -1;
+  for (int i = 0; i < nv; i++) { const int p = s->dof_parentid[i]; dd[i] = p < 0 ? 0 : dd[p] + 1; if (dd[i] > maxdd) maxdd = dd[i]; }
+  m.ndoflevel = maxdd + 1; at = 0;
+  for (int l = 0; l <= maxdd; l++) { m.doflevel_adr[l] = (short)at; for (int i = 0; i < nv; i++) if (dd[i] == l) m.doflevel_dof[at++] = (short)i; }
+  m.doflevel_adr[maxdd + 1] = (short)at;
+  auto is_anc = [&](int a, int i) { for (int j = s->dof_parentid[i]; j >= 0; j = s->dof_parentid[j]) if (j == a) return true; return false; };
+  int ad = 0, aa = 0, fp = 0, mp = 0;
+  for (int i = 0; i < nv; i++) {
+    m.dofdesc_adr[i] = (short)ad;
+    for (int k = nv - 1; k > i; k--) if (is_anc(i, k)) { if (ad >= T::NTRI) { *why = "dof tree too dense"; return -1; } m.dofdesc[ad++] = (short)k; }
+    m.dofanc_adr[i] = (short)aa;
+    for (int j = s->dof_parentid[i]; j >= 0; j = s->dof_parentid[j]) { if (aa >= T::NTRI) { *why = "dof tree too deep"; return -1; } m.dofanc[aa++] = (short)j; }
+    m.fpair_adr[i] = (short)fp;
+    for (int a = s->dof_parentid[i]; a >= 0; a = s->dof_parentid[a])
+      for (int j = a; j >= 0; j = s->dof_parentid[j]) {
+        if (fp >= T::NFPAIR) { *why = "elimination schedule overflow"; return -1; }
+        m.fpair_i[fp] = (unsigned char)a; m.fpair_j[fp] = (unsigned char)j; fp++;
+      }
+    for (int j = i; j >= 0; j = s->dof_parentid[j]) { m.mpair_i[mp] = (unsigned char)i; m.mpair_j[mp] = (unsigned char)j; mp++; }
+  }
+  m.dofdesc_adr[nv] = (short)ad; m.dofanc_adr[nv] = (short)aa; m.fpair_adr[nv] = (short)fp; m.nmpair = mp;
+  m.nfrictionrow = 0;
+  for (int i = 0; i < nv; i++) {
+    m.dof_frictionrow[i] = -1;
+    if (s->dof_frictionloss[i] > 0) { m.dof_frictionrow[i] = (short)m.nfrictionrow; m.frictionrow_dof[m.nfrictionrow++] = (short)i; }
+  }
+  return 0;
 }
 
 template <class T>
@@ -121,6 +178,7 @@ inline int fill_model(const PsModel* s, const PairList& pl, void* out, std::stri
   for (int i = 0; i < s->nv; i++) if (s->dof_damping[i] > 0) m.any_damping = 1;
   for (int p = 0; p < m.npair; p++) { m.pair_geom1[p] = pl.g1[p]; m.pair_geom2[p] = pl.g2[p]; m.geom_used[pl.g1[p]] = 1; m.geom_used[pl.g2[p]] = 1; }
   for (int i = 0; i < s->nsensor; i++) if (s->sensor_objtype[i] == PS_OBJ_GEOM && s->sensor_objid[i] >= 0) m.geom_used[s->sensor_objid[i]] = 1;
+  if (build_schedules<T>(s, m, why)) return -1;
   // Ground() ray candidates: group-0 geoms; the device carries static plane / sphere / box scenery only
   m.ray_complete = 1;
   for (int g = 0; g < s->ngeom; g++) {
@@ -129,6 +187,12 @@ inline int fill_model(const PsModel* s, const PairList& pl, void* out, std::stri
     const bool ok = weld_body(s, s->geom_bodyid[g]) == 0 && (tp == PS_GEOM_PLANE || tp == PS_GEOM_SPHERE || tp == PS_GEOM_BOX);
     if (ok && m.nray < kMaxRayGeom) { m.ray_geom[m.nray++] = g; m.geom_used[g] = 1; } else m.ray_complete = 0;
   }
+  // geoms whose world frame the cooperative engine keeps: ray scenery + sensor geoms (+ task geoms, set_task)
+  for (int g = 0; g < s->ngeom; g++) m.geom_trackslot[g] = -1;
+  m.ntrack = 0;
+  for (int k = 0; k < m.nray; k++) track_geom(m, m.ray_geom[k]);
+  for (int i = 0; i < s->nsensor; i++) if (s->sensor_objtype[i] == PS_OBJ_GEOM && s->sensor_objid[i] >= 0) track_geom(m, s->sensor_objid[i]);
+  m.ntrack_model = m.ntrack;
   return 0;
 }
 
@@ -138,8 +202,15 @@ inline void set_options(void* c, double timestep, int integrator) {
 }
 
 template <class T>
+inline void set_debug(void* c, int mask) { reinterpret_cast<Constants<T>*>(c)->m.debug_serial = mask; }
+
+template <class T>
 inline void set_task(void* c, const DevTask& t, int need_subtreevel) {
   Constants<T>* k = reinterpret_cast<Constants<T>*>(c); k->t = t; k->m.need_subtreevel = need_subtreevel;
+  DevModel<T>& m = k->m;
+  for (int i = m.ntrack_model; i < m.ntrack; i++) m.geom_trackslot[m.track_geom[i]] = -1;
+  m.ntrack = m.ntrack_model;
+  if (t.task_id == TASK_QUADRUPED) for (int f = 0; f < 4; f++) track_geom(m, t.iaux[3 + f]);
 }
 
 template <class T>

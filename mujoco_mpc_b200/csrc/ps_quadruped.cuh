@@ -59,14 +59,14 @@ PS_HD double ray_box(const double* pos, const double* mat, const double* size, c
 }
 
 // height of the nearest group-0 geom under `pos`
-template <class T>
-PS_FN double ground_height(const DevModel<T>& m, const RolloutData<T>& d, const double* pos) {
+template <class T, class D>
+PS_FN double ground_height(const DevModel<T>& m, const D& d, const double* pos) {
   const double down[3] = {0, 0, -1}; const double offset = 0.5;
   const double query[3] = {pos[0], pos[1], pos[2] + offset};
   double dist = -1;
   for (int k = 0; k < m.nray; k++) {
     const int g = m.ray_geom[k];
-    const double* gp = d.geom_xpos + 3 * g; const double* gm = d.geom_xmat + 9 * g; const double* sz = m.geom_size + 3 * g;
+    const double* gp = geom_world_pos(m, d, g); const double* gm = geom_world_mat(m, d, g); const double* sz = m.geom_size + 3 * g;
     const int tp = m.geom_type[g];
     const double x = tp == GEOM_PLANE ? ray_plane(gp, gm, sz, query, down)
                    : tp == GEOM_SPHERE ? ray_sphere(gp, sz, query, down) : ray_box(gp, gm, sz, query, down);
@@ -168,15 +168,15 @@ PS_HD void quat_difference(double* res, const double* qa, const double* qb) {
 }  // namespace quad
 
 // ---------------------------------------------------------------- residual (42 values, 9 terms)
-template <class T>
-PS_FN void quadruped_residual(const DevModel<T>& m, const RolloutData<T>& d, const DevTask& t, double* r) {
+template <class T, class D>
+PS_FN void quadruped_residual(const DevModel<T>& m, const D& d, const DevTask& t, double* r) {
   using namespace quad;
   const double* a = t.aux; const double* P = t.parameters;
   const int mode = (int)a[A_MODE], torso = t.iaux[0];
   const int handstand = as_int(P[t.iaux[7]]);
   const bool biped = mode == MODE_BIPED;
   const double* foot[4];
-  for (int f = 0; f < 4; f++) foot[f] = d.geom_xpos + 3 * t.iaux[3 + f];
+  for (int f = 0; f < 4; f++) foot[f] = geom_world_pos(m, d, t.iaux[3 + f]);
   double avg[3];
   if (biped) {
     const double* fa = handstand ? foot[FOOT_FL] : foot[FOOT_HL]; const double* fb = handstand ? foot[FOOT_FR] : foot[FOOT_HR];

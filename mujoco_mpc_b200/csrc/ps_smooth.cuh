@@ -7,6 +7,7 @@
 // mj_factorM, mj_comVel, mj_passive, mj_rne, mj_fwdActuation, mj_fwdAcceleration.
 #pragma once
 #include "ps_math.cuh"
+#include "ps_coop.cuh"
 
 namespace ps {
 
@@ -273,9 +274,9 @@ PS_FN void rne_bias(const DevModel<T>& m, const RolloutData<T>& d, const double*
 }
 
 // 6D velocity [ang; lin] of a frame at `pos` fixed to `body`, world orientation
-template <class T>
-PS_HD void frame_velocity(const DevModel<T>& m, const RolloutData<T>& d, int body, const double* pos, double* res) {
-  const double* cv = d.cvel + 6 * body;
+template <class T, class D>
+PS_HD void frame_velocity(const DevModel<T>& m, const D& d, int body, const double* pos, double* res) {
+  const double* cv = body_cvel(d) + 6 * body;
   double dif[3], cr[3];
   for (int k = 0; k < 3; k++) dif[k] = pos[k] - d.subtree_com[3 * m.body_rootid[body] + k];
   cross3(cr, dif, cv);

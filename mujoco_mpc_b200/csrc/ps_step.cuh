@@ -40,13 +40,13 @@ PS_FN void subtree_velocity(const DevModel<T>& m, RolloutData<T>& d) {
 
 // evaluate model sensor `s` from the current rollout data (replaces SensorByName + sensordata,
 // mjpc/utilities.cc:166-175); returns the number of values written
-template <class T>
-PS_FN int read_sensor(const DevModel<T>& m, const RolloutData<T>& d, int s, double* out) {
+template <class T, class D>
+PS_FN int read_sensor(const DevModel<T>& m, const D& d, int s, double* out) {
   const int type = m.sensor_type[s], ot = m.sensor_objtype[s], id = m.sensor_objid[s];
   const double* pos; const double* mat; int body;
   if (ot == OBJ_BODY) { pos = d.xipos + 3 * id; mat = d.ximat + 9 * id; body = id; }
   else if (ot == OBJ_XBODY) { pos = d.xpos + 3 * id; mat = d.xmat + 9 * id; body = id; }
-  else if (ot == OBJ_GEOM) { pos = d.geom_xpos + 3 * id; mat = d.geom_xmat + 9 * id; body = m.geom_bodyid[id]; }
+  else if (ot == OBJ_GEOM) { pos = geom_world_pos(m, d, id); mat = geom_world_mat(m, d, id); body = m.geom_bodyid[id]; }
   else { pos = d.site_xpos + 3 * id; mat = d.site_xmat + 9 * id; body = m.site_bodyid[id]; }
   switch (type) {
     case SENS_JOINTPOS: out[0] = d.qpos[m.jnt_qposadr[id]]; return 1;

@@ -28,10 +28,11 @@ constexpr int kMaxResidual = 48;    // quadruped: 42
 constexpr int kMaxTaskParam = 16;
 constexpr int kMaxTaskAux = 96;
 constexpr int kMaxRayGeom = 8;
+constexpr int kMaxTrackGeom = 16;
 
 // compile-time capacities of one engine instantiation
 template <int NQ_, int NV_, int NU_, int NA_, int NBODY_, int NJNT_, int NGEOM_, int NSITE_,
-          int NMOCAP_, int NPAIR_, int MAXCON_, int MAXEFC_, int NSENSOR_, bool ELLIPTIC_>
+          int NMOCAP_, int NPAIR_, int MAXCON_, int MAXEFC_, int NSENSOR_, bool ELLIPTIC_, int NCH_ = 0, int NJROW_ = 0>
 struct Traits {
   static constexpr int NQ = NQ_, NV = NV_, NU = NU_, NA = (NA_ > 0 ? NA_ : 1), NBODY = NBODY_,
                        NJNT = NJNT_, NGEOM = NGEOM_, NSITE = (NSITE_ > 0 ? NSITE_ : 1),
@@ -39,7 +40,11 @@ struct Traits {
                        MAXCON = (MAXCON_ > 0 ? MAXCON_ : 1), MAXEFC = (MAXEFC_ > 0 ? MAXEFC_ : 1),
                        NSENSOR = (NSENSOR_ > 0 ? NSENSOR_ : 1);
   static constexpr bool ELLIPTIC = ELLIPTIC_;
+  // cooperative engine: max dofs one contact's Jacobian touches, rows of the compressed Jacobian pool
+  static constexpr int NCH = NCH_ > 0 ? NCH_ : NV_, NJROW = NJROW_ > 0 ? NJROW_ : (MAXEFC_ > 0 ? MAXEFC_ : 1);
   static constexpr int NCONEH = ELLIPTIC_ ? MAXCON : 1;
+  static constexpr int NTRI = NV_ * (NV_ - 1) / 2 + 1;                  // strictly-lower entries of an NV x NV matrix
+  static constexpr int NFPAIR = NV_ * (NV_ + 1) * (NV_ + 2) / 6 + 1;    // worst case (serial chain) of the elimination pairs
 };
 
 enum { JNT_FREE = 0, JNT_BALL = 1, JNT_SLIDE = 2, JNT_HINGE = 3 };
@@ -73,7 +78,7 @@ struct alignas(16) DevModel {
   int nray;            // group-0 scenery the Ground() ray cast visits (utilities.cc:538-556)
   int ray_geom[kMaxRayGeom];
   int ray_complete;    // every group-0 geom is static plane/sphere/box scenery and fits ray_geom
-  int pad_;
+  int debug_serial;    // diagnostics: bit k runs stage k of the cooperative engine on one lane
   double qpos0[T::NQ], qpos_spring[T::NQ];
   // bodies
   int body_parentid[T::NBODY], body_rootid[T::NBODY], body_jntnum[T::NBODY], body_jntadr[T::NBODY],
@@ -106,6 +111,21 @@ struct alignas(16) DevModel {
       act_forcerange[T::NU * 2], act_actrange[T::NU * 2], act_gear[T::NU];
   // sensors the residuals may read
   int sensor_type[T::NSENSOR], sensor_objtype[T::NSENSOR], sensor_objid[T::NSENSOR];
+  // ---- schedules for the warp-cooperative engine (ps_coop*.cuh), built once on the host
+  // bodies grouped by tree depth; children of each body in DECREASING index order (the order in
+  // which the sequential backward passes fold a child into its parent)
+  int nlevel, ndoflevel, nmpair, nfrictionrow, ntrack, ntrack_model;
+  short level_adr[T::NBODY + 1], level_body[T::NBODY], child_adr[T::NBODY + 1], child_list[T::NBODY];
+  // dofs grouped by depth in the dof tree; per dof: descendants (decreasing), ancestors (parent first)
+  short doflevel_adr[T::NV + 1], doflevel_dof[T::NV];
+  short dofdesc_adr[T::NV + 1], dofdesc[T::NTRI], dofanc_adr[T::NV + 1], dofanc[T::NTRI];
+  // L'DL elimination step k touches entries (i, j), i an ancestor of k, j an ancestor-or-self of i
+  short fpair_adr[T::NV + 1]; unsigned char fpair_i[T::NFPAIR], fpair_j[T::NFPAIR];
+  // nonzeros of the mass matrix: (i, j) with j an ancestor-or-self of i
+  unsigned char mpair_i[T::NTRI + T::NV], mpair_j[T::NTRI + T::NV];
+  short frictionrow_dof[T::NV], dof_frictionrow[T::NV];
+  // geoms whose world frames the task reads (feet, ray scenery, sensor geoms)
+  short track_geom[kMaxTrackGeom], geom_trackslot[T::NGEOM];
 };
 
 // Cost specification + residual snapshot (what Task::Residual()/BaseResidualFn::Update hands the

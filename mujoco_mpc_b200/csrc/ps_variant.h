@@ -2,33 +2,75 @@
 // class.  Each variant is its own translation unit so the three kernels compile in parallel.
 #pragma once
 #include "ps_kernels.cuh"
+#include "ps_coop_rollout.cuh"
 #include "ps_host_model.h"
 
 namespace ps {
 
+// thread-per-rollout launch; returns the number of blocks (= entries written to block_min)
 template <class T, int BLOCK>
-inline void launch_rollout(cudaStream_t st, const void* dconst, const double* knots, int stride, int first, int n,
-                           long long offset, double* returns, unsigned char* failure, MinLoc* block_min, Writeback wb, bool writeback) {
+inline int launch_rollout(cudaStream_t st, const void* dconst, const double* knots, int stride, int first, int n,
+                          long long offset, double* returns, unsigned char* failure, MinLoc* block_min, Writeback wb, bool writeback,
+                          int* counter) {
+  (void)counter;
   const int grid = (n + BLOCK - 1) / BLOCK;
   const Constants<T>* c = reinterpret_cast<const Constants<T>*>(dconst);
   if (writeback) rollout_kernel<T, BLOCK, true><<<grid, BLOCK, 0, st>>>(c, knots, stride, first, n, offset, returns, failure, block_min, wb);
   else rollout_kernel<T, BLOCK, false><<<grid, BLOCK, 0, st>>>(c, knots, stride, first, n, offset, returns, failure, block_min, wb);
+  return grid;
+}
+
+// warp-per-rollout persistent launch: as many blocks as stay resident, WARPS rollouts in flight per block
+template <class T, int WARPS>
+inline int launch_coop(cudaStream_t st, const void* dconst, const double* knots, int stride, int first, int n,
+                       long long offset, double* returns, unsigned char* failure, MinLoc* block_min, Writeback wb, bool writeback,
+                       int* counter) {
+  constexpr size_t kConst = (sizeof(Constants<T>) + 127) / 128 * 128, kData = (sizeof(CoopData<T>) + 127) / 128 * 128;
+  constexpr size_t smem = kConst + WARPS * kData;
+  static int resident[2] = {0, 0};                 // blocks the device keeps resident, per kernel flavour
+  const int f = writeback ? 1 : 0;
+  if (!resident[f]) {
+    int dev = 0, sms = 0, per_sm = 0;
+    cudaGetDevice(&dev); cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    if (writeback) {
+      cudaFuncSetAttribute(coop_rollout_kernel<T, WARPS, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+      cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, coop_rollout_kernel<T, WARPS, true>, WARPS * 32, smem);
+    } else {
+      cudaFuncSetAttribute(coop_rollout_kernel<T, WARPS, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+      cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, coop_rollout_kernel<T, WARPS, false>, WARPS * 32, smem);
+    }
+    resident[f] = sms * (per_sm > 0 ? per_sm : 1);
+  }
+  int grid = (n + WARPS - 1) / WARPS;
+  if (grid > resident[f]) grid = resident[f];
+  const Constants<T>* c = reinterpret_cast<const Constants<T>*>(dconst);
+  cudaMemsetAsync(counter, 0, sizeof(int), st);
+  if (writeback) coop_rollout_kernel<T, WARPS, true><<<grid, WARPS * 32, smem, st>>>(c, knots, stride, first, n, offset, returns, failure, block_min, wb, counter);
+  else coop_rollout_kernel<T, WARPS, false><<<grid, WARPS * 32, smem, st>>>(c, knots, stride, first, n, offset, returns, failure, block_min, wb, counter);
+  return grid;
 }
 
 struct Variant {
-  const char* name; size_t const_bytes; int block;
+  const char* name; size_t const_bytes; int block; bool coop;
   int (*fill)(const PsModel*, const PairList&, void*, std::string*);
   void (*options)(void*, double, int);
+  void (*debug)(void*, int);
   void (*task)(void*, const DevTask&, int);
   int (*plan)(void*, const double*, int, const double*, int, double, const double*, int, int, int);
-  void (*launch)(cudaStream_t, const void*, const double*, int, int, int, long long, double*, unsigned char*, MinLoc*, Writeback, bool);
+  int (*launch)(cudaStream_t, const void*, const double*, int, int, int, long long, double*, unsigned char*, MinLoc*, Writeback, bool, int*);
 };
 template <class T, int BLOCK>
 inline Variant make_variant(const char* name) {
-  return Variant{name, sizeof(Constants<T>), BLOCK, fill_model<T>, set_options<T>, set_task<T>, set_plan<T>, launch_rollout<T, BLOCK>};
+  return Variant{name, sizeof(Constants<T>), BLOCK, false, fill_model<T>, set_options<T>, set_debug<T>, set_task<T>, set_plan<T>, launch_rollout<T, BLOCK>};
+}
+template <class T, int WARPS>
+inline Variant make_coop_variant(const char* name) {
+  return Variant{name, sizeof(Constants<T>), WARPS * 32, true, fill_model<T>, set_options<T>, set_debug<T>, set_task<T>, set_plan<T>, launch_coop<T, WARPS>};
 }
 const Variant* variant_tiny();
 const Variant* variant_planar();
 const Variant* variant_legged();
+const Variant* variant_planar_coop();
+const Variant* variant_legged_coop();
 
 }  // namespace ps

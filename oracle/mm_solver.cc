@@ -91,12 +91,15 @@ static void gradientAndDirection(const Model* m, Data* d, Ctx& c) {
       double D = d->efc_D[r]; const double* J = &d->efc_J[r * nv];
       for (int i = 0; i < nv; i++) { if (J[i] == 0) continue; double s = D * J[i]; for (int j = 0; j <= i; j++) H[i * nv + j] += s * J[j]; }
     } else if (st == STATE_CONE && d->efc_type[r] == CNSTR_CONTACT_ELLIPTIC) {
+      // cone block J_c' (Hc J_c): T = Hc J_c first, then the symmetric update, one add per cone row
       const Contact& con = d->contact[d->efc_id[r]]; int dim = con.dim;
-      for (int a = 0; a < dim; a++) for (int b = 0; b < dim; b++) {
-        double h = con.H[a * dim + b]; if (h == 0) continue;
-        const double* Ja = &d->efc_J[(r + a) * nv]; const double* Jb = &d->efc_J[(r + b) * nv];
-        for (int i = 0; i < nv; i++) { double s = h * Ja[i]; if (s == 0) continue; for (int j = 0; j <= i; j++) H[i * nv + j] += s * Jb[j]; }
+      double T[6 * 64];
+      for (int a = 0; a < dim; a++) for (int j = 0; j < nv; j++) {
+        double t = 0; for (int b = 0; b < dim; b++) t += con.H[a * dim + b] * d->efc_J[(r + b) * nv + j];
+        T[a * nv + j] = t;
       }
+      for (int i = 0; i < nv; i++) for (int j = 0; j <= i; j++)
+        for (int a = 0; a < dim; a++) H[i * nv + j] += d->efc_J[(r + a) * nv + i] * T[a * nv + j];
       r += dim - 1;
     }
   }
@@ -111,7 +114,7 @@ static void gradientAndDirection(const Model* m, Data* d, Ctx& c) {
   }
   copy(c.Mgrad.data(), c.grad.data(), nv);
   for (int i = 0; i < nv; i++) { double s = c.Mgrad[i]; for (int k = 0; k < i; k++) s -= H[i * nv + k] * c.Mgrad[k]; c.Mgrad[i] = s / H[i * nv + i]; }
-  for (int i = nv - 1; i >= 0; i--) { double s = c.Mgrad[i]; for (int k = i + 1; k < nv; k++) s -= H[k * nv + i] * c.Mgrad[k]; c.Mgrad[i] = s / H[i * nv + i]; }
+  for (int i = nv - 1; i >= 0; i--) { double s = c.Mgrad[i]; for (int k = nv - 1; k > i; k--) s -= H[k * nv + i] * c.Mgrad[k]; c.Mgrad[i] = s / H[i * nv + i]; }
   for (int i = 0; i < nv; i++) c.search[i] = -c.Mgrad[i];
 }
 

@@ -15,7 +15,7 @@ def hostsim_lib(oracle_lib):
     return driver.build()
 
 
-def check(name, H, prep=None, N=3, sigma=0.2, time=0.3, seed=0):
+def check(name, H, prep=None, N=3, sigma=0.2, time=0.3, seed=0, coop=False):
     m, t, s = registry.load(name)
     if prep:
         prep(m, t)
@@ -28,7 +28,7 @@ def check(name, H, prep=None, N=3, sigma=0.2, time=0.3, seed=0):
     for i in range(N):
         ot = o.trajectory(i)
         _, kn = o.policy(2 + i)
-        h = driver.rollout(m, t, st, time, nt, kn, interp, H, s["timestep"], s["integrator"])
+        h = driver.rollout(m, t, st, time, nt, kn, interp, H, s["timestep"], s["integrator"], coop=coop)
         assert h["flags"] == (1 if ot["failure"] else 0)
         if ot["failure"]:
             continue
@@ -47,6 +47,18 @@ def test_kernel_source_matches_oracle(hostsim_lib, name, H):
 def test_kernel_source_matches_oracle_quadruped(hostsim_lib, mode, gait, angvel):
     check("Quadruped Flat", 60, prep=lambda m, t: T.quadruped_snapshot(
         m, t, mode=mode, gait=gait, time=0.3, position=(0.1, 0.2), heading=(0.5, 0.1), speed=0.5, angvel=angvel))
+
+
+@pytest.mark.parametrize("mode,gait,angvel", [("Quadruped", "Trot", 0.0), ("Biped", "Trot", 0.0), ("Walk", "Canter", 0.5),
+                                               ("Scramble", "Gallop", 0.0), ("Flip", "Stand", 0.0)])
+def test_cooperative_source_matches_oracle_quadruped(hostsim_lib, mode, gait, angvel):
+    # the warp-per-rollout engine (ps_coop*.cuh) compiled with a lane count of 1
+    check("Quadruped Flat", 60, coop=True, prep=lambda m, t: T.quadruped_snapshot(
+        m, t, mode=mode, gait=gait, time=0.3, position=(0.1, 0.2), heading=(0.5, 0.1), speed=0.5, angvel=angvel))
+
+
+def test_cooperative_source_matches_oracle_walker(hostsim_lib):
+    check("Walker", 80, coop=True)
 
 
 def test_ground_ray_sees_props(oracle_lib):
