@@ -22,7 +22,7 @@ PS_HD int hit_plane_sphere(RawContact* c, const double* pp, const double* pm, co
   return 1;
 }
 
-PS_HD int hit_plane_capsule(RawContact* c, const double* pp, const double* pm, const double* cp, const double* cm,
+PS_NI int hit_plane_capsule(RawContact* c, const double* pp, const double* pm, const double* cp, const double* cm,
                             const double* size, double margin) {
   const double axis[3] = {cm[2], cm[5], cm[8]};
   int cnt = 0;
@@ -34,7 +34,7 @@ PS_HD int hit_plane_capsule(RawContact* c, const double* pp, const double* pm, c
   return cnt;
 }
 
-PS_HD int hit_plane_cylinder(RawContact* c, const double* pp, const double* pm, const double* cp, const double* cm,
+PS_NI int hit_plane_cylinder(RawContact* c, const double* pp, const double* pm, const double* cp, const double* cm,
                              const double* size, double margin) {
   const double n[3] = {pm[2], pm[5], pm[8]}; double axis[3] = {cm[2], cm[5], cm[8]};
   const double r = size[0], h = size[1];
@@ -77,7 +77,7 @@ PS_HD int hit_plane_cylinder(RawContact* c, const double* pp, const double* pm, 
   return cnt;
 }
 
-PS_HD int hit_plane_box(RawContact* c, const double* pp, const double* pm, const double* bp, const double* bm,
+PS_NI int hit_plane_box(RawContact* c, const double* pp, const double* pm, const double* bp, const double* bm,
                         const double* size, double margin) {
   const double n[3] = {pm[2], pm[5], pm[8]};
   const double dif[3] = {bp[0] - pp[0], bp[1] - pp[1], bp[2] - pp[2]};
@@ -107,7 +107,7 @@ PS_HD int hit_sphere_sphere(RawContact* c, const double* p1, double r1, const do
   return 1;
 }
 
-PS_HD int hit_sphere_capsule(RawContact* c, const double* p1, double r1, const double* p2, const double* m2,
+PS_NI int hit_sphere_capsule(RawContact* c, const double* p1, double r1, const double* p2, const double* m2,
                              const double* size2, double margin) {
   const double axis[3] = {m2[2], m2[5], m2[8]};
   const double dif[3] = {p1[0] - p2[0], p1[1] - p2[1], p1[2] - p2[2]};
@@ -116,7 +116,7 @@ PS_HD int hit_sphere_capsule(RawContact* c, const double* p1, double r1, const d
   return hit_sphere_sphere(c, p1, r1, q, size2[0], margin);
 }
 
-PS_HD int hit_capsule_capsule(RawContact* c, const double* p1, const double* m1, const double* s1,
+PS_NI int hit_capsule_capsule(RawContact* c, const double* p1, const double* m1, const double* s1,
                               const double* p2, const double* m2, const double* s2, double margin) {
   const double a1[3] = {m1[2], m1[5], m1[8]}, a2[3] = {m2[2], m2[5], m2[8]};
   const double dif[3] = {p1[0] - p2[0], p1[1] - p2[1], p1[2] - p2[2]};
@@ -239,7 +239,7 @@ PS_HD double pow_small(double x, double p) {
   return pow(x, p);
 }
 
-PS_HD double impedance_at(const double* si, double pos, double margin) {
+PS_NI double impedance_at(const double* si, double pos, double margin) {
   if (si[0] == si[1] || si[2] <= kMinVal) return 0.5 * (si[0] + si[1]);
   const double x = fabs((pos - margin) / si[2]);
   if (x >= 1) return si[1];

@@ -17,6 +17,7 @@ namespace ps {
 // ---------------------------------------------------------------- lanes
 struct Lanes {
 #ifdef __CUDA_ARCH__
+  static constexpr bool single = false;
   int lane;
   int width;      // 32; the diagnostics mode (DevModel::debug_serial) runs chosen stages with one working lane
   __device__ __forceinline__ void sync() const { __syncwarp(); }
@@ -36,6 +37,7 @@ struct Lanes {
     return v;
   }
 #else
+  static constexpr bool single = true;
   static constexpr int lane = 0;
   static constexpr int width = 1;
   void sync() const {}

@@ -23,7 +23,7 @@ PS_HD double co_row_dot(const DevModel<T>& m, const CoopData<T>& d, int r, const
 
 // ---------------------------------------------------------------- narrow phase over the static pair list
 template <class T>
-PS_FN void co_detect_contacts(const Lanes& L, const DevModel<T>& m, CoopData<T>& d) {
+PS_NI void co_detect_contacts(const Lanes& L, const DevModel<T>& m, CoopData<T>& d) { PS_ASSUME_SHARED(&m); PS_ASSUME_SHARED(&d);
   int ncon = 0;
   if (!(m.disableflags & (DSBL_CONTACT | DSBL_CONSTRAINT))) {
     CO_ROUNDS(base, m.npair) {
@@ -73,7 +73,7 @@ PS_FN void co_detect_contacts(const Lanes& L, const DevModel<T>& m, CoopData<T>&
 }
 
 // impedance / reference parameters of one row; R is left un-adjusted (cone scaling follows)
-PS_HD void co_row_params(double timestep, int disableflags, const double* sr, const double* si, double pos, double margin,
+PS_NI void co_row_params(double timestep, int disableflags, const double* sr, const double* si, double pos, double margin,
                          double diag, bool zero_stiffness, double* R, double* B, double* c) {
   double solref[2], solimp[5];
   sanitize_sol(timestep, disableflags, sr, si, solref, solimp);
@@ -90,7 +90,7 @@ PS_HD void co_row_params(double timestep, int disableflags, const double* sr, co
 
 // rows of contact ci: compressed Jacobian, impedance, cone scaling.  Runs on ONE lane.
 template <class T>
-PS_FN void co_contact_rows(const DevModel<T>& m, CoopData<T>& d, int ci) {
+PS_NI void co_contact_rows(const DevModel<T>& m, CoopData<T>& d, int ci) { PS_ASSUME_SHARED(&m); PS_ASSUME_SHARED(&d);
   constexpr int NCH = T::NCH;
   CoopContact& con = d.contact[ci];
   const int dim = con.dim, adr = con.efc_address;
@@ -174,7 +174,7 @@ PS_FN void co_contact_rows(const DevModel<T>& m, CoopData<T>& d, int ci) {
 }
 
 template <class T>
-PS_FN void co_make_constraints(const Lanes& L, const DevModel<T>& m, CoopData<T>& d) {
+PS_NI void co_make_constraints(const Lanes& L, const DevModel<T>& m, CoopData<T>& d) { PS_ASSUME_SHARED(&m); PS_ASSUME_SHARED(&d);
   if (m.disableflags & DSBL_CONSTRAINT) { if (L.lane == 0) { d.nefc = 0; d.ncon = 0; d.nlimit = 0; } L.sync(); return; }
   co_detect_contacts(L, m, d);
   const int ncon = d.ncon;
@@ -242,7 +242,7 @@ PS_FN void co_make_constraints(const Lanes& L, const DevModel<T>& m, CoopData<T>
 
 // aref = -B (J v) - K imp (pos - margin); B and the position term were parked in efc_force / efc_aref
 template <class T>
-PS_FN void co_reference_acceleration(const Lanes& L, const DevModel<T>& m, CoopData<T>& d) {
+PS_NI void co_reference_acceleration(const Lanes& L, const DevModel<T>& m, CoopData<T>& d) { PS_ASSUME_SHARED(&m); PS_ASSUME_SHARED(&d);
   CO_FOR(i, d.nefc) {
     const double vel = co_row_dot(m, d, i, d.qvel);
     d.efc_aref[i] = -d.efc_force[i] * vel - d.efc_aref[i];

@@ -8,7 +8,7 @@ namespace ps {
 
 // ---------------------------------------------------------------- kinematics, one tree level per phase
 template <class T>
-PS_FN void co_body_frame(const DevModel<T>& m, CoopData<T>& d, int b) {
+PS_NI void co_body_frame(const DevModel<T>& m, CoopData<T>& d, int b) { PS_ASSUME_SHARED(&m); PS_ASSUME_SHARED(&d);
   double pos[3], quat[4];
   const int par = m.body_parentid[b], jn = m.body_jntnum[b], ja = m.body_jntadr[b];
   if (m.body_mocapid[b] >= 0) {
@@ -51,7 +51,7 @@ PS_FN void co_body_frame(const DevModel<T>& m, CoopData<T>& d, int b) {
 }
 
 template <class T>
-PS_FN void co_kinematics(const Lanes& L, const DevModel<T>& m, CoopData<T>& d) {
+PS_NI void co_kinematics(const Lanes& L, const DevModel<T>& m, CoopData<T>& d) { PS_ASSUME_SHARED(&m); PS_ASSUME_SHARED(&d);
   // quaternion normalisation of the state (mj_kinematics does it in place) + world body
   CO_FOR(j, m.njnt) {
     if (m.jnt_type[j] == JNT_FREE) unit4(d.qpos + m.jnt_qposadr[j] + 3);
@@ -81,7 +81,7 @@ PS_FN void co_kinematics(const Lanes& L, const DevModel<T>& m, CoopData<T>& d) {
 // fold children into parents, deepest level first: x[p] += x[c] for c in children(p), decreasing c,
 // `n` values per body.  include_world: whether body 0 accumulates too.
 template <class T>
-PS_FN void co_fold_children(const Lanes& L, const DevModel<T>& m, double* x, int n, bool include_world) {
+PS_NI void co_fold_children(const Lanes& L, const DevModel<T>& m, double* x, int n, bool include_world) { PS_ASSUME_SHARED(&m);
   for (int l = m.nlevel - 2; l >= (include_world ? 0 : 1); l--) {
     const int a = m.level_adr[l], nb = m.level_adr[l + 1] - a;
     CO_FOR(w, nb * n) {
@@ -96,7 +96,7 @@ PS_FN void co_fold_children(const Lanes& L, const DevModel<T>& m, double* x, int
 
 // ---------------------------------------------------------------- CoM frame quantities
 template <class T>
-PS_FN void co_com_position(const Lanes& L, const DevModel<T>& m, CoopData<T>& d) {
+PS_NI void co_com_position(const Lanes& L, const DevModel<T>& m, CoopData<T>& d) { PS_ASSUME_SHARED(&m); PS_ASSUME_SHARED(&d);
   const int nb = m.nbody;
   double* sc = d.subtree_com;
   CO_FOR(w, 3 * nb) sc[w] = m.body_mass[w / 3] * d.xipos[w];
@@ -150,7 +150,7 @@ PS_FN void co_com_position(const Lanes& L, const DevModel<T>& m, CoopData<T>& d)
 // ---------------------------------------------------------------- tree-sparse L'DL
 // in-place factorisation of the symmetric matrix in A (lower triangle, tree sparsity)
 template <class T>
-PS_FN void co_factor_tree(const Lanes& L, const DevModel<T>& m, double* A, double* dinv) {
+PS_NI void co_factor_tree(const Lanes& L, const DevModel<T>& m, double* A, double* dinv) { PS_ASSUME_SHARED(&m);
   constexpr int S = T::NV; const int nv = m.nv;
   for (int k = nv - 1; k >= 0; k--) {
     double dk = A[k * S + k];
@@ -174,7 +174,7 @@ PS_FN void co_factor_tree(const Lanes& L, const DevModel<T>& m, double* A, doubl
 
 // x <- (L' D L)^-1 x
 template <class T>
-PS_FN void co_solve_tree(const Lanes& L, const DevModel<T>& m, double* x, const double* A, const double* dinv) {
+PS_NI void co_solve_tree(const Lanes& L, const DevModel<T>& m, double* x, const double* A, const double* dinv) { PS_ASSUME_SHARED(&m);
   constexpr int S = T::NV; const int nv = m.nv;
   // x <- L^-T x : a dof collects from its descendants (deepest first, decreasing index)
   for (int l = m.ndoflevel - 2; l >= 0; l--) {
@@ -204,7 +204,7 @@ PS_FN void co_solve_tree(const Lanes& L, const DevModel<T>& m, double* x, const 
 
 // ---------------------------------------------------------------- composite inertia, mass matrix
 template <class T>
-PS_FN void co_mass_matrix(const Lanes& L, const DevModel<T>& m, CoopData<T>& d) {
+PS_NI void co_mass_matrix(const Lanes& L, const DevModel<T>& m, CoopData<T>& d) { PS_ASSUME_SHARED(&m); PS_ASSUME_SHARED(&d);
   constexpr int S = T::NV; const int nb = m.nbody, nv = m.nv;
   double* crb = d.crb();
   CO_FOR(w, 10 * nb) crb[w] = d.cinert[w];
@@ -227,12 +227,12 @@ PS_FN void co_mass_matrix(const Lanes& L, const DevModel<T>& m, CoopData<T>& d) 
 }
 
 template <class T>
-PS_FN void co_mul_M(const Lanes& L, const DevModel<T>& m, const CoopData<T>& d, double* res, const double* vec) {
+PS_NI void co_mul_M(const Lanes& L, const DevModel<T>& m, const CoopData<T>& d, double* res, const double* vec) { PS_ASSUME_SHARED(&m); PS_ASSUME_SHARED(&d);
   CO_FOR(i, m.nv) res[i] = vdot(d.qM + i * T::NV, vec, m.nv);
 }
 
 template <class T>
-PS_FN void co_position_smooth(const Lanes& L, const DevModel<T>& m, CoopData<T>& d) {
+PS_NI void co_position_smooth(const Lanes& L, const DevModel<T>& m, CoopData<T>& d) { PS_ASSUME_SHARED(&m); PS_ASSUME_SHARED(&d);
   co_kinematics(L, m, d);
   CO_FOR(i, m.nu) d.actuator_length[i] = m.act_gear[i] * d.qpos[m.jnt_qposadr[m.act_jntid[i]]];
   L.sync();
@@ -242,7 +242,7 @@ PS_FN void co_position_smooth(const Lanes& L, const DevModel<T>& m, CoopData<T>&
 
 // ---------------------------------------------------------------- velocity stage
 template <class T>
-PS_FN void co_body_velocity(const DevModel<T>& m, const CoopData<T>& d, const double* qvel, double* cvel, double* cdof_dot, int i) {
+PS_NI void co_body_velocity(const DevModel<T>& m, const CoopData<T>& d, const double* qvel, double* cvel, double* cdof_dot, int i) { PS_ASSUME_SHARED(&m); PS_ASSUME_SHARED(&d);
   double v[6]; vcopy(v, cvel + 6 * m.body_parentid[i], 6);
   const int ja = m.body_jntadr[i];
   for (int j = ja; j < ja + m.body_jntnum[i]; j++) {
@@ -266,7 +266,7 @@ PS_FN void co_body_velocity(const DevModel<T>& m, const CoopData<T>& d, const do
 }
 
 template <class T>
-PS_FN void co_velocity_stage(const Lanes& L, const DevModel<T>& m, CoopData<T>& d) {
+PS_NI void co_velocity_stage(const Lanes& L, const DevModel<T>& m, CoopData<T>& d) { PS_ASSUME_SHARED(&m); PS_ASSUME_SHARED(&d);
   const int nv = m.nv, nb = m.nbody;
   double* cvel = d.cvel(); double* cdd = d.cdof_dot();
   CO_FOR(i, m.nu) d.actuator_velocity[i] = m.act_gear[i] * d.qvel[m.jnt_dofadr[m.act_jntid[i]]];
@@ -317,7 +317,7 @@ PS_FN void co_velocity_stage(const Lanes& L, const DevModel<T>& m, CoopData<T>& 
 
 // ---------------------------------------------------------------- subtree momentum (sensor support)
 template <class T>
-PS_FN void co_subtree_velocity(const Lanes& L, const DevModel<T>& m, CoopData<T>& d) {
+PS_NI void co_subtree_velocity(const Lanes& L, const DevModel<T>& m, CoopData<T>& d) { PS_ASSUME_SHARED(&m); PS_ASSUME_SHARED(&d);
   const int nb = m.nbody;
   double* bodyvel = d.scratch; double* lv = d.subtree_linvel; double* am = d.subtree_angmom;
   CO_FOR(i, nb) {
@@ -358,7 +358,7 @@ PS_FN void co_subtree_velocity(const Lanes& L, const DevModel<T>& m, CoopData<T>
 
 // ---------------------------------------------------------------- actuation + smooth acceleration
 template <class T>
-PS_FN void co_actuation_stage(const Lanes& L, const DevModel<T>& m, CoopData<T>& d) {
+PS_NI void co_actuation_stage(const Lanes& L, const DevModel<T>& m, CoopData<T>& d) { PS_ASSUME_SHARED(&m); PS_ASSUME_SHARED(&d);
   const int nv = m.nv, nu = m.nu;
   CO_FOR(i, nv) d.qfrc_actuator[i] = 0;
   CO_FOR(i, m.na) d.act_dot[i] = 0;
@@ -400,7 +400,7 @@ PS_FN void co_actuation_stage(const Lanes& L, const DevModel<T>& m, CoopData<T>&
 }
 
 template <class T>
-PS_FN void co_acceleration_stage(const Lanes& L, const DevModel<T>& m, CoopData<T>& d) {
+PS_NI void co_acceleration_stage(const Lanes& L, const DevModel<T>& m, CoopData<T>& d) { PS_ASSUME_SHARED(&m); PS_ASSUME_SHARED(&d);
   CO_FOR(i, m.nv) {
     d.qfrc_smooth[i] = d.qfrc_passive[i] - d.qfrc_bias[i] + d.qfrc_actuator[i];
     d.qacc_smooth[i] = d.qfrc_smooth[i];

@@ -9,7 +9,7 @@ namespace ps {
 
 // state, force and cost term of every row for jar = J a - aref; returns the summed cost
 template <class T>
-PS_FN double co_update_rows(const Lanes& L, const DevModel<T>& m, CoopData<T>& d, const double* jar) {
+PS_NI double co_update_rows(const Lanes& L, const DevModel<T>& m, CoopData<T>& d, const double* jar) { PS_ASSUME_SHARED(&m); PS_ASSUME_SHARED(&d);
   const int nefc = d.nefc;
   CO_FOR(i, nefc) {
     const int tp = d.efc_type[i];
@@ -57,7 +57,7 @@ PS_FN double co_update_rows(const Lanes& L, const DevModel<T>& m, CoopData<T>& d
 struct CoSolverScalars { double cost, gauss, prev_cost; };
 
 template <class T>
-PS_FN void co_update_cost(const Lanes& L, const DevModel<T>& m, CoopData<T>& d, CoSolverScalars& c) {
+PS_NI void co_update_cost(const Lanes& L, const DevModel<T>& m, CoopData<T>& d, CoSolverScalars& c) { PS_ASSUME_SHARED(&m); PS_ASSUME_SHARED(&d);
   const int nv = m.nv;
   const double cc = co_update_rows(L, m, d, d.sv_Jaref);
   double g = 0;
@@ -90,7 +90,7 @@ PS_FN void co_update_cost(const Lanes& L, const DevModel<T>& m, CoopData<T>& d, 
 
 // H = M + J' D_active J (+ cone blocks) -> Cholesky -> search = -H^-1 grad
 template <class T>
-PS_FN void co_newton_direction(const Lanes& L, const DevModel<T>& m, CoopData<T>& d) {
+PS_NI void co_newton_direction(const Lanes& L, const DevModel<T>& m, CoopData<T>& d) { PS_ASSUME_SHARED(&m); PS_ASSUME_SHARED(&d);
   constexpr int S = T::NV, NCH = T::NCH; const int nv = m.nv;
   double* H = d.qH;
   CO_FOR(i, nv) d.sv_grad[i] = d.sv_Ma[i] - d.qfrc_smooth[i] - d.qfrc_constraint[i];
@@ -140,9 +140,7 @@ PS_FN void co_newton_direction(const Lanes& L, const DevModel<T>& m, CoopData<T>
       L.sync();
     }
     CO_FOR(w, npair) {
-      // w -> (ki >= kj)
-      int ki = 0; while ((ki + 1) * (ki + 2) / 2 <= w) ki++;
-      const int kj = w - ki * (ki + 1) / 2;
+      const int ki = m.tri_a[w], kj = m.tri_b[w];     // ki >= kj
       double* h = H + dof[ki] * S + dof[kj];
       double acc = *h;
       if (cone) { for (int a = 0; a < con.dim; a++) acc += J[a * NCH + ki] * d.sv_T[a * NCH + kj]; }
@@ -151,17 +149,21 @@ PS_FN void co_newton_direction(const Lanes& L, const DevModel<T>& m, CoopData<T>
     }
     L.sync();
   }
-  // Cholesky by columns: entry (i, j) = (H_ij - sum_{k<j} L_ik L_jk) / L_jj
+  // right-looking Cholesky: scale column j, then subtract its outer product from the trailing
+  // triangle.  Entry (i, k) receives the products of columns 0 .. k-1 in that order, which is the
+  // summation order of the row-by-row formulation (s -= L_ik' L_kk', k' ascending).
   for (int j = 0; j < nv; j++) {
-    double dg = 0;
+    const double dg = sqrt(fmax(H[j * S + j], kMinVal));
+    L.sync();
     for (int base = j; base < nv; base += L.width) {
       const int i = base + L.lane;
-      double s = 0;
-      if (i < nv) { s = H[i * S + j]; for (int k = 0; k < j; k++) s -= H[i * S + k] * H[j * S + k]; }
-      if (base == j) {
-        dg = L.bcast(sqrt(fmax(s, kMinVal)), 0);
-        if (i == j) H[j * S + j] = dg; else if (i < nv) H[i * S + j] = s / dg;
-      } else if (i < nv) H[i * S + j] = s / dg;
+      if (i == j) H[j * S + j] = dg; else if (i < nv) H[i * S + j] = H[i * S + j] / dg;
+    }
+    L.sync();
+    const int n = nv - 1 - j;
+    CO_FOR(w, n * (n + 1) / 2) {
+      const int i = j + 1 + m.tri_a[w], k = j + 1 + m.tri_b[w];
+      H[i * S + k] -= H[i * S + j] * H[k * S + j];
     }
     L.sync();
   }
@@ -189,8 +191,8 @@ PS_FN void co_newton_direction(const Lanes& L, const DevModel<T>& m, CoopData<T>
 
 // value, slope and curvature of the total cost along the search direction at step alpha
 template <class T>
-PS_FN void co_line_eval(const Lanes& L, const DevModel<T>& m, CoopData<T>& d, const double* qg, double alpha,
-                        double* cost, double* d1, double* d2) {
+PS_NI void co_line_eval(const Lanes& L, const DevModel<T>& m, CoopData<T>& d, const double* qg, double alpha,
+                        double* cost, double* d1, double* d2) { PS_ASSUME_SHARED(&m); PS_ASSUME_SHARED(&d);
   const int nefc = d.nefc;
   double* tf = d.sv_tmp; double* tg = d.efc_force; double* th = d.efc_aref;     // both dead during the line search
   CO_FOR(i, nefc) {
@@ -231,16 +233,22 @@ PS_FN void co_line_eval(const Lanes& L, const DevModel<T>& m, CoopData<T>& d, co
     }
   }
   L.sync();
-  double f = qg[0] + alpha * qg[1] + alpha * alpha * qg[2];
-  double g = qg[1] + 2 * alpha * qg[2];
-  double h = 2 * qg[2];
-  for (int i = 0; i < nefc; i++) { f += tf[i]; g += tg[i]; h += th[i]; }
+  double f, g, h;
+  if (Lanes::single || L.width == 1) {       // one working lane: plain sequential sums
+    f = qg[0] + alpha * qg[1] + alpha * alpha * qg[2]; g = qg[1] + 2 * alpha * qg[2]; h = 2 * qg[2];
+    for (int i = 0; i < nefc; i++) { f += tf[i]; g += tg[i]; h += th[i]; }
+  } else {                                   // three lanes add up one quantity each, in row order, then broadcast
+    double acc = L.lane == 0 ? qg[0] + alpha * qg[1] + alpha * alpha * qg[2] : (L.lane == 1 ? qg[1] + 2 * alpha * qg[2] : 2 * qg[2]);
+    const double* src = L.lane == 0 ? tf : (L.lane == 1 ? tg : th);
+    if (L.lane < 3) for (int i = 0; i < nefc; i++) acc += src[i];
+    f = L.bcast(acc, 0); g = L.bcast(acc, 1); h = L.bcast(acc, 2);
+  }
   L.sync();
   *cost = f; *d1 = g; *d2 = h;
 }
 
 template <class T>
-PS_FN double co_line_search(const Lanes& L, const DevModel<T>& m, CoopData<T>& d, const CoSolverScalars& c) {
+PS_NI double co_line_search(const Lanes& L, const DevModel<T>& m, CoopData<T>& d, const CoSolverScalars& c) { PS_ASSUME_SHARED(&m); PS_ASSUME_SHARED(&d);
   const int nv = m.nv, nefc = d.nefc;
   const double snorm = sqrt(vdot(d.sv_search, d.sv_search, nv));
   if (snorm < kMinVal) return 0;
@@ -269,7 +277,7 @@ PS_FN double co_line_search(const Lanes& L, const DevModel<T>& m, CoopData<T>& d
 }
 
 template <class T>
-PS_FN void co_constraint_stage(const Lanes& L, const DevModel<T>& m, CoopData<T>& d) {
+PS_NI void co_constraint_stage(const Lanes& L, const DevModel<T>& m, CoopData<T>& d) { PS_ASSUME_SHARED(&m); PS_ASSUME_SHARED(&d);
   const int nv = m.nv, nefc = d.nefc;
   if (!nefc) {
     CO_FOR(i, nv) { d.qacc[i] = d.qacc_smooth[i]; d.qacc_warmstart[i] = d.qacc_smooth[i]; d.qfrc_constraint[i] = 0; }

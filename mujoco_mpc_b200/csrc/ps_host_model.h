@@ -112,6 +112,7 @@ inline int build_schedules(const PsModel* s, DevModel<T>& m, std::string* why) {
     for (int j = i; j >= 0; j = s->dof_parentid[j]) { m.mpair_i[mp] = (unsigned char)i; m.mpair_j[mp] = (unsigned char)j; mp++; }
   }
   m.dofdesc_adr[nv] = (short)ad; m.dofanc_adr[nv] = (short)aa; m.fpair_adr[nv] = (short)fp; m.nmpair = mp;
+  for (int a = 0, w = 0; a < T::NV; a++) for (int b = 0; b <= a; b++, w++) { m.tri_a[w] = (unsigned char)a; m.tri_b[w] = (unsigned char)b; }
   m.nfrictionrow = 0;
   for (int i = 0; i < nv; i++) {
     m.dof_frictionrow[i] = -1;

@@ -13,9 +13,18 @@
 #if defined(__CUDACC__)
 #define PS_HD __host__ __device__ __forceinline__
 #define PS_FN __host__ __device__ inline
+// out-of-line on the device: the rollout kernels are hundreds of KB of SASS when everything is
+// inlined, and a warp that walks that much code stalls on instruction fetch
+#define PS_NI __host__ __device__ __noinline__ inline
 #else
 #define PS_HD inline
 #define PS_FN inline
+#define PS_NI inline
+#endif
+#if defined(__CUDA_ARCH__)
+#define PS_ASSUME_SHARED(p) __builtin_assume(__isShared(p))
+#else
+#define PS_ASSUME_SHARED(p) ((void)0)
 #endif
 
 namespace ps {
@@ -124,6 +133,8 @@ struct alignas(16) DevModel {
   // nonzeros of the mass matrix: (i, j) with j an ancestor-or-self of i
   unsigned char mpair_i[T::NTRI + T::NV], mpair_j[T::NTRI + T::NV];
   short frictionrow_dof[T::NV], dof_frictionrow[T::NV];
+  // w -> (a, b), a >= b: row-major enumeration of a lower triangle (entry w = a (a + 1) / 2 + b)
+  unsigned char tri_a[T::NTRI + T::NV], tri_b[T::NTRI + T::NV];
   // geoms whose world frames the task reads (feet, ray scenery, sensor geoms)
   short track_geom[kMaxTrackGeom], geom_trackslot[T::NGEOM];
 };
