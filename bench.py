@@ -32,7 +32,6 @@ WORKLOADS = {
 }
 DEFAULT_WORKLOAD = "acrobot+particle_4096_cubic"
 METRIC = "rollout sample-steps/sec"
-CONST_BYTES = {"tiny": 6144, "planar": 11264, "legged": 23552}   # sizeof(Constants<T>) rounded up
 # FP64 flops per sample-step (FMA = 2), from the ncu instruction counts of the rollout kernel
 # (profiles/flops_per_sample_step.json, see DESIGN.md "Measurement")
 FLOPS_FILE = os.path.join(ROOT, "profiles", "flops_per_sample_step.json")
@@ -272,7 +271,7 @@ def main():
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     e2e_value = units / float(t.item())
     # per iteration: the whole Constants block (model + task + plan, pinned) + nominal knots go up, the winner record comes back
-    h2d = sum(CONST_BYTES.get(e.variant(), 0) + 8 * c["P"] * c["model"].nu for e, c in zip(engines, cases))
+    h2d = sum(e.constants_bytes() + 8 * c["P"] * c["model"].nu for e, c in zip(engines, cases))
     d2h = sum(8 * (3 + c["P"] * c["model"].nu) for c in cases)
 
     if rank == 0:
@@ -285,6 +284,7 @@ def main():
                 "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
                 "data": "synthetic", "config": {"workload": args.workload, "samples_per_gpu": [c["N"] for c in cases],
                                                 "horizon_steps": [c["H"] for c in cases], "l2": "flushed (256 MB write) between iterations",
+                                                "kernels": [e.variant() for e in engines],
                                                 "parallelism": f"samples sharded over {world} rank(s), NCCL all-gather min-loc"},
                 "planning_iteration_latency_ms": ms_step, "kernel_ms": {"perturb": kern_ms[0] / args.steps, "rollout": rollout_ms, "argmin": kern_ms[2] / args.steps},
                 "e2e": {"value": e2e_value, "unit": "sample-steps/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,

@@ -94,8 +94,12 @@ int ps_stream(PsEngine* e, void** stream);
 /* ps_rollouts without the final device->host read: results stay in the winner record */
 int ps_rollouts_async(PsEngine* e, int N, int H, double sigma0, double sigma1, int sample_offset);
 int ps_name(char* out, int cap);
-/* engine instantiation chosen for the model ("tiny" / "planar" / "legged") */
+/* kernel instantiation that served the last batch: "tiny", "planar", "legged" (thread-per-rollout),
+   "planar_coop" / "legged_coop" (warp-per-rollout, small batches), "legged_sparse" (thread-per-rollout over
+   the compressed-Jacobian phases, large batches) */
 int ps_variant(PsEngine* e, char* out, int cap);
+/* bytes of model + task + plan constants uploaded per planning iteration for that kernel */
+int ps_constants_bytes(PsEngine* e);
 /* ps_rollouts with full per-step writeback of every sample (parity tests, traces) */
 int ps_rollouts_writeback(PsEngine* e, int N, int H, double sigma0, double sigma1, int sample_offset,
                           int* winner, double* winner_return, double* nominal_return);

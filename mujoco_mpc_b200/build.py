@@ -9,7 +9,8 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 OUT = os.path.join(HERE, "libps_engine.so")
 UNITS = ["ps_engine.cu", "ps_variant_tiny.cu", "ps_variant_planar.cu", "ps_variant_legged.cu",
-         "ps_variant_planar_coop.cu", "ps_variant_legged_coop.cu"]
+         "ps_variant_planar_coop.cu", "ps_variant_legged_coop.cu", "ps_variant_planar_sparse.cu",
+         "ps_variant_legged_sparse.cu"]
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 # -fmad=false: FP64 multiply-adds are NOT contracted, so the device arithmetic is operation-for-operation
 # the IEEE sequence the oracle executes (-ffp-contract=off).  Contact-rich rollouts amplify rounding
@@ -47,7 +48,7 @@ def build(force=False, verbose=False, extra=()):
         if r.returncode:
             raise RuntimeError("nvcc failed: " + " ".join(cmd))
 
-    with ThreadPoolExecutor(max_workers=6) as ex:
+    with ThreadPoolExecutor(max_workers=8) as ex:
         list(ex.map(run, jobs))
     if jobs or force or _stale(OUT, objs):
         run([NVCC, "-shared", "-o", OUT] + objs + ["-lcudart"])

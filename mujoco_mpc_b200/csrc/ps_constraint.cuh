@@ -22,7 +22,7 @@ PS_HD int hit_plane_sphere(RawContact* c, const double* pp, const double* pm, co
   return 1;
 }
 
-PS_NI int hit_plane_capsule(RawContact* c, const double* pp, const double* pm, const double* cp, const double* cm,
+PS_NT int hit_plane_capsule(RawContact* c, const double* pp, const double* pm, const double* cp, const double* cm,
                             const double* size, double margin) {
   const double axis[3] = {cm[2], cm[5], cm[8]};
   int cnt = 0;
@@ -34,7 +34,7 @@ PS_NI int hit_plane_capsule(RawContact* c, const double* pp, const double* pm, c
   return cnt;
 }
 
-PS_NI int hit_plane_cylinder(RawContact* c, const double* pp, const double* pm, const double* cp, const double* cm,
+PS_NT int hit_plane_cylinder(RawContact* c, const double* pp, const double* pm, const double* cp, const double* cm,
                              const double* size, double margin) {
   const double n[3] = {pm[2], pm[5], pm[8]}; double axis[3] = {cm[2], cm[5], cm[8]};
   const double r = size[0], h = size[1];
@@ -77,7 +77,7 @@ PS_NI int hit_plane_cylinder(RawContact* c, const double* pp, const double* pm, 
   return cnt;
 }
 
-PS_NI int hit_plane_box(RawContact* c, const double* pp, const double* pm, const double* bp, const double* bm,
+PS_NT int hit_plane_box(RawContact* c, const double* pp, const double* pm, const double* bp, const double* bm,
                         const double* size, double margin) {
   const double n[3] = {pm[2], pm[5], pm[8]};
   const double dif[3] = {bp[0] - pp[0], bp[1] - pp[1], bp[2] - pp[2]};
@@ -107,7 +107,7 @@ PS_HD int hit_sphere_sphere(RawContact* c, const double* p1, double r1, const do
   return 1;
 }
 
-PS_NI int hit_sphere_capsule(RawContact* c, const double* p1, double r1, const double* p2, const double* m2,
+PS_NT int hit_sphere_capsule(RawContact* c, const double* p1, double r1, const double* p2, const double* m2,
                              const double* size2, double margin) {
   const double axis[3] = {m2[2], m2[5], m2[8]};
   const double dif[3] = {p1[0] - p2[0], p1[1] - p2[1], p1[2] - p2[2]};
@@ -116,7 +116,7 @@ PS_NI int hit_sphere_capsule(RawContact* c, const double* p1, double r1, const d
   return hit_sphere_sphere(c, p1, r1, q, size2[0], margin);
 }
 
-PS_NI int hit_capsule_capsule(RawContact* c, const double* p1, const double* m1, const double* s1,
+PS_NT int hit_capsule_capsule(RawContact* c, const double* p1, const double* m1, const double* s1,
                               const double* p2, const double* m2, const double* s2, double margin) {
   const double a1[3] = {m1[2], m1[5], m1[8]}, a2[3] = {m2[2], m2[5], m2[8]};
   const double dif[3] = {p1[0] - p2[0], p1[1] - p2[1], p1[2] - p2[2]};
@@ -157,7 +157,7 @@ PS_HD void complete_frame(double* f) {
 }
 
 template <class T, class C>
-PS_FN void mix_contact_params(const DevModel<T>& m, int g1, int g2, C* con) {
+PS_NT void mix_contact_params(const DevModel<T>& m, int g1, int g2, C* con) {
   const int p1 = m.geom_priority[g1], p2 = m.geom_priority[g2];
   double fri[3];
   if (p1 != p2) {
@@ -182,7 +182,7 @@ PS_FN void mix_contact_params(const DevModel<T>& m, int g1, int g2, C* con) {
 }
 
 template <class T>
-PS_FN void detect_contacts(const DevModel<T>& m, RolloutData<T>& d) {
+PS_NT void detect_contacts(const DevModel<T>& m, RolloutData<T>& d) {
   d.ncon = 0;
   if (m.disableflags & (DSBL_CONTACT | DSBL_CONSTRAINT)) return;
   for (int p = 0; p < m.npair; p++) {
@@ -239,7 +239,7 @@ PS_HD double pow_small(double x, double p) {
   return pow(x, p);
 }
 
-PS_NI double impedance_at(const double* si, double pos, double margin) {
+PS_NT double impedance_at(const double* si, double pos, double margin) {
   if (si[0] == si[1] || si[2] <= kMinVal) return 0.5 * (si[0] + si[1]);
   const double x = fabs((pos - margin) / si[2]);
   if (x >= 1) return si[1];
@@ -260,7 +260,7 @@ PS_HD bool push_row(RolloutData<T>& d, double pos, double margin, double floss, 
 }
 
 template <class T>
-PS_FN void make_constraints(const DevModel<T>& m, RolloutData<T>& d) {
+PS_NT void make_constraints(const DevModel<T>& m, RolloutData<T>& d) {
   constexpr int S = T::NV; const int nv = m.nv;
   d.nefc = 0; d.ncon = 0;
   if (m.disableflags & DSBL_CONSTRAINT) return;
@@ -388,7 +388,7 @@ PS_FN void make_constraints(const DevModel<T>& m, RolloutData<T>& d) {
 
 // aref = -B (J v) - K imp (pos - margin)
 template <class T>
-PS_FN void reference_acceleration(const DevModel<T>& m, RolloutData<T>& d) {
+PS_NT void reference_acceleration(const DevModel<T>& m, RolloutData<T>& d) {
   for (int i = 0; i < d.nefc; i++) {
     const double vel = vdot(d.efc_J + i * T::NV, d.qvel, m.nv);
     const double* k = d.efc_KBI + 3 * i;
@@ -399,7 +399,7 @@ PS_FN void reference_acceleration(const DevModel<T>& m, RolloutData<T>& d) {
 // ---------------------------------------------------------------- Newton solver
 // per-row state / force / cost for jar = J a - aref
 template <class T>
-PS_FN double update_rows(const DevModel<T>& m, RolloutData<T>& d, const double* jar, bool cone_hessian) {
+PS_NT double update_rows(const DevModel<T>& m, RolloutData<T>& d, const double* jar, bool cone_hessian) {
   double cost = 0;
   const int nefc = d.nefc;
   for (int i = 0; i < nefc; i++) {
@@ -455,7 +455,7 @@ PS_FN double update_rows(const DevModel<T>& m, RolloutData<T>& d, const double* 
 struct SolverScalars { double cost, gauss, prev_cost; };
 
 template <class T>
-PS_FN void update_cost(const DevModel<T>& m, RolloutData<T>& d, SolverScalars& c, bool coneH) {
+PS_NT void update_cost(const DevModel<T>& m, RolloutData<T>& d, SolverScalars& c, bool coneH) {
   constexpr int S = T::NV; const int nv = m.nv;
   const double cc = update_rows(m, d, d.sv_Jaref, coneH);
   double g = 0;
@@ -470,7 +470,7 @@ PS_FN void update_cost(const DevModel<T>& m, RolloutData<T>& d, SolverScalars& c
 
 // H = M + J' D_active J (+ cone blocks), dense Cholesky, search = -H^-1 grad
 template <class T>
-PS_FN void newton_direction(const DevModel<T>& m, RolloutData<T>& d) {
+PS_NT void newton_direction(const DevModel<T>& m, RolloutData<T>& d) {
   constexpr int S = T::NV; const int nv = m.nv, nefc = d.nefc;
   for (int i = 0; i < nv; i++) d.sv_grad[i] = d.sv_Ma[i] - d.qfrc_smooth[i] - d.qfrc_constraint[i];
   double* H = d.sv_H;
@@ -507,7 +507,7 @@ PS_FN void newton_direction(const DevModel<T>& m, RolloutData<T>& d) {
 
 // value, slope and curvature of the total cost along the search direction at step alpha
 template <class T>
-PS_FN void line_eval(const DevModel<T>& m, const RolloutData<T>& d, const double* qg, double alpha,
+PS_NT void line_eval(const DevModel<T>& m, const RolloutData<T>& d, const double* qg, double alpha,
                      double* cost, double* d1, double* d2) {
   double f = qg[0] + alpha * qg[1] + alpha * alpha * qg[2];
   double g = qg[1] + 2 * alpha * qg[2];
@@ -552,7 +552,7 @@ PS_FN void line_eval(const DevModel<T>& m, const RolloutData<T>& d, const double
 }
 
 template <class T>
-PS_FN double line_search(const DevModel<T>& m, RolloutData<T>& d, const SolverScalars& c) {
+PS_NT double line_search(const DevModel<T>& m, RolloutData<T>& d, const SolverScalars& c) {
   constexpr int S = T::NV; const int nv = m.nv, nefc = d.nefc;
   const double snorm = sqrt(vdot(d.sv_search, d.sv_search, nv));
   if (snorm < kMinVal) return 0;
@@ -580,7 +580,7 @@ PS_FN double line_search(const DevModel<T>& m, RolloutData<T>& d, const SolverSc
 }
 
 template <class T>
-PS_FN void constraint_stage(const DevModel<T>& m, RolloutData<T>& d) {
+PS_NT void constraint_stage(const DevModel<T>& m, RolloutData<T>& d) {
   constexpr int S = T::NV; const int nv = m.nv, nefc = d.nefc;
   d.solver_iter = 0;
   if (!nefc) {

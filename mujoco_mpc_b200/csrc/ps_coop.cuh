@@ -15,9 +15,23 @@
 namespace ps {
 
 // ---------------------------------------------------------------- lanes
+// One working lane: the host build (tests/hostsim) and the thread-per-rollout instantiation of the
+// same phases, where every "parallel-for" is an ordinary loop.
+struct Lanes1 {
+  static constexpr bool single = true, kSharedData = false;
+  static constexpr int lane = 0, width = 1;
+  PS_HD void sync() const {}
+  PS_HD int bcast(int v, int) const { return v; }
+  PS_HD double bcast(double v, int) const { return v; }
+  PS_HD bool any(bool p) const { return p; }
+  PS_HD int scan(int v, int* total) const { *total = v; return 0; }
+  PS_HD int min(int v) const { return v; }
+};
+
+#ifdef __CUDACC__
+// The 32 lanes of a warp working on one rollout held in shared memory.
 struct Lanes {
-#ifdef __CUDA_ARCH__
-  static constexpr bool single = false;
+  static constexpr bool single = false, kSharedData = true;
   int lane;
   int width;      // 32; the diagnostics mode (DevModel::debug_serial) runs chosen stages with one working lane
   __device__ __forceinline__ void sync() const { __syncwarp(); }
@@ -36,18 +50,10 @@ struct Lanes {
     for (int o = 16; o > 0; o >>= 1) { const int t = __shfl_xor_sync(0xffffffffu, v, o); v = t < v ? t : v; }
     return v;
   }
-#else
-  static constexpr bool single = true;
-  static constexpr int lane = 0;
-  static constexpr int width = 1;
-  void sync() const {}
-  int bcast(int v, int) const { return v; }
-  double bcast(double v, int) const { return v; }
-  bool any(bool p) const { return p; }
-  int scan(int v, int* total) const { *total = v; return 0; }
-  int min(int v) const { return v; }
-#endif
 };
+#else
+typedef Lanes1 Lanes;
+#endif
 
 // parallel-for over [0, n): item i is handled by lane i mod width
 #define CO_FOR(i, n) for (int i = L.lane; i < (n); i += L.width)

@@ -22,8 +22,8 @@ PS_HD double co_row_dot(const DevModel<T>& m, const CoopData<T>& d, int r, const
 }
 
 // ---------------------------------------------------------------- narrow phase over the static pair list
-template <class T>
-PS_NI void co_detect_contacts(const Lanes& L, const DevModel<T>& m, CoopData<T>& d) { PS_ASSUME_SHARED(&m); PS_ASSUME_SHARED(&d);
+template <class T, class LT>
+PS_NI void co_detect_contacts(const LT& L, const DevModel<T>& m, CoopData<T>& d) { PS_ASSUME_SHARED(&m); if (LT::kSharedData) PS_ASSUME_SHARED(&d);
   int ncon = 0;
   if (!(m.disableflags & (DSBL_CONTACT | DSBL_CONSTRAINT))) {
     CO_ROUNDS(base, m.npair) {
@@ -89,8 +89,8 @@ PS_NI void co_row_params(double timestep, int disableflags, const double* sr, co
 }
 
 // rows of contact ci: compressed Jacobian, impedance, cone scaling.  Runs on ONE lane.
-template <class T>
-PS_NI void co_contact_rows(const DevModel<T>& m, CoopData<T>& d, int ci) { PS_ASSUME_SHARED(&m); PS_ASSUME_SHARED(&d);
+template <class T, class LT>
+PS_NI void co_contact_rows(const DevModel<T>& m, CoopData<T>& d, int ci) { PS_ASSUME_SHARED(&m); if (LT::kSharedData) PS_ASSUME_SHARED(&d);
   constexpr int NCH = T::NCH;
   CoopContact& con = d.contact[ci];
   const int dim = con.dim, adr = con.efc_address;
@@ -173,8 +173,8 @@ PS_NI void co_contact_rows(const DevModel<T>& m, CoopData<T>& d, int ci) { PS_AS
   for (int q = 0; q < nrow; q++) d.efc_D[adr + q] = 1 / R[q];
 }
 
-template <class T>
-PS_NI void co_make_constraints(const Lanes& L, const DevModel<T>& m, CoopData<T>& d) { PS_ASSUME_SHARED(&m); PS_ASSUME_SHARED(&d);
+template <class T, class LT>
+PS_NI void co_make_constraints(const LT& L, const DevModel<T>& m, CoopData<T>& d) { PS_ASSUME_SHARED(&m); if (LT::kSharedData) PS_ASSUME_SHARED(&d);
   if (m.disableflags & DSBL_CONSTRAINT) { if (L.lane == 0) { d.nefc = 0; d.ncon = 0; d.nlimit = 0; } L.sync(); return; }
   co_detect_contacts(L, m, d);
   const int ncon = d.ncon;
@@ -230,7 +230,7 @@ PS_NI void co_make_constraints(const Lanes& L, const DevModel<T>& m, CoopData<T>
       if (nr > 0 && ci < firstbad) {
         CoopContact& con = d.contact[ci];
         con.efc_address = (short)(nefc + off); con.jadr = (short)(jrows + off); con.nrow = (short)nr;
-        co_contact_rows(m, d, ci);
+        co_contact_rows<T, LT>(m, d, ci);
       }
       if (firstbad != 0x7fffffff) { nefc += L.bcast(off, firstbad - base); overflow = true; break; }
       nefc += total; jrows += total;
@@ -241,8 +241,8 @@ PS_NI void co_make_constraints(const Lanes& L, const DevModel<T>& m, CoopData<T>
 }
 
 // aref = -B (J v) - K imp (pos - margin); B and the position term were parked in efc_force / efc_aref
-template <class T>
-PS_NI void co_reference_acceleration(const Lanes& L, const DevModel<T>& m, CoopData<T>& d) { PS_ASSUME_SHARED(&m); PS_ASSUME_SHARED(&d);
+template <class T, class LT>
+PS_NI void co_reference_acceleration(const LT& L, const DevModel<T>& m, CoopData<T>& d) { PS_ASSUME_SHARED(&m); if (LT::kSharedData) PS_ASSUME_SHARED(&d);
   CO_FOR(i, d.nefc) {
     const double vel = co_row_dot(m, d, i, d.qvel);
     d.efc_aref[i] = -d.efc_force[i] * vel - d.efc_aref[i];

@@ -12,15 +12,16 @@
 namespace ps {
 
 // lanes a stage runs on: all of them, or (diagnostics) a single working lane
-PS_HD Lanes stage_lanes(const Lanes& L, int debug_serial, int stage) {
-#ifdef __CUDA_ARCH__
+PS_HD Lanes1 stage_lanes(const Lanes1& L, int, int) { return L; }
+#ifdef __CUDACC__
+__device__ __forceinline__ Lanes stage_lanes(const Lanes& L, int debug_serial, int stage) {
   if ((debug_serial >> stage) & 1) { Lanes S; S.lane = L.lane == 0 ? 0 : (1 << 28); S.width = 1; return S; }
-#endif
   return L;
 }
+#endif
 
-template <class T>
-PS_FN void co_forward_pass(const Lanes& L, const DevModel<T>& m, CoopData<T>& d) {
+template <class T, class LT>
+PS_FN void co_forward_pass(const LT& L, const DevModel<T>& m, CoopData<T>& d) {
   const int dbg = m.debug_serial;
   co_position_smooth(stage_lanes(L, dbg, 0), m, d);
   co_make_constraints(stage_lanes(L, dbg, 1), m, d);
@@ -34,8 +35,8 @@ PS_FN void co_forward_pass(const Lanes& L, const DevModel<T>& m, CoopData<T>& d)
 
 // semi-implicit Euler with implicit joint damping (mj_Euler); other integrators stay with the
 // thread-per-rollout engine
-template <class T>
-PS_FN void co_integrate(const Lanes& L, const DevModel<T>& m, CoopData<T>& d) {
+template <class T, class LT>
+PS_FN void co_integrate(const LT& L, const DevModel<T>& m, CoopData<T>& d) {
   constexpr int S = T::NV; const int nv = m.nv; const double dt = m.timestep;
   double* qacc = d.sv_x;
   if (!m.any_damping || (m.disableflags & DSBL_EULERDAMP)) { CO_FOR(i, nv) qacc[i] = d.qacc[i]; L.sync(); }
@@ -76,8 +77,8 @@ PS_FN void co_integrate(const Lanes& L, const DevModel<T>& m, CoopData<T>& d) {
 }
 
 // knots: SoA [P*nu][stride]; i = this rollout's column.  flags: bit0 failure, bit1 capacity overflow
-template <class T, bool WB>
-PS_FN double co_rollout(const Lanes& L, const DevModel<T>& m, const DevTask& task, const DevPlan<T>& plan, const double* knots,
+template <class T, bool WB, class LT>
+PS_FN double co_rollout(const LT& L, const DevModel<T>& m, const DevTask& task, const DevPlan<T>& plan, const double* knots,
                         int stride, int i, const Writeback& wb, CoopData<T>& d, int* flags) {
   const int nq = m.nq, nv = m.nv, na = m.na, nu = m.nu, ns = nq + nv + na, nr = task.num_residual;
   const int H = plan.horizon, P = plan.num_spline_points, ntr = 3 * task.num_trace;
@@ -197,6 +198,58 @@ coop_rollout_kernel(const Constants<T>* __restrict__ gconst, const double* __res
   if (threadIdx.x == 0) {
     for (int w = 1; w < WARPS; w++) if (better(warp_min[w].cost, warp_min[w].index, best, best_i)) { best = warp_min[w].cost; best_i = warp_min[w].index; }
     block_min[blockIdx.x].cost = best; block_min[blockIdx.x].index = best_i;
+  }
+}
+
+// ---------------------------------------------------------------- thread-per-rollout flavour of the same phases
+// One THREAD per rollout with a single working lane (Lanes1): the compressed-Jacobian algorithms of
+// the cooperative engine, SIMD across rollouts.  Its working set sits in local memory, so it needs
+// tens of thousands of rollouts in flight to hide that latency -- the large-batch engine, where the
+// warp-per-rollout kernel above is the small-batch (latency) engine.
+template <class T, int BLOCK, bool WB>
+__global__ void __launch_bounds__(BLOCK)
+sparse_rollout_kernel(const Constants<T>* __restrict__ gconst, const double* __restrict__ knots, int stride, int first, int n,
+                      long long sample_offset, double* __restrict__ returns, unsigned char* __restrict__ failure,
+                      MinLoc* __restrict__ block_min, Writeback wb) {
+  __shared__ Constants<T> sc;
+  __shared__ alignas(8) uint64_t bar;
+  __shared__ MinLoc warp_min[BLOCK / 32];
+  if (threadIdx.x == 0) { mbar_init(&bar, 1); asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    constexpr uint32_t total = (uint32_t)sizeof(Constants<T>);
+    mbar_expect_tx(&bar, total);
+    const char* src = reinterpret_cast<const char*>(gconst); char* dst = reinterpret_cast<char*>(&sc);
+    for (uint32_t off = 0; off < total; off += 32768u) {
+      const uint32_t sz = total - off < 32768u ? total - off : 32768u;
+      tma_bulk_g2s(dst + off, src + off, sz, &bar);
+    }
+  }
+  mbar_wait(&bar, 0);
+  const int i = first + blockIdx.x * BLOCK + threadIdx.x;
+  const bool active = i < first + n;
+  double total = 1.0e300;
+  if (active) {
+    int flags = 0;
+    CoopData<T> d;
+    Lanes1 L;
+    total = co_rollout<T, WB>(L, sc.m, sc.t, sc.p, knots, stride, i, wb, d, &flags);
+    returns[i] = total;
+    failure[i] = (unsigned char)flags;
+  }
+  double c = active ? total : 1.0e300; long long gi = active ? sample_offset + i : 0x7fffffffffffffffLL;
+  if (!(c == c)) c = 1.0e300;
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    const double oc = __shfl_down_sync(0xffffffffu, c, o);
+    const long long oi = __shfl_down_sync(0xffffffffu, gi, o);
+    if (better(oc, oi, c, gi)) { c = oc; gi = oi; }
+  }
+  if ((threadIdx.x & 31) == 0) { warp_min[threadIdx.x >> 5].cost = c; warp_min[threadIdx.x >> 5].index = gi; }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    for (int w = 1; w < BLOCK / 32; w++) if (better(warp_min[w].cost, warp_min[w].index, c, gi)) { c = warp_min[w].cost; gi = warp_min[w].index; }
+    block_min[blockIdx.x].cost = c; block_min[blockIdx.x].index = gi;
   }
 }
 #endif

@@ -7,8 +7,8 @@
 namespace ps {
 
 // ---------------------------------------------------------------- kinematics, one tree level per phase
-template <class T>
-PS_NI void co_body_frame(const DevModel<T>& m, CoopData<T>& d, int b) { PS_ASSUME_SHARED(&m); PS_ASSUME_SHARED(&d);
+template <class T, class LT>
+PS_NI void co_body_frame(const DevModel<T>& m, CoopData<T>& d, int b) { PS_ASSUME_SHARED(&m); if (LT::kSharedData) PS_ASSUME_SHARED(&d);
   double pos[3], quat[4];
   const int par = m.body_parentid[b], jn = m.body_jntnum[b], ja = m.body_jntadr[b];
   if (m.body_mocapid[b] >= 0) {
@@ -50,8 +50,8 @@ PS_NI void co_body_frame(const DevModel<T>& m, CoopData<T>& d, int b) { PS_ASSUM
   double qi[4]; quat_mul(qi, quat, m.body_iquat + 4 * b); quat_to_mat(d.ximat + 9 * b, qi);
 }
 
-template <class T>
-PS_NI void co_kinematics(const Lanes& L, const DevModel<T>& m, CoopData<T>& d) { PS_ASSUME_SHARED(&m); PS_ASSUME_SHARED(&d);
+template <class T, class LT>
+PS_NI void co_kinematics(const LT& L, const DevModel<T>& m, CoopData<T>& d) { PS_ASSUME_SHARED(&m); if (LT::kSharedData) PS_ASSUME_SHARED(&d);
   // quaternion normalisation of the state (mj_kinematics does it in place) + world body
   CO_FOR(j, m.njnt) {
     if (m.jnt_type[j] == JNT_FREE) unit4(d.qpos + m.jnt_qposadr[j] + 3);
@@ -66,7 +66,7 @@ PS_NI void co_kinematics(const Lanes& L, const DevModel<T>& m, CoopData<T>& d) {
   L.sync();
   for (int l = 1; l < m.nlevel; l++) {
     const int a = m.level_adr[l], n = m.level_adr[l + 1] - a;
-    CO_FOR(k, n) co_body_frame(m, d, m.level_body[a + k]);
+    CO_FOR(k, n) co_body_frame<T, LT>(m, d, m.level_body[a + k]);
     L.sync();
   }
   CO_FOR(s, m.nsite) {
@@ -80,8 +80,8 @@ PS_NI void co_kinematics(const Lanes& L, const DevModel<T>& m, CoopData<T>& d) {
 
 // fold children into parents, deepest level first: x[p] += x[c] for c in children(p), decreasing c,
 // `n` values per body.  include_world: whether body 0 accumulates too.
-template <class T>
-PS_NI void co_fold_children(const Lanes& L, const DevModel<T>& m, double* x, int n, bool include_world) { PS_ASSUME_SHARED(&m);
+template <class T, class LT>
+PS_NI void co_fold_children(const LT& L, const DevModel<T>& m, double* x, int n, bool include_world) { PS_ASSUME_SHARED(&m);
   for (int l = m.nlevel - 2; l >= (include_world ? 0 : 1); l--) {
     const int a = m.level_adr[l], nb = m.level_adr[l + 1] - a;
     CO_FOR(w, nb * n) {
@@ -95,8 +95,8 @@ PS_NI void co_fold_children(const Lanes& L, const DevModel<T>& m, double* x, int
 }
 
 // ---------------------------------------------------------------- CoM frame quantities
-template <class T>
-PS_NI void co_com_position(const Lanes& L, const DevModel<T>& m, CoopData<T>& d) { PS_ASSUME_SHARED(&m); PS_ASSUME_SHARED(&d);
+template <class T, class LT>
+PS_NI void co_com_position(const LT& L, const DevModel<T>& m, CoopData<T>& d) { PS_ASSUME_SHARED(&m); if (LT::kSharedData) PS_ASSUME_SHARED(&d);
   const int nb = m.nbody;
   double* sc = d.subtree_com;
   CO_FOR(w, 3 * nb) sc[w] = m.body_mass[w / 3] * d.xipos[w];
@@ -149,8 +149,8 @@ PS_NI void co_com_position(const Lanes& L, const DevModel<T>& m, CoopData<T>& d)
 
 // ---------------------------------------------------------------- tree-sparse L'DL
 // in-place factorisation of the symmetric matrix in A (lower triangle, tree sparsity)
-template <class T>
-PS_NI void co_factor_tree(const Lanes& L, const DevModel<T>& m, double* A, double* dinv) { PS_ASSUME_SHARED(&m);
+template <class T, class LT>
+PS_NI void co_factor_tree(const LT& L, const DevModel<T>& m, double* A, double* dinv) { PS_ASSUME_SHARED(&m);
   constexpr int S = T::NV; const int nv = m.nv;
   for (int k = nv - 1; k >= 0; k--) {
     double dk = A[k * S + k];
@@ -173,8 +173,8 @@ PS_NI void co_factor_tree(const Lanes& L, const DevModel<T>& m, double* A, doubl
 }
 
 // x <- (L' D L)^-1 x
-template <class T>
-PS_NI void co_solve_tree(const Lanes& L, const DevModel<T>& m, double* x, const double* A, const double* dinv) { PS_ASSUME_SHARED(&m);
+template <class T, class LT>
+PS_NI void co_solve_tree(const LT& L, const DevModel<T>& m, double* x, const double* A, const double* dinv) { PS_ASSUME_SHARED(&m);
   constexpr int S = T::NV; const int nv = m.nv;
   // x <- L^-T x : a dof collects from its descendants (deepest first, decreasing index)
   for (int l = m.ndoflevel - 2; l >= 0; l--) {
@@ -203,8 +203,8 @@ PS_NI void co_solve_tree(const Lanes& L, const DevModel<T>& m, double* x, const 
 }
 
 // ---------------------------------------------------------------- composite inertia, mass matrix
-template <class T>
-PS_NI void co_mass_matrix(const Lanes& L, const DevModel<T>& m, CoopData<T>& d) { PS_ASSUME_SHARED(&m); PS_ASSUME_SHARED(&d);
+template <class T, class LT>
+PS_NI void co_mass_matrix(const LT& L, const DevModel<T>& m, CoopData<T>& d) { PS_ASSUME_SHARED(&m); if (LT::kSharedData) PS_ASSUME_SHARED(&d);
   constexpr int S = T::NV; const int nb = m.nbody, nv = m.nv;
   double* crb = d.crb();
   CO_FOR(w, 10 * nb) crb[w] = d.cinert[w];
@@ -226,13 +226,13 @@ PS_NI void co_mass_matrix(const Lanes& L, const DevModel<T>& m, CoopData<T>& d) 
   co_factor_tree(L, m, d.qH, d.qLDiagInv);
 }
 
-template <class T>
-PS_NI void co_mul_M(const Lanes& L, const DevModel<T>& m, const CoopData<T>& d, double* res, const double* vec) { PS_ASSUME_SHARED(&m); PS_ASSUME_SHARED(&d);
+template <class T, class LT>
+PS_NI void co_mul_M(const LT& L, const DevModel<T>& m, const CoopData<T>& d, double* res, const double* vec) { PS_ASSUME_SHARED(&m); if (LT::kSharedData) PS_ASSUME_SHARED(&d);
   CO_FOR(i, m.nv) res[i] = vdot(d.qM + i * T::NV, vec, m.nv);
 }
 
-template <class T>
-PS_NI void co_position_smooth(const Lanes& L, const DevModel<T>& m, CoopData<T>& d) { PS_ASSUME_SHARED(&m); PS_ASSUME_SHARED(&d);
+template <class T, class LT>
+PS_NI void co_position_smooth(const LT& L, const DevModel<T>& m, CoopData<T>& d) { PS_ASSUME_SHARED(&m); if (LT::kSharedData) PS_ASSUME_SHARED(&d);
   co_kinematics(L, m, d);
   CO_FOR(i, m.nu) d.actuator_length[i] = m.act_gear[i] * d.qpos[m.jnt_qposadr[m.act_jntid[i]]];
   L.sync();
@@ -241,8 +241,8 @@ PS_NI void co_position_smooth(const Lanes& L, const DevModel<T>& m, CoopData<T>&
 }
 
 // ---------------------------------------------------------------- velocity stage
-template <class T>
-PS_NI void co_body_velocity(const DevModel<T>& m, const CoopData<T>& d, const double* qvel, double* cvel, double* cdof_dot, int i) { PS_ASSUME_SHARED(&m); PS_ASSUME_SHARED(&d);
+template <class T, class LT>
+PS_NI void co_body_velocity(const DevModel<T>& m, const CoopData<T>& d, const double* qvel, double* cvel, double* cdof_dot, int i) { PS_ASSUME_SHARED(&m); if (LT::kSharedData) PS_ASSUME_SHARED(&d);
   double v[6]; vcopy(v, cvel + 6 * m.body_parentid[i], 6);
   const int ja = m.body_jntadr[i];
   for (int j = ja; j < ja + m.body_jntnum[i]; j++) {
@@ -265,8 +265,8 @@ PS_NI void co_body_velocity(const DevModel<T>& m, const CoopData<T>& d, const do
   vcopy(cvel + 6 * i, v, 6);
 }
 
-template <class T>
-PS_NI void co_velocity_stage(const Lanes& L, const DevModel<T>& m, CoopData<T>& d) { PS_ASSUME_SHARED(&m); PS_ASSUME_SHARED(&d);
+template <class T, class LT>
+PS_NI void co_velocity_stage(const LT& L, const DevModel<T>& m, CoopData<T>& d) { PS_ASSUME_SHARED(&m); if (LT::kSharedData) PS_ASSUME_SHARED(&d);
   const int nv = m.nv, nb = m.nbody;
   double* cvel = d.cvel(); double* cdd = d.cdof_dot();
   CO_FOR(i, m.nu) d.actuator_velocity[i] = m.act_gear[i] * d.qvel[m.jnt_dofadr[m.act_jntid[i]]];
@@ -274,7 +274,7 @@ PS_NI void co_velocity_stage(const Lanes& L, const DevModel<T>& m, CoopData<T>& 
   L.sync();
   for (int l = 1; l < m.nlevel; l++) {
     const int a = m.level_adr[l], n = m.level_adr[l + 1] - a;
-    CO_FOR(k, n) co_body_velocity(m, d, d.qvel, cvel, cdd, m.level_body[a + k]);
+    CO_FOR(k, n) co_body_velocity<T, LT>(m, d, d.qvel, cvel, cdd, m.level_body[a + k]);
     L.sync();
   }
   // passive: joint springs + dof damping (the fluid model stays with the thread-per-rollout engine)
@@ -316,8 +316,8 @@ PS_NI void co_velocity_stage(const Lanes& L, const DevModel<T>& m, CoopData<T>& 
 }
 
 // ---------------------------------------------------------------- subtree momentum (sensor support)
-template <class T>
-PS_NI void co_subtree_velocity(const Lanes& L, const DevModel<T>& m, CoopData<T>& d) { PS_ASSUME_SHARED(&m); PS_ASSUME_SHARED(&d);
+template <class T, class LT>
+PS_NI void co_subtree_velocity(const LT& L, const DevModel<T>& m, CoopData<T>& d) { PS_ASSUME_SHARED(&m); if (LT::kSharedData) PS_ASSUME_SHARED(&d);
   const int nb = m.nbody;
   double* bodyvel = d.scratch; double* lv = d.subtree_linvel; double* am = d.subtree_angmom;
   CO_FOR(i, nb) {
@@ -357,8 +357,8 @@ PS_NI void co_subtree_velocity(const Lanes& L, const DevModel<T>& m, CoopData<T>
 }
 
 // ---------------------------------------------------------------- actuation + smooth acceleration
-template <class T>
-PS_NI void co_actuation_stage(const Lanes& L, const DevModel<T>& m, CoopData<T>& d) { PS_ASSUME_SHARED(&m); PS_ASSUME_SHARED(&d);
+template <class T, class LT>
+PS_NI void co_actuation_stage(const LT& L, const DevModel<T>& m, CoopData<T>& d) { PS_ASSUME_SHARED(&m); if (LT::kSharedData) PS_ASSUME_SHARED(&d);
   const int nv = m.nv, nu = m.nu;
   CO_FOR(i, nv) d.qfrc_actuator[i] = 0;
   CO_FOR(i, m.na) d.act_dot[i] = 0;
@@ -399,8 +399,8 @@ PS_NI void co_actuation_stage(const Lanes& L, const DevModel<T>& m, CoopData<T>&
   L.sync();
 }
 
-template <class T>
-PS_NI void co_acceleration_stage(const Lanes& L, const DevModel<T>& m, CoopData<T>& d) { PS_ASSUME_SHARED(&m); PS_ASSUME_SHARED(&d);
+template <class T, class LT>
+PS_NI void co_acceleration_stage(const LT& L, const DevModel<T>& m, CoopData<T>& d) { PS_ASSUME_SHARED(&m); if (LT::kSharedData) PS_ASSUME_SHARED(&d);
   CO_FOR(i, m.nv) {
     d.qfrc_smooth[i] = d.qfrc_passive[i] - d.qfrc_bias[i] + d.qfrc_actuator[i];
     d.qacc_smooth[i] = d.qfrc_smooth[i];

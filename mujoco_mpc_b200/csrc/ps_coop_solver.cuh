@@ -8,8 +8,8 @@
 namespace ps {
 
 // state, force and cost term of every row for jar = J a - aref; returns the summed cost
-template <class T>
-PS_NI double co_update_rows(const Lanes& L, const DevModel<T>& m, CoopData<T>& d, const double* jar) { PS_ASSUME_SHARED(&m); PS_ASSUME_SHARED(&d);
+template <class T, class LT>
+PS_NI double co_update_rows(const LT& L, const DevModel<T>& m, CoopData<T>& d, const double* jar) { PS_ASSUME_SHARED(&m); if (LT::kSharedData) PS_ASSUME_SHARED(&d);
   const int nefc = d.nefc;
   CO_FOR(i, nefc) {
     const int tp = d.efc_type[i];
@@ -56,8 +56,8 @@ PS_NI double co_update_rows(const Lanes& L, const DevModel<T>& m, CoopData<T>& d
 
 struct CoSolverScalars { double cost, gauss, prev_cost; };
 
-template <class T>
-PS_NI void co_update_cost(const Lanes& L, const DevModel<T>& m, CoopData<T>& d, CoSolverScalars& c) { PS_ASSUME_SHARED(&m); PS_ASSUME_SHARED(&d);
+template <class T, class LT>
+PS_NI void co_update_cost(const LT& L, const DevModel<T>& m, CoopData<T>& d, CoSolverScalars& c) { PS_ASSUME_SHARED(&m); if (LT::kSharedData) PS_ASSUME_SHARED(&d);
   const int nv = m.nv;
   const double cc = co_update_rows(L, m, d, d.sv_Jaref);
   double g = 0;
@@ -89,8 +89,8 @@ PS_NI void co_update_cost(const Lanes& L, const DevModel<T>& m, CoopData<T>& d, 
 }
 
 // H = M + J' D_active J (+ cone blocks) -> Cholesky -> search = -H^-1 grad
-template <class T>
-PS_NI void co_newton_direction(const Lanes& L, const DevModel<T>& m, CoopData<T>& d) { PS_ASSUME_SHARED(&m); PS_ASSUME_SHARED(&d);
+template <class T, class LT>
+PS_NI void co_newton_direction(const LT& L, const DevModel<T>& m, CoopData<T>& d) { PS_ASSUME_SHARED(&m); if (LT::kSharedData) PS_ASSUME_SHARED(&d);
   constexpr int S = T::NV, NCH = T::NCH; const int nv = m.nv;
   double* H = d.qH;
   CO_FOR(i, nv) d.sv_grad[i] = d.sv_Ma[i] - d.qfrc_smooth[i] - d.qfrc_constraint[i];
@@ -190,9 +190,9 @@ PS_NI void co_newton_direction(const Lanes& L, const DevModel<T>& m, CoopData<T>
 }
 
 // value, slope and curvature of the total cost along the search direction at step alpha
-template <class T>
-PS_NI void co_line_eval(const Lanes& L, const DevModel<T>& m, CoopData<T>& d, const double* qg, double alpha,
-                        double* cost, double* d1, double* d2) { PS_ASSUME_SHARED(&m); PS_ASSUME_SHARED(&d);
+template <class T, class LT>
+PS_NI void co_line_eval(const LT& L, const DevModel<T>& m, CoopData<T>& d, const double* qg, double alpha,
+                        double* cost, double* d1, double* d2) { PS_ASSUME_SHARED(&m); if (LT::kSharedData) PS_ASSUME_SHARED(&d);
   const int nefc = d.nefc;
   double* tf = d.sv_tmp; double* tg = d.efc_force; double* th = d.efc_aref;     // both dead during the line search
   CO_FOR(i, nefc) {
@@ -234,7 +234,7 @@ PS_NI void co_line_eval(const Lanes& L, const DevModel<T>& m, CoopData<T>& d, co
   }
   L.sync();
   double f, g, h;
-  if (Lanes::single || L.width == 1) {       // one working lane: plain sequential sums
+  if (LT::single || L.width == 1) {       // one working lane: plain sequential sums
     f = qg[0] + alpha * qg[1] + alpha * alpha * qg[2]; g = qg[1] + 2 * alpha * qg[2]; h = 2 * qg[2];
     for (int i = 0; i < nefc; i++) { f += tf[i]; g += tg[i]; h += th[i]; }
   } else {                                   // three lanes add up one quantity each, in row order, then broadcast
@@ -247,8 +247,8 @@ PS_NI void co_line_eval(const Lanes& L, const DevModel<T>& m, CoopData<T>& d, co
   *cost = f; *d1 = g; *d2 = h;
 }
 
-template <class T>
-PS_NI double co_line_search(const Lanes& L, const DevModel<T>& m, CoopData<T>& d, const CoSolverScalars& c) { PS_ASSUME_SHARED(&m); PS_ASSUME_SHARED(&d);
+template <class T, class LT>
+PS_NI double co_line_search(const LT& L, const DevModel<T>& m, CoopData<T>& d, const CoSolverScalars& c) { PS_ASSUME_SHARED(&m); if (LT::kSharedData) PS_ASSUME_SHARED(&d);
   const int nv = m.nv, nefc = d.nefc;
   const double snorm = sqrt(vdot(d.sv_search, d.sv_search, nv));
   if (snorm < kMinVal) return 0;
@@ -276,8 +276,8 @@ PS_NI double co_line_search(const Lanes& L, const DevModel<T>& m, CoopData<T>& d
   return alpha;
 }
 
-template <class T>
-PS_NI void co_constraint_stage(const Lanes& L, const DevModel<T>& m, CoopData<T>& d) { PS_ASSUME_SHARED(&m); PS_ASSUME_SHARED(&d);
+template <class T, class LT>
+PS_NI void co_constraint_stage(const LT& L, const DevModel<T>& m, CoopData<T>& d) { PS_ASSUME_SHARED(&m); if (LT::kSharedData) PS_ASSUME_SHARED(&d);
   const int nv = m.nv, nefc = d.nefc;
   if (!nefc) {
     CO_FOR(i, nv) { d.qacc[i] = d.qacc_smooth[i]; d.qacc_warmstart[i] = d.qacc_smooth[i]; d.qfrc_constraint[i] = 0; }

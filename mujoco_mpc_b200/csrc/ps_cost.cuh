@@ -43,7 +43,7 @@ PS_FN void spline_sample(const double* times, int P, int dim, int interp, double
 }
 
 // ---------------------------------------------------------------- norms (NormType, mjpc/norm.h:24-35)
-PS_NI double norm_value(const double* x, const double* params, int n, int type) {
+PS_NT double norm_value(const double* x, const double* params, int n, int type) {
   double y = 0; const double p = params[0], q = params[1];
   switch (type) {
     case -1: y = x[0]; break;                                                           // kNull
@@ -61,7 +61,7 @@ PS_NI double norm_value(const double* x, const double* params, int n, int type) 
   return y;
 }
 
-PS_NI double cost_value(const DevTask& t, const double* residual) {
+PS_NT double cost_value(const DevTask& t, const double* residual) {
   double cost = 0; int fs = 0, ps_ = 0;
   for (int k = 0; k < t.num_term; k++) {
     double prm[2] = {0, 0};
@@ -78,7 +78,7 @@ enum { TASK_PARTICLE = 0, TASK_PARTICLE_FIXED, TASK_PARTICLE_TEST, TASK_CARTPOLE
        TASK_WALKER, TASK_QUADRUPED };
 
 template <class T, class D>
-PS_NI void task_residual(const DevModel<T>& m, const D& d, const DevTask& t, double* r) {
+PS_NT void task_residual(const DevModel<T>& m, const D& d, const DevTask& t, double* r) {
   double s0[3], s1[3];
   switch (t.task_id) {
     case TASK_PARTICLE: case TASK_PARTICLE_FIXED: {

@@ -21,8 +21,17 @@ static int fail(const std::string& s) { g_error = s; return -1; }
 #define CU(call)                                                                                   \
   do { cudaError_t e_ = (call); if (e_ != cudaSuccess) return fail(std::string(#call) + ": " + cudaGetErrorString(e_)); } while (0)
 
-// tried in order; the warp-per-rollout instantiations come before their thread-per-rollout fallbacks
-static const Variant* const kVariants[] = {variant_tiny(), variant_planar_coop(), variant_planar(), variant_legged_coop(), variant_legged()};
+// Engine families, tried in order.  A family with two kernels shares one Constants layout: `small`
+// (warp-per-rollout, shared-memory working set) serves batches up to `crossover` rollouts -- the
+// planning-latency regime -- and `large` (thread-per-rollout over the same phases) the big batches.
+struct Family { const Variant* small; const Variant* large; int crossover; };
+static const Family kFamilies[] = {
+    {variant_tiny(), nullptr, 0},
+    {variant_planar_coop(), variant_planar(), 2048},         // nv ~ 9: dense thread-per-rollout wins the big batches
+    {variant_planar(), nullptr, 0},
+    {variant_legged_coop(), variant_legged_sparse(), 8192},  // nv ~ 18: compressed-Jacobian thread-per-rollout
+    {variant_legged(), nullptr, 0},
+};
 
 // the cooperative engine carries semi-implicit Euler and no fluid forces
 static bool coop_supported(const PsModel* m, std::string* why) {
@@ -36,8 +45,11 @@ struct PsEngine_ {
   int device = 0; cudaStream_t stream = nullptr;
   const Variant* var = nullptr;
   void* h_const = nullptr; void* d_const = nullptr;             // pinned host mirror + device copy
+  void* h_const2 = nullptr; void* d_const2 = nullptr;           // same, in the layout of the large-batch kernel
   int nq = 0, nv = 0, nu = 0, na = 0, nmocap = 0, nsensor = 0, ns = 0;
-  std::vector<int> sensor_type; bool ray_ok = false; bool force_thread_variant = false; int* d_counter = nullptr;
+  std::vector<int> sensor_type; bool ray_ok = false; int* d_counter = nullptr;
+  const Variant* var_large = nullptr; const Variant* last = nullptr; int crossover = 0; void* last_dconst = nullptr;
+  int engine_override = 0;   // PS_ENGINE: 0 auto, 1 warp, 2 thread (compressed phases), 3 dense thread-per-rollout
   std::vector<double> ctrlrange;
   DevTask task{}; bool have_task = false, have_model = false;
   int P = 0, interp = 0, H = 0, N = 0, cap = 0, stride = 0, nelem = 0, nblocks = 0;
@@ -81,8 +93,10 @@ PsEngine* ps_create(int device_ordinal) {
   cudaMallocHost(&e->h_record, (3 + 36 * 32) * sizeof(double));
   cudaMalloc(&e->d_record, (3 + 36 * 32) * sizeof(double));
   cudaMalloc(&e->d_counter, sizeof(int));
-  const char* env = std::getenv("PS_THREAD_PER_ROLLOUT");       // diagnostics: keep the warp-per-rollout engine out
-  e->force_thread_variant = env && env[0] == '1';
+  if (const char* env = std::getenv("PS_ENGINE")) {              // diagnostics / benchmarking: pin one kernel flavour
+    const std::string v(env);
+    e->engine_override = v == "warp" ? 1 : v == "thread" ? 2 : v == "dense" ? 3 : 0;
+  }
   return e;
 }
 
@@ -91,9 +105,10 @@ void ps_destroy(PsEngine* e) {
   cudaSetDevice(e->device);
   cudaStreamSynchronize(e->stream);
   void* bufs[] = {e->d_const, e->d_nominal, e->d_ctrlrange, e->d_knots, e->d_returns, e->d_record, e->d_z, e->d_failure, e->d_std2,
-                  e->d_blockmin, e->d_counter, e->wb.states, e->wb.actions, e->wb.residual, e->wb.costs, e->wb.times, e->wb.trace, e->d_scratch};
+                  e->d_blockmin, e->d_counter, e->d_const2, e->wb.states, e->wb.actions, e->wb.residual, e->wb.costs, e->wb.times, e->wb.trace, e->d_scratch};
   for (void* b : bufs) if (b) cudaFree(b);
   if (e->h_const) cudaFreeHost(e->h_const);
+  if (e->h_const2) cudaFreeHost(e->h_const2);
   if (e->h_record) cudaFreeHost(e->h_record);
   for (auto& ev : e->ev) if (ev) cudaEventDestroy(ev);
   cudaStreamDestroy(e->stream);
@@ -105,19 +120,27 @@ int ps_set_model(PsEngine* e, const PsModel* m) {
   CU(cudaSetDevice(e->device));
   PairList pl = static_pairs(m);
   std::string why, all;
-  const Variant* chosen = nullptr; void* host = nullptr;
-  for (const Variant* vp : kVariants) {
-    const Variant& v = *vp;
-    if (v.coop && (e->force_thread_variant || !coop_supported(m, &why))) { all += std::string(v.name) + ": " + (e->force_thread_variant ? "disabled" : why) + "; "; continue; }
+  const Variant* chosen = nullptr; void* host = nullptr; const Family* fam = nullptr;
+  for (const Family& f : kFamilies) {
+    const Variant& v = *f.small;
+    if (v.coop && (e->engine_override == 3 || !coop_supported(m, &why))) { all += std::string(v.name) + ": " + (e->engine_override == 3 ? "disabled" : why) + "; "; continue; }
     void* h = nullptr; CU(cudaMallocHost(&h, v.const_bytes)); std::memset(h, 0, v.const_bytes);
-    if (v.fill(m, pl, h, &why) == 0) { chosen = &v; host = h; break; }
+    if (v.fill(m, pl, h, &why) == 0) { chosen = &v; host = h; fam = &f; break; }
     all += std::string(v.name) + ": " + why + "; "; cudaFreeHost(h);
   }
   if (!chosen) return fail("ps_set_model: model outside the supported class (" + all + ")");
   if (e->h_const) cudaFreeHost(e->h_const);
   if (e->d_const) cudaFree(e->d_const);
-  e->var = chosen; e->h_const = host;
+  if (e->h_const2) cudaFreeHost(e->h_const2);
+  if (e->d_const2) cudaFree(e->d_const2);
+  e->h_const2 = nullptr; e->d_const2 = nullptr;
+  e->var = chosen; e->h_const = host; e->var_large = nullptr; e->crossover = fam->crossover; e->last = chosen;
   CU(cudaMalloc(&e->d_const, chosen->const_bytes));
+  if (fam->large) {
+    void* h2 = nullptr; CU(cudaMallocHost(&h2, fam->large->const_bytes)); std::memset(h2, 0, fam->large->const_bytes);
+    if (fam->large->fill(m, pl, h2, &why) == 0) { e->var_large = fam->large; e->h_const2 = h2; CU(cudaMalloc(&e->d_const2, fam->large->const_bytes)); }
+    else cudaFreeHost(h2);     // the model fits only the small-batch kernel's capacities: it serves every batch size
+  }
   e->nq = m->nq; e->nv = m->nv; e->nu = m->nu; e->na = m->na; e->nmocap = m->nmocap; e->nsensor = m->nsensor; e->ns = m->nq + m->nv + m->na;
   e->sensor_type.assign(m->sensor_type, m->sensor_type + m->nsensor);
   e->ray_ok = ray_scenery_ok(m);
@@ -134,6 +157,7 @@ int ps_set_model(PsEngine* e, const PsModel* m) {
   }
   std::vector<double> st(e->ns, 0.0); for (int i = 0; i < m->nq; i++) st[i] = m->qpos0[i];
   chosen->plan(e->h_const, st.data(), e->ns, mocap.data(), m->nmocap, 0.0, nullptr, 0, 0, 0);
+  if (e->var_large) e->var_large->plan(e->h_const2, st.data(), e->ns, mocap.data(), m->nmocap, 0.0, nullptr, 0, 0, 0);
   if (const char* dbg = std::getenv("PS_COOP_SERIAL")) chosen->debug(e->h_const, std::atoi(dbg));
   e->have_model = true; e->have_task = false; e->wb_valid = false;
   return 0;
@@ -141,10 +165,12 @@ int ps_set_model(PsEngine* e, const PsModel* m) {
 
 int ps_set_options(PsEngine* e, double timestep, int integrator) {
   if (!e || !e->have_model) return fail("ps_set_options: no model");
-  if (e->var->coop && integrator != PS_INT_EULER)
+  if ((e->var->coop || (e->var_large && e->var_large->coop)) && integrator != PS_INT_EULER)
     return fail("ps_set_options: this model runs on the warp-per-rollout engine (Euler); call ps_set_model with the new integrator");
   if (integrator == PS_INT_RK4) return fail("ps_set_options: RK4 integrator is not supported");
-  e->var->options(e->h_const, timestep, integrator); return 0;
+  e->var->options(e->h_const, timestep, integrator);
+  if (e->var_large) e->var_large->options(e->h_const2, timestep, integrator);
+  return 0;
 }
 
 int ps_set_task(PsEngine* e, const PsTask* t) {
@@ -158,6 +184,7 @@ int ps_set_task(PsEngine* e, const PsTask* t) {
   }
   e->task = d; e->have_task = true;
   e->var->task(e->h_const, d, need_sub);
+  if (e->var_large) e->var_large->task(e->h_const2, d, need_sub);
   return 0;
 }
 
@@ -165,6 +192,7 @@ int ps_set_state(PsEngine* e, const double* state, const double* mocap, const do
   (void)userdata;   // none of the supported tasks read userdata on the planning path
   if (!e || !e->have_model) return fail("ps_set_state: no model");
   e->var->plan(e->h_const, state, e->ns, mocap, e->nmocap, time, nullptr, 0, 0, 0);
+  if (e->var_large) e->var_large->plan(e->h_const2, state, e->ns, mocap, e->nmocap, time, nullptr, 0, 0, 0);
   return 0;
 }
 
@@ -174,6 +202,7 @@ int ps_set_nominal(PsEngine* e, const double* times, const double* knots, int P,
   CU(cudaSetDevice(e->device));
   const double nan = std::nan("");
   e->var->plan(e->h_const, nullptr, 0, nullptr, 0, nan, times, P, interpolation, 0);
+  if (e->var_large) e->var_large->plan(e->h_const2, nullptr, 0, nullptr, 0, nan, times, P, interpolation, 0);
   e->P = P; e->interp = interpolation; e->nelem = P * e->nu;
   if (!e->d_nominal) CU(cudaMalloc(&e->d_nominal, sizeof(double) * 36 * 32));
   CU(cudaMemcpyAsync(e->d_nominal, knots, sizeof(double) * e->nelem, cudaMemcpyHostToDevice, e->stream));
@@ -220,8 +249,14 @@ static int run_iteration(PsEngine* e, int N, int H, double sigma0, double sigma1
   CU(cudaSetDevice(e->device));
   if (alloc_samples(e, N)) return -1;
   e->N = N; e->H = H; e->offset = sample_offset; e->sigma0 = sigma0; e->sigma1 = sigma1;
+  const Variant* run = e->var;
+  if (e->var_large && (e->engine_override == 2 || (e->engine_override == 0 && N > e->crossover))) run = e->var_large;
+  const bool large = run == e->var_large;
+  void* hc = large ? e->h_const2 : e->h_const; void* dc = large ? e->d_const2 : e->d_const;
   e->var->plan(e->h_const, nullptr, 0, nullptr, 0, std::nan(""), nullptr, 0, 0, H);
-  CU(cudaMemcpyAsync(e->d_const, e->h_const, e->var->const_bytes, cudaMemcpyHostToDevice, e->stream));
+  if (e->var_large) e->var_large->plan(e->h_const2, nullptr, 0, nullptr, 0, std::nan(""), nullptr, 0, 0, H);
+  CU(cudaMemcpyAsync(dc, hc, run->const_bytes, cudaMemcpyHostToDevice, e->stream));
+  e->last = run; e->last_dconst = dc;
   const int stride = e->stride, nelem = e->nelem;
   if (writeback) {
     const size_t ns = e->ns, nr = e->task.num_residual, nt = 3 * (size_t)e->task.num_trace;
@@ -235,7 +270,7 @@ static int run_iteration(PsEngine* e, int N, int H, double sigma0, double sigma1
                                             (long long)sample_offset, e->have_noise ? e->d_z : nullptr,
                                             e->have_noise ? e->d_std2 : nullptr, e->d_knots, stride);
   CU(cudaEventRecord(e->ev[1], e->stream));
-  e->nblocks = e->var->launch(e->stream, e->d_const, e->d_knots, stride, 0, N, (long long)sample_offset, e->d_returns, e->d_failure, e->d_blockmin, e->wb, writeback, e->d_counter);
+  e->nblocks = run->launch(e->stream, dc, e->d_knots, stride, 0, N, (long long)sample_offset, e->d_returns, e->d_failure, e->d_blockmin, e->wb, writeback, e->d_counter);
   CU(cudaEventRecord(e->ev[2], e->stream));
   argmin_kernel<<<1, 256, 0, e->stream>>>(e->d_blockmin, e->nblocks, e->d_returns, e->d_knots, stride, nelem, (long long)sample_offset, e->d_record);
   CU(cudaEventRecord(e->ev[3], e->stream));
@@ -310,7 +345,8 @@ int ps_get_trajectory(PsEngine* e, int sample, double* states, double* actions, 
     // zero this sample's column lazily: a failed rollout leaves later steps untouched, so clear all
     for (int k = 0; k < 6; k++) CU(cudaMemsetAsync(*ptr[k], 0, need[k] * sizeof(double), e->stream));
     MinLoc* tmp = e->d_blockmin + e->cap;   // spare slot
-    e->var->launch(e->stream, e->d_const, e->d_knots, stride, sample, 1, e->offset, e->d_returns, e->d_failure, tmp, e->wb, true, e->d_counter);
+    // single re-roll: whichever kernel scored the batch (its constants are still resident)
+    e->last->launch(e->stream, e->last_dconst, e->d_knots, stride, sample, 1, e->offset, e->d_returns, e->d_failure, tmp, e->wb, true, e->d_counter);
     e->launches++;
     CU(cudaGetLastError());
   }
@@ -404,7 +440,9 @@ int ps_get_winner_record(PsEngine* e, double* out, int cap) {
 int ps_stream(PsEngine* e, void** stream) { if (!e) return fail("null engine"); *stream = (void*)e->stream; return 0; }
 
 int ps_variant(PsEngine* e, char* out, int cap) {
-  if (!e || !e->var) return fail("no model"); std::snprintf(out, cap, "%s", e->var->name); return 0;
+  if (!e || !e->var) return fail("no model"); std::snprintf(out, cap, "%s", (e->last ? e->last : e->var)->name); return 0;
 }
+
+int ps_constants_bytes(PsEngine* e) { return (e && e->var) ? (int)(e->last ? e->last : e->var)->const_bytes : -1; }
 
 }  // extern "C"

@@ -61,7 +61,7 @@ PS_HD void quat_rotate(double* r, const double* v, const double* q) {
 // one another in the last bit for a few percent of arguments, and contact-rich rollouts amplify
 // a one-ulp difference by ten orders of magnitude; evaluating the pair this way makes the
 // rollout independent of the math library underneath it.
-PS_NI void sincos_det(double x, double* sn, double* cs) {
+PS_NT void sincos_det(double x, double* sn, double* cs) {
   if (!(fabs(x) < 1.0e6)) { *sn = sin(x); *cs = cos(x); return; }   // out of the reduction's range (never an angle)
   const double fn = floor(x * 6.36619772367581382433e-01 + 0.5);
   const double t = x - fn * 1.57079632673412561417e+00;

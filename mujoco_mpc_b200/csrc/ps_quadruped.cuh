@@ -60,7 +60,7 @@ PS_HD double ray_box(const double* pos, const double* mat, const double* size, c
 
 // height of the nearest group-0 geom under `pos`
 template <class T, class D>
-PS_NI double ground_height(const DevModel<T>& m, const D& d, const double* pos) {
+PS_NT double ground_height(const DevModel<T>& m, const D& d, const double* pos) {
   const double down[3] = {0, 0, -1}; const double offset = 0.5;
   const double query[3] = {pos[0], pos[1], pos[2] + offset};
   double dist = -1;
@@ -169,7 +169,7 @@ PS_HD void quat_difference(double* res, const double* qa, const double* qb) {
 
 // ---------------------------------------------------------------- residual (42 values, 9 terms)
 template <class T, class D>
-PS_NI void quadruped_residual(const DevModel<T>& m, const D& d, const DevTask& t, double* r) {
+PS_NT void quadruped_residual(const DevModel<T>& m, const D& d, const DevTask& t, double* r) {
   using namespace quad;
   const double* a = t.aux; const double* P = t.parameters;
   const int mode = (int)a[A_MODE], torso = t.iaux[0];

@@ -13,7 +13,7 @@ namespace ps {
 
 // ---------------------------------------------------------------- forward kinematics
 template <class T>
-PS_FN void kinematics(const DevModel<T>& m, RolloutData<T>& d) {
+PS_NT void kinematics(const DevModel<T>& m, RolloutData<T>& d) {
   vzero(d.xpos, 3); d.xquat[0] = 1; d.xquat[1] = d.xquat[2] = d.xquat[3] = 0;
   vzero(d.xmat, 9); d.xmat[0] = d.xmat[4] = d.xmat[8] = 1;
   vzero(d.xipos, 3); vcopy(d.ximat, d.xmat, 9);
@@ -86,7 +86,7 @@ PS_HD void dof_motion(double* res, const double* axis, const double* offset_or_n
 }
 
 template <class T>
-PS_FN void com_position(const DevModel<T>& m, RolloutData<T>& d) {
+PS_NT void com_position(const DevModel<T>& m, RolloutData<T>& d) {
   const int nb = m.nbody;
   double* sc = d.subtree_com;
   for (int i = 0; i < nb; i++) for (int k = 0; k < 3; k++) sc[3 * i + k] = m.body_mass[i] * d.xipos[3 * i + k];
@@ -138,7 +138,7 @@ PS_FN void com_position(const DevModel<T>& m, RolloutData<T>& d) {
 // ---------------------------------------------------------------- mass matrix + factorisation
 // factor a symmetric matrix with the dof tree's sparsity in place: L'DL, reverse dof order
 template <class T>
-PS_FN void factor_tree(const DevModel<T>& m, double* L, double* dinv) {
+PS_NT void factor_tree(const DevModel<T>& m, double* L, double* dinv) {
   constexpr int S = T::NV; const int nv = m.nv;
   for (int k = nv - 1; k >= 0; k--) {
     if (L[k * S + k] < kMinVal) L[k * S + k] = kMinVal;
@@ -153,7 +153,7 @@ PS_FN void factor_tree(const DevModel<T>& m, double* L, double* dinv) {
 }
 
 template <class T>
-PS_FN void solve_tree(const DevModel<T>& m, double* x, const double* L, const double* dinv) {
+PS_NT void solve_tree(const DevModel<T>& m, double* x, const double* L, const double* dinv) {
   constexpr int S = T::NV; const int nv = m.nv;
   for (int i = nv - 1; i >= 0; i--) {
     const double xi = x[i];
@@ -165,7 +165,7 @@ PS_FN void solve_tree(const DevModel<T>& m, double* x, const double* L, const do
 }
 
 template <class T>
-PS_FN void mass_matrix(const DevModel<T>& m, RolloutData<T>& d) {
+PS_NT void mass_matrix(const DevModel<T>& m, RolloutData<T>& d) {
   constexpr int S = T::NV; const int nb = m.nbody, nv = m.nv;
   vcopy(d.crb, d.cinert, 10 * nb);
   for (int i = nb - 1; i > 0; i--) {
@@ -193,7 +193,7 @@ PS_HD void mul_M(const DevModel<T>& m, const RolloutData<T>& d, double* res, con
 // translational / rotational Jacobian rows of a world point attached to `body`;
 // jacp / jacr are [3][T::NV] (may be null)
 template <class T>
-PS_FN void point_jacobian(const DevModel<T>& m, const RolloutData<T>& d, double* jacp, double* jacr,
+PS_NT void point_jacobian(const DevModel<T>& m, const RolloutData<T>& d, double* jacp, double* jacr,
                           const double* point, int body) {
   constexpr int S = T::NV;
   if (jacp) vzero(jacp, 3 * S);
@@ -220,7 +220,7 @@ PS_FN void position_smooth(const DevModel<T>& m, RolloutData<T>& d) {
 // ---------------------------------------------------------------- velocity propagation
 // cvel / cdof_dot for generalized velocity qvel (outputs may alias d's own arrays)
 template <class T>
-PS_FN void com_velocity(const DevModel<T>& m, const RolloutData<T>& d, const double* qvel, double* cvel, double* cdof_dot) {
+PS_NT void com_velocity(const DevModel<T>& m, const RolloutData<T>& d, const double* qvel, double* cvel, double* cdof_dot) {
   vzero(cvel, 6);
   for (int i = 1; i < m.nbody; i++) {
     double v[6]; vcopy(v, cvel + 6 * m.body_parentid[i], 6);
@@ -248,7 +248,7 @@ PS_FN void com_velocity(const DevModel<T>& m, const RolloutData<T>& d, const dou
 
 // bias = C(q, v) v + g(q) by recursive Newton-Euler with zero acceleration
 template <class T>
-PS_FN void rne_bias(const DevModel<T>& m, const RolloutData<T>& d, const double* qvel, const double* cvel,
+PS_NT void rne_bias(const DevModel<T>& m, const RolloutData<T>& d, const double* qvel, const double* cvel,
                     const double* cdof_dot, double* result) {
   const int nb = m.nbody, nv = m.nv;
   double cacc[6 * T::NBODY], cfrc[6 * T::NBODY];
@@ -303,7 +303,7 @@ PS_HD void body_local_velocity(const DevModel<T>& m, const RolloutData<T>& d, in
 }
 
 template <class T>
-PS_FN void fluid_forces(const DevModel<T>& m, const RolloutData<T>& d, double* qfrc) {
+PS_NT void fluid_forces(const DevModel<T>& m, const RolloutData<T>& d, double* qfrc) {
   constexpr int S = T::NV; const int nv = m.nv;
   double jp[3 * S], jr[3 * S];
   for (int i = 1; i < m.nbody; i++) {
@@ -338,7 +338,7 @@ PS_FN void fluid_forces(const DevModel<T>& m, const RolloutData<T>& d, double* q
 }
 
 template <class T>
-PS_FN void velocity_stage(const DevModel<T>& m, RolloutData<T>& d) {
+PS_NT void velocity_stage(const DevModel<T>& m, RolloutData<T>& d) {
   const int nv = m.nv;
   for (int i = 0; i < m.nu; i++) d.actuator_velocity[i] = m.act_gear[i] * d.qvel[m.jnt_dofadr[m.act_jntid[i]]];
   com_velocity(m, d, d.qvel, d.cvel, d.cdof_dot);
@@ -361,7 +361,7 @@ PS_FN void velocity_stage(const DevModel<T>& m, RolloutData<T>& d) {
 
 // ---------------------------------------------------------------- actuation + smooth acceleration
 template <class T>
-PS_FN void actuation_stage(const DevModel<T>& m, RolloutData<T>& d) {
+PS_NT void actuation_stage(const DevModel<T>& m, RolloutData<T>& d) {
   const int nv = m.nv, nu = m.nu;
   vzero(d.qfrc_actuator, nv); vzero(d.actuator_force, nu);
   for (int i = 0; i < m.na; i++) d.act_dot[i] = 0;
@@ -392,7 +392,7 @@ PS_FN void actuation_stage(const DevModel<T>& m, RolloutData<T>& d) {
 }
 
 template <class T>
-PS_FN void acceleration_stage(const DevModel<T>& m, RolloutData<T>& d) {
+PS_NT void acceleration_stage(const DevModel<T>& m, RolloutData<T>& d) {
   const int nv = m.nv;
   for (int i = 0; i < nv; i++) {
     d.qfrc_smooth[i] = d.qfrc_passive[i] - d.qfrc_bias[i] + d.qfrc_actuator[i];

@@ -12,7 +12,7 @@ namespace ps {
 
 // ---------------------------------------------------------------- subtree momentum (sensor support)
 template <class T>
-PS_FN void subtree_velocity(const DevModel<T>& m, RolloutData<T>& d) {
+PS_NT void subtree_velocity(const DevModel<T>& m, RolloutData<T>& d) {
   const int nb = m.nbody;
   double bodyvel[6 * T::NBODY];
   double* lv = d.subtree_linvel; double* am = d.subtree_angmom;
@@ -41,7 +41,7 @@ PS_FN void subtree_velocity(const DevModel<T>& m, RolloutData<T>& d) {
 // evaluate model sensor `s` from the current rollout data (replaces SensorByName + sensordata,
 // mjpc/utilities.cc:166-175); returns the number of values written
 template <class T, class D>
-PS_FN int read_sensor(const DevModel<T>& m, const D& d, int s, double* out) {
+PS_NT int read_sensor(const DevModel<T>& m, const D& d, int s, double* out) {
   const int type = m.sensor_type[s], ot = m.sensor_objtype[s], id = m.sensor_objid[s];
   const double* pos; const double* mat; int body;
   if (ot == OBJ_BODY) { pos = d.xipos + 3 * id; mat = d.ximat + 9 * id; body = id; }
@@ -78,7 +78,7 @@ PS_FN void forward_pass(const DevModel<T>& m, RolloutData<T>& d) {
 
 // ---------------------------------------------------------------- d(qfrc_smooth)/d(qvel) for implicit integrators
 template <class T>
-PS_FN void smooth_vel_derivative(const DevModel<T>& m, RolloutData<T>& d, double* D, bool with_bias) {
+PS_NT void smooth_vel_derivative(const DevModel<T>& m, RolloutData<T>& d, double* D, bool with_bias) {
   constexpr int S = T::NV; const int nv = m.nv;
   for (int i = 0; i < nv; i++) for (int j = 0; j < nv; j++) D[i * S + j] = 0;
   for (int i = 0; i < m.nu; i++) {
@@ -135,7 +135,7 @@ PS_FN void smooth_vel_derivative(const DevModel<T>& m, RolloutData<T>& d, double
 
 // ---------------------------------------------------------------- integration
 template <class T>
-PS_FN void integrate(const DevModel<T>& m, RolloutData<T>& d) {
+PS_NT void integrate(const DevModel<T>& m, RolloutData<T>& d) {
   constexpr int S = T::NV; const int nv = m.nv; const double dt = m.timestep;
   double qacc[S];
   if (m.integrator == INT_EULER || m.integrator == INT_RK4) {

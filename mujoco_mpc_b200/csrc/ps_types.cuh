@@ -21,6 +21,13 @@
 #define PS_FN inline
 #define PS_NI inline
 #endif
+// stage functions of the thread-per-rollout engines: out of line except in the tiny instantiation,
+// whose short steps lose more to call overhead than they gain in instruction-cache footprint
+#ifdef PS_THREAD_INLINE
+#define PS_NT PS_FN
+#else
+#define PS_NT PS_NI
+#endif
 #if defined(__CUDA_ARCH__)
 #define PS_ASSUME_SHARED(p) __builtin_assume(__isShared(p))
 #else

@@ -50,6 +50,19 @@ inline int launch_coop(cudaStream_t st, const void* dconst, const double* knots,
   return grid;
 }
 
+// thread-per-rollout launch of the compressed-Jacobian phases (sparse_rollout_kernel)
+template <class T, int BLOCK>
+inline int launch_sparse(cudaStream_t st, const void* dconst, const double* knots, int stride, int first, int n,
+                         long long offset, double* returns, unsigned char* failure, MinLoc* block_min, Writeback wb, bool writeback,
+                         int* counter) {
+  (void)counter;
+  const int grid = (n + BLOCK - 1) / BLOCK;
+  const Constants<T>* c = reinterpret_cast<const Constants<T>*>(dconst);
+  if (writeback) sparse_rollout_kernel<T, BLOCK, true><<<grid, BLOCK, 0, st>>>(c, knots, stride, first, n, offset, returns, failure, block_min, wb);
+  else sparse_rollout_kernel<T, BLOCK, false><<<grid, BLOCK, 0, st>>>(c, knots, stride, first, n, offset, returns, failure, block_min, wb);
+  return grid;
+}
+
 struct Variant {
   const char* name; size_t const_bytes; int block; bool coop;
   int (*fill)(const PsModel*, const PairList&, void*, std::string*);
@@ -70,6 +83,12 @@ inline Variant make_coop_variant(const char* name) {
 const Variant* variant_tiny();
 const Variant* variant_planar();
 const Variant* variant_legged();
+template <class T, int BLOCK>
+inline Variant make_sparse_variant(const char* name) {
+  return Variant{name, sizeof(Constants<T>), BLOCK, true, fill_model<T>, set_options<T>, set_debug<T>, set_task<T>, set_plan<T>, launch_sparse<T, BLOCK>};
+}
+const Variant* variant_planar_sparse();
+const Variant* variant_legged_sparse();
 const Variant* variant_planar_coop();
 const Variant* variant_legged_coop();
 

@@ -15,7 +15,7 @@ _LIB = None
 EXPORTS = ["ps_last_error", "ps_create", "ps_destroy", "ps_set_model", "ps_set_options", "ps_set_task", "ps_set_state",
            "ps_set_nominal", "ps_set_noise", "ps_set_seed", "ps_rollouts", "ps_rollouts_async", "ps_rollouts_writeback",
            "ps_get_returns", "ps_get_knots", "ps_get_trajectory", "ps_get_all_trajectories", "ps_last_kernel_ms",
-           "ps_kernel_launch_count", "ps_winner_record_device", "ps_stream", "ps_name", "ps_variant", "ps_fp64_peak"]
+           "ps_kernel_launch_count", "ps_winner_record_device", "ps_stream", "ps_name", "ps_variant", "ps_fp64_peak", "ps_constants_bytes"]
 
 
 class EngineError(RuntimeError):
@@ -78,6 +78,9 @@ class Engine:
         b = ctypes.create_string_buffer(64)
         self._ck(self.L.ps_variant(self.h, b, 64))
         return b.value.decode()
+
+    def constants_bytes(self):
+        return int(self.L.ps_constants_bytes(self.h))
 
     def set_task(self, task):
         self.task = task
