@@ -19,6 +19,7 @@ typedef Traits<9, 9, 6, 5, 9, 9, 18, 6, 1, 8, 14, 64, 20, false> PlanarT;    // 
 typedef Traits<19, 18, 12, 0, 16, 13, 44, 8, 2, 40, 16, 96, 16, true> LeggedT;  // quadruped (free joint, elliptic cones)
 
 // warp-per-rollout instantiations: + NCH (dofs one contact touches), NJROW (compressed Jacobian rows)
+typedef Traits<2, 2, 2, 0, 4, 2, 8, 2, 1, 0, 0, 4, 12, false, 2, 4> TinyCoopT;
 typedef Traits<9, 9, 6, 5, 9, 9, 18, 6, 1, 8, 14, 64, 20, false, 9, 52> PlanarCoopT;
 typedef Traits<19, 18, 12, 0, 16, 13, 44, 8, 2, 40, 24, 120, 16, true, 12, 84> LeggedCoopT;
 

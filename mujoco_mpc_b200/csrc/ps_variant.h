@@ -89,6 +89,7 @@ inline Variant make_sparse_variant(const char* name) {
 }
 const Variant* variant_planar_sparse();
 const Variant* variant_legged_sparse();
+const Variant* variant_tiny_coop();
 const Variant* variant_planar_coop();
 const Variant* variant_legged_coop();
 
