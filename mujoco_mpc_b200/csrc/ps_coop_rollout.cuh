@@ -207,7 +207,7 @@ coop_rollout_kernel(const Constants<T>* __restrict__ gconst, const double* __res
 // tens of thousands of rollouts in flight to hide that latency -- the large-batch engine, where the
 // warp-per-rollout kernel above is the small-batch (latency) engine.
 template <class T, int BLOCK, bool WB>
-__global__ void __launch_bounds__(BLOCK)
+__global__ void __launch_bounds__(BLOCK, 512 / BLOCK)
 sparse_rollout_kernel(const Constants<T>* __restrict__ gconst, const double* __restrict__ knots, int stride, int first, int n,
                       long long sample_offset, double* __restrict__ returns, unsigned char* __restrict__ failure,
                       MinLoc* __restrict__ block_min, Writeback wb) {
@@ -226,7 +226,7 @@ sparse_rollout_kernel(const Constants<T>* __restrict__ gconst, const double* __r
     }
   }
   mbar_wait(&bar, 0);
-  const int i = first + blockIdx.x * BLOCK + threadIdx.x;
+  const int i = first + blockIdx.x * blockDim.x + threadIdx.x;
   const bool active = i < first + n;
   double total = 1.0e300;
   if (active) {
@@ -248,7 +248,7 @@ sparse_rollout_kernel(const Constants<T>* __restrict__ gconst, const double* __r
   if ((threadIdx.x & 31) == 0) { warp_min[threadIdx.x >> 5].cost = c; warp_min[threadIdx.x >> 5].index = gi; }
   __syncthreads();
   if (threadIdx.x == 0) {
-    for (int w = 1; w < BLOCK / 32; w++) if (better(warp_min[w].cost, warp_min[w].index, c, gi)) { c = warp_min[w].cost; gi = warp_min[w].index; }
+    for (int w = 1; w < (int)(blockDim.x >> 5); w++) if (better(warp_min[w].cost, warp_min[w].index, c, gi)) { c = warp_min[w].cost; gi = warp_min[w].index; }
     block_min[blockIdx.x].cost = c; block_min[blockIdx.x].index = gi;
   }
 }

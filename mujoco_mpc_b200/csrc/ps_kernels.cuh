@@ -67,7 +67,7 @@ rollout_kernel(const Constants<T>* __restrict__ gconst, const double* __restrict
   }
   mbar_wait(&bar, 0);
 
-  const int i = first + blockIdx.x * BLOCK + threadIdx.x;       // local sample index
+  const int i = first + blockIdx.x * blockDim.x + threadIdx.x;  // local sample index (blockDim.x <= BLOCK, chosen per batch)
   const bool active = i < first + n;
   double total = 1.0e300; bool failed = false;
 
@@ -91,8 +91,8 @@ rollout_kernel(const Constants<T>* __restrict__ gconst, const double* __restrict
   if ((threadIdx.x & 31) == 0) { warp_min[threadIdx.x >> 5].cost = c; warp_min[threadIdx.x >> 5].index = gi; }
   __syncthreads();
   if (threadIdx.x < 32) {
-    c = threadIdx.x < BLOCK / 32 ? warp_min[threadIdx.x].cost : 1.0e300;
-    gi = threadIdx.x < BLOCK / 32 ? warp_min[threadIdx.x].index : 0x7fffffffffffffffLL;
+    c = threadIdx.x < (blockDim.x >> 5) ? warp_min[threadIdx.x].cost : 1.0e300;
+    gi = threadIdx.x < (blockDim.x >> 5) ? warp_min[threadIdx.x].index : 0x7fffffffffffffffLL;
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) {
       const double oc = __shfl_down_sync(0xffffffffu, c, o);

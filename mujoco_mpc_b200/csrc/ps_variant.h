@@ -7,16 +7,28 @@
 
 namespace ps {
 
+// Threads per block for a thread-per-rollout launch of n rollouts: small batches are latency bound
+// (one warp per scheduler at best), so they are spread over as many SMs as possible -- each warp then
+// has an SM's instruction cache and L1 to itself (measured: acrobot N=4096 5.87 -> 4.60 ms); large
+// batches use the full block so one Constants copy serves more threads.
+inline int pick_block(int n, int max_block) {
+  static int sms = 0;
+  if (!sms) { int dev = 0; cudaGetDevice(&dev); cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev); if (sms <= 0) sms = 148; }
+  int b = 32;
+  while (b < max_block && (n + b - 1) / b > sms) b <<= 1;
+  return b;
+}
+
 // thread-per-rollout launch; returns the number of blocks (= entries written to block_min)
 template <class T, int BLOCK>
 inline int launch_rollout(cudaStream_t st, const void* dconst, const double* knots, int stride, int first, int n,
                           long long offset, double* returns, unsigned char* failure, MinLoc* block_min, Writeback wb, bool writeback,
                           int* counter) {
   (void)counter;
-  const int grid = (n + BLOCK - 1) / BLOCK;
+  const int block = pick_block(n, BLOCK), grid = (n + block - 1) / block;
   const Constants<T>* c = reinterpret_cast<const Constants<T>*>(dconst);
-  if (writeback) rollout_kernel<T, BLOCK, true><<<grid, BLOCK, 0, st>>>(c, knots, stride, first, n, offset, returns, failure, block_min, wb);
-  else rollout_kernel<T, BLOCK, false><<<grid, BLOCK, 0, st>>>(c, knots, stride, first, n, offset, returns, failure, block_min, wb);
+  if (writeback) rollout_kernel<T, BLOCK, true><<<grid, block, 0, st>>>(c, knots, stride, first, n, offset, returns, failure, block_min, wb);
+  else rollout_kernel<T, BLOCK, false><<<grid, block, 0, st>>>(c, knots, stride, first, n, offset, returns, failure, block_min, wb);
   return grid;
 }
 
@@ -56,10 +68,10 @@ inline int launch_sparse(cudaStream_t st, const void* dconst, const double* knot
                          long long offset, double* returns, unsigned char* failure, MinLoc* block_min, Writeback wb, bool writeback,
                          int* counter) {
   (void)counter;
-  const int grid = (n + BLOCK - 1) / BLOCK;
+  const int block = pick_block(n, BLOCK), grid = (n + block - 1) / block;
   const Constants<T>* c = reinterpret_cast<const Constants<T>*>(dconst);
-  if (writeback) sparse_rollout_kernel<T, BLOCK, true><<<grid, BLOCK, 0, st>>>(c, knots, stride, first, n, offset, returns, failure, block_min, wb);
-  else sparse_rollout_kernel<T, BLOCK, false><<<grid, BLOCK, 0, st>>>(c, knots, stride, first, n, offset, returns, failure, block_min, wb);
+  if (writeback) sparse_rollout_kernel<T, BLOCK, true><<<grid, block, 0, st>>>(c, knots, stride, first, n, offset, returns, failure, block_min, wb);
+  else sparse_rollout_kernel<T, BLOCK, false><<<grid, block, 0, st>>>(c, knots, stride, first, n, offset, returns, failure, block_min, wb);
   return grid;
 }
 

@@ -1,5 +1,8 @@
 // Engine instantiation "legged_sparse": thread-per-rollout, compressed-Jacobian phases, quadruped capacities.
 #include "ps_variant.h"
+#ifndef PS_SPARSE_BLOCK
+#define PS_SPARSE_BLOCK 128
+#endif
 namespace ps {
-const Variant* variant_legged_sparse() { static const Variant v = make_sparse_variant<LeggedCoopT, 64>("legged_sparse"); return &v; }
+const Variant* variant_legged_sparse() { static const Variant v = make_sparse_variant<LeggedCoopT, PS_SPARSE_BLOCK>("legged_sparse"); return &v; }
 }  // namespace ps

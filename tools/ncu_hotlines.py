@@ -49,6 +49,9 @@ for f, c in by_file.most_common():
 print("--- top lines by executed instructions")
 for (f, l), c in by_line.most_common(45):
     print(f"{f}:{l:<5d} {100 * c / tot:6.2f}%  samples {100 * samp_line[(f, l)] / max(tots, 1):6.2f}%")
+print("--- top lines by stall samples")
+for (f, l), c in samp_line.most_common(45):
+    print(f"{f}:{l:<5d} samples {100 * c / max(tots, 1):6.2f}%  instr {100 * by_line[(f, l)] / tot:6.2f}%")
 if len(sys.argv) > 4:
     print("--- requested lines (file:line -> warp-instructions, static instrs)")
     static = collections.Counter()
