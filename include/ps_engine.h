@@ -68,6 +68,18 @@ int ps_set_nominal(PsEngine* e, const double* times, const double* knots, int P,
  * runs); pass NULL to use the on-device counter-based generator seeded by ps_set_seed */
 int ps_set_noise(PsEngine* e, const double* z, const unsigned char* use_std2, int N);
 int ps_set_seed(PsEngine* e, unsigned long long seed);
+/* Cross-entropy mode (CrossEntropyPlanner::AddNoiseToPolicy, cross_entropy/planner.cc:343-375): per-parameter
+ * noise standard deviations param_std[P][nu] = max(sqrt(variance_k), std_min), applied un-scaled to EVERY
+ * candidate; the LAST column of the next ps_rollouts batch stays un-noised and carries the nominal rollout
+ * the reference schedules beside the candidates (:416).  NULL returns to Predictive Sampling noise. */
+int ps_set_param_std(PsEngine* e, const double* param_std);
+/* Elite update of CrossEntropyPlanner::OptimizePolicy (cross_entropy/planner.cc:196-262) over candidates
+ * [0, n_candidates) of the last batch: ranks them by (return, index) on the device, then mean_knots[P][nu] =
+ * elite mean, variance[P][nu] (the reference's formula, see elite_stats_kernel), avg_return over the elites,
+ * best_return; order[n_elite] (optional) = candidate indices best first. */
+int ps_elite_update(PsEngine* e, int n_candidates, int n_elite, double* mean_knots, double* variance, double* avg_return,
+                    double* best_return, int* order);
+int ps_elite_update_ms(PsEngine* e, float* ms);
 /* K1+K2+K3: perturb (sample_offset..sample_offset+N of a global batch), roll out H steps,
  * reduce.  Outputs: local winner index (lowest index on ties), its return, nominal return. */
 int ps_rollouts(PsEngine* e, int N, int H, double sigma0, double sigma1, int sample_offset,

@@ -66,6 +66,9 @@ struct PsEngine_ {
   cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
   long long launches = 0;
   double* d_scratch = nullptr; size_t scratch_cap = 0;
+  // cross-entropy mode: per-parameter noise std, elite ranks, update record
+  double* d_param_std = nullptr; bool have_param_std = false; int* d_elite = nullptr; int elite_cap = 0;
+  double* d_ce_out = nullptr; double* h_ce_out = nullptr; float ce_ms = 0;
 };
 
 static int ensure(double** p, size_t* cap, size_t need) {
@@ -225,6 +228,51 @@ int ps_set_noise(PsEngine* e, const double* z, const unsigned char* use_std2, in
   return 0;
 }
 
+int ps_set_param_std(PsEngine* e, const double* param_std) {
+  if (!e || !e->have_model) return fail("ps_set_param_std: no model");
+  CU(cudaSetDevice(e->device));
+  if (!param_std) { e->have_param_std = false; return 0; }
+  if (e->P <= 0) return fail("ps_set_param_std: set the nominal plan first");
+  if (!e->d_param_std) CU(cudaMalloc(&e->d_param_std, sizeof(double) * 36 * 32));
+  CU(cudaMemcpyAsync(e->d_param_std, param_std, sizeof(double) * e->nelem, cudaMemcpyHostToDevice, e->stream));
+  CU(cudaStreamSynchronize(e->stream));
+  e->have_param_std = true;
+  return 0;
+}
+
+int ps_elite_update(PsEngine* e, int n_candidates, int n_elite, double* mean_knots, double* variance, double* avg_return,
+                    double* best_return, int* order) {
+  if (!e || e->N <= 0) return fail("ps_elite_update: no rollouts yet");
+  if (n_candidates < 1 || n_candidates > e->N) return fail("ps_elite_update: n_candidates out of range");
+  if (n_elite < 1 || n_elite > n_candidates) return fail("ps_elite_update: n_elite out of range");
+  CU(cudaSetDevice(e->device));
+  if (e->elite_cap < n_elite) {
+    if (e->d_elite) cudaFree(e->d_elite);
+    e->d_elite = nullptr; e->elite_cap = 0;
+    CU(cudaMalloc(&e->d_elite, sizeof(int) * n_elite)); e->elite_cap = n_elite;
+  }
+  const int nout = 2 + 2 * e->nelem;
+  if (!e->d_ce_out) { CU(cudaMalloc(&e->d_ce_out, sizeof(double) * (2 + 2 * 36 * 32))); CU(cudaMallocHost(&e->h_ce_out, sizeof(double) * (2 + 2 * 36 * 32))); }
+  CU(cudaEventRecord(e->ev[0], e->stream));
+  rank_kernel<<<(n_candidates + 255) / 256, 256, 0, e->stream>>>(e->d_returns, n_candidates, n_elite, e->d_elite);
+  elite_stats_kernel<<<(e->nelem + 127) / 128, 128, 0, e->stream>>>(e->d_returns, e->d_knots, e->stride, e->nelem, e->d_elite, n_elite, e->d_ce_out);
+  CU(cudaEventRecord(e->ev[1], e->stream));
+  CU(cudaMemcpyAsync(e->h_ce_out, e->d_ce_out, sizeof(double) * nout, cudaMemcpyDeviceToHost, e->stream));
+  std::vector<int> ord;
+  if (order) CU(cudaMemcpyAsync(order, e->d_elite, sizeof(int) * n_elite, cudaMemcpyDeviceToHost, e->stream));
+  CU(cudaStreamSynchronize(e->stream));
+  CU(cudaGetLastError());
+  cudaEventElapsedTime(&e->ce_ms, e->ev[0], e->ev[1]);
+  e->launches += 2;
+  if (avg_return) *avg_return = e->h_ce_out[0];
+  if (best_return) *best_return = e->h_ce_out[1];
+  if (mean_knots) std::memcpy(mean_knots, e->h_ce_out + 2, sizeof(double) * e->nelem);
+  if (variance) std::memcpy(variance, e->h_ce_out + 2 + e->nelem, sizeof(double) * e->nelem);
+  return 0;
+}
+
+int ps_elite_update_ms(PsEngine* e, float* ms) { if (!e) return fail("null engine"); if (ms) *ms = e->ce_ms; return 0; }
+
 int ps_set_seed(PsEngine* e, unsigned long long seed) { if (!e) return fail("null engine"); e->seed = seed; e->iteration = 0; return 0; }
 
 static int alloc_samples(PsEngine* e, int N) {
@@ -269,7 +317,7 @@ static int run_iteration(PsEngine* e, int N, int H, double sigma0, double sigma1
   dim3 pg((N + 255) / 256, nelem);
   perturb_kernel<<<pg, 256, 0, e->stream>>>(e->d_nominal, e->d_ctrlrange, N, nelem, e->nu, sigma0, sigma1, e->seed, e->iteration,
                                             (long long)sample_offset, e->have_noise ? e->d_z : nullptr,
-                                            e->have_noise ? e->d_std2 : nullptr, e->d_knots, stride);
+                                            e->have_noise ? e->d_std2 : nullptr, e->d_knots, stride, e->have_param_std ? e->d_param_std : nullptr);
   CU(cudaEventRecord(e->ev[1], e->stream));
   e->nblocks = run->launch(e->stream, dc, e->d_knots, stride, 0, N, (long long)sample_offset, e->d_returns, e->d_failure, e->d_blockmin, e->wb, writeback, e->d_counter);
   CU(cudaEventRecord(e->ev[2], e->stream));

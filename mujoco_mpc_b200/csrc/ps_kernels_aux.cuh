@@ -26,7 +26,8 @@ __device__ __forceinline__ double u01_open(uint32_t hi, uint32_t lo) {   // (0, 
 __global__ void perturb_kernel(const double* __restrict__ nominal, const double* __restrict__ ctrlrange, int n, int nelem, int nu,
                                double sigma0, double sigma1, unsigned long long seed, unsigned long long iteration,
                                long long sample_offset, const double* __restrict__ z_injected,
-                               const unsigned char* __restrict__ std2_injected, double* __restrict__ knots, int stride) {
+                               const unsigned char* __restrict__ std2_injected, double* __restrict__ knots, int stride,
+                               const double* __restrict__ param_std) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   const int e = blockIdx.y;
   if (i >= n) return;
@@ -34,7 +35,11 @@ __global__ void perturb_kernel(const double* __restrict__ nominal, const double*
   const int a = e % nu;
   const double lo = ctrlrange[2 * a], hi = ctrlrange[2 * a + 1];
   double v = nominal[e];
-  if (gi != 0) {
+  // Predictive Sampling leaves sample 0 un-noised (sampling/planner.cc:361); the cross-entropy planner
+  // perturbs every candidate (cross_entropy/planner.cc:395-409) and rolls the nominal out separately:
+  // here that is the LAST column of the batch (param_std != nullptr selects this mode)
+  const bool noisy = param_std ? (i != n - 1) : (gi != 0);
+  if (noisy) {
     double sd = sigma0, z;
     if (z_injected) {
       z = z_injected[(size_t)i * nelem + e];
@@ -51,8 +56,8 @@ __global__ void perturb_kernel(const double* __restrict__ nominal, const double*
       const double u1 = u01_open(c[0], c[1]), u2 = u01_open(c[2], c[3]);
       z = sqrt(-2.0 * log(u1)) * cospi(2.0 * u2);        // Box-Muller
     }
-    const double scale = 0.5 * (hi - lo);
-    v += (scale * sd) * z;
+    if (param_std) v += param_std[e] * z;                  // N(0, max(sqrt(variance_k), std_min)), cross_entropy/planner.cc:360-363
+    else { const double scale = 0.5 * (hi - lo); v += (scale * sd) * z; }
     v = clampd(v, lo, hi);
   }
   knots[(size_t)e * stride + i] = v;
@@ -96,6 +101,50 @@ __global__ void argmin_kernel(const MinLoc* __restrict__ block_min, int nblocks,
   __syncthreads();
   const long long w = win;
   for (int e = threadIdx.x; e < nelem; e += blockDim.x) record[3 + e] = knots[(size_t)e * stride + w];
+}
+
+// ---------------------------------------------------------------- K4 / K5: cross-entropy elite update
+// Rank of every candidate under (return, index) order -- the total order of the partial_sort in
+// cross_entropy/planner.cc:201-207 with ties broken by index; NaN sorts last.  O(n^2 / tile) compares
+// through a shared-memory tile of the returns: 65,536 candidates = 4.3e9 compares, well under a
+// millisecond of the iteration.  Candidates ranked below n_elite write their index to elite[rank].
+__global__ void rank_kernel(const double* __restrict__ returns, int n, int n_elite, int* __restrict__ elite) {
+  __shared__ double tile[1024];
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  double mine = i < n ? returns[i] : 0.0;
+  if (!(mine == mine)) mine = 1.0e300;
+  int rank = 0;
+  for (int base = 0; base < n; base += 1024) {
+    const int cnt = n - base < 1024 ? n - base : 1024;
+    __syncthreads();
+    for (int k = threadIdx.x; k < cnt; k += blockDim.x) { double v = returns[base + k]; tile[k] = (v == v) ? v : 1.0e300; }
+    __syncthreads();
+    for (int k = 0; k < cnt; k++) { const double v = tile[k]; rank += (v < mine) || (v == mine && base + k < i); }
+  }
+  if (i < n && rank < n_elite) elite[rank] = i;
+}
+
+// out = [avg_return, best_return, mean[nelem], variance[nelem]].  One thread per spline parameter; the
+// sums run over the elites in rank order, sequentially, exactly as cross_entropy/planner.cc:224-262
+// (including its variance, which measures the BEST candidate's distance from the elite mean n_elite
+// times -- `n` is fetched once from trajectory_order[0] at :246 and not per elite).
+__global__ void elite_stats_kernel(const double* __restrict__ returns, const double* __restrict__ knots, int stride, int nelem,
+                                   const int* __restrict__ elite, int n_elite, double* __restrict__ out) {
+  const int e = blockIdx.x * blockDim.x + threadIdx.x;
+  if (e == 0) {
+    double s = 0;
+    for (int r = 0; r < n_elite; r++) s += returns[elite[r]];
+    out[0] = s / n_elite; out[1] = returns[elite[0]];
+  }
+  if (e >= nelem) return;
+  const double* row = knots + (size_t)e * stride;
+  double s = 0;
+  for (int r = 0; r < n_elite; r++) s += row[elite[r]];
+  const double avg = s * (1.0 / n_elite);                 // mju_scl(.., 1.0 / n_elite), :239
+  const double diff = row[elite[0]] - avg;
+  double var = 0;
+  for (int r = 0; r < n_elite; r++) var += diff * diff / (n_elite - 1);
+  out[2 + e] = avg; out[2 + nelem + e] = var;
 }
 
 // gather one sample's SoA column into a dense host-order array: out[r] = src[r * stride + i]

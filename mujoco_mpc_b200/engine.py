@@ -15,7 +15,8 @@ _LIB = None
 EXPORTS = ["ps_last_error", "ps_create", "ps_destroy", "ps_set_model", "ps_set_options", "ps_set_task", "ps_set_state",
            "ps_set_nominal", "ps_set_noise", "ps_set_seed", "ps_rollouts", "ps_rollouts_async", "ps_rollouts_writeback",
            "ps_get_returns", "ps_get_knots", "ps_get_trajectory", "ps_get_all_trajectories", "ps_last_kernel_ms",
-           "ps_kernel_launch_count", "ps_winner_record_device", "ps_stream", "ps_name", "ps_variant", "ps_fp64_peak", "ps_constants_bytes"]
+           "ps_kernel_launch_count", "ps_winner_record_device", "ps_stream", "ps_name", "ps_variant", "ps_fp64_peak", "ps_constants_bytes",
+           "ps_set_param_std", "ps_elite_update", "ps_elite_update_ms"]
 
 
 class EngineError(RuntimeError):
@@ -108,6 +109,22 @@ class Engine:
         u = np.ascontiguousarray(use_std2, dtype=np.uint8) if use_std2 is not None else None
         self._ck(self.L.ps_set_noise(self.h, _p(z), u.ctypes.data_as(ctypes.POINTER(ctypes.c_ubyte)) if u is not None else None,
                                      z.shape[0]))
+
+    def set_param_std(self, param_std):
+        """cross-entropy mode: per-parameter noise std [P][nu]; None returns to Predictive Sampling noise"""
+        if param_std is None:
+            self._ck(self.L.ps_set_param_std(self.h, None))
+            return
+        self._ck(self.L.ps_set_param_std(self.h, _p(_arr(param_std))))
+
+    def elite_update(self, n_candidates, n_elite):
+        """rank candidates on the device and reduce the elites: (mean knots [P][nu], variance [P][nu], avg return,
+        best return, order[n_elite])"""
+        mean = np.zeros((self.P, self.model.nu)); var = np.zeros((self.P, self.model.nu))
+        avg = ctypes.c_double(); best = ctypes.c_double(); order = np.zeros(n_elite, dtype=np.int32)
+        self._ck(self.L.ps_elite_update(self.h, int(n_candidates), int(n_elite), _p(mean), _p(var), ctypes.byref(avg), ctypes.byref(best),
+                                        order.ctypes.data_as(ctypes.POINTER(ctypes.c_int))))
+        return mean, var, avg.value, best.value, order
 
     def set_seed(self, seed):
         self._ck(self.L.ps_set_seed(self.h, ctypes.c_ulonglong(seed)))

@@ -83,3 +83,82 @@ int psp_best_trajectory(void* h, double* states, double* actions, double* times,
 void* psp_engine(void* h) { return ((CudaSamplingPlanner*)h)->engine(); }
 
 }  // extern "C"
+
+// ---- CudaCrossEntropyPlanner
+#include "cuda_cross_entropy_planner.h"
+using mjpc_b200::CudaCrossEntropyPlanner;
+
+extern "C" {
+
+void* pce_create(const PsModel* model, const PsTask* task, int device) {
+  CudaCrossEntropyPlanner* p = new CudaCrossEntropyPlanner;
+  p->Initialize(model, task, device); p->Allocate(); p->Reset(mjpc_b200::kMaxTrajectoryHorizon);
+  return p;
+}
+void pce_destroy(void* h) { delete (CudaCrossEntropyPlanner*)h; }
+void pce_reset(void* h, int horizon, const double* initial_repeated_action) { ((CudaCrossEntropyPlanner*)h)->Reset(horizon, initial_repeated_action); }
+void pce_set_state(void* h, const double* state, const double* mocap, const double* userdata, double time) {
+  ((CudaCrossEntropyPlanner*)h)->SetState(state, mocap, userdata, time);
+}
+void pce_set_task(void* h, const PsTask* t) { ((CudaCrossEntropyPlanner*)h)->SetTask(t); }
+// negative / non-positive arguments keep the value read from the model's numerics at Initialize
+void pce_configure(void* h, int num_trajectory, int n_elite, int interpolation, int num_spline_points, double std_initial, double std_min) {
+  CudaCrossEntropyPlanner* p = (CudaCrossEntropyPlanner*)h;
+  if (num_trajectory > 0) p->num_trajectory_ = num_trajectory;
+  if (n_elite > 0) p->n_elite_ = n_elite;
+  if (interpolation >= 0) p->interpolation_ = interpolation;
+  if (num_spline_points > 0) for (mjpc_b200::SamplingPolicy* q : {&p->policy, &p->previous_policy, &p->resampled_policy}) q->num_spline_points = num_spline_points;
+  if (std_initial >= 0) p->std_initial_ = std_initial;
+  if (std_min >= 0) p->std_min_ = std_min;
+}
+void pce_set_policy(void* h, const double* times, const double* knots, int P, int interpolation) {
+  CudaCrossEntropyPlanner* p = (CudaCrossEntropyPlanner*)h;
+  mjpc_b200::TimeSpline plan(p->NumParameters() / p->policy.num_spline_points, (mjpc_b200::SplineInterpolation)interpolation);
+  const int nu = p->NumParameters() / p->policy.num_spline_points;
+  for (int k = 0; k < P; k++) plan.AddNode(times[k], knots + (size_t)k * nu);
+  p->policy.plan = plan;
+}
+void pce_set_variance(void* h, const double* v, int n) { CudaCrossEntropyPlanner* p = (CudaCrossEntropyPlanner*)h; for (int i = 0; i < n && i < (int)p->variance.size(); i++) p->variance[i] = v[i]; }
+int pce_get_variance(void* h, double* v, int cap) { CudaCrossEntropyPlanner* p = (CudaCrossEntropyPlanner*)h; int n = cap < (int)p->variance.size() ? cap : (int)p->variance.size(); std::memcpy(v, p->variance.data(), sizeof(double) * n); return n; }
+void pce_set_noise(void* h, const double* z, int N) { ((CudaCrossEntropyPlanner*)h)->SetNoise(z, N); }
+void pce_set_seed(void* h, unsigned long long seed) { ((CudaCrossEntropyPlanner*)h)->SetSeed(seed); }
+void pce_optimize_policy(void* h, int horizon) { ((CudaCrossEntropyPlanner*)h)->OptimizePolicy(horizon); }
+void pce_nominal_trajectory(void* h, int horizon) { ((CudaCrossEntropyPlanner*)h)->NominalTrajectory(horizon); }
+void pce_action_from_policy(void* h, double* action, double time, int use_previous) {
+  ((CudaCrossEntropyPlanner*)h)->ActionFromPolicy(action, nullptr, time, use_previous != 0);
+}
+double pce_improvement(void* h) { return ((CudaCrossEntropyPlanner*)h)->improvement; }
+double pce_avg_return(void* h) { return ((CudaCrossEntropyPlanner*)h)->avg_return; }
+double pce_best_return(void* h) { return ((CudaCrossEntropyPlanner*)h)->best_return; }
+int pce_order(void* h, int* order, int cap) {
+  CudaCrossEntropyPlanner* p = (CudaCrossEntropyPlanner*)h;
+  int n = cap < (int)p->trajectory_order.size() ? cap : (int)p->trajectory_order.size();
+  for (int i = 0; i < n; i++) order[i] = p->trajectory_order[i];
+  return n;
+}
+int pce_get_policy(void* h, int which, double* times, double* knots) {
+  CudaCrossEntropyPlanner* p = (CudaCrossEntropyPlanner*)h;
+  const mjpc_b200::TimeSpline& s = which == 1 ? p->previous_policy.plan : which == 2 ? p->resampled_policy.plan : p->policy.plan;
+  std::memcpy(times, s.times().data(), sizeof(double) * s.times().size());
+  std::memcpy(knots, s.values().data(), sizeof(double) * s.values().size());
+  return s.Size();
+}
+int pce_best_trajectory(void* h, double* states, double* actions, double* times, double* residual, double* costs, double* total_return, int* failure) {
+  const mjpc_b200::Trajectory* t = ((CudaCrossEntropyPlanner*)h)->BestTrajectory();
+  if (!t) return 0;
+  if (states) std::memcpy(states, t->states.data(), sizeof(double) * t->states.size());
+  if (actions) std::memcpy(actions, t->actions.data(), sizeof(double) * t->actions.size());
+  if (times) std::memcpy(times, t->times.data(), sizeof(double) * t->times.size());
+  if (residual) std::memcpy(residual, t->residual.data(), sizeof(double) * t->residual.size());
+  if (costs) std::memcpy(costs, t->costs.data(), sizeof(double) * t->costs.size());
+  if (total_return) *total_return = t->total_return;
+  if (failure) *failure = t->failure;
+  return t->horizon;
+}
+void pce_timers(void* h, double* noise_us, double* rollouts_us, double* policy_update_us) {
+  CudaCrossEntropyPlanner* p = (CudaCrossEntropyPlanner*)h;
+  *noise_us = p->noise_compute_time; *rollouts_us = p->rollouts_compute_time; *policy_update_us = p->policy_update_compute_time;
+}
+void* pce_engine(void* h) { return ((CudaCrossEntropyPlanner*)h)->engine(); }
+
+}  // extern "C"

@@ -155,3 +155,112 @@ class CudaSamplingPlanner:
             return None
         return dict(states=st, actions=ac, times=tm, residual=rs, costs=cs, trace=tr[:, :3 * t.num_trace], total_return=ret.value,
                     failure=bool(fail.value))
+
+
+class CudaCrossEntropyPlanner:
+    """ctypes binding of mjpc_b200::CudaCrossEntropyPlanner (drop-in for mjpc::CrossEntropyPlanner,
+    mjpc/planners/cross_entropy/planner.h): same rollout kernels, elite ranking + statistics on the device."""
+
+    def __init__(self, model, task, device=0):
+        self.L = lib()
+        for f in ("pce_improvement", "pce_avg_return", "pce_best_return"):
+            getattr(self.L, f).restype = ctypes.c_double
+        self.L.pce_create.restype = ctypes.c_void_p
+        self.L.pce_engine.restype = ctypes.c_void_p
+        self.model, self.task = model, task
+        self.h = ctypes.c_void_p(self.L.pce_create(ctypes.byref(model.c_struct()), ctypes.byref(task), device))
+        self.ns = model.nq + model.nv + model.na
+        self.horizon = 0
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.L.pce_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def Reset(self, horizon, initial_repeated_action=None):
+        a = _arr(initial_repeated_action) if initial_repeated_action is not None else None
+        self.L.pce_reset(self.h, horizon, _p(a))
+
+    def configure(self, num_trajectory=-1, n_elite=-1, interpolation=-1, num_spline_points=-1, std_initial=-1.0, std_min=-1.0):
+        self.L.pce_configure(self.h, num_trajectory, n_elite, interpolation, num_spline_points, ctypes.c_double(std_initial),
+                             ctypes.c_double(std_min))
+
+    def SetState(self, state, time, mocap=None, userdata=None):
+        s = _arr(state); mo = _arr(mocap) if mocap is not None else None; ud = _arr(userdata) if userdata is not None else None
+        self.L.pce_set_state(self.h, _p(s), _p(mo), _p(ud), ctypes.c_double(time))
+
+    def SetTask(self, task):
+        self.task = task
+        self.L.pce_set_task(self.h, ctypes.byref(task))
+
+    def set_policy(self, times, knots, interp):
+        t = _arr(times); k = _arr(knots)
+        self.L.pce_set_policy(self.h, _p(t), _p(k), len(t), int(interp))
+
+    def set_variance(self, v):
+        v = _arr(v); self.L.pce_set_variance(self.h, _p(v), v.size)
+
+    def variance(self, P):
+        v = np.zeros(P * self.model.nu); self.L.pce_get_variance(self.h, _p(v), v.size)
+        return v.reshape(P, self.model.nu)
+
+    def SetNoise(self, z):
+        if z is None:
+            self.L.pce_set_noise(self.h, None, 0); return
+        z = _arr(z); self.L.pce_set_noise(self.h, _p(z), z.shape[0])
+
+    def SetSeed(self, seed):
+        self.L.pce_set_seed(self.h, ctypes.c_ulonglong(seed))
+
+    def OptimizePolicy(self, horizon):
+        self.horizon = horizon
+        self.L.pce_optimize_policy(self.h, horizon)
+
+    def NominalTrajectory(self, horizon):
+        self.horizon = horizon
+        self.L.pce_nominal_trajectory(self.h, horizon)
+
+    def ActionFromPolicy(self, time, use_previous=False):
+        a = np.zeros(max(self.model.nu, 1)); self.L.pce_action_from_policy(self.h, _p(a), ctypes.c_double(time), int(use_previous))
+        return a[:self.model.nu]
+
+    @property
+    def improvement(self):
+        return self.L.pce_improvement(self.h)
+
+    @property
+    def avg_return(self):
+        return self.L.pce_avg_return(self.h)
+
+    @property
+    def best_return(self):
+        return self.L.pce_best_return(self.h)
+
+    def order(self, n):
+        o = np.zeros(n, dtype=np.int32)
+        k = self.L.pce_order(self.h, o.ctypes.data_as(ctypes.POINTER(ctypes.c_int)), n)
+        return o[:k]
+
+    def policy(self, which=0):
+        """which: 0 policy (elite mean), 1 previous_policy, 2 resampled_policy (the nominal that was rolled out)"""
+        t = np.zeros(64); k = np.zeros(64 * max(self.model.nu, 1))
+        P = self.L.pce_get_policy(self.h, which, _p(t), _p(k))
+        return t[:P].copy(), k[:P * self.model.nu].reshape(P, self.model.nu).copy()
+
+    def BestTrajectory(self):
+        H, m, t = self.horizon, self.model, self.task
+        st = np.zeros((H, self.ns)); ac = np.zeros((H, m.nu)); tm = np.zeros(H); rs = np.zeros((H, t.num_residual)); cs = np.zeros(H)
+        ret = ctypes.c_double(); fail = ctypes.c_int()
+        h = self.L.pce_best_trajectory(self.h, _p(st), _p(ac), _p(tm), _p(rs), _p(cs), ctypes.byref(ret), ctypes.byref(fail))
+        if not h:
+            return None
+        return dict(states=st, actions=ac, times=tm, residual=rs, costs=cs, total_return=ret.value, failure=bool(fail.value))
+
+    def engine_ptr(self):
+        return self.L.pce_engine(self.h)

@@ -7,6 +7,7 @@
 
 namespace mm {
 void optimizePolicy(Planner* pl, int N, int horizon, const double* z, const unsigned char* use_std2, int nthread);
+void optimizePolicyCE(Planner* pl, int N, int horizon, const double* z, int nthread);
 }
 using namespace mm;
 
@@ -85,6 +86,14 @@ void mmo_set_policy(void* hp, const double* times, const double* knots, int P, i
 void mmo_optimize(void* hp, int N, int H, const double* z, const unsigned char* use_std2, int nthread) {
   optimizePolicy(&((Handle*)hp)->pl, N, H, z, use_std2, nthread);
 }
+// cross-entropy planner: std_min / n_elite, variance in/out, one iteration, elite order and nominal return
+void mmo_ce_config(void* hp, double std_min, int n_elite) { Planner& p = ((Handle*)hp)->pl; p.std_min = std_min; p.n_elite = n_elite; }
+void mmo_ce_set_variance(void* hp, const double* v, int n) { ((Handle*)hp)->pl.variance.assign(v, v + n); }
+int mmo_ce_get_variance(void* hp, double* v, int cap) { Planner& p = ((Handle*)hp)->pl; int n = std::min<int>(cap, (int)p.variance.size()); copy(v, p.variance.data(), n); return (int)p.variance.size(); }
+void mmo_optimize_ce(void* hp, int N, int H, const double* z, int nthread) { optimizePolicyCE(&((Handle*)hp)->pl, N, H, z, nthread); }
+int mmo_ce_order(void* hp, int* order, int cap) { Planner& p = ((Handle*)hp)->pl; int n = std::min<int>(cap, (int)p.trajectory_order.size()); for (int i = 0; i < n; i++) order[i] = p.trajectory_order[i]; return n; }
+double mmo_ce_avg_return(void* hp) { return ((Handle*)hp)->pl.avg_return; }
+double mmo_ce_nominal_return(void* hp) { return ((Handle*)hp)->pl.nominal_trajectory.total_return; }
 int mmo_winner(void* hp) { return ((Handle*)hp)->pl.winner; }
 double mmo_improvement(void* hp) { return ((Handle*)hp)->pl.improvement; }
 int mmo_get_policy(void* hp, int which /*0 policy,1 previous,2+i candidate i*/, double* times, double* knots) {

@@ -113,4 +113,66 @@ void optimizePolicy(Planner* pl, int N, int horizon, const double* z, const unsi
   pl->improvement = std::fmax(pl->trajectory[0].total_return - pl->trajectory[best].total_return, 0.0);
 }
 
+// CrossEntropyPlanner::OptimizePolicy (mjpc/planners/cross_entropy/planner.cc:164-284) with injected noise
+// z[N][P][nu]: ResamplePolicy (:317-341, no zero-order special case), AddNoiseToPolicy for EVERY candidate
+// with std max(sqrt(variance_k), std_min) un-scaled by the control range (:343-375), N rollouts plus the
+// nominal one (:378-423), elite mean -> new policy, the reference's variance formula (:243-256: `n` is the
+// BEST candidate's node for every elite i), improvement = max(avg_return - best, 0).  partial_sort ties
+// are resolved towards the lower index.
+void optimizePolicyCE(Planner* pl, int N, int horizon, const double* z, int nthread) {
+  const Model* m = pl->model; int nu = m->nu;
+  int P = pl->num_spline_points, np = P * nu;
+  int n_elite = std::min(pl->n_elite, N);
+  if ((int)pl->variance.size() != np) pl->variance.assign(np, pl->noise_exploration[0] * pl->noise_exploration[0]);   // Reset: std_initial^2 (:109-111)
+  // resample the nominal to the current time
+  Policy rp; rp.interp = pl->interpolation; rp.times.resize(P); rp.knots.resize(np);
+  {
+    Policy src = pl->policy; src.interp = pl->interpolation;
+    double t = pl->time, shift = std::fmax((horizon - 1) * m->opt_timestep / (P - 1), 1.0e-5);
+    for (int k = 0; k < P; k++) { rp.times[k] = t; policyAction(m, src, t, &rp.knots[k * nu]); t += shift; }
+  }
+  pl->candidate.assign(N, rp);
+  pl->trajectory.resize(N);
+  for (int i = 0; i < N; i++) {
+    Policy& c = pl->candidate[i];
+    for (int k = 0; k < P; k++) {
+      for (int a = 0; a < nu; a++) c.knots[k * nu + a] += std::max(std::sqrt(pl->variance[k * nu + a]), pl->std_min) * z[((size_t)i * P + k) * nu + a];
+      for (int a = 0; a < nu; a++) c.knots[k * nu + a] = clip(c.knots[k * nu + a], m->actuator_ctrlrange[2 * a], m->actuator_ctrlrange[2 * a + 1]);
+    }
+  }
+  nthread = std::max(1, nthread);
+  if ((int)pl->data.size() < nthread) { size_t old = pl->data.size(); pl->data.resize(nthread); for (size_t k = old; k < pl->data.size(); k++) makeData(m, &pl->data[k]); }
+  auto work = [&](int tid) {
+    for (int i = tid; i <= N; i += nthread)
+      rollout(m, &pl->task, &pl->data[tid], i < N ? pl->candidate[i] : rp, pl->state.data(), pl->time, pl->mocap.data(), pl->userdata.data(), horizon,
+              i < N ? &pl->trajectory[i] : &pl->nominal_trajectory);
+  };
+  if (nthread == 1) work(0);
+  else { std::vector<std::thread> th; for (int k = 0; k < nthread; k++) th.emplace_back(work, k); for (auto& x : th) x.join(); }
+  pl->trajectory_order.resize(N);
+  for (int i = 0; i < N; i++) pl->trajectory_order[i] = i;
+  std::stable_sort(pl->trajectory_order.begin(), pl->trajectory_order.end(), [&](int a, int b) {
+    double ra = pl->trajectory[a].total_return, rb = pl->trajectory[b].total_return;
+    if (!(ra == ra)) ra = 1.0e300;
+    if (!(rb == rb)) rb = 1.0e300;
+    return ra < rb; });
+  std::vector<double> mean(np, 0.0); double avg_return = 0;
+  for (int e = 0; e < n_elite; e++) {
+    int idx = pl->trajectory_order[e];
+    for (int k = 0; k < np; k++) mean[k] += pl->candidate[idx].knots[k];
+    avg_return += pl->trajectory[idx].total_return;
+  }
+  for (int k = 0; k < np; k++) mean[k] = mean[k] * (1.0 / n_elite);
+  avg_return /= n_elite;
+  std::fill(pl->variance.begin(), pl->variance.end(), 0.0);
+  const Policy& best = pl->candidate[pl->trajectory_order[0]];
+  for (int k = 0; k < np; k++) {
+    for (int i = 0; i < n_elite; i++) { double diff = best.knots[k] - mean[k]; pl->variance[k] += diff * diff / (n_elite - 1); }
+  }
+  // previous_policy is only ever set by Reset in the reference (cross_entropy/planner.cc:129)
+  pl->policy.times = rp.times; pl->policy.knots = mean; pl->policy.interp = pl->interpolation;
+  pl->winner = pl->trajectory_order[0]; pl->avg_return = avg_return;
+  pl->improvement = std::fmax(avg_return - pl->trajectory[pl->trajectory_order[0]].total_return, 0.0);
+}
+
 }  // namespace mm

@@ -35,6 +35,9 @@ struct Planner {
   int num_spline_points = 0, interpolation = PS_SPLINE_CUBIC;
   double noise_exploration[2] = {0.1, 0};
   std::vector<Data> data;     // one per worker thread
+  // CrossEntropyPlanner state (mjpc/planners/cross_entropy/planner.h): per-parameter variance, elites
+  std::vector<double> variance; double std_min = 0.1; int n_elite = 2;
+  std::vector<int> trajectory_order; Trajectory nominal_trajectory; double avg_return = 0;
 };
 
 // SamplingPolicy::Action (policy.cc:52-59): spline sample then clamp to ctrlrange

@@ -137,6 +137,22 @@ class Oracle:
         self.L.mmo_optimize(self.h, N, H, _p(z), u.ctypes.data_as(ctypes.c_char_p) if u is not None else None, nthread)
         return self.L.mmo_winner(self.h)
 
+    # ---- cross-entropy planner (mjpc/planners/cross_entropy/planner.cc)
+    def ce_configure(self, std_min, n_elite, variance=None):
+        self.L.mmo_ce_config(self.h, ctypes.c_double(std_min), int(n_elite))
+        if variance is not None:
+            v = _arr(variance); self.L.mmo_ce_set_variance(self.h, _p(v), v.size)
+
+    def ce_optimize(self, N, H, z, nthread=1):
+        z = _arr(z); self.N, self.H = N, H
+        self.L.mmo_optimize_ce(self.h, N, H, _p(z), nthread)
+        order = np.zeros(N, dtype=np.int32)
+        n = self.L.mmo_ce_order(self.h, order.ctypes.data_as(ctypes.POINTER(ctypes.c_int)), N)
+        var = np.zeros(64 * max(self.model.nu, 1)); nv = self.L.mmo_ce_get_variance(self.h, _p(var), var.size)
+        self.L.mmo_ce_avg_return.restype = ctypes.c_double; self.L.mmo_ce_nominal_return.restype = ctypes.c_double
+        return dict(order=order[:n], variance=var[:nv].reshape(-1, self.model.nu).copy(), avg_return=self.L.mmo_ce_avg_return(self.h),
+                    nominal_return=self.L.mmo_ce_nominal_return(self.h), improvement=self.improvement())
+
     def policy(self, which=0):
         nu = self.model.nu
         t = np.zeros(64); k = np.zeros(64 * max(nu, 1))
