@@ -261,10 +261,10 @@ PS_HD bool push_row(RolloutData<T>& d, double pos, double margin, double floss, 
 
 template <class T>
 PS_NT void make_constraints(const DevModel<T>& m, RolloutData<T>& d) {
-  constexpr int S = T::NV; const int nv = m.nv;
+  constexpr int S = T::NV; const int nv = nv_of(m);
   d.nefc = 0; d.ncon = 0;
   if (m.disableflags & DSBL_CONSTRAINT) return;
-  detect_contacts(m, d);
+  if (T::CONTACTS) detect_contacts(m, d);
   if (!(m.disableflags & DSBL_FRICTIONLOSS))
     for (int i = 0; i < nv; i++) if (m.dof_frictionloss[i] > 0) {
       const int r = d.nefc;
@@ -287,7 +287,7 @@ PS_NT void make_constraints(const DevModel<T>& m, RolloutData<T>& d) {
       }
     }
   // contacts: Jacobian difference of the two bodies at the contact point, rotated into the frame
-  {
+  if (T::CONTACTS) {
     double jp1[3 * S], jp2[3 * S], jr1[3 * S], jr2[3 * S], Jc[6 * S];
     for (int ci = 0; ci < d.ncon; ci++) {
       Contact& con = d.contact[ci];
@@ -333,7 +333,7 @@ PS_NT void make_constraints(const DevModel<T>& m, RolloutData<T>& d) {
     const int id = d.efc_id[i], tp = d.efc_type[i];
     // efc_R temporarily holds diagApprox
     if (tp == EFC_FRICTION_DOF) d.efc_R[i] = m.dof_invweight0[id];
-    else if (tp == EFC_LIMIT_JOINT) d.efc_R[i] = m.dof_invweight0[m.jnt_dofadr[id]];
+    else if (!T::CONTACTS || tp == EFC_LIMIT_JOINT) d.efc_R[i] = m.dof_invweight0[m.jnt_dofadr[id]];
     else {
       const Contact& con = d.contact[id];
       const int b1 = m.geom_bodyid[con.geom1], b2 = m.geom_bodyid[con.geom2];
@@ -354,7 +354,7 @@ PS_NT void make_constraints(const DevModel<T>& m, RolloutData<T>& d) {
     const int id = d.efc_id[i], tp = d.efc_type[i];
     double solref[2], solimp[5];
     if (tp == EFC_FRICTION_DOF) sanitize_sol(m.timestep, m.disableflags, m.dof_solref + 2 * id, m.dof_solimp + 5 * id, solref, solimp);
-    else if (tp == EFC_LIMIT_JOINT) sanitize_sol(m.timestep, m.disableflags, m.jnt_solref + 2 * id, m.jnt_solimp + 5 * id, solref, solimp);
+    else if (!T::CONTACTS || tp == EFC_LIMIT_JOINT) sanitize_sol(m.timestep, m.disableflags, m.jnt_solref + 2 * id, m.jnt_solimp + 5 * id, solref, solimp);
     else sanitize_sol(m.timestep, m.disableflags, d.contact[id].solref, d.contact[id].solimp, solref, solimp);
     const double imp = impedance_at(solimp, d.efc_pos[i], d.efc_margin[i]);
     const double dmax = solimp[1]; double K, B;
@@ -362,12 +362,12 @@ PS_NT void make_constraints(const DevModel<T>& m, RolloutData<T>& d) {
       K = 1 / fmax(kMinVal, dmax * dmax * solref[0] * solref[0] * solref[1] * solref[1]);
       B = 2 / fmax(kMinVal, dmax * solref[0]);
     } else { K = -solref[0] / fmax(kMinVal, dmax * dmax); B = -solref[1] / fmax(kMinVal, dmax); }
-    const bool ell_fric = tp == EFC_CONTACT_ELLIPTIC && i > d.contact[id].efc_address;
+    const bool ell_fric = T::ELLIPTIC && tp == EFC_CONTACT_ELLIPTIC && i > d.contact[id].efc_address;
     if (tp == EFC_FRICTION_DOF || ell_fric) K = 0;
     d.efc_KBI[3 * i] = K; d.efc_KBI[3 * i + 1] = B; d.efc_KBI[3 * i + 2] = imp;
     d.efc_R[i] = fmax(kMinVal, (1 - imp) * d.efc_R[i] / imp);
   }
-  for (int ci = 0; ci < d.ncon; ci++) {
+  if (T::CONTACTS) for (int ci = 0; ci < d.ncon; ci++) {
     Contact& con = d.contact[ci];
     const int i = con.efc_address, dim = con.dim;
     if (i < 0 || dim == 1) continue;
@@ -390,7 +390,7 @@ PS_NT void make_constraints(const DevModel<T>& m, RolloutData<T>& d) {
 template <class T>
 PS_NT void reference_acceleration(const DevModel<T>& m, RolloutData<T>& d) {
   for (int i = 0; i < d.nefc; i++) {
-    const double vel = vdot(d.efc_J + i * T::NV, d.qvel, m.nv);
+    const double vel = vdot(d.efc_J + i * T::NV, d.qvel, nv_of(m));
     const double* k = d.efc_KBI + 3 * i;
     d.efc_aref[i] = -k[1] * vel - k[0] * k[2] * (d.efc_pos[i] - d.efc_margin[i]);
   }
@@ -410,7 +410,7 @@ PS_NT double update_rows(const DevModel<T>& m, RolloutData<T>& d, const double* 
       if (x <= -R * f) { d.efc_state[i] = ST_LINEARNEG; d.efc_force[i] = f; cost += -0.5 * R * f * f - f * x; }
       else if (x >= R * f) { d.efc_state[i] = ST_LINEARPOS; d.efc_force[i] = -f; cost += -0.5 * R * f * f + f * x; }
       else { d.efc_state[i] = ST_QUADRATIC; d.efc_force[i] = -D * x; cost += 0.5 * D * x * x; }
-    } else if (tp != EFC_CONTACT_ELLIPTIC) {
+    } else if (!T::ELLIPTIC || tp != EFC_CONTACT_ELLIPTIC) {
       if (x < 0) { d.efc_state[i] = ST_QUADRATIC; d.efc_force[i] = -D * x; cost += 0.5 * D * x * x; }
       else { d.efc_state[i] = ST_SATISFIED; d.efc_force[i] = 0; }
     } else {
@@ -456,7 +456,7 @@ struct SolverScalars { double cost, gauss, prev_cost; };
 
 template <class T>
 PS_NT void update_cost(const DevModel<T>& m, RolloutData<T>& d, SolverScalars& c, bool coneH) {
-  constexpr int S = T::NV; const int nv = m.nv;
+  constexpr int S = T::NV; const int nv = nv_of(m);
   const double cc = update_rows(m, d, d.sv_Jaref, coneH);
   double g = 0;
   for (int i = 0; i < nv; i++) g += 0.5 * (d.sv_Ma[i] - d.qfrc_smooth[i]) * (d.qacc[i] - d.qacc_smooth[i]);
@@ -471,7 +471,7 @@ PS_NT void update_cost(const DevModel<T>& m, RolloutData<T>& d, SolverScalars& c
 // H = M + J' D_active J (+ cone blocks), dense Cholesky, search = -H^-1 grad
 template <class T>
 PS_NT void newton_direction(const DevModel<T>& m, RolloutData<T>& d) {
-  constexpr int S = T::NV; const int nv = m.nv, nefc = d.nefc;
+  constexpr int S = T::NV; const int nv = nv_of(m), nefc = d.nefc;
   for (int i = 0; i < nv; i++) d.sv_grad[i] = d.sv_Ma[i] - d.qfrc_smooth[i] - d.qfrc_constraint[i];
   double* H = d.sv_H;
   for (int i = 0; i < nv; i++) for (int j = 0; j < nv; j++) H[i * S + j] = d.qM[i * S + j];
@@ -522,7 +522,7 @@ PS_NT void line_eval(const DevModel<T>& m, const RolloutData<T>& d, const double
       if (x <= -R * fl) { f += -0.5 * R * fl * fl - fl * x; g += -fl * v; }
       else if (x >= R * fl) { f += -0.5 * R * fl * fl + fl * x; g += fl * v; }
       else { f += 0.5 * D * x * x; g += D * x * v; h += D * v * v; }
-    } else if (tp != EFC_CONTACT_ELLIPTIC) {
+    } else if (!T::ELLIPTIC || tp != EFC_CONTACT_ELLIPTIC) {
       if (x < 0) { f += 0.5 * D * x * x; g += D * x * v; h += D * v * v; }
     } else {
       const Contact& con = d.contact[d.efc_id[i]];
@@ -553,7 +553,7 @@ PS_NT void line_eval(const DevModel<T>& m, const RolloutData<T>& d, const double
 
 template <class T>
 PS_NT double line_search(const DevModel<T>& m, RolloutData<T>& d, const SolverScalars& c) {
-  constexpr int S = T::NV; const int nv = m.nv, nefc = d.nefc;
+  constexpr int S = T::NV; const int nv = nv_of(m), nefc = d.nefc;
   const double snorm = sqrt(vdot(d.sv_search, d.sv_search, nv));
   if (snorm < kMinVal) return 0;
   const double scale = 1.0 / (m.meaninertia * (nv > 1 ? nv : 1));
@@ -581,7 +581,7 @@ PS_NT double line_search(const DevModel<T>& m, RolloutData<T>& d, const SolverSc
 
 template <class T>
 PS_NT void constraint_stage(const DevModel<T>& m, RolloutData<T>& d) {
-  constexpr int S = T::NV; const int nv = m.nv, nefc = d.nefc;
+  constexpr int S = T::NV; const int nv = nv_of(m), nefc = d.nefc;
   d.solver_iter = 0;
   if (!nefc) {
     for (int i = 0; i < nv; i++) { d.qacc[i] = d.qacc_smooth[i]; d.qacc_warmstart[i] = d.qacc_smooth[i]; d.qfrc_constraint[i] = 0; }

@@ -103,20 +103,20 @@ PS_NT void task_residual(const DevModel<T>& m, const D& d, const DevTask& t, dou
       r[0] = d.site_xpos[2] - d.site_xpos[5]; r[1] = d.site_xpos[0] - d.site_xpos[3];
       r[2] = d.qvel[0]; r[3] = d.qvel[1]; r[4] = d.ctrl[0];
       break;
-    case TASK_SWIMMER: {
+    case TASK_SWIMMER: if (!T::LEAN) {
       // swimmer.cc:33-45; sensor_id = {nose, target}
       for (int i = 0; i < m.nu; i++) r[i] = d.ctrl[i];
       read_sensor(m, d, t.sensor_id[0], s0); read_sensor(m, d, t.sensor_id[1], s1);
       r[m.nu] = s0[0] - s1[0]; r[m.nu + 1] = s0[1] - s1[1];
     } break;
-    case TASK_WALKER: {
+    case TASK_WALKER: if (!T::LEAN) {
       // walker.cc:38-69; sensor_id = {torso_position, torso_zaxis, torso_subtreelinvel}
       int c = 0; for (int i = 0; i < m.nu; i++) r[c++] = d.ctrl[i];
       read_sensor(m, d, t.sensor_id[0], s0); r[c++] = s0[2] - t.parameters[0];
       read_sensor(m, d, t.sensor_id[1], s0); r[c++] = s0[2] - 1.0;
       read_sensor(m, d, t.sensor_id[2], s0); r[c++] = s0[0] - t.parameters[1];
     } break;
-    case TASK_QUADRUPED: quadruped_residual(m, d, t, r); break;
+    case TASK_QUADRUPED: if constexpr (T::NQ != T::NV) quadruped_residual(m, d, t, r); break;   // needs the free joint
     default: break;
   }
 }

@@ -169,8 +169,8 @@ int ps_set_model(PsEngine* e, const PsModel* m) {
 
 int ps_set_options(PsEngine* e, double timestep, int integrator) {
   if (!e || !e->have_model) return fail("ps_set_options: no model");
-  if ((e->var->coop || (e->var_large && e->var_large->coop)) && integrator != PS_INT_EULER)
-    return fail("ps_set_options: this model runs on the warp-per-rollout engine (Euler); call ps_set_model with the new integrator");
+  if ((e->var->euler_only || (e->var_large && e->var_large->euler_only)) && integrator != PS_INT_EULER)
+    return fail("ps_set_options: this model runs on an Euler-only kernel instantiation; call ps_set_model with the new integrator");
   if (integrator == PS_INT_RK4) return fail("ps_set_options: RK4 integrator is not supported");
   e->var->options(e->h_const, timestep, integrator);
   if (e->var_large) e->var_large->options(e->h_const2, timestep, integrator);

@@ -135,6 +135,15 @@ inline int fill_model(const PsModel* s, const PairList& pl, void* out, std::stri
   if (s->opt_solver != PS_SOL_NEWTON && !(s->opt_disableflags & PS_DSBL_CONSTRAINT)) { *why = "only the Newton solver is supported"; return -1; }
   if (pl.unsupported) { *why = "model has colliding geom pairs outside the supported narrow-phase set"; return -1; }
   if (s->opt_cone == PS_CONE_ELLIPTIC && !T::ELLIPTIC && !pl.g1.empty()) { *why = "elliptic cones not in this instantiation"; return -1; }
+  if (!T::CONTACTS && !pl.g1.empty()) { *why = "contacts not in this instantiation"; return -1; }
+  if (T::LEAN) {     // features compiled out of the lean instantiation (ps_types.cuh: Traits::LEAN)
+    if (s->nv != T::NV || s->nq != T::NQ) { *why = "lean instantiation needs nq == nv == its capacity"; return -1; }
+    if (s->na) { *why = "activations not in the lean instantiation"; return -1; }
+    if (s->opt_integrator != PS_INT_EULER) { *why = "lean instantiation is Euler only"; return -1; }
+    if (s->opt_density > 0 || s->opt_viscosity > 0) { *why = "fluid forces not in the lean instantiation"; return -1; }
+    for (int j = 0; j < s->njnt; j++) if (s->jnt_type[j] != PS_JNT_HINGE && s->jnt_type[j] != PS_JNT_SLIDE) { *why = "lean instantiation carries hinge / slide joints only"; return -1; }
+    for (int i = 0; i < s->nu; i++) if (s->actuator_dyntype[i] != 0) { *why = "actuator dynamics not in the lean instantiation"; return -1; }
+  }
   m.timestep = s->opt_timestep; m.impratio = s->opt_impratio; m.tolerance = s->opt_tolerance; m.ls_tolerance = s->opt_ls_tolerance;
   m.density = s->opt_density; m.viscosity = s->opt_viscosity; m.meaninertia = s->stat_meaninertia;
   for (int k = 0; k < 3; k++) { m.gravity[k] = s->opt_gravity[k]; m.wind[k] = s->opt_wind[k]; }

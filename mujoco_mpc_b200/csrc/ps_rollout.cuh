@@ -21,7 +21,7 @@ template <class T, bool WB>
 PS_FN double rollout_sample(const DevModel<T>& m, const DevTask& task, const DevPlan<T>& plan, const double* knots,
                             int stride, int i, const Writeback& wb, int* flags) {
   RolloutData<T> d;
-  const int nq = m.nq, nv = m.nv, na = m.na, nu = m.nu, ns = nq + nv + na, nr = task.num_residual;
+  const int nq = nq_of(m), nv = nv_of(m), na = m.na, nu = m.nu, ns = nq + nv + na, nr = task.num_residual;
   const int H = plan.horizon, P = plan.num_spline_points, ntr = 3 * task.num_trace;
   for (int k = 0; k < nq; k++) d.qpos[k] = plan.state[k];
   for (int k = 0; k < nv; k++) { d.qvel[k] = plan.state[nq + k]; d.qacc_warmstart[k] = 0; d.qacc[k] = 0; }

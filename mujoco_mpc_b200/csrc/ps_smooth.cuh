@@ -17,7 +17,7 @@ PS_NT void kinematics(const DevModel<T>& m, RolloutData<T>& d) {
   vzero(d.xpos, 3); d.xquat[0] = 1; d.xquat[1] = d.xquat[2] = d.xquat[3] = 0;
   vzero(d.xmat, 9); d.xmat[0] = d.xmat[4] = d.xmat[8] = 1;
   vzero(d.xipos, 3); vcopy(d.ximat, d.xmat, 9);
-  for (int j = 0; j < m.njnt; j++) {
+  if (!T::LEAN) for (int j = 0; j < m.njnt; j++) {
     if (m.jnt_type[j] == JNT_FREE) unit4(d.qpos + m.jnt_qposadr[j] + 3);
     else if (m.jnt_type[j] == JNT_BALL) unit4(d.qpos + m.jnt_qposadr[j]);
   }
@@ -29,7 +29,7 @@ PS_NT void kinematics(const DevModel<T>& m, RolloutData<T>& d) {
     if (m.body_mocapid[b] >= 0) {
       vcopy(pos, d.mocap_pos + 3 * m.body_mocapid[b], 3);
       vcopy(quat, d.mocap_quat + 4 * m.body_mocapid[b], 4);
-    } else if (jn == 1 && m.jnt_type[ja] == JNT_FREE) {
+    } else if (!T::LEAN && jn == 1 && m.jnt_type[ja] == JNT_FREE) {
       const int qa = m.jnt_qposadr[ja];
       vcopy(pos, d.qpos + qa, 3); vcopy(quat, d.qpos + qa + 3, 4);
       vcopy(d.xanchor + 3 * ja, pos, 3); vcopy(d.xaxis + 3 * ja, m.jnt_axis + 3 * ja, 3);
@@ -47,9 +47,9 @@ PS_NT void kinematics(const DevModel<T>& m, RolloutData<T>& d) {
         if (jt == JNT_SLIDE) {
           const double dq = d.qpos[qa] - m.qpos0[qa];
           for (int k = 0; k < 3; k++) pos[k] += axis[k] * dq;
-        } else if (jt == JNT_HINGE || jt == JNT_BALL) {
+        } else if (jt == JNT_HINGE || (!T::LEAN && jt == JNT_BALL)) {
           double ql[4];
-          if (jt == JNT_BALL) vcopy(ql, d.qpos + qa, 4);
+          if (!T::LEAN && jt == JNT_BALL) vcopy(ql, d.qpos + qa, 4);
           else axis_angle_quat(ql, m.jnt_axis + 3 * j, d.qpos[qa] - m.qpos0[qa]);
           quat_mul(quat, quat, ql);
           quat_rotate(v, m.jnt_pos + 3 * j, quat);   // keep the anchor fixed under the rotation
@@ -121,11 +121,11 @@ PS_NT void com_position(const DevModel<T>& m, RolloutData<T>& d) {
     double off[3]; const double* root = sc + 3 * m.body_rootid[b];
     for (int k = 0; k < 3; k++) off[k] = root[k] - d.xanchor[3 * j + k];
     const int jt = m.jnt_type[j];
-    if (jt == JNT_FREE) {
+    if (!T::LEAN && jt == JNT_FREE) {
       for (int k = 0; k < 3; k++) { double ax[3] = {0, 0, 0}; ax[k] = 1; dof_motion(d.cdof + 6 * (da + k), ax, nullptr); }
       da += 3;
     }
-    if (jt == JNT_FREE || jt == JNT_BALL) {
+    if (!T::LEAN && (jt == JNT_FREE || jt == JNT_BALL)) {
       for (int k = 0; k < 3; k++) {
         double ax[3] = {d.xmat[9 * b + k], d.xmat[9 * b + 3 + k], d.xmat[9 * b + 6 + k]};
         dof_motion(d.cdof + 6 * (da + k), ax, off);
@@ -139,7 +139,7 @@ PS_NT void com_position(const DevModel<T>& m, RolloutData<T>& d) {
 // factor a symmetric matrix with the dof tree's sparsity in place: L'DL, reverse dof order
 template <class T>
 PS_NT void factor_tree(const DevModel<T>& m, double* L, double* dinv) {
-  constexpr int S = T::NV; const int nv = m.nv;
+  constexpr int S = T::NV; const int nv = nv_of(m);
   for (int k = nv - 1; k >= 0; k--) {
     if (L[k * S + k] < kMinVal) L[k * S + k] = kMinVal;
     const double dk = L[k * S + k];
@@ -154,7 +154,7 @@ PS_NT void factor_tree(const DevModel<T>& m, double* L, double* dinv) {
 
 template <class T>
 PS_NT void solve_tree(const DevModel<T>& m, double* x, const double* L, const double* dinv) {
-  constexpr int S = T::NV; const int nv = m.nv;
+  constexpr int S = T::NV; const int nv = nv_of(m);
   for (int i = nv - 1; i >= 0; i--) {
     const double xi = x[i];
     if (xi != 0) for (int j = m.dof_parentid[i]; j >= 0; j = m.dof_parentid[j]) x[j] -= L[i * S + j] * xi;
@@ -166,7 +166,7 @@ PS_NT void solve_tree(const DevModel<T>& m, double* x, const double* L, const do
 
 template <class T>
 PS_NT void mass_matrix(const DevModel<T>& m, RolloutData<T>& d) {
-  constexpr int S = T::NV; const int nb = m.nbody, nv = m.nv;
+  constexpr int S = T::NV; const int nb = m.nbody, nv = nv_of(m);
   vcopy(d.crb, d.cinert, 10 * nb);
   for (int i = nb - 1; i > 0; i--) {
     const int p = m.body_parentid[i];
@@ -187,7 +187,7 @@ PS_NT void mass_matrix(const DevModel<T>& m, RolloutData<T>& d) {
 
 template <class T>
 PS_HD void mul_M(const DevModel<T>& m, const RolloutData<T>& d, double* res, const double* vec) {
-  for (int i = 0; i < m.nv; i++) res[i] = vdot(d.qM + i * T::NV, vec, m.nv);
+  for (int i = 0; i < nv_of(m); i++) res[i] = vdot(d.qM + i * T::NV, vec, nv_of(m));
 }
 
 // translational / rotational Jacobian rows of a world point attached to `body`;
@@ -227,14 +227,14 @@ PS_NT void com_velocity(const DevModel<T>& m, const RolloutData<T>& d, const dou
     const int ja = m.body_jntadr[i];
     for (int j = ja; j < ja + m.body_jntnum[i]; j++) {
       int da = m.jnt_dofadr[j]; const int jt = m.jnt_type[j];
-      if (jt == JNT_FREE) {
+      if (!T::LEAN && jt == JNT_FREE) {
         for (int k = 0; k < 3; k++) {
           vzero(cdof_dot + 6 * (da + k), 6);
           for (int r = 0; r < 6; r++) v[r] += d.cdof[6 * (da + k) + r] * qvel[da + k];
         }
         da += 3;
       }
-      if (jt == JNT_FREE || jt == JNT_BALL) {
+      if (!T::LEAN && (jt == JNT_FREE || jt == JNT_BALL)) {
         for (int k = 0; k < 3; k++) cross_motion(cdof_dot + 6 * (da + k), v, d.cdof + 6 * (da + k));
         for (int k = 0; k < 3; k++) for (int r = 0; r < 6; r++) v[r] += d.cdof[6 * (da + k) + r] * qvel[da + k];
       } else {
@@ -250,7 +250,7 @@ PS_NT void com_velocity(const DevModel<T>& m, const RolloutData<T>& d, const dou
 template <class T>
 PS_NT void rne_bias(const DevModel<T>& m, const RolloutData<T>& d, const double* qvel, const double* cvel,
                     const double* cdof_dot, double* result) {
-  const int nb = m.nbody, nv = m.nv;
+  const int nb = m.nbody, nv = nv_of(m);
   double cacc[6 * T::NBODY], cfrc[6 * T::NBODY];
   const bool grav = !(m.disableflags & DSBL_GRAVITY);
   for (int k = 0; k < 3; k++) { cacc[k] = 0; cacc[3 + k] = grav ? -m.gravity[k] : 0.0; }
@@ -304,7 +304,7 @@ PS_HD void body_local_velocity(const DevModel<T>& m, const RolloutData<T>& d, in
 
 template <class T>
 PS_NT void fluid_forces(const DevModel<T>& m, const RolloutData<T>& d, double* qfrc) {
-  constexpr int S = T::NV; const int nv = m.nv;
+  constexpr int S = T::NV; const int nv = nv_of(m);
   double jp[3 * S], jr[3 * S];
   for (int i = 1; i < m.nbody; i++) {
     if (m.body_mass[i] < kMinVal) continue;
@@ -339,7 +339,7 @@ PS_NT void fluid_forces(const DevModel<T>& m, const RolloutData<T>& d, double* q
 
 template <class T>
 PS_NT void velocity_stage(const DevModel<T>& m, RolloutData<T>& d) {
-  const int nv = m.nv;
+  const int nv = nv_of(m);
   for (int i = 0; i < m.nu; i++) d.actuator_velocity[i] = m.act_gear[i] * d.qvel[m.jnt_dofadr[m.act_jntid[i]]];
   com_velocity(m, d, d.qvel, d.cvel, d.cdof_dot);
   // passive forces: spring + damper + fluid
@@ -353,7 +353,7 @@ PS_NT void velocity_stage(const DevModel<T>& m, RolloutData<T>& d) {
       if (m.jnt_type[j] == JNT_HINGE || m.jnt_type[j] == JNT_SLIDE)
         spring[m.jnt_dofadr[j]] = -k * (d.qpos[m.jnt_qposadr[j]] - m.qpos_spring[m.jnt_qposadr[j]]);
     }
-    if (m.viscosity > 0 || m.density > 0) fluid_forces(m, d, fluid);
+    if (!T::LEAN && (m.viscosity > 0 || m.density > 0)) fluid_forces(m, d, fluid);
     for (int i = 0; i < nv; i++) d.qfrc_passive[i] = spring[i] + (-m.dof_damping[i] * d.qvel[i]) + fluid[i];
   }
   rne_bias(m, d, d.qvel, d.cvel, d.cdof_dot, d.qfrc_bias);
@@ -362,7 +362,7 @@ PS_NT void velocity_stage(const DevModel<T>& m, RolloutData<T>& d) {
 // ---------------------------------------------------------------- actuation + smooth acceleration
 template <class T>
 PS_NT void actuation_stage(const DevModel<T>& m, RolloutData<T>& d) {
-  const int nv = m.nv, nu = m.nu;
+  const int nv = nv_of(m), nu = m.nu;
   vzero(d.qfrc_actuator, nv); vzero(d.actuator_force, nu);
   for (int i = 0; i < m.na; i++) d.act_dot[i] = 0;
   if (!nu || (m.disableflags & DSBL_ACTUATION)) return;
@@ -373,7 +373,7 @@ PS_NT void actuation_stage(const DevModel<T>& m, RolloutData<T>& d) {
       ctrl = clampd(ctrl, m.act_ctrlrange[2 * i], m.act_ctrlrange[2 * i + 1]);
     double in = ctrl;
     const int dyn = m.act_dyntype[i];
-    if (dyn != DYN_NONE) {
+    if (!T::LEAN && dyn != DYN_NONE) {
       const int aa = m.act_actadr[i];
       if (dyn == DYN_INTEGRATOR) d.act_dot[aa] = ctrl;
       else d.act_dot[aa] = (ctrl - d.act[aa]) / fmax(kMinVal, m.act_dynprm[3 * i]);
@@ -393,7 +393,7 @@ PS_NT void actuation_stage(const DevModel<T>& m, RolloutData<T>& d) {
 
 template <class T>
 PS_NT void acceleration_stage(const DevModel<T>& m, RolloutData<T>& d) {
-  const int nv = m.nv;
+  const int nv = nv_of(m);
   for (int i = 0; i < nv; i++) {
     d.qfrc_smooth[i] = d.qfrc_passive[i] - d.qfrc_bias[i] + d.qfrc_actuator[i];
     d.qacc_smooth[i] = d.qfrc_smooth[i];

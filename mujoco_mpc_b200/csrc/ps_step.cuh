@@ -79,7 +79,7 @@ PS_FN void forward_pass(const DevModel<T>& m, RolloutData<T>& d) {
 // ---------------------------------------------------------------- d(qfrc_smooth)/d(qvel) for implicit integrators
 template <class T>
 PS_NT void smooth_vel_derivative(const DevModel<T>& m, RolloutData<T>& d, double* D, bool with_bias) {
-  constexpr int S = T::NV; const int nv = m.nv;
+  constexpr int S = T::NV; const int nv = nv_of(m);
   for (int i = 0; i < nv; i++) for (int j = 0; j < nv; j++) D[i * S + j] = 0;
   for (int i = 0; i < m.nu; i++) {
     double bv = 0;
@@ -136,9 +136,9 @@ PS_NT void smooth_vel_derivative(const DevModel<T>& m, RolloutData<T>& d, double
 // ---------------------------------------------------------------- integration
 template <class T>
 PS_NT void integrate(const DevModel<T>& m, RolloutData<T>& d) {
-  constexpr int S = T::NV; const int nv = m.nv; const double dt = m.timestep;
+  constexpr int S = T::NV; const int nv = nv_of(m); const double dt = m.timestep;
   double qacc[S];
-  if (m.integrator == INT_EULER || m.integrator == INT_RK4) {
+  if (T::LEAN || m.integrator == INT_EULER || m.integrator == INT_RK4) {
     if (!m.any_damping || (m.disableflags & DSBL_EULERDAMP)) vcopy(qacc, d.qacc, nv);
     else {
       double* L = d.sv_H; double dinv[S];
@@ -171,7 +171,7 @@ PS_NT void integrate(const DevModel<T>& m, RolloutData<T>& d) {
     }
   }
   // advance activations, velocities, positions, time
-  if (m.na && !(m.disableflags & DSBL_ACTUATION)) {
+  if (!T::LEAN && m.na && !(m.disableflags & DSBL_ACTUATION)) {
     for (int i = 0; i < m.nu; i++) {
       if (m.act_dyntype[i] == DYN_NONE) continue;
       const int a = m.act_actadr[i];
@@ -187,10 +187,10 @@ PS_NT void integrate(const DevModel<T>& m, RolloutData<T>& d) {
   for (int i = 0; i < nv; i++) d.qvel[i] += qacc[i] * dt;
   for (int j = 0; j < m.njnt; j++) {
     const int qa = m.jnt_qposadr[j], da = m.jnt_dofadr[j], jt = m.jnt_type[j];
-    if (jt == JNT_FREE) {
+    if (!T::LEAN && jt == JNT_FREE) {
       for (int k = 0; k < 3; k++) d.qpos[qa + k] += dt * d.qvel[da + k];
       quat_integrate(d.qpos + qa + 3, d.qvel + da + 3, dt);
-    } else if (jt == JNT_BALL) quat_integrate(d.qpos + qa, d.qvel + da, dt);
+    } else if (!T::LEAN && jt == JNT_BALL) quat_integrate(d.qpos + qa, d.qvel + da, dt);
     else d.qpos[qa] += dt * d.qvel[da];
   }
   d.time += dt;
@@ -200,13 +200,13 @@ PS_NT void integrate(const DevModel<T>& m, RolloutData<T>& d) {
 // by the caller (CheckWarnings, mjpc/utilities.cc:787-800; mjpc/trajectory.cc:169-173)
 template <class T>
 PS_HD bool state_is_bad(const DevModel<T>& m, RolloutData<T>& d) {
-  for (int i = 0; i < m.nq; i++) if (bad_number(d.qpos[i])) { d.warning |= WARN_BADQPOS; return true; }
-  for (int i = 0; i < m.nv; i++) if (bad_number(d.qvel[i])) { d.warning |= WARN_BADQVEL; return true; }
+  for (int i = 0; i < nq_of(m); i++) if (bad_number(d.qpos[i])) { d.warning |= WARN_BADQPOS; return true; }
+  for (int i = 0; i < nv_of(m); i++) if (bad_number(d.qvel[i])) { d.warning |= WARN_BADQVEL; return true; }
   return false;
 }
 template <class T>
 PS_HD bool acc_is_bad(const DevModel<T>& m, RolloutData<T>& d) {
-  for (int i = 0; i < m.nv; i++) if (bad_number(d.qacc[i])) { d.warning |= WARN_BADQACC; return true; }
+  for (int i = 0; i < nv_of(m); i++) if (bad_number(d.qacc[i])) { d.warning |= WARN_BADQACC; return true; }
   return false;
 }
 

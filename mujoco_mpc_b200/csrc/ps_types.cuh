@@ -56,6 +56,15 @@ struct Traits {
                        MAXCON = (MAXCON_ > 0 ? MAXCON_ : 1), MAXEFC = (MAXEFC_ > 0 ? MAXEFC_ : 1),
                        NSENSOR = (NSENSOR_ > 0 ? NSENSOR_ : 1);
   static constexpr bool ELLIPTIC = ELLIPTIC_;
+  // Feature switches derived from the capacities.  CONTACTS: the instantiation carries collision and
+  // contact rows at all.  LEAN (the tiny thread-per-rollout engine): nq == nv == the capacity exactly,
+  // hinge / slide joints only, no contacts, no activations, no fluid, Euler only -- the other code paths
+  // are compiled out and the dof loops have compile-time trip counts, which keeps the per-step
+  // instruction stream inside the SM's instruction cache (ncu: sm__icc_request_hit_rate 46 % and
+  // `no_instruction` the top stall with everything compiled in).  fill_model<T> rejects models that
+  // need a switched-off feature, so they fall through to the next larger instantiation.
+  static constexpr bool CONTACTS = MAXCON_ > 0;
+  static constexpr bool LEAN = (NV_ <= 2) && (NQ_ == NV_) && (NA_ == 0) && (MAXCON_ == 0) && (NCH_ == 0);
   // cooperative engine: max dofs one contact's Jacobian touches, rows of the compressed Jacobian pool
   static constexpr int NCH = NCH_ > 0 ? NCH_ : NV_, NJROW = NJROW_ > 0 ? NJROW_ : (MAXEFC_ > 0 ? MAXEFC_ : 1);
   static constexpr int NCONEH = ELLIPTIC_ ? MAXCON : 1;
@@ -169,6 +178,10 @@ struct alignas(16) DevPlan {
   double spline_times[36];   // kMaxSplinePoints-ish cap of the reference GUI (sampling/planner.h:36)
   int num_spline_points, interpolation, horizon, pad_;
 };
+
+// dof counts: compile-time in a LEAN instantiation (loops over dofs unroll, small arrays stay in registers)
+template <class T> PS_HD int nv_of(const DevModel<T>& m) { if constexpr (T::LEAN) return T::NV; else return m.nv; }
+template <class T> PS_HD int nq_of(const DevModel<T>& m) { if constexpr (T::LEAN) return T::NQ; else return m.nq; }
 
 struct Contact {
   double dist, pos[3], frame[9], includemargin, friction[5], solref[2], solimp[5], mu;

@@ -76,7 +76,7 @@ inline int launch_sparse(cudaStream_t st, const void* dconst, const double* knot
 }
 
 struct Variant {
-  const char* name; size_t const_bytes; int block; bool coop;
+  const char* name; size_t const_bytes; int block; bool coop; bool euler_only;
   int (*fill)(const PsModel*, const PairList&, void*, std::string*);
   void (*options)(void*, double, int);
   void (*debug)(void*, int);
@@ -86,18 +86,18 @@ struct Variant {
 };
 template <class T, int BLOCK>
 inline Variant make_variant(const char* name) {
-  return Variant{name, sizeof(Constants<T>), BLOCK, false, fill_model<T>, set_options<T>, set_debug<T>, set_task<T>, set_plan<T>, launch_rollout<T, BLOCK>};
+  return Variant{name, sizeof(Constants<T>), BLOCK, false, T::LEAN, fill_model<T>, set_options<T>, set_debug<T>, set_task<T>, set_plan<T>, launch_rollout<T, BLOCK>};
 }
 template <class T, int WARPS>
 inline Variant make_coop_variant(const char* name) {
-  return Variant{name, sizeof(Constants<T>), WARPS * 32, true, fill_model<T>, set_options<T>, set_debug<T>, set_task<T>, set_plan<T>, launch_coop<T, WARPS>};
+  return Variant{name, sizeof(Constants<T>), WARPS * 32, true, true, fill_model<T>, set_options<T>, set_debug<T>, set_task<T>, set_plan<T>, launch_coop<T, WARPS>};
 }
 const Variant* variant_tiny();
 const Variant* variant_planar();
 const Variant* variant_legged();
 template <class T, int BLOCK>
 inline Variant make_sparse_variant(const char* name) {
-  return Variant{name, sizeof(Constants<T>), BLOCK, true, fill_model<T>, set_options<T>, set_debug<T>, set_task<T>, set_plan<T>, launch_sparse<T, BLOCK>};
+  return Variant{name, sizeof(Constants<T>), BLOCK, true, true, fill_model<T>, set_options<T>, set_debug<T>, set_task<T>, set_plan<T>, launch_sparse<T, BLOCK>};
 }
 const Variant* variant_planar_sparse();
 const Variant* variant_legged_sparse();
