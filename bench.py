@@ -55,7 +55,7 @@ class ClockSampler(threading.Thread):
         self.index, self.rows, self.stop_flag = index, [], False
 
     def run(self):
-        while not self.stop_flag:
+        while not self.stop_flag or not self.rows:      # at least one sample, taken while the caller is still stepping
             try:
                 out = subprocess.run(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-i", str(self.index)],
                                      capture_output=True, text=True, timeout=5).stdout.strip()
@@ -145,8 +145,8 @@ def run_reference(args, rank, world):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=20)
-    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--steps", type=int, default=100)
+    ap.add_argument("--warmup", type=int, default=10)
     ap.add_argument("--impl", default="b200")
     ap.add_argument("--workload", default=DEFAULT_WORKLOAD, choices=sorted(WORKLOADS))
     ap.add_argument("--no-cpu-baseline", action="store_true")
@@ -244,13 +244,12 @@ def main():
     launches0 = sum(e.launches() for e in engines)
     sampler = ClockSampler(local); sampler.start()
     barrier()
-    ms_total = 0.0; kern_ms = np.zeros(3)
+    ms_total = 0.0; kern_ms = np.zeros(3); lat = []
     for _ in range(args.steps):
-        ms_total += device_step(True)
+        ms = device_step(True); ms_total += ms; lat.append(ms)
         for e in engines:
             kern_ms += np.array(e.kernel_ms())
     barrier()
-    clocks = sampler.summary()
     launches = sum(e.launches() for e in engines) - launches0
     t = torch.tensor([ms_total], dtype=torch.float64, device=f"cuda:{local}")
     if world > 1:
@@ -266,6 +265,11 @@ def main():
     for _ in range(args.steps):
         e2e_step()
     barrier(); e2e_s = (time.perf_counter() - t0) / args.steps
+    # the clocks sampler spans both timed regions (device-timed and end-to-end); if they were shorter than one
+    # nvidia-smi query, keep stepping until it has seen the GPU under this load
+    while len(sampler.rows) < 3 and time.perf_counter() - t0 < 5.0:
+        device_step(False)
+    clocks = sampler.summary()
     t = torch.tensor([e2e_s], dtype=torch.float64, device=f"cuda:{local}")
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
@@ -279,6 +283,10 @@ def main():
         peak = engines[0].fp64_peak()
         rollout_ms = kern_ms[1] / args.steps
         alg = sum(flops.get(c["name"], 0.0) * c["N"] * (c["H"] - 1) for c in cases)
+        # DRAM bytes (read + write) of the rollout kernels of one step, from the ncu --set full captures
+        dram = flops.get("_dram_bytes_per_sample_step", {})
+        traffic = sum(dram.get(c["name"], float("nan")) * c["N"] * (c["H"] - 1) for c in cases)
+        traffic = None if traffic != traffic else traffic
         achieved = alg / (rollout_ms * 1e-3) / 1e12 if alg else None
         line = {"metric": METRIC, "value": value, "unit": "sample-steps/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
                 "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
@@ -286,12 +294,12 @@ def main():
                                                 "horizon_steps": [c["H"] for c in cases], "l2": "flushed (256 MB write) between iterations",
                                                 "kernels": [e.variant() for e in engines],
                                                 "parallelism": f"samples sharded over {world} rank(s), NCCL all-gather min-loc"},
-                "planning_iteration_latency_ms": ms_step, "kernel_ms": {"perturb": kern_ms[0] / args.steps, "rollout": rollout_ms, "argmin": kern_ms[2] / args.steps},
+                "planning_iteration_latency_ms": {"mean": ms_step, "p50": float(np.percentile(lat, 50)), "p95": float(np.percentile(lat, 95))}, "kernel_ms": {"perturb": kern_ms[0] / args.steps, "rollout": rollout_ms, "argmin": kern_ms[2] / args.steps},
                 "e2e": {"value": e2e_value, "unit": "sample-steps/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                         "latency_ms": e2e_s * 1e3},
                 "gpu_launches": int(launches), "clocks": clocks,
                 "roofline": {"bound": "fp64", "achieved": achieved, "peak": peak, "unit": "TFLOP/s", "frac": (achieved / peak) if achieved else None,
-                             "traffic": None, "peak_source": "DFMA probe measured in this run (MEASURED_PEAKS.json has no FP64 figure)"}}
+                             "traffic": traffic, "traffic_unit": "bytes per step (sum of the step's rollout launches)", "peak_source": "DFMA probe measured in this run (MEASURED_PEAKS.json has no FP64 figure)"}}
         if not args.no_cpu_baseline and world == 1:
             from oracle import pyoracle
             pyoracle.build()

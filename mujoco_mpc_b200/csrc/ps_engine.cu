@@ -26,9 +26,10 @@ static int fail(const std::string& s) { g_error = s; return -1; }
 // planning-latency regime -- and `large` (thread-per-rollout over the same phases) the big batches.
 struct Family { const Variant* small; const Variant* large; int crossover; };
 static const Family kFamilies[] = {
-    {variant_tiny_coop(), variant_tiny(), 768},               // nv ~ 2: the warp kernel only trims latency of small batches
+    {variant_tiny_coop(), variant_tiny(), 0},                 // nv ~ 2: the lean thread-per-rollout kernel wins at every batch size (1.4 vs 2.3 ms at N <= 1024);
+                                                              // the warp kernel serves small models that need a feature the lean kernel compiles out
     {variant_tiny(), nullptr, 0},
-    {variant_planar_coop(), variant_planar(), 1536},         // nv ~ 9: dense thread-per-rollout wins the big batches
+    {variant_planar_coop(), variant_planar(), 2560},         // nv ~ 9: dense thread-per-rollout wins the big batches
     {variant_planar(), nullptr, 0},
     {variant_legged_coop(), variant_legged_sparse(), 8192},  // nv ~ 18: compressed-Jacobian thread-per-rollout
     {variant_legged(), nullptr, 0},

@@ -136,6 +136,7 @@ inline int fill_model(const PsModel* s, const PairList& pl, void* out, std::stri
   if (pl.unsupported) { *why = "model has colliding geom pairs outside the supported narrow-phase set"; return -1; }
   if (s->opt_cone == PS_CONE_ELLIPTIC && !T::ELLIPTIC && !pl.g1.empty()) { *why = "elliptic cones not in this instantiation"; return -1; }
   if (!T::CONTACTS && !pl.g1.empty()) { *why = "contacts not in this instantiation"; return -1; }
+  if (!T::QUAT) for (int j = 0; j < s->njnt; j++) if (s->jnt_type[j] != PS_JNT_HINGE && s->jnt_type[j] != PS_JNT_SLIDE) { *why = "free / ball joints not in this instantiation"; return -1; }
   if (T::LEAN) {     // features compiled out of the lean instantiation (ps_types.cuh: Traits::LEAN)
     if (s->nv != T::NV || s->nq != T::NQ) { *why = "lean instantiation needs nq == nv == its capacity"; return -1; }
     if (s->na) { *why = "activations not in the lean instantiation"; return -1; }

@@ -17,7 +17,7 @@ PS_NT void kinematics(const DevModel<T>& m, RolloutData<T>& d) {
   vzero(d.xpos, 3); d.xquat[0] = 1; d.xquat[1] = d.xquat[2] = d.xquat[3] = 0;
   vzero(d.xmat, 9); d.xmat[0] = d.xmat[4] = d.xmat[8] = 1;
   vzero(d.xipos, 3); vcopy(d.ximat, d.xmat, 9);
-  if (!T::LEAN) for (int j = 0; j < m.njnt; j++) {
+  if (T::QUAT) for (int j = 0; j < m.njnt; j++) {
     if (m.jnt_type[j] == JNT_FREE) unit4(d.qpos + m.jnt_qposadr[j] + 3);
     else if (m.jnt_type[j] == JNT_BALL) unit4(d.qpos + m.jnt_qposadr[j]);
   }
@@ -29,7 +29,7 @@ PS_NT void kinematics(const DevModel<T>& m, RolloutData<T>& d) {
     if (m.body_mocapid[b] >= 0) {
       vcopy(pos, d.mocap_pos + 3 * m.body_mocapid[b], 3);
       vcopy(quat, d.mocap_quat + 4 * m.body_mocapid[b], 4);
-    } else if (!T::LEAN && jn == 1 && m.jnt_type[ja] == JNT_FREE) {
+    } else if (T::QUAT && jn == 1 && m.jnt_type[ja] == JNT_FREE) {
       const int qa = m.jnt_qposadr[ja];
       vcopy(pos, d.qpos + qa, 3); vcopy(quat, d.qpos + qa + 3, 4);
       vcopy(d.xanchor + 3 * ja, pos, 3); vcopy(d.xaxis + 3 * ja, m.jnt_axis + 3 * ja, 3);
@@ -47,9 +47,9 @@ PS_NT void kinematics(const DevModel<T>& m, RolloutData<T>& d) {
         if (jt == JNT_SLIDE) {
           const double dq = d.qpos[qa] - m.qpos0[qa];
           for (int k = 0; k < 3; k++) pos[k] += axis[k] * dq;
-        } else if (jt == JNT_HINGE || (!T::LEAN && jt == JNT_BALL)) {
+        } else if (jt == JNT_HINGE || (T::QUAT && jt == JNT_BALL)) {
           double ql[4];
-          if (!T::LEAN && jt == JNT_BALL) vcopy(ql, d.qpos + qa, 4);
+          if (T::QUAT && jt == JNT_BALL) vcopy(ql, d.qpos + qa, 4);
           else axis_angle_quat(ql, m.jnt_axis + 3 * j, d.qpos[qa] - m.qpos0[qa]);
           quat_mul(quat, quat, ql);
           quat_rotate(v, m.jnt_pos + 3 * j, quat);   // keep the anchor fixed under the rotation
@@ -121,11 +121,11 @@ PS_NT void com_position(const DevModel<T>& m, RolloutData<T>& d) {
     double off[3]; const double* root = sc + 3 * m.body_rootid[b];
     for (int k = 0; k < 3; k++) off[k] = root[k] - d.xanchor[3 * j + k];
     const int jt = m.jnt_type[j];
-    if (!T::LEAN && jt == JNT_FREE) {
+    if (T::QUAT && jt == JNT_FREE) {
       for (int k = 0; k < 3; k++) { double ax[3] = {0, 0, 0}; ax[k] = 1; dof_motion(d.cdof + 6 * (da + k), ax, nullptr); }
       da += 3;
     }
-    if (!T::LEAN && (jt == JNT_FREE || jt == JNT_BALL)) {
+    if (T::QUAT && (jt == JNT_FREE || jt == JNT_BALL)) {
       for (int k = 0; k < 3; k++) {
         double ax[3] = {d.xmat[9 * b + k], d.xmat[9 * b + 3 + k], d.xmat[9 * b + 6 + k]};
         dof_motion(d.cdof + 6 * (da + k), ax, off);
@@ -227,14 +227,14 @@ PS_NT void com_velocity(const DevModel<T>& m, const RolloutData<T>& d, const dou
     const int ja = m.body_jntadr[i];
     for (int j = ja; j < ja + m.body_jntnum[i]; j++) {
       int da = m.jnt_dofadr[j]; const int jt = m.jnt_type[j];
-      if (!T::LEAN && jt == JNT_FREE) {
+      if (T::QUAT && jt == JNT_FREE) {
         for (int k = 0; k < 3; k++) {
           vzero(cdof_dot + 6 * (da + k), 6);
           for (int r = 0; r < 6; r++) v[r] += d.cdof[6 * (da + k) + r] * qvel[da + k];
         }
         da += 3;
       }
-      if (!T::LEAN && (jt == JNT_FREE || jt == JNT_BALL)) {
+      if (T::QUAT && (jt == JNT_FREE || jt == JNT_BALL)) {
         for (int k = 0; k < 3; k++) cross_motion(cdof_dot + 6 * (da + k), v, d.cdof + 6 * (da + k));
         for (int k = 0; k < 3; k++) for (int r = 0; r < 6; r++) v[r] += d.cdof[6 * (da + k) + r] * qvel[da + k];
       } else {

@@ -187,10 +187,10 @@ PS_NT void integrate(const DevModel<T>& m, RolloutData<T>& d) {
   for (int i = 0; i < nv; i++) d.qvel[i] += qacc[i] * dt;
   for (int j = 0; j < m.njnt; j++) {
     const int qa = m.jnt_qposadr[j], da = m.jnt_dofadr[j], jt = m.jnt_type[j];
-    if (!T::LEAN && jt == JNT_FREE) {
+    if (T::QUAT && jt == JNT_FREE) {
       for (int k = 0; k < 3; k++) d.qpos[qa + k] += dt * d.qvel[da + k];
       quat_integrate(d.qpos + qa + 3, d.qvel + da + 3, dt);
-    } else if (!T::LEAN && jt == JNT_BALL) quat_integrate(d.qpos + qa, d.qvel + da, dt);
+    } else if (T::QUAT && jt == JNT_BALL) quat_integrate(d.qpos + qa, d.qvel + da, dt);
     else d.qpos[qa] += dt * d.qvel[da];
   }
   d.time += dt;

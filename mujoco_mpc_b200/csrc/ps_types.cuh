@@ -64,6 +64,7 @@ struct Traits {
   // `no_instruction` the top stall with everything compiled in).  fill_model<T> rejects models that
   // need a switched-off feature, so they fall through to the next larger instantiation.
   static constexpr bool CONTACTS = MAXCON_ > 0;
+  static constexpr bool QUAT = NQ_ != NV_;      // free / ball joints possible at all
   static constexpr bool LEAN = (NV_ <= 2) && (NQ_ == NV_) && (NA_ == 0) && (MAXCON_ == 0) && (NCH_ == 0);
   // cooperative engine: max dofs one contact's Jacobian touches, rows of the compressed Jacobian pool
   static constexpr int NCH = NCH_ > 0 ? NCH_ : NV_, NJROW = NJROW_ > 0 ? NJROW_ : (MAXEFC_ > 0 ? MAXEFC_ : 1);

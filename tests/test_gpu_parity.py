@@ -16,7 +16,7 @@ def rel_err(a, b):
     return np.abs(a - b).max() / max(1.0, np.abs(b).max())
 
 
-def run_case(name, N, interp, H=None, seed=2024, sigma=None, time=0.37, warm=True, prep=None):
+def run_case(name, N, interp, H=None, seed=2024, sigma=None, time=0.37, warm=True, prep=None, engine=None, expect=None):
     model, task, s = registry.load(name)
     if prep is not None:
         prep(model, task)
@@ -32,11 +32,19 @@ def run_case(name, N, interp, H=None, seed=2024, sigma=None, time=0.37, warm=Tru
         nk = rng.uniform(-0.6, 0.6, (P, model.nu)) * 0.5 * (model.actuator_ctrlrange[:, 1] - model.actuator_ctrlrange[:, 0])
         nominal = (nt, nk)
     o, nt, nk, w = oracle_iteration(model, task, s, state, time, N, H, P, interp, sigma, z, nominal=nominal)
-    e = Engine(model, task)
+    import os
+    if engine:                       # pin one kernel flavour (read by ps_create)
+        os.environ["PS_ENGINE"] = engine
+    try:
+        e = Engine(model, task)
+    finally:
+        os.environ.pop("PS_ENGINE", None)
     e.set_state(state, time)
     e.set_nominal(nt, nk, interp)
     e.set_noise(z)
     gw, gwr, gnr = e.rollouts(N, H, sigma, writeback=True)
+    if expect:
+        assert e.variant() == expect, (e.variant(), expect)
     oret, ofail = o.returns()
     gret, gfail = e.returns()
     assert np.array_equal(ofail.astype(bool), (gfail & 1).astype(bool))
@@ -114,6 +122,17 @@ def test_parity_quadruped_one_second_horizon(oracle_lib):
     from mujoco_mpc_b200 import task as T
     run_case("Quadruped Flat", N=512, interp=2, H=101,
              prep=lambda m, t: T.quadruped_snapshot(m, t, mode="Quadruped", gait="Trot", time=0.37))
+
+
+@pytest.mark.parametrize("name,engine,expect", [
+    ("Cartpole", "warp", "tiny_coop"), ("Cartpole", "thread", "tiny"), ("Acrobot", "warp", "tiny_coop"),
+    ("Walker", "warp", "planar_coop"), ("Walker", "thread", "planar"),
+    ("Quadruped Flat", "warp", "legged_coop"), ("Quadruped Flat", "thread", "legged_sparse"), ("Quadruped Flat", "dense", "legged")])
+def test_parity_every_kernel_flavour(oracle_lib, name, engine, expect):
+    # the engine picks a kernel by batch size; here each flavour is pinned and checked on the same batch
+    from mujoco_mpc_b200 import task as T
+    prep = (lambda m, t: T.quadruped_snapshot(m, t, mode="Quadruped", gait="Trot", time=0.37)) if name.startswith("Quadruped") else None
+    run_case(name, N=160, interp=2, H=41, prep=prep, engine=engine, expect=expect)
 
 
 def test_first_iteration_zero_nominal(oracle_lib):
