@@ -1,0 +1,99 @@
+"""Headless closed loop of the reference's `testspeed` harness (mjpc/testspeed.cc:43-132,
+`SynchronousPlanningCost`) with BOTH sides of the loop on the B200: the planner is
+CudaSamplingPlanner, and the plant's `mj_step` is the same device forward step, run as a one-sample
+rollout with writeback between planning iterations (BASELINE.json
+configs[0] is `testspeed --task=Cartpole` semantics).
+
+Loop, per plant step i (testspeed.cc:96-113): action = ActionFromPolicy(state, time); mj_step; cost =
+CostValue(sensordata); every `steps_per_planning_iteration` steps PlanIteration (agent.cc:270-315:
+SetState, steps = clamp(horizon / agent_timestep + 1, 1, 512), OptimizePolicy).  Tasks whose
+Transition() is the base no-op are covered (cartpole, acrobot, swimmer, walker).
+
+    python -m mujoco_mpc_b200.testspeed --task Cartpole --steps_per_planning_iteration 4 --total_time 10
+"""
+import argparse
+import math
+import os
+import time as _time
+
+import numpy as np
+
+from . import mjcf, registry, task as _task
+from .engine import Engine
+from .planner import CudaSamplingPlanner
+
+
+def plant_model(name):
+    """The model as the plant sees it: the XML's own opt.timestep / integrator (the agent overrides only
+    touch the Agent's private copy, agent.cc:74,275-276)."""
+    return mjcf.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "tasks", registry.TASKS[name]))
+
+
+def synchronous_planning_cost(task_name, steps_per_planning_iteration=4, total_time=10.0, num_trajectory=None,
+                              interpolation=None, seed=1, noise=None, device=0, verbose=False):
+    """Returns dict(total_cost, average_cost, steps, plans, wall_s, plan_s, state, time).  `noise(k, N, P, nu)` may
+    return the injected N(0,1) tensor of planning iteration k (parity runs); default is the device generator."""
+    model, task, s = registry.load(task_name)
+    pm = plant_model(task_name)
+    ptask = _task.make_task(pm, registry._TASK_ID_NAME.get(task_name, task_name))
+    N = num_trajectory or s["num_trajectory"]
+    interp = s["interpolation"] if interpolation is None else interpolation
+    P = min(s["num_spline_points"], 36)
+    pl = CudaSamplingPlanner(model, task, device=device)
+    pl.configure(num_trajectory=N, interpolation=interp, sigma0=s["exploration"], sigma1=s["exploration2"])
+    pl.SetSeed(seed)
+    plant = Engine(pm, ptask, device=device)
+    state = registry.home_state(pm)                 # mj_resetDataKeyframe(model, data, "home"), testspeed.cc:72-76
+    pl.Reset(s["steps"], np.zeros(model.nu))          # agent.Reset(data->ctrl)
+    t = 0.0
+    total_steps = int(math.ceil(total_time / pm.opt_timestep))
+    total_cost, plans, plan_s = 0.0, 0, 0.0
+    t0 = _time.perf_counter()
+    i = 0
+    while i < total_steps:
+        # plant steps until (and including) the next step after which the planner runs
+        spp = steps_per_planning_iteration
+        k = min(-(-i // spp) * spp - i + 1, total_steps - i)      # the planner runs after steps 0, spp, 2 spp, ...
+        times, knots = pl.policy()
+        if len(times) == 0:
+            times, knots = np.zeros(1), np.zeros((1, model.nu))
+        plant.set_state(state, t)
+        plant.set_nominal(times, knots, interp)
+        plant.rollouts(1, k + 1, 0.0, writeback=True)
+        tr = plant.trajectory(0)
+        total_cost += float(np.sum(tr["costs"][:k]))
+        state = tr["states"][k].copy(); t = float(tr["times"][k])
+        last = i + k - 1
+        i += k
+        if last % steps_per_planning_iteration == 0:
+            p0 = _time.perf_counter()
+            if noise is not None:
+                pl.SetNoise(noise(plans, N, P, model.nu))
+            pl.SetState(state, t)
+            pl.OptimizePolicy(s["steps"])
+            plan_s += _time.perf_counter() - p0
+            plans += 1
+        if verbose and math.floor(t) > math.floor(t - k * pm.opt_timestep):
+            print(f"sim time: {math.floor(t)}, cost: {tr['costs'][k - 1]:.6g}")
+    wall = _time.perf_counter() - t0
+    pl.close(); plant.close()
+    return dict(total_cost=total_cost, average_cost=total_cost / total_steps, steps=total_steps, plans=plans, wall_s=wall,
+                plan_s=plan_s, state=state, time=t)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--task", default="Cartpole")
+    ap.add_argument("--steps_per_planning_iteration", type=int, default=4)
+    ap.add_argument("--total_time", type=float, default=10.0)
+    ap.add_argument("--num_trajectory", type=int, default=None)
+    ap.add_argument("--interpolation", type=int, default=None, help="0 zero, 1 linear, 2 cubic (default: the task's)")
+    a = ap.parse_args()
+    r = synchronous_planning_cost(a.task, a.steps_per_planning_iteration, a.total_time, a.num_trajectory, a.interpolation, verbose=True)
+    print(f"Total wall time ({r['plans']} planning steps): {r['wall_s']:.3f} s ({a.total_time / r['wall_s']:.2f}x realtime); "
+          f"planning {r['plan_s'] / max(r['plans'], 1) * 1e3:.3f} ms / iteration")
+    print(f"Average cost per step (lower is better): {r['average_cost']:.6g}")
+
+
+if __name__ == "__main__":
+    main()

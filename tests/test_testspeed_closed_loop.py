@@ -1,0 +1,63 @@
+"""BASELINE.json configs[0]: the reference's `testspeed` closed loop (mjpc/testspeed.cc:43-132) on
+Cartpole -- 10 samples, 1 s horizon, zero-order spline -- with planner AND plant on the B200
+(mujoco_mpc_b200/testspeed.py), against the same loop restated on the oracle under the same injected
+noise: total cost, final state and every planned policy must agree."""
+import math
+import numpy as np
+import pytest
+from mujoco_mpc_b200 import registry, task as T
+from oracle import pyoracle
+
+pytestmark = pytest.mark.gpu
+
+
+def oracle_closed_loop(task_name, spp, total_time, N, interp, noise):
+    from mujoco_mpc_b200.testspeed import plant_model
+    model, task, s = registry.load(task_name)
+    pm = plant_model(task_name)
+    ptask = T.make_task(pm, registry._TASK_ID_NAME.get(task_name, task_name))
+    P = min(s["num_spline_points"], 36)
+    planner = pyoracle.Oracle(model, task); planner.configure(P, interp, s["exploration"])
+    planner.set_policy(np.zeros(1), np.zeros((1, model.nu)), interp)       # agent.Reset(data->ctrl)
+    plant = pyoracle.Oracle(pm, ptask)
+    st = registry.home_state(pm)
+    plant.reset_data(); plant.set("qpos", st[:pm.nq]); plant.set("qvel", st[pm.nq:pm.nq + pm.nv]); plant.set("time", [0.0])
+    total_steps = int(math.ceil(total_time / pm.opt_timestep)); total = 0.0; plans = 0
+    for i in range(total_steps):
+        t = plant.get("time")[0]
+        plant.set("ctrl", planner.action(t))
+        plant.step()
+        total += plant.cost(plant.get("sensordata")[:ptask.num_residual])
+        if i % spp == 0:
+            state = np.concatenate([plant.get("qpos")[:pm.nq], plant.get("qvel")[:pm.nv]])
+            planner.set_state(state, plant.get("time")[0])
+            planner.optimize(N, s["steps"], noise(plans, N, P, model.nu)); plans += 1
+    state = np.concatenate([plant.get("qpos")[:pm.nq], plant.get("qvel")[:pm.nv]])
+    return dict(total_cost=total, state=state, time=plant.get("time")[0], plans=plans, policy=planner.policy(0))
+
+
+@pytest.mark.parametrize("task_name,interp,N", [("Cartpole", 0, 10), ("Acrobot", 2, 16)])
+def test_testspeed_closed_loop_matches_oracle(oracle_lib, task_name, interp, N):
+    from mujoco_mpc_b200.testspeed import synchronous_planning_cost
+    cache = {}
+
+    def noise(k, n, P, nu):
+        if k not in cache:
+            cache[k] = np.random.default_rng(1000 + k).standard_normal((n, P, nu))
+        return cache[k]
+    from mujoco_mpc_b200.testspeed import plant_model
+    total_time = 120 * plant_model(task_name).opt_timestep          # 120 plant steps, a plan after every 4th
+    g = synchronous_planning_cost(task_name, steps_per_planning_iteration=4, total_time=total_time, num_trajectory=N, interpolation=interp, noise=noise)
+    o = oracle_closed_loop(task_name, 4, total_time, N, interp, noise)
+    assert g["plans"] == o["plans"] == 30
+    assert abs(g["time"] - o["time"]) < 1e-12
+    assert np.abs(g["state"] - o["state"]).max() <= 1e-9 * max(1.0, np.abs(o["state"]).max())
+    assert abs(g["total_cost"] - o["total_cost"]) <= 1e-8 * max(1.0, abs(o["total_cost"]))
+
+
+def test_testspeed_runs_with_device_noise():
+    # the CLI path: on-device Philox noise, planner default settings; cost is finite and the loop plans every 4th step
+    from mujoco_mpc_b200.testspeed import synchronous_planning_cost
+    from mujoco_mpc_b200.testspeed import plant_model
+    r = synchronous_planning_cost("Cartpole", steps_per_planning_iteration=4, total_time=50 * plant_model("Cartpole").opt_timestep, interpolation=0)
+    assert r["plans"] == 13 and r["steps"] == 50 and np.isfinite(r["total_cost"]) and r["total_cost"] > 0
