@@ -92,6 +92,9 @@ int ps_get_trajectory(PsEngine* e, int sample, double* states, double* actions, 
                       double* residual, double* costs, double* trace, double* total_return, int* failure);
 /* writeback of ALL samples for parity tests: states[N][H][ns], residual[N][H][nr] (may be NULL) */
 int ps_get_all_trajectories(PsEngine* e, double* states, double* actions, double* residual, double* costs);
+/* trace points of ALL samples of the last ps_rollouts_writeback: trace[N][H][3*num_trace] -- what
+ * SamplingPlanner::Traces (planners/sampling/planner.cc:388-434) draws as line segments between steps */
+int ps_get_all_traces(PsEngine* e, double* trace);
 /* device time of the last ps_rollouts kernels in milliseconds (CUDA events) */
 int ps_last_kernel_ms(PsEngine* e, float* perturb_ms, float* rollout_ms, float* reduce_ms);
 int ps_kernel_launch_count(PsEngine* e, long long* launches);

@@ -436,6 +436,13 @@ int ps_get_all_trajectories(PsEngine* e, double* states, double* actions, double
   return 0;
 }
 
+int ps_get_all_traces(PsEngine* e, double* trace) {
+  if (!e || !e->wb_valid) return fail("ps_get_all_traces: call ps_rollouts_writeback first");
+  if (e->task.num_trace <= 0) return fail("ps_get_all_traces: the task has no trace sensors");
+  CU(cudaSetDevice(e->device));
+  return transpose_out(e, e->wb.trace, e->H * 3 * e->task.num_trace, trace);
+}
+
 int ps_last_kernel_ms(PsEngine* e, float* perturb_ms, float* rollout_ms, float* reduce_ms) {
   if (!e) return fail("null engine");
   CU(cudaSetDevice(e->device));

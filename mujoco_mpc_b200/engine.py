@@ -16,7 +16,7 @@ EXPORTS = ["ps_last_error", "ps_create", "ps_destroy", "ps_set_model", "ps_set_o
            "ps_set_nominal", "ps_set_noise", "ps_set_seed", "ps_rollouts", "ps_rollouts_async", "ps_rollouts_writeback",
            "ps_get_returns", "ps_get_knots", "ps_get_trajectory", "ps_get_all_trajectories", "ps_last_kernel_ms",
            "ps_kernel_launch_count", "ps_winner_record_device", "ps_stream", "ps_name", "ps_variant", "ps_fp64_peak", "ps_constants_bytes",
-           "ps_set_param_std", "ps_elite_update", "ps_elite_update_ms"]
+           "ps_set_param_std", "ps_elite_update", "ps_elite_update_ms", "ps_get_all_traces"]
 
 
 class EngineError(RuntimeError):
@@ -169,6 +169,12 @@ class Engine:
         st = np.zeros((N, H, self.ns)); ac = np.zeros((N, H, m.nu)); rs = np.zeros((N, H, t.num_residual)); cs = np.zeros((N, H))
         self._ck(self.L.ps_get_all_trajectories(self.h, _p(st), _p(ac), _p(rs), _p(cs)))
         return dict(states=st, actions=ac, residual=rs, costs=cs)
+
+    def all_traces(self):
+        """trace[N][H][3*num_trace] of the last writeback batch (SamplingPlanner::Traces, planner.cc:388-434)"""
+        out = np.zeros((self.N, self.H, 3 * self.task.num_trace))
+        self._ck(self.L.ps_get_all_traces(self.h, _p(out)))
+        return out
 
     def kernel_ms(self):
         a, b, c = ctypes.c_float(), ctypes.c_float(), ctypes.c_float()

@@ -157,6 +157,26 @@ def test_reroll_single_trajectory(oracle_lib):
     e.close()
 
 
+def test_traces_of_all_samples(oracle_lib):
+    # SamplingPlanner::Traces (planner.cc:388-434) draws trace[i][t] -> trace[i][t+1] for every sample:
+    # the writeback batch exposes exactly those points
+    model, task, s = registry.load("Walker")
+    N, H, P = 48, 31, 3
+    z = np.random.default_rng(3).standard_normal((N, P, model.nu))
+    state = synthetic_state(model)
+    o, nt, nk, w = oracle_iteration(model, task, s, state, 0.0, N, H, P, 2, 0.5, z)
+    e = Engine(model, task)
+    e.set_state(state, 0.0); e.set_nominal(nt, nk, 2); e.set_noise(z)
+    e.rollouts(N, H, 0.5, writeback=True)
+    tr = e.all_traces()
+    assert tr.shape == (N, H, 3 * task.num_trace) and task.num_trace > 0
+    for i in range(N):
+        ot = o.trajectory(i)
+        if not ot["failure"]:
+            assert rel_err(tr[i], ot["trace"]) <= 1e-9
+    e.close()
+
+
 def test_device_rng_statistics():
     model, task, s = registry.load("Particle")
     e = Engine(model, task)
