@@ -267,7 +267,9 @@ def main():
     barrier(); e2e_s = (time.perf_counter() - t0) / args.steps
     # the clocks sampler spans both timed regions (device-timed and end-to-end); if they were shorter than one
     # nvidia-smi query, keep stepping until it has seen the GPU under this load
-    while len(sampler.rows) < 3 and time.perf_counter() - t0 < 5.0:
+    # (single rank only: under torchrun every device_step holds a collective, so the step count must be the
+    # same on every rank -- a rank-local loop here deadlocks the all-gather)
+    while world == 1 and len(sampler.rows) < 3 and time.perf_counter() - t0 < 5.0:
         device_step(False)
     clocks = sampler.summary()
     t = torch.tensor([e2e_s], dtype=torch.float64, device=f"cuda:{local}")
