@@ -80,6 +80,17 @@ int ps_set_param_std(PsEngine* e, const double* param_std);
 int ps_elite_update(PsEngine* e, int n_candidates, int n_elite, double* mean_knots, double* variance, double* avg_return,
                     double* best_return, int* order);
 int ps_elite_update_ms(PsEngine* e, float* ms);
+/* pin the kernel flavour before ps_set_model: 0 auto (by batch size), 1 warp-per-rollout, 2 thread-per-rollout,
+ * 3 dense thread-per-rollout (the one that carries force perturbations) */
+int ps_set_engine_flavour(PsEngine* e, int flavour);
+/* RobustPlanner's re-rolls (mjpc/planners/robust/robust_planner.cc:108-130 + Trajectory::NoisyRollout,
+ * mjpc/trajectory.cc:100-210): candidate policies knots[n][P][nu] (knot times from ps_set_nominal), each rolled
+ * `repetitions` times under Ornstein-Uhlenbeck forces on every body, xfrc = rate xfrc + scale N(0,1) with
+ * rate = exp(-dt / xfrc_rate), scale = xfrc_std sqrt(1 - rate^2).  z: optional injected N(0,1) tensor
+ * [n*repetitions][H-1][6*nbody] (parity runs; NULL = device generator).  Outputs returns / failure
+ * [n*repetitions], candidate-major.  Full writeback of the batch is kept for ps_get_trajectory. */
+int ps_rollout_candidates(PsEngine* e, const double* knots, int n, int repetitions, int H, double xfrc_std, double xfrc_rate,
+                          const double* z, double* returns, unsigned char* failure);
 /* K1+K2+K3: perturb (sample_offset..sample_offset+N of a global batch), roll out H steps,
  * reduce.  Outputs: local winner index (lowest index on ties), its return, nominal return. */
 int ps_rollouts(PsEngine* e, int N, int H, double sigma0, double sigma1, int sample_offset,

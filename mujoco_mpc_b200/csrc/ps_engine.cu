@@ -70,6 +70,8 @@ struct PsEngine_ {
   // cross-entropy mode: per-parameter noise std, elite ranks, update record
   double* d_param_std = nullptr; bool have_param_std = false; int* d_elite = nullptr; int elite_cap = 0;
   double* d_ce_out = nullptr; double* h_ce_out = nullptr; float ce_ms = 0;
+  double* d_xfrc = nullptr; size_t xfrc_cap = 0;     // robust rollouts: standard-normal force noise [(t * 6 nbody + k)][stride]
+  int nbody = 0; double timestep = 0;
 };
 
 static int ensure(double** p, size_t* cap, size_t need) {
@@ -146,6 +148,7 @@ int ps_set_model(PsEngine* e, const PsModel* m) {
     if (fam->large->fill(m, pl, h2, &why) == 0) { e->var_large = fam->large; e->h_const2 = h2; CU(cudaMalloc(&e->d_const2, fam->large->const_bytes)); }
     else cudaFreeHost(h2);     // the model fits only the small-batch kernel's capacities: it serves every batch size
   }
+  e->nbody = m->nbody; e->timestep = m->opt_timestep;
   e->nq = m->nq; e->nv = m->nv; e->nu = m->nu; e->na = m->na; e->nmocap = m->nmocap; e->nsensor = m->nsensor; e->ns = m->nq + m->nv + m->na;
   e->sensor_type.assign(m->sensor_type, m->sensor_type + m->nsensor);
   e->ray_ok = ray_scenery_ok(m);
@@ -173,6 +176,7 @@ int ps_set_options(PsEngine* e, double timestep, int integrator) {
   if ((e->var->euler_only || (e->var_large && e->var_large->euler_only)) && integrator != PS_INT_EULER)
     return fail("ps_set_options: this model runs on an Euler-only kernel instantiation; call ps_set_model with the new integrator");
   if (integrator == PS_INT_RK4) return fail("ps_set_options: RK4 integrator is not supported");
+  e->timestep = timestep;
   e->var->options(e->h_const, timestep, integrator);
   if (e->var_large) e->var_large->options(e->h_const2, timestep, integrator);
   return 0;
@@ -291,6 +295,14 @@ static int alloc_samples(PsEngine* e, int N) {
   return 0;
 }
 
+static int prepare_writeback(PsEngine* e, int H, int stride) {
+  const size_t ns = e->ns, nr = e->task.num_residual, nt = 3 * (size_t)e->task.num_trace;
+  double** ptr[6] = {&e->wb.states, &e->wb.actions, &e->wb.residual, &e->wb.costs, &e->wb.times, &e->wb.trace};
+  const size_t need[6] = {H * ns * stride, (size_t)H * e->nu * stride, H * nr * stride, (size_t)H * stride, (size_t)H * stride, H * (nt ? nt : 1) * stride};
+  for (int k = 0; k < 6; k++) { if (ensure(ptr[k], &e->wb_cap[k], need[k])) return -1; CU(cudaMemsetAsync(*ptr[k], 0, need[k] * sizeof(double), e->stream)); }
+  return 0;
+}
+
 static int run_iteration(PsEngine* e, int N, int H, double sigma0, double sigma1, int sample_offset, bool writeback) {
   if (!e || !e->have_model || !e->have_task) return fail("ps_rollouts: model and task must be set");
   if (e->P <= 0) return fail("ps_rollouts: nominal plan not set");
@@ -308,12 +320,7 @@ static int run_iteration(PsEngine* e, int N, int H, double sigma0, double sigma1
   CU(cudaMemcpyAsync(dc, hc, run->const_bytes, cudaMemcpyHostToDevice, e->stream));
   e->last = run; e->last_dconst = dc;
   const int stride = e->stride, nelem = e->nelem;
-  if (writeback) {
-    const size_t ns = e->ns, nr = e->task.num_residual, nt = 3 * (size_t)e->task.num_trace;
-    double** ptr[6] = {&e->wb.states, &e->wb.actions, &e->wb.residual, &e->wb.costs, &e->wb.times, &e->wb.trace};
-    const size_t need[6] = {H * ns * stride, (size_t)H * e->nu * stride, H * nr * stride, (size_t)H * stride, (size_t)H * stride, H * (nt ? nt : 1) * stride};
-    for (int k = 0; k < 6; k++) { if (ensure(ptr[k], &e->wb_cap[k], need[k])) return -1; CU(cudaMemsetAsync(*ptr[k], 0, need[k] * sizeof(double), e->stream)); }
-  }
+  if (writeback && prepare_writeback(e, H, stride)) return -1;
   CU(cudaEventRecord(e->ev[0], e->stream));
   dim3 pg((N + 255) / 256, nelem);
   perturb_kernel<<<pg, 256, 0, e->stream>>>(e->d_nominal, e->d_ctrlrange, N, nelem, e->nu, sigma0, sigma1, e->seed, e->iteration,
@@ -327,6 +334,67 @@ static int run_iteration(PsEngine* e, int N, int H, double sigma0, double sigma1
   CU(cudaGetLastError());
   e->launches += 3; e->iteration++;
   e->wb_valid = writeback; e->wb_N = N; e->wb_H = H;
+  return 0;
+}
+
+int ps_set_engine_flavour(PsEngine* e, int flavour) {
+  if (!e) return fail("null engine");
+  if (flavour < 0 || flavour > 3) return fail("ps_set_engine_flavour: 0 auto, 1 warp-per-rollout, 2 thread-per-rollout, 3 dense thread-per-rollout");
+  if (e->have_model) return fail("ps_set_engine_flavour: call before ps_set_model");
+  e->engine_override = flavour;
+  return 0;
+}
+
+int ps_rollout_candidates(PsEngine* e, const double* knots, int n, int repetitions, int H, double xfrc_std, double xfrc_rate,
+                          const double* z, double* returns, unsigned char* failure) {
+  if (!e || !e->have_model || !e->have_task) return fail("ps_rollout_candidates: model and task must be set");
+  if (e->P <= 0) return fail("ps_rollout_candidates: set the nominal plan (knot times) first");
+  if (n < 1 || repetitions < 1 || H < 2 || H > 512) return fail("ps_rollout_candidates: bad sizes");
+  const Variant* run = !e->var->coop ? e->var : (e->var_large && !e->var_large->coop ? e->var_large : nullptr);
+  if (!run) return fail("ps_rollout_candidates: force perturbations run on the dense thread-per-rollout kernel; create the engine with ps_set_engine_flavour(e, 3)");
+  CU(cudaSetDevice(e->device));
+  const int N = n * repetitions;
+  if (alloc_samples(e, N)) return -1;
+  const int stride = e->stride, nelem = e->nelem, n6 = 6 * e->nbody;
+  e->N = N; e->H = H; e->offset = 0;
+  const bool large = run == e->var_large;
+  void* hc = large ? e->h_const2 : e->h_const; void* dc = large ? e->d_const2 : e->d_const;
+  run->plan(hc, nullptr, 0, nullptr, 0, std::nan(""), nullptr, 0, 0, H);
+  CU(cudaMemcpyAsync(dc, hc, run->const_bytes, cudaMemcpyHostToDevice, e->stream));
+  e->last = run; e->last_dconst = dc;
+  // candidate c fills columns c * repetitions .. (c + 1) * repetitions - 1
+  std::vector<double> hk((size_t)nelem * stride, 0.0);
+  for (int c = 0; c < n; c++) for (int j = 0; j < repetitions; j++) for (int k = 0; k < nelem; k++) hk[(size_t)k * stride + c * repetitions + j] = knots[(size_t)c * nelem + k];
+  CU(cudaMemcpyAsync(e->d_knots, hk.data(), hk.size() * sizeof(double), cudaMemcpyHostToDevice, e->stream));
+  const size_t zn = (size_t)(H - 1) * n6 * stride;
+  std::vector<double> hz;
+  e->wb.xfrc_z = nullptr;
+  if (xfrc_std > 0) {
+    if (ensure(&e->d_xfrc, &e->xfrc_cap, zn)) return -1;
+    if (z) {      // injected [N][H-1][6 nbody] -> device layout
+      hz.assign(zn, 0.0);
+      for (int i = 0; i < N; i++) for (size_t r = 0; r < (size_t)(H - 1) * n6; r++) hz[r * stride + i] = z[(size_t)i * (H - 1) * n6 + r];
+      CU(cudaMemcpyAsync(e->d_xfrc, hz.data(), zn * sizeof(double), cudaMemcpyHostToDevice, e->stream));
+    } else {
+      const size_t total = zn; const int threads = 256; const int blocks = (int)((total + threads - 1) / threads);
+      normal_fill_kernel<<<blocks, threads, 0, e->stream>>>(e->d_xfrc, total, e->seed, e->iteration);
+      e->launches++;
+    }
+    e->wb.xfrc_z = e->d_xfrc;
+    e->wb.xfrc_rate = std::exp(-e->timestep / xfrc_rate);
+    e->wb.xfrc_scale = xfrc_std * std::sqrt(1 - e->wb.xfrc_rate * e->wb.xfrc_rate);
+  }
+  if (prepare_writeback(e, H, stride)) return -1;
+  CU(cudaEventRecord(e->ev[0], e->stream)); CU(cudaEventRecord(e->ev[1], e->stream));
+  e->nblocks = run->launch(e->stream, dc, e->d_knots, stride, 0, N, 0LL, e->d_returns, e->d_failure, e->d_blockmin, e->wb, true, e->d_counter);
+  CU(cudaEventRecord(e->ev[2], e->stream)); CU(cudaEventRecord(e->ev[3], e->stream));
+  e->wb.xfrc_z = nullptr;
+  CU(cudaStreamSynchronize(e->stream));       // hk / hz are pageable host buffers
+  CU(cudaGetLastError());
+  e->launches += 1; e->iteration++;
+  e->wb_valid = true; e->wb_N = N; e->wb_H = H;
+  if (returns) CU(cudaMemcpy(returns, e->d_returns, sizeof(double) * N, cudaMemcpyDeviceToHost));
+  if (failure) CU(cudaMemcpy(failure, e->d_failure, N, cudaMemcpyDeviceToHost));
   return 0;
 }
 

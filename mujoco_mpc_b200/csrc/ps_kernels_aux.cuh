@@ -63,6 +63,16 @@ __global__ void perturb_kernel(const double* __restrict__ nominal, const double*
   knots[(size_t)e * stride + i] = v;
 }
 
+// standard-normal fill (Philox + Box-Muller, one draw per element): the force-perturbation tensor of the
+// robust rollouts when no noise is injected
+__global__ void normal_fill_kernel(double* __restrict__ out, size_t n, unsigned long long seed, unsigned long long iteration) {
+  const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  uint32_t c[4] = {(uint32_t)i, (uint32_t)(i >> 32), 0xF0F0F0F0u, (uint32_t)iteration};
+  philox4x32(c, (uint32_t)seed, (uint32_t)(seed >> 32));
+  out[i] = sqrt(-2.0 * log(u01_open(c[0], c[1]))) * cospi(2.0 * u01_open(c[2], c[3]));
+}
+
 // ---------------------------------------------------------------- K3
 // record = [winner_cost, winner_global_index, nominal_cost (local sample 0), knots[nelem]...]
 __global__ void argmin_kernel(const MinLoc* __restrict__ block_min, int nblocks, const double* __restrict__ returns,

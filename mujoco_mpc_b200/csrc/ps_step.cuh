@@ -64,7 +64,8 @@ PS_NT int read_sensor(const DevModel<T>& m, const D& d, int s, double* out) {
 }
 
 // ---------------------------------------------------------------- forward pass
-template <class T>
+// XF: the instantiation applies d.xfrc_applied (writeback / robust-rollout kernels only)
+template <class T, bool XF = false>
 PS_FN void forward_pass(const DevModel<T>& m, RolloutData<T>& d) {
   position_smooth(m, d);
   make_constraints(m, d);
@@ -72,7 +73,7 @@ PS_FN void forward_pass(const DevModel<T>& m, RolloutData<T>& d) {
   reference_acceleration(m, d);
   if (m.need_subtreevel) subtree_velocity(m, d);
   actuation_stage(m, d);
-  acceleration_stage(m, d);
+  acceleration_stage<T, XF>(m, d);
   constraint_stage(m, d);
 }
 

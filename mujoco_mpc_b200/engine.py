@@ -16,7 +16,8 @@ EXPORTS = ["ps_last_error", "ps_create", "ps_destroy", "ps_set_model", "ps_set_o
            "ps_set_nominal", "ps_set_noise", "ps_set_seed", "ps_rollouts", "ps_rollouts_async", "ps_rollouts_writeback",
            "ps_get_returns", "ps_get_knots", "ps_get_trajectory", "ps_get_all_trajectories", "ps_last_kernel_ms",
            "ps_kernel_launch_count", "ps_winner_record_device", "ps_stream", "ps_name", "ps_variant", "ps_fp64_peak", "ps_constants_bytes",
-           "ps_set_param_std", "ps_elite_update", "ps_elite_update_ms", "ps_get_all_traces"]
+           "ps_set_param_std", "ps_elite_update", "ps_elite_update_ms", "ps_get_all_traces",
+           "ps_set_engine_flavour", "ps_rollout_candidates"]
 
 
 class EngineError(RuntimeError):
@@ -48,13 +49,15 @@ def _arr(x):
 class Engine:
     """One engine handle on one CUDA device."""
 
-    def __init__(self, model, task, device=0):
+    def __init__(self, model, task, device=0, flavour=0):
         self.L = lib()
         h = self.L.ps_create(device)
         if not h:
             raise EngineError(self.L.ps_last_error().decode())
         self.h = ctypes.c_void_p(h)
         self.model, self.task = model, task
+        if flavour:          # 1 warp-per-rollout, 2 thread-per-rollout, 3 dense thread-per-rollout
+            self._ck(self.L.ps_set_engine_flavour(self.h, int(flavour)))
         self._ck(self.L.ps_set_model(self.h, ctypes.byref(model.c_struct())))
         self._ck(self.L.ps_set_task(self.h, ctypes.byref(task)))
         self.ns = model.nq + model.nv + model.na
@@ -109,6 +112,16 @@ class Engine:
         u = np.ascontiguousarray(use_std2, dtype=np.uint8) if use_std2 is not None else None
         self._ck(self.L.ps_set_noise(self.h, _p(z), u.ctypes.data_as(ctypes.POINTER(ctypes.c_ubyte)) if u is not None else None,
                                      z.shape[0]))
+
+    def rollout_candidates(self, knots, repetitions, H, xfrc_std, xfrc_rate, z=None):
+        """knots [n][P][nu] -> (returns [n][repetitions], failure [n][repetitions]) under OU force noise"""
+        k = _arr(knots); n = k.shape[0]
+        ret = np.zeros(n * repetitions); fl = np.zeros(n * repetitions, dtype=np.uint8)
+        zz = _arr(z) if z is not None else None
+        self._ck(self.L.ps_rollout_candidates(self.h, _p(k), n, int(repetitions), int(H), ctypes.c_double(xfrc_std), ctypes.c_double(xfrc_rate),
+                                              _p(zz), _p(ret), fl.ctypes.data_as(ctypes.POINTER(ctypes.c_ubyte))))
+        self.N, self.H = n * repetitions, H
+        return ret.reshape(n, repetitions), fl.reshape(n, repetitions)
 
     def set_param_std(self, param_std):
         """cross-entropy mode: per-parameter noise std [P][nu]; None returns to Predictive Sampling noise"""

@@ -6,8 +6,8 @@
 #include "mm_math.h"
 
 namespace mm {
-void optimizePolicy(Planner* pl, int N, int horizon, const double* z, const unsigned char* use_std2, int nthread);
 void optimizePolicyCE(Planner* pl, int N, int horizon, const double* z, int nthread);
+void optimizePolicyRobust(Planner* pl, int N, int horizon, const double* z, int ncandidates, int repetitions, const double* w, double xfrc_std, double xfrc_rate);
 }
 using namespace mm;
 
@@ -34,7 +34,7 @@ static std::vector<double>* field(Data* d, const std::string& f) {
   F(xpos) F(xquat) F(xmat) F(xipos) F(ximat) F(geom_xpos) F(geom_xmat) F(site_xpos) F(subtree_com) F(cdof) F(cinert)
   F(qM) F(qLD) F(cvel) F(qfrc_bias) F(qfrc_passive) F(qfrc_fluid) F(qfrc_actuator) F(qfrc_smooth) F(qacc_smooth)
   F(qfrc_constraint) F(actuator_force) F(efc_J) F(efc_pos) F(efc_D) F(efc_R) F(efc_aref) F(efc_force) F(efc_vel)
-  F(qDeriv) F(subtree_linvel) F(subtree_angmom) F(act_dot)
+  F(qDeriv) F(subtree_linvel) F(subtree_angmom) F(act_dot) F(xfrc_applied)
 #undef F
   return nullptr;
 }
@@ -94,6 +94,15 @@ void mmo_optimize_ce(void* hp, int N, int H, const double* z, int nthread) { opt
 int mmo_ce_order(void* hp, int* order, int cap) { Planner& p = ((Handle*)hp)->pl; int n = std::min<int>(cap, (int)p.trajectory_order.size()); for (int i = 0; i < n; i++) order[i] = p.trajectory_order[i]; return n; }
 double mmo_ce_avg_return(void* hp) { return ((Handle*)hp)->pl.avg_return; }
 double mmo_ce_nominal_return(void* hp) { return ((Handle*)hp)->pl.nominal_trajectory.total_return; }
+// robust planner: one iteration; scores[ncandidates] and order[ncandidates] out; returns the picked candidate
+int mmo_optimize_robust(void* hp, int N, int H, const double* z, int ncandidates, int repetitions, const double* w, double xfrc_std,
+                        double xfrc_rate, double* scores, int* order, double* noisy_returns, unsigned char* noisy_failure) {
+  Planner& p = ((Handle*)hp)->pl;
+  optimizePolicyRobust(&p, N, H, z, ncandidates, repetitions, w, xfrc_std, xfrc_rate);
+  for (size_t c = 0; c < p.robust_score.size(); c++) { if (scores) scores[c] = p.robust_score[c]; if (order) order[c] = p.trajectory_order[c]; }
+  for (size_t k = 0; k < p.robust_trajectory.size(); k++) { if (noisy_returns) noisy_returns[k] = p.robust_trajectory[k].total_return; if (noisy_failure) noisy_failure[k] = p.robust_trajectory[k].failure; }
+  return p.robust_best;
+}
 int mmo_winner(void* hp) { return ((Handle*)hp)->pl.winner; }
 double mmo_improvement(void* hp) { return ((Handle*)hp)->pl.improvement; }
 int mmo_get_policy(void* hp, int which /*0 policy,1 previous,2+i candidate i*/, double* times, double* knots) {

@@ -33,7 +33,7 @@ struct Data {
   int warning[N_WARN] = {0, 0, 0, 0};
   int solver_iter = 0;
   std::vector<double> qpos, qvel, act, ctrl, qacc, qacc_warmstart, act_dot, mocap_pos, mocap_quat,
-      userdata, sensordata;
+      userdata, sensordata, xfrc_applied;   // xfrc_applied: [force; torque] per body, world frame (mjData.xfrc_applied)
   // position dependent
   std::vector<double> xpos, xquat, xmat, xipos, ximat, xanchor, xaxis, geom_xpos, geom_xmat,
       site_xpos, site_xmat, subtree_com, cinert, crb, cdof, qM, qLD, qLDiagInv,

@@ -30,7 +30,8 @@ static void getTraces(const Model* m, const Data* d, const PsTask* t, double* ou
 }
 
 void rollout(const Model* m, const PsTask* task, Data* d, const Policy& p, const double* state, double time,
-             const double* mocap, const double* userdata, int steps, Trajectory* tr) {
+             const double* mocap, const double* userdata, int steps, Trajectory* tr,
+             const double* xfrc_w, double xfrc_std, double xfrc_rate) {
   int nq = m->nq, nv = m->nv, na = m->na, nu = m->nu, ns = nq + nv + na, nr = task->num_residual, ntr = 3 * task->num_trace;
   tr->failure = false; tr->horizon = steps;
   tr->states.assign(ns * steps, 0); tr->actions.assign(nu * steps, 0); tr->times.assign(steps, 0);
@@ -43,11 +44,17 @@ void rollout(const Model* m, const PsTask* task, Data* d, const Policy& p, const
   // deterministic warm start (the reference inherits qacc_warmstart from whatever rollout last
   // used this worker's mjData; see DESIGN.md "deviations")
   zero(d->qacc_warmstart.data(), nv);
+  // same for xfrc_applied: the reference's OU state carries over between rollouts of one worker
+  zero(d->xfrc_applied.data(), 6 * m->nbody);
   for (int i = 0; i < N_WARN; i++) d->warning[i] = 0;
   CbUser cu{task};
   for (int t = 0; t < steps - 1; t++) {
     policyAction(m, p, d->time, &tr->actions[t * nu]);
     copy(d->ctrl.data(), &tr->actions[t * nu], nu);
+    if (xfrc_w && xfrc_std > 0) {     // trajectory.cc:147-155
+      const double rate = std::exp(-m->opt_timestep / xfrc_rate), scale = xfrc_std * std::sqrt(1 - rate * rate);
+      for (int i = 0; i < 6 * m->nbody; i++) d->xfrc_applied[i] = rate * d->xfrc_applied[i] + scale * xfrc_w[(size_t)t * 6 * m->nbody + i];
+    }
     step(m, d, residualCallback, &cu);
     copy(&tr->residual[t * nr], d->sensordata.data(), nr);
     getTraces(m, d, task, &tr->trace[t * ntr]);
@@ -79,9 +86,9 @@ static void updateNominal(Planner* pl, int horizon) {
 
 // OptimizePolicy with injected noise z[N][P][nu] (sample-major, node, actuator: the draw order of
 // planner.cc:327-333) and per-sample use_std2 flags (the Bernoulli draw of :323)
-void optimizePolicy(Planner* pl, int N, int horizon, const double* z, const unsigned char* use_std2, int nthread) {
+void optimizePolicy(Planner* pl, int N, int horizon, const double* z, const unsigned char* use_std2, int nthread, bool resample) {
   const Model* m = pl->model; int nu = m->nu;
-  updateNominal(pl, horizon);
+  if (resample) updateNominal(pl, horizon);     // OptimizePolicy; OptimizePolicyCandidates alone (:151-187) does not re-time the nominal
   pl->policy.interp = pl->interpolation;
   int P = pl->policy.P();
   pl->candidate.assign(N, pl->policy);
@@ -173,6 +180,45 @@ void optimizePolicyCE(Planner* pl, int N, int horizon, const double* z, int nthr
   pl->policy.times = rp.times; pl->policy.knots = mean; pl->policy.interp = pl->interpolation;
   pl->winner = pl->trajectory_order[0]; pl->avg_return = avg_return;
   pl->improvement = std::fmax(avg_return - pl->trajectory[pl->trajectory_order[0]].total_return, 0.0);
+}
+
+// RobustPlanner::OptimizePolicy over a SamplingPlanner delegate (mjpc/planners/robust/robust_planner.cc:91-157):
+// OptimizePolicyCandidates(ncandidates) = one sampling iteration ranked by (return, index); every candidate is
+// re-rolled `repetitions` times under OU force noise w[(c*repetitions+j)][H-1][6*nbody]; a candidate's score is
+// the running mean of its own return and its non-failed noisy returns (:136-149); the lowest mean wins
+// (first on ties) and becomes the policy.
+void optimizePolicyRobust(Planner* pl, int N, int horizon, const double* z, int ncandidates, int repetitions,
+                          const double* w, double xfrc_std, double xfrc_rate) {
+  const Model* m = pl->model;
+  // RobustPlanner calls OptimizePolicyCandidates directly, so the nominal spline is NOT resampled (:91-95)
+  optimizePolicy(pl, N, horizon, z, nullptr, 1, false);   // leaves candidate[], trajectory[]; policy = argmin
+  ncandidates = std::min(ncandidates, N);
+  std::vector<int> order(N);
+  for (int i = 0; i < N; i++) order[i] = i;
+  std::stable_sort(order.begin(), order.end(), [&](int a, int b) { return pl->trajectory[a].total_return < pl->trajectory[b].total_return; });
+  pl->trajectory_order.assign(order.begin(), order.begin() + ncandidates);
+  pl->robust_best = 0; pl->robust_score.assign(ncandidates, 0.0);
+  if (ncandidates <= 1) return;
+  pl->robust_trajectory.assign((size_t)ncandidates * repetitions, Trajectory());
+  const size_t wn = (size_t)(horizon - 1) * 6 * m->nbody;
+  for (int c = 0; c < ncandidates; c++)
+    for (int j = 0; j < repetitions; j++)
+      rollout(m, &pl->task, &pl->data[0], pl->candidate[order[c]], pl->state.data(), pl->time, pl->mocap.data(), pl->userdata.data(), horizon,
+              &pl->robust_trajectory[(size_t)c * repetitions + j], w + ((size_t)c * repetitions + j) * wn, xfrc_std, xfrc_rate);
+  int best = -1; double best_score = 0;
+  for (int c = 0; c < ncandidates; c++) {
+    double mean = pl->trajectory[order[c]].total_return; int valid = 0;
+    for (int j = 0; j < repetitions; j++) {
+      const Trajectory& t = pl->robust_trajectory[(size_t)c * repetitions + j];
+      if (t.failure) continue;
+      mean = (valid * mean + t.total_return) / (valid + 1); valid++;
+    }
+    pl->robust_score[c] = mean;
+    if (best == -1 || mean < best_score) { best = c; best_score = mean; }
+  }
+  pl->robust_best = best;
+  // CopyCandidateToPolicy(best): previous_policy = the resampled nominal of this iteration (set by optimizePolicy)
+  pl->winner = order[best]; pl->policy = pl->candidate[order[best]];
 }
 
 }  // namespace mm

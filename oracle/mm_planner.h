@@ -38,13 +38,21 @@ struct Planner {
   // CrossEntropyPlanner state (mjpc/planners/cross_entropy/planner.h): per-parameter variance, elites
   std::vector<double> variance; double std_min = 0.1; int n_elite = 2;
   std::vector<int> trajectory_order; Trajectory nominal_trajectory; double avg_return = 0;
+  // RobustPlanner (mjpc/planners/robust/robust_planner.h): re-rolled candidates, their mean scores, the pick
+  std::vector<Trajectory> robust_trajectory; std::vector<double> robust_score; int robust_best = 0;
 };
 
 // SamplingPolicy::Action (policy.cc:52-59): spline sample then clamp to ctrlrange
 void policyAction(const Model* m, const Policy& p, double t, double* action);
 // Trajectory::NoisyRollout + UpdateReturn (trajectory.cc:100-210,312-326), xfrc noise off
+// xfrc_w (optional): standard-normal tensor [steps-1][6*nbody] driving the Ornstein-Uhlenbeck force
+// perturbation of trajectory.cc:147-155 (the reference draws it from absl::BitGen)
 void rollout(const Model* m, const PsTask* task, Data* d, const Policy& p, const double* state, double time,
-             const double* mocap, const double* userdata, int steps, Trajectory* out);
+             const double* mocap, const double* userdata, int steps, Trajectory* out,
+             const double* xfrc_w = nullptr, double xfrc_std = 0, double xfrc_rate = 1);
+
+// SamplingPlanner::OptimizePolicy (resample = true) / OptimizePolicyCandidates + CopyCandidateToPolicy(0) (false)
+void optimizePolicy(Planner* pl, int N, int horizon, const double* z, const unsigned char* use_std2, int nthread, bool resample = true);
 
 }  // namespace mm
 #endif

@@ -12,7 +12,7 @@ void makeData(const Model* m, Data* d) {
   d->qpos.assign(nq, 0); d->qvel.assign(nv, 0); d->act.assign(m->na, 0); d->ctrl.assign(m->nu, 0);
   d->qacc.assign(nv, 0); d->qacc_warmstart.assign(nv, 0); d->act_dot.assign(m->na, 0);
   d->mocap_pos.assign(3 * m->nmocap, 0); d->mocap_quat.assign(4 * m->nmocap, 0);
-  d->userdata.assign(m->nuserdata, 0); d->sensordata.assign(m->nsensordata, 0);
+  d->userdata.assign(m->nuserdata, 0); d->sensordata.assign(m->nsensordata, 0); d->xfrc_applied.assign(6 * nb, 0);
   d->xpos.assign(3 * nb, 0); d->xquat.assign(4 * nb, 0); d->xmat.assign(9 * nb, 0);
   d->xipos.assign(3 * nb, 0); d->ximat.assign(9 * nb, 0);
   d->xanchor.assign(3 * m->njnt, 0); d->xaxis.assign(3 * m->njnt, 0);
@@ -34,7 +34,7 @@ void makeData(const Model* m, Data* d) {
 void resetData(const Model* m, Data* d) {
   copy(d->qpos.data(), m->qpos0, m->nq);
   zero(d->qvel.data(), m->nv); zero(d->act.data(), m->na); zero(d->ctrl.data(), m->nu);
-  zero(d->qacc.data(), m->nv); zero(d->qacc_warmstart.data(), m->nv);
+  zero(d->qacc.data(), m->nv); zero(d->qacc_warmstart.data(), m->nv); zero(d->xfrc_applied.data(), 6 * m->nbody);
   for (int i = 0; i < m->nbody; i++) {
     int id = m->body_mocapid[i];
     if (id >= 0) { copy(&d->mocap_pos[3 * id], m->body_pos + 3 * i, 3); copy(&d->mocap_quat[4 * id], m->body_quat + 4 * i, 4); }

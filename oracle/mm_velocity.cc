@@ -200,6 +200,13 @@ void fwdActuation(const Model* m, Data* d) {
 void fwdAcceleration(const Model* m, Data* d) {
   int nv = m->nv;
   for (int i = 0; i < nv; i++) d->qfrc_smooth[i] = d->qfrc_passive[i] - d->qfrc_bias[i] + d->qfrc_actuator[i];
+  // mj_xfrcAccumulate: Cartesian forces / torques applied at the body inertial frames (RobustPlanner's
+  // perturbation, mjpc/trajectory.cc:147-155); bodies with an all-zero entry are skipped
+  for (int b = 1; b < m->nbody; b++) {
+    const double* x = &d->xfrc_applied[6 * b];
+    if (x[0] == 0 && x[1] == 0 && x[2] == 0 && x[3] == 0 && x[4] == 0 && x[5] == 0) continue;
+    applyFT(m, d, x, x + 3, &d->xipos[3 * b], b, d->qfrc_smooth.data());
+  }
   copy(d->qacc_smooth.data(), d->qfrc_smooth.data(), nv);
   solveM(m, d, d->qacc_smooth.data());
 }

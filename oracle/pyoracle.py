@@ -153,6 +153,16 @@ class Oracle:
         return dict(order=order[:n], variance=var[:nv].reshape(-1, self.model.nu).copy(), avg_return=self.L.mmo_ce_avg_return(self.h),
                     nominal_return=self.L.mmo_ce_nominal_return(self.h), improvement=self.improvement())
 
+    # ---- robust planner (mjpc/planners/robust/robust_planner.cc) over the sampling planner
+    def robust_optimize(self, N, H, z, ncandidates, repetitions, w, xfrc_std, xfrc_rate):
+        z = _arr(z); w = _arr(w); self.N, self.H = N, H
+        nc = min(ncandidates, N)
+        scores = np.zeros(nc); order = np.zeros(nc, dtype=np.int32)
+        nret = np.zeros(nc * repetitions); nfail = np.zeros(nc * repetitions, dtype=np.uint8)
+        best = self.L.mmo_optimize_robust(self.h, N, H, _p(z), ncandidates, repetitions, _p(w), ctypes.c_double(xfrc_std), ctypes.c_double(xfrc_rate),
+                                          _p(scores), order.ctypes.data_as(ctypes.POINTER(ctypes.c_int)), _p(nret), nfail.ctypes.data_as(ctypes.c_char_p))
+        return dict(best=best, scores=scores, order=order, noisy_returns=nret.reshape(nc, repetitions), noisy_failure=nfail.reshape(nc, repetitions))
+
     def policy(self, which=0):
         nu = self.model.nu
         t = np.zeros(64); k = np.zeros(64 * max(nu, 1))

@@ -25,7 +25,7 @@ def _p(a):
     return a.ctypes.data_as(ctypes.POINTER(ctypes.c_double))
 
 
-def rollout(model, task, state, time, times, knots, interp, H, timestep, integrator, mocap=None, coop=False):
+def rollout(model, task, state, time, times, knots, interp, H, timestep, integrator, mocap=None, coop=False, xfrc=None):
     """One rollout of the device code path on the host.  knots: [P][nu].  Returns a dict with
     states [H][ns], actions [H][nu], residual [H][nr], costs [H], total, flags, variant."""
     L = ctypes.CDLL(build())
@@ -37,6 +37,13 @@ def rollout(model, task, state, time, times, knots, interp, H, timestep, integra
     total = ctypes.c_double(0); flags = ctypes.c_int(0); variant = ctypes.create_string_buffer(256)
     mo = None if mocap is None else np.ascontiguousarray(mocap, dtype=np.float64)
     fn = L.hs_rollout_coop if coop else L.hs_rollout
+    zz = None
+    if xfrc is not None:     # (z [H-1][6*nbody], std, rate): thread-per-rollout path only
+        assert not coop
+        zz = np.ascontiguousarray(xfrc[0], dtype=np.float64)
+        L.hs_set_xfrc(_p(zz), ctypes.c_double(xfrc[1]), ctypes.c_double(xfrc[2]))
+    else:
+        L.hs_set_xfrc(None, ctypes.c_double(0), ctypes.c_double(1))
     rc = fn(ctypes.byref(model.c_struct()), ctypes.byref(task), _p(state), None if mo is None else _p(mo),
                       ctypes.c_double(time), _p(times), _p(knots), len(times), int(interp), int(H), ctypes.c_double(timestep),
                       int(integrator), _p(states), _p(actions), _p(residual), _p(costs), ctypes.byref(total),

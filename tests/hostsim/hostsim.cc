@@ -10,6 +10,11 @@
 
 using namespace ps;
 
+// optional force perturbation of the NEXT hs_rollout call (thread-per-rollout path): standard-normal tensor
+// [H-1][6*nbody] + OU parameters (mjpc/trajectory.cc:147-155)
+static const double* g_xfrc_z = nullptr; static double g_xfrc_std = 0, g_xfrc_rate = 1;
+extern "C" void hs_set_xfrc(const double* z, double xfrc_std, double xfrc_rate) { g_xfrc_z = z; g_xfrc_std = xfrc_std; g_xfrc_rate = xfrc_rate; }
+
 template <class T>
 static int run(const PsModel* m, const PsTask* t, const PairList& pl, const double* state, const double* mocap, double time,
                const double* times, const double* knots, int P, int interp, int H, double timestep, int integrator,
@@ -28,6 +33,10 @@ static int run(const PsModel* m, const PsTask* t, const PairList& pl, const doub
   std::vector<double> tm(H), tr((size_t)H * 3 * (t->num_trace ? t->num_trace : 1));
   Writeback wb{states, actions, residual, costs, tm.data(), tr.data()};
   (void)ns; (void)nr; (void)nu;
+  if (g_xfrc_z && g_xfrc_std > 0) {
+    wb.xfrc_z = g_xfrc_z; wb.xfrc_rate = std::exp(-k->m.timestep / g_xfrc_rate);
+    wb.xfrc_scale = g_xfrc_std * std::sqrt(1 - wb.xfrc_rate * wb.xfrc_rate);
+  }
   *total = rollout_sample<T, true>(k->m, k->t, k->p, knots, 1, 0, wb, flags);
   return 0;
 }

@@ -1,0 +1,133 @@
+"""Parity at BASELINE.json's full sizes, through size-independent properties (the oracle cannot roll
+out 65,536 samples in test time):
+
+* every kernel flavour of a family (warp-per-rollout, thread-per-rollout, dense) returns bit-identical
+  costs on the same batch -- three independent codings / schedules of the same arithmetic;
+* a batch rolled out in one launch equals the same global samples rolled out as shards with
+  `sample_offset` (the multi-GPU partitioning): noise is keyed by the global sample index;
+* the same seed gives the same result twice; the winner record is the lowest-index argmin of the
+  returns; global sample 0 is the un-noised nominal, and a sub-batch that the oracle CAN roll out
+  (the first samples, under the noise the device generated) matches it."""
+import os
+import numpy as np
+import pytest
+from mujoco_mpc_b200 import registry, task as T
+from mujoco_mpc_b200.engine import Engine
+from tests.common import synthetic_state
+
+# Written after this round's GPU minutes were spent: these have not run on hardware yet, so a failure is
+# reported (xfail) instead of turning the suite red; a pass shows up as XPASS.
+pytestmark = [pytest.mark.gpu, pytest.mark.xfail(strict=False, reason="not yet run on a B200 (GPU budget of the round exhausted)")]
+
+
+def make(name, engine=None):
+    model, task, s = registry.load(name)
+    if name.startswith("Quadruped"):
+        T.quadruped_snapshot(model, task, mode="Quadruped", gait="Trot", time=0.0)
+    if engine:
+        os.environ["PS_ENGINE"] = engine
+    try:
+        e = Engine(model, task)
+    finally:
+        os.environ.pop("PS_ENGINE", None)
+    return model, task, s, e
+
+
+def knot_times(s, H, P):
+    # accumulated exactly as UpdateNominalPolicy does (t += shift), so the oracle's resampling reproduces them
+    shift = max((H - 1) * s["timestep"] / (P - 1), 1e-5)
+    out, t = [], 0.0
+    for _ in range(P):
+        out.append(t); t += shift
+    return np.array(out)
+
+
+def prime(e, model, s, H, P, seed=77):
+    e.set_state(synthetic_state(model), 0.0)
+    half = 0.5 * (model.actuator_ctrlrange[:, 1] - model.actuator_ctrlrange[:, 0])
+    knots = 0.2 * half * np.random.default_rng(4).standard_normal((P, model.nu))
+    e.set_nominal(knot_times(s, H, P), knots, 2)
+    e.set_seed(seed)
+    return knots
+
+
+@pytest.mark.parametrize("name,N,H", [("Cartpole", 65536, 101), ("Acrobot", 4096, 201), ("Particle", 4096, 51)])
+def test_full_size_determinism_sharding_and_argmin(name, N, H):
+    model, task, s, e = make(name)
+    P = min(s["num_spline_points"], 36)
+    prime(e, model, s, H, P)
+    w, wr, nr = e.rollouts(N, H, s["exploration"])
+    ret, fail = e.returns()
+    # winner = lowest-index argmin, nominal return = sample 0
+    assert w == int(np.argmin(ret)) and wr == ret[w] and nr == ret[0]
+    # same seed, same iteration counter -> identical batch
+    e.set_seed(77)
+    w2, _, _ = e.rollouts(N, H, s["exploration"])
+    ret2, _ = e.returns()
+    assert w2 == w and np.array_equal(ret, ret2)
+    # the same global samples as 8 shards (what 8 ranks would roll out)
+    shard = N // 8
+    best = (np.inf, -1)
+    for r in range(8):
+        e.set_seed(77)
+        ws, wrs, _ = e.rollouts(shard, H, s["exploration"], sample_offset=r * shard)
+        rs, _ = e.returns()
+        assert np.array_equal(rs, ret[r * shard:(r + 1) * shard]), (name, r)
+        if wrs < best[0]:
+            best = (wrs, r * shard + ws)
+    assert best[1] == w
+    e.close()
+
+
+@pytest.mark.parametrize("name,N,H,flavours", [
+    ("Cartpole", 8192, 101, ["warp", "thread"]),
+    ("Walker", 4096, 41, ["warp", "thread"]),
+    ("Quadruped Flat", 2048, 31, ["warp", "thread", "dense"])])
+def test_kernel_flavours_agree_bit_for_bit(name, N, H, flavours):
+    out = []
+    for f in flavours:
+        model, task, s, e = make(name, engine=f)
+        P = min(s["num_spline_points"], 36)
+        prime(e, model, s, H, P)
+        w, wr, nr = e.rollouts(N, H, s["exploration"])
+        ret, fail = e.returns()
+        out.append((e.variant(), w, ret.copy(), fail.copy()))
+        e.close()
+    assert len({o[0] for o in out}) == len(flavours), [o[0] for o in out]
+    for o in out[1:]:
+        same_caps = (o[3] & 2) == (out[0][3] & 2)          # capacity flags can differ between capacity classes
+        ok = same_caps & ((o[3] & 2) == 0)
+        assert ok.mean() > 0.98
+        assert np.array_equal(o[2][ok], out[0][2][ok]), (name, o[0], out[0][0], np.abs(o[2][ok] - out[0][2][ok]).max())
+        if ok.all():
+            assert o[1] == out[0][1]
+
+
+def test_quadruped_one_second_first_samples_match_oracle(oracle_lib):
+    # BASELINE config 4 geometry at a large batch: the device's own Philox noise is read back through the
+    # candidate knots, and the first samples are re-rolled by the oracle from exactly those knots
+    from oracle import pyoracle
+    model, task, s, e = make("Quadruped Flat")
+    N, H, P = 16384, 101, min(s["num_spline_points"], 36)
+    knots = prime(e, model, s, H, P)
+    e.rollouts(N, H, s["exploration"])
+    assert e.variant() == "legged_sparse"
+    ret, fail = e.returns()
+    o = pyoracle.Oracle(model, task); o.configure(P, 2, s["exploration"])
+    times = knot_times(s, H, P)
+    checked = 0
+    for i in (0, 1, 2, 3, 5000, N - 1):
+        if fail[i]:
+            continue
+        ki = e.knots(i)
+        if i == 0:
+            assert np.array_equal(ki, np.clip(knots, model.actuator_ctrlrange[:, 0], model.actuator_ctrlrange[:, 1]))
+        # an oracle "iteration" whose nominal is candidate i and whose only sample is the un-noised one
+        o.set_state(synthetic_state(model), 0.0); o.set_policy(times, ki, 2)
+        o.optimize(1, H, np.zeros((1, P, model.nu)))
+        oret, ofail = o.returns()
+        assert not ofail[0]
+        assert abs(ret[i] - oret[0]) <= 1e-8 * max(1.0, abs(oret[0])), (i, ret[i], oret[0])
+        checked += 1
+    assert checked >= 4
+    e.close()
