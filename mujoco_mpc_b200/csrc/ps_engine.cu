@@ -350,7 +350,7 @@ int ps_rollout_candidates(PsEngine* e, const double* knots, int n, int repetitio
   if (!e || !e->have_model || !e->have_task) return fail("ps_rollout_candidates: model and task must be set");
   if (e->P <= 0) return fail("ps_rollout_candidates: set the nominal plan (knot times) first");
   if (n < 1 || repetitions < 1 || H < 2 || H > 512) return fail("ps_rollout_candidates: bad sizes");
-  const Variant* run = !e->var->coop ? e->var : (e->var_large && !e->var_large->coop ? e->var_large : nullptr);
+  const Variant* run = e->var->robust ? e->var : (e->var_large && e->var_large->robust ? e->var_large : nullptr);
   if (!run) return fail("ps_rollout_candidates: force perturbations run on the dense thread-per-rollout kernel; create the engine with ps_set_engine_flavour(e, 3)");
   CU(cudaSetDevice(e->device));
   const int N = n * repetitions;
@@ -368,7 +368,7 @@ int ps_rollout_candidates(PsEngine* e, const double* knots, int n, int repetitio
   CU(cudaMemcpyAsync(e->d_knots, hk.data(), hk.size() * sizeof(double), cudaMemcpyHostToDevice, e->stream));
   const size_t zn = (size_t)(H - 1) * n6 * stride;
   std::vector<double> hz;
-  e->wb.xfrc_z = nullptr;
+  XfrcNoise xf{nullptr, 0.0, 0.0};
   if (xfrc_std > 0) {
     if (ensure(&e->d_xfrc, &e->xfrc_cap, zn)) return -1;
     if (z) {      // injected [N][H-1][6 nbody] -> device layout
@@ -380,15 +380,14 @@ int ps_rollout_candidates(PsEngine* e, const double* knots, int n, int repetitio
       normal_fill_kernel<<<blocks, threads, 0, e->stream>>>(e->d_xfrc, total, e->seed, e->iteration);
       e->launches++;
     }
-    e->wb.xfrc_z = e->d_xfrc;
-    e->wb.xfrc_rate = std::exp(-e->timestep / xfrc_rate);
-    e->wb.xfrc_scale = xfrc_std * std::sqrt(1 - e->wb.xfrc_rate * e->wb.xfrc_rate);
+    xf.z = e->d_xfrc;
+    xf.rate = std::exp(-e->timestep / xfrc_rate);
+    xf.scale = xfrc_std * std::sqrt(1 - xf.rate * xf.rate);
   }
   if (prepare_writeback(e, H, stride)) return -1;
   CU(cudaEventRecord(e->ev[0], e->stream)); CU(cudaEventRecord(e->ev[1], e->stream));
-  e->nblocks = run->launch(e->stream, dc, e->d_knots, stride, 0, N, 0LL, e->d_returns, e->d_failure, e->d_blockmin, e->wb, true, e->d_counter);
+  run->robust(e->stream, dc, e->d_knots, stride, N, e->d_returns, e->d_failure, e->wb, xf);
   CU(cudaEventRecord(e->ev[2], e->stream)); CU(cudaEventRecord(e->ev[3], e->stream));
-  e->wb.xfrc_z = nullptr;
   CU(cudaStreamSynchronize(e->stream));       // hk / hz are pageable host buffers
   CU(cudaGetLastError());
   e->launches += 1; e->iteration++;

@@ -103,4 +103,34 @@ rollout_kernel(const Constants<T>* __restrict__ gconst, const double* __restrict
   }
 }
 
+// ---------------------------------------------------------------- robust re-rolls
+// RobustPlanner's NoisyRollout (mjpc/trajectory.cc:100-210 with xfrc_std > 0): the same thread-per-rollout
+// recursion with full writeback plus Ornstein-Uhlenbeck forces on every body.  Its own kernel so that the
+// planning kernels above carry none of this; batches are candidates x repetitions, i.e. small.
+template <class T, int BLOCK>
+__global__ void __launch_bounds__(BLOCK)
+robust_rollout_kernel(const Constants<T>* __restrict__ gconst, const double* __restrict__ knots, int stride, int n,
+                      double* __restrict__ returns, unsigned char* __restrict__ failure, Writeback wb, XfrcNoise xf) {
+  __shared__ Constants<T> sc;
+  __shared__ alignas(8) uint64_t bar;
+  if (threadIdx.x == 0) { mbar_init(&bar, 1); asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    constexpr uint32_t total = (uint32_t)sizeof(Constants<T>);
+    mbar_expect_tx(&bar, total);
+    const char* src = reinterpret_cast<const char*>(gconst); char* dst = reinterpret_cast<char*>(&sc);
+    for (uint32_t off = 0; off < total; off += 32768u) {
+      const uint32_t sz = total - off < 32768u ? total - off : 32768u;
+      tma_bulk_g2s(dst + off, src + off, sz, &bar);
+    }
+  }
+  mbar_wait(&bar, 0);
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  int flags = 0;
+  const double total = rollout_sample<T, true, true>(sc.m, sc.t, sc.p, knots, stride, i, wb, &flags, &xf);
+  returns[i] = total;
+  failure[i] = (unsigned char)flags;
+}
+
 }  // namespace ps

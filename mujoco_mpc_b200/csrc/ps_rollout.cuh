@@ -14,15 +14,17 @@ struct alignas(128) Constants { DevModel<T> m; DevTask t; DevPlan<T> p; };
 // optional full-trajectory outputs, SoA [t][field][stride] with the sample index fastest
 struct Writeback {
   double* states; double* actions; double* residual; double* costs; double* times; double* trace;
-  // optional force perturbation: standard-normal tensor [(t * 6 nbody + k)][stride] and the discrete OU
-  // coefficients rate = exp(-dt / xfrc_rate), scale = xfrc_std sqrt(1 - rate^2) (trajectory.cc:149-151)
-  const double* xfrc_z; double xfrc_rate, xfrc_scale;
 };
 
+// Force perturbation of the robust re-rolls: standard-normal tensor [(t * 6 nbody + k)][stride] and the discrete
+// Ornstein-Uhlenbeck coefficients rate = exp(-dt / xfrc_rate), scale = xfrc_std sqrt(1 - rate^2) (trajectory.cc:149-151)
+struct XfrcNoise { const double* z; double rate, scale; };
+
 // knots: SoA [P*nu][stride]; i = this rollout's column.  flags: bit0 failure, bit1 capacity overflow
-template <class T, bool WB>
+// XF: apply Cartesian perturbation forces (own kernel instantiation: robust_rollout_kernel)
+template <class T, bool WB, bool XF = false>
 PS_FN double rollout_sample(const DevModel<T>& m, const DevTask& task, const DevPlan<T>& plan, const double* knots,
-                            int stride, int i, const Writeback& wb, int* flags) {
+                            int stride, int i, const Writeback& wb, int* flags, const XfrcNoise* xf = nullptr) {
   RolloutData<T> d;
   const int nq = nq_of(m), nv = nv_of(m), na = m.na, nu = m.nu, ns = nq + nv + na, nr = task.num_residual;
   const int H = plan.horizon, P = plan.num_spline_points, ntr = 3 * task.num_trace;
@@ -37,19 +39,22 @@ PS_FN double rollout_sample(const DevModel<T>& m, const DevTask& task, const Dev
   double residual[kMaxResidual];
   double sum = 0; bool failed = false;
   if (WB) { for (int k = 0; k < ns; k++) wb.states[(size_t)k * stride + i] = plan.state[k]; wb.times[i] = d.time; }
-  const bool xfrc = WB && wb.xfrc_z != nullptr;
-  if (WB) for (int k = 0; k < 6 * m.nbody; k++) d.xfrc_applied[k] = 0;
+  // Cartesian perturbation forces [force; torque] per body (mjData.xfrc_applied): writeback / robust-rollout
+  // instantiation only (RobustPlanner's Ornstein-Uhlenbeck noise, mjpc/trajectory.cc:147-155)
+  const bool xfrc = XF && xf && xf->z != nullptr;
+  double xfrc_applied[XF ? 6 * T::NBODY : 1];
+  if (XF) for (int k = 0; k < 6 * m.nbody; k++) xfrc_applied[k] = 0;
 
   for (int t = 0; t < H - 1; t++) {
     spline_sample(plan.spline_times, P, nu, plan.interpolation, d.time, kn, d.ctrl);
     for (int a = 0; a < nu; a++) d.ctrl[a] = clampd(d.ctrl[a], m.act_ctrlrange[2 * a], m.act_ctrlrange[2 * a + 1]);
     if (WB) for (int a = 0; a < nu; a++) wb.actions[((size_t)t * nu + a) * stride + i] = d.ctrl[a];
-    if (WB) if (xfrc) {
-      const int n6 = 6 * m.nbody; const double* zc = wb.xfrc_z + (size_t)t * n6 * stride + i;
-      for (int k = 0; k < n6; k++) d.xfrc_applied[k] = wb.xfrc_rate * d.xfrc_applied[k] + wb.xfrc_scale * zc[(size_t)k * stride];
+    if (XF) if (xfrc) {
+      const int n6 = 6 * m.nbody; const double* zc = xf->z + (size_t)t * n6 * stride + i;
+      for (int k = 0; k < n6; k++) xfrc_applied[k] = xf->rate * xfrc_applied[k] + xf->scale * zc[(size_t)k * stride];
     }
     if (state_is_bad(m, d)) { failed = true; break; }
-    forward_pass<T, WB>(m, d);
+    forward_pass<T, XF>(m, d, xfrc_applied);
     task_residual(m, d, task, residual);
     const double c = cost_value(task, residual);
     if (WB) {
@@ -75,7 +80,7 @@ PS_FN double rollout_sample(const DevModel<T>& m, const DevTask& task, const Dev
   if (!failed) {
     // terminal: ctrl is NOT rewritten before the final forward pass (trajectory.cc:190-198)
     if (WB && H > 1) for (int a = 0; a < nu; a++) wb.actions[((size_t)(H - 1) * nu + a) * stride + i] = d.ctrl[a];
-    forward_pass<T, WB>(m, d);
+    forward_pass<T, XF>(m, d, xfrc_applied);
     task_residual(m, d, task, residual);
     const double c = cost_value(task, residual);
     if (WB) {

@@ -392,13 +392,13 @@ PS_NT void actuation_stage(const DevModel<T>& m, RolloutData<T>& d) {
 }
 
 template <class T, bool XF = false>
-PS_NT void acceleration_stage(const DevModel<T>& m, RolloutData<T>& d) {
+PS_NT void acceleration_stage(const DevModel<T>& m, RolloutData<T>& d, const double* xfrc_applied = nullptr) {
   constexpr int S = T::NV; const int nv = nv_of(m);
   for (int i = 0; i < nv; i++) d.qfrc_smooth[i] = d.qfrc_passive[i] - d.qfrc_bias[i] + d.qfrc_actuator[i];
   if (XF) {      // mj_xfrcAccumulate: J(xipos_b, b)' [force; torque] for every body with a non-zero entry
     double jp[3 * S], jr[3 * S];
     for (int b = 1; b < m.nbody; b++) {
-      const double* x = d.xfrc_applied + 6 * b;
+      const double* x = xfrc_applied + 6 * b;
       if (x[0] == 0 && x[1] == 0 && x[2] == 0 && x[3] == 0 && x[4] == 0 && x[5] == 0) continue;
       point_jacobian(m, d, jp, jr, d.xipos + 3 * b, b);
       for (int c = 0; c < nv; c++)

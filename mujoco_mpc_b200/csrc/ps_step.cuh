@@ -66,14 +66,14 @@ PS_NT int read_sensor(const DevModel<T>& m, const D& d, int s, double* out) {
 // ---------------------------------------------------------------- forward pass
 // XF: the instantiation applies d.xfrc_applied (writeback / robust-rollout kernels only)
 template <class T, bool XF = false>
-PS_FN void forward_pass(const DevModel<T>& m, RolloutData<T>& d) {
+PS_FN void forward_pass(const DevModel<T>& m, RolloutData<T>& d, const double* xfrc_applied = nullptr) {
   position_smooth(m, d);
   make_constraints(m, d);
   velocity_stage(m, d);
   reference_acceleration(m, d);
   if (m.need_subtreevel) subtree_velocity(m, d);
   actuation_stage(m, d);
-  acceleration_stage<T, XF>(m, d);
+  acceleration_stage<T, XF>(m, d, xfrc_applied);
   constraint_stage(m, d);
 }
 

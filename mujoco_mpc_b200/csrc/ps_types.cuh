@@ -218,9 +218,6 @@ struct RolloutData {
   // solver scratch
   double sv_Ma[T::NV], sv_grad[T::NV], sv_search[T::NV], sv_Mv[T::NV], sv_H[T::NV * T::NV];
   double sv_Jaref[T::MAXEFC], sv_Jv[T::MAXEFC];
-  // Cartesian perturbation forces [force; torque] per body (mjData.xfrc_applied), written only by the
-  // writeback / robust-rollout kernels (RobustPlanner's Ornstein-Uhlenbeck noise, mjpc/trajectory.cc:147-155)
-  double xfrc_applied[6 * T::NBODY];
 };
 
 enum { WARN_BADQPOS = 1, WARN_BADQVEL = 2, WARN_BADQACC = 4, WARN_BADCTRL = 8, WARN_CAPACITY = 16 };

@@ -32,6 +32,15 @@ inline int launch_rollout(cudaStream_t st, const void* dconst, const double* kno
   return grid;
 }
 
+// force-perturbed re-rolls of candidate policies (dense thread-per-rollout instantiations only)
+template <class T, int BLOCK>
+inline int launch_robust(cudaStream_t st, const void* dconst, const double* knots, int stride, int n, double* returns,
+                         unsigned char* failure, Writeback wb, XfrcNoise xf) {
+  const int block = pick_block(n, BLOCK), grid = (n + block - 1) / block;
+  robust_rollout_kernel<T, BLOCK><<<grid, block, 0, st>>>(reinterpret_cast<const Constants<T>*>(dconst), knots, stride, n, returns, failure, wb, xf);
+  return grid;
+}
+
 // warp-per-rollout persistent launch: as many blocks as stay resident, WARPS rollouts in flight per block
 template <class T, int WARPS>
 inline int launch_coop(cudaStream_t st, const void* dconst, const double* knots, int stride, int first, int n,
@@ -83,21 +92,22 @@ struct Variant {
   void (*task)(void*, const DevTask&, int);
   int (*plan)(void*, const double*, int, const double*, int, double, const double*, int, int, int);
   int (*launch)(cudaStream_t, const void*, const double*, int, int, int, long long, double*, unsigned char*, MinLoc*, Writeback, bool, int*);
+  int (*robust)(cudaStream_t, const void*, const double*, int, int, double*, unsigned char*, Writeback, XfrcNoise);   // null: no force perturbations
 };
 template <class T, int BLOCK>
 inline Variant make_variant(const char* name) {
-  return Variant{name, sizeof(Constants<T>), BLOCK, false, T::LEAN, fill_model<T>, set_options<T>, set_debug<T>, set_task<T>, set_plan<T>, launch_rollout<T, BLOCK>};
+  return Variant{name, sizeof(Constants<T>), BLOCK, false, T::LEAN, fill_model<T>, set_options<T>, set_debug<T>, set_task<T>, set_plan<T>, launch_rollout<T, BLOCK>, launch_robust<T, BLOCK>};
 }
 template <class T, int WARPS>
 inline Variant make_coop_variant(const char* name) {
-  return Variant{name, sizeof(Constants<T>), WARPS * 32, true, true, fill_model<T>, set_options<T>, set_debug<T>, set_task<T>, set_plan<T>, launch_coop<T, WARPS>};
+  return Variant{name, sizeof(Constants<T>), WARPS * 32, true, true, fill_model<T>, set_options<T>, set_debug<T>, set_task<T>, set_plan<T>, launch_coop<T, WARPS>, nullptr};
 }
 const Variant* variant_tiny();
 const Variant* variant_planar();
 const Variant* variant_legged();
 template <class T, int BLOCK>
 inline Variant make_sparse_variant(const char* name) {
-  return Variant{name, sizeof(Constants<T>), BLOCK, true, true, fill_model<T>, set_options<T>, set_debug<T>, set_task<T>, set_plan<T>, launch_sparse<T, BLOCK>};
+  return Variant{name, sizeof(Constants<T>), BLOCK, true, true, fill_model<T>, set_options<T>, set_debug<T>, set_task<T>, set_plan<T>, launch_sparse<T, BLOCK>, nullptr};
 }
 const Variant* variant_planar_sparse();
 const Variant* variant_legged_sparse();

@@ -33,9 +33,11 @@ static int run(const PsModel* m, const PsTask* t, const PairList& pl, const doub
   std::vector<double> tm(H), tr((size_t)H * 3 * (t->num_trace ? t->num_trace : 1));
   Writeback wb{states, actions, residual, costs, tm.data(), tr.data()};
   (void)ns; (void)nr; (void)nu;
-  if (g_xfrc_z && g_xfrc_std > 0) {
-    wb.xfrc_z = g_xfrc_z; wb.xfrc_rate = std::exp(-k->m.timestep / g_xfrc_rate);
-    wb.xfrc_scale = g_xfrc_std * std::sqrt(1 - wb.xfrc_rate * wb.xfrc_rate);
+  if (g_xfrc_z && g_xfrc_std > 0) {      // the instantiation robust_rollout_kernel runs
+    XfrcNoise xf{g_xfrc_z, std::exp(-k->m.timestep / g_xfrc_rate), 0.0};
+    xf.scale = g_xfrc_std * std::sqrt(1 - xf.rate * xf.rate);
+    *total = rollout_sample<T, true, true>(k->m, k->t, k->p, knots, 1, 0, wb, flags, &xf);
+    return 0;
   }
   *total = rollout_sample<T, true>(k->m, k->t, k->p, knots, 1, 0, wb, flags);
   return 0;
