@@ -48,7 +48,7 @@ void CudaSamplingPlanner::Fail(const char* what) const {
 CudaSamplingPlanner::~CudaSamplingPlanner() { if (engine_) ps_destroy(engine_); }
 
 void CudaSamplingPlanner::Initialize(const PsModel* model, const PsTask* task, int device_ordinal) {
-  model_ = model; task_ = *task;
+  model_ = model; task_ = *task; device_ = device_ordinal;
   noise_exploration[0] = NumberOrDefault(0.1, model, "sampling_exploration");
   noise_exploration[1] = 0.0;
   const int se = FindNumeric(model, "sampling_exploration");

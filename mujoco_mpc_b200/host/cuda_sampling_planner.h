@@ -66,6 +66,10 @@ class CudaSamplingPlanner {
   void SetSeed(unsigned long long seed);
   void SetSharding(int rank, int world, AllGatherFn fn, void* ctx);       // samples [rank*N, (rank+1)*N) of world*N
   PsEngine* engine() { return engine_; }
+  const SamplingPolicy& CandidatePolicy(int candidate) const { return ranked_[candidate]; }   // candidate_policy[trajectory_order[c]]
+  const PsModel* model() const { return model_; }
+  const PsTask& task() const { return task_; }
+  int device() const { return device_; }
 
   // ---- public members the reference exposes (sampling/planner.h:115-162)
   SamplingPolicy policy, previous_policy;
@@ -81,7 +85,7 @@ class CudaSamplingPlanner {
  private:
   void UpdateNominalPolicy(int horizon);                                              // :236-310
   void Fail(const char* what) const;
-  const PsModel* model_ = nullptr; PsTask task_{}; PsEngine* engine_ = nullptr;
+  const PsModel* model_ = nullptr; PsTask task_{}; PsEngine* engine_ = nullptr; int device_ = 0;
   SamplingPolicy candidate_winner_;          // candidate_policy[winner] of the last iteration
   std::vector<SamplingPolicy> ranked_;       // candidate policies of the last OptimizePolicyCandidates, best first
   std::vector<double> ranked_score_; std::vector<int> trajectory_order;

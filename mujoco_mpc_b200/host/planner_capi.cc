@@ -1,6 +1,8 @@
 // extern "C" surface over CudaSamplingPlanner for language bindings (tests/, bench.py use it via
 // ctypes).  House style follows the reference's own C plugin ABI, mjpc/interface.cc:77-115.
+#include <algorithm>
 #include <cstring>
+#include <memory>
 #include "cuda_sampling_planner.h"
 
 using mjpc_b200::CudaSamplingPlanner;
@@ -160,5 +162,66 @@ void pce_timers(void* h, double* noise_us, double* rollouts_us, double* policy_u
   *noise_us = p->noise_compute_time; *rollouts_us = p->rollouts_compute_time; *policy_update_us = p->policy_update_compute_time;
 }
 void* pce_engine(void* h) { return ((CudaCrossEntropyPlanner*)h)->engine(); }
+
+}  // extern "C"
+
+// ---- CudaRobustPlanner
+#include "cuda_robust_planner.h"
+using mjpc_b200::CudaRobustPlanner;
+
+extern "C" {
+
+// parity runs start from a given nominal spline instead of the Reset() one
+void psp_set_policy(void* h, const double* times, const double* knots, int P, int interpolation) {
+  CudaSamplingPlanner* p = (CudaSamplingPlanner*)h;
+  p->interpolation_ = interpolation;
+  p->policy.plan = mjpc_b200::TimeSpline(p->model()->nu, (mjpc_b200::SplineInterpolation)interpolation);
+  for (int k = 0; k < P; k++) p->policy.plan.AddNode(times[k], knots + (size_t)k * p->model()->nu);
+}
+
+void* prb_create(const PsModel* model, const PsTask* task, int device) {
+  CudaRobustPlanner* p = new CudaRobustPlanner(std::make_unique<CudaSamplingPlanner>());
+  p->Initialize(model, task, device); p->Allocate(); p->Reset(mjpc_b200::kMaxTrajectoryHorizon);
+  return p;
+}
+void prb_destroy(void* h) { delete (CudaRobustPlanner*)h; }
+void* prb_delegate(void* h) { return ((CudaRobustPlanner*)h)->delegate(); }      // a psp_* handle owned by the robust planner
+void* prb_engine(void* h) { return ((CudaRobustPlanner*)h)->engine(); }
+void prb_reset(void* h, int horizon, const double* initial_repeated_action) { ((CudaRobustPlanner*)h)->Reset(horizon, initial_repeated_action); }
+void prb_set_state(void* h, const double* state, const double* mocap, const double* userdata, double time) {
+  ((CudaRobustPlanner*)h)->SetState(state, mocap, userdata, time);
+}
+void prb_set_task(void* h, const PsTask* t) { ((CudaRobustPlanner*)h)->SetTask(t); }
+// negative / zero arguments keep the value read from the model's numerics
+void prb_configure(void* h, int ncandidates, int nrepetitions, double xfrc_std, double xfrc_rate) {
+  CudaRobustPlanner* p = (CudaRobustPlanner*)h;
+  if (ncandidates > 0) p->ncandidates_ = ncandidates;
+  if (nrepetitions > 0) p->nrepetitions_ = nrepetitions;
+  if (xfrc_std >= 0) p->xfrc_std_ = xfrc_std;
+  if (xfrc_rate > 0) p->xfrc_rate_ = xfrc_rate;
+}
+void prb_get_settings(void* h, int* ncandidates, int* nrepetitions, double* xfrc_std, double* xfrc_rate) {
+  CudaRobustPlanner* p = (CudaRobustPlanner*)h;
+  *ncandidates = p->ncandidates_; *nrepetitions = p->nrepetitions_; *xfrc_std = p->xfrc_std_; *xfrc_rate = p->xfrc_rate_;
+}
+void prb_set_force_noise(void* h, const double* z, int rollouts, int horizon) { ((CudaRobustPlanner*)h)->SetForceNoise(z, rollouts, horizon); }
+void prb_set_seed(void* h, unsigned long long seed) { ((CudaRobustPlanner*)h)->SetSeed(seed); }
+void prb_optimize_policy(void* h, int horizon) { ((CudaRobustPlanner*)h)->OptimizePolicy(horizon); }
+void prb_nominal_trajectory(void* h, int horizon) { ((CudaRobustPlanner*)h)->NominalTrajectory(horizon); }
+void prb_action_from_policy(void* h, double* action, double time, int use_previous) {
+  ((CudaRobustPlanner*)h)->ActionFromPolicy(action, nullptr, time, use_previous != 0);
+}
+int prb_best_candidate(void* h) { return ((CudaRobustPlanner*)h)->best_candidate; }
+// scores[ncandidates], noisy returns / failure [ncandidates][nrepetitions]; returns the number of candidates scored
+int prb_results(void* h, double* scores, double* noisy_return, unsigned char* noisy_failure, int cap_candidates) {
+  CudaRobustPlanner* p = (CudaRobustPlanner*)h;
+  const int n = std::min((int)p->candidate_score.size(), cap_candidates);
+  const int rep = n ? (int)(p->noisy_return.size() / p->candidate_score.size()) : 0;
+  if (scores) std::memcpy(scores, p->candidate_score.data(), sizeof(double) * n);
+  if (noisy_return) std::memcpy(noisy_return, p->noisy_return.data(), sizeof(double) * n * rep);
+  if (noisy_failure) std::memcpy(noisy_failure, p->noisy_failure.data(), (size_t)n * rep);
+  return n;
+}
+double prb_noisy_rollouts_us(void* h) { return ((CudaRobustPlanner*)h)->noisy_rollouts_compute_time; }
 
 }  // extern "C"

@@ -264,3 +264,110 @@ class CudaCrossEntropyPlanner:
 
     def engine_ptr(self):
         return self.L.pce_engine(self.h)
+
+
+class _Delegate(CudaSamplingPlanner):
+    """The CudaSamplingPlanner a CudaRobustPlanner wraps: same methods, handle owned by the robust planner."""
+
+    def __init__(self, L, model, task, handle):
+        self.L, self.model, self.task = L, model, task
+        self.h = ctypes.c_void_p(handle)
+        self.ns = model.nq + model.nv + model.na
+        self._cb = None
+        self.horizon = 0
+
+    def set_policy(self, times, knots, interp):
+        t = _arr(times); k = _arr(knots)
+        self.L.psp_set_policy(self.h, _p(t), _p(k), len(t), int(interp))
+
+    def close(self):
+        self.h = None
+
+
+class CudaRobustPlanner:
+    """ctypes binding of mjpc_b200::CudaRobustPlanner (drop-in for mjpc::RobustPlanner,
+    mjpc/planners/robust/robust_planner.h): the delegate's best candidates re-rolled under random body forces
+    in one launch of the force-perturbed rollout kernel; the lowest mean return is kept."""
+
+    def __init__(self, model, task, device=0):
+        self.L = lib()
+        for f in ("prb_create", "prb_delegate", "prb_engine"):
+            getattr(self.L, f).restype = ctypes.c_void_p
+        self.L.prb_noisy_rollouts_us.restype = ctypes.c_double
+        self.model, self.task = model, task
+        self.h = ctypes.c_void_p(self.L.prb_create(ctypes.byref(model.c_struct()), ctypes.byref(task), device))
+        self.delegate = _Delegate(self.L, model, task, self.L.prb_delegate(self.h))
+        self.horizon = 0
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.delegate.close()
+            self.L.prb_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def Reset(self, horizon, initial_repeated_action=None):
+        a = _arr(initial_repeated_action) if initial_repeated_action is not None else None
+        self.L.prb_reset(self.h, horizon, _p(a))
+
+    def configure(self, ncandidates=-1, nrepetitions=-1, xfrc_std=-1.0, xfrc_rate=-1.0):
+        self.L.prb_configure(self.h, ncandidates, nrepetitions, ctypes.c_double(xfrc_std), ctypes.c_double(xfrc_rate))
+
+    def settings(self):
+        a, b, c, d = ctypes.c_int(), ctypes.c_int(), ctypes.c_double(), ctypes.c_double()
+        self.L.prb_get_settings(self.h, ctypes.byref(a), ctypes.byref(b), ctypes.byref(c), ctypes.byref(d))
+        return dict(ncandidates=a.value, nrepetitions=b.value, xfrc_std=c.value, xfrc_rate=d.value)
+
+    def SetState(self, state, time, mocap=None, userdata=None):
+        s = _arr(state); mo = _arr(mocap) if mocap is not None else None; ud = _arr(userdata) if userdata is not None else None
+        self.L.prb_set_state(self.h, _p(s), _p(mo), _p(ud), ctypes.c_double(time))
+
+    def SetTask(self, task):
+        self.task = task; self.delegate.task = task
+        self.L.prb_set_task(self.h, ctypes.byref(task))
+
+    def SetForceNoise(self, z, horizon):
+        """z: N(0,1) tensor [ncandidates * nrepetitions][horizon - 1][6 * nbody] (parity runs); None = device generator"""
+        if z is None:
+            self.L.prb_set_force_noise(self.h, None, 0, 0); return
+        z = _arr(z); self.L.prb_set_force_noise(self.h, _p(z), z.shape[0], horizon)
+
+    def SetSeed(self, seed):
+        self.L.prb_set_seed(self.h, ctypes.c_ulonglong(seed))
+
+    def OptimizePolicy(self, horizon):
+        self.horizon = self.delegate.horizon = horizon
+        self.L.prb_optimize_policy(self.h, horizon)
+
+    def NominalTrajectory(self, horizon):
+        self.horizon = self.delegate.horizon = horizon
+        self.L.prb_nominal_trajectory(self.h, horizon)
+
+    def ActionFromPolicy(self, time, use_previous=False):
+        a = np.zeros(max(self.model.nu, 1)); self.L.prb_action_from_policy(self.h, _p(a), ctypes.c_double(time), int(use_previous))
+        return a[:self.model.nu]
+
+    def BestTrajectory(self):
+        return self.delegate.BestTrajectory()
+
+    def NumParameters(self):
+        return self.delegate.NumParameters()
+
+    def policy(self, previous=False):
+        return self.delegate.policy(previous)
+
+    @property
+    def best_candidate(self):
+        return self.L.prb_best_candidate(self.h)
+
+    def results(self):
+        s = self.settings(); nc, rep = max(s["ncandidates"], 1), s["nrepetitions"]
+        scores = np.zeros(nc); ret = np.zeros(nc * rep); fail = np.zeros(nc * rep, dtype=np.uint8)
+        n = self.L.prb_results(self.h, _p(scores), _p(ret), fail.ctypes.data_as(ctypes.POINTER(ctypes.c_ubyte)), nc)
+        return dict(scores=scores[:n], noisy_returns=ret[:n * rep].reshape(n, rep), noisy_failure=fail[:n * rep].reshape(n, rep),
+                    noisy_rollouts_us=self.L.prb_noisy_rollouts_us(self.h))

@@ -57,3 +57,15 @@ def test_task_models_compile(name, nq, nv, nu, na):
     assert s["steps"] == int(s["horizon"] / s["timestep"] + 1)
     M = np.asarray(m.dof_invweight0)
     assert np.all(M > 0)
+
+
+def test_planner_library_exports_every_wrapper(englib):
+    # the host planner classes (sampling / cross-entropy / robust) behind their extern "C" wrappers
+    from mujoco_mpc_b200 import build, planner
+    build.build_host()
+    src = open(os.path.join(ROOT, "mujoco_mpc_b200", "host", "planner_capi.cc")).read()
+    names = set(re.findall(r"^(?:void\*?|int|double)\s+(p(?:sp|ce|rb)_[a-z0-9_]+)\s*\(", src, flags=re.M))
+    assert {"psp_create", "pce_create", "prb_create", "prb_optimize_policy", "prb_results", "psp_set_policy"} <= names
+    L = planner.lib()
+    for n in sorted(names):
+        assert hasattr(L, n), n

@@ -86,3 +86,76 @@ def test_zero_force_noise_repeats_the_clean_return(oracle_lib):
     ret, _ = o.returns()
     for c in range(ncand):
         assert np.all(out["noisy_returns"][c] == ret[out["order"][c]])
+
+
+# ---- GPU: the host class over the engine.  Written after this round's GPU minutes were spent; not yet run on
+# hardware, so a failure is reported as xfail and a pass as XPASS (the device rollout code itself is pinned by the
+# hostsim tests above).
+_unverified = pytest.mark.xfail(strict=False, reason="not yet run on a B200 (GPU budget of the round exhausted)")
+
+
+@pytest.mark.gpu
+@_unverified
+@pytest.mark.parametrize("name,H,std", [("Cartpole", 41, 0.5), ("Walker", 31, 2.0), ("Quadruped Flat", 26, 1.0)])
+def test_cuda_robust_planner_matches_oracle(oracle_lib, name, H, std):
+    from mujoco_mpc_b200.planner import CudaRobustPlanner
+    N, ncand, reps, rate = 64, 6, 4, 0.1
+    model, task, s, o, out, state, z, w, nominal, interp = setup(name, N, H, ncand, reps, std, rate, seed=12)
+    P = len(nominal[0])
+    pl = CudaRobustPlanner(model, task)
+    pl.configure(ncandidates=ncand, nrepetitions=reps, xfrc_std=std, xfrc_rate=rate)
+    pl.delegate.configure(num_trajectory=N, interpolation=interp, num_spline_points=P, sigma0=s["exploration"], sigma1=0.0)
+    pl.delegate.set_policy(nominal[0], nominal[1], interp)
+    pl.delegate.SetNoise(z)
+    pl.SetForceNoise(w, H)
+    pl.SetState(state, 0.0)
+    pl.OptimizePolicy(H)
+    r = pl.results()
+    ret, _ = o.returns()
+    # the delegate's ranking and clean scores
+    for c in range(ncand):
+        assert abs(pl.delegate.CandidateScore(c) - ret[out["order"][c]]) <= 1e-8 * max(1.0, abs(ret[out["order"][c]]))
+    assert np.array_equal((r["noisy_failure"] & 1).astype(bool), out["noisy_failure"].astype(bool))
+    ok = ~out["noisy_failure"].astype(bool)
+    assert np.allclose(r["noisy_returns"][ok], out["noisy_returns"][ok], rtol=1e-8, atol=1e-8)
+    assert np.allclose(r["scores"], out["scores"], rtol=1e-8, atol=1e-8)
+    assert pl.best_candidate == out["best"]
+    pt, pk = pl.policy(); ot, ok_ = o.policy(0)
+    assert np.array_equal(pt, ot) and np.allclose(pk, ok_, rtol=0, atol=1e-12)
+    assert pl.delegate.winner == out["order"][out["best"]]
+    pl.close()
+
+
+@pytest.mark.gpu
+@_unverified
+def test_cuda_robust_planner_device_noise_and_settings():
+    from mujoco_mpc_b200.planner import CudaRobustPlanner
+    model, task, s = registry.load("Cartpole")
+    pl = CudaRobustPlanner(model, task)
+    st = pl.settings()
+    # robust_planner.cc:48-57: defaults when the model has no robust_* numerics
+    assert st["nrepetitions"] == 5 and st["xfrc_std"] == 0.1 and st["xfrc_rate"] == 0.1
+    assert st["ncandidates"] == s["num_trajectory"] // 5
+    pl.configure(ncandidates=8, nrepetitions=3, xfrc_std=1.0)
+    pl.delegate.configure(num_trajectory=256)
+    pl.SetSeed(5)
+    pl.Reset(s["steps"], np.zeros(model.nu))
+    state = synthetic_state(model)
+    H = 51
+    costs = []
+    for k in range(4):
+        pl.SetState(state, 0.0)
+        pl.OptimizePolicy(H)
+        r = pl.results()
+        assert r["scores"].shape == (8,) and r["noisy_returns"].shape == (8, 3)
+        assert 0 <= pl.best_candidate < 8 and pl.best_candidate == int(np.argmin(r["scores"]))
+        # repetitions of one candidate see different forces
+        assert len(np.unique(r["noisy_returns"][0])) == 3
+        costs.append(r["scores"].min())
+    # one candidate: no re-rolls, the delegate's winner is taken
+    pl.configure(ncandidates=1)
+    pl.SetState(state, 0.0); pl.OptimizePolicy(H)
+    assert pl.best_candidate == 0 and pl.results()["scores"].size == 0
+    a = pl.ActionFromPolicy(0.0)
+    assert np.all(a >= model.actuator_ctrlrange[:, 0]) and np.all(a <= model.actuator_ctrlrange[:, 1])
+    pl.close()
