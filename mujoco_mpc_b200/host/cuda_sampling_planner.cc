@@ -86,7 +86,7 @@ void CudaSamplingPlanner::Reset(int /*horizon*/, const double* initial_repeated_
     p->plan.Clear();
     if (initial_repeated_action) p->plan.AddNode(0, initial_repeated_action);   // policy.cc:44-49
   }
-  ranked_.clear(); ranked_score_.clear(); trajectory_order.clear();
+  ranked_.clear(); ranked_score_.clear(); trajectory_order.clear(); ranked_local_.clear();
   improvement = 0.0; winner = 0; best_valid_ = false;
 }
 
@@ -192,7 +192,7 @@ int CudaSamplingPlanner::OptimizePolicyCandidates(int ncandidates, int horizon) 
     winner_is_local_ = best == rank_;
   }
   nominal_return_ = nret; winner_return_ = wret;
-  ranked_.clear(); ranked_score_.clear(); trajectory_order.clear();
+  ranked_.clear(); ranked_score_.clear(); trajectory_order.clear(); ranked_local_.clear();
   auto make_policy = [&](const double* knots) {
     SamplingPolicy p; p.model = model_; p.num_spline_points = policy.num_spline_points;
     p.plan = TimeSpline(nu, (SplineInterpolation)interpolation_);
@@ -200,6 +200,7 @@ int CudaSamplingPlanner::OptimizePolicyCandidates(int ncandidates, int horizon) 
     return p;
   };
   trajectory_order.push_back((int)global_winner); ranked_.push_back(make_policy(rec.data() + 3)); ranked_score_.push_back(wret);
+  ranked_local_.push_back(winner_is_local_ ? local_winner : -1);
   if (ncandidates > 1) {
     // top-k beyond the argmin: rank the per-sample returns on the host (single-rank only; RobustPlanner path)
     std::vector<double> ret(num_trajectory);
@@ -211,6 +212,7 @@ int CudaSamplingPlanner::OptimizePolicyCandidates(int ncandidates, int horizon) 
     for (int c = 1; c < ncandidates; c++) {
       if (ps_get_knots(engine_, order[c], knots.data())) Fail("ps_get_knots");
       trajectory_order.push_back(order[c] + rank_ * num_trajectory); ranked_.push_back(make_policy(knots.data())); ranked_score_.push_back(ret[order[c]]);
+      ranked_local_.push_back(order[c]);
     }
   }
   rollouts_compute_time = Micros(rollouts_start);
@@ -238,6 +240,12 @@ void CudaSamplingPlanner::ActionFromCandidatePolicy(double* action, int candidat
 // planner.cc:525-534
 void CudaSamplingPlanner::CopyCandidateToPolicy(int candidate) {
   winner = trajectory_order[candidate];
+  // BestTrajectory() is trajectory[winner] (planner.cc:383-385): follow the candidate that was picked
+  if (candidate < (int)ranked_local_.size() && ranked_local_[candidate] != local_winner_) {
+    winner_is_local_ = ranked_local_[candidate] >= 0;
+    if (winner_is_local_) local_winner_ = ranked_local_[candidate];
+    best_valid_ = false;
+  }
   std::unique_lock<std::shared_mutex> lock(mtx_);
   previous_policy = policy;
   policy = ranked_[candidate];

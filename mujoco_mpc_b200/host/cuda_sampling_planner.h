@@ -89,6 +89,7 @@ class CudaSamplingPlanner {
   SamplingPolicy candidate_winner_;          // candidate_policy[winner] of the last iteration
   std::vector<SamplingPolicy> ranked_;       // candidate policies of the last OptimizePolicyCandidates, best first
   std::vector<double> ranked_score_; std::vector<int> trajectory_order;
+  std::vector<int> ranked_local_;            // local sample index of each candidate (-1: lives on another rank)
   Trajectory best_; bool best_valid_ = false; int last_horizon_ = 0;
   double nominal_return_ = 0, winner_return_ = 0;
   int rank_ = 0, world_ = 1; AllGatherFn gather_ = nullptr; void* gather_ctx_ = nullptr;

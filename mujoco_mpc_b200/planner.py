@@ -17,13 +17,17 @@ def lib():
         if not os.path.exists(LIB_PATH):
             raise RuntimeError(f"{LIB_PATH} not built (python -c 'from mujoco_mpc_b200 import build; build.build(); build.build_host()')")
         ctypes.CDLL(os.path.join(_HERE, "libps_engine.so"), mode=ctypes.RTLD_GLOBAL)
-        L = ctypes.CDLL(LIB_PATH)
-        L.psp_create.restype = ctypes.c_void_p
-        L.psp_engine.restype = ctypes.c_void_p
-        L.psp_candidate_score.restype = ctypes.c_double
-        L.psp_improvement.restype = ctypes.c_double
-        _LIB = L
+        _LIB = prototype(ctypes.CDLL(LIB_PATH))
     return _LIB
+
+
+def prototype(L):
+    """return types of the psp_* wrappers (also used by the CPU test-suite on its host-compiled build of the classes)"""
+    L.psp_create.restype = ctypes.c_void_p
+    L.psp_engine.restype = ctypes.c_void_p
+    L.psp_candidate_score.restype = ctypes.c_double
+    L.psp_improvement.restype = ctypes.c_double
+    return L
 
 
 def _p(a):

@@ -18,3 +18,14 @@ def oracle_iteration(model, task, settings, state, time, N, H, P, interp, sigma,
     w = o.optimize(N, H, z, nthread=nthread)
     nt, nk = o.policy(1)      # previous_policy = the resampled nominal of this iteration
     return o, nt, nk, w
+
+
+def model_mocap(model):
+    """mocap pose [nmocap][7] of the model as loaded (what mjData holds after mj_resetData)"""
+    out = np.zeros((max(model.nmocap, 0), 7))
+    for b in range(model.nbody):
+        i = int(model.body_mocapid[b])
+        if i >= 0:
+            out[i, :3] = np.asarray(model.body_pos).reshape(-1, 3)[b]
+            out[i, 3:] = np.asarray(model.body_quat).reshape(-1, 4)[b]
+    return out.reshape(-1) if model.nmocap else None

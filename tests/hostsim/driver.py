@@ -21,6 +21,24 @@ def build(force=False):
     return _LIB
 
 
+def build_planner_host(force=False):
+    """libps_planner_host.so: the product's host planner classes (mujoco_mpc_b200/host/*.cc, unchanged) linked
+    against hostengine.cc, the host-compiled stand-in of the engine ABI.  -Bsymbolic keeps its ps_* references
+    inside the library even when the real libps_engine.so is loaded in the same process."""
+    hdir = os.path.join(_HERE, "..", "..", "mujoco_mpc_b200", "host")
+    out = os.path.join(_HERE, "libps_planner_host.so")
+    srcs = [os.path.join(_HERE, "hostengine.cc")] + [os.path.join(hdir, f) for f in sorted(os.listdir(hdir)) if f.endswith(".cc")]
+    deps = srcs + [os.path.join(hdir, f) for f in os.listdir(hdir) if f.endswith(".h")] + \
+        [os.path.join(_CSRC, f) for f in os.listdir(_CSRC) if f.endswith((".cuh", ".h"))]
+    if not force and os.path.exists(out) and all(os.path.getmtime(out) >= os.path.getmtime(d) for d in deps):
+        return out
+    cmd = ["g++", "-std=c++17", "-O2", "-ffp-contract=off", "-fPIC", "-shared", "-Wl,-Bsymbolic", "-o", out]
+    for s in srcs:
+        cmd += ["-x", "c++", s]
+    subprocess.run(cmd + ["-lpthread"], check=True)
+    return out
+
+
 def _p(a):
     return a.ctypes.data_as(ctypes.POINTER(ctypes.c_double))
 

@@ -1,0 +1,121 @@
+"""The product's host planner classes (mujoco_mpc_b200/host/*.cc: CudaSamplingPlanner, CudaRobustPlanner),
+compiled unchanged and linked against tests/hostsim/hostengine.cc -- a host-compiled stand-in for the engine
+ABI whose rollouts are the engine's own kernel-source headers run through g++ -- against the oracle.
+
+This is what can be said on a machine without a GPU about the host control flow: knot times and resampling,
+candidate ranking, the layout of what is handed to ps_rollout_candidates, the running-mean selection and which
+trajectory BestTrajectory() returns.  The CUDA launches themselves are covered by the `-m gpu` tests."""
+import ctypes
+import numpy as np
+import pytest
+from mujoco_mpc_b200 import planner, registry, task as T
+from oracle import pyoracle
+from tests.common import model_mocap, synthetic_state
+from tests.hostsim import driver
+
+
+@pytest.fixture()
+def hostlib(oracle_lib, monkeypatch):
+    L = planner.prototype(ctypes.CDLL(driver.build_planner_host()))
+    monkeypatch.setattr(planner, "_LIB", L)
+    return L
+
+
+def case(name, N, H, seed):
+    model, task, s = registry.load(name)
+    if name.startswith("Quadruped"):
+        T.quadruped_snapshot(model, task, mode="Quadruped", gait="Trot", time=0.2)
+    P, interp = min(s["num_spline_points"], 36), 2
+    rng = np.random.default_rng(seed)
+    z = rng.standard_normal((N, P, model.nu))
+    shift = max((H - 1) * s["timestep"] / (P - 1), 1e-5)
+    times = np.array([k * shift for k in range(P)])
+    half = 0.5 * (model.actuator_ctrlrange[:, 1] - model.actuator_ctrlrange[:, 0])
+    knots = 0.2 * half * rng.standard_normal((P, model.nu))
+    return model, task, s, P, interp, z, times, knots, synthetic_state(model), rng
+
+
+@pytest.mark.parametrize("name,H", [("Cartpole", 31), ("Walker", 21)])
+def test_sampling_planner_iterations_match_oracle(hostlib, name, H):
+    N = 10
+    model, task, s, P, interp, z, times, knots, state, rng = case(name, N, H, seed=21)
+    o = pyoracle.Oracle(model, task); o.configure(P, interp, s["exploration"])
+    pl = planner.CudaSamplingPlanner(model, task)
+    pl.configure(num_trajectory=N, interpolation=interp, num_spline_points=P, sigma0=s["exploration"], sigma1=0.0)
+    pl.Reset(H, np.zeros(model.nu)); o.set_policy(np.zeros(1), np.zeros((1, model.nu)), interp)      # Reset(): one knot at t = 0
+    t = 0.0
+    for it in range(3):                       # three planning iterations: resampling of the previous winner included
+        zi = rng.standard_normal((N, P, model.nu))
+        o.set_state(state, t); ow = o.optimize(N, H, zi)
+        pl.SetNoise(zi); pl.SetState(state, t); pl.OptimizePolicy(H)
+        ret, _ = o.returns()
+        assert pl.winner == ow
+        ot, ok = o.policy(0); pt, pk = pl.policy()
+        assert np.array_equal(ot, pt) and np.array_equal(ok, pk), (name, it)
+        assert pl.improvement == o.improvement()
+        bt = pl.BestTrajectory()
+        assert bt["total_return"] == ret[ow]
+        for tq in (t, t + 0.37 * (H - 1) * s["timestep"]):
+            assert np.array_equal(pl.ActionFromPolicy(tq), o.action(tq))
+        t += 3 * s["timestep"]
+    pl.close()
+
+
+@pytest.mark.parametrize("name,H,std", [("Cartpole", 31, 0.5), ("Walker", 21, 2.0), ("Quadruped Flat", 16, 1.0)])
+def test_robust_planner_matches_oracle(hostlib, name, H, std):
+    N, ncand, reps, rate = 12, 4, 3, 0.1
+    model, task, s, P, interp, z, times, knots, state, rng = case(name, N, H, seed=33)
+    w = rng.standard_normal((ncand * reps, H - 1, 6 * model.nbody))
+    o = pyoracle.Oracle(model, task); o.configure(P, interp, s["exploration"])
+    mocap = model_mocap(model)
+    o.set_state(state, 0.0, mocap=mocap); o.set_policy(times, knots, interp)
+    out = o.robust_optimize(N, H, z, ncand, reps, w, std, rate)
+    ret, _ = o.returns()
+
+    pl = planner.CudaRobustPlanner(model, task)
+    pl.configure(ncandidates=ncand, nrepetitions=reps, xfrc_std=std, xfrc_rate=rate)
+    pl.delegate.configure(num_trajectory=N, interpolation=interp, num_spline_points=P, sigma0=s["exploration"], sigma1=0.0)
+    pl.delegate.set_policy(times, knots, interp)
+    pl.delegate.SetNoise(z)
+    pl.SetForceNoise(w, H)
+    pl.SetState(state, 0.0, mocap=mocap)
+    pl.OptimizePolicy(H)
+    r = pl.results()
+    for c in range(ncand):
+        assert pl.delegate.CandidateScore(c) == ret[out["order"][c]]
+    assert np.array_equal((r["noisy_failure"] & 1).astype(bool), out["noisy_failure"].astype(bool))
+    ok = ~out["noisy_failure"].astype(bool)
+    assert np.array_equal(r["noisy_returns"][ok], out["noisy_returns"][ok])
+    assert np.array_equal(r["scores"], out["scores"])
+    assert pl.best_candidate == out["best"]
+    assert pl.delegate.winner == out["order"][out["best"]]
+    pt, pk = pl.policy(); ot, okn = o.policy(0)
+    assert np.array_equal(pt, ot) and np.array_equal(pk, okn)
+    assert np.array_equal(pt, times)                     # OptimizePolicyCandidates does not re-time the plan
+    # BestTrajectory() is the delegate's clean rollout of the candidate that was picked
+    bt = pl.BestTrajectory()
+    assert bt["total_return"] == ret[out["order"][out["best"]]]
+    pl.close()
+
+
+def test_robust_planner_settings_and_single_candidate(hostlib):
+    model, task, s = registry.load("Cartpole")
+    pl = planner.CudaRobustPlanner(model, task)
+    st = pl.settings()
+    # robust_planner.cc:48-57: defaults when the model carries no robust_* numerics
+    assert st["nrepetitions"] == 5 and st["xfrc_std"] == 0.1 and st["xfrc_rate"] == 0.1
+    assert st["ncandidates"] == s["num_trajectory"] // 5
+    N, H, P = 6, 21, 1
+    pl.configure(ncandidates=1)
+    pl.delegate.configure(num_trajectory=N)
+    pl.Reset(H, np.zeros(model.nu))                   # one knot at t = 0: the plan RobustPlanner keeps (it never resamples)
+    z = np.random.default_rng(2).standard_normal((N, P, model.nu))
+    pl.delegate.SetNoise(z)
+    pl.SetState(synthetic_state(model), 0.0)
+    pl.OptimizePolicy(H)
+    assert pl.best_candidate == 0 and pl.results()["scores"].size == 0
+    t, k = pl.policy()
+    assert len(t) == 1 and t[0] == 0.0
+    a = pl.ActionFromPolicy(0.3)
+    assert np.array_equal(a, np.clip(k[0], model.actuator_ctrlrange[:, 0], model.actuator_ctrlrange[:, 1]))
+    pl.close()

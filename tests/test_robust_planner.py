@@ -9,7 +9,7 @@ import numpy as np
 import pytest
 from mujoco_mpc_b200 import registry, task as T
 from oracle import pyoracle
-from tests.common import synthetic_state
+from tests.common import model_mocap, synthetic_state
 from tests.hostsim import driver
 
 
@@ -32,7 +32,7 @@ def setup(name, N, H, ncand, reps, std, rate, seed=3):
     times = np.array([k * shift for k in range(P)])
     half = 0.5 * (model.actuator_ctrlrange[:, 1] - model.actuator_ctrlrange[:, 0])
     knots = 0.2 * half * rng.standard_normal((P, model.nu))
-    o.set_state(state, 0.0); o.set_policy(times, knots, interp)
+    o.set_state(state, 0.0, mocap=model_mocap(model)); o.set_policy(times, knots, interp)
     out = o.robust_optimize(N, H, z, ncand, reps, w, std, rate)
     return model, task, s, o, out, state, z, w, (times, knots), interp
 
@@ -108,7 +108,7 @@ def test_cuda_robust_planner_matches_oracle(oracle_lib, name, H, std):
     pl.delegate.set_policy(nominal[0], nominal[1], interp)
     pl.delegate.SetNoise(z)
     pl.SetForceNoise(w, H)
-    pl.SetState(state, 0.0)
+    pl.SetState(state, 0.0, mocap=model_mocap(model))
     pl.OptimizePolicy(H)
     r = pl.results()
     ret, _ = o.returns()
