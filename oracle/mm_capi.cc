@@ -71,6 +71,7 @@ void mmo_planner_config(void* hp, int num_spline_points, int interpolation, doub
   Planner& p = ((Handle*)hp)->pl; p.num_spline_points = num_spline_points; p.interpolation = interpolation;
   p.noise_exploration[0] = s0; p.noise_exploration[1] = s1;
 }
+void mmo_set_sliding_plan(void* hp, int on) { ((Handle*)hp)->pl.sliding_plan = on; }
 void mmo_set_state(void* hp, const double* state, const double* mocap, const double* userdata, double time) {
   Planner& p = ((Handle*)hp)->pl;
   copy(p.state.data(), state, (int)p.state.size());

@@ -72,8 +72,38 @@ void rollout(const Model* m, const PsTask* task, Data* d, const Policy& p, const
   tr->total_return /= std::max(steps, 1);
 }
 
+// TimeSpline::DiscardBefore (mjpc/spline/spline.cc:164-188): drop the nodes the interpolation at `time` no
+// longer needs -- everything before the last node with t <= time, one more kept for the cubic's slope
+static void discardBefore(Policy* p, double time, int nu) {
+  int first = (int)(std::upper_bound(p->times.begin(), p->times.end(), time) - p->times.begin());
+  if (first == 0) return;
+  int last = first - 1;
+  if (p->interp == PS_SPLINE_CUBIC && last > 0) last--;
+  p->times.erase(p->times.begin(), p->times.begin() + last);
+  p->knots.erase(p->knots.begin(), p->knots.begin() + (size_t)last * nu);
+}
+
+// SamplingPlanner::UpdateNominalPolicy, sliding branch (planner.cc:244-281): the plan keeps its nodes, the
+// ones behind `time` are dropped and copies of the last node are appended further in the future
+static void updateNominalSliding(Planner* pl, int horizon) {
+  const Model* m = pl->model;
+  int P = pl->num_spline_points, nu = m->nu;
+  double th = (horizon - 1) * m->opt_timestep;
+  int extra = pl->interpolation == PS_SPLINE_ZERO ? 1 : pl->interpolation == PS_SPLINE_LINEAR ? 2 : 4;
+  double shift = P > extra ? std::fmax(th / (P - extra), 1.0e-5) : th;
+  Policy& p = pl->policy;
+  discardBefore(&p, pl->time, nu);
+  if (p.times.empty()) { p.times.push_back(pl->time); p.knots.insert(p.knots.end(), nu, 0.0); }
+  while ((int)p.times.size() < P) {
+    p.times.push_back(p.times.back() + shift);
+    std::vector<double> last(p.knots.end() - nu, p.knots.end());
+    p.knots.insert(p.knots.end(), last.begin(), last.end());
+  }
+}
+
 // SamplingPlanner::UpdateNominalPolicy, non-sliding branch (planner.cc:282-309)
 static void updateNominal(Planner* pl, int horizon) {
+  if (pl->sliding_plan) { updateNominalSliding(pl, horizon); return; }
   const Model* m = pl->model;
   const Policy& src = pl->candidate.empty() ? pl->policy : pl->candidate[pl->winner];
   int P = pl->num_spline_points, nu = m->nu;

@@ -33,6 +33,7 @@ struct Planner {
   std::vector<Trajectory> trajectory;
   int winner = 0; double improvement = 0;
   int num_spline_points = 0, interpolation = PS_SPLINE_CUBIC;
+  int sliding_plan = 0;                      // sampling_sliding_plan (planner.cc:65, :244-281)
   double noise_exploration[2] = {0.1, 0};
   std::vector<Data> data;     // one per worker thread
   // CrossEntropyPlanner state (mjpc/planners/cross_entropy/planner.h): per-parameter variance, elites

@@ -121,6 +121,9 @@ class Oracle:
         self.P = num_spline_points
         self.L.mmo_planner_config(self.h, num_spline_points, interpolation, ctypes.c_double(sigma0), ctypes.c_double(sigma1))
 
+    def set_sliding_plan(self, on):
+        self.L.mmo_set_sliding_plan(self.h, int(on))
+
     def set_state(self, state, time, mocap=None, userdata=None):
         s = _arr(state); mo = _arr(mocap) if mocap is not None else None
         ud = _arr(userdata) if userdata is not None else None

@@ -35,29 +35,38 @@ def case(name, N, H, seed):
     return model, task, s, P, interp, z, times, knots, synthetic_state(model), rng
 
 
-@pytest.mark.parametrize("name,H", [("Cartpole", 31), ("Walker", 21)])
-def test_sampling_planner_iterations_match_oracle(hostlib, name, H):
+@pytest.mark.parametrize("name,H,sliding,interp", [("Cartpole", 31, 0, 2), ("Walker", 21, 0, 2), ("Cartpole", 31, 1, 2), ("Walker", 21, 1, 1),
+                                                    ("Particle", 21, 1, 0), ("Particle", 21, 0, 0)])
+def test_sampling_planner_iterations_match_oracle(hostlib, name, H, sliding, interp):
     N = 10
-    model, task, s, P, interp, z, times, knots, state, rng = case(name, N, H, seed=21)
-    o = pyoracle.Oracle(model, task); o.configure(P, interp, s["exploration"])
+    model, task, s, P, _, z, times, knots, state, rng = case(name, N, H, seed=21)
+    mocap = model_mocap(model)
+    o = pyoracle.Oracle(model, task); o.configure(P, interp, s["exploration"]); o.set_sliding_plan(sliding)
     pl = planner.CudaSamplingPlanner(model, task)
-    pl.configure(num_trajectory=N, interpolation=interp, num_spline_points=P, sigma0=s["exploration"], sigma1=0.0)
+    pl.configure(num_trajectory=N, interpolation=interp, num_spline_points=P, sigma0=s["exploration"], sigma1=0.0, sliding=sliding)
     pl.Reset(H, np.zeros(model.nu)); o.set_policy(np.zeros(1), np.zeros((1, model.nu)), interp)      # Reset(): one knot at t = 0
     t = 0.0
-    for it in range(3):                       # three planning iterations: resampling of the previous winner included
+    first = []
+    for it in range(6):                       # planning iterations: resampling / sliding of the previous winner included
         zi = rng.standard_normal((N, P, model.nu))
-        o.set_state(state, t); ow = o.optimize(N, H, zi)
-        pl.SetNoise(zi); pl.SetState(state, t); pl.OptimizePolicy(H)
+        o.set_state(state, t, mocap=mocap); ow = o.optimize(N, H, zi)
+        pl.SetNoise(zi); pl.SetState(state, t, mocap=mocap); pl.OptimizePolicy(H)
         ret, _ = o.returns()
         assert pl.winner == ow
         ot, ok = o.policy(0); pt, pk = pl.policy()
         assert np.array_equal(ot, pt) and np.array_equal(ok, pk), (name, it)
+        assert len(pt) == P
+        # a resampled plan starts at the planning time; a sliding plan keeps older nodes
+        assert pt[0] <= t if sliding else pt[0] == t
+        first.append(pt[0])
         assert pl.improvement == o.improvement()
         bt = pl.BestTrajectory()
         assert bt["total_return"] == ret[ow]
         for tq in (t, t + 0.37 * (H - 1) * s["timestep"]):
             assert np.array_equal(pl.ActionFromPolicy(tq), o.action(tq))
-        t += 3 * s["timestep"]
+        t += (0.45 if it % 2 else 0.04) * (H - 1) * s["timestep"]      # the long hops drop nodes of a sliding plan
+    if sliding and P > 6:
+        assert first[-1] > first[0]           # nodes behind the planning time were discarded
     pl.close()
 
 
