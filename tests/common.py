@@ -29,3 +29,13 @@ def model_mocap(model):
             out[i, :3] = np.asarray(model.body_pos).reshape(-1, 3)[b]
             out[i, 3:] = np.asarray(model.body_quat).reshape(-1, 4)[b]
     return out.reshape(-1) if model.nmocap else None
+
+
+def run_isolated(module, func, *args, timeout=900):
+    """Run `module.func(*args)` in a child interpreter.  Used by GPU tests whose CUDA path has not run on hardware
+    yet: a device fault or an abort() in there must not take the verified tests of the same session down with it."""
+    import os, subprocess, sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    code = f"import {module} as m; m.{func}(*{args!r}); print('ISOLATED-OK')"
+    r = subprocess.run([sys.executable, "-c", code], cwd=root, capture_output=True, text=True, timeout=timeout)
+    assert r.returncode == 0 and "ISOLATED-OK" in r.stdout, f"exit {r.returncode}\n{r.stdout[-2000:]}\n{r.stderr[-4000:]}"

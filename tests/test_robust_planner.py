@@ -9,7 +9,7 @@ import numpy as np
 import pytest
 from mujoco_mpc_b200 import registry, task as T
 from oracle import pyoracle
-from tests.common import model_mocap, synthetic_state
+from tests.common import model_mocap, run_isolated, synthetic_state
 from tests.hostsim import driver
 
 
@@ -98,6 +98,10 @@ _unverified = pytest.mark.xfail(strict=False, reason="not yet run on a B200 (GPU
 @_unverified
 @pytest.mark.parametrize("name,H,std", [("Cartpole", 41, 0.5), ("Walker", 31, 2.0), ("Quadruped Flat", 26, 1.0)])
 def test_cuda_robust_planner_matches_oracle(oracle_lib, name, H, std):
+    run_isolated("tests.test_robust_planner", "check_cuda_robust_planner_matches_oracle", name, H, std)
+
+
+def check_cuda_robust_planner_matches_oracle(name, H, std):
     from mujoco_mpc_b200.planner import CudaRobustPlanner
     N, ncand, reps, rate = 64, 6, 4, 0.1
     model, task, s, o, out, state, z, w, nominal, interp = setup(name, N, H, ncand, reps, std, rate, seed=12)
@@ -128,7 +132,11 @@ def test_cuda_robust_planner_matches_oracle(oracle_lib, name, H, std):
 
 @pytest.mark.gpu
 @_unverified
-def test_cuda_robust_planner_device_noise_and_settings():
+def test_cuda_robust_planner_device_noise_and_settings(oracle_lib):
+    run_isolated("tests.test_robust_planner", "check_cuda_robust_planner_device_noise_and_settings")
+
+
+def check_cuda_robust_planner_device_noise_and_settings():
     from mujoco_mpc_b200.planner import CudaRobustPlanner
     model, task, s = registry.load("Cartpole")
     pl = CudaRobustPlanner(model, task)
