@@ -112,11 +112,13 @@ void ps_destroy(PsEngine* e) {
   cudaSetDevice(e->device);
   cudaStreamSynchronize(e->stream);
   void* bufs[] = {e->d_const, e->d_nominal, e->d_ctrlrange, e->d_knots, e->d_returns, e->d_record, e->d_z, e->d_failure, e->d_std2,
-                  e->d_blockmin, e->d_counter, e->d_const2, e->wb.states, e->wb.actions, e->wb.residual, e->wb.costs, e->wb.times, e->wb.trace, e->d_scratch};
+                  e->d_blockmin, e->d_counter, e->d_const2, e->wb.states, e->wb.actions, e->wb.residual, e->wb.costs, e->wb.times, e->wb.trace, e->d_scratch,
+                  e->d_xfrc, e->d_param_std, e->d_elite, e->d_ce_out};
   for (void* b : bufs) if (b) cudaFree(b);
   if (e->h_const) cudaFreeHost(e->h_const);
   if (e->h_const2) cudaFreeHost(e->h_const2);
   if (e->h_record) cudaFreeHost(e->h_record);
+  if (e->h_ce_out) cudaFreeHost(e->h_ce_out);
   for (auto& ev : e->ev) if (ev) cudaEventDestroy(ev);
   cudaStreamDestroy(e->stream);
   delete e;

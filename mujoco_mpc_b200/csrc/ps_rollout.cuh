@@ -20,6 +20,26 @@ struct Writeback {
 // Ornstein-Uhlenbeck coefficients rate = exp(-dt / xfrc_rate), scale = xfrc_std sqrt(1 - rate^2) (trajectory.cc:149-151)
 struct XfrcNoise { const double* z; double rate, scale; };
 
+// Per-rollout perturbation state.  The planning kernels instantiate the empty one (their forward pass is the plain
+// forward_pass they were verified with); robust_rollout_kernel instantiates the one that carries
+// mjData.xfrc_applied ([force; torque] per body) through the Ornstein-Uhlenbeck recursion of trajectory.cc:147-155.
+template <class T, bool XF> struct Perturbation;
+template <class T> struct Perturbation<T, false> {
+  PS_HD Perturbation(const DevModel<T>&, const XfrcNoise*) {}
+  PS_HD void advance(const DevModel<T>&, int, int, int) {}
+  PS_HD void forward(const DevModel<T>& m, RolloutData<T>& d) { forward_pass(m, d); }
+};
+template <class T> struct Perturbation<T, true> {
+  const XfrcNoise* xf; double applied[6 * T::NBODY];
+  PS_HD Perturbation(const DevModel<T>& m, const XfrcNoise* x) : xf(x) { for (int k = 0; k < 6 * m.nbody; k++) applied[k] = 0; }
+  PS_HD void advance(const DevModel<T>& m, int t, int stride, int i) {
+    if (!xf || !xf->z) return;
+    const int n6 = 6 * m.nbody; const double* zc = xf->z + (size_t)t * n6 * stride + i;
+    for (int k = 0; k < n6; k++) applied[k] = xf->rate * applied[k] + xf->scale * zc[(size_t)k * stride];
+  }
+  PS_HD void forward(const DevModel<T>& m, RolloutData<T>& d) { forward_pass_xfrc(m, d, applied); }
+};
+
 // knots: SoA [P*nu][stride]; i = this rollout's column.  flags: bit0 failure, bit1 capacity overflow
 // XF: apply Cartesian perturbation forces (own kernel instantiation: robust_rollout_kernel)
 template <class T, bool WB, bool XF = false>
@@ -39,22 +59,15 @@ PS_FN double rollout_sample(const DevModel<T>& m, const DevTask& task, const Dev
   double residual[kMaxResidual];
   double sum = 0; bool failed = false;
   if (WB) { for (int k = 0; k < ns; k++) wb.states[(size_t)k * stride + i] = plan.state[k]; wb.times[i] = d.time; }
-  // Cartesian perturbation forces [force; torque] per body (mjData.xfrc_applied): writeback / robust-rollout
-  // instantiation only (RobustPlanner's Ornstein-Uhlenbeck noise, mjpc/trajectory.cc:147-155)
-  const bool xfrc = XF && xf && xf->z != nullptr;
-  double xfrc_applied[XF ? 6 * T::NBODY : 1];
-  if (XF) for (int k = 0; k < 6 * m.nbody; k++) xfrc_applied[k] = 0;
+  Perturbation<T, XF> pert(m, xf);
 
   for (int t = 0; t < H - 1; t++) {
     spline_sample(plan.spline_times, P, nu, plan.interpolation, d.time, kn, d.ctrl);
     for (int a = 0; a < nu; a++) d.ctrl[a] = clampd(d.ctrl[a], m.act_ctrlrange[2 * a], m.act_ctrlrange[2 * a + 1]);
     if (WB) for (int a = 0; a < nu; a++) wb.actions[((size_t)t * nu + a) * stride + i] = d.ctrl[a];
-    if (XF) if (xfrc) {
-      const int n6 = 6 * m.nbody; const double* zc = xf->z + (size_t)t * n6 * stride + i;
-      for (int k = 0; k < n6; k++) xfrc_applied[k] = xf->rate * xfrc_applied[k] + xf->scale * zc[(size_t)k * stride];
-    }
+    pert.advance(m, t, stride, i);
     if (state_is_bad(m, d)) { failed = true; break; }
-    forward_pass<T, XF>(m, d, xfrc_applied);
+    pert.forward(m, d);
     task_residual(m, d, task, residual);
     const double c = cost_value(task, residual);
     if (WB) {
@@ -80,7 +93,7 @@ PS_FN double rollout_sample(const DevModel<T>& m, const DevTask& task, const Dev
   if (!failed) {
     // terminal: ctrl is NOT rewritten before the final forward pass (trajectory.cc:190-198)
     if (WB && H > 1) for (int a = 0; a < nu; a++) wb.actions[((size_t)(H - 1) * nu + a) * stride + i] = d.ctrl[a];
-    forward_pass<T, XF>(m, d, xfrc_applied);
+    pert.forward(m, d);
     task_residual(m, d, task, residual);
     const double c = cost_value(task, residual);
     if (WB) {

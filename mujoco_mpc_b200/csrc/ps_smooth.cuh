@@ -391,19 +391,30 @@ PS_NT void actuation_stage(const DevModel<T>& m, RolloutData<T>& d) {
   }
 }
 
-template <class T, bool XF = false>
-PS_NT void acceleration_stage(const DevModel<T>& m, RolloutData<T>& d, const double* xfrc_applied = nullptr) {
+template <class T>
+PS_NT void acceleration_stage(const DevModel<T>& m, RolloutData<T>& d) {
+  const int nv = nv_of(m);
+  for (int i = 0; i < nv; i++) {
+    d.qfrc_smooth[i] = d.qfrc_passive[i] - d.qfrc_bias[i] + d.qfrc_actuator[i];
+    d.qacc_smooth[i] = d.qfrc_smooth[i];
+  }
+  solve_tree(m, d.qacc_smooth, d.qLD, d.qLDiagInv);
+}
+
+// the same stage with Cartesian perturbation forces (mjData.xfrc_applied, [force; torque] per body) added to
+// qfrc_smooth by mj_xfrcAccumulate: J(xipos_b, b)' x for every body with a non-zero entry.  A separate function so
+// that the planning kernels keep the exact code they were verified with.
+template <class T>
+PS_NT void acceleration_stage_xfrc(const DevModel<T>& m, RolloutData<T>& d, const double* xfrc_applied) {
   constexpr int S = T::NV; const int nv = nv_of(m);
   for (int i = 0; i < nv; i++) d.qfrc_smooth[i] = d.qfrc_passive[i] - d.qfrc_bias[i] + d.qfrc_actuator[i];
-  if (XF) {      // mj_xfrcAccumulate: J(xipos_b, b)' [force; torque] for every body with a non-zero entry
-    double jp[3 * S], jr[3 * S];
-    for (int b = 1; b < m.nbody; b++) {
-      const double* x = xfrc_applied + 6 * b;
-      if (x[0] == 0 && x[1] == 0 && x[2] == 0 && x[3] == 0 && x[4] == 0 && x[5] == 0) continue;
-      point_jacobian(m, d, jp, jr, d.xipos + 3 * b, b);
-      for (int c = 0; c < nv; c++)
-        for (int k = 0; k < 3; k++) d.qfrc_smooth[c] += jp[k * S + c] * x[k] + jr[k * S + c] * x[3 + k];
-    }
+  double jp[3 * S], jr[3 * S];
+  for (int b = 1; b < m.nbody; b++) {
+    const double* x = xfrc_applied + 6 * b;
+    if (x[0] == 0 && x[1] == 0 && x[2] == 0 && x[3] == 0 && x[4] == 0 && x[5] == 0) continue;
+    point_jacobian(m, d, jp, jr, d.xipos + 3 * b, b);
+    for (int c = 0; c < nv; c++)
+      for (int k = 0; k < 3; k++) d.qfrc_smooth[c] += jp[k * S + c] * x[k] + jr[k * S + c] * x[3 + k];
   }
   for (int i = 0; i < nv; i++) d.qacc_smooth[i] = d.qfrc_smooth[i];
   solve_tree(m, d.qacc_smooth, d.qLD, d.qLDiagInv);

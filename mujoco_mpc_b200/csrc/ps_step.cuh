@@ -64,16 +64,28 @@ PS_NT int read_sensor(const DevModel<T>& m, const D& d, int s, double* out) {
 }
 
 // ---------------------------------------------------------------- forward pass
-// XF: the instantiation applies d.xfrc_applied (writeback / robust-rollout kernels only)
-template <class T, bool XF = false>
-PS_FN void forward_pass(const DevModel<T>& m, RolloutData<T>& d, const double* xfrc_applied = nullptr) {
+template <class T>
+PS_FN void forward_pass(const DevModel<T>& m, RolloutData<T>& d) {
   position_smooth(m, d);
   make_constraints(m, d);
   velocity_stage(m, d);
   reference_acceleration(m, d);
   if (m.need_subtreevel) subtree_velocity(m, d);
   actuation_stage(m, d);
-  acceleration_stage<T, XF>(m, d, xfrc_applied);
+  acceleration_stage(m, d);
+  constraint_stage(m, d);
+}
+
+// forward pass under Cartesian perturbation forces (robust_rollout_kernel only)
+template <class T>
+PS_FN void forward_pass_xfrc(const DevModel<T>& m, RolloutData<T>& d, const double* xfrc_applied) {
+  position_smooth(m, d);
+  make_constraints(m, d);
+  velocity_stage(m, d);
+  reference_acceleration(m, d);
+  if (m.need_subtreevel) subtree_velocity(m, d);
+  actuation_stage(m, d);
+  acceleration_stage_xfrc(m, d, xfrc_applied);
   constraint_stage(m, d);
 }
 

@@ -94,9 +94,15 @@ struct Variant {
   int (*launch)(cudaStream_t, const void*, const double*, int, int, int, long long, double*, unsigned char*, MinLoc*, Writeback, bool, int*);
   int (*robust)(cudaStream_t, const void*, const double*, int, int, double*, unsigned char*, Writeback, XfrcNoise);   // null: no force perturbations
 };
+// the force-perturbed kernels live in their own translation unit (ps_variant_robust.cu), so that the code
+// generated for the planning kernels of a variant's unit does not depend on them
+using RobustFn = int (*)(cudaStream_t, const void*, const double*, int, int, double*, unsigned char*, Writeback, XfrcNoise);
+int launch_robust_tiny(cudaStream_t, const void*, const double*, int, int, double*, unsigned char*, Writeback, XfrcNoise);
+int launch_robust_planar(cudaStream_t, const void*, const double*, int, int, double*, unsigned char*, Writeback, XfrcNoise);
+int launch_robust_legged(cudaStream_t, const void*, const double*, int, int, double*, unsigned char*, Writeback, XfrcNoise);
 template <class T, int BLOCK>
-inline Variant make_variant(const char* name) {
-  return Variant{name, sizeof(Constants<T>), BLOCK, false, T::LEAN, fill_model<T>, set_options<T>, set_debug<T>, set_task<T>, set_plan<T>, launch_rollout<T, BLOCK>, launch_robust<T, BLOCK>};
+inline Variant make_variant(const char* name, RobustFn robust) {
+  return Variant{name, sizeof(Constants<T>), BLOCK, false, T::LEAN, fill_model<T>, set_options<T>, set_debug<T>, set_task<T>, set_plan<T>, launch_rollout<T, BLOCK>, robust};
 }
 template <class T, int WARPS>
 inline Variant make_coop_variant(const char* name) {

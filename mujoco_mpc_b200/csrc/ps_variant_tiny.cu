@@ -5,5 +5,5 @@
 #define PS_TINY_BLOCK 128
 #endif
 namespace ps {
-const Variant* variant_tiny() { static const Variant v = make_variant<TinyT, PS_TINY_BLOCK>("tiny"); return &v; }
+const Variant* variant_tiny() { static const Variant v = make_variant<TinyT, PS_TINY_BLOCK>("tiny", launch_robust_tiny); return &v; }
 }  // namespace ps
