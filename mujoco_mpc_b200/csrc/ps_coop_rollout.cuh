@@ -33,6 +33,38 @@ PS_FN void co_forward_pass(const LT& L, const DevModel<T>& m, CoopData<T>& d) {
   co_constraint_stage(stage_lanes(L, dbg, 7), m, d);
 }
 
+// forward pass under Cartesian perturbation forces (robust re-rolls only)
+template <class T, class LT>
+PS_FN void co_forward_pass_xfrc(const LT& L, const DevModel<T>& m, CoopData<T>& d, const double* xfrc_applied) {
+  const int dbg = m.debug_serial;
+  co_position_smooth(stage_lanes(L, dbg, 0), m, d);
+  co_make_constraints(stage_lanes(L, dbg, 1), m, d);
+  co_velocity_stage(stage_lanes(L, dbg, 2), m, d);
+  co_reference_acceleration(stage_lanes(L, dbg, 3), m, d);
+  if (m.need_subtreevel) co_subtree_velocity(stage_lanes(L, dbg, 4), m, d);
+  co_actuation_stage(stage_lanes(L, dbg, 5), m, d);
+  co_acceleration_stage_xfrc(stage_lanes(L, dbg, 6), m, d, xfrc_applied);
+  co_constraint_stage(stage_lanes(L, dbg, 7), m, d);
+}
+
+// Per-rollout perturbation state of the phase-parallel coding (see Perturbation<T, XF> in ps_rollout.cuh): the
+// planning kernels use the empty one; the robust kernels hand in storage for xfrc_applied (shared memory for a
+// warp, a local array for a single lane) and the Ornstein-Uhlenbeck driving noise.
+template <class T, bool XF> struct CoPerturbation;
+template <class T> struct CoPerturbation<T, false> { static constexpr bool kActive = false; };   // never touched by the rollout
+template <class T> struct CoPerturbation<T, true> {
+  static constexpr bool kActive = true;
+  double* applied; const XfrcNoise* xf;          // applied: [6 * nbody], visible to every lane of the rollout
+  template <class LT> PS_HD void reset(const LT& L, const DevModel<T>& m) const { CO_FOR(k, 6 * m.nbody) applied[k] = 0; L.sync(); }
+  template <class LT> PS_HD void advance(const LT& L, const DevModel<T>& m, int t, int stride, int i) const {
+    if (!xf || !xf->z) return;
+    const int n6 = 6 * m.nbody; const double* zc = xf->z + (size_t)t * n6 * stride + i;
+    CO_FOR(k, n6) applied[k] = xf->rate * applied[k] + xf->scale * zc[(size_t)k * stride];
+    L.sync();
+  }
+  template <class LT> PS_HD void forward(const LT& L, const DevModel<T>& m, CoopData<T>& d) const { co_forward_pass_xfrc(L, m, d, applied); }
+};
+
 // semi-implicit Euler with implicit joint damping (mj_Euler); other integrators stay with the
 // thread-per-rollout engine
 template <class T, class LT>
@@ -77,9 +109,9 @@ PS_FN void co_integrate(const LT& L, const DevModel<T>& m, CoopData<T>& d) {
 }
 
 // knots: SoA [P*nu][stride]; i = this rollout's column.  flags: bit0 failure, bit1 capacity overflow
-template <class T, bool WB, class LT>
+template <class T, bool WB, class LT, class PT = CoPerturbation<T, false>>
 PS_FN double co_rollout(const LT& L, const DevModel<T>& m, const DevTask& task, const DevPlan<T>& plan, const double* knots,
-                        int stride, int i, const Writeback& wb, CoopData<T>& d, int* flags) {
+                        int stride, int i, const Writeback& wb, CoopData<T>& d, int* flags, const PT pert = PT()) {
   const int nq = m.nq, nv = m.nv, na = m.na, nu = m.nu, ns = nq + nv + na, nr = task.num_residual;
   const int H = plan.horizon, P = plan.num_spline_points, ntr = 3 * task.num_trace;
   CO_FOR(k, nq) d.qpos[k] = plan.state[k];
@@ -90,6 +122,7 @@ PS_FN double co_rollout(const LT& L, const DevModel<T>& m, const DevTask& task, 
   if (L.lane == 0) { d.time = plan.time; d.warning = 0; d.ncon = 0; d.nefc = 0; d.nlimit = 0; d.solver_iter = 0; }
   if (WB) { CO_FOR(k, ns) wb.states[(size_t)k * stride + i] = plan.state[k]; if (L.lane == 0) wb.times[i] = plan.time; }
   L.sync();
+  if constexpr (PT::kActive) pert.reset(L, m);
   const double* kcol = knots + i;
   double sum = 0; bool failed = false;
 
@@ -103,6 +136,7 @@ PS_FN double co_rollout(const LT& L, const DevModel<T>& m, const DevTask& task, 
         double u; spline_sample(plan.spline_times, P, 1, plan.interpolation, time, kn, &u);
         d.ctrl[a] = clampd(u, m.act_ctrlrange[2 * a], m.act_ctrlrange[2 * a + 1]);
       }
+      if constexpr (PT::kActive) pert.advance(L, m, t, stride, i);
       bool bad = false;
       CO_FOR(k, nq) bad = bad || bad_number(d.qpos[k]);
       CO_FOR(k, nv) bad = bad || bad_number(d.qvel[k]);
@@ -110,7 +144,7 @@ PS_FN double co_rollout(const LT& L, const DevModel<T>& m, const DevTask& task, 
       if (L.any(bad)) { failed = true; if (WB) { CO_FOR(a, nu) wb.actions[((size_t)t * nu + a) * stride + i] = d.ctrl[a]; } break; }
     }
     if (WB && (!terminal || H > 1)) CO_FOR(a, nu) wb.actions[((size_t)t * nu + a) * stride + i] = d.ctrl[a];
-    co_forward_pass(L, m, d);
+    if constexpr (PT::kActive) pert.forward(L, m, d); else co_forward_pass(L, m, d);
     if (L.lane == 0) {
       task_residual(m, d, task, d.residual);
       d.sc_cost = cost_value(task, d.residual);
@@ -199,6 +233,42 @@ coop_rollout_kernel(const Constants<T>* __restrict__ gconst, const double* __res
     for (int w = 1; w < WARPS; w++) if (better(warp_min[w].cost, warp_min[w].index, best, best_i)) { best = warp_min[w].cost; best_i = warp_min[w].index; }
     block_min[blockIdx.x].cost = best; block_min[blockIdx.x].index = best_i;
   }
+}
+
+// ---------------------------------------------------------------- robust re-rolls, one warp per rollout
+// RobustPlanner's candidates x repetitions under force perturbations (robust_planner.cc:108-130): the batch is
+// small, so each rollout gets a warp and its working set (+ xfrc_applied) in shared memory; always full writeback.
+template <class T, int WARPS>
+__global__ void __launch_bounds__(WARPS * 32)
+coop_robust_kernel(const Constants<T>* __restrict__ gconst, const double* __restrict__ knots, int stride, int n,
+                   double* __restrict__ returns, unsigned char* __restrict__ failure, Writeback wb, XfrcNoise xf) {
+  extern __shared__ __align__(128) unsigned char smem[];
+  Constants<T>& sc = *reinterpret_cast<Constants<T>*>(smem);
+  constexpr size_t kConst = (sizeof(Constants<T>) + 127) / 128 * 128;
+  constexpr size_t kData = (sizeof(CoopData<T>) + 127) / 128 * 128;
+  constexpr size_t kXf = (sizeof(double) * 6 * T::NBODY + 127) / 128 * 128;
+  __shared__ alignas(8) uint64_t bar;
+  if (threadIdx.x == 0) { mbar_init(&bar, 1); asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    constexpr uint32_t total = (uint32_t)sizeof(Constants<T>);
+    mbar_expect_tx(&bar, total);
+    const char* src = reinterpret_cast<const char*>(gconst); char* dst = reinterpret_cast<char*>(&sc);
+    for (uint32_t off = 0; off < total; off += 32768u) {
+      const uint32_t sz = total - off < 32768u ? total - off : 32768u;
+      tma_bulk_g2s(dst + off, src + off, sz, &bar);
+    }
+  }
+  mbar_wait(&bar, 0);
+  const int warp = threadIdx.x >> 5;
+  const int i = blockIdx.x * WARPS + warp;
+  if (i >= n) return;                                  // whole warps leave together; no block-level sync below
+  Lanes L; L.lane = threadIdx.x & 31; L.width = 32;
+  CoopData<T>& d = *reinterpret_cast<CoopData<T>*>(smem + kConst + warp * (kData + kXf));
+  CoPerturbation<T, true> pert{reinterpret_cast<double*>(smem + kConst + warp * (kData + kXf) + kData), &xf};
+  int flags = 0;
+  const double total = co_rollout<T, true, Lanes, CoPerturbation<T, true>>(L, sc.m, sc.t, sc.p, knots, stride, i, wb, d, &flags, pert);
+  if (L.lane == 0) { returns[i] = total; failure[i] = (unsigned char)flags; }
 }
 
 // ---------------------------------------------------------------- thread-per-rollout flavour of the same phases

@@ -409,4 +409,34 @@ PS_NI void co_acceleration_stage(const LT& L, const DevModel<T>& m, CoopData<T>&
   co_solve_tree(L, m, d.qacc_smooth, d.qH, d.qLDiagInv);
 }
 
+// The same stage under Cartesian perturbation forces (mjData.xfrc_applied, [force; torque] per body; robust
+// re-rolls only): one dof per lane, each adding J(xipos_b, b)' x of the bodies whose chain holds that dof, in
+// body order -- the summation order of mj_xfrcAccumulate / the dense acceleration_stage_xfrc.
+template <class T, class LT>
+PS_NI void co_acceleration_stage_xfrc(const LT& L, const DevModel<T>& m, CoopData<T>& d, const double* xfrc_applied) {
+  PS_ASSUME_SHARED(&m); if (LT::kSharedData) PS_ASSUME_SHARED(&d);
+  CO_FOR(c, m.nv) {
+    double acc = d.qfrc_passive[c] - d.qfrc_bias[c] + d.qfrc_actuator[c];
+    const double* cd = d.cdof + 6 * c;
+    for (int b = 1; b < m.nbody; b++) {
+      const double* x = xfrc_applied + 6 * b;
+      if (x[0] == 0 && x[1] == 0 && x[2] == 0 && x[3] == 0 && x[4] == 0 && x[5] == 0) continue;
+      const int w = m.body_weldid[b];
+      if (w <= 0) continue;
+      int i = m.body_dofadr[w] + m.body_dofnum[w] - 1;
+      while (i > c) i = m.dof_parentid[i];          // a dof's parent has a lower index
+      if (i != c) continue;                         // dof c does not move body b
+      double off[3], t[3];
+      const double* root = d.subtree_com + 3 * m.body_rootid[w];
+      for (int k = 0; k < 3; k++) off[k] = d.xipos[3 * b + k] - root[k];
+      cross3(t, cd, off);
+      for (int k = 0; k < 3; k++) acc += (cd[3 + k] + t[k]) * x[k] + cd[k] * x[3 + k];
+    }
+    d.qfrc_smooth[c] = acc;
+    d.qacc_smooth[c] = acc;
+  }
+  L.sync();
+  co_solve_tree(L, m, d.qacc_smooth, d.qH, d.qLDiagInv);
+}
+
 }  // namespace ps

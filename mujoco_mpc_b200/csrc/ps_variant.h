@@ -41,6 +41,21 @@ inline int launch_robust(cudaStream_t st, const void* dconst, const double* knot
   return grid;
 }
 
+// force-perturbed re-rolls on the warp-per-rollout coding
+template <class T, int WARPS>
+inline int launch_coop_robust(cudaStream_t st, const void* dconst, const double* knots, int stride, int n, double* returns,
+                              unsigned char* failure, Writeback wb, XfrcNoise xf) {
+  constexpr size_t kConst = (sizeof(Constants<T>) + 127) / 128 * 128, kData = (sizeof(CoopData<T>) + 127) / 128 * 128;
+  constexpr size_t kXf = (sizeof(double) * 6 * T::NBODY + 127) / 128 * 128;
+  constexpr size_t smem = kConst + WARPS * (kData + kXf);
+  static_assert(smem <= 227 * 1024, "robust warp-per-rollout kernel: working sets exceed the shared memory of an SM");
+  static bool configured = false;
+  if (!configured) { cudaFuncSetAttribute(coop_robust_kernel<T, WARPS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); configured = true; }
+  const int grid = (n + WARPS - 1) / WARPS;
+  coop_robust_kernel<T, WARPS><<<grid, WARPS * 32, smem, st>>>(reinterpret_cast<const Constants<T>*>(dconst), knots, stride, n, returns, failure, wb, xf);
+  return grid;
+}
+
 // warp-per-rollout persistent launch: as many blocks as stay resident, WARPS rollouts in flight per block
 template <class T, int WARPS>
 inline int launch_coop(cudaStream_t st, const void* dconst, const double* knots, int stride, int first, int n,
@@ -100,13 +115,15 @@ using RobustFn = int (*)(cudaStream_t, const void*, const double*, int, int, dou
 int launch_robust_tiny(cudaStream_t, const void*, const double*, int, int, double*, unsigned char*, Writeback, XfrcNoise);
 int launch_robust_planar(cudaStream_t, const void*, const double*, int, int, double*, unsigned char*, Writeback, XfrcNoise);
 int launch_robust_legged(cudaStream_t, const void*, const double*, int, int, double*, unsigned char*, Writeback, XfrcNoise);
+int launch_robust_planar_coop(cudaStream_t, const void*, const double*, int, int, double*, unsigned char*, Writeback, XfrcNoise);
+int launch_robust_legged_coop(cudaStream_t, const void*, const double*, int, int, double*, unsigned char*, Writeback, XfrcNoise);
 template <class T, int BLOCK>
 inline Variant make_variant(const char* name, RobustFn robust) {
   return Variant{name, sizeof(Constants<T>), BLOCK, false, T::LEAN, fill_model<T>, set_options<T>, set_debug<T>, set_task<T>, set_plan<T>, launch_rollout<T, BLOCK>, robust};
 }
 template <class T, int WARPS>
-inline Variant make_coop_variant(const char* name) {
-  return Variant{name, sizeof(Constants<T>), WARPS * 32, true, true, fill_model<T>, set_options<T>, set_debug<T>, set_task<T>, set_plan<T>, launch_coop<T, WARPS>, nullptr};
+inline Variant make_coop_variant(const char* name, RobustFn robust = nullptr) {
+  return Variant{name, sizeof(Constants<T>), WARPS * 32, true, true, fill_model<T>, set_options<T>, set_debug<T>, set_task<T>, set_plan<T>, launch_coop<T, WARPS>, robust};
 }
 const Variant* variant_tiny();
 const Variant* variant_planar();

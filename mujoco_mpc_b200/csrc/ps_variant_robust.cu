@@ -19,4 +19,14 @@ int launch_robust_legged(cudaStream_t st, const void* dconst, const double* knot
                          unsigned char* failure, Writeback wb, XfrcNoise xf) {
   return launch_robust<LeggedT, 64>(st, dconst, knots, stride, n, returns, failure, wb, xf);
 }
+// warp-per-rollout coding (walker / quadruped class models on the Euler integrator): the latency engine, which is
+// what a batch of a few dozen re-rolls wants
+int launch_robust_planar_coop(cudaStream_t st, const void* dconst, const double* knots, int stride, int n, double* returns,
+                              unsigned char* failure, Writeback wb, XfrcNoise xf) {
+  return launch_coop_robust<PlanarCoopT, 4>(st, dconst, knots, stride, n, returns, failure, wb, xf);
+}
+int launch_robust_legged_coop(cudaStream_t st, const void* dconst, const double* knots, int stride, int n, double* returns,
+                              unsigned char* failure, Writeback wb, XfrcNoise xf) {
+  return launch_coop_robust<LeggedCoopT, 4>(st, dconst, knots, stride, n, returns, failure, wb, xf);
+}
 }  // namespace ps

@@ -39,7 +39,7 @@ void CudaRobustPlanner::Initialize(const PsModel* model, const PsTask* task, int
   if (engine_) { ps_destroy(engine_); engine_ = nullptr; }
   engine_ = ps_create(device_ordinal);
   if (!engine_) Fail("ps_create");
-  if (ps_set_engine_flavour(engine_, 3)) Fail("ps_set_engine_flavour");    // the kernel that carries xfrc_applied
+  if (ps_set_engine_flavour(engine_, engine_flavour_)) Fail("ps_set_engine_flavour");
   if (ps_set_model(engine_, model)) Fail("ps_set_model");
   if (ps_set_task(engine_, task)) Fail("ps_set_task");
 }

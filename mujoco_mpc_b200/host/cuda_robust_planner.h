@@ -3,8 +3,8 @@
 // CudaSamplingPlanner (the reference wraps any RankedPlanner; SamplingPlanner is the one it ships,
 // planners/include.cc); its best `ncandidates_` policies are re-rolled `nrepetitions_` times each under
 // Ornstein-Uhlenbeck force perturbations on every body (Trajectory::NoisyRollout,
-// mjpc/trajectory.cc:100-210) by ONE launch of robust_rollout_kernel on a second engine handle pinned to
-// the dense thread-per-rollout flavour, and the candidate with the lowest running-mean return is
+// mjpc/trajectory.cc:100-210) by ONE launch of the force-perturbed rollout kernel (coop_robust_kernel, one warp per
+// rollout, or robust_rollout_kernel, one thread per rollout) on a second engine handle, and the candidate with the lowest running-mean return is
 // copied into the policy (robust_planner.cc:132-156).  SURVEY.md section 8(f) row 2.
 #ifndef MJPC_B200_CUDA_ROBUST_PLANNER_H_
 #define MJPC_B200_CUDA_ROBUST_PLANNER_H_
@@ -42,6 +42,9 @@ class CudaRobustPlanner {
 
   // ---- settings (private in the reference, set from the model's numerics / its GUI sliders)
   int ncandidates_ = 12, nrepetitions_ = 5;
+  // kernel of the re-rolls, read by Initialize(): 0 = warp-per-rollout where the model class has one (walker /
+  // quadruped on the Euler integrator), else dense thread-per-rollout; 3 = always dense (ps_set_engine_flavour)
+  int engine_flavour_ = 0;
   double xfrc_std_ = 0.1, xfrc_rate_ = 0.1;
 
   // ---- results of the last OptimizePolicy

@@ -184,6 +184,13 @@ void* prb_create(const PsModel* model, const PsTask* task, int device) {
   p->Initialize(model, task, device); p->Allocate(); p->Reset(mjpc_b200::kMaxTrajectoryHorizon);
   return p;
 }
+// flavour of the re-roll kernel: 0 auto (warp-per-rollout where available), 3 dense thread-per-rollout
+void* prb_create_flavour(const PsModel* model, const PsTask* task, int device, int flavour) {
+  CudaRobustPlanner* p = new CudaRobustPlanner(std::make_unique<CudaSamplingPlanner>());
+  p->engine_flavour_ = flavour;
+  p->Initialize(model, task, device); p->Allocate(); p->Reset(mjpc_b200::kMaxTrajectoryHorizon);
+  return p;
+}
 void prb_destroy(void* h) { delete (CudaRobustPlanner*)h; }
 void* prb_delegate(void* h) { return ((CudaRobustPlanner*)h)->delegate(); }      // a psp_* handle owned by the robust planner
 void* prb_engine(void* h) { return ((CudaRobustPlanner*)h)->engine(); }

@@ -293,13 +293,14 @@ class CudaRobustPlanner:
     mjpc/planners/robust/robust_planner.h): the delegate's best candidates re-rolled under random body forces
     in one launch of the force-perturbed rollout kernel; the lowest mean return is kept."""
 
-    def __init__(self, model, task, device=0):
+    def __init__(self, model, task, device=0, flavour=0):
+        """flavour of the re-roll kernel: 0 = warp-per-rollout where the model class has one, 3 = dense thread-per-rollout"""
         self.L = lib()
-        for f in ("prb_create", "prb_delegate", "prb_engine"):
+        for f in ("prb_create", "prb_create_flavour", "prb_delegate", "prb_engine"):
             getattr(self.L, f).restype = ctypes.c_void_p
         self.L.prb_noisy_rollouts_us.restype = ctypes.c_double
         self.model, self.task = model, task
-        self.h = ctypes.c_void_p(self.L.prb_create(ctypes.byref(model.c_struct()), ctypes.byref(task), device))
+        self.h = ctypes.c_void_p(self.L.prb_create_flavour(ctypes.byref(model.c_struct()), ctypes.byref(task), device, int(flavour)))
         self.delegate = _Delegate(self.L, model, task, self.L.prb_delegate(self.h))
         self.horizon = 0
 
@@ -375,3 +376,10 @@ class CudaRobustPlanner:
         n = self.L.prb_results(self.h, _p(scores), _p(ret), fail.ctypes.data_as(ctypes.POINTER(ctypes.c_ubyte)), nc)
         return dict(scores=scores[:n], noisy_returns=ret[:n * rep].reshape(n, rep), noisy_failure=fail[:n * rep].reshape(n, rep),
                     noisy_rollouts_us=self.L.prb_noisy_rollouts_us(self.h))
+
+    def reroll_kernel(self):
+        """name of the engine variant the force-perturbed rollouts ran on"""
+        buf = ctypes.create_string_buffer(64)
+        eng = ctypes.CDLL(os.path.join(_HERE, "libps_engine.so"))
+        eng.ps_variant(ctypes.c_void_p(self.L.prb_engine(self.h)), buf, 64)
+        return buf.value.decode()

@@ -56,8 +56,7 @@ def rollout(model, task, state, time, times, knots, interp, H, timestep, integra
     mo = None if mocap is None else np.ascontiguousarray(mocap, dtype=np.float64)
     fn = L.hs_rollout_coop if coop else L.hs_rollout
     zz = None
-    if xfrc is not None:     # (z [H-1][6*nbody], std, rate): thread-per-rollout path only
-        assert not coop
+    if xfrc is not None:     # (z [H-1][6*nbody], std, rate): the force-perturbed instantiation of either coding
         zz = np.ascontiguousarray(xfrc[0], dtype=np.float64)
         L.hs_set_xfrc(_p(zz), ctypes.c_double(xfrc[1]), ctypes.c_double(xfrc[2]))
     else:

@@ -65,6 +65,14 @@ static int run_coop(const PsModel* m, const PsTask* t, const PairList& pl, const
   CoopData<T>* d = (CoopData<T>*)(((uintptr_t)dbuf.data() + 127) & ~(uintptr_t)127);
   std::memset((void*)d, 0xFF, sizeof(CoopData<T>));   // poison: a read-before-write shows up as NaN
   Lanes L;
+  if (g_xfrc_z && g_xfrc_std > 0) {      // the instantiation coop_robust_kernel runs (with one lane here)
+    XfrcNoise xf{g_xfrc_z, std::exp(-k->m.timestep / g_xfrc_rate), 0.0};
+    xf.scale = g_xfrc_std * std::sqrt(1 - xf.rate * xf.rate);
+    std::vector<double> applied(6 * T::NBODY, -1.0e300);     // poison: reset() must clear it
+    CoPerturbation<T, true> pert{applied.data(), &xf};
+    *total = co_rollout<T, true, Lanes, CoPerturbation<T, true>>(L, k->m, k->t, k->p, knots, 1, 0, wb, *d, flags, pert);
+    return 0;
+  }
   *total = co_rollout<T, true>(L, k->m, k->t, k->p, knots, 1, 0, wb, *d, flags);
   return 0;
 }

@@ -57,6 +57,25 @@ def test_noisy_rollout_device_code_matches_oracle(hostsim_lib, name, H, std):
     assert h["total"] == ret[out["order"][0]]
 
 
+@pytest.mark.parametrize("name,H,std", [("Walker", 31, 2.0), ("Quadruped Flat", 26, 1.0), ("Cartpole", 41, 0.5)])
+def test_noisy_rollout_phase_parallel_coding_matches_oracle(hostsim_lib, name, H, std):
+    # the coding coop_robust_kernel runs (one lane here): per-dof accumulation of J' x instead of per-body Jacobians
+    N, ncand, reps, rate = 12, 3, 2, 0.1
+    model, task, s, o, out, state, z, w, nominal, interp = setup(name, N, H, ncand, reps, std, rate)
+    ret, _ = o.returns()
+    for c in range(ncand):
+        kt, kn = o.policy(2 + int(out["order"][c]))
+        for j in range(reps):
+            h = driver.rollout(model, task, state, 0.0, kt, kn, interp, H, s["timestep"], s["integrator"], coop=True,
+                               xfrc=(w[c * reps + j], std, rate))
+            assert bool(h["flags"] & 1) == bool(out["noisy_failure"][c, j])
+            if not out["noisy_failure"][c, j]:
+                assert h["total"] == out["noisy_returns"][c, j], (name, c, j, h["total"], out["noisy_returns"][c, j])
+    kt, kn = o.policy(2 + int(out["order"][0]))
+    h = driver.rollout(model, task, state, 0.0, kt, kn, interp, H, s["timestep"], s["integrator"], coop=True)
+    assert h["total"] == ret[out["order"][0]]
+
+
 def test_robust_selection_rule(oracle_lib):
     N, H, ncand, reps, std, rate = 16, 31, 4, 3, 1.5, 0.1
     model, task, s, o, out, state, z, w, nominal, interp = setup("Walker", N, H, ncand, reps, std, rate, seed=8)
@@ -96,17 +115,19 @@ _unverified = pytest.mark.xfail(strict=False, reason="not yet run on a B200 (GPU
 
 @pytest.mark.gpu
 @_unverified
-@pytest.mark.parametrize("name,H,std", [("Cartpole", 41, 0.5), ("Walker", 31, 2.0), ("Quadruped Flat", 26, 1.0)])
-def test_cuda_robust_planner_matches_oracle(oracle_lib, name, H, std):
-    run_isolated("tests.test_robust_planner", "check_cuda_robust_planner_matches_oracle", name, H, std)
+@pytest.mark.parametrize("name,H,std,flavour,kernel", [
+    ("Cartpole", 41, 0.5, 0, "tiny"), ("Walker", 31, 2.0, 0, "planar_coop"), ("Quadruped Flat", 26, 1.0, 0, "legged_coop"),
+    ("Walker", 31, 2.0, 3, "planar"), ("Quadruped Flat", 26, 1.0, 3, "legged")])
+def test_cuda_robust_planner_matches_oracle(oracle_lib, name, H, std, flavour, kernel):
+    run_isolated("tests.test_robust_planner", "check_cuda_robust_planner_matches_oracle", name, H, std, flavour, kernel)
 
 
-def check_cuda_robust_planner_matches_oracle(name, H, std):
+def check_cuda_robust_planner_matches_oracle(name, H, std, flavour, kernel):
     from mujoco_mpc_b200.planner import CudaRobustPlanner
     N, ncand, reps, rate = 64, 6, 4, 0.1
     model, task, s, o, out, state, z, w, nominal, interp = setup(name, N, H, ncand, reps, std, rate, seed=12)
     P = len(nominal[0])
-    pl = CudaRobustPlanner(model, task)
+    pl = CudaRobustPlanner(model, task, flavour=flavour)
     pl.configure(ncandidates=ncand, nrepetitions=reps, xfrc_std=std, xfrc_rate=rate)
     pl.delegate.configure(num_trajectory=N, interpolation=interp, num_spline_points=P, sigma0=s["exploration"], sigma1=0.0)
     pl.delegate.set_policy(nominal[0], nominal[1], interp)
@@ -127,6 +148,7 @@ def check_cuda_robust_planner_matches_oracle(name, H, std):
     pt, pk = pl.policy(); ot, ok_ = o.policy(0)
     assert np.array_equal(pt, ot) and np.allclose(pk, ok_, rtol=0, atol=1e-12)
     assert pl.delegate.winner == out["order"][out["best"]]
+    assert pl.reroll_kernel() == kernel, pl.reroll_kernel()
     pl.close()
 
 
