@@ -81,7 +81,7 @@ int ps_elite_update(PsEngine* e, int n_candidates, int n_elite, double* mean_kno
                     double* best_return, int* order);
 int ps_elite_update_ms(PsEngine* e, float* ms);
 /* pin the kernel flavour before ps_set_model: 0 auto (by batch size), 1 warp-per-rollout, 2 thread-per-rollout,
- * 3 dense thread-per-rollout (the one that carries force perturbations) */
+ * 3 dense thread-per-rollout.  Force perturbations (ps_rollout_candidates) exist for 1 (walker / quadruped class) and 3 */
 int ps_set_engine_flavour(PsEngine* e, int flavour);
 /* RobustPlanner's re-rolls (mjpc/planners/robust/robust_planner.cc:108-130 + Trajectory::NoisyRollout,
  * mjpc/trajectory.cc:100-210): candidate policies knots[n][P][nu] (knot times from ps_set_nominal), each rolled
