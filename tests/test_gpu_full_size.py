@@ -53,7 +53,7 @@ def prime(e, model, s, H, P, seed=77):
 
 @pytest.mark.parametrize("name,N,H", [("Cartpole", 65536, 101), ("Acrobot", 4096, 201), ("Particle", 4096, 51)])
 def test_full_size_determinism_sharding_and_argmin(name, N, H):
-    run_isolated("tests.test_gpu_full_size", "check_full_size_determinism_sharding_and_argmin", name, N, H)
+    run_isolated("tests.test_gpu_full_size", "check_full_size_determinism_sharding_and_argmin", name, N, H, timeout=300)
 
 
 def check_full_size_determinism_sharding_and_argmin(name, N, H):
@@ -88,7 +88,7 @@ def check_full_size_determinism_sharding_and_argmin(name, N, H):
     ("Walker", 4096, 41, ["warp", "thread"]),
     ("Quadruped Flat", 2048, 31, ["warp", "thread", "dense"])])
 def test_kernel_flavours_agree_bit_for_bit(name, N, H, flavours):
-    run_isolated("tests.test_gpu_full_size", "check_kernel_flavours_agree_bit_for_bit", name, N, H, flavours)
+    run_isolated("tests.test_gpu_full_size", "check_kernel_flavours_agree_bit_for_bit", name, N, H, flavours, timeout=300)
 
 
 def check_kernel_flavours_agree_bit_for_bit(name, N, H, flavours):
@@ -112,7 +112,7 @@ def check_kernel_flavours_agree_bit_for_bit(name, N, H, flavours):
 
 
 def test_quadruped_one_second_first_samples_match_oracle(oracle_lib):
-    run_isolated("tests.test_gpu_full_size", "check_quadruped_one_second_first_samples_match_oracle")
+    run_isolated("tests.test_gpu_full_size", "check_quadruped_one_second_first_samples_match_oracle", timeout=300)
 
 
 def check_quadruped_one_second_first_samples_match_oracle():

@@ -119,7 +119,7 @@ _unverified = pytest.mark.xfail(strict=False, reason="not yet run on a B200 (GPU
     ("Cartpole", 41, 0.5, 0, "tiny"), ("Walker", 31, 2.0, 0, "planar_coop"), ("Quadruped Flat", 26, 1.0, 0, "legged_coop"),
     ("Walker", 31, 2.0, 3, "planar"), ("Quadruped Flat", 26, 1.0, 3, "legged")])
 def test_cuda_robust_planner_matches_oracle(oracle_lib, name, H, std, flavour, kernel):
-    run_isolated("tests.test_robust_planner", "check_cuda_robust_planner_matches_oracle", name, H, std, flavour, kernel)
+    run_isolated("tests.test_robust_planner", "check_cuda_robust_planner_matches_oracle", name, H, std, flavour, kernel, timeout=240)
 
 
 def check_cuda_robust_planner_matches_oracle(name, H, std, flavour, kernel):
@@ -155,7 +155,7 @@ def check_cuda_robust_planner_matches_oracle(name, H, std, flavour, kernel):
 @pytest.mark.gpu
 @_unverified
 def test_cuda_robust_planner_device_noise_and_settings(oracle_lib):
-    run_isolated("tests.test_robust_planner", "check_cuda_robust_planner_device_noise_and_settings")
+    run_isolated("tests.test_robust_planner", "check_cuda_robust_planner_device_noise_and_settings", timeout=240)
 
 
 def check_cuda_robust_planner_device_noise_and_settings():
