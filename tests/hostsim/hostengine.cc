@@ -1,6 +1,6 @@
 // TEST INFRASTRUCTURE (not product): a host-compiled stand-in for the subset of the C ABI
 // (include/ps_engine.h) that the host planner classes call, so that CudaSamplingPlanner /
-// CudaRobustPlanner (mujoco_mpc_b200/host/*.cc, compiled unchanged) can be exercised against the
+// CudaCrossEntropyPlanner / CudaRobustPlanner (mujoco_mpc_b200/host/*.cc, compiled unchanged) can be exercised against the
 // oracle in this GPU-less container.  Rollouts run the engine's own kernel-source headers
 // (csrc/ps_*.cuh: rollout_sample<T, true> and <T, true, true>) through the host compiler, one sample
 // after the other; the knot perturbation restates K1 for INJECTED noise only (no generator here).
@@ -247,8 +247,38 @@ int ps_get_trajectory(PsEngine* e, int sample, double* states, double* actions, 
   if (failure) *failure = e->failure[sample] & 1;
   return 0;
 }
-// elite ranking / statistics (K4, K5) are device kernels with no host build: the cross-entropy host class is
-// covered on the GPU only
-int ps_elite_update(PsEngine*, int, int, double*, double*, double*, double*, int*) { return fail("ps_elite_update: not in the host stand-in"); }
+// K4 + K5 restated (csrc/ps_kernels_aux.cuh: rank_kernel, elite_stats_kernel): rank by (return, index), NaN last;
+// elite mean; the reference's variance formula (cross_entropy/planner.cc:224-262); average and best return
+int ps_elite_update(PsEngine* e, int n_candidates, int n_elite, double* mean_knots, double* variance, double* avg_return,
+                    double* best_return, int* order) {
+  if (e->N <= 0) return fail("ps_elite_update: no rollouts yet");
+  if (n_candidates < 1 || n_candidates > e->N || n_elite < 1 || n_elite > n_candidates) return fail("ps_elite_update: sizes out of range");
+  const int nelem = e->P * e->m->nu;
+  std::vector<double> r(n_candidates);
+  for (int i = 0; i < n_candidates; i++) r[i] = e->returns[i] == e->returns[i] ? e->returns[i] : 1.0e300;
+  std::vector<int> elite(n_elite, 0);
+  for (int i = 0; i < n_candidates; i++) {
+    int rank = 0;
+    for (int k = 0; k < n_candidates; k++) rank += (r[k] < r[i]) || (r[k] == r[i] && k < i);
+    if (rank < n_elite) elite[rank] = i;
+  }
+  double s = 0;
+  for (int k = 0; k < n_elite; k++) s += e->returns[elite[k]];
+  if (avg_return) *avg_return = s / n_elite;
+  if (best_return) *best_return = e->returns[elite[0]];
+  for (int el = 0; el < nelem; el++) {
+    double sum = 0;
+    for (int k = 0; k < n_elite; k++) sum += e->knots[(size_t)elite[k] * nelem + el];
+    const double avg = sum * (1.0 / n_elite);
+    const double diff = e->knots[(size_t)elite[0] * nelem + el] - avg;
+    double var = 0;
+    for (int k = 0; k < n_elite; k++) var += diff * diff / (n_elite - 1);
+    if (mean_knots) mean_knots[el] = avg;
+    if (variance) variance[el] = var;
+  }
+  if (order) for (int k = 0; k < n_elite; k++) order[k] = elite[k];
+  e->launches += 2;
+  return 0;
+}
 
 }  // extern "C"

@@ -128,3 +128,35 @@ def test_robust_planner_settings_and_single_candidate(hostlib):
     a = pl.ActionFromPolicy(0.3)
     assert np.array_equal(a, np.clip(k[0], model.actuator_ctrlrange[:, 0], model.actuator_ctrlrange[:, 1]))
     pl.close()
+
+
+@pytest.mark.parametrize("name,interp,N,n_elite", [("Particle", 2, 16, 4), ("Cartpole", 1, 20, 5), ("Walker", 2, 12, 3)])
+def test_cross_entropy_planner_matches_oracle(hostlib, name, interp, N, n_elite):
+    # the closed loop of tests/test_cross_entropy.py::test_gpu_cross_entropy_matches_oracle, on the host stand-in
+    model, task, s = registry.load(name)
+    H, P = min(s["steps"], 31), min(s["num_spline_points"], 36)
+    std_min = 0.5 * s["exploration"]
+    rng = np.random.default_rng(21)
+    pl = planner.CudaCrossEntropyPlanner(model, task)
+    pl.configure(num_trajectory=N, n_elite=n_elite, interpolation=interp, std_initial=s["exploration"], std_min=std_min)
+    pl.Reset(H)
+    o = pyoracle.Oracle(model, task); o.configure(P, interp, s["exploration"]); o.ce_configure(std_min, n_elite)
+    times = np.linspace(0, (H - 1) * s["timestep"], P); knots = np.zeros((P, model.nu))
+    pl.set_policy(times, knots, interp); o.set_policy(times, knots, interp)
+    state = synthetic_state(model); t = 0.0
+    for it in range(4):
+        z = rng.standard_normal((N, P, model.nu))
+        pl.SetState(state, t); pl.SetNoise(z); pl.OptimizePolicy(H)
+        o.set_state(state, t); out = o.ce_optimize(N, H, z)
+        assert np.array_equal(pl.order(n_elite), out["order"][:n_elite]), it
+        gt, gk = pl.policy(0); ot, ok = o.policy(0)
+        assert np.array_equal(gt, ot) and np.array_equal(gk, ok), it
+        assert np.array_equal(pl.variance(P), out["variance"][:P]), it
+        assert pl.avg_return == out["avg_return"] and pl.improvement == out["improvement"]
+        for tq in (t, t + 0.017, t + 9.0):
+            assert np.array_equal(pl.ActionFromPolicy(tq), o.action(tq))
+        bt = pl.BestTrajectory()      # the NOMINAL trajectory (cross_entropy/planner.cc:426-428)
+        assert bt["total_return"] == out["nominal_return"]
+        best = o.trajectory(int(out["order"][0]))
+        state = best["states"][2].copy(); t = best["times"][2]
+    pl.close()
