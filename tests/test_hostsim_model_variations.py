@@ -136,3 +136,16 @@ SMALL = [
 @pytest.mark.parametrize("name,what,edits,integrator", SMALL, ids=[f"{s[0]}: {s[1]}" for s in SMALL])
 def test_small_model_variations(hostsim_lib, name, what, edits, integrator):
     vary(name, edits, integrator=integrator, H=50, coop=False, compare=not (name == "Particle" and integrator == IMPLICITFAST))
+
+
+@pytest.mark.parametrize("block", range(4))
+def test_random_parameter_sets(hostsim_lib, block):
+    # random rescalings of friction / damping / masses / inertias / armature under strong control noise and long
+    # horizons (falls, many contacts, limit hits): walker and quadruped, both codings, 15 parameter sets per block
+    for seed in range(15 * block, 15 * (block + 1)):
+        rng = np.random.default_rng(1000 + seed)
+        f = lambda lo, hi: (lambda a, r=rng.uniform(lo, hi): a * r)                      # noqa: E731
+        edits = dict(geom_friction=f(0.3, 1.5), dof_damping=f(0.2, 4.0), body_mass=f(0.6, 1.6), body_inertia=f(0.6, 1.6),
+                     dof_armature=lambda a, r=rng.uniform(0, 0.05): a + r)
+        vary("Walker", edits, H=120, N=3, sigma=0.8, coop=True, seed=seed, compare=False)
+        vary("Quadruped Flat", edits, H=60, N=3, sigma=0.3, coop=True, seed=seed, compare=False)
