@@ -29,13 +29,17 @@ def lib():
     if _LIB is None:
         if not os.path.exists(LIB_PATH):
             raise EngineError(f"{LIB_PATH} not built (run python mujoco_mpc_b200/build.py); there is no CPU fallback")
-        L = ctypes.CDLL(LIB_PATH)
-        L.ps_last_error.restype = ctypes.c_char_p
-        L.ps_create.restype = ctypes.c_void_p
-        L.ps_create.argtypes = [ctypes.c_int]
-        L.ps_destroy.argtypes = [ctypes.c_void_p]
-        _LIB = L
+        _LIB = prototype(ctypes.CDLL(LIB_PATH))
     return _LIB
+
+
+def prototype(L):
+    """pointer-typed signatures of the handle functions (also used by the CPU test-suite on its host stand-in)"""
+    L.ps_last_error.restype = ctypes.c_char_p
+    L.ps_create.restype = ctypes.c_void_p
+    L.ps_create.argtypes = [ctypes.c_int]
+    L.ps_destroy.argtypes = [ctypes.c_void_p]
+    return L
 
 
 def _p(a):

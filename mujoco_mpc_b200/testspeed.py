@@ -4,10 +4,14 @@ CudaSamplingPlanner, and the plant's `mj_step` is the same device forward step, 
 rollout with writeback between planning iterations (BASELINE.json
 configs[0] is `testspeed --task=Cartpole` semantics).
 
-Loop, per plant step i (testspeed.cc:96-113): action = ActionFromPolicy(state, time); mj_step; cost =
-CostValue(sensordata); every `steps_per_planning_iteration` steps PlanIteration (agent.cc:270-315:
-SetState, steps = clamp(horizon / agent_timestep + 1, 1, 512), OptimizePolicy).  Tasks whose
-Transition() is the base no-op are covered (cartpole, acrobot, swimmer, walker).
+Loop, per plant step i (testspeed.cc:95-113): Transition; agent.state.Set(data) -- the state BEFORE the step;
+action = ActionFromPolicy(state, time); mj_step; cost = CostValue(sensordata); after every
+`steps_per_planning_iteration`-th step PlanIteration (agent.cc:270-315: planner.SetState(agent.state) -- still
+the pre-step state --, steps = clamp(horizon / agent_timestep + 1, 1, 512), OptimizePolicy).  Covered: the tasks
+whose Transition() is the base no-op (cartpole, acrobot, swimmer, walker) and Particle (Transition moves the goal
+mocap along a Lissajous curve, particle.cc:58-65).  One deviation: the plant runs as one launch per planning
+period, and a launch starts its constraint solver from a zero warm start where the reference's mjData carries
+qacc_warmstart over -- the same solution to solver tolerance (last-bit differences on the contact tasks).
 
     python -m mujoco_mpc_b200.testspeed --task Cartpole --steps_per_planning_iteration 4 --total_time 10
 """
@@ -27,6 +31,26 @@ def plant_model(name):
     """The model as the plant sees it: the XML's own opt.timestep / integrator (the agent overrides only
     touch the Agent's private copy, agent.cc:74,275-276)."""
     return mjcf.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "tasks", registry.TASKS[name]))
+
+
+def _model_mocap(model):
+    out = np.zeros((max(model.nmocap, 1), 7))
+    for b in range(model.nbody):
+        i = int(model.body_mocapid[b])
+        if i >= 0:
+            out[i, :3] = np.asarray(model.body_pos).reshape(-1, 3)[b]
+            out[i, 3:] = np.asarray(model.body_quat).reshape(-1, 4)[b]
+    return out
+
+
+def transition_mocap(task_name, model, time):
+    """Task::Transition() as far as it reaches the planner: the mocap poses [nmocap][7] at `time` (None: no mocap)."""
+    if model.nmocap == 0:
+        return None
+    mo = _model_mocap(model)
+    if task_name == "Particle":                      # particle.cc:58-65: x, y of the goal follow a Lissajous curve
+        mo[0, 0] = 0.25 * math.sin(time); mo[0, 1] = 0.25 * math.cos(time / math.pi)
+    return mo.reshape(-1)
 
 
 def synchronous_planning_cost(task_name, steps_per_planning_iteration=4, total_time=10.0, num_trajectory=None,
@@ -57,11 +81,13 @@ def synchronous_planning_cost(task_name, steps_per_planning_iteration=4, total_t
         times, knots = pl.policy()
         if len(times) == 0:
             times, knots = np.zeros(1), np.zeros((1, model.nu))
-        plant.set_state(state, t)
+        plant.set_state(state, t, mocap=transition_mocap(task_name, pm, t))
         plant.set_nominal(times, knots, interp)
         plant.rollouts(1, k + 1, 0.0, writeback=True)
         tr = plant.trajectory(0)
         total_cost += float(np.sum(tr["costs"][:k]))
+        # agent.state was captured BEFORE the last step (testspeed.cc:97 precedes mj_step): that is what plans
+        plan_state = tr["states"][k - 1].copy(); plan_time = float(tr["times"][k - 1])
         state = tr["states"][k].copy(); t = float(tr["times"][k])
         last = i + k - 1
         i += k
@@ -69,7 +95,7 @@ def synchronous_planning_cost(task_name, steps_per_planning_iteration=4, total_t
             p0 = _time.perf_counter()
             if noise is not None:
                 pl.SetNoise(noise(plans, N, P, model.nu))
-            pl.SetState(state, t)
+            pl.SetState(plan_state, plan_time, mocap=transition_mocap(task_name, model, plan_time))
             pl.OptimizePolicy(s["steps"])
             plan_s += _time.perf_counter() - p0
             plans += 1

@@ -195,6 +195,14 @@ int ps_rollouts(PsEngine* e, int N, int H, double sigma0, double sigma1, int sam
   return 0;
 }
 
+// the stand-in always keeps every sample's trajectory
+int ps_rollouts_writeback(PsEngine* e, int N, int H, double sigma0, double sigma1, int sample_offset, int* winner,
+                          double* winner_return, double* nominal_return) {
+  return ps_rollouts(e, N, H, sigma0, sigma1, sample_offset, winner, winner_return, nominal_return);
+}
+int ps_variant(PsEngine*, char* out, int cap) { std::snprintf(out, cap, "host stand-in"); return 0; }
+int ps_kernel_launch_count(PsEngine* e, long long* launches) { if (launches) *launches = e->launches; return 0; }
+
 int ps_rollout_candidates(PsEngine* e, const double* knots, int n, int repetitions, int H, double xfrc_std, double xfrc_rate,
                           const double* z, double* returns, unsigned char* failure) {
   if (n < 1 || repetitions < 1) return fail("ps_rollout_candidates: bad sizes");

@@ -160,3 +160,33 @@ def test_cross_entropy_planner_matches_oracle(hostlib, name, interp, N, n_elite)
         best = o.trajectory(int(out["order"][0]))
         state = best["states"][2].copy(); t = best["times"][2]
     pl.close()
+
+
+@pytest.mark.parametrize("task_name,interp,N,steps", [("Cartpole", 0, 10, 60), ("Acrobot", 2, 8, 24), ("Particle", 2, 8, 24),
+                                                    ("Swimmer", 2, 6, 16), ("Walker", 2, 6, 16)])
+def test_testspeed_closed_loop_matches_oracle(hostlib, monkeypatch, task_name, interp, N, steps):
+    # mujoco_mpc_b200/testspeed.py (planner AND plant behind the C ABI) on the host stand-in, against the reference's
+    # testspeed loop restated on the oracle (tests/common.py: oracle_closed_loop); the GPU run of the same loop is
+    # tests/test_testspeed_closed_loop.py
+    from mujoco_mpc_b200 import engine
+    from mujoco_mpc_b200.testspeed import plant_model, synchronous_planning_cost
+    from tests.common import oracle_closed_loop
+    monkeypatch.setattr(engine, "_LIB", engine.prototype(hostlib))
+    cache = {}
+
+    def noise(k, n, P, nu):
+        if k not in cache:
+            cache[k] = np.random.default_rng(1000 + k).standard_normal((n, P, nu))
+        return cache[k]
+    total_time = steps * plant_model(task_name).opt_timestep
+    g = synchronous_planning_cost(task_name, steps_per_planning_iteration=4, total_time=total_time, num_trajectory=N, interpolation=interp, noise=noise)
+    o = oracle_closed_loop(task_name, 4, total_time, N, interp, noise)
+    assert g["plans"] == o["plans"] == steps // 4
+    assert g["time"] == o["time"]
+    if task_name == "Walker":
+        # contacts: the plant's solver warm start restarts from zero at every launch boundary (each planning period),
+        # where the reference's mjData carries it over -- same fixed point, last-bit differences
+        assert np.abs(g["state"] - o["state"]).max() <= 1e-9
+    else:
+        assert np.array_equal(g["state"], o["state"])
+    assert abs(g["total_cost"] - o["total_cost"]) <= 1e-13 * max(1.0, abs(o["total_cost"]))      # summed in segments there

@@ -2,41 +2,16 @@
 Cartpole -- 10 samples, 1 s horizon, zero-order spline -- with planner AND plant on the B200
 (mujoco_mpc_b200/testspeed.py), against the same loop restated on the oracle under the same injected
 noise: total cost, final state and every planned policy must agree."""
-import math
 import numpy as np
 import pytest
-from mujoco_mpc_b200 import registry, task as T
-from oracle import pyoracle
 
 pytestmark = pytest.mark.gpu
 
 
-def oracle_closed_loop(task_name, spp, total_time, N, interp, noise):
-    from mujoco_mpc_b200.testspeed import plant_model
-    model, task, s = registry.load(task_name)
-    pm = plant_model(task_name)
-    ptask = T.make_task(pm, registry._TASK_ID_NAME.get(task_name, task_name))
-    P = min(s["num_spline_points"], 36)
-    planner = pyoracle.Oracle(model, task); planner.configure(P, interp, s["exploration"])
-    planner.set_policy(np.zeros(1), np.zeros((1, model.nu)), interp)       # agent.Reset(data->ctrl)
-    plant = pyoracle.Oracle(pm, ptask)
-    st = registry.home_state(pm)
-    plant.reset_data(); plant.set("qpos", st[:pm.nq]); plant.set("qvel", st[pm.nq:pm.nq + pm.nv]); plant.set("time", [0.0])
-    total_steps = int(math.ceil(total_time / pm.opt_timestep)); total = 0.0; plans = 0
-    for i in range(total_steps):
-        t = plant.get("time")[0]
-        plant.set("ctrl", planner.action(t))
-        plant.step()
-        total += plant.cost(plant.get("sensordata")[:ptask.num_residual])
-        if i % spp == 0:
-            state = np.concatenate([plant.get("qpos")[:pm.nq], plant.get("qvel")[:pm.nv]])
-            planner.set_state(state, plant.get("time")[0])
-            planner.optimize(N, s["steps"], noise(plans, N, P, model.nu)); plans += 1
-    state = np.concatenate([plant.get("qpos")[:pm.nq], plant.get("qvel")[:pm.nv]])
-    return dict(total_cost=total, state=state, time=plant.get("time")[0], plans=plans, policy=planner.policy(0))
+from tests.common import oracle_closed_loop  # noqa: E402
 
 
-@pytest.mark.parametrize("task_name,interp,N", [("Cartpole", 0, 10), ("Acrobot", 2, 16)])
+@pytest.mark.parametrize("task_name,interp,N", [("Cartpole", 0, 10), ("Acrobot", 2, 16), ("Particle", 2, 16)])
 def test_testspeed_closed_loop_matches_oracle(oracle_lib, task_name, interp, N):
     from mujoco_mpc_b200.testspeed import synchronous_planning_cost
     cache = {}
