@@ -56,6 +56,11 @@ for name, N in (("Cartpole", 1024), ("Walker", 1024), ("Quadruped Flat", 1024)):
 EOF
 cat "$out/robust_latency.log"
 
+step "5b. trajectory writeback bandwidth (north_star evidence item)"
+timeout 600 python tools/writeback_bandwidth.py --task Cartpole --samples 65536 --horizon 101 > "$out/writeback_bandwidth.log" 2>&1
+timeout 600 python tools/writeback_bandwidth.py --task Walker --samples 16384 --horizon 41 >> "$out/writeback_bandwidth.log" 2>&1
+cat "$out/writeback_bandwidth.log"
+
 step "6. ncu launch list of the default bench (kernel share of the step)"
 timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file "$out/launches_default.csv" \
   python bench.py --steps 2 --warmup 3 --no-cpu-baseline > "$out/ncu_launches.log" 2>&1
