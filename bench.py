@@ -290,6 +290,15 @@ def main():
         traffic = sum(dram.get(c["name"], float("nan")) * c["N"] * (c["H"] - 1) for c in cases)
         traffic = None if traffic != traffic else traffic
         achieved = alg / (rollout_ms * 1e-3) / 1e12 if alg else None
+        # the same kernel against HBM: its measured DRAM traffic (mostly the thread-private working set of the larger
+        # models spilling) over its duration, as a fraction of the measured copy bandwidth (MEASURED_PEAKS.json)
+        hbm_peak = None
+        try:
+            with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+                hbm_peak = float(json.load(f)["hbm_gbs"])
+        except Exception:
+            pass
+        traffic_gbs = traffic / (rollout_ms * 1e-3) / 1e9 if (traffic and rollout_ms > 0) else None
         line = {"metric": METRIC, "value": value, "unit": "sample-steps/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
                 "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
                 "data": "synthetic", "config": {"workload": args.workload, "samples_per_gpu": [c["N"] for c in cases],
@@ -301,7 +310,9 @@ def main():
                         "latency_ms": e2e_s * 1e3},
                 "gpu_launches": int(launches), "clocks": clocks,
                 "roofline": {"bound": "fp64", "achieved": achieved, "peak": peak, "unit": "TFLOP/s", "frac": (achieved / peak) if achieved else None,
-                             "traffic": traffic, "traffic_unit": "bytes per step (sum of the step's rollout launches)", "peak_source": "DFMA probe measured in this run (MEASURED_PEAKS.json has no FP64 figure)"}}
+                             "traffic": traffic, "traffic_unit": "bytes per step (sum of the step's rollout launches)", "peak_source": "DFMA probe measured in this run (MEASURED_PEAKS.json has no FP64 figure)",
+                             "traffic_gbs": traffic_gbs, "hbm_peak_gbs": hbm_peak,
+                             "traffic_frac_of_hbm": (traffic_gbs / hbm_peak) if (traffic_gbs and hbm_peak) else None}}
         if not args.no_cpu_baseline and world == 1:
             from oracle import pyoracle
             pyoracle.build()
