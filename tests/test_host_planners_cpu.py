@@ -190,3 +190,39 @@ def test_testspeed_closed_loop_matches_oracle(hostlib, monkeypatch, task_name, i
     else:
         assert np.array_equal(g["state"], o["state"])
     assert abs(g["total_cost"] - o["total_cost"]) <= 1e-13 * max(1.0, abs(o["total_cost"]))      # summed in segments there
+
+
+def test_reference_robust_planner_test_random_search(hostlib):
+    # mjpc/test/planners/robust/robust_planner_test.cc:47-127 re-expressed: particle_task.xml, keyframe "ctrl_test",
+    # Reset() with the keyframe's ctrl, dt 0.1, 26 steps, default robust settings (2 candidates x 5 repetitions,
+    # xfrc 0.1), 1000 iterations from the same state; same expectations.  Noise is numpy's (the stand-in has no
+    # generator); the reference draws from absl, so only the test's own tolerances are comparable.
+    import os
+    from mujoco_mpc_b200 import mjcf
+    m = mjcf.load(os.path.join(os.path.dirname(__file__), "fixtures", "particle_task.xml"))
+    m.v["opt_timestep"] = 0.1; m._c = None
+    t = T.make_task(m, "ParticleTest")
+    pl = planner.CudaRobustPlanner(m, t)
+    st = pl.settings()
+    assert (st["ncandidates"], st["nrepetitions"], st["xfrc_std"], st["xfrc_rate"]) == (2, 5, 0.1, 0.1)
+    key = m.name2id("key", "ctrl_test")
+    pl.Reset(512, m.key_ctrl[key])
+    a = pl.ActionFromPolicy(2.0)                       # "some arbitrary, hard-coded time"
+    assert abs(a[0] - 0.1) < 1e-4 and abs(a[1] - 0.2) < 1e-4
+    steps = int(max(min(2.5 / 0.1 + 1, 512), 1))
+    state = np.concatenate([m.key_qpos[key], m.key_qvel[key]])
+    mocap = model_mocap(m)
+    pl.SetState(state, 0.0, mocap=mocap)
+    rng = np.random.default_rng(0)
+    N, P = 10, 1                                       # sampling_trajectories default; the plan Reset() left: one node
+    for _ in range(1000):
+        pl.delegate.SetNoise(rng.standard_normal((N, P, m.nu)))
+        pl.SetForceNoise(rng.standard_normal((2 * 5, steps - 1, 6 * m.nbody)), steps)
+        pl.OptimizePolicy(steps)
+    bt = pl.BestTrajectory()
+    final = bt["states"][steps - 1]
+    assert abs(final[0] - mocap[0]) < 1e-1 and abs(final[1] - mocap[1]) < 1e-1
+    assert abs(final[2]) < 1e-1 and abs(final[3]) < 1e-1
+    lo, hi = m.actuator_ctrlrange[:, 0], m.actuator_ctrlrange[:, 1]
+    assert np.all(bt["actions"][:steps - 1] <= hi) and np.all(bt["actions"][:steps - 1] >= lo)
+    pl.close()
