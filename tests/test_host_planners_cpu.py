@@ -226,3 +226,61 @@ def test_reference_robust_planner_test_random_search(hostlib):
     lo, hi = m.actuator_ctrlrange[:, 0], m.actuator_ctrlrange[:, 1]
     assert np.all(bt["actions"][:steps - 1] <= hi) and np.all(bt["actions"][:steps - 1] >= lo)
     pl.close()
+
+
+def _particle_fixture(timestep=None):
+    import os
+    from mujoco_mpc_b200 import mjcf
+    m = mjcf.load(os.path.join(os.path.dirname(__file__), "fixtures", "particle_task.xml"))
+    if timestep:
+        m.v["opt_timestep"] = timestep; m._c = None
+    return m, T.make_task(m, "ParticleTest")
+
+
+def test_reference_sampling_planner_test_random_search(hostlib):
+    # mjpc/test/sampling_planner/sampling_planner_test.cc:44-113 re-expressed on the stand-in (numpy noise): dt 0.1,
+    # 26 steps, 10 samples, exploration 0.01, 1000 iterations from the same state; the test's own expectations
+    m, t = _particle_fixture(timestep=0.1)
+    pl = planner.CudaSamplingPlanner(m, t)
+    pl.configure(sigma0=0.01)
+    steps = int(max(min(2.5 / 0.1 + 1, 512), 1))
+    mocap = model_mocap(m)
+    pl.SetState(np.zeros(4), 0.0, mocap=mocap)
+    rng = np.random.default_rng(3)
+    P = 11                                              # sampling_spline_points of the fixture
+    for _ in range(1000):
+        pl.SetNoise(rng.standard_normal((10, P, m.nu)))
+        pl.OptimizePolicy(steps)
+    bt = pl.BestTrajectory()
+    final = bt["states"][steps - 1]
+    assert abs(final[0] - mocap[0]) < 1e-1 and abs(final[1] - mocap[1]) < 1e-1 and abs(final[2]) < 1e-1 and abs(final[3]) < 1e-1
+    assert np.all(bt["actions"][:steps - 1] <= 1.0) and np.all(bt["actions"][:steps - 1] >= -1.0)
+    pl.close()
+
+
+def test_reference_rollout_test_residual_state_alignment(hostlib):
+    # mjpc/test/agent/rollout_test.cc:127-144: for the copy-residual task residual[t] == states[t] (minus the goal in the
+    # position block): the residual is evaluated at the PRE-step state
+    m, t = _particle_fixture()
+    pl = planner.CudaSamplingPlanner(m, t)
+    pl.configure(num_trajectory=4, sigma0=0.3)
+    st = np.array([0.05, -0.02, 0.3, -0.1]); mocap = np.array([0.1, 0.2, 0.01, 1, 0, 0, 0.0])
+    pl.SetNoise(np.random.default_rng(1).standard_normal((4, 11, m.nu)))
+    pl.SetState(st, 0.0, mocap=mocap); pl.OptimizePolicy(100)
+    bt = pl.BestTrajectory()
+    expect = bt["states"].copy(); expect[:, 0] -= 0.1; expect[:, 1] -= 0.2
+    assert np.abs(expect - bt["residual"]).sum() < 1e-5
+    pl.close()
+
+
+def test_reference_agent_test_previous_policy(hostlib):
+    # mjpc/test/agent/agent_test.cc:204-262: ActionFromPolicy(use_previous=true) returns the pre-iteration policy exactly
+    m, t = _particle_fixture(timestep=0.1)
+    pl = planner.CudaSamplingPlanner(m, t); pl.configure(num_trajectory=16)
+    rng = np.random.default_rng(5)
+    pl.SetNoise(rng.standard_normal((16, 11, m.nu))); pl.SetState(np.zeros(4), 0.0); pl.OptimizePolicy(51)
+    before = [pl.ActionFromPolicy(tq) for tq in (0.0, 0.1, 0.2)]
+    pl.SetNoise(rng.standard_normal((16, 11, m.nu))); pl.SetState(np.zeros(4), 0.0); pl.OptimizePolicy(51)
+    for a, tq in zip(before, (0.0, 0.1, 0.2)):
+        assert np.array_equal(a, pl.ActionFromPolicy(tq, use_previous=True))
+    pl.close()
