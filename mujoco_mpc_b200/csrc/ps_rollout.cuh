@@ -20,6 +20,10 @@ struct Writeback {
 // Ornstein-Uhlenbeck coefficients rate = exp(-dt / xfrc_rate), scale = xfrc_std sqrt(1 - rate^2) (trajectory.cc:149-151)
 struct XfrcNoise { const double* z; double rate, scale; };
 
+#ifndef PS_ROLLOUT_SINGLE_SITE
+#define PS_ROLLOUT_SINGLE_SITE 0
+#endif
+
 // Per-rollout perturbation state.  The planning kernels instantiate the empty one (their forward pass is the plain
 // forward_pass they were verified with); robust_rollout_kernel instantiates the one that carries
 // mjData.xfrc_applied ([force; torque] per body) through the Ornstein-Uhlenbeck recursion of trajectory.cc:147-155.
@@ -61,6 +65,46 @@ PS_FN double rollout_sample(const DevModel<T>& m, const DevTask& task, const Dev
   if (WB) { for (int k = 0; k < ns; k++) wb.states[(size_t)k * stride + i] = plan.state[k]; wb.times[i] = d.time; }
   Perturbation<T, XF> pert(m, xf);
 
+#if PS_ROLLOUT_SINGLE_SITE
+  // Experiment (off by default): ONE call site of the forward pass / residual / cost for the running steps and the
+  // terminal step, instead of a loop plus a terminal copy.  Where the stage functions are inlined (tiny, planar)
+  // the terminal copy duplicates the whole step in the instruction stream, and the tiny kernel is bound by
+  // instruction fetch.  Same arithmetic in the same order.
+  for (int t = 0; t < H; t++) {
+    const bool terminal = t == H - 1;
+    if (!terminal) {
+      spline_sample(plan.spline_times, P, nu, plan.interpolation, d.time, kn, d.ctrl);
+      for (int a = 0; a < nu; a++) d.ctrl[a] = clampd(d.ctrl[a], m.act_ctrlrange[2 * a], m.act_ctrlrange[2 * a + 1]);
+      pert.advance(m, t, stride, i);
+    }
+    // terminal: ctrl is NOT rewritten before the final forward pass (trajectory.cc:190-198)
+    if (WB && (!terminal || H > 1)) for (int a = 0; a < nu; a++) wb.actions[((size_t)t * nu + a) * stride + i] = d.ctrl[a];
+    if (!terminal && state_is_bad(m, d)) { failed = true; break; }
+    pert.forward(m, d);
+    task_residual(m, d, task, residual);
+    const double c = cost_value(task, residual);
+    if (WB) {
+      for (int k = 0; k < nr; k++) wb.residual[((size_t)t * nr + k) * stride + i] = residual[k];
+      wb.costs[(size_t)t * stride + i] = c;
+      for (int k = 0; k < task.num_trace; k++) {
+        double tr[3]; read_sensor(m, d, task.trace_sensor[k], tr);
+        for (int x = 0; x < 3; x++) wb.trace[((size_t)t * ntr + 3 * k + x) * stride + i] = tr[x];
+      }
+    }
+    if (terminal) { sum += c; break; }
+    if (acc_is_bad(m, d) || (d.warning & (WARN_BADQPOS | WARN_BADQVEL | WARN_BADQACC | WARN_BADCTRL))) { failed = true; break; }
+    sum += c;
+    integrate(m, d);
+    if (WB) {
+      double* s = wb.states + ((size_t)(t + 1) * ns) * stride + i;
+      for (int k = 0; k < nq; k++) s[(size_t)k * stride] = d.qpos[k];
+      for (int k = 0; k < nv; k++) s[(size_t)(nq + k) * stride] = d.qvel[k];
+      for (int k = 0; k < na; k++) s[(size_t)(nq + nv + k) * stride] = d.act[k];
+      wb.times[(size_t)(t + 1) * stride + i] = d.time;
+    }
+  }
+  const double total = failed ? 1.0e6 : sum / (H > 1 ? H : 1);
+#else
   for (int t = 0; t < H - 1; t++) {
     spline_sample(plan.spline_times, P, nu, plan.interpolation, d.time, kn, d.ctrl);
     for (int a = 0; a < nu; a++) d.ctrl[a] = clampd(d.ctrl[a], m.act_ctrlrange[2 * a], m.act_ctrlrange[2 * a + 1]);
@@ -107,6 +151,7 @@ PS_FN double rollout_sample(const DevModel<T>& m, const DevTask& task, const Dev
     sum += c;
     total = sum / (H > 1 ? H : 1);
   } else total = 1.0e6;
+#endif
   *flags = (failed ? 1 : 0) | ((d.warning & WARN_CAPACITY) ? 2 : 0);
   return total;
 }

@@ -7,7 +7,11 @@ import subprocess
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-_LIB = os.path.join(_HERE, "libhostsim.so")
+# PS_HOSTSIM_DEFINES="-DPS_ROLLOUT_SINGLE_SITE=1 ..." builds (and tests) an experimental configuration of the kernel
+# source next to the default one
+_EXTRA = os.environ.get("PS_HOSTSIM_DEFINES", "").split()
+_TAG = ("_" + "".join(c if c.isalnum() else "_" for c in "".join(_EXTRA))) if _EXTRA else ""
+_LIB = os.path.join(_HERE, f"libhostsim{_TAG}.so")
 _CSRC = os.path.join(_HERE, "..", "..", "mujoco_mpc_b200", "csrc")
 
 
@@ -16,7 +20,7 @@ def build(force=False):
     deps = [src] + [os.path.join(_CSRC, f) for f in os.listdir(_CSRC) if f.endswith((".cuh", ".h"))]
     if not force and os.path.exists(_LIB) and all(os.path.getmtime(_LIB) >= os.path.getmtime(d) for d in deps):
         return _LIB
-    cmd = ["g++", "-std=c++17", "-O2", "-ffp-contract=off", "-fPIC", "-shared", "-x", "c++", src, "-o", _LIB]
+    cmd = ["g++", "-std=c++17", "-O2", "-ffp-contract=off", "-fPIC", "-shared"] + _EXTRA + ["-x", "c++", src, "-o", _LIB]
     subprocess.run(cmd, check=True)
     return _LIB
 
@@ -26,13 +30,13 @@ def build_planner_host(force=False):
     against hostengine.cc, the host-compiled stand-in of the engine ABI.  -Bsymbolic keeps its ps_* references
     inside the library even when the real libps_engine.so is loaded in the same process."""
     hdir = os.path.join(_HERE, "..", "..", "mujoco_mpc_b200", "host")
-    out = os.path.join(_HERE, "libps_planner_host.so")
+    out = os.path.join(_HERE, f"libps_planner_host{_TAG}.so")
     srcs = [os.path.join(_HERE, "hostengine.cc")] + [os.path.join(hdir, f) for f in sorted(os.listdir(hdir)) if f.endswith(".cc")]
     deps = srcs + [os.path.join(hdir, f) for f in os.listdir(hdir) if f.endswith(".h")] + \
         [os.path.join(_CSRC, f) for f in os.listdir(_CSRC) if f.endswith((".cuh", ".h"))]
     if not force and os.path.exists(out) and all(os.path.getmtime(out) >= os.path.getmtime(d) for d in deps):
         return out
-    cmd = ["g++", "-std=c++17", "-O2", "-ffp-contract=off", "-fPIC", "-shared", "-Wl,-Bsymbolic", "-o", out]
+    cmd = ["g++", "-std=c++17", "-O2", "-ffp-contract=off", "-fPIC", "-shared", "-Wl,-Bsymbolic"] + _EXTRA + ["-o", out]
     for s in srcs:
         cmd += ["-x", "c++", s]
     subprocess.run(cmd + ["-lpthread"], check=True)
