@@ -64,4 +64,18 @@ cat "$out/writeback_bandwidth.log"
 step "6. ncu launch list of the default bench (kernel share of the step)"
 timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file "$out/launches_default.csv" \
   python bench.py --steps 2 --warmup 3 --no-cpu-baseline > "$out/ncu_launches.log" 2>&1
+step "7. prepared experiment: single call site of the per-step work (rebuilds the engine IN THIS BOX COPY only; last step)"
+timeout 900 python -c "from mujoco_mpc_b200 import build; build.build(force=True, extra=['-DPS_ROLLOUT_SINGLE_SITE=1'])" > "$out/exp_single_site_build.log" 2>&1
+timeout 600 python -m pytest tests/test_gpu_parity.py -m gpu -q > "$out/exp_single_site_pytest.log" 2>&1; tail -3 "$out/exp_single_site_pytest.log"
+timeout 600 python bench.py --no-cpu-baseline > "$out/exp_single_site_bench_default.json" 2>> "$out/exp_single_site_build.log"
+timeout 600 python bench.py --workload cartpole_65536_1s --steps 20 --warmup 3 --no-cpu-baseline > "$out/exp_single_site_bench_cartpole.json" 2>> "$out/exp_single_site_build.log"
+python - <<'PY'
+import json
+for w in ("default", "cartpole"):
+    try:
+        a = json.load(open(f"gpurun_out/first_call/bench_{w}.json")); b = json.load(open(f"gpurun_out/first_call/exp_single_site_bench_{w}.json"))
+        print(f"{w}: {a['value']:.4g} -> {b['value']:.4g} sample-steps/s ({b['value'] / a['value']:.3f}x) with PS_ROLLOUT_SINGLE_SITE")
+    except Exception as e:
+        print(w, "n/a", e)
+PY
 echo done | tee -a "$out/steps.log"
