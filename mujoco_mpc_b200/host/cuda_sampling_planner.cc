@@ -113,6 +113,14 @@ void CudaSamplingPlanner::SetNoise(const double* z, const unsigned char* use_std
   }
 }
 void CudaSamplingPlanner::SetSeed(unsigned long long seed) { ps_set_seed(engine_, seed); }
+// Replaces the nominal AND the policy the next UpdateNominalPolicy resamples from (candidate_policy[winner]).
+void CudaSamplingPlanner::SetPolicy(const double* times, const double* knots, int P, int interpolation) {
+  std::unique_lock<std::shared_mutex> lock(mtx_);
+  interpolation_ = interpolation;
+  policy.plan = TimeSpline(model_->nu, (SplineInterpolation)interpolation);
+  for (int k = 0; k < P; k++) policy.plan.AddNode(times[k], knots + (size_t)k * model_->nu);
+  candidate_winner_.plan = policy.plan;
+}
 void CudaSamplingPlanner::SetSharding(int rank, int world, AllGatherFn fn, void* ctx) {
   rank_ = rank; world_ = world; gather_ = fn; gather_ctx_ = ctx;
 }

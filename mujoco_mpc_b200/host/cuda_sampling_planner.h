@@ -64,6 +64,7 @@ class CudaSamplingPlanner {
   // ---- engine-specific controls
   void SetNoise(const double* z, const unsigned char* use_std2, int N);   // injected N(0,1) tensor (parity runs)
   void SetSeed(unsigned long long seed);
+  void SetPolicy(const double* times, const double* knots, int P, int interpolation);   // start from a given nominal (parity runs)
   void SetSharding(int rank, int world, AllGatherFn fn, void* ctx);       // samples [rank*N, (rank+1)*N) of world*N
   PsEngine* engine() { return engine_; }
   const SamplingPolicy& CandidatePolicy(int candidate) const { return ranked_[candidate]; }   // candidate_policy[trajectory_order[c]]

@@ -173,10 +173,7 @@ extern "C" {
 
 // parity runs start from a given nominal spline instead of the Reset() one
 void psp_set_policy(void* h, const double* times, const double* knots, int P, int interpolation) {
-  CudaSamplingPlanner* p = (CudaSamplingPlanner*)h;
-  p->interpolation_ = interpolation;
-  p->policy.plan = mjpc_b200::TimeSpline(p->model()->nu, (mjpc_b200::SplineInterpolation)interpolation);
-  for (int k = 0; k < P; k++) p->policy.plan.AddNode(times[k], knots + (size_t)k * p->model()->nu);
+  ((CudaSamplingPlanner*)h)->SetPolicy(times, knots, P, interpolation);
 }
 
 void* prb_create(const PsModel* model, const PsTask* task, int device) {

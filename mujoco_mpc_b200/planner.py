@@ -90,6 +90,11 @@ class CudaSamplingPlanner:
     def SetSeed(self, seed):
         self.L.psp_set_seed(self.h, ctypes.c_ulonglong(seed))
 
+    def set_policy(self, times, knots, interp):
+        """start from a given nominal spline instead of the Reset() one (parity runs)"""
+        t = _arr(times); k = _arr(knots)
+        self.L.psp_set_policy(self.h, _p(t), _p(k), len(t), int(interp))
+
     def SetSharding(self, rank, world, gather):
         """gather(mine: np.ndarray[count]) -> np.ndarray[world, count]"""
         def cb(ctx, mine, all_, count):
@@ -279,10 +284,6 @@ class _Delegate(CudaSamplingPlanner):
         self.ns = model.nq + model.nv + model.na
         self._cb = None
         self.horizon = 0
-
-    def set_policy(self, times, knots, interp):
-        t = _arr(times); k = _arr(knots)
-        self.L.psp_set_policy(self.h, _p(t), _p(k), len(t), int(interp))
 
     def close(self):
         self.h = None

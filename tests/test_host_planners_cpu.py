@@ -284,3 +284,27 @@ def test_reference_agent_test_previous_policy(hostlib):
     for a, tq in zip(before, (0.0, 0.1, 0.2)):
         assert np.array_equal(a, pl.ActionFromPolicy(tq, use_previous=True))
     pl.close()
+
+
+def test_sampling_planner_second_exploration_std(hostlib):
+    # noise_exploration[1] > 0: a sample uses the second std when its Bernoulli(0.2) draw says so (planner.cc:319-325);
+    # the draw is injected as a per-sample flag on both sides
+    N, H = 12, 31
+    model, task, s, P, interp, z, times, knots, state, rng = case("Cartpole", N, H, seed=44)
+    flags = (rng.uniform(size=N) < 0.4).astype(np.uint8); flags[0] = 0
+    assert flags.any() and not flags.all()
+    o = pyoracle.Oracle(model, task); o.configure(P, interp, 0.2, 0.9)
+    o.set_policy(times, knots, interp); o.set_state(state, 0.0)
+    w = o.optimize(N, H, z, use_std2=flags)
+    pl = planner.CudaSamplingPlanner(model, task)
+    pl.configure(num_trajectory=N, interpolation=interp, num_spline_points=P, sigma0=0.2, sigma1=0.9)
+    pl.set_policy(times, knots, interp)
+    pl.SetNoise(z, use_std2=flags); pl.SetState(state, 0.0); pl.OptimizePolicy(H)
+    assert pl.winner == w
+    ot, ok = o.policy(0); pt, pk = pl.policy()
+    assert np.array_equal(ot, pt) and np.array_equal(ok, pk)
+    # the flag matters: without it the candidates differ
+    o2 = pyoracle.Oracle(model, task); o2.configure(P, interp, 0.2, 0.9)
+    o2.set_policy(times, knots, interp); o2.set_state(state, 0.0); o2.optimize(N, H, z)
+    assert not np.array_equal(o2.returns()[0], o.returns()[0])
+    pl.close()
