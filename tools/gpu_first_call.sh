@@ -16,7 +16,7 @@ timeout 900 python -m pytest tests -m gpu -q -rxX > "$out/pytest_gpu.log" 2>&1; 
 tail -15 "$out/pytest_gpu.log"
 
 step "2. the not-yet-run tests again with failures shown in full (no xfail masking)"
-timeout 600 python -m pytest tests/test_robust_planner.py tests/test_gpu_full_size.py -m gpu -q --runxfail > "$out/pytest_unverified.log" 2>&1
+timeout 600 python -m pytest tests/test_robust_planner.py tests/test_gpu_full_size.py tests/test_agent_api.py -m gpu -q --runxfail > "$out/pytest_unverified.log" 2>&1
 echo "exit $?" >> "$out/pytest_unverified.log"; tail -25 "$out/pytest_unverified.log"
 
 step "3. smoke + default bench, both arms"
