@@ -62,6 +62,9 @@ class Agent:
         m = self.model
         self._term_names = [m.name_of("sensor", i) for i in range(self.task.num_term)]
         self._param_names = [m.name_of("numeric", i) for i in range(m.nnumeric) if m.name_of("numeric", i).startswith("residual_")]
+        tr = m.text("task_transition")                      # Task::mode names (grpc_agent_util.cc GetAllModes)
+        self._modes = tr.split("|") if tr else ["default_mode"]
+        self._mode = 0
         self._default_weights = [self.task.weight[i] for i in range(self.task.num_term)]
         self._default_parameters = [self.task.parameters[i] for i in range(self.task.num_parameters)]
         self.reset()
@@ -249,3 +252,20 @@ class Agent:
             i = self._param_names.index(key)
             self.task.parameters[i] = float(value); self.plant_task.parameters[i] = float(value)
         self._push_task()
+
+    # ---- modes (Task::mode; custom text "task_transition")
+    def get_all_modes(self):
+        return list(self._modes)
+
+    def get_mode(self):
+        return self._modes[self._mode]
+
+    def set_mode(self, mode):
+        if mode not in self._modes:
+            raise ValueError(f"Mode '{mode}' not found in task '{self.task_id}'")       # INVALID_ARGUMENT in the service
+        self._mode = self._modes.index(mode)
+        if self.task_id.startswith("Quadruped"):
+            # what the task's next Transition() leaves in the residual snapshot: the mode and its start time
+            for mdl, tsk in ((self.model, self.task), (self.plant_model, self.plant_task)):
+                _task.quadruped_snapshot(mdl, tsk, mode=mode, time=self.time, set_gait_parameters=False)
+            self._push_task()

@@ -201,3 +201,21 @@ def check_agent_on_the_device(planner_name):
         agent.set_cost_weights({"Vertical": 0, "Velocity": 0, "Centered": 0, "Control": 1})
         agent.planner_step()
         assert np.allclose(agent.get_action(), 0)
+
+
+def test_modes(hostlib):
+    # agent_test.py: test_get_set_default_mode / test_get_set_mode / test_get_all_modes / test_set_mode_error
+    with make("Cartpole") as agent:
+        agent.set_mode("default_mode")
+        assert agent.get_mode() == "default_mode" and agent.get_all_modes() == ["default_mode"]
+    with make("Quadruped Flat") as agent:
+        assert tuple(agent.get_all_modes()) == ("Quadruped", "Biped", "Walk", "Scramble", "Flip")
+        assert agent.get_mode() == "Quadruped"
+        agent.set_mode("Walk")
+        assert agent.get_mode() == "Walk"
+        with pytest.raises(ValueError):
+            agent.set_mode("Run")
+        # the mode reaches the residual: the cost at the same state differs between modes
+        c_walk = agent.get_total_cost()
+        agent.set_mode("Biped")
+        assert agent.get_total_cost() != c_walk
