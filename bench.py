@@ -150,7 +150,15 @@ def main():
     ap.add_argument("--impl", default="b200")
     ap.add_argument("--workload", default=DEFAULT_WORKLOAD, choices=sorted(WORKLOADS))
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    # BASELINE.json configs[4] (sample-count x horizon sweep, also under torchrun): one task at a chosen size
+    ap.add_argument("--task", default=None, help='e.g. "Cartpole" or "Quadruped Flat": overrides --workload')
+    ap.add_argument("--samples", type=int, default=65536, help="samples PER GPU (with --task)")
+    ap.add_argument("--horizon", type=int, default=101, help="rollout steps incl. the terminal one (with --task)")
+    ap.add_argument("--interpolation", type=int, default=2)
     args = ap.parse_args()
+    if args.task:
+        args.workload = f"{args.task.lower().replace(' ', '_')}_{args.samples}_{args.horizon}"
+        WORKLOADS[args.workload] = [(args.task, args.samples, args.interpolation, args.horizon)]
     args.warmup = max(args.warmup, 3) if args.impl != "reference" else args.warmup
     rank = int(os.environ.get("RANK", 0)); world = int(os.environ.get("WORLD_SIZE", 1)); local = int(os.environ.get("LOCAL_RANK", 0))
     if args.impl == "reference":
