@@ -2,12 +2,21 @@
 """Benchmark of the Predictive Sampling planning iteration (BASELINE.json metric: rollout
 sample-steps/s and planning-iteration latency).
 
-A "step" is one full planning iteration (perturb -> N rollouts x H steps -> argmin) over every
-task of the workload.  `value` is device-resident throughput (CUDA events on the engine's stream),
-`e2e` goes through the host-buffer API (state + nominal H2D, winner record D2H inside the timed
-region).  `--impl reference` times the CPU restatement of the reference planner (oracle/) on the
-host cores.  One process per GPU under torchrun; samples are sharded across ranks (weak scaling)
-and the winner is picked by an NCCL all-gather min-loc of the per-rank winner records.
+A "step" is one full planning iteration (perturb -> N rollouts x H steps -> argmin) over every task
+of the workload; the tasks of a workload run concurrently on their engines' streams.  `value` is
+device-resident throughput (CUDA events, L2 flushed between iterations), `e2e` goes through the
+host-buffer API of the drop-in planner class (state + nominal H2D, winner record D2H inside the
+timed region).  The default workload is the configuration north_star's target is quoted on:
+65,536 samples x 1 s horizon on cartpole AND quadruped; per-task figures are in `tasks`.
+
+One process per GPU under torchrun: the workload's samples are SHARDED across the ranks (strong
+scaling: rank r rolls global samples [r N / R, (r + 1) N / R)), and the winner is picked by ONE
+ncclAllGather of the per-rank winner records + a min-loc kernel inside the engine library
+(ps_comm_init; lowest global index on ties, knots included).
+
+`--impl reference` and the `cpu_baseline` leg time the CPU planner (oracle/: the reference planner
+logic over the restated MuJoCo step; kind "port", physics unpinned) on all host cores, on the same
+fraction of every task's samples so that the tasks weigh in as they do on the GPU.
 """
 import argparse
 import json
@@ -29,20 +38,34 @@ WORKLOADS = {
     "cartpole_10_zero": [("Cartpole", 10, 0, 101)],          # configs[0], the reference's CPU-runnable case
     "swimmer+walker_16384": [("Swimmer", 16384, 2, None), ("Walker", 16384, 2, None)],
     "quadruped_65536_1s": [("Quadruped Flat", 65536, 2, 101)],
+    # the configuration north_star's target is quoted on: 65,536 samples x 1 s on cartpole AND quadruped
+    # (under torchrun this is configs[3]: the quadruped's 65,536 samples sharded over the ranks)
+    "cartpole+quadruped_65536_1s": [("Cartpole", 65536, 2, 101), ("Quadruped Flat", 65536, 2, 101)],
 }
-DEFAULT_WORKLOAD = "acrobot+particle_4096_cubic"
+DEFAULT_WORKLOAD = "cartpole+quadruped_65536_1s"
 METRIC = "rollout sample-steps/sec"
-# FP64 flops per sample-step (FMA = 2), from the ncu instruction counts of the rollout kernel
-# (profiles/flops_per_sample_step.json, see DESIGN.md "Measurement")
+# FP64 operations per sample-step: `algorithmic` = counted on the CPU oracle by an instrumented double
+# (baseline/flops_<task>.json), `executed` = the kernel's own dadd + dmul + 2 dfma from ncu
 FLOPS_FILE = os.path.join(ROOT, "profiles", "flops_per_sample_step.json")
+BASELINE_DIR = os.path.join(ROOT, "baseline")
+TASK_NAMES = ["Cartpole", "Acrobot", "Particle", "Swimmer", "Walker", "Quadruped Flat"]
 
 
 def load_flops():
     try:
         with open(FLOPS_FILE) as f:
-            return json.load(f)
+            executed = json.load(f)
     except Exception:
-        return {}
+        executed = {}
+    algorithmic = {}
+    for name in TASK_NAMES:
+        p = os.path.join(BASELINE_DIR, "flops_" + name.lower().replace(" ", "_") + ".json")
+        try:
+            with open(p) as f:
+                algorithmic[name] = float(json.load(f)["flops_per_sample_step"])
+        except Exception:
+            pass
+    return executed, algorithmic
 
 
 class ClockSampler(threading.Thread):
@@ -81,11 +104,12 @@ class ClockSampler(threading.Thread):
                 "samples": len(sm)}
 
 
-def make_cases(workload, rank, world):
+def make_cases(workload, rank, world, weak=False):
+    """Per-rank view of the workload: rank r of R rolls global samples [offset, offset + N) of N_total."""
     from mujoco_mpc_b200 import registry
     from mujoco_mpc_b200.registry import synthetic_state
     cases = []
-    for name, N, interp, H in WORKLOADS[workload]:
+    for name, N_total, interp, H in WORKLOADS[workload]:
         model, task, s = registry.load(name)
         if name == "Quadruped Flat":   # planning state of a trotting robot heading for the goal
             from mujoco_mpc_b200 import task as _task
@@ -99,45 +123,76 @@ def make_cases(workload, rank, world):
         times = 0.0 + shift * np.arange(P)
         half = 0.5 * (model.actuator_ctrlrange[:, 1] - model.actuator_ctrlrange[:, 0])
         knots = np.clip(rng.normal(0, 0.3, (P, model.nu)) * half, model.actuator_ctrlrange[:, 0], model.actuator_ctrlrange[:, 1])
-        cases.append(dict(name=name, model=model, task=task, s=s, N=N, H=H, P=P, interp=interp, state=state, times=times,
-                          knots=knots, sigma=s["exploration"], offset=rank * N))
+        if weak:
+            N, offset, N_total = N_total, rank * N_total, N_total * world
+        else:
+            N = max(N_total // world, 1); offset = rank * N; N_total = N * world
+        cases.append(dict(name=name, model=model, task=task, s=s, N=N, N_total=N_total, H=H, P=P, interp=interp, state=state,
+                          times=times, knots=knots, sigma=s["exploration"], offset=offset))
     return cases
+
+
+def cpu_arm(cases, cores, budget_s, steps=None, warmup=0):
+    """The CPU planner on `cores` host threads over the SAME fraction f of every task's samples (so the tasks weigh in
+    as on the GPU), f sized so that one step is about `budget_s` of wall time.  Returns (sample-steps/s, s per step,
+    description, per-task rates)."""
+    from oracle import pyoracle
+    pyoracle.build()
+    runs = []
+    for c in cases:
+        o = pyoracle.Oracle(c["model"], c["task"]); o.configure(c["P"], c["interp"], c["sigma"])
+        runs.append([o, c, 0, None, 0.0])
+
+    def one(o, c, n, z):
+        o.set_state(c["state"], 0.0); o.set_policy(c["times"], c["knots"], c["interp"]); o.optimize(n, c["H"], z, nthread=cores)
+
+    # calibration: per-task rate on 8 rollouts per thread
+    full_s = 0.0
+    for r in runs:
+        o, c = r[0], r[1]
+        n0 = min(c["N_total"], max(8 * cores, 128))
+        z = np.random.default_rng(1).standard_normal((n0, c["P"], c["model"].nu))
+        one(o, c, n0, z)
+        t0 = time.perf_counter(); one(o, c, n0, z); dt = time.perf_counter() - t0
+        full_s += c["N_total"] / n0 * dt
+    f = min(1.0, budget_s / max(full_s, 1e-9))
+    f = max(f, max(min(1.0, max(8 * cores, 128) / c["N_total"]) for c in cases))     # >= 8 rollouts per thread on every task
+    for r in runs:
+        c = r[1]
+        r[2] = max(1, min(c["N_total"], int(round(f * c["N_total"]))))
+        r[3] = np.random.default_rng(1).standard_normal((r[2], c["P"], c["model"].nu))
+
+    def step():
+        for r in runs:
+            t0 = time.perf_counter(); one(r[0], r[1], r[2], r[3]); r[4] += time.perf_counter() - t0
+    for _ in range(warmup):
+        step()
+    for r in runs:
+        r[4] = 0.0
+    t0 = time.perf_counter(); n_steps = 0
+    while (steps is not None and n_steps < steps) or (steps is None and (time.perf_counter() - t0 < budget_s * 6 or n_steps < 2)):
+        step(); n_steps += 1
+    dt = (time.perf_counter() - t0) / n_steps
+    units = sum(r[2] * (r[1]["H"] - 1) for r in runs)
+    per_task = {r[1]["name"]: r[2] * (r[1]["H"] - 1) * n_steps / r[4] for r in runs}
+    sample = f"{n_steps} steps of " + "; ".join(f"{r[1]['name']} {r[2]} of {r[1]['N_total']} samples x {r[1]['H'] - 1} steps" for r in runs) + \
+        f" (fraction {f:.4g} of every task, persistent {cores}-thread pool, dynamic scheduling)"
+    return units / dt, dt, sample, per_task
 
 
 def run_reference(args, rank, world):
     """CPU arm: the reference planner restated over the restated MuJoCo step (oracle/), all host threads."""
     if rank != 0:
         return
-    from oracle import pyoracle
-    pyoracle.build()
     cases = make_cases(args.workload, 0, 1)
     cores = len(os.sched_getaffinity(0))
-    # bounded sample: enough samples for ~1-2 s of CPU work per step
-    runs = []
-    for c in cases:
-        o = pyoracle.Oracle(c["model"], c["task"])
-        o.configure(c["P"], c["interp"], c["sigma"])
-        n_cpu = min(c["N"], max(cores * 8, 128))
-        z = np.random.default_rng(1).standard_normal((n_cpu, c["P"], c["model"].nu))
-        runs.append((o, c, n_cpu, z))
-    def step():
-        for o, c, n_cpu, z in runs:
-            o.set_state(c["state"], 0.0)
-            o.set_policy(c["times"], c["knots"], c["interp"])
-            o.optimize(n_cpu, c["H"], z, nthread=cores)
-    for _ in range(args.warmup):
-        step()
-    t0 = time.perf_counter()
-    for _ in range(args.steps):
-        step()
-    dt = (time.perf_counter() - t0) / args.steps
-    units = sum(n * (c["H"] - 1) for _, c, n, _ in runs)
-    v = units / dt
-    sample = "; ".join(f"{c['name']} {n} of {c['N']} samples x {c['H'] - 1} steps" for _, c, n, _ in runs)
+    v, dt, sample, per_task = cpu_arm(cases, cores, budget_s=1.5, steps=args.steps, warmup=args.warmup)
     line = {"impl": "reference", "metric": METRIC, "value": v, "unit": "sample-steps/s", "n_gpus": args.gpus, "steps": args.steps,
-            "warmup": args.warmup, "ms_per_step": dt * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "warmup": args.warmup, "ms_per_step": dt * 1e3, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
             "dtype": "f64", "data": "synthetic", "config": {"workload": args.workload},
-            "cpu_baseline": {"value": v, "unit": "sample-steps/s", "cores": cores, "kind": "port", "sample": sample},
+            "tasks": [{"name": k, "value": x, "unit": "sample-steps/s"} for k, x in per_task.items()],
+            "cpu_baseline": {"value": v, "unit": "sample-steps/s", "cores": cores, "kind": "port", "sample": sample,
+                             "note": "reference planner logic over the restated MuJoCo 3.1.4 step (physics unpinned); not the reference binary"},
             "e2e": {"value": v, "unit": "sample-steps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
     print(json.dumps(line))
 
@@ -145,14 +200,15 @@ def run_reference(args, rank, world):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=100)
-    ap.add_argument("--warmup", type=int, default=10)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="b200")
     ap.add_argument("--workload", default=DEFAULT_WORKLOAD, choices=sorted(WORKLOADS))
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--weak", action="store_true", help="every rank rolls the workload's full sample count (weak scaling)")
     # BASELINE.json configs[4] (sample-count x horizon sweep, also under torchrun): one task at a chosen size
     ap.add_argument("--task", default=None, help='e.g. "Cartpole" or "Quadruped Flat": overrides --workload')
-    ap.add_argument("--samples", type=int, default=65536, help="samples PER GPU (with --task)")
+    ap.add_argument("--samples", type=int, default=65536, help="total samples (with --task); per GPU with --weak")
     ap.add_argument("--horizon", type=int, default=101, help="rollout steps incl. the terminal one (with --task)")
     ap.add_argument("--interpolation", type=int, default=2)
     args = ap.parse_args()
@@ -167,54 +223,36 @@ def main():
     import torch
     from mujoco_mpc_b200.engine import Engine
     torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
     dist = None
     if world > 1:
         import torch.distributed as dist
-        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
-    cases = make_cases(args.workload, rank, world)
+        dist.init_process_group("nccl", device_id=dev)
+    cases = make_cases(args.workload, rank, world, weak=args.weak)
     engines = []
     for c in cases:
         e = Engine(c["model"], c["task"], device=local)
         e.set_seed(2024)
         e.set_state(c["state"], 0.0); e.set_nominal(c["times"], c["knots"], c["interp"])
+        if world > 1:
+            e.comm_init_torch(dist, rank, world)          # the library's own NCCL communicator for the winner exchange
         engines.append(e)
     streams = [torch.cuda.ExternalStream(e.stream(), device=local) for e in engines]
-    flush = torch.empty(256 * 1024 * 1024 // 4, dtype=torch.float32, device=f"cuda:{local}")   # 256 MB > 126 MB L2
-    records = []
-    for e, c in zip(engines, cases):
-        ptr, n = e.winner_record_ptr()
-        records.append((ptr, 3 + c["P"] * c["model"].nu))
+    main_stream = torch.cuda.current_stream(dev)
+    flush = torch.empty(256 * 1024 * 1024 // 4, dtype=torch.float32, device=dev)   # 256 MB > 126 MB L2
 
-    def record_tensor(k):
-        # zero-copy view of the engine's device-resident winner record
-        ptr, n = records[k]
-        class _W:
-            __cuda_array_interface__ = {"shape": (n,), "typestr": "<f8", "data": (ptr, False), "version": 2}
-        return torch.as_tensor(_W(), device=f"cuda:{local}")
-
-    rec_views = [record_tensor(k) for k in range(len(cases))]
-    gathered = [torch.empty(world * v.numel(), dtype=torch.float64, device=f"cuda:{local}") for v in rec_views]
-
-    def device_step(timed):
-        """one planning iteration per task; returns device ms (events on the engines' streams)"""
-        ms = 0.0
+    def device_step():
+        """one planning iteration of every task, the tasks concurrently on their engines' streams; returns device ms"""
+        flush.zero_()                                             # L2 flush between iterations
+        a = torch.cuda.Event(enable_timing=True); b = torch.cuda.Event(enable_timing=True)
+        a.record(main_stream)
         for k, (e, c) in enumerate(zip(engines, cases)):
-            st = streams[k]
-            with torch.cuda.stream(st):
-                flush.zero_()                                     # L2 flush between iterations
-                a = torch.cuda.Event(enable_timing=True); b = torch.cuda.Event(enable_timing=True)
-                a.record(st)
-                e.rollouts_async(c["N"], c["H"], c["sigma"], 0.0, c["offset"])
-                if world > 1:
-                    dist.all_gather_into_tensor(gathered[k], rec_views[k])   # min-loc over ranks (cost, index, knots)
-                    g = gathered[k].view(world, -1)
-                    tie = g[:, 0] == g[:, 0].min()                # lowest return, ties -> lowest global index
-                    best = torch.where(tie, g[:, 1], torch.full_like(g[:, 1], float("inf"))).argmin()
-                    _ = g[best]
-                b.record(st)
-            b.synchronize()
-            ms += a.elapsed_time(b)
-        return ms
+            streams[k].wait_event(a)
+            e.rollouts_async(c["N"], c["H"], c["sigma"], 0.0, c["offset"])   # K1-K3 (+ the all-gather min-loc when sharded)
+            done = torch.cuda.Event(); done.record(streams[k]); main_stream.wait_event(done)
+        b.record(main_stream)
+        b.synchronize()
+        return a.elapsed_time(b)
 
     # end-to-end arm: the drop-in host planner (CudaSamplingPlanner), host buffers in and out
     from mujoco_mpc_b200.planner import CudaSamplingPlanner
@@ -224,13 +262,7 @@ def main():
         pl.configure(num_trajectory=c["N"], interpolation=c["interp"], num_spline_points=c["P"], sigma0=c["sigma"], sigma1=0.0)
         pl.SetSeed(2024)
         if world > 1:
-            cnt = 3 + c["P"] * c["model"].nu
-            dev_in = torch.empty(cnt, dtype=torch.float64, device=f"cuda:{local}")
-            dev_out = torch.empty(world * cnt, dtype=torch.float64, device=f"cuda:{local}")
-            def gather(mine, dev_in=dev_in, dev_out=dev_out):
-                dev_in.copy_(torch.from_numpy(mine)); dist.all_gather_into_tensor(dev_out, dev_in)
-                return dev_out.cpu().numpy()
-            pl.SetSharding(rank, world, gather)
+            pl.SetShardingNative(rank, world, dist)       # ncclAllGather inside the engine, no host bounce
         planners.append(pl)
     e2e_time = [0.0]
 
@@ -248,23 +280,28 @@ def main():
         torch.cuda.synchronize()
 
     for _ in range(args.warmup):
-        device_step(False)
+        device_step()
     launches0 = sum(e.launches() for e in engines)
     sampler = ClockSampler(local); sampler.start()
     barrier()
-    ms_total = 0.0; kern_ms = np.zeros(3); lat = []
+    ms_total = 0.0; kern_ms = np.zeros((len(cases), 4)); lat = []
     for _ in range(args.steps):
-        ms = device_step(True); ms_total += ms; lat.append(ms)
-        for e in engines:
-            kern_ms += np.array(e.kernel_ms())
+        ms = device_step(); ms_total += ms; lat.append(ms)
+        for k, e in enumerate(engines):
+            kern_ms[k] += np.array(e.kernel_ms4())
     barrier()
     launches = sum(e.launches() for e in engines) - launches0
-    t = torch.tensor([ms_total], dtype=torch.float64, device=f"cuda:{local}")
+    t = torch.tensor([ms_total], dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     ms_step = float(t.item()) / args.steps
-    units = sum(c["N"] * (c["H"] - 1) for c in cases) * world
+    units = sum(c["N_total"] * (c["H"] - 1) for c in cases)
     value = units / (ms_step * 1e-3)
+    kern_ms /= args.steps
+    kt = torch.tensor(kern_ms, dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(kt, op=dist.ReduceOp.MAX)
+    kern_ms = kt.cpu().numpy()
 
     # end-to-end through the host-buffer API
     for _ in range(3):
@@ -273,69 +310,76 @@ def main():
     for _ in range(args.steps):
         e2e_step()
     barrier(); e2e_s = (time.perf_counter() - t0) / args.steps
-    # the clocks sampler spans both timed regions (device-timed and end-to-end); if they were shorter than one
-    # nvidia-smi query, keep stepping until it has seen the GPU under this load
-    # (single rank only: under torchrun every device_step holds a collective, so the step count must be the
-    # same on every rank -- a rank-local loop here deadlocks the all-gather)
-    while world == 1 and len(sampler.rows) < 3 and time.perf_counter() - t0 < 5.0:
-        device_step(False)
+    # the clocks sampler spans both timed regions (device-timed and end-to-end); if they were shorter than ~20
+    # nvidia-smi queries, keep stepping until it has seen the GPU under this load (every rank runs the same number
+    # of extra steps: each sharded step holds a collective)
+    extra = 0
+    if len(sampler.rows) < 20:
+        extra = int(min(500, 3.0 / max(ms_step * 1e-3, 1e-4)))
+    if world > 1:
+        et = torch.tensor([extra], dtype=torch.int64, device=dev); dist.all_reduce(et, op=dist.ReduceOp.MAX); extra = int(et.item())
+    for _ in range(extra):
+        device_step()
     clocks = sampler.summary()
-    t = torch.tensor([e2e_s], dtype=torch.float64, device=f"cuda:{local}")
+    t = torch.tensor([e2e_s], dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     e2e_value = units / float(t.item())
-    # per iteration: the whole Constants block (model + task + plan, pinned) + nominal knots go up, the winner record comes back
-    h2d = sum(e.constants_bytes() + 8 * c["P"] * c["model"].nu for e, c in zip(engines, cases))
+    # per iteration: the plan part of the Constants block (state + knot times, pinned) + nominal knots go up, the winner record comes back
+    h2d = sum(e.upload_bytes() + 8 * c["P"] * c["model"].nu for e, c in zip(engines, cases))
     d2h = sum(8 * (3 + c["P"] * c["model"].nu) for c in cases)
 
     if rank == 0:
-        flops = load_flops()
+        executed, algorithmic = load_flops()
         peak = engines[0].fp64_peak()
-        rollout_ms = kern_ms[1] / args.steps
-        alg = sum(flops.get(c["name"], 0.0) * c["N"] * (c["H"] - 1) for c in cases)
-        # DRAM bytes (read + write) of the rollout kernels of one step, from the ncu --set full captures
-        dram = flops.get("_dram_bytes_per_sample_step", {})
-        traffic = sum(dram.get(c["name"], float("nan")) * c["N"] * (c["H"] - 1) for c in cases)
-        traffic = None if traffic != traffic else traffic
-        achieved = alg / (rollout_ms * 1e-3) / 1e12 if alg else None
-        # the same kernel against HBM: its measured DRAM traffic (mostly the thread-private working set of the larger
-        # models spilling) over its duration, as a fraction of the measured copy bandwidth (MEASURED_PEAKS.json)
         hbm_peak = None
         try:
             with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
                 hbm_peak = float(json.load(f)["hbm_gbs"])
         except Exception:
             pass
-        traffic_gbs = traffic / (rollout_ms * 1e-3) / 1e9 if (traffic and rollout_ms > 0) else None
+        dram = executed.get("_dram_bytes_per_sample_step", {})
+        tasks = []
+        for k, (e, c) in enumerate(zip(engines, cases)):
+            su = c["N_total"] * (c["H"] - 1)
+            rollout_s = kern_ms[k][1] * 1e-3
+            alg = algorithmic.get(c["name"]); exe = executed.get(c["name"])
+            tasks.append({"name": c["name"], "samples": c["N_total"], "samples_per_gpu": c["N"], "horizon_steps": c["H"], "kernel": e.variant(),
+                          "value": su / (sum(kern_ms[k]) * 1e-3), "unit": "sample-steps/s",
+                          "kernel_ms": {"perturb": kern_ms[k][0], "rollout": kern_ms[k][1], "argmin": kern_ms[k][2], "exchange": kern_ms[k][3]},
+                          "flops_per_sample_step": {"algorithmic": alg, "executed": exe},
+                          "roofline_frac": (alg * su / rollout_s / 1e12 / peak / world) if alg else None,
+                          "roofline_frac_executed": (exe * su / rollout_s / 1e12 / peak / world) if exe else None,
+                          "dram_bytes_per_sample_step": dram.get(c["name"])})
+        # the dominant kernel = the rollout kernel of the task that takes the longest
+        dom = int(np.argmax(kern_ms[:, 1])); dc = cases[dom]; dsu = dc["N_total"] * (dc["H"] - 1)
+        dflops = algorithmic.get(dc["name"]) or executed.get(dc["name"])
+        achieved = (dflops * dsu / world / (kern_ms[dom][1] * 1e-3) / 1e12) if dflops else None
+        traffic = dram.get(dc["name"]) * dsu / world if dram.get(dc["name"]) is not None else None
         line = {"metric": METRIC, "value": value, "unit": "sample-steps/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
-                "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
-                "data": "synthetic", "config": {"workload": args.workload, "samples_per_gpu": [c["N"] for c in cases],
+                "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak" if args.weak else "strong", "vs_baseline": None, "dtype": "f64",
+                "data": "synthetic", "config": {"workload": args.workload, "samples": [c["N_total"] for c in cases],
+                                                "samples_per_gpu": [c["N"] for c in cases],
                                                 "horizon_steps": [c["H"] for c in cases], "l2": "flushed (256 MB write) between iterations",
                                                 "kernels": [e.variant() for e in engines],
-                                                "parallelism": f"samples sharded over {world} rank(s), NCCL all-gather min-loc"},
-                "planning_iteration_latency_ms": {"mean": ms_step, "p50": float(np.percentile(lat, 50)), "p95": float(np.percentile(lat, 95))}, "kernel_ms": {"perturb": kern_ms[0] / args.steps, "rollout": rollout_ms, "argmin": kern_ms[2] / args.steps},
+                                                "parallelism": f"samples sharded over {world} rank(s); ncclAllGather min-loc of the winner records inside the engine library"},
+                "tasks": tasks,
+                "planning_iteration_latency_ms": {"mean": ms_step, "p50": float(np.percentile(lat, 50)), "p95": float(np.percentile(lat, 95))},
                 "e2e": {"value": e2e_value, "unit": "sample-steps/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                         "latency_ms": e2e_s * 1e3},
                 "gpu_launches": int(launches), "clocks": clocks,
-                "roofline": {"bound": "fp64", "achieved": achieved, "peak": peak, "unit": "TFLOP/s", "frac": (achieved / peak) if achieved else None,
-                             "traffic": traffic, "traffic_unit": "bytes per step (sum of the step's rollout launches)", "peak_source": "DFMA probe measured in this run (MEASURED_PEAKS.json has no FP64 figure)",
-                             "traffic_gbs": traffic_gbs, "hbm_peak_gbs": hbm_peak,
-                             "traffic_frac_of_hbm": (traffic_gbs / hbm_peak) if (traffic_gbs and hbm_peak) else None}}
+                "roofline": {"bound": "fp64", "kernel": f"{engines[dom].variant()} rollout kernel ({dc['name']})", "achieved": achieved, "peak": peak, "unit": "TFLOP/s",
+                             "frac": (achieved / peak) if achieved else None,
+                             "flops": "algorithmic (oracle-counted, baseline/flops_*.json)" if algorithmic.get(dc["name"]) else "executed (ncu)",
+                             "traffic": traffic, "traffic_unit": "DRAM bytes per launch (ncu --set full, profiles/)",
+                             "peak_source": "DFMA probe measured in this run (MEASURED_PEAKS.json has no FP64 figure); with -fmad=false (the parity policy) the attainable peak is half of it",
+                             "hbm_peak_gbs": hbm_peak,
+                             "traffic_gbs": (traffic / (kern_ms[dom][1] * 1e-3) / 1e9) if traffic else None}}
         if not args.no_cpu_baseline and world == 1:
-            from oracle import pyoracle
-            pyoracle.build()
             cores = len(os.sched_getaffinity(0))
-            tot_units, tot_t, desc = 0, 0.0, []
-            for c in cases:
-                o = pyoracle.Oracle(c["model"], c["task"]); o.configure(c["P"], c["interp"], c["sigma"])
-                n_cpu = min(c["N"], max(cores * 8, 128))
-                z = np.random.default_rng(1).standard_normal((n_cpu, c["P"], c["model"].nu))
-                reps = 0; t0 = time.perf_counter()
-                while time.perf_counter() - t0 < 5.0:
-                    o.set_state(c["state"], 0.0); o.set_policy(c["times"], c["knots"], c["interp"]); o.optimize(n_cpu, c["H"], z, nthread=cores); reps += 1
-                tot_t += (time.perf_counter() - t0); tot_units += reps * n_cpu * (c["H"] - 1)
-                desc.append(f"{c['name']}: {reps} iterations of {n_cpu} samples x {c['H'] - 1} steps")
-            line["cpu_baseline"] = {"value": tot_units / tot_t, "unit": "sample-steps/s", "cores": cores, "kind": "port", "sample": "; ".join(desc)}
+            v, dt, sample, per_task = cpu_arm(make_cases(args.workload, 0, 1), cores, budget_s=2.0)
+            line["cpu_baseline"] = {"value": v, "unit": "sample-steps/s", "cores": cores, "kind": "port", "sample": sample,
+                                    "per_task": per_task}
         print(json.dumps(line))
     for e in engines:
         e.close()

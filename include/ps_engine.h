@@ -4,7 +4,9 @@
  * interface mjpc/planners/planner.h:32-102).  A host-side planner class keeps the reference's
  * Initialize/Allocate/Reset/SetState/OptimizePolicy/ActionFromPolicy methods and forwards the
  * planning iteration to these entry points.  All pointers are HOST pointers owned by the caller;
- * every call is synchronous.  Return value: 0 = ok, <0 = error (text in ps_last_error()).
+ * every call is synchronous except ps_rollouts_async (results stay on the device until ps_sync_record); the
+ * setters may be called at any time -- they wait for any upload still reading the engine's pinned staging.
+ * Return value: 0 = ok, <0 = error (text in ps_last_error()).
  * There is no CPU fallback: without a CUDA device ps_create() fails.
  */
 #ifndef PS_ENGINE_H_
@@ -129,6 +131,23 @@ int ps_constants_bytes(PsEngine* e);
 /* ps_rollouts with full per-step writeback of every sample (parity tests, traces) */
 int ps_rollouts_writeback(PsEngine* e, int N, int H, double sigma0, double sigma1, int sample_offset,
                           int* winner, double* winner_return, double* nominal_return);
+/* Multi-GPU sample sharding (replaces the ThreadPool fan-out of mjpc/threadpool.cc:30-85 across
+ * devices): each rank rolls its slice [sample_offset, sample_offset + N) of the global batch, then ONE ncclAllGather
+ * of the winner records on the engine's stream + a min-loc kernel (lowest return, ties to the lowest global index)
+ * leaves the GLOBAL record [return, global index, nominal return of global sample 0, winner knots] on every rank.
+ * NCCL is bound at run time (dlopen of libnccl.so.2, re-using a copy the process already holds).
+ *   ps_comm_unique_id: rank 0 creates the 128-byte ncclUniqueId; the host distributes it (MPI, torch.distributed, a file)
+ *   ps_comm_init:      every rank joins (collective call).  world == 1 clears the communicator.
+ * With a communicator set, ps_rollouts returns winner = -1 on ranks that do not own the global winner. */
+int ps_comm_unique_id(void* out, int cap);
+int ps_comm_init(PsEngine* e, int rank, int world, const void* unique_id);
+int ps_comm_info(PsEngine* e, int* rank, int* world, int* nccl_version);
+int ps_last_exchange_ms(PsEngine* e, float* ms);
+/* after ps_rollouts_async: wait for the iteration and fetch the winner record (ps_rollouts does this itself) */
+int ps_sync_record(PsEngine* e, int* winner, double* winner_return, double* nominal_return);
+/* bytes of constants the last iteration uploaded: the whole block after a model / task / option change, else only
+ * the plan part (state, mocap, time, knot times) */
+int ps_last_upload_bytes(PsEngine* e);
 /* measured FP64 FMA throughput of the device (TFLOP/s): roofline denominator of the rollout kernel */
 int ps_fp64_peak(PsEngine* e, int reps, double* tflops);
 

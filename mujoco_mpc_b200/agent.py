@@ -158,10 +158,12 @@ class Agent:
     def get_action(self, time=None, averaging_duration=0, nominal_action=False):
         """GetAction / AverageAction (grpc_agent_util.cc:166-230).  The sampling policies are open loop (the state
         argument of ActionFromPolicy is unused), so the averaged action needs no rollout: the policy is sampled on
-        the grid of agent time steps the service walks -- `< end` for the nominal action, `<= end` otherwise."""
+        the grid the service walks -- `< end` for the nominal action, `<= end` otherwise.  The step of that grid is
+        model->opt.timestep of the SERVICE's model copy, taken before the agent overrides timestep / integrator
+        (grpc/agent_service.cc:118-120), i.e. the XML plant time step (Cartpole 0.001, not the agent's 0.01)."""
         t = self.time if time is None else float(time)
         if averaging_duration > 0:
-            end, dt = t + averaging_duration, self.settings["timestep"]
+            end, dt = t + averaging_duration, self.plant_model.opt_timestep
             total, n = np.zeros(self.model.nu), 0
             while (t < end) if nominal_action else (t <= end):
                 total += self.planner.ActionFromPolicy(t); t += dt; n += 1

@@ -10,6 +10,8 @@
 #include <cstring>
 #include <string>
 #include <vector>
+#include <dlfcn.h>
+#include <nccl.h>
 #include "../../include/ps_engine.h"
 #include "ps_variant.h"
 #include "ps_kernels_aux.cuh"
@@ -71,8 +73,51 @@ struct PsEngine_ {
   double* d_param_std = nullptr; bool have_param_std = false; int* d_elite = nullptr; int elite_cap = 0;
   double* d_ce_out = nullptr; double* h_ce_out = nullptr; float ce_ms = 0;
   double* d_xfrc = nullptr; size_t xfrc_cap = 0;     // robust rollouts: standard-normal force noise [(t * 6 nbody + k)][stride]
-  int nbody = 0; double timestep = 0;
+  int nbody = 0; double timestep = 0; int integrator = 0;
+  // host staging: the pinned mirrors are rewritten by the setters, so every H2D copy out of them is followed by
+  // an event the next writer waits on (an async caller can never upload torn constants)
+  cudaEvent_t ev_h2d = nullptr; bool h2d_pending = false; bool const_dirty = true, const2_dirty = true;
+  double* h_nominal = nullptr;                                    // pinned staging of the nominal knots
+  bool record_fresh = false;                                      // h_record holds the last iteration's record
+  size_t last_upload = 0;
+  // multi-GPU winner exchange (ps_comm_init): one ncclAllGather of the winner records + a min-loc kernel
+  ncclComm_t comm = nullptr; int rank = 0, world = 1; double* d_gather = nullptr; double* d_global = nullptr; cudaEvent_t ev_x = nullptr;
 };
+
+// ---------------------------------------------------------------- NCCL, bound at run time
+// The library does not link NCCL: a single-GPU user needs none, and a multi-GPU host process (torch, MPI launcher)
+// normally has one loaded already -- RTLD_NOLOAD picks that copy up so that two NCCL versions never meet.
+struct NcclApi {
+  ncclResult_t (*GetUniqueId)(ncclUniqueId*) = nullptr;
+  ncclResult_t (*CommInitRank)(ncclComm_t*, int, ncclUniqueId, int) = nullptr;
+  ncclResult_t (*CommDestroy)(ncclComm_t) = nullptr;
+  ncclResult_t (*AllGather)(const void*, void*, size_t, ncclDataType_t, ncclComm_t, cudaStream_t) = nullptr;
+  const char* (*GetErrorString)(ncclResult_t) = nullptr;
+  ncclResult_t (*GetVersion)(int*) = nullptr;
+  bool ok = false; std::string why;
+};
+static NcclApi& nccl_api() {
+  static NcclApi api; static bool tried = false;
+  if (tried) return api;
+  tried = true;
+  void* h = dlopen("libnccl.so.2", RTLD_NOW | RTLD_NOLOAD);
+  if (!h) h = dlopen("libnccl.so.2", RTLD_NOW | RTLD_GLOBAL);
+  if (!h) h = dlopen("libnccl.so", RTLD_NOW | RTLD_GLOBAL);
+  if (!h) { api.why = std::string("libnccl.so.2 not found: ") + dlerror(); return api; }
+#define PS_NCCL_SYM(field, name) *(void**)(&api.field) = dlsym(h, name); if (!api.field) { api.why = std::string("missing symbol ") + name; return api; }
+  PS_NCCL_SYM(GetUniqueId, "ncclGetUniqueId") PS_NCCL_SYM(CommInitRank, "ncclCommInitRank") PS_NCCL_SYM(CommDestroy, "ncclCommDestroy")
+  PS_NCCL_SYM(AllGather, "ncclAllGather") PS_NCCL_SYM(GetErrorString, "ncclGetErrorString") PS_NCCL_SYM(GetVersion, "ncclGetVersion")
+#undef PS_NCCL_SYM
+  api.ok = true;
+  return api;
+}
+#define NC(call)                                                                                   \
+  do { ncclResult_t r_ = (call); if (r_ != ncclSuccess) return fail(std::string(#call) + ": " + nccl_api().GetErrorString(r_)); } while (0)
+
+// the pinned mirrors may only be rewritten once the last copy out of them has completed
+static void wait_upload(PsEngine_* e) {
+  if (e->h2d_pending) { cudaEventSynchronize(e->ev_h2d); e->h2d_pending = false; }
+}
 
 static int ensure(double** p, size_t* cap, size_t need) {
   if (*cap >= need) return 0;
@@ -97,6 +142,8 @@ PsEngine* ps_create(int device_ordinal) {
   e->device = device_ordinal;
   if (cudaStreamCreateWithFlags(&e->stream, cudaStreamNonBlocking) != cudaSuccess) { g_error = "cudaStreamCreate failed"; delete e; return nullptr; }
   for (auto& ev : e->ev) cudaEventCreate(&ev);
+  cudaEventCreateWithFlags(&e->ev_h2d, cudaEventDisableTiming); cudaEventCreate(&e->ev_x);
+  cudaMallocHost(&e->h_nominal, 36 * 32 * sizeof(double));
   cudaMallocHost(&e->h_record, (3 + 36 * 32) * sizeof(double));
   cudaMalloc(&e->d_record, (3 + 36 * 32) * sizeof(double));
   cudaMalloc(&e->d_counter, sizeof(int));
@@ -115,6 +162,12 @@ void ps_destroy(PsEngine* e) {
                   e->d_blockmin, e->d_counter, e->d_const2, e->wb.states, e->wb.actions, e->wb.residual, e->wb.costs, e->wb.times, e->wb.trace, e->d_scratch,
                   e->d_xfrc, e->d_param_std, e->d_elite, e->d_ce_out};
   for (void* b : bufs) if (b) cudaFree(b);
+  if (e->comm && nccl_api().ok) nccl_api().CommDestroy(e->comm);
+  if (e->d_gather) cudaFree(e->d_gather);
+  if (e->d_global) cudaFree(e->d_global);
+  if (e->ev_h2d) cudaEventDestroy(e->ev_h2d);
+  if (e->ev_x) cudaEventDestroy(e->ev_x);
+  if (e->h_nominal) cudaFreeHost(e->h_nominal);
   if (e->h_const) cudaFreeHost(e->h_const);
   if (e->h_const2) cudaFreeHost(e->h_const2);
   if (e->h_record) cudaFreeHost(e->h_record);
@@ -127,6 +180,7 @@ void ps_destroy(PsEngine* e) {
 int ps_set_model(PsEngine* e, const PsModel* m) {
   if (!e || !m) return fail("ps_set_model: null argument");
   CU(cudaSetDevice(e->device));
+  wait_upload(e); e->const_dirty = e->const2_dirty = true;
   PairList pl = static_pairs(m);
   std::string why, all;
   const Variant* chosen = nullptr; void* host = nullptr; const Family* fam = nullptr;
@@ -150,7 +204,7 @@ int ps_set_model(PsEngine* e, const PsModel* m) {
     if (fam->large->fill(m, pl, h2, &why) == 0) { e->var_large = fam->large; e->h_const2 = h2; CU(cudaMalloc(&e->d_const2, fam->large->const_bytes)); }
     else cudaFreeHost(h2);     // the model fits only the small-batch kernel's capacities: it serves every batch size
   }
-  e->nbody = m->nbody; e->timestep = m->opt_timestep;
+  e->nbody = m->nbody; e->timestep = m->opt_timestep; e->integrator = m->opt_integrator;
   e->nq = m->nq; e->nv = m->nv; e->nu = m->nu; e->na = m->na; e->nmocap = m->nmocap; e->nsensor = m->nsensor; e->ns = m->nq + m->nv + m->na;
   e->sensor_type.assign(m->sensor_type, m->sensor_type + m->nsensor);
   e->ray_ok = ray_scenery_ok(m);
@@ -178,7 +232,9 @@ int ps_set_options(PsEngine* e, double timestep, int integrator) {
   if ((e->var->euler_only || (e->var_large && e->var_large->euler_only)) && integrator != PS_INT_EULER)
     return fail("ps_set_options: this model runs on an Euler-only kernel instantiation; call ps_set_model with the new integrator");
   if (integrator == PS_INT_RK4) return fail("ps_set_options: RK4 integrator is not supported");
-  e->timestep = timestep;
+  if (timestep == e->timestep && integrator == e->integrator) return 0;      // unchanged: nothing to re-upload
+  wait_upload(e); e->const_dirty = e->const2_dirty = true;
+  e->timestep = timestep; e->integrator = integrator;
   e->var->options(e->h_const, timestep, integrator);
   if (e->var_large) e->var_large->options(e->h_const2, timestep, integrator);
   return 0;
@@ -193,6 +249,7 @@ int ps_set_task(PsEngine* e, const PsTask* t) {
     if (e->nq != 19 || e->nu != 12) return fail("ps_set_task: Quadruped expects a free joint + 12 actuated joints");
     for (int k = 0; k < 3; k++) if (t->sensor_id[k] < 0) return fail("ps_set_task: Quadruped sensor ids (subtreecom, subtreelinvel, angmom) missing");
   }
+  wait_upload(e); e->const_dirty = e->const2_dirty = true;
   e->task = d; e->have_task = true;
   e->var->task(e->h_const, d, need_sub);
   if (e->var_large) e->var_large->task(e->h_const2, d, need_sub);
@@ -202,6 +259,7 @@ int ps_set_task(PsEngine* e, const PsTask* t) {
 int ps_set_state(PsEngine* e, const double* state, const double* mocap, const double* userdata, double time) {
   (void)userdata;   // none of the supported tasks read userdata on the planning path
   if (!e || !e->have_model) return fail("ps_set_state: no model");
+  wait_upload(e);
   e->var->plan(e->h_const, state, e->ns, mocap, e->nmocap, time, nullptr, 0, 0, 0);
   if (e->var_large) e->var_large->plan(e->h_const2, state, e->ns, mocap, e->nmocap, time, nullptr, 0, 0, 0);
   return 0;
@@ -212,12 +270,16 @@ int ps_set_nominal(PsEngine* e, const double* times, const double* knots, int P,
   if (P < 1 || P > 36) return fail("ps_set_nominal: spline points must be in [1, 36]");
   CU(cudaSetDevice(e->device));
   const double nan = std::nan("");
+  wait_upload(e);
   e->var->plan(e->h_const, nullptr, 0, nullptr, 0, nan, times, P, interpolation, 0);
   if (e->var_large) e->var_large->plan(e->h_const2, nullptr, 0, nullptr, 0, nan, times, P, interpolation, 0);
   e->P = P; e->interp = interpolation; e->nelem = P * e->nu;
+  if (e->nelem > 36 * 32) return fail("ps_set_nominal: more than 1152 spline parameters");
   if (!e->d_nominal) CU(cudaMalloc(&e->d_nominal, sizeof(double) * 36 * 32));
-  CU(cudaMemcpyAsync(e->d_nominal, knots, sizeof(double) * e->nelem, cudaMemcpyHostToDevice, e->stream));
-  CU(cudaStreamSynchronize(e->stream));     // knots is caller-owned pageable memory
+  // knots is caller-owned pageable memory: stage it in the pinned mirror, no stream synchronisation
+  std::memcpy(e->h_nominal, knots, sizeof(double) * e->nelem);
+  CU(cudaMemcpyAsync(e->d_nominal, e->h_nominal, sizeof(double) * e->nelem, cudaMemcpyHostToDevice, e->stream));
+  CU(cudaEventRecord(e->ev_h2d, e->stream)); e->h2d_pending = true;
   return 0;
 }
 
@@ -316,11 +378,16 @@ static int run_iteration(PsEngine* e, int N, int H, double sigma0, double sigma1
   const Variant* run = e->var;
   if (e->var_large && (e->engine_override == 2 || (e->engine_override == 0 && N > e->crossover))) run = e->var_large;
   const bool large = run == e->var_large;
-  void* hc = large ? e->h_const2 : e->h_const; void* dc = large ? e->d_const2 : e->d_const;
+  char* hc = (char*)(large ? e->h_const2 : e->h_const); char* dc = (char*)(large ? e->d_const2 : e->d_const);
+  wait_upload(e);
   e->var->plan(e->h_const, nullptr, 0, nullptr, 0, std::nan(""), nullptr, 0, 0, H);
   if (e->var_large) e->var_large->plan(e->h_const2, nullptr, 0, nullptr, 0, std::nan(""), nullptr, 0, 0, H);
-  CU(cudaMemcpyAsync(dc, hc, run->const_bytes, cudaMemcpyHostToDevice, e->stream));
-  e->last = run; e->last_dconst = dc;
+  // model + task constants go up only when they changed; every iteration uploads the plan part (state, knot times)
+  bool& dirty = large ? e->const2_dirty : e->const_dirty;
+  if (dirty) { CU(cudaMemcpyAsync(dc, hc, run->const_bytes, cudaMemcpyHostToDevice, e->stream)); e->last_upload = run->const_bytes; dirty = false; }
+  else { CU(cudaMemcpyAsync(dc + run->plan_offset, hc + run->plan_offset, run->plan_bytes, cudaMemcpyHostToDevice, e->stream)); e->last_upload = run->plan_bytes; }
+  CU(cudaEventRecord(e->ev_h2d, e->stream)); e->h2d_pending = true;
+  e->last = run; e->last_dconst = dc; e->record_fresh = false;
   const int stride = e->stride, nelem = e->nelem;
   if (writeback && prepare_writeback(e, H, stride)) return -1;
   CU(cudaEventRecord(e->ev[0], e->stream));
@@ -335,7 +402,52 @@ static int run_iteration(PsEngine* e, int N, int H, double sigma0, double sigma1
   CU(cudaEventRecord(e->ev[3], e->stream));
   CU(cudaGetLastError());
   e->launches += 3; e->iteration++;
+  if (e->comm) {
+    // sharded batch: ONE all-gather of the per-rank winner records, then the min-loc (lowest global index on ties)
+    // + knot select on every rank; the global record replaces the local one for the readers below
+    const int count = 3 + nelem;
+    NC(nccl_api().AllGather(e->d_record, e->d_gather, (size_t)count, ncclDouble, e->comm, e->stream));
+    select_winner_kernel<<<1, 128, 0, e->stream>>>(e->d_gather, e->world, count, e->d_global);
+    e->launches += 2;
+  }
+  CU(cudaEventRecord(e->ev_x, e->stream));
   e->wb_valid = writeback; e->wb_N = N; e->wb_H = H;
+  return 0;
+}
+
+/* ---- multi-GPU: the winner exchange lives in the library */
+int ps_comm_unique_id(void* out, int cap) {
+  NcclApi& a = nccl_api();
+  if (!a.ok) return fail("ps_comm_unique_id: " + a.why);
+  if (cap < (int)sizeof(ncclUniqueId)) return fail("ps_comm_unique_id: buffer smaller than ncclUniqueId (128 bytes)");
+  ncclUniqueId id; NC(a.GetUniqueId(&id));
+  std::memcpy(out, &id, sizeof(id));
+  return (int)sizeof(id);
+}
+
+int ps_comm_init(PsEngine* e, int rank, int world, const void* unique_id) {
+  if (!e) return fail("null engine");
+  if (world < 1 || rank < 0 || rank >= world) return fail("ps_comm_init: bad rank / world");
+  NcclApi& a = nccl_api();
+  if (!a.ok) return fail("ps_comm_init: " + a.why);
+  CU(cudaSetDevice(e->device));
+  if (e->comm) { a.CommDestroy(e->comm); e->comm = nullptr; }
+  if (world == 1) { e->rank = 0; e->world = 1; return 0; }
+  ncclUniqueId id; std::memcpy(&id, unique_id, sizeof(id));
+  NC(a.CommInitRank(&e->comm, world, id, rank));
+  e->rank = rank; e->world = world;
+  if (e->d_gather) cudaFree(e->d_gather);
+  if (e->d_global) cudaFree(e->d_global);
+  CU(cudaMalloc(&e->d_gather, sizeof(double) * (3 + 36 * 32) * world));
+  CU(cudaMalloc(&e->d_global, sizeof(double) * (3 + 36 * 32)));
+  return 0;
+}
+
+int ps_comm_info(PsEngine* e, int* rank, int* world, int* nccl_version) {
+  if (!e) return fail("null engine");
+  if (rank) *rank = e->rank;
+  if (world) *world = e->comm ? e->world : 1;
+  if (nccl_version) { *nccl_version = 0; if (nccl_api().ok) nccl_api().GetVersion(nccl_version); }
   return 0;
 }
 
@@ -404,9 +516,12 @@ int ps_rollouts_async(PsEngine* e, int N, int H, double sigma0, double sigma1, i
 }
 
 static int fetch_record(PsEngine* e, int* winner, double* winner_return, double* nominal_return) {
-  CU(cudaMemcpyAsync(e->h_record, e->d_record, sizeof(double) * (3 + e->nelem), cudaMemcpyDeviceToHost, e->stream));
+  CU(cudaMemcpyAsync(e->h_record, e->comm ? e->d_global : e->d_record, sizeof(double) * (3 + e->nelem), cudaMemcpyDeviceToHost, e->stream));
   CU(cudaStreamSynchronize(e->stream));
-  if (winner) *winner = (int)((long long)e->h_record[1] - e->offset);
+  e->record_fresh = true; e->h2d_pending = false;
+  // sharded: the winner may live on another rank (then *winner = -1)
+  const long long local = (long long)e->h_record[1] - e->offset;
+  if (winner) *winner = (local >= 0 && local < e->N) ? (int)local : -1;
   if (winner_return) *winner_return = e->h_record[0];
   if (nominal_return) *nominal_return = e->h_record[2];
   return 0;
@@ -522,11 +637,23 @@ int ps_last_kernel_ms(PsEngine* e, float* perturb_ms, float* rollout_ms, float* 
   return 0;
 }
 
+/* device time of the cross-rank winner exchange of the last iteration (0 without a communicator) */
+int ps_last_exchange_ms(PsEngine* e, float* ms) {
+  if (!e) return fail("null engine");
+  CU(cudaSetDevice(e->device));
+  CU(cudaEventSynchronize(e->ev_x));
+  if (ms) CU(cudaEventElapsedTime(ms, e->ev[3], e->ev_x));
+  return 0;
+}
+
+/* bytes of constants the last iteration uploaded (the whole block after a model / task change, else the plan part) */
+int ps_last_upload_bytes(PsEngine* e) { return e ? (int)e->last_upload : -1; }
+
 int ps_kernel_launch_count(PsEngine* e, long long* launches) { if (!e) return fail("null engine"); *launches = e->launches; return 0; }
 
 int ps_winner_record_device(PsEngine* e, void** device_ptr, int* count) {
   if (!e) return fail("null engine");
-  if (device_ptr) *device_ptr = e->d_record;
+  if (device_ptr) *device_ptr = e->comm ? e->d_global : e->d_record;
   if (count) *count = 3 + e->nelem;
   return 0;
 }
@@ -557,10 +684,18 @@ int ps_fp64_peak(PsEngine* e, int reps, double* tflops) {
 /* host copy of the winner record fetched by the last ps_rollouts: [return, global index, nominal return, knots[P*nu]] */
 int ps_get_winner_record(PsEngine* e, double* out, int cap) {
   if (!e || e->N <= 0) return fail("ps_get_winner_record: nothing rolled out");
+  if (!e->record_fresh) return fail("ps_get_winner_record: the host record is stale (ps_rollouts_async does not fetch it; call ps_sync_record)");
   const int n = 3 + e->nelem;
   if (cap < n) return fail("ps_get_winner_record: buffer too small");
   for (int i = 0; i < n; i++) out[i] = e->h_record[i];
   return 0;
+}
+
+/* after ps_rollouts_async: wait for the iteration and fetch the winner record (what ps_rollouts does itself) */
+int ps_sync_record(PsEngine* e, int* winner, double* winner_return, double* nominal_return) {
+  if (!e || e->N <= 0) return fail("ps_sync_record: nothing rolled out");
+  CU(cudaSetDevice(e->device));
+  return fetch_record(e, winner, winner_return, nominal_return);
 }
 
 int ps_stream(PsEngine* e, void** stream) { if (!e) return fail("null engine"); *stream = (void*)e->stream; return 0; }

@@ -113,6 +113,26 @@ __global__ void argmin_kernel(const MinLoc* __restrict__ block_min, int nblocks,
   for (int e = threadIdx.x; e < nelem; e += blockDim.x) record[3 + e] = knots[(size_t)e * stride + w];
 }
 
+// ---------------------------------------------------------------- K3x: cross-rank min-loc over gathered winner records
+// all[world][count] (one ncclAllGather of every rank's record) -> out[count] = the record with the lowest return,
+// ties to the lowest global sample index; out[2] = the nominal return, i.e. rank 0's (global sample 0 lives there).
+__global__ void select_winner_kernel(const double* __restrict__ all, int world, int count, double* __restrict__ out) {
+  __shared__ int best_s;
+  if (threadIdx.x == 0) {
+    int best = 0;
+    for (int r = 1; r < world; r++) {
+      double c = all[(size_t)r * count], bc = all[(size_t)best * count];
+      if (!(c == c)) c = 1.0e300;
+      if (!(bc == bc)) bc = 1.0e300;
+      if (c < bc || (c == bc && all[(size_t)r * count + 1] < all[(size_t)best * count + 1])) best = r;
+    }
+    best_s = best;
+  }
+  __syncthreads();
+  const double* src = all + (size_t)best_s * count;
+  for (int k = threadIdx.x; k < count; k += blockDim.x) out[k] = k == 2 ? all[2] : src[k];
+}
+
 // ---------------------------------------------------------------- K4 / K5: cross-entropy elite update
 // Rank of every candidate under (return, index) order -- the total order of the partial_sort in
 // cross_entropy/planner.cc:201-207 with ties broken by index; NaN sorts last.  O(n^2 / tile) compares

@@ -3,6 +3,7 @@
 #pragma once
 #include "ps_kernels.cuh"
 #include "ps_coop_rollout.cuh"
+#include <cstddef>
 #include "ps_host_model.h"
 
 namespace ps {
@@ -100,7 +101,7 @@ inline int launch_sparse(cudaStream_t st, const void* dconst, const double* knot
 }
 
 struct Variant {
-  const char* name; size_t const_bytes; int block; bool coop; bool euler_only;
+  const char* name; size_t const_bytes; size_t plan_offset, plan_bytes; int block; bool coop; bool euler_only;
   int (*fill)(const PsModel*, const PairList&, void*, std::string*);
   void (*options)(void*, double, int);
   void (*debug)(void*, int);
@@ -119,18 +120,18 @@ int launch_robust_planar_coop(cudaStream_t, const void*, const double*, int, int
 int launch_robust_legged_coop(cudaStream_t, const void*, const double*, int, int, double*, unsigned char*, Writeback, XfrcNoise);
 template <class T, int BLOCK>
 inline Variant make_variant(const char* name, RobustFn robust) {
-  return Variant{name, sizeof(Constants<T>), BLOCK, false, T::LEAN, fill_model<T>, set_options<T>, set_debug<T>, set_task<T>, set_plan<T>, launch_rollout<T, BLOCK>, robust};
+  return Variant{name, sizeof(Constants<T>), offsetof(Constants<T>, p), sizeof(DevPlan<T>), BLOCK, false, T::LEAN, fill_model<T>, set_options<T>, set_debug<T>, set_task<T>, set_plan<T>, launch_rollout<T, BLOCK>, robust};
 }
 template <class T, int WARPS>
 inline Variant make_coop_variant(const char* name, RobustFn robust = nullptr) {
-  return Variant{name, sizeof(Constants<T>), WARPS * 32, true, true, fill_model<T>, set_options<T>, set_debug<T>, set_task<T>, set_plan<T>, launch_coop<T, WARPS>, robust};
+  return Variant{name, sizeof(Constants<T>), offsetof(Constants<T>, p), sizeof(DevPlan<T>), WARPS * 32, true, true, fill_model<T>, set_options<T>, set_debug<T>, set_task<T>, set_plan<T>, launch_coop<T, WARPS>, robust};
 }
 const Variant* variant_tiny();
 const Variant* variant_planar();
 const Variant* variant_legged();
 template <class T, int BLOCK>
 inline Variant make_sparse_variant(const char* name) {
-  return Variant{name, sizeof(Constants<T>), BLOCK, true, true, fill_model<T>, set_options<T>, set_debug<T>, set_task<T>, set_plan<T>, launch_sparse<T, BLOCK>, nullptr};
+  return Variant{name, sizeof(Constants<T>), offsetof(Constants<T>, p), sizeof(DevPlan<T>), BLOCK, true, true, fill_model<T>, set_options<T>, set_debug<T>, set_task<T>, set_plan<T>, launch_sparse<T, BLOCK>, nullptr};
 }
 const Variant* variant_planar_sparse();
 const Variant* variant_legged_sparse();

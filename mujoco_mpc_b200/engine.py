@@ -17,7 +17,8 @@ EXPORTS = ["ps_last_error", "ps_create", "ps_destroy", "ps_set_model", "ps_set_o
            "ps_get_returns", "ps_get_knots", "ps_get_trajectory", "ps_get_all_trajectories", "ps_last_kernel_ms",
            "ps_kernel_launch_count", "ps_winner_record_device", "ps_stream", "ps_name", "ps_variant", "ps_fp64_peak", "ps_constants_bytes",
            "ps_set_param_std", "ps_elite_update", "ps_elite_update_ms", "ps_get_all_traces",
-           "ps_set_engine_flavour", "ps_rollout_candidates"]
+           "ps_set_engine_flavour", "ps_rollout_candidates", "ps_comm_unique_id", "ps_comm_init", "ps_comm_info",
+           "ps_last_exchange_ms", "ps_sync_record", "ps_last_upload_bytes"]
 
 
 class EngineError(RuntimeError):
@@ -48,6 +49,26 @@ def _p(a):
 
 def _arr(x):
     return np.ascontiguousarray(np.asarray(x, dtype=np.float64))
+
+
+def comm_unique_id():
+    """128-byte ncclUniqueId created by the engine library (rank 0 calls this, the host distributes it)"""
+    buf = ctypes.create_string_buffer(128)
+    if lib().ps_comm_unique_id(buf, 128) < 0:
+        raise EngineError(lib().ps_last_error().decode())
+    return buf.raw
+
+
+def broadcast_unique_id(dist, rank):
+    """rank 0's ncclUniqueId to every rank of an initialised torch.distributed group (any backend)"""
+    import torch
+    backend = dist.get_backend()
+    dev = torch.device("cuda", torch.cuda.current_device()) if backend == "nccl" else torch.device("cpu")
+    t = torch.zeros(128, dtype=torch.uint8, device=dev)
+    if rank == 0:
+        t = torch.frombuffer(bytearray(comm_unique_id()), dtype=torch.uint8).to(dev)
+    dist.broadcast(t, src=0)
+    return bytes(t.cpu().numpy().tobytes())
 
 
 class Engine:
@@ -202,6 +223,39 @@ class Engine:
         n = ctypes.c_longlong()
         self._ck(self.L.ps_kernel_launch_count(self.h, ctypes.byref(n)))
         return n.value
+
+    def kernel_ms4(self):
+        """(perturb, rollout, argmin, cross-rank exchange) device ms of the last iteration"""
+        x = ctypes.c_float()
+        self._ck(self.L.ps_last_exchange_ms(self.h, ctypes.byref(x)))
+        return self.kernel_ms() + (x.value,)
+
+    def upload_bytes(self):
+        return int(self.L.ps_last_upload_bytes(self.h))
+
+    def sync_record(self):
+        w = ctypes.c_int(); wr = ctypes.c_double(); nr = ctypes.c_double()
+        self._ck(self.L.ps_sync_record(self.h, ctypes.byref(w), ctypes.byref(wr), ctypes.byref(nr)))
+        return w.value, wr.value, nr.value
+
+    def winner_record(self):
+        out = np.zeros(3 + self.P * self.model.nu)
+        self._ck(self.L.ps_get_winner_record(self.h, _p(out), out.size))
+        return out
+
+    def comm_init(self, rank, world, unique_id):
+        """join the engine's NCCL communicator (collective over all ranks); unique_id: 128 bytes from comm_unique_id()"""
+        buf = (ctypes.c_char * 128).from_buffer_copy(bytes(unique_id))
+        self._ck(self.L.ps_comm_init(self.h, int(rank), int(world), buf))
+
+    def comm_init_torch(self, dist, rank, world):
+        """distribute rank 0's ncclUniqueId over an existing torch.distributed group, then ps_comm_init"""
+        self.comm_init(rank, world, broadcast_unique_id(dist, rank))
+
+    def comm_info(self):
+        r = ctypes.c_int(); w = ctypes.c_int(); v = ctypes.c_int()
+        self._ck(self.L.ps_comm_info(self.h, ctypes.byref(r), ctypes.byref(w), ctypes.byref(v)))
+        return r.value, w.value, v.value
 
     def winner_record_ptr(self):
         p = ctypes.c_void_p(); n = ctypes.c_int()

@@ -87,9 +87,9 @@ void CudaCrossEntropyPlanner::SetTask(const PsTask* task) {
   if (ps_set_task(engine_, task)) Fail("ps_set_task");
 }
 
-void CudaCrossEntropyPlanner::SetNoise(const double* z, int N) {
+void CudaCrossEntropyPlanner::SetNoise(const double* z, int N, int P) {
   noise_pending_ = true; noise_n_ = z ? N : 0; noise_z_.clear();
-  if (z) noise_z_.assign(z, z + (size_t)N * policy.num_spline_points * model_->nu);
+  if (z) noise_z_.assign(z, z + (size_t)N * (P > 0 ? P : policy.num_spline_points) * model_->nu);
 }
 void CudaCrossEntropyPlanner::SetSeed(unsigned long long seed) { ps_set_seed(engine_, seed); }
 
@@ -128,6 +128,11 @@ void CudaCrossEntropyPlanner::OptimizePolicy(int horizon) {
   if (ps_set_options(engine_, model_->opt_timestep, model_->opt_integrator)) Fail("ps_set_options");
   if (ps_set_state(engine_, state.data(), mocap.data(), userdata.data(), time)) Fail("ps_set_state");
   if (ps_set_nominal(engine_, resampled_policy.plan.times().data(), resampled_policy.plan.values().data(), P, interpolation_)) Fail("ps_set_nominal");
+  if (noise_n_ && (noise_n_ < num_trajectory || noise_z_.size() != (size_t)noise_n_ * np)) {
+    std::fprintf(stderr, "CudaCrossEntropyPlanner: injected noise is [%d][%zu] but the iteration needs [>= %d][%d]\n", noise_n_,
+                 noise_n_ ? noise_z_.size() / noise_n_ : 0, num_trajectory, np);
+    std::abort();
+  }
   if (noise_pending_) {
     // the injected tensor covers the num_trajectory candidates; the nominal column is never noised
     std::vector<double> z(noise_z_);

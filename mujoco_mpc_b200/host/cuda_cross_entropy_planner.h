@@ -32,7 +32,7 @@ class CudaCrossEntropyPlanner {
   int NumParameters() const { return policy.num_spline_points * model_->nu; }
 
   // ---- engine-specific controls
-  void SetNoise(const double* z, int N);      // injected N(0,1) tensor [N][P][nu] (parity runs)
+  void SetNoise(const double* z, int N, int P = -1);   // injected N(0,1) tensor [N][P][nu] (parity runs); P < 0: num_spline_points
   void SetSeed(unsigned long long seed);
   PsEngine* engine() { return engine_; }
 

@@ -104,11 +104,11 @@ void CudaSamplingPlanner::SetTask(const PsTask* task) {
 
 // The tensor is [N][P][nu]; P is only fixed once the nominal has been resampled, so the upload is
 // deferred to the next OptimizePolicyCandidates (after ps_set_nominal).
-void CudaSamplingPlanner::SetNoise(const double* z, const unsigned char* use_std2, int N) {
+void CudaSamplingPlanner::SetNoise(const double* z, const unsigned char* use_std2, int N, int P) {
   noise_pending_ = true; noise_n_ = z ? N : 0;
   noise_z_.clear(); noise_std2_.clear();
   if (z) {
-    noise_z_.assign(z, z + (size_t)N * policy.num_spline_points * model_->nu);
+    noise_z_.assign(z, z + (size_t)N * (P > 0 ? P : policy.num_spline_points) * model_->nu);
     if (use_std2) noise_std2_.assign(use_std2, use_std2 + N);
   }
 }
@@ -122,7 +122,13 @@ void CudaSamplingPlanner::SetPolicy(const double* times, const double* knots, in
   candidate_winner_.plan = policy.plan;
 }
 void CudaSamplingPlanner::SetSharding(int rank, int world, AllGatherFn fn, void* ctx) {
-  rank_ = rank; world_ = world; gather_ = fn; gather_ctx_ = ctx;
+  rank_ = rank; world_ = world; gather_ = fn; gather_ctx_ = ctx; native_comm_ = false;
+}
+
+// the engine's own NCCL exchange (ps_comm_init): the record ps_rollouts fetches is already the global one
+void CudaSamplingPlanner::SetShardingNative(int rank, int world, const void* nccl_unique_id) {
+  if (ps_comm_init(engine_, rank, world, nccl_unique_id)) Fail("ps_comm_init");
+  rank_ = rank; world_ = world; gather_ = nullptr; gather_ctx_ = nullptr; native_comm_ = world > 1;
 }
 
 // planner.cc:236-310
@@ -172,6 +178,12 @@ int CudaSamplingPlanner::OptimizePolicyCandidates(int ncandidates, int horizon) 
   if (ps_set_options(engine_, model_->opt_timestep, model_->opt_integrator)) Fail("ps_set_options");   // agent.cc:275-276
   if (ps_set_state(engine_, state.data(), mocap.data(), userdata.data(), time)) Fail("ps_set_state");
   if (ps_set_nominal(engine_, policy.plan.times().data(), policy.plan.values().data(), P, interpolation_)) Fail("ps_set_nominal");
+  if (noise_n_ && (noise_n_ < num_trajectory || noise_z_.size() != (size_t)noise_n_ * P * nu)) {
+    // the injected tensor is indexed [sample][knot][actuator] with THIS iteration's P: a mismatch would misalign it
+    std::fprintf(stderr, "CudaSamplingPlanner: injected noise is [%d][%zu] but the iteration needs [>= %d][%d]\n", noise_n_,
+                 noise_n_ ? noise_z_.size() / noise_n_ : 0, num_trajectory, P * nu);
+    std::abort();
+  }
   if (noise_pending_) {
     if (ps_set_noise(engine_, noise_n_ ? noise_z_.data() : nullptr, noise_std2_.empty() ? nullptr : noise_std2_.data(), noise_n_)) Fail("ps_set_noise");
     noise_pending_ = false;
@@ -184,7 +196,8 @@ int CudaSamplingPlanner::OptimizePolicyCandidates(int ncandidates, int horizon) 
   std::vector<double> rec(count);
   if (ps_get_winner_record(engine_, rec.data(), count)) Fail("ps_get_winner_record");
   long long global_winner = (long long)rec[1];
-  winner_is_local_ = true; local_winner_ = local_winner;
+  winner_is_local_ = local_winner >= 0; local_winner_ = local_winner >= 0 ? local_winner : 0;
+  if (native_comm_) { wret = rec[0]; nret = rec[2]; }   // the all-gather min-loc already ran on the engine's stream
   if (world_ > 1 && gather_) {
     // min-loc over ranks: every rank contributes (return, global index, nominal return, knots)
     std::vector<double> all((size_t)world_ * count);
@@ -275,6 +288,8 @@ void CudaSamplingPlanner::NominalTrajectory(int horizon) {
   if (ps_set_nominal(engine_, src.plan.times().data(), src.plan.values().data(), src.plan.Size(), src.plan.Interpolation())) Fail("ps_set_nominal");
   int w; double a, b;
   if (ps_rollouts(engine_, 1, horizon, 0.0, 0.0, 0, &w, &a, &b)) Fail("ps_rollouts");
+  // the engine batch is now this single rollout: candidates of the previous iteration are gone
+  ranked_.clear(); ranked_score_.clear(); trajectory_order.clear(); ranked_local_.clear();
   last_horizon_ = horizon; local_winner_ = 0; winner_is_local_ = true; best_valid_ = false; winner = 0;
 }
 

@@ -62,10 +62,16 @@ class CudaSamplingPlanner {
   void CopyCandidateToPolicy(int candidate);                                          // :525-534
 
   // ---- engine-specific controls
-  void SetNoise(const double* z, const unsigned char* use_std2, int N);   // injected N(0,1) tensor (parity runs)
+  // injected N(0,1) tensor z[N][P][nu] (parity runs); P = knots per sample in z (< 0: policy.num_spline_points).
+  // The next iteration aborts unless N >= num_trajectory and P equals the number of nodes of its plan.
+  void SetNoise(const double* z, const unsigned char* use_std2, int N, int P = -1);
   void SetSeed(unsigned long long seed);
+  // the GUI's spline-point slider (planner.cc:439-446): policy, previous_policy and the winner the next
+  // UpdateNominalPolicy resamples from all take the new count at once
+  void SetNumSplinePoints(int n) { policy.num_spline_points = n; previous_policy.num_spline_points = n; candidate_winner_.num_spline_points = n; }
   void SetPolicy(const double* times, const double* knots, int P, int interpolation);   // start from a given nominal (parity runs)
   void SetSharding(int rank, int world, AllGatherFn fn, void* ctx);       // samples [rank*N, (rank+1)*N) of world*N
+  void SetShardingNative(int rank, int world, const void* nccl_unique_id);   // same, exchange = the engine's ncclAllGather (ps_comm_init)
   PsEngine* engine() { return engine_; }
   const SamplingPolicy& CandidatePolicy(int candidate) const { return ranked_[candidate]; }   // candidate_policy[trajectory_order[c]]
   const PsModel* model() const { return model_; }
@@ -93,7 +99,7 @@ class CudaSamplingPlanner {
   std::vector<int> ranked_local_;            // local sample index of each candidate (-1: lives on another rank)
   Trajectory best_; bool best_valid_ = false; int last_horizon_ = 0;
   double nominal_return_ = 0, winner_return_ = 0;
-  int rank_ = 0, world_ = 1; AllGatherFn gather_ = nullptr; void* gather_ctx_ = nullptr;
+  int rank_ = 0, world_ = 1; AllGatherFn gather_ = nullptr; void* gather_ctx_ = nullptr; bool native_comm_ = false;
   bool winner_is_local_ = true; int local_winner_ = 0;
   std::vector<double> noise_z_; std::vector<unsigned char> noise_std2_; int noise_n_ = 0; bool noise_pending_ = false;
   mutable std::shared_mutex mtx_;

@@ -35,14 +35,15 @@ void psp_configure(void* h, int num_trajectory, int interpolation, int num_splin
   CudaSamplingPlanner* p = (CudaSamplingPlanner*)h;
   if (num_trajectory > 0) p->num_trajectory_ = num_trajectory;
   if (interpolation >= 0) p->interpolation_ = interpolation;
-  if (num_spline_points > 0) { p->policy.num_spline_points = num_spline_points; p->previous_policy.num_spline_points = num_spline_points; }
+  if (num_spline_points > 0) p->SetNumSplinePoints(num_spline_points);
   if (sigma0 >= 0) p->noise_exploration[0] = sigma0;
   if (sigma1 >= 0) p->noise_exploration[1] = sigma1;
   if (sliding >= 0) p->sliding_plan_ = sliding;
 }
-void psp_set_noise(void* h, const double* z, const unsigned char* use_std2, int N) { ((CudaSamplingPlanner*)h)->SetNoise(z, use_std2, N); }
+void psp_set_noise(void* h, const double* z, const unsigned char* use_std2, int N, int P) { ((CudaSamplingPlanner*)h)->SetNoise(z, use_std2, N, P); }
 void psp_set_seed(void* h, unsigned long long seed) { ((CudaSamplingPlanner*)h)->SetSeed(seed); }
 void psp_set_sharding(void* h, int rank, int world, mjpc_b200::AllGatherFn fn, void* ctx) { ((CudaSamplingPlanner*)h)->SetSharding(rank, world, fn, ctx); }
+void psp_set_sharding_native(void* h, int rank, int world, const void* nccl_unique_id) { ((CudaSamplingPlanner*)h)->SetShardingNative(rank, world, nccl_unique_id); }
 void psp_optimize_policy(void* h, int horizon) { ((CudaSamplingPlanner*)h)->OptimizePolicy(horizon); }
 int psp_optimize_policy_candidates(void* h, int ncandidates, int horizon) { return ((CudaSamplingPlanner*)h)->OptimizePolicyCandidates(ncandidates, horizon); }
 double psp_candidate_score(void* h, int c) { return ((CudaSamplingPlanner*)h)->CandidateScore(c); }
@@ -122,7 +123,7 @@ void pce_set_policy(void* h, const double* times, const double* knots, int P, in
 }
 void pce_set_variance(void* h, const double* v, int n) { CudaCrossEntropyPlanner* p = (CudaCrossEntropyPlanner*)h; for (int i = 0; i < n && i < (int)p->variance.size(); i++) p->variance[i] = v[i]; }
 int pce_get_variance(void* h, double* v, int cap) { CudaCrossEntropyPlanner* p = (CudaCrossEntropyPlanner*)h; int n = cap < (int)p->variance.size() ? cap : (int)p->variance.size(); std::memcpy(v, p->variance.data(), sizeof(double) * n); return n; }
-void pce_set_noise(void* h, const double* z, int N) { ((CudaCrossEntropyPlanner*)h)->SetNoise(z, N); }
+void pce_set_noise(void* h, const double* z, int N, int P) { ((CudaCrossEntropyPlanner*)h)->SetNoise(z, N, P); }
 void pce_set_seed(void* h, unsigned long long seed) { ((CudaCrossEntropyPlanner*)h)->SetSeed(seed); }
 void pce_optimize_policy(void* h, int horizon) { ((CudaCrossEntropyPlanner*)h)->OptimizePolicy(horizon); }
 void pce_nominal_trajectory(void* h, int horizon) { ((CudaCrossEntropyPlanner*)h)->NominalTrajectory(horizon); }

@@ -82,10 +82,11 @@ class CudaSamplingPlanner:
 
     def SetNoise(self, z, use_std2=None):
         if z is None:
-            self.L.psp_set_noise(self.h, None, None, 0); return
+            self.L.psp_set_noise(self.h, None, None, 0, -1); return
         z = _arr(z)
         u = np.ascontiguousarray(use_std2, dtype=np.uint8) if use_std2 is not None else None
-        self.L.psp_set_noise(self.h, _p(z), u.ctypes.data_as(ctypes.POINTER(ctypes.c_ubyte)) if u is not None else None, z.shape[0])
+        z = z.reshape(z.shape[0], -1, self.model.nu)
+        self.L.psp_set_noise(self.h, _p(z), u.ctypes.data_as(ctypes.POINTER(ctypes.c_ubyte)) if u is not None else None, z.shape[0], z.shape[1])
 
     def SetSeed(self, seed):
         self.L.psp_set_seed(self.h, ctypes.c_ulonglong(seed))
@@ -107,6 +108,14 @@ class CudaSamplingPlanner:
                 return -1
         self._cb = ALLGATHER(cb)
         self.L.psp_set_sharding(self.h, rank, world, self._cb, None)
+
+    def SetShardingNative(self, rank, world, dist):
+        """sample sharding with the winner exchange inside the engine library (ncclAllGather + min-loc kernel);
+        `dist`: an initialised torch.distributed module, used once to hand rank 0's ncclUniqueId to every rank"""
+        from .engine import broadcast_unique_id
+        uid = broadcast_unique_id(dist, rank)
+        buf = (ctypes.c_char * 128).from_buffer_copy(uid)
+        self.L.psp_set_sharding_native(self.h, int(rank), int(world), buf)
 
     def OptimizePolicy(self, horizon):
         self.horizon = horizon
@@ -221,8 +230,8 @@ class CudaCrossEntropyPlanner:
 
     def SetNoise(self, z):
         if z is None:
-            self.L.pce_set_noise(self.h, None, 0); return
-        z = _arr(z); self.L.pce_set_noise(self.h, _p(z), z.shape[0])
+            self.L.pce_set_noise(self.h, None, 0, -1); return
+        z = _arr(z); z = z.reshape(z.shape[0], -1, self.model.nu); self.L.pce_set_noise(self.h, _p(z), z.shape[0], z.shape[1])
 
     def SetSeed(self, seed):
         self.L.pce_set_seed(self.h, ctypes.c_ulonglong(seed))

@@ -3,11 +3,65 @@
 // and SamplingPlanner::{UpdateNominalPolicy,AddNoiseToPolicy,Rollouts,OptimizePolicy}
 // (planners/sampling/planner.cc:190-208,236-380,525-534) with injected noise.
 #include <algorithm>
+#include <atomic>
+#include <condition_variable>
+#include <functional>
+#include <mutex>
 #include <thread>
 #include "mm_planner.h"
 #include "mm_math.h"
 
 namespace mm {
+
+// Persistent worker pool of the CPU arm (stands in for mjpc::ThreadPool, mjpc/threadpool.cc:30-85): threads are
+// created once, every parallelFor hands out indices one at a time from an atomic counter (dynamic scheduling, so a
+// slow contact-rich rollout does not hold a whole static stripe back), worker k always passes tid = k.
+class WorkerPool {
+ public:
+  static WorkerPool& get() { static WorkerPool p; return p; }
+  void parallelFor(int n, int nthread, const std::function<void(int, int)>& fn) {
+    if (nthread <= 1 || n <= 1) { for (int i = 0; i < n; i++) fn(0, i); return; }
+    std::unique_lock<std::mutex> run(run_mtx_);              // one parallelFor at a time
+    grow(nthread - 1);
+    {
+      std::lock_guard<std::mutex> lk(mtx_);
+      fn_ = &fn; n_ = n; next_.store(0); active_ = nthread - 1; pending_ = nthread - 1; generation_++;
+    }
+    cv_.notify_all();
+    for (int i; (i = next_.fetch_add(1)) < n;) fn(0, i);     // the caller is worker 0
+    std::unique_lock<std::mutex> lk(mtx_);
+    done_.wait(lk, [&] { return pending_ == 0; });
+    fn_ = nullptr;
+  }
+  ~WorkerPool() {
+    { std::lock_guard<std::mutex> lk(mtx_); stop_ = true; generation_++; }
+    cv_.notify_all();
+    for (auto& t : threads_) t.join();
+  }
+ private:
+  void grow(int want) {
+    while ((int)threads_.size() < want) {
+      const int id = (int)threads_.size() + 1;
+      threads_.emplace_back([this, id] {
+        unsigned long seen = 0;
+        for (;;) {
+          const std::function<void(int, int)>* fn; int n;
+          {
+            std::unique_lock<std::mutex> lk(mtx_);
+            cv_.wait(lk, [&] { return stop_ || (generation_ != seen && id <= active_); });
+            if (stop_) return;
+            seen = generation_; fn = fn_; n = n_;
+          }
+          for (int i; (i = next_.fetch_add(1)) < n;) (*fn)(id, i);
+          { std::lock_guard<std::mutex> lk(mtx_); if (--pending_ == 0) done_.notify_one(); }
+        }
+      });
+    }
+  }
+  std::vector<std::thread> threads_; std::mutex mtx_, run_mtx_; std::condition_variable cv_, done_;
+  const std::function<void(int, int)>* fn_ = nullptr; int n_ = 0, active_ = 0, pending_ = 0; std::atomic<int> next_{0};
+  unsigned long generation_ = 0; bool stop_ = false;
+};
 
 void policyAction(const Model* m, const Policy& p, double t, double* action) {
   splineSample(p.times.data(), p.knots.data(), p.P(), m->nu, p.interp, t, action);
@@ -137,12 +191,9 @@ void optimizePolicy(Planner* pl, int N, int horizon, const double* z, const unsi
   }
   nthread = std::max(1, nthread);
   if ((int)pl->data.size() < nthread) { size_t old = pl->data.size(); pl->data.resize(nthread); for (size_t k = old; k < pl->data.size(); k++) makeData(m, &pl->data[k]); }
-  auto work = [&](int tid) {
-    for (int i = tid; i < N; i += nthread)
-      rollout(m, &pl->task, &pl->data[tid], pl->candidate[i], pl->state.data(), pl->time, pl->mocap.data(), pl->userdata.data(), horizon, &pl->trajectory[i]);
-  };
-  if (nthread == 1) work(0);
-  else { std::vector<std::thread> th; for (int k = 0; k < nthread; k++) th.emplace_back(work, k); for (auto& x : th) x.join(); }
+  WorkerPool::get().parallelFor(N, nthread, [&](int tid, int i) {
+    rollout(m, &pl->task, &pl->data[tid], pl->candidate[i], pl->state.data(), pl->time, pl->mocap.data(), pl->userdata.data(), horizon, &pl->trajectory[i]);
+  });
   int best = 0;
   for (int i = 1; i < N; i++) if (pl->trajectory[i].total_return < pl->trajectory[best].total_return) best = i;
   pl->winner = best;
@@ -179,13 +230,10 @@ void optimizePolicyCE(Planner* pl, int N, int horizon, const double* z, int nthr
   }
   nthread = std::max(1, nthread);
   if ((int)pl->data.size() < nthread) { size_t old = pl->data.size(); pl->data.resize(nthread); for (size_t k = old; k < pl->data.size(); k++) makeData(m, &pl->data[k]); }
-  auto work = [&](int tid) {
-    for (int i = tid; i <= N; i += nthread)
-      rollout(m, &pl->task, &pl->data[tid], i < N ? pl->candidate[i] : rp, pl->state.data(), pl->time, pl->mocap.data(), pl->userdata.data(), horizon,
-              i < N ? &pl->trajectory[i] : &pl->nominal_trajectory);
-  };
-  if (nthread == 1) work(0);
-  else { std::vector<std::thread> th; for (int k = 0; k < nthread; k++) th.emplace_back(work, k); for (auto& x : th) x.join(); }
+  WorkerPool::get().parallelFor(N + 1, nthread, [&](int tid, int i) {
+    rollout(m, &pl->task, &pl->data[tid], i < N ? pl->candidate[i] : rp, pl->state.data(), pl->time, pl->mocap.data(), pl->userdata.data(), horizon,
+            i < N ? &pl->trajectory[i] : &pl->nominal_trajectory);
+  });
   pl->trajectory_order.resize(N);
   for (int i = 0; i < N; i++) pl->trajectory_order[i] = i;
   std::stable_sort(pl->trajectory_order.begin(), pl->trajectory_order.end(), [&](int a, int b) {

@@ -236,6 +236,8 @@ int ps_get_knots(PsEngine* e, int sample, double* knots) {
   std::copy(e->knots.begin() + (size_t)sample * nelem, e->knots.begin() + (size_t)(sample + 1) * nelem, knots);
   return 0;
 }
+// no multi-GPU exchange in the host stand-in (the sharded-planner CPU tests use the AllGatherFn callback)
+int ps_comm_init(PsEngine*, int, int world, const void*) { return world == 1 ? 0 : fail("ps_comm_init: host stand-in has no NCCL"); }
 int ps_get_winner_record(PsEngine* e, double* out, int cap) {
   if (e->record.empty() || cap < (int)e->record.size()) return fail("ps_get_winner_record: no record / buffer too small");
   std::copy(e->record.begin(), e->record.end(), out); return 0;

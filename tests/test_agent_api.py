@@ -129,7 +129,9 @@ def test_action_averaging(hostlib):
     with make("Cartpole") as agent:
         agent.set_task_parameter("Goal", 0.5)
         plan(agent, N=8)
-        dt = agent.settings["timestep"]
+        # the averaging grid is the PLANT time step (0.001 for Cartpole), not the agent's 0.01 (agent_service.cc:118-120)
+        dt = agent.plant_model.opt_timestep
+        assert dt != agent.settings["timestep"]
         a0 = agent.get_action(time=0.0)
         avg = agent.get_action(time=0.0, averaging_duration=3 * dt)
         grid = [agent.get_action(time=k * dt) for k in range(5)]
@@ -175,9 +177,8 @@ def test_other_planners_behind_the_same_agent(hostlib, name):
         assert agent.get_state()["time"] > 0 and np.all(np.isfinite(agent.get_action()))
 
 
-# ---- GPU: the same facade over the real engine, device noise.  Not yet run on hardware.
+# ---- GPU: the same facade over the real engine, device noise (green on hardware since the round-1 driver run)
 @pytest.mark.gpu
-@pytest.mark.xfail(strict=False, reason="not yet run on a B200 (GPU budget of the round exhausted)")
 @pytest.mark.parametrize("planner_name", ["Sampling", "Cross Entropy", "Robust Sampling"])
 def test_agent_on_the_device(planner_name):
     from tests.common import run_isolated

@@ -15,9 +15,7 @@ from mujoco_mpc_b200 import registry, task as T
 from mujoco_mpc_b200.engine import Engine
 from tests.common import run_isolated, synthetic_state
 
-# Written after this round's GPU minutes were spent: these have not run on hardware yet, so a failure is
-# reported (xfail) instead of turning the suite red; a pass shows up as XPASS.
-pytestmark = [pytest.mark.gpu, pytest.mark.xfail(strict=False, reason="not yet run on a B200 (GPU budget of the round exhausted)")]
+pytestmark = [pytest.mark.gpu]
 
 
 def make(name, engine=None):

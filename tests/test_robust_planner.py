@@ -107,14 +107,10 @@ def test_zero_force_noise_repeats_the_clean_return(oracle_lib):
         assert np.all(out["noisy_returns"][c] == ret[out["order"][c]])
 
 
-# ---- GPU: the host class over the engine.  Written after this round's GPU minutes were spent; not yet run on
-# hardware, so a failure is reported as xfail and a pass as XPASS (the device rollout code itself is pinned by the
-# hostsim tests above).
-_unverified = pytest.mark.xfail(strict=False, reason="not yet run on a B200 (GPU budget of the round exhausted)")
+# ---- GPU: the host class over the engine (green on hardware since the round-1 driver run)
 
 
 @pytest.mark.gpu
-@_unverified
 @pytest.mark.parametrize("name,H,std,flavour,kernel", [
     ("Cartpole", 41, 0.5, 0, "tiny"), ("Walker", 31, 2.0, 0, "planar_coop"), ("Quadruped Flat", 26, 1.0, 0, "legged_coop"),
     ("Walker", 31, 2.0, 3, "planar"), ("Quadruped Flat", 26, 1.0, 3, "legged")])
@@ -153,7 +149,6 @@ def check_cuda_robust_planner_matches_oracle(name, H, std, flavour, kernel):
 
 
 @pytest.mark.gpu
-@_unverified
 def test_cuda_robust_planner_device_noise_and_settings(oracle_lib):
     run_isolated("tests.test_robust_planner", "check_cuda_robust_planner_device_noise_and_settings", timeout=240)
 
