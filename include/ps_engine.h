@@ -151,6 +151,19 @@ int ps_last_upload_bytes(PsEngine* e);
 /* measured FP64 FMA throughput of the device (TFLOP/s): roofline denominator of the rollout kernel */
 int ps_fp64_peak(PsEngine* e, int reps, double* tflops);
 
+/* Allocation-free winner selection.  NO COUNTERPART IN THE REFERENCE: added for
+ * callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * It is the engine's argmin (block-level min-loc + grid-level min-loc, lowest index on ties, NaN never wins) over a
+ * caller-owned DEVICE array d_returns[n]; d_out (DEVICE, 2 doubles) receives [min return, sample_offset + index].
+ * The per-block partial results live in a file-scope __device__ array of ps_noalloc_scratch_bytes() bytes (16.6 KB,
+ * held by every GPU that loads the library until the process exits) instead of a cudaMalloc'ed buffer; the call
+ * performs no cudaMalloc / cudaFree / allocating library call and is asynchronous on `stream` (cudaStream_t, NULL =
+ * default stream).  n > PS_NOALLOC_MAX_RETURNS is rejected.  All calls on one device share the scratch: calls that
+ * overlap on the GPU (different streams, no dependency) race -- serialise them. */
+#define PS_NOALLOC_MAX_RETURNS (1 << 20)
+int ps_argmin_noalloc(int device_ordinal, void* stream, const double* d_returns, int n, long long sample_offset, double* d_out);
+int ps_noalloc_scratch_bytes(void);
+
 #ifdef __cplusplus
 }
 #endif

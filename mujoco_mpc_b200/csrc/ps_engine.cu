@@ -130,6 +130,8 @@ static int ensure(double** p, size_t* cap, size_t need) {
 extern "C" {
 
 const char* ps_last_error(void) { return g_error.c_str(); }
+/* other translation units of the library (ps_noalloc.cu) report through the same per-thread text */
+void ps_set_last_error_(const char* s) { g_error = s ? s : ""; }
 int ps_name(char* out, int cap) { std::snprintf(out, cap, "mujoco_mpc_b200 predictive-sampling engine (sm_100a)"); return 0; }
 
 PsEngine* ps_create(int device_ordinal) {

@@ -18,7 +18,7 @@ EXPORTS = ["ps_last_error", "ps_create", "ps_destroy", "ps_set_model", "ps_set_o
            "ps_kernel_launch_count", "ps_winner_record_device", "ps_stream", "ps_name", "ps_variant", "ps_fp64_peak", "ps_constants_bytes",
            "ps_set_param_std", "ps_elite_update", "ps_elite_update_ms", "ps_get_all_traces",
            "ps_set_engine_flavour", "ps_rollout_candidates", "ps_comm_unique_id", "ps_comm_init", "ps_comm_info",
-           "ps_last_exchange_ms", "ps_sync_record", "ps_last_upload_bytes"]
+           "ps_last_exchange_ms", "ps_sync_record", "ps_last_upload_bytes", "ps_argmin_noalloc", "ps_noalloc_scratch_bytes"]
 
 
 class EngineError(RuntimeError):
@@ -271,3 +271,13 @@ class Engine:
         p = ctypes.c_void_p()
         self._ck(self.L.ps_stream(self.h, ctypes.byref(p)))
         return p.value
+
+
+def argmin_noalloc(d_returns_ptr, n, d_out_ptr, sample_offset=0, device=0, stream=None):
+    """ps_argmin_noalloc: allocation-free min-loc over a caller-owned DEVICE array (raw pointers; asynchronous on `stream`)"""
+    L = lib()
+    L.ps_argmin_noalloc.argtypes = [ctypes.c_int, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int, ctypes.c_longlong, ctypes.c_void_p]
+    r = L.ps_argmin_noalloc(int(device), ctypes.c_void_p(stream or 0), ctypes.c_void_p(d_returns_ptr), int(n), int(sample_offset),
+                            ctypes.c_void_p(d_out_ptr))
+    if r != 0:
+        raise EngineError(L.ps_last_error().decode())
