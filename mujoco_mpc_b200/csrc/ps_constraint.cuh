@@ -266,18 +266,18 @@ PS_NT void make_constraints(const DevModel<T>& m, RolloutData<T>& d) {
   if (m.disableflags & DSBL_CONSTRAINT) return;
   if (T::CONTACTS) detect_contacts(m, d);
   if (!(m.disableflags & DSBL_FRICTIONLOSS))
-    for (int i = 0; i < nv; i++) if (m.dof_frictionloss[i] > 0) {
+    PS_SPEC_UNROLL for (int i = 0; i < nv; i++) if (m.dof_frictionloss[i] > 0) {
       const int r = d.nefc;
       if (!push_row(d, 0, 0, m.dof_frictionloss[i], EFC_FRICTION_DOF, i)) break;
       vzero(d.efc_J + r * S, nv); d.efc_J[r * S + i] = 1;
     }
   if (!(m.disableflags & DSBL_LIMIT))
-    for (int j = 0; j < m.njnt; j++) {
+    PS_SPEC_UNROLL for (int j = 0; j < m.njnt; j++) {
       if (!m.jnt_limited[j]) continue;
       const int jt = m.jnt_type[j];
       if (jt != JNT_HINGE && jt != JNT_SLIDE) continue;
       const double value = d.qpos[m.jnt_qposadr[j]], margin = m.jnt_margin[j];
-      for (int side = -1; side <= 1; side += 2) {
+      PS_SPEC_UNROLL for (int side = -1; side <= 1; side += 2) {
         const double dist = side * (m.jnt_range[2 * j + (side + 1) / 2] - value);
         if (dist < margin) {
           const int r = d.nefc;
@@ -459,12 +459,12 @@ PS_NT void update_cost(const DevModel<T>& m, RolloutData<T>& d, SolverScalars& c
   constexpr int S = T::NV; const int nv = nv_of(m);
   const double cc = update_rows(m, d, d.sv_Jaref, coneH);
   double g = 0;
-  for (int i = 0; i < nv; i++) g += 0.5 * (d.sv_Ma[i] - d.qfrc_smooth[i]) * (d.qacc[i] - d.qacc_smooth[i]);
+  PS_SPEC_UNROLL for (int i = 0; i < nv; i++) g += 0.5 * (d.sv_Ma[i] - d.qfrc_smooth[i]) * (d.qacc[i] - d.qacc_smooth[i]);
   c.gauss = g; c.prev_cost = c.cost; c.cost = g + cc;
   vzero(d.qfrc_constraint, nv);
   for (int r = 0; r < d.nefc; r++) {
     const double f = d.efc_force[r];
-    if (f != 0) for (int i = 0; i < nv; i++) d.qfrc_constraint[i] += d.efc_J[r * S + i] * f;
+    if (f != 0) PS_SPEC_UNROLL for (int i = 0; i < nv; i++) d.qfrc_constraint[i] += d.efc_J[r * S + i] * f;
   }
 }
 
@@ -472,37 +472,37 @@ PS_NT void update_cost(const DevModel<T>& m, RolloutData<T>& d, SolverScalars& c
 template <class T>
 PS_NT void newton_direction(const DevModel<T>& m, RolloutData<T>& d) {
   constexpr int S = T::NV; const int nv = nv_of(m), nefc = d.nefc;
-  for (int i = 0; i < nv; i++) d.sv_grad[i] = d.sv_Ma[i] - d.qfrc_smooth[i] - d.qfrc_constraint[i];
+  PS_SPEC_UNROLL for (int i = 0; i < nv; i++) d.sv_grad[i] = d.sv_Ma[i] - d.qfrc_smooth[i] - d.qfrc_constraint[i];
   double* H = d.sv_H;
-  for (int i = 0; i < nv; i++) for (int j = 0; j < nv; j++) H[i * S + j] = d.qM[i * S + j];
+  PS_SPEC_UNROLL for (int i = 0; i < nv; i++) PS_SPEC_UNROLL for (int j = 0; j < nv; j++) H[i * S + j] = d.qM[i * S + j];
   for (int r = 0; r < nefc; r++) {
     const int st = d.efc_state[r];
     if (st == ST_QUADRATIC) {
       const double D = d.efc_D[r]; const double* J = d.efc_J + r * S;
-      for (int i = 0; i < nv; i++) { if (J[i] == 0) continue; const double s = D * J[i]; for (int j = 0; j <= i; j++) H[i * S + j] += s * J[j]; }
+      PS_SPEC_UNROLL for (int i = 0; i < nv; i++) { if (J[i] == 0) continue; const double s = D * J[i]; PS_SPEC_UNROLL for (int j = 0; j <= i; j++) H[i * S + j] += s * J[j]; }
     } else if (T::ELLIPTIC && st == ST_CONE && d.efc_type[r] == EFC_CONTACT_ELLIPTIC) {
       // cone block J_c' (Hc J_c): T = Hc J_c first, then the symmetric update, one add per cone row
       const int ci = d.efc_id[r]; const int dim = d.contact[ci].dim; const double* CH = d.coneH + 36 * ci;
       double Tm[6 * S];
-      for (int a = 0; a < dim; a++) for (int j = 0; j < nv; j++) {
+      for (int a = 0; a < dim; a++) PS_SPEC_UNROLL for (int j = 0; j < nv; j++) {
         double t = 0; for (int b = 0; b < dim; b++) t += CH[a * dim + b] * d.efc_J[(r + b) * S + j];
         Tm[a * S + j] = t;
       }
-      for (int i = 0; i < nv; i++) for (int j = 0; j <= i; j++)
+      PS_SPEC_UNROLL for (int i = 0; i < nv; i++) PS_SPEC_UNROLL for (int j = 0; j <= i; j++)
         for (int a = 0; a < dim; a++) H[i * S + j] += d.efc_J[(r + a) * S + i] * Tm[a * S + j];
       r += dim - 1;
     }
   }
-  for (int i = 0; i < nv; i++)
-    for (int j = 0; j <= i; j++) {
+  PS_SPEC_UNROLL for (int i = 0; i < nv; i++)
+    PS_SPEC_UNROLL for (int j = 0; j <= i; j++) {
       double s = H[i * S + j];
-      for (int k = 0; k < j; k++) s -= H[i * S + k] * H[j * S + k];
+      PS_SPEC_UNROLL for (int k = 0; k < j; k++) s -= H[i * S + k] * H[j * S + k];
       if (i == j) H[i * S + i] = sqrt(fmax(s, kMinVal)); else H[i * S + j] = s / H[j * S + j];
     }
   double* x = d.sv_search;
-  for (int i = 0; i < nv; i++) { double s = d.sv_grad[i]; for (int k = 0; k < i; k++) s -= H[i * S + k] * x[k]; x[i] = s / H[i * S + i]; }
-  for (int i = nv - 1; i >= 0; i--) { double s = x[i]; for (int k = nv - 1; k > i; k--) s -= H[k * S + i] * x[k]; x[i] = s / H[i * S + i]; }
-  for (int i = 0; i < nv; i++) x[i] = -x[i];
+  PS_SPEC_UNROLL for (int i = 0; i < nv; i++) { double s = d.sv_grad[i]; PS_SPEC_UNROLL for (int k = 0; k < i; k++) s -= H[i * S + k] * x[k]; x[i] = s / H[i * S + i]; }
+  PS_SPEC_UNROLL for (int i = nv - 1; i >= 0; i--) { double s = x[i]; PS_SPEC_UNROLL for (int k = nv - 1; k > i; k--) s -= H[k * S + i] * x[k]; x[i] = s / H[i * S + i]; }
+  PS_SPEC_UNROLL for (int i = 0; i < nv; i++) x[i] = -x[i];
 }
 
 // value, slope and curvature of the total cost along the search direction at step alpha
@@ -561,7 +561,7 @@ PS_NT double line_search(const DevModel<T>& m, RolloutData<T>& d, const SolverSc
   mul_M(m, d, d.sv_Mv, d.sv_search);
   for (int r = 0; r < nefc; r++) d.sv_Jv[r] = vdot(d.efc_J + r * S, d.sv_search, nv);
   double qg[3] = {c.gauss, 0, 0};
-  for (int i = 0; i < nv; i++) { qg[1] += d.sv_search[i] * (d.sv_Ma[i] - d.qfrc_smooth[i]); qg[2] += 0.5 * d.sv_search[i] * d.sv_Mv[i]; }
+  PS_SPEC_UNROLL for (int i = 0; i < nv; i++) { qg[1] += d.sv_search[i] * (d.sv_Ma[i] - d.qfrc_smooth[i]); qg[2] += 0.5 * d.sv_search[i] * d.sv_Mv[i]; }
   double c0, d0, h0; line_eval(m, d, qg, 0, &c0, &d0, &h0);
   if (!(h0 > 0) || d0 >= 0) return 0;
   double lo = 0, hi = -1;
@@ -584,7 +584,7 @@ PS_NT void constraint_stage(const DevModel<T>& m, RolloutData<T>& d) {
   constexpr int S = T::NV; const int nv = nv_of(m), nefc = d.nefc;
   d.solver_iter = 0;
   if (!nefc) {
-    for (int i = 0; i < nv; i++) { d.qacc[i] = d.qacc_smooth[i]; d.qacc_warmstart[i] = d.qacc_smooth[i]; d.qfrc_constraint[i] = 0; }
+    PS_SPEC_UNROLL for (int i = 0; i < nv; i++) { d.qacc[i] = d.qacc_smooth[i]; d.qacc_warmstart[i] = d.qacc_smooth[i]; d.qfrc_constraint[i] = 0; }
     return;
   }
   SolverScalars c; c.cost = 0; c.prev_cost = 0; c.gauss = 0;
@@ -595,7 +595,7 @@ PS_NT void constraint_stage(const DevModel<T>& m, RolloutData<T>& d) {
     mul_M(m, d, d.sv_Ma, d.qacc);
     for (int r = 0; r < nefc; r++) d.sv_Jaref[r] = vdot(d.efc_J + r * S, d.qacc, nv) - d.efc_aref[r];
     double cw = update_rows(m, d, d.sv_Jaref, false);
-    for (int i = 0; i < nv; i++) cw += 0.5 * (d.sv_Ma[i] - d.qfrc_smooth[i]) * (d.qacc[i] - d.qacc_smooth[i]);
+    PS_SPEC_UNROLL for (int i = 0; i < nv; i++) cw += 0.5 * (d.sv_Ma[i] - d.qfrc_smooth[i]) * (d.qacc[i] - d.qacc_smooth[i]);
     for (int r = 0; r < nefc; r++) d.sv_Jv[r] = vdot(d.efc_J + r * S, d.qacc_smooth, nv) - d.efc_aref[r];
     const double cs = update_rows(m, d, d.sv_Jv, false);
     if (cw > cs) vcopy(d.qacc, d.qacc_smooth, nv);
@@ -609,7 +609,7 @@ PS_NT void constraint_stage(const DevModel<T>& m, RolloutData<T>& d) {
   while (iter < m.iterations) {
     const double alpha = line_search(m, d, c);
     if (alpha == 0) break;
-    for (int i = 0; i < nv; i++) { d.qacc[i] += alpha * d.sv_search[i]; d.sv_Ma[i] += alpha * d.sv_Mv[i]; }
+    PS_SPEC_UNROLL for (int i = 0; i < nv; i++) { d.qacc[i] += alpha * d.sv_search[i]; d.sv_Ma[i] += alpha * d.sv_Mv[i]; }
     for (int r = 0; r < nefc; r++) d.sv_Jaref[r] += alpha * d.sv_Jv[r];
     update_cost(m, d, c, coneH);
     newton_direction(m, d);

@@ -61,10 +61,13 @@ PS_NT double norm_value(const double* x, const double* params, int n, int type) 
   return y;
 }
 
-PS_NT double cost_value(const DevTask& t, const double* residual) {
+template <class TK>
+PS_NT double cost_value(const TK& t, const double* residual) {
   double cost = 0; int fs = 0, ps_ = 0;
+  PS_SPEC_UNROLL
   for (int k = 0; k < t.num_term; k++) {
     double prm[2] = {0, 0};
+    PS_SPEC_UNROLL
     for (int j = 0; j < t.num_norm_parameter[k]; j++) prm[j] = t.norm_parameter[ps_ + j];
     cost += t.weight[k] * norm_value(residual + fs, prm, t.dim_norm_residual[k], t.norm[k]);
     fs += t.dim_norm_residual[k]; ps_ += t.num_norm_parameter[k];
@@ -77,8 +80,8 @@ PS_NT double cost_value(const DevTask& t, const double* residual) {
 enum { TASK_PARTICLE = 0, TASK_PARTICLE_FIXED, TASK_PARTICLE_TEST, TASK_CARTPOLE, TASK_ACROBOT, TASK_SWIMMER,
        TASK_WALKER, TASK_QUADRUPED };
 
-template <class T, class D>
-PS_NT void task_residual(const DevModel<T>& m, const D& d, const DevTask& t, double* r) {
+template <class T, class D, class TK>
+PS_NT void task_residual(const DevModel<T>& m, const D& d, const TK& t, double* r) {
   double s0[3], s1[3];
   switch (t.task_id) {
     case TASK_PARTICLE: case TASK_PARTICLE_FIXED: {

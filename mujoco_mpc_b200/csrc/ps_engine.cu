@@ -26,8 +26,14 @@ static int fail(const std::string& s) { g_error = s; return -1; }
 // Engine families, tried in order.  A family with two kernels shares one Constants layout: `small`
 // (warp-per-rollout, shared-memory working set) serves batches up to `crossover` rollouts -- the
 // planning-latency regime -- and `large` (thread-per-rollout over the same phases) the big batches.
-struct Family { const Variant* small; const Variant* large; int crossover; };
+struct Family { const Variant* small; const Variant* large; int crossover; bool large_required; };
 static const Family kFamilies[] = {
+    // model-specialised lean kernels of the registered tiny tasks: taken only when every integer of the model matches
+    // the compiled-in description (else the next family); the generic lean kernel stays beside them for cost
+    // specifications the specialisation was not compiled for and for the dense flavour
+#define PS_SPEC_FAMILY(N) {variant_tiny(), variant_spec_##N(), 0, true},
+    PS_SPEC_LIST(PS_SPEC_FAMILY)
+#undef PS_SPEC_FAMILY
     {variant_tiny_coop(), variant_tiny(), 0},                 // nv ~ 2: the lean thread-per-rollout kernel wins at every batch size (1.4 vs 2.3 ms at N <= 1024);
                                                               // the warp kernel serves small models that need a feature the lean kernel compiles out
     {variant_tiny(), nullptr, 0},
@@ -53,6 +59,7 @@ struct PsEngine_ {
   int nq = 0, nv = 0, nu = 0, na = 0, nmocap = 0, nsensor = 0, ns = 0;
   std::vector<int> sensor_type; bool ray_ok = false; int* d_counter = nullptr;
   const Variant* var_large = nullptr; const Variant* last = nullptr; int crossover = 0; void* last_dconst = nullptr;
+  bool large_ok = true;      // the large-batch kernel accepts the current cost specification (model-specialised kernels)
   int engine_override = 0;   // PS_ENGINE: 0 auto, 1 warp, 2 thread (compressed phases), 3 dense thread-per-rollout
   std::vector<double> ctrlrange;
   DevTask task{}; bool have_task = false, have_model = false;
@@ -186,8 +193,15 @@ int ps_set_model(PsEngine* e, const PsModel* m) {
   PairList pl = static_pairs(m);
   std::string why, all;
   const Variant* chosen = nullptr; void* host = nullptr; const Family* fam = nullptr;
+  static const bool no_spec = std::getenv("PS_NO_SPEC") != nullptr;      // diagnostics: A/B against the generic lean kernel
   for (const Family& f : kFamilies) {
     const Variant& v = *f.small;
+    if (f.large_required) {
+      if (no_spec || e->engine_override == 1) continue;
+      std::vector<char> probe(f.large->const_bytes + 128);
+      void* pa = (void*)(((uintptr_t)probe.data() + 127) & ~(uintptr_t)127);
+      if (f.large->fill(m, pl, pa, &why) != 0) { all += std::string(f.large->name) + ": " + why + "; "; continue; }
+    }
     if (v.coop && (e->engine_override == 3 || !coop_supported(m, &why))) { all += std::string(v.name) + ": " + (e->engine_override == 3 ? "disabled" : why) + "; "; continue; }
     void* h = nullptr; CU(cudaMallocHost(&h, v.const_bytes)); std::memset(h, 0, v.const_bytes);
     if (v.fill(m, pl, h, &why) == 0) { chosen = &v; host = h; fam = &f; break; }
@@ -225,7 +239,7 @@ int ps_set_model(PsEngine* e, const PsModel* m) {
   chosen->plan(e->h_const, st.data(), e->ns, mocap.data(), m->nmocap, 0.0, nullptr, 0, 0, 0);
   if (e->var_large) e->var_large->plan(e->h_const2, st.data(), e->ns, mocap.data(), m->nmocap, 0.0, nullptr, 0, 0, 0);
   if (const char* dbg = std::getenv("PS_COOP_SERIAL")) chosen->debug(e->h_const, std::atoi(dbg));
-  e->have_model = true; e->have_task = false; e->wb_valid = false;
+  e->have_model = true; e->have_task = false; e->wb_valid = false; e->large_ok = true;
   return 0;
 }
 
@@ -253,6 +267,7 @@ int ps_set_task(PsEngine* e, const PsTask* t) {
   }
   wait_upload(e); e->const_dirty = e->const2_dirty = true;
   e->task = d; e->have_task = true;
+  e->large_ok = !(e->var_large && e->var_large->task_ok) || e->var_large->task_ok(d, need_sub) != 0;
   e->var->task(e->h_const, d, need_sub);
   if (e->var_large) e->var_large->task(e->h_const2, d, need_sub);
   return 0;
@@ -378,7 +393,7 @@ static int run_iteration(PsEngine* e, int N, int H, double sigma0, double sigma1
   if (alloc_samples(e, N)) return -1;
   e->N = N; e->H = H; e->offset = sample_offset; e->sigma0 = sigma0; e->sigma1 = sigma1;
   const Variant* run = e->var;
-  if (e->var_large && (e->engine_override == 2 || (e->engine_override == 0 && N > e->crossover))) run = e->var_large;
+  if (e->var_large && e->large_ok && (e->engine_override == 2 || (e->engine_override == 0 && N > e->crossover))) run = e->var_large;
   const bool large = run == e->var_large;
   char* hc = (char*)(large ? e->h_const2 : e->h_const); char* dc = (char*)(large ? e->d_const2 : e->d_const);
   wait_upload(e);

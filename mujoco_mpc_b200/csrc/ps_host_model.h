@@ -8,7 +8,11 @@
 #include <string>
 #include <vector>
 #include "../../include/ps_engine.h"
+#include <cstdlib>
 #include "ps_rollout.cuh"
+#ifndef PS_NO_SPEC_HEADER      // tools/spec_dump.cc (the generator of that header) compiles without it
+#include "ps_spec_generated.h"
+#endif
 
 namespace ps {
 
@@ -207,6 +211,82 @@ inline int fill_model(const PsModel* s, const PairList& pl, void* out, std::stri
   m.ntrack_model = m.ntrack;
   return 0;
 }
+
+#ifndef PS_NO_SPEC_HEADER
+// ---------------------------------------------------------------- model-specialised instantiations (SpecTraits, ps_types.cuh)
+// The model is flattened by the generic fill_model into a scratch DevModel of the same capacities; every integer of it
+// must equal the Spec's compile-time value (else this instantiation is not for this model and the caller falls through
+// to the generic lean kernel), the doubles are copied.
+template <class T>
+inline int fill_model_spec(const PsModel* s, const PairList& pl, void* out, std::string* why) {
+  using B = typename T::Base; using Spec = typename T::Topo;
+  if (s->nq != Spec::NQ || s->nv != Spec::NV || s->nu != Spec::NU || s->na != 0 || s->nbody != Spec::NBODY || s->njnt != Spec::NJNT ||
+      s->ngeom != Spec::NGEOM || s->nsite != Spec::NSITE || s->nmocap != Spec::NMOCAP || s->nsensor != Spec::NSENSOR) {
+    *why = std::string("sizes differ from the ") + Spec::kName + " specialisation"; return -1;
+  }
+  void* raw = std::aligned_alloc(128, (sizeof(Constants<B>) + 127) / 128 * 128);
+  if (!raw) { *why = "out of memory"; return -1; }
+  struct Free { void* p; ~Free() { std::free(p); } } guard{raw};
+  if (fill_model<B>(s, pl, raw, why)) return -1;
+  const DevModel<B>& g = reinterpret_cast<Constants<B>*>(raw)->m;
+  DevModel<T>& m = reinterpret_cast<Constants<T>*>(out)->m;
+  const typename Spec::ModelInts si{};
+  const char* bad = nullptr;
+#define CK(f) if (!bad && g.f != si.f) bad = #f;
+#define CKT(f, n) for (int i_ = 0; i_ < (n) && !bad; i_++) if (g.f[i_] != si.f[i_]) bad = #f;
+  CK(integrator) CK(cone) CK(iterations) CK(ls_iterations) CK(disableflags) CK(npair) CK(any_damping) CK(nray) CK(ray_complete)
+  CKT(ray_geom, g.nray)
+  CKT(body_parentid, g.nbody) CKT(body_rootid, g.nbody) CKT(body_jntnum, g.nbody) CKT(body_jntadr, g.nbody) CKT(body_dofnum, g.nbody)
+  CKT(body_dofadr, g.nbody) CKT(body_mocapid, g.nbody) CKT(body_weldid, g.nbody)
+  CKT(jnt_type, g.njnt) CKT(jnt_qposadr, g.njnt) CKT(jnt_dofadr, g.njnt) CKT(jnt_bodyid, g.njnt) CKT(jnt_limited, g.njnt)
+  CKT(dof_bodyid, g.nv) CKT(dof_jntid, g.nv) CKT(dof_parentid, g.nv)
+  CKT(geom_type, g.ngeom) CKT(geom_condim, g.ngeom) CKT(geom_bodyid, g.ngeom) CKT(geom_priority, g.ngeom) CKT(geom_group, g.ngeom) CKT(geom_used, g.ngeom)
+  CKT(site_bodyid, g.nsite)
+  CKT(act_dyntype, g.nu) CKT(act_gaintype, g.nu) CKT(act_biastype, g.nu) CKT(act_jntid, g.nu) CKT(act_actadr, g.nu) CKT(act_ctrllimited, g.nu)
+  CKT(act_forcelimited, g.nu) CKT(act_actlimited, g.nu)
+  CKT(sensor_type, g.nsensor) CKT(sensor_objtype, g.nsensor) CKT(sensor_objid, g.nsensor)
+#undef CK
+#undef CKT
+  if (bad) { *why = std::string(bad) + " differs from the " + Spec::kName + " specialisation"; return -1; }
+  std::memset(static_cast<void*>(&m), 0, sizeof(m));
+  m.timestep = g.timestep; m.impratio = g.impratio; m.tolerance = g.tolerance; m.ls_tolerance = g.ls_tolerance;
+  m.density = g.density; m.viscosity = g.viscosity; m.meaninertia = g.meaninertia;
+#define CPD(f) static_assert(sizeof(m.f) == sizeof(g.f), #f); std::memcpy(m.f, g.f, sizeof(m.f));
+  CPD(gravity) CPD(wind) CPD(qpos0) CPD(qpos_spring)
+  CPD(body_pos) CPD(body_quat) CPD(body_ipos) CPD(body_iquat) CPD(body_mass) CPD(body_subtreemass) CPD(body_inertia) CPD(body_invweight0)
+  CPD(jnt_pos) CPD(jnt_axis) CPD(jnt_stiffness) CPD(jnt_range) CPD(jnt_margin) CPD(jnt_solref) CPD(jnt_solimp)
+  CPD(dof_armature) CPD(dof_damping) CPD(dof_frictionloss) CPD(dof_solref) CPD(dof_solimp) CPD(dof_invweight0)
+  CPD(geom_size) CPD(geom_pos) CPD(geom_quat) CPD(geom_friction) CPD(geom_solmix) CPD(geom_solref) CPD(geom_solimp) CPD(geom_margin)
+  CPD(geom_gap) CPD(geom_rbound) CPD(site_pos) CPD(site_quat)
+  CPD(act_dynprm) CPD(act_gainprm) CPD(act_biasprm) CPD(act_ctrlrange) CPD(act_forcerange) CPD(act_actrange) CPD(act_gear)
+#undef CPD
+  return 0;
+}
+
+template <class T>
+inline void set_options_spec(void* c, double timestep, int integrator) {
+  (void)integrator;      // Euler only (Variant::euler_only): ps_set_options refuses anything else before it gets here
+  reinterpret_cast<Constants<T>*>(c)->m.timestep = timestep;
+}
+template <class T> inline void set_debug_spec(void*, int) {}
+template <class T>
+inline void set_task_spec(void* c, const DevTask& t, int) { reinterpret_cast<Constants<T>*>(c)->t = t; }
+
+// does the cost specification carry the integers this instantiation was compiled for?
+template <class T>
+inline int task_matches_spec(const DevTask& d, int need_subtreevel) {
+  using Spec = typename T::Topo;
+  const typename Spec::TaskInts ti{};
+  if (d.task_id != ti.task_id || d.num_residual != ti.num_residual || d.num_term != ti.num_term || d.num_trace != ti.num_trace) return 0;
+  if (need_subtreevel != Spec::ModelInts::need_subtreevel) return 0;
+  for (int k = 0; k < d.num_term; k++)
+    if (d.dim_norm_residual[k] != ti.dim_norm_residual[k] || d.num_norm_parameter[k] != ti.num_norm_parameter[k] || d.norm[k] != ti.norm[k]) return 0;
+  for (int k = 0; k < 16; k++) if (d.sensor_id[k] != ti.sensor_id[k]) return 0;
+  for (int k = 0; k < d.num_trace; k++) if (d.trace_sensor[k] != ti.trace_sensor[k]) return 0;
+  return 1;
+}
+
+#endif  // PS_NO_SPEC_HEADER
 
 template <class T>
 inline void set_options(void* c, double timestep, int integrator) {

@@ -44,8 +44,13 @@ __device__ __forceinline__ bool better(double c, long long i, double bc, long lo
 }
 
 // ---------------------------------------------------------------- K2
+// model-specialised instantiations keep their working set in registers: cap the count so that PS_SPEC_MINBLOCKS blocks stay
+// resident per SM (the generic instantiations keep the plain bound they were tuned with)
+#ifndef PS_SPEC_MINBLOCKS
+#define PS_SPEC_MINBLOCKS 2
+#endif
 template <class T, int BLOCK, bool WB>
-__global__ void __launch_bounds__(BLOCK)
+__global__ void __launch_bounds__(BLOCK, (T::SPEC ? PS_SPEC_MINBLOCKS : 1))
 rollout_kernel(const Constants<T>* __restrict__ gconst, const double* __restrict__ knots, int stride, int first, int n,
                long long sample_offset, double* __restrict__ returns, unsigned char* __restrict__ failure,
                MinLoc* __restrict__ block_min, Writeback wb) {
@@ -73,7 +78,10 @@ rollout_kernel(const Constants<T>* __restrict__ gconst, const double* __restrict
 
   if (active) {
     int flags = 0;
-    total = rollout_sample<T, WB>(sc.m, sc.t, sc.p, knots, stride, i, wb, &flags);
+    if constexpr (T::SPEC) {      // model-specialised: the cost specification's integers are compile-time too
+      const SpecTaskView<typename T::Topo> tv(sc.t);
+      total = rollout_sample<T, WB, false, SpecTaskView<typename T::Topo>>(sc.m, tv, sc.p, knots, stride, i, wb, &flags);
+    } else total = rollout_sample<T, WB>(sc.m, sc.t, sc.p, knots, stride, i, wb, &flags);
     failed = flags & 1;
     returns[i] = total;
     failure[i] = (unsigned char)flags;

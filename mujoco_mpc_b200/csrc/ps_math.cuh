@@ -7,9 +7,9 @@
 
 namespace ps {
 
-PS_HD void vcopy(double* r, const double* a, int n) { for (int i = 0; i < n; i++) r[i] = a[i]; }
-PS_HD void vzero(double* r, int n) { for (int i = 0; i < n; i++) r[i] = 0.0; }
-PS_HD double vdot(const double* a, const double* b, int n) { double s = 0; for (int i = 0; i < n; i++) s += a[i] * b[i]; return s; }
+PS_HD void vcopy(double* r, const double* a, int n) { PS_SPEC_UNROLL for (int i = 0; i < n; i++) r[i] = a[i]; }
+PS_HD void vzero(double* r, int n) { PS_SPEC_UNROLL for (int i = 0; i < n; i++) r[i] = 0.0; }
+PS_HD double vdot(const double* a, const double* b, int n) { double s = 0; PS_SPEC_UNROLL for (int i = 0; i < n; i++) s += a[i] * b[i]; return s; }
 PS_HD double dot3(const double* a, const double* b) { return a[0] * b[0] + a[1] * b[1] + a[2] * b[2]; }
 PS_HD void cross3(double* r, const double* a, const double* b) {
   double x = a[1] * b[2] - a[2] * b[1], y = a[2] * b[0] - a[0] * b[2], z = a[0] * b[1] - a[1] * b[0];

@@ -46,23 +46,28 @@ template <class T> struct Perturbation<T, true> {
 
 // knots: SoA [P*nu][stride]; i = this rollout's column.  flags: bit0 failure, bit1 capacity overflow
 // XF: apply Cartesian perturbation forces (own kernel instantiation: robust_rollout_kernel)
-template <class T, bool WB, bool XF = false>
-PS_FN double rollout_sample(const DevModel<T>& m, const DevTask& task, const DevPlan<T>& plan, const double* knots,
+template <class T, bool WB, bool XF = false, class TK = DevTask>
+PS_FN double rollout_sample(const DevModel<T>& m, const TK& task, const DevPlan<T>& plan, const double* knots,
                             int stride, int i, const Writeback& wb, int* flags, const XfrcNoise* xf = nullptr) {
-  RolloutData<T> d;
+  typename RolloutData<T>::Rows rows; RolloutData<T> d; d.bind(rows);
   const int nq = nq_of(m), nv = nv_of(m), na = m.na, nu = m.nu, ns = nq + nv + na, nr = task.num_residual;
   const int H = plan.horizon, P = plan.num_spline_points, ntr = 3 * task.num_trace;
+  PS_SPEC_UNROLL
   for (int k = 0; k < nq; k++) d.qpos[k] = plan.state[k];
+  PS_SPEC_UNROLL
   for (int k = 0; k < nv; k++) { d.qvel[k] = plan.state[nq + k]; d.qacc_warmstart[k] = 0; d.qacc[k] = 0; }
+  PS_SPEC_UNROLL
   for (int k = 0; k < na; k++) d.act[k] = plan.state[nq + nv + k];
+  PS_SPEC_UNROLL
   for (int k = 0; k < nu; k++) d.ctrl[k] = 0;
+  PS_SPEC_UNROLL
   for (int k = 0; k < m.nmocap; k++) { vcopy(d.mocap_pos + 3 * k, plan.mocap + 7 * k, 3); vcopy(d.mocap_quat + 4 * k, plan.mocap + 7 * k + 3, 4); }
   d.time = plan.time; d.warning = 0; d.ncon = 0; d.nefc = 0; d.solver_iter = 0;
   const double* kcol = knots + i;
   auto kn = [&](int p, int a) { return kcol[(size_t)(p * nu + a) * stride]; };
   double residual[kMaxResidual];
   double sum = 0; bool failed = false;
-  if (WB) { for (int k = 0; k < ns; k++) wb.states[(size_t)k * stride + i] = plan.state[k]; wb.times[i] = d.time; }
+  if (WB) { PS_SPEC_UNROLL for (int k = 0; k < ns; k++) wb.states[(size_t)k * stride + i] = plan.state[k]; wb.times[i] = d.time; }
   Perturbation<T, XF> pert(m, xf);
 
 #if PS_ROLLOUT_SINGLE_SITE
@@ -74,21 +79,24 @@ PS_FN double rollout_sample(const DevModel<T>& m, const DevTask& task, const Dev
     const bool terminal = t == H - 1;
     if (!terminal) {
       spline_sample(plan.spline_times, P, nu, plan.interpolation, d.time, kn, d.ctrl);
+      PS_SPEC_UNROLL
       for (int a = 0; a < nu; a++) d.ctrl[a] = clampd(d.ctrl[a], m.act_ctrlrange[2 * a], m.act_ctrlrange[2 * a + 1]);
       pert.advance(m, t, stride, i);
     }
     // terminal: ctrl is NOT rewritten before the final forward pass (trajectory.cc:190-198)
-    if (WB && (!terminal || H > 1)) for (int a = 0; a < nu; a++) wb.actions[((size_t)t * nu + a) * stride + i] = d.ctrl[a];
+    if (WB && (!terminal || H > 1)) PS_SPEC_UNROLL for (int a = 0; a < nu; a++) wb.actions[((size_t)t * nu + a) * stride + i] = d.ctrl[a];
     if (!terminal && state_is_bad(m, d)) { failed = true; break; }
     pert.forward(m, d);
     task_residual(m, d, task, residual);
     const double c = cost_value(task, residual);
     if (WB) {
+      PS_SPEC_UNROLL
       for (int k = 0; k < nr; k++) wb.residual[((size_t)t * nr + k) * stride + i] = residual[k];
       wb.costs[(size_t)t * stride + i] = c;
+      PS_SPEC_UNROLL
       for (int k = 0; k < task.num_trace; k++) {
         double tr[3]; read_sensor(m, d, task.trace_sensor[k], tr);
-        for (int x = 0; x < 3; x++) wb.trace[((size_t)t * ntr + 3 * k + x) * stride + i] = tr[x];
+        PS_SPEC_UNROLL for (int x = 0; x < 3; x++) wb.trace[((size_t)t * ntr + 3 * k + x) * stride + i] = tr[x];
       }
     }
     if (terminal) { sum += c; break; }
@@ -97,8 +105,11 @@ PS_FN double rollout_sample(const DevModel<T>& m, const DevTask& task, const Dev
     integrate(m, d);
     if (WB) {
       double* s = wb.states + ((size_t)(t + 1) * ns) * stride + i;
+      PS_SPEC_UNROLL
       for (int k = 0; k < nq; k++) s[(size_t)k * stride] = d.qpos[k];
+      PS_SPEC_UNROLL
       for (int k = 0; k < nv; k++) s[(size_t)(nq + k) * stride] = d.qvel[k];
+      PS_SPEC_UNROLL
       for (int k = 0; k < na; k++) s[(size_t)(nq + nv + k) * stride] = d.act[k];
       wb.times[(size_t)(t + 1) * stride + i] = d.time;
     }
@@ -107,19 +118,22 @@ PS_FN double rollout_sample(const DevModel<T>& m, const DevTask& task, const Dev
 #else
   for (int t = 0; t < H - 1; t++) {
     spline_sample(plan.spline_times, P, nu, plan.interpolation, d.time, kn, d.ctrl);
+    PS_SPEC_UNROLL
     for (int a = 0; a < nu; a++) d.ctrl[a] = clampd(d.ctrl[a], m.act_ctrlrange[2 * a], m.act_ctrlrange[2 * a + 1]);
-    if (WB) for (int a = 0; a < nu; a++) wb.actions[((size_t)t * nu + a) * stride + i] = d.ctrl[a];
+    if (WB) PS_SPEC_UNROLL for (int a = 0; a < nu; a++) wb.actions[((size_t)t * nu + a) * stride + i] = d.ctrl[a];
     pert.advance(m, t, stride, i);
     if (state_is_bad(m, d)) { failed = true; break; }
     pert.forward(m, d);
     task_residual(m, d, task, residual);
     const double c = cost_value(task, residual);
     if (WB) {
+      PS_SPEC_UNROLL
       for (int k = 0; k < nr; k++) wb.residual[((size_t)t * nr + k) * stride + i] = residual[k];
       wb.costs[(size_t)t * stride + i] = c;
+      PS_SPEC_UNROLL
       for (int k = 0; k < task.num_trace; k++) {
         double tr[3]; read_sensor(m, d, task.trace_sensor[k], tr);
-        for (int x = 0; x < 3; x++) wb.trace[((size_t)t * ntr + 3 * k + x) * stride + i] = tr[x];
+        PS_SPEC_UNROLL for (int x = 0; x < 3; x++) wb.trace[((size_t)t * ntr + 3 * k + x) * stride + i] = tr[x];
       }
     }
     if (acc_is_bad(m, d) || (d.warning & (WARN_BADQPOS | WARN_BADQVEL | WARN_BADQACC | WARN_BADCTRL))) { failed = true; break; }
@@ -127,8 +141,11 @@ PS_FN double rollout_sample(const DevModel<T>& m, const DevTask& task, const Dev
     integrate(m, d);
     if (WB) {
       double* s = wb.states + ((size_t)(t + 1) * ns) * stride + i;
+      PS_SPEC_UNROLL
       for (int k = 0; k < nq; k++) s[(size_t)k * stride] = d.qpos[k];
+      PS_SPEC_UNROLL
       for (int k = 0; k < nv; k++) s[(size_t)(nq + k) * stride] = d.qvel[k];
+      PS_SPEC_UNROLL
       for (int k = 0; k < na; k++) s[(size_t)(nq + nv + k) * stride] = d.act[k];
       wb.times[(size_t)(t + 1) * stride + i] = d.time;
     }
@@ -136,16 +153,18 @@ PS_FN double rollout_sample(const DevModel<T>& m, const DevTask& task, const Dev
   double total;
   if (!failed) {
     // terminal: ctrl is NOT rewritten before the final forward pass (trajectory.cc:190-198)
-    if (WB && H > 1) for (int a = 0; a < nu; a++) wb.actions[((size_t)(H - 1) * nu + a) * stride + i] = d.ctrl[a];
+    if (WB && H > 1) PS_SPEC_UNROLL for (int a = 0; a < nu; a++) wb.actions[((size_t)(H - 1) * nu + a) * stride + i] = d.ctrl[a];
     pert.forward(m, d);
     task_residual(m, d, task, residual);
     const double c = cost_value(task, residual);
     if (WB) {
+      PS_SPEC_UNROLL
       for (int k = 0; k < nr; k++) wb.residual[((size_t)(H - 1) * nr + k) * stride + i] = residual[k];
       wb.costs[(size_t)(H - 1) * stride + i] = c;
+      PS_SPEC_UNROLL
       for (int k = 0; k < task.num_trace; k++) {
         double tr[3]; read_sensor(m, d, task.trace_sensor[k], tr);
-        for (int x = 0; x < 3; x++) wb.trace[((size_t)(H - 1) * ntr + 3 * k + x) * stride + i] = tr[x];
+        PS_SPEC_UNROLL for (int x = 0; x < 3; x++) wb.trace[((size_t)(H - 1) * ntr + 3 * k + x) * stride + i] = tr[x];
       }
     }
     sum += c;

@@ -17,13 +17,13 @@ PS_NT void kinematics(const DevModel<T>& m, RolloutData<T>& d) {
   vzero(d.xpos, 3); d.xquat[0] = 1; d.xquat[1] = d.xquat[2] = d.xquat[3] = 0;
   vzero(d.xmat, 9); d.xmat[0] = d.xmat[4] = d.xmat[8] = 1;
   vzero(d.xipos, 3); vcopy(d.ximat, d.xmat, 9);
-  if (T::QUAT) for (int j = 0; j < m.njnt; j++) {
+  if (T::QUAT) PS_SPEC_UNROLL for (int j = 0; j < m.njnt; j++) {
     if (m.jnt_type[j] == JNT_FREE) unit4(d.qpos + m.jnt_qposadr[j] + 3);
     else if (m.jnt_type[j] == JNT_BALL) unit4(d.qpos + m.jnt_qposadr[j]);
   }
-  for (int i = 0; i < m.nmocap; i++) unit4(d.mocap_quat + 4 * i);
+  PS_SPEC_UNROLL for (int i = 0; i < m.nmocap; i++) unit4(d.mocap_quat + 4 * i);
 
-  for (int b = 1; b < m.nbody; b++) {
+  PS_SPEC_UNROLL for (int b = 1; b < m.nbody; b++) {
     double pos[3], quat[4];
     const int par = m.body_parentid[b], jn = m.body_jntnum[b], ja = m.body_jntadr[b];
     if (m.body_mocapid[b] >= 0) {
@@ -35,25 +35,25 @@ PS_NT void kinematics(const DevModel<T>& m, RolloutData<T>& d) {
       vcopy(d.xanchor + 3 * ja, pos, 3); vcopy(d.xaxis + 3 * ja, m.jnt_axis + 3 * ja, 3);
     } else {
       double t[3]; mat_vec3(t, d.xmat + 9 * par, m.body_pos + 3 * b);
-      for (int k = 0; k < 3; k++) pos[k] = d.xpos[3 * par + k] + t[k];
+      PS_SPEC_UNROLL for (int k = 0; k < 3; k++) pos[k] = d.xpos[3 * par + k] + t[k];
       quat_mul(quat, d.xquat + 4 * par, m.body_quat + 4 * b);
-      for (int j = ja; j < ja + jn; j++) {
+      PS_SPEC_UNROLL for (int j = ja; j < ja + jn; j++) {
         const int qa = m.jnt_qposadr[j];
         double* anchor = d.xanchor + 3 * j; double* axis = d.xaxis + 3 * j;
         double v[3]; quat_rotate(v, m.jnt_pos + 3 * j, quat);
-        for (int k = 0; k < 3; k++) anchor[k] = v[k] + pos[k];
+        PS_SPEC_UNROLL for (int k = 0; k < 3; k++) anchor[k] = v[k] + pos[k];
         quat_rotate(axis, m.jnt_axis + 3 * j, quat);
         const int jt = m.jnt_type[j];
         if (jt == JNT_SLIDE) {
           const double dq = d.qpos[qa] - m.qpos0[qa];
-          for (int k = 0; k < 3; k++) pos[k] += axis[k] * dq;
+          PS_SPEC_UNROLL for (int k = 0; k < 3; k++) pos[k] += axis[k] * dq;
         } else if (jt == JNT_HINGE || (T::QUAT && jt == JNT_BALL)) {
           double ql[4];
           if (T::QUAT && jt == JNT_BALL) vcopy(ql, d.qpos + qa, 4);
           else axis_angle_quat(ql, m.jnt_axis + 3 * j, d.qpos[qa] - m.qpos0[qa]);
           quat_mul(quat, quat, ql);
           quat_rotate(v, m.jnt_pos + 3 * j, quat);   // keep the anchor fixed under the rotation
-          for (int k = 0; k < 3; k++) pos[k] = anchor[k] - v[k];
+          PS_SPEC_UNROLL for (int k = 0; k < 3; k++) pos[k] = anchor[k] - v[k];
         }
       }
     }
@@ -61,20 +61,20 @@ PS_NT void kinematics(const DevModel<T>& m, RolloutData<T>& d) {
     vcopy(d.xquat + 4 * b, quat, 4); vcopy(d.xpos + 3 * b, pos, 3);
     quat_to_mat(d.xmat + 9 * b, quat);
     double t[3]; mat_vec3(t, d.xmat + 9 * b, m.body_ipos + 3 * b);
-    for (int k = 0; k < 3; k++) d.xipos[3 * b + k] = pos[k] + t[k];
+    PS_SPEC_UNROLL for (int k = 0; k < 3; k++) d.xipos[3 * b + k] = pos[k] + t[k];
     double qi[4]; quat_mul(qi, quat, m.body_iquat + 4 * b); quat_to_mat(d.ximat + 9 * b, qi);
   }
-  for (int g = 0; g < m.ngeom; g++) {
+  PS_SPEC_UNROLL for (int g = 0; g < m.ngeom; g++) {
     if (!m.geom_used[g]) continue;     // geoms that neither collide nor are read by the task
     const int b = m.geom_bodyid[g]; double t[3], q[4];
     mat_vec3(t, d.xmat + 9 * b, m.geom_pos + 3 * g);
-    for (int k = 0; k < 3; k++) d.geom_xpos[3 * g + k] = d.xpos[3 * b + k] + t[k];
+    PS_SPEC_UNROLL for (int k = 0; k < 3; k++) d.geom_xpos[3 * g + k] = d.xpos[3 * b + k] + t[k];
     quat_mul(q, d.xquat + 4 * b, m.geom_quat + 4 * g); quat_to_mat(d.geom_xmat + 9 * g, q);
   }
-  for (int s = 0; s < m.nsite; s++) {
+  PS_SPEC_UNROLL for (int s = 0; s < m.nsite; s++) {
     const int b = m.site_bodyid[s]; double t[3], q[4];
     mat_vec3(t, d.xmat + 9 * b, m.site_pos + 3 * s);
-    for (int k = 0; k < 3; k++) d.site_xpos[3 * s + k] = d.xpos[3 * b + k] + t[k];
+    PS_SPEC_UNROLL for (int k = 0; k < 3; k++) d.site_xpos[3 * s + k] = d.xpos[3 * b + k] + t[k];
     quat_mul(q, d.xquat + 4 * b, m.site_quat + 4 * s); quat_to_mat(d.site_xmat + 9 * s, q);
   }
 }
@@ -89,16 +89,16 @@ template <class T>
 PS_NT void com_position(const DevModel<T>& m, RolloutData<T>& d) {
   const int nb = m.nbody;
   double* sc = d.subtree_com;
-  for (int i = 0; i < nb; i++) for (int k = 0; k < 3; k++) sc[3 * i + k] = m.body_mass[i] * d.xipos[3 * i + k];
-  for (int i = nb - 1; i > 0; i--) { const int p = m.body_parentid[i]; for (int k = 0; k < 3; k++) sc[3 * p + k] += sc[3 * i + k]; }
-  for (int i = 0; i < nb; i++) {
+  PS_SPEC_UNROLL for (int i = 0; i < nb; i++) PS_SPEC_UNROLL for (int k = 0; k < 3; k++) sc[3 * i + k] = m.body_mass[i] * d.xipos[3 * i + k];
+  PS_SPEC_UNROLL for (int i = nb - 1; i > 0; i--) { const int p = m.body_parentid[i]; PS_SPEC_UNROLL for (int k = 0; k < 3; k++) sc[3 * p + k] += sc[3 * i + k]; }
+  PS_SPEC_UNROLL for (int i = 0; i < nb; i++) {
     if (m.body_subtreemass[i] < kMinVal) vcopy(sc + 3 * i, d.xipos + 3 * i, 3);
-    else for (int k = 0; k < 3; k++) sc[3 * i + k] /= m.body_subtreemass[i];
+    else PS_SPEC_UNROLL for (int k = 0; k < 3; k++) sc[3 * i + k] /= m.body_subtreemass[i];
   }
   vzero(d.cinert, 10);
-  for (int i = 1; i < nb; i++) {
+  PS_SPEC_UNROLL for (int i = 1; i < nb; i++) {
     double off[3]; const double* root = sc + 3 * m.body_rootid[i];
-    for (int k = 0; k < 3; k++) off[k] = d.xipos[3 * i + k] - root[k];
+    PS_SPEC_UNROLL for (int k = 0; k < 3; k++) off[k] = d.xipos[3 * i + k] - root[k];
     const double* R = d.ximat + 9 * i; const double* I = m.body_inertia + 3 * i; const double mass = m.body_mass[i];
     // world-aligned rotational inertia R diag(I) R'
     double w00 = R[0] * I[0] * R[0] + R[1] * I[1] * R[1] + R[2] * I[2] * R[2];
@@ -116,17 +116,17 @@ PS_NT void com_position(const DevModel<T>& m, RolloutData<T>& d) {
     c[5] = w12 - mass * off[1] * off[2];
     c[6] = mass * off[0]; c[7] = mass * off[1]; c[8] = mass * off[2]; c[9] = mass;
   }
-  for (int j = 0; j < m.njnt; j++) {
+  PS_SPEC_UNROLL for (int j = 0; j < m.njnt; j++) {
     const int b = m.jnt_bodyid[j]; int da = m.jnt_dofadr[j];
     double off[3]; const double* root = sc + 3 * m.body_rootid[b];
-    for (int k = 0; k < 3; k++) off[k] = root[k] - d.xanchor[3 * j + k];
+    PS_SPEC_UNROLL for (int k = 0; k < 3; k++) off[k] = root[k] - d.xanchor[3 * j + k];
     const int jt = m.jnt_type[j];
     if (T::QUAT && jt == JNT_FREE) {
-      for (int k = 0; k < 3; k++) { double ax[3] = {0, 0, 0}; ax[k] = 1; dof_motion(d.cdof + 6 * (da + k), ax, nullptr); }
+      PS_SPEC_UNROLL for (int k = 0; k < 3; k++) { double ax[3] = {0, 0, 0}; ax[k] = 1; dof_motion(d.cdof + 6 * (da + k), ax, nullptr); }
       da += 3;
     }
     if (T::QUAT && (jt == JNT_FREE || jt == JNT_BALL)) {
-      for (int k = 0; k < 3; k++) {
+      PS_SPEC_UNROLL for (int k = 0; k < 3; k++) {
         double ax[3] = {d.xmat[9 * b + k], d.xmat[9 * b + 3 + k], d.xmat[9 * b + 6 + k]};
         dof_motion(d.cdof + 6 * (da + k), ax, off);
       }
@@ -140,54 +140,54 @@ PS_NT void com_position(const DevModel<T>& m, RolloutData<T>& d) {
 template <class T>
 PS_NT void factor_tree(const DevModel<T>& m, double* L, double* dinv) {
   constexpr int S = T::NV; const int nv = nv_of(m);
-  for (int k = nv - 1; k >= 0; k--) {
+  PS_SPEC_UNROLL for (int k = nv - 1; k >= 0; k--) {
     if (L[k * S + k] < kMinVal) L[k * S + k] = kMinVal;
     const double dk = L[k * S + k];
-    for (int i = m.dof_parentid[k]; i >= 0; i = m.dof_parentid[i]) {
+    PS_CHAIN(i, m.dof_parentid[k], k, m.dof_parentid) {
       const double tmp = L[k * S + i] / dk;
-      for (int j = i; j >= 0; j = m.dof_parentid[j]) L[i * S + j] -= L[k * S + j] * tmp;
+      PS_CHAIN(j, i, i + 1, m.dof_parentid) L[i * S + j] -= L[k * S + j] * tmp;
       L[k * S + i] = tmp;
     }
   }
-  for (int i = 0; i < nv; i++) dinv[i] = 1.0 / L[i * S + i];
+  PS_SPEC_UNROLL for (int i = 0; i < nv; i++) dinv[i] = 1.0 / L[i * S + i];
 }
 
 template <class T>
 PS_NT void solve_tree(const DevModel<T>& m, double* x, const double* L, const double* dinv) {
   constexpr int S = T::NV; const int nv = nv_of(m);
-  for (int i = nv - 1; i >= 0; i--) {
+  PS_SPEC_UNROLL for (int i = nv - 1; i >= 0; i--) {
     const double xi = x[i];
-    if (xi != 0) for (int j = m.dof_parentid[i]; j >= 0; j = m.dof_parentid[j]) x[j] -= L[i * S + j] * xi;
+    if (xi != 0) PS_CHAIN(j, m.dof_parentid[i], i, m.dof_parentid) x[j] -= L[i * S + j] * xi;
   }
-  for (int i = 0; i < nv; i++) x[i] *= dinv[i];
-  for (int i = 0; i < nv; i++)
-    for (int j = m.dof_parentid[i]; j >= 0; j = m.dof_parentid[j]) x[i] -= L[i * S + j] * x[j];
+  PS_SPEC_UNROLL for (int i = 0; i < nv; i++) x[i] *= dinv[i];
+  PS_SPEC_UNROLL for (int i = 0; i < nv; i++)
+    PS_CHAIN(j, m.dof_parentid[i], i, m.dof_parentid) x[i] -= L[i * S + j] * x[j];
 }
 
 template <class T>
 PS_NT void mass_matrix(const DevModel<T>& m, RolloutData<T>& d) {
   constexpr int S = T::NV; const int nb = m.nbody, nv = nv_of(m);
   vcopy(d.crb, d.cinert, 10 * nb);
-  for (int i = nb - 1; i > 0; i--) {
+  PS_SPEC_UNROLL for (int i = nb - 1; i > 0; i--) {
     const int p = m.body_parentid[i];
-    if (p > 0) for (int k = 0; k < 10; k++) d.crb[10 * p + k] += d.crb[10 * i + k];
+    if (p > 0) PS_SPEC_UNROLL for (int k = 0; k < 10; k++) d.crb[10 * p + k] += d.crb[10 * i + k];
   }
-  for (int i = 0; i < nv; i++) for (int j = 0; j < nv; j++) d.qM[i * S + j] = 0;
-  for (int i = 0; i < nv; i++) {
+  PS_SPEC_UNROLL for (int i = 0; i < nv; i++) PS_SPEC_UNROLL for (int j = 0; j < nv; j++) d.qM[i * S + j] = 0;
+  PS_SPEC_UNROLL for (int i = 0; i < nv; i++) {
     double f[6]; inert_vec(f, d.crb + 10 * m.dof_bodyid[i], d.cdof + 6 * i);
     d.qM[i * S + i] = m.dof_armature[i];
-    for (int j = i; j >= 0; j = m.dof_parentid[j]) {
+    PS_CHAIN(j, i, i + 1, m.dof_parentid) {
       const double v = vdot(d.cdof + 6 * j, f, 6);
       if (j == i) d.qM[i * S + i] += v; else { d.qM[i * S + j] = v; d.qM[j * S + i] = v; }
     }
   }
-  for (int i = 0; i < nv; i++) for (int j = 0; j < nv; j++) d.qLD[i * S + j] = d.qM[i * S + j];
+  PS_SPEC_UNROLL for (int i = 0; i < nv; i++) PS_SPEC_UNROLL for (int j = 0; j < nv; j++) d.qLD[i * S + j] = d.qM[i * S + j];
   factor_tree(m, d.qLD, d.qLDiagInv);
 }
 
 template <class T>
 PS_HD void mul_M(const DevModel<T>& m, const RolloutData<T>& d, double* res, const double* vec) {
-  for (int i = 0; i < nv_of(m); i++) res[i] = vdot(d.qM + i * T::NV, vec, nv_of(m));
+  PS_SPEC_UNROLL for (int i = 0; i < nv_of(m); i++) res[i] = vdot(d.qM + i * T::NV, vec, nv_of(m));
 }
 
 // translational / rotational Jacobian rows of a world point attached to `body`;
@@ -201,11 +201,11 @@ PS_NT void point_jacobian(const DevModel<T>& m, const RolloutData<T>& d, double*
   body = m.body_weldid[body];
   if (body <= 0) return;
   double off[3]; const double* root = d.subtree_com + 3 * m.body_rootid[body];
-  for (int k = 0; k < 3; k++) off[k] = point[k] - root[k];
-  for (int i = m.body_dofadr[body] + m.body_dofnum[body] - 1; i >= 0; i = m.dof_parentid[i]) {
+  PS_SPEC_UNROLL for (int k = 0; k < 3; k++) off[k] = point[k] - root[k];
+  PS_SPEC_UNROLL for (int i = m.body_dofadr[body] + m.body_dofnum[body] - 1; i >= 0; i = m.dof_parentid[i]) {
     const double* c = d.cdof + 6 * i;
-    if (jacr) for (int k = 0; k < 3; k++) jacr[k * S + i] = c[k];
-    if (jacp) { double t[3]; cross3(t, c, off); for (int k = 0; k < 3; k++) jacp[k * S + i] = c[3 + k] + t[k]; }
+    if (jacr) PS_SPEC_UNROLL for (int k = 0; k < 3; k++) jacr[k * S + i] = c[k];
+    if (jacp) { double t[3]; cross3(t, c, off); PS_SPEC_UNROLL for (int k = 0; k < 3; k++) jacp[k * S + i] = c[3 + k] + t[k]; }
   }
 }
 
@@ -213,7 +213,7 @@ template <class T>
 PS_FN void position_smooth(const DevModel<T>& m, RolloutData<T>& d) {
   kinematics(m, d);
   com_position(m, d);
-  for (int i = 0; i < m.nu; i++) d.actuator_length[i] = m.act_gear[i] * d.qpos[m.jnt_qposadr[m.act_jntid[i]]];
+  PS_SPEC_UNROLL for (int i = 0; i < m.nu; i++) d.actuator_length[i] = m.act_gear[i] * d.qpos[m.jnt_qposadr[m.act_jntid[i]]];
   mass_matrix(m, d);
 }
 
@@ -222,24 +222,24 @@ PS_FN void position_smooth(const DevModel<T>& m, RolloutData<T>& d) {
 template <class T>
 PS_NT void com_velocity(const DevModel<T>& m, const RolloutData<T>& d, const double* qvel, double* cvel, double* cdof_dot) {
   vzero(cvel, 6);
-  for (int i = 1; i < m.nbody; i++) {
+  PS_SPEC_UNROLL for (int i = 1; i < m.nbody; i++) {
     double v[6]; vcopy(v, cvel + 6 * m.body_parentid[i], 6);
     const int ja = m.body_jntadr[i];
-    for (int j = ja; j < ja + m.body_jntnum[i]; j++) {
+    PS_SPEC_UNROLL for (int j = ja; j < ja + m.body_jntnum[i]; j++) {
       int da = m.jnt_dofadr[j]; const int jt = m.jnt_type[j];
       if (T::QUAT && jt == JNT_FREE) {
-        for (int k = 0; k < 3; k++) {
+        PS_SPEC_UNROLL for (int k = 0; k < 3; k++) {
           vzero(cdof_dot + 6 * (da + k), 6);
-          for (int r = 0; r < 6; r++) v[r] += d.cdof[6 * (da + k) + r] * qvel[da + k];
+          PS_SPEC_UNROLL for (int r = 0; r < 6; r++) v[r] += d.cdof[6 * (da + k) + r] * qvel[da + k];
         }
         da += 3;
       }
       if (T::QUAT && (jt == JNT_FREE || jt == JNT_BALL)) {
-        for (int k = 0; k < 3; k++) cross_motion(cdof_dot + 6 * (da + k), v, d.cdof + 6 * (da + k));
-        for (int k = 0; k < 3; k++) for (int r = 0; r < 6; r++) v[r] += d.cdof[6 * (da + k) + r] * qvel[da + k];
+        PS_SPEC_UNROLL for (int k = 0; k < 3; k++) cross_motion(cdof_dot + 6 * (da + k), v, d.cdof + 6 * (da + k));
+        PS_SPEC_UNROLL for (int k = 0; k < 3; k++) PS_SPEC_UNROLL for (int r = 0; r < 6; r++) v[r] += d.cdof[6 * (da + k) + r] * qvel[da + k];
       } else {
         cross_motion(cdof_dot + 6 * da, v, d.cdof + 6 * da);
-        for (int r = 0; r < 6; r++) v[r] += d.cdof[6 * da + r] * qvel[da];
+        PS_SPEC_UNROLL for (int r = 0; r < 6; r++) v[r] += d.cdof[6 * da + r] * qvel[da];
       }
     }
     vcopy(cvel + 6 * i, v, 6);
@@ -253,24 +253,24 @@ PS_NT void rne_bias(const DevModel<T>& m, const RolloutData<T>& d, const double*
   const int nb = m.nbody, nv = nv_of(m);
   double cacc[6 * T::NBODY], cfrc[6 * T::NBODY];
   const bool grav = !(m.disableflags & DSBL_GRAVITY);
-  for (int k = 0; k < 3; k++) { cacc[k] = 0; cacc[3 + k] = grav ? -m.gravity[k] : 0.0; }
+  PS_SPEC_UNROLL for (int k = 0; k < 3; k++) { cacc[k] = 0; cacc[3 + k] = grav ? -m.gravity[k] : 0.0; }
   vzero(cfrc, 6);
-  for (int i = 1; i < nb; i++) {
+  PS_SPEC_UNROLL for (int i = 1; i < nb; i++) {
     const int bda = m.body_dofadr[i];
     double* ca = cacc + 6 * i; vcopy(ca, cacc + 6 * m.body_parentid[i], 6);
-    for (int j = 0; j < m.body_dofnum[i]; j++)
-      for (int r = 0; r < 6; r++) ca[r] += cdof_dot[6 * (bda + j) + r] * qvel[bda + j];
+    PS_SPEC_UNROLL for (int j = 0; j < m.body_dofnum[i]; j++)
+      PS_SPEC_UNROLL for (int r = 0; r < 6; r++) ca[r] += cdof_dot[6 * (bda + j) + r] * qvel[bda + j];
     double t1[6], t2[6], t3[6];
     inert_vec(t1, d.cinert + 10 * i, ca);
     inert_vec(t2, d.cinert + 10 * i, cvel + 6 * i);
     cross_force(t3, cvel + 6 * i, t2);
-    for (int r = 0; r < 6; r++) cfrc[6 * i + r] = t1[r] + t3[r];
+    PS_SPEC_UNROLL for (int r = 0; r < 6; r++) cfrc[6 * i + r] = t1[r] + t3[r];
   }
-  for (int i = nb - 1; i > 0; i--) {
+  PS_SPEC_UNROLL for (int i = nb - 1; i > 0; i--) {
     const int p = m.body_parentid[i];
-    if (p > 0) for (int r = 0; r < 6; r++) cfrc[6 * p + r] += cfrc[6 * i + r];
+    if (p > 0) PS_SPEC_UNROLL for (int r = 0; r < 6; r++) cfrc[6 * p + r] += cfrc[6 * i + r];
   }
-  for (int i = 0; i < nv; i++) result[i] = vdot(d.cdof + 6 * i, cfrc + 6 * m.dof_bodyid[i], 6);
+  PS_SPEC_UNROLL for (int i = 0; i < nv; i++) result[i] = vdot(d.cdof + 6 * i, cfrc + 6 * m.dof_bodyid[i], 6);
 }
 
 // 6D velocity [ang; lin] of a frame at `pos` fixed to `body`, world orientation
@@ -278,9 +278,9 @@ template <class T, class D>
 PS_HD void frame_velocity(const DevModel<T>& m, const D& d, int body, const double* pos, double* res) {
   const double* cv = body_cvel(d) + 6 * body;
   double dif[3], cr[3];
-  for (int k = 0; k < 3; k++) dif[k] = pos[k] - d.subtree_com[3 * m.body_rootid[body] + k];
+  PS_SPEC_UNROLL for (int k = 0; k < 3; k++) dif[k] = pos[k] - d.subtree_com[3 * m.body_rootid[body] + k];
   cross3(cr, dif, cv);
-  for (int k = 0; k < 3; k++) { res[k] = cv[k]; res[3 + k] = cv[3 + k] - cr[k]; }
+  PS_SPEC_UNROLL for (int k = 0; k < 3; k++) { res[k] = cv[k]; res[3 + k] = cv[3 + k] - cr[k]; }
 }
 
 // ---------------------------------------------------------------- inertia-box fluid model
@@ -299,14 +299,14 @@ PS_HD void body_local_velocity(const DevModel<T>& m, const RolloutData<T>& d, in
   matT_vec3(lvel, d.ximat + 9 * i, v);
   matT_vec3(lvel + 3, d.ximat + 9 * i, v + 3);
   double lw[3]; matT_vec3(lw, d.ximat + 9 * i, m.wind);
-  for (int k = 0; k < 3; k++) lvel[3 + k] -= lw[k];
+  PS_SPEC_UNROLL for (int k = 0; k < 3; k++) lvel[3 + k] -= lw[k];
 }
 
 template <class T>
 PS_NT void fluid_forces(const DevModel<T>& m, const RolloutData<T>& d, double* qfrc) {
   constexpr int S = T::NV; const int nv = nv_of(m);
   double jp[3 * S], jr[3 * S];
-  for (int i = 1; i < m.nbody; i++) {
+  PS_SPEC_UNROLL for (int i = 1; i < m.nbody; i++) {
     if (m.body_mass[i] < kMinVal) continue;
     double box[3], lvel[6], lf[6], wf[6];
     inertia_box(m, i, box);
@@ -315,7 +315,7 @@ PS_NT void fluid_forces(const DevModel<T>& m, const RolloutData<T>& d, double* q
     const double visc = m.viscosity, dens = m.density;
     if (visc > 0) {
       const double diam = (box[0] + box[1] + box[2]) / 3.0;
-      for (int k = 0; k < 3; k++) {
+      PS_SPEC_UNROLL for (int k = 0; k < 3; k++) {
         lf[k] = -kPi * diam * diam * diam * visc * lvel[k];
         lf[3 + k] = -3.0 * kPi * diam * visc * lvel[3 + k];
       }
@@ -332,29 +332,29 @@ PS_NT void fluid_forces(const DevModel<T>& m, const RolloutData<T>& d, double* q
     mat_vec3(wf, d.ximat + 9 * i, lf);           // torque, world
     mat_vec3(wf + 3, d.ximat + 9 * i, lf + 3);   // force, world
     point_jacobian(m, d, jp, jr, d.xipos + 3 * i, i);
-    for (int c = 0; c < nv; c++)
-      for (int k = 0; k < 3; k++) qfrc[c] += jp[k * S + c] * wf[3 + k] + jr[k * S + c] * wf[k];
+    PS_SPEC_UNROLL for (int c = 0; c < nv; c++)
+      PS_SPEC_UNROLL for (int k = 0; k < 3; k++) qfrc[c] += jp[k * S + c] * wf[3 + k] + jr[k * S + c] * wf[k];
   }
 }
 
 template <class T>
 PS_NT void velocity_stage(const DevModel<T>& m, RolloutData<T>& d) {
   const int nv = nv_of(m);
-  for (int i = 0; i < m.nu; i++) d.actuator_velocity[i] = m.act_gear[i] * d.qvel[m.jnt_dofadr[m.act_jntid[i]]];
+  PS_SPEC_UNROLL for (int i = 0; i < m.nu; i++) d.actuator_velocity[i] = m.act_gear[i] * d.qvel[m.jnt_dofadr[m.act_jntid[i]]];
   com_velocity(m, d, d.qvel, d.cvel, d.cdof_dot);
   // passive forces: spring + damper + fluid
   if (m.disableflags & DSBL_PASSIVE) vzero(d.qfrc_passive, nv);
   else {
     double spring[T::NV], fluid[T::NV];
     vzero(spring, nv); vzero(fluid, nv);
-    for (int j = 0; j < m.njnt; j++) {
+    PS_SPEC_UNROLL for (int j = 0; j < m.njnt; j++) {
       const double k = m.jnt_stiffness[j];
       if (k == 0) continue;
       if (m.jnt_type[j] == JNT_HINGE || m.jnt_type[j] == JNT_SLIDE)
         spring[m.jnt_dofadr[j]] = -k * (d.qpos[m.jnt_qposadr[j]] - m.qpos_spring[m.jnt_qposadr[j]]);
     }
     if (!T::LEAN && (m.viscosity > 0 || m.density > 0)) fluid_forces(m, d, fluid);
-    for (int i = 0; i < nv; i++) d.qfrc_passive[i] = spring[i] + (-m.dof_damping[i] * d.qvel[i]) + fluid[i];
+    PS_SPEC_UNROLL for (int i = 0; i < nv; i++) d.qfrc_passive[i] = spring[i] + (-m.dof_damping[i] * d.qvel[i]) + fluid[i];
   }
   rne_bias(m, d, d.qvel, d.cvel, d.cdof_dot, d.qfrc_bias);
 }
@@ -364,11 +364,11 @@ template <class T>
 PS_NT void actuation_stage(const DevModel<T>& m, RolloutData<T>& d) {
   const int nv = nv_of(m), nu = m.nu;
   vzero(d.qfrc_actuator, nv); vzero(d.actuator_force, nu);
-  for (int i = 0; i < m.na; i++) d.act_dot[i] = 0;
+  PS_SPEC_UNROLL for (int i = 0; i < m.na; i++) d.act_dot[i] = 0;
   if (!nu || (m.disableflags & DSBL_ACTUATION)) return;
-  for (int i = 0; i < nu; i++) {
+  PS_SPEC_UNROLL for (int i = 0; i < nu; i++) {
     double ctrl = d.ctrl[i];
-    if (bad_number(ctrl)) { d.warning |= WARN_BADCTRL; ctrl = 0; for (int k = 0; k < nu; k++) d.ctrl[k] = 0; }
+    if (bad_number(ctrl)) { d.warning |= WARN_BADCTRL; ctrl = 0; PS_SPEC_UNROLL for (int k = 0; k < nu; k++) d.ctrl[k] = 0; }
     if (m.act_ctrllimited[i] && !(m.disableflags & DSBL_CLAMPCTRL))
       ctrl = clampd(ctrl, m.act_ctrlrange[2 * i], m.act_ctrlrange[2 * i + 1]);
     double in = ctrl;
@@ -394,7 +394,7 @@ PS_NT void actuation_stage(const DevModel<T>& m, RolloutData<T>& d) {
 template <class T>
 PS_NT void acceleration_stage(const DevModel<T>& m, RolloutData<T>& d) {
   const int nv = nv_of(m);
-  for (int i = 0; i < nv; i++) {
+  PS_SPEC_UNROLL for (int i = 0; i < nv; i++) {
     d.qfrc_smooth[i] = d.qfrc_passive[i] - d.qfrc_bias[i] + d.qfrc_actuator[i];
     d.qacc_smooth[i] = d.qfrc_smooth[i];
   }
@@ -407,16 +407,16 @@ PS_NT void acceleration_stage(const DevModel<T>& m, RolloutData<T>& d) {
 template <class T>
 PS_NT void acceleration_stage_xfrc(const DevModel<T>& m, RolloutData<T>& d, const double* xfrc_applied) {
   constexpr int S = T::NV; const int nv = nv_of(m);
-  for (int i = 0; i < nv; i++) d.qfrc_smooth[i] = d.qfrc_passive[i] - d.qfrc_bias[i] + d.qfrc_actuator[i];
+  PS_SPEC_UNROLL for (int i = 0; i < nv; i++) d.qfrc_smooth[i] = d.qfrc_passive[i] - d.qfrc_bias[i] + d.qfrc_actuator[i];
   double jp[3 * S], jr[3 * S];
-  for (int b = 1; b < m.nbody; b++) {
+  PS_SPEC_UNROLL for (int b = 1; b < m.nbody; b++) {
     const double* x = xfrc_applied + 6 * b;
     if (x[0] == 0 && x[1] == 0 && x[2] == 0 && x[3] == 0 && x[4] == 0 && x[5] == 0) continue;
     point_jacobian(m, d, jp, jr, d.xipos + 3 * b, b);
-    for (int c = 0; c < nv; c++)
-      for (int k = 0; k < 3; k++) d.qfrc_smooth[c] += jp[k * S + c] * x[k] + jr[k * S + c] * x[3 + k];
+    PS_SPEC_UNROLL for (int c = 0; c < nv; c++)
+      PS_SPEC_UNROLL for (int k = 0; k < 3; k++) d.qfrc_smooth[c] += jp[k * S + c] * x[k] + jr[k * S + c] * x[3 + k];
   }
-  for (int i = 0; i < nv; i++) d.qacc_smooth[i] = d.qfrc_smooth[i];
+  PS_SPEC_UNROLL for (int i = 0; i < nv; i++) d.qacc_smooth[i] = d.qfrc_smooth[i];
   solve_tree(m, d.qacc_smooth, d.qLD, d.qLDiagInv);
 }
 

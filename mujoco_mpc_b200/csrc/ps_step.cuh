@@ -16,25 +16,25 @@ PS_NT void subtree_velocity(const DevModel<T>& m, RolloutData<T>& d) {
   const int nb = m.nbody;
   double bodyvel[6 * T::NBODY];
   double* lv = d.subtree_linvel; double* am = d.subtree_angmom;
-  for (int i = 0; i < nb; i++) {
+  PS_SPEC_UNROLL for (int i = 0; i < nb; i++) {
     frame_velocity(m, d, i, d.xipos + 3 * i, bodyvel + 6 * i);
-    for (int k = 0; k < 3; k++) lv[3 * i + k] = m.body_mass[i] * bodyvel[6 * i + 3 + k];
+    PS_SPEC_UNROLL for (int k = 0; k < 3; k++) lv[3 * i + k] = m.body_mass[i] * bodyvel[6 * i + 3 + k];
     double t[3], t2[3]; matT_vec3(t, d.ximat + 9 * i, bodyvel + 6 * i);
-    for (int k = 0; k < 3; k++) t[k] *= m.body_inertia[3 * i + k];
+    PS_SPEC_UNROLL for (int k = 0; k < 3; k++) t[k] *= m.body_inertia[3 * i + k];
     mat_vec3(t2, d.ximat + 9 * i, t); vcopy(am + 3 * i, t2, 3);
   }
-  for (int i = nb - 1; i >= 0; i--) {
-    if (i) for (int k = 0; k < 3; k++) lv[3 * m.body_parentid[i] + k] += lv[3 * i + k];
-    for (int k = 0; k < 3; k++) lv[3 * i + k] /= fmax(kMinVal, m.body_subtreemass[i]);
+  PS_SPEC_UNROLL for (int i = nb - 1; i >= 0; i--) {
+    if (i) PS_SPEC_UNROLL for (int k = 0; k < 3; k++) lv[3 * m.body_parentid[i] + k] += lv[3 * i + k];
+    PS_SPEC_UNROLL for (int k = 0; k < 3; k++) lv[3 * i + k] /= fmax(kMinVal, m.body_subtreemass[i]);
   }
-  for (int i = nb - 1; i > 0; i--) {
+  PS_SPEC_UNROLL for (int i = nb - 1; i > 0; i--) {
     const int p = m.body_parentid[i]; double dx[3], dv[3], dL[3];
-    for (int k = 0; k < 3; k++) { dx[k] = d.xipos[3 * i + k] - d.subtree_com[3 * i + k]; dv[k] = (bodyvel[6 * i + 3 + k] - lv[3 * i + k]) * m.body_mass[i]; }
+    PS_SPEC_UNROLL for (int k = 0; k < 3; k++) { dx[k] = d.xipos[3 * i + k] - d.subtree_com[3 * i + k]; dv[k] = (bodyvel[6 * i + 3 + k] - lv[3 * i + k]) * m.body_mass[i]; }
     cross3(dL, dx, dv);
-    for (int k = 0; k < 3; k++) { am[3 * i + k] += dL[k]; am[3 * p + k] += am[3 * i + k]; }
-    for (int k = 0; k < 3; k++) { dx[k] = d.subtree_com[3 * i + k] - d.subtree_com[3 * p + k]; dv[k] = (lv[3 * i + k] - lv[3 * p + k]) * m.body_subtreemass[i]; }
+    PS_SPEC_UNROLL for (int k = 0; k < 3; k++) { am[3 * i + k] += dL[k]; am[3 * p + k] += am[3 * i + k]; }
+    PS_SPEC_UNROLL for (int k = 0; k < 3; k++) { dx[k] = d.subtree_com[3 * i + k] - d.subtree_com[3 * p + k]; dv[k] = (lv[3 * i + k] - lv[3 * p + k]) * m.body_subtreemass[i]; }
     cross3(dL, dx, dv);
-    for (int k = 0; k < 3; k++) am[3 * p + k] += dL[k];
+    PS_SPEC_UNROLL for (int k = 0; k < 3; k++) am[3 * p + k] += dL[k];
   }
 }
 
@@ -93,8 +93,8 @@ PS_FN void forward_pass_xfrc(const DevModel<T>& m, RolloutData<T>& d, const doub
 template <class T>
 PS_NT void smooth_vel_derivative(const DevModel<T>& m, RolloutData<T>& d, double* D, bool with_bias) {
   constexpr int S = T::NV; const int nv = nv_of(m);
-  for (int i = 0; i < nv; i++) for (int j = 0; j < nv; j++) D[i * S + j] = 0;
-  for (int i = 0; i < m.nu; i++) {
+  PS_SPEC_UNROLL for (int i = 0; i < nv; i++) PS_SPEC_UNROLL for (int j = 0; j < nv; j++) D[i * S + j] = 0;
+  PS_SPEC_UNROLL for (int i = 0; i < m.nu; i++) {
     double bv = 0;
     if (m.act_biastype[i] == 1) bv += m.act_biasprm[3 * i + 2];
     if (m.act_gaintype[i] == 1) {
@@ -104,14 +104,14 @@ PS_NT void smooth_vel_derivative(const DevModel<T>& m, RolloutData<T>& d, double
     if (bv != 0) { const int dof = m.jnt_dofadr[m.act_jntid[i]]; const double g = m.act_gear[i]; D[dof * S + dof] += g * g * bv; }
   }
   if (!(m.disableflags & DSBL_PASSIVE)) {
-    for (int i = 0; i < nv; i++) D[i * S + i] -= m.dof_damping[i];
+    PS_SPEC_UNROLL for (int i = 0; i < nv; i++) D[i * S + i] -= m.dof_damping[i];
     if (m.viscosity > 0 || m.density > 0) {
       double jp[3 * S], jr[3 * S], Jl[6 * S];
-      for (int b = 1; b < m.nbody; b++) {
+      PS_SPEC_UNROLL for (int b = 1; b < m.nbody; b++) {
         if (m.body_mass[b] < kMinVal) continue;
         double box[3], lvel[6]; inertia_box(m, b, box); body_local_velocity(m, d, b, lvel);
         double B[6] = {0, 0, 0, 0, 0, 0}; const double dens = m.density, visc = m.viscosity;
-        if (visc > 0) { const double diam = (box[0] + box[1] + box[2]) / 3.0; for (int k = 0; k < 3; k++) { B[k] -= kPi * diam * diam * diam * visc; B[3 + k] -= 3.0 * kPi * diam * visc; } }
+        if (visc > 0) { const double diam = (box[0] + box[1] + box[2]) / 3.0; PS_SPEC_UNROLL for (int k = 0; k < 3; k++) { B[k] -= kPi * diam * diam * diam * visc; B[3 + k] -= 3.0 * kPi * diam * visc; } }
         if (dens > 0) {
           B[3] -= dens * box[1] * box[2] * fabs(lvel[3]); B[4] -= dens * box[0] * box[2] * fabs(lvel[4]); B[5] -= dens * box[0] * box[1] * fabs(lvel[5]);
           const double b0 = box[0], b1 = box[1], b2 = box[2];
@@ -121,13 +121,13 @@ PS_NT void smooth_vel_derivative(const DevModel<T>& m, RolloutData<T>& d, double
         }
         point_jacobian(m, d, jp, jr, d.xipos + 3 * b, b);
         const double* R = d.ximat + 9 * b;
-        for (int i = 0; i < nv; i++) for (int r = 0; r < 3; r++) {
+        PS_SPEC_UNROLL for (int i = 0; i < nv; i++) PS_SPEC_UNROLL for (int r = 0; r < 3; r++) {
           Jl[r * S + i] = R[r] * jr[i] + R[3 + r] * jr[S + i] + R[6 + r] * jr[2 * S + i];
           Jl[(3 + r) * S + i] = R[r] * jp[i] + R[3 + r] * jp[S + i] + R[6 + r] * jp[2 * S + i];
         }
-        for (int r = 0; r < 6; r++) for (int i = 0; i < nv; i++) {
+        PS_SPEC_UNROLL for (int r = 0; r < 6; r++) PS_SPEC_UNROLL for (int i = 0; i < nv; i++) {
           const double s = B[r] * Jl[r * S + i]; if (s == 0) continue;
-          for (int j = 0; j < nv; j++) D[i * S + j] += s * Jl[r * S + j];
+          PS_SPEC_UNROLL for (int j = 0; j < nv; j++) D[i * S + j] += s * Jl[r * S + j];
         }
       }
     }
@@ -138,10 +138,10 @@ PS_NT void smooth_vel_derivative(const DevModel<T>& m, RolloutData<T>& d, double
     double g[S], cv[S], ce[S], cve[S], v[S], cvel[6 * T::NBODY], cdd[6 * S];
     vzero(v, nv); com_velocity(m, d, v, cvel, cdd); rne_bias(m, d, v, cvel, cdd, g);
     com_velocity(m, d, d.qvel, cvel, cdd); rne_bias(m, d, d.qvel, cvel, cdd, cv);
-    for (int j = 0; j < nv; j++) {
+    PS_SPEC_UNROLL for (int j = 0; j < nv; j++) {
       vzero(v, nv); v[j] = 1; com_velocity(m, d, v, cvel, cdd); rne_bias(m, d, v, cvel, cdd, ce);
       vcopy(v, d.qvel, nv); v[j] += 1; com_velocity(m, d, v, cvel, cdd); rne_bias(m, d, v, cvel, cdd, cve);
-      for (int i = 0; i < nv; i++) D[i * S + j] -= (cve[i] - g[i]) - (cv[i] - g[i]) - (ce[i] - g[i]);
+      PS_SPEC_UNROLL for (int i = 0; i < nv; i++) D[i * S + j] -= (cve[i] - g[i]) - (cv[i] - g[i]) - (ce[i] - g[i]);
     }
   }
 }
@@ -155,29 +155,29 @@ PS_NT void integrate(const DevModel<T>& m, RolloutData<T>& d) {
     if (!m.any_damping || (m.disableflags & DSBL_EULERDAMP)) vcopy(qacc, d.qacc, nv);
     else {
       double* L = d.sv_H; double dinv[S];
-      for (int i = 0; i < nv; i++) for (int j = 0; j < nv; j++) L[i * S + j] = d.qM[i * S + j];
-      for (int i = 0; i < nv; i++) L[i * S + i] += dt * m.dof_damping[i];
+      PS_SPEC_UNROLL for (int i = 0; i < nv; i++) PS_SPEC_UNROLL for (int j = 0; j < nv; j++) L[i * S + j] = d.qM[i * S + j];
+      PS_SPEC_UNROLL for (int i = 0; i < nv; i++) L[i * S + i] += dt * m.dof_damping[i];
       factor_tree(m, L, dinv);
-      for (int i = 0; i < nv; i++) qacc[i] = d.qfrc_smooth[i] + d.qfrc_constraint[i];
+      PS_SPEC_UNROLL for (int i = 0; i < nv; i++) qacc[i] = d.qfrc_smooth[i] + d.qfrc_constraint[i];
       solve_tree(m, qacc, L, dinv);
     }
   } else {
     const bool full = m.integrator == INT_IMPLICIT;
     double D[S * S]; double* L = d.sv_H;
     smooth_vel_derivative(m, d, D, full);
-    for (int i = 0; i < nv; i++) qacc[i] = d.qfrc_smooth[i] + d.qfrc_constraint[i];
+    PS_SPEC_UNROLL for (int i = 0; i < nv; i++) qacc[i] = d.qfrc_smooth[i] + d.qfrc_constraint[i];
     if (full) {
-      for (int i = 0; i < nv; i++) for (int j = 0; j < nv; j++) L[i * S + j] = d.qM[i * S + j] - dt * D[i * S + j];
-      for (int k = 0; k < nv; k++)
-        for (int i = k + 1; i < nv; i++) {
+      PS_SPEC_UNROLL for (int i = 0; i < nv; i++) PS_SPEC_UNROLL for (int j = 0; j < nv; j++) L[i * S + j] = d.qM[i * S + j] - dt * D[i * S + j];
+      PS_SPEC_UNROLL for (int k = 0; k < nv; k++)
+        PS_SPEC_UNROLL for (int i = k + 1; i < nv; i++) {
           const double f = L[i * S + k] / L[k * S + k]; L[i * S + k] = f;
-          for (int j = k + 1; j < nv; j++) L[i * S + j] -= f * L[k * S + j];
+          PS_SPEC_UNROLL for (int j = k + 1; j < nv; j++) L[i * S + j] -= f * L[k * S + j];
         }
-      for (int i = 0; i < nv; i++) for (int k = 0; k < i; k++) qacc[i] -= L[i * S + k] * qacc[k];
-      for (int i = nv - 1; i >= 0; i--) { for (int k = i + 1; k < nv; k++) qacc[i] -= L[i * S + k] * qacc[k]; qacc[i] /= L[i * S + i]; }
+      PS_SPEC_UNROLL for (int i = 0; i < nv; i++) PS_SPEC_UNROLL for (int k = 0; k < i; k++) qacc[i] -= L[i * S + k] * qacc[k];
+      PS_SPEC_UNROLL for (int i = nv - 1; i >= 0; i--) { PS_SPEC_UNROLL for (int k = i + 1; k < nv; k++) qacc[i] -= L[i * S + k] * qacc[k]; qacc[i] /= L[i * S + i]; }
     } else {
       double dinv[S];
-      for (int i = 0; i < nv; i++) for (int j = 0; j < nv; j++)
+      PS_SPEC_UNROLL for (int i = 0; i < nv; i++) PS_SPEC_UNROLL for (int j = 0; j < nv; j++)
         L[i * S + j] = d.qM[i * S + j] - dt * 0.5 * (D[i * S + j] + D[j * S + i]);
       factor_tree(m, L, dinv);
       solve_tree(m, qacc, L, dinv);
@@ -185,7 +185,7 @@ PS_NT void integrate(const DevModel<T>& m, RolloutData<T>& d) {
   }
   // advance activations, velocities, positions, time
   if (!T::LEAN && m.na && !(m.disableflags & DSBL_ACTUATION)) {
-    for (int i = 0; i < m.nu; i++) {
+    PS_SPEC_UNROLL for (int i = 0; i < m.nu; i++) {
       if (m.act_dyntype[i] == DYN_NONE) continue;
       const int a = m.act_actadr[i];
       double act = d.act[a];
@@ -197,11 +197,11 @@ PS_NT void integrate(const DevModel<T>& m, RolloutData<T>& d) {
       d.act[a] = act;
     }
   }
-  for (int i = 0; i < nv; i++) d.qvel[i] += qacc[i] * dt;
-  for (int j = 0; j < m.njnt; j++) {
+  PS_SPEC_UNROLL for (int i = 0; i < nv; i++) d.qvel[i] += qacc[i] * dt;
+  PS_SPEC_UNROLL for (int j = 0; j < m.njnt; j++) {
     const int qa = m.jnt_qposadr[j], da = m.jnt_dofadr[j], jt = m.jnt_type[j];
     if (T::QUAT && jt == JNT_FREE) {
-      for (int k = 0; k < 3; k++) d.qpos[qa + k] += dt * d.qvel[da + k];
+      PS_SPEC_UNROLL for (int k = 0; k < 3; k++) d.qpos[qa + k] += dt * d.qvel[da + k];
       quat_integrate(d.qpos + qa + 3, d.qvel + da + 3, dt);
     } else if (T::QUAT && jt == JNT_BALL) quat_integrate(d.qpos + qa, d.qvel + da, dt);
     else d.qpos[qa] += dt * d.qvel[da];
@@ -213,13 +213,13 @@ PS_NT void integrate(const DevModel<T>& m, RolloutData<T>& d) {
 // by the caller (CheckWarnings, mjpc/utilities.cc:787-800; mjpc/trajectory.cc:169-173)
 template <class T>
 PS_HD bool state_is_bad(const DevModel<T>& m, RolloutData<T>& d) {
-  for (int i = 0; i < nq_of(m); i++) if (bad_number(d.qpos[i])) { d.warning |= WARN_BADQPOS; return true; }
-  for (int i = 0; i < nv_of(m); i++) if (bad_number(d.qvel[i])) { d.warning |= WARN_BADQVEL; return true; }
+  PS_SPEC_UNROLL for (int i = 0; i < nq_of(m); i++) if (bad_number(d.qpos[i])) { d.warning |= WARN_BADQPOS; return true; }
+  PS_SPEC_UNROLL for (int i = 0; i < nv_of(m); i++) if (bad_number(d.qvel[i])) { d.warning |= WARN_BADQVEL; return true; }
   return false;
 }
 template <class T>
 PS_HD bool acc_is_bad(const DevModel<T>& m, RolloutData<T>& d) {
-  for (int i = 0; i < nv_of(m); i++) if (bad_number(d.qacc[i])) { d.warning |= WARN_BADQACC; return true; }
+  PS_SPEC_UNROLL for (int i = 0; i < nv_of(m); i++) if (bad_number(d.qacc[i])) { d.warning |= WARN_BADQACC; return true; }
   return false;
 }
 

@@ -28,6 +28,15 @@
 #else
 #define PS_NT PS_NI
 #endif
+// Model-specialised translation units (ps_variant_tiny_spec.cu) ask for full unrolling of the loops over bodies /
+// joints / dofs / cost terms: their trip counts and index tables are compile-time there, so every array index
+// becomes a constant and the per-rollout working set is promoted to registers.  Everywhere else the macro is empty
+// and the generic kernels compile exactly as before.
+#ifdef PS_SPEC_BUILD
+#define PS_SPEC_UNROLL _Pragma("unroll")
+#else
+#define PS_SPEC_UNROLL
+#endif
 #if defined(__CUDA_ARCH__)
 #define PS_ASSUME_SHARED(p) __builtin_assume(__isShared(p))
 #else
@@ -56,6 +65,7 @@ struct Traits {
                        MAXCON = (MAXCON_ > 0 ? MAXCON_ : 1), MAXEFC = (MAXEFC_ > 0 ? MAXEFC_ : 1),
                        NSENSOR = (NSENSOR_ > 0 ? NSENSOR_ : 1);
   static constexpr bool ELLIPTIC = ELLIPTIC_;
+  static constexpr bool SPEC = false;           // model-specialised instantiation (SpecTraits below)
   // Feature switches derived from the capacities.  CONTACTS: the instantiation carries collision and
   // contact rows at all.  LEAN (the tiny thread-per-rollout engine): nq == nv == the capacity exactly,
   // hinge / slide joints only, no contacts, no activations, no fluid, Euler only -- the other code paths
@@ -156,6 +166,60 @@ struct alignas(16) DevModel {
   short track_geom[kMaxTrackGeom], geom_trackslot[T::NGEOM];
 };
 
+// ------------------------------------------------------------------------------------------
+// Model-specialised instantiation.  `Spec` (csrc/ps_spec_generated.h, written by tools/gen_spec_header.py from a
+// registered task's model + cost specification) carries every INTEGER of the model and of the cost specification --
+// sizes, topology tables, joint / actuator / sensor types, norm types -- as compile-time constants; the doubles
+// (inertias, offsets, gains, weights ...) stay run-time data in shared memory.  DevModel<SpecTraits<Spec>> keeps the
+// field names of the generic DevModel, so the stage functions compile unchanged: `m.nbody` is a static constexpr
+// and `m.body_parentid[b]` goes through a constexpr table proxy that folds once the loop over b is unrolled.  With
+// every index constant the RolloutData of the rollout is promoted to registers and the branches on joint / sensor /
+// norm types disappear.  fill_model rejects (falls through to the generic lean kernel) any model whose integers
+// differ from the Spec's.
+// PS_TAB(name, expr): table proxy whose operator[] is a pure expression in the index (a chain of conditionals written by
+// the generator), so it folds to a constant wherever the index is one and never touches memory where it is not
+#define PS_TAB(name, expr) struct name##_t { PS_HD constexpr int operator[](int i_) const { return expr; } } name
+
+// Walk the dof tree upwards: i = first, parent[first], ... while i >= 0 (every index is < bound).  Model-specialised
+// builds iterate i = bound-1 .. 0 with a compile-time trip count and skip the non-members, so that the walk unrolls and
+// every visited index is a constant; the visiting order -- and hence the arithmetic -- is the same.
+#ifdef PS_SPEC_BUILD
+#define PS_CHAIN(i, first, bound, par) \
+  _Pragma("unroll") for (int i = (bound) - 1, nx_##i = (first); i >= 0; i--) if (i == nx_##i && ((nx_##i = par[i]), true))
+#else
+#define PS_CHAIN(i, first, bound, par) for (int i = (first); i >= 0; i = par[i])
+#endif
+
+template <class Spec>
+struct SpecTraits : Traits<Spec::NQ, Spec::NV, Spec::NU, 0, Spec::NBODY, Spec::NJNT, Spec::NGEOM, Spec::NSITE, Spec::NMOCAP, 0, 0, 4,
+                           Spec::NSENSOR, false> {
+  using Topo = Spec;
+  using Base = Traits<Spec::NQ, Spec::NV, Spec::NU, 0, Spec::NBODY, Spec::NJNT, Spec::NGEOM, Spec::NSITE, Spec::NMOCAP, 0, 0, 4,
+                      Spec::NSENSOR, false>;
+  static constexpr bool SPEC = true;
+  static_assert(Base::LEAN, "model specialisation is built on the lean instantiation (nv <= 2, no contacts, Euler)");
+};
+
+template <class Spec>
+struct alignas(16) DevModel<SpecTraits<Spec>> : Spec::ModelInts {
+  using T = SpecTraits<Spec>;
+  double timestep, impratio, tolerance, ls_tolerance, density, viscosity, meaninertia;
+  double gravity[3], wind[3];
+  double qpos0[T::NQ], qpos_spring[T::NQ];
+  double body_pos[T::NBODY * 3], body_quat[T::NBODY * 4], body_ipos[T::NBODY * 3], body_iquat[T::NBODY * 4],
+      body_mass[T::NBODY], body_subtreemass[T::NBODY], body_inertia[T::NBODY * 3], body_invweight0[T::NBODY * 2];
+  double jnt_pos[T::NJNT * 3], jnt_axis[T::NJNT * 3], jnt_stiffness[T::NJNT], jnt_range[T::NJNT * 2],
+      jnt_margin[T::NJNT], jnt_solref[T::NJNT * 2], jnt_solimp[T::NJNT * 5];
+  double dof_armature[T::NV], dof_damping[T::NV], dof_frictionloss[T::NV], dof_solref[T::NV * 2],
+      dof_solimp[T::NV * 5], dof_invweight0[T::NV];
+  double geom_size[T::NGEOM * 3], geom_pos[T::NGEOM * 3], geom_quat[T::NGEOM * 4], geom_friction[T::NGEOM * 3],
+      geom_solmix[T::NGEOM], geom_solref[T::NGEOM * 2], geom_solimp[T::NGEOM * 5], geom_margin[T::NGEOM],
+      geom_gap[T::NGEOM], geom_rbound[T::NGEOM];
+  double site_pos[T::NSITE * 3], site_quat[T::NSITE * 4];
+  double act_dynprm[T::NU * 3], act_gainprm[T::NU * 3], act_biasprm[T::NU * 3], act_ctrlrange[T::NU * 2],
+      act_forcerange[T::NU * 2], act_actrange[T::NU * 2], act_gear[T::NU];
+};
+
 // Cost specification + residual snapshot (what Task::Residual()/BaseResidualFn::Update hands the
 // planner every iteration, mjpc/task.cc:112-128), trimmed to device capacities.
 struct alignas(16) DevTask {
@@ -168,6 +232,16 @@ struct alignas(16) DevTask {
   double risk;
   double parameters[kMaxTaskParam];
   double aux[kMaxTaskAux];
+};
+
+// Cost specification as a model-specialised instantiation sees it: the integers (term layout, norm types, sensor ids)
+// are the Spec's compile-time constants, the doubles are read from the DevTask in shared memory.  Same member names
+// as DevTask, so cost_value / task_residual compile for either.
+template <class Spec>
+struct SpecTaskView : Spec::TaskInts {
+  const double* weight; const double* norm_parameter; const double* parameters; const double* aux; const int* iaux; double risk;
+  PS_HD explicit SpecTaskView(const DevTask& t)
+      : weight(t.weight), norm_parameter(t.norm_parameter), parameters(t.parameters), aux(t.aux), iaux(t.iaux), risk(t.risk) {}
 };
 
 // Per-iteration inputs shared by all rollouts.
@@ -192,6 +266,8 @@ struct Contact {
 // Working set of ONE rollout (thread-private).
 template <class T>
 struct RolloutData {
+  struct Rows {};                       // see the model-specialised RolloutData below
+  PS_HD void bind(Rows&) {}
   double time;
   double qpos[T::NQ], qvel[T::NV], act[T::NA], ctrl[T::NU], qacc[T::NV], qacc_warmstart[T::NV], act_dot[T::NA];
   double mocap_pos[3 * T::NMOCAP], mocap_quat[4 * T::NMOCAP];
@@ -218,6 +294,48 @@ struct RolloutData {
   // solver scratch
   double sv_Ma[T::NV], sv_grad[T::NV], sv_search[T::NV], sv_Mv[T::NV], sv_H[T::NV * T::NV];
   double sv_Jaref[T::MAXEFC], sv_Jv[T::MAXEFC];
+};
+
+// Model-specialised working set.  Everything indexed by body / joint / dof lives in this struct and -- all indices
+// being compile-time constants after unrolling -- is promoted to registers.  The constraint rows are the one part whose
+// indices are data dependent (a joint-limit row exists only while the joint is near its limit), and a single
+// variable-index access would keep the WHOLE struct in local memory; so the row arrays live in a separate object
+// (Rows, a cold local-memory block touched only on steps with active rows) and this struct holds pointers to them.
+template <class Spec>
+struct RolloutData<SpecTraits<Spec>> {
+  using T = SpecTraits<Spec>;
+  struct Rows {
+    int efc_type[T::MAXEFC], efc_id[T::MAXEFC], efc_state[T::MAXEFC];
+    double efc_J[T::MAXEFC * T::NV], efc_pos[T::MAXEFC], efc_margin[T::MAXEFC], efc_frictionloss[T::MAXEFC],
+        efc_D[T::MAXEFC], efc_R[T::MAXEFC], efc_aref[T::MAXEFC], efc_force[T::MAXEFC], efc_KBI[3 * T::MAXEFC];
+    double sv_Jaref[T::MAXEFC], sv_Jv[T::MAXEFC];
+  };
+  PS_HD void bind(Rows& r) {
+    efc_type = r.efc_type; efc_id = r.efc_id; efc_state = r.efc_state; efc_J = r.efc_J; efc_pos = r.efc_pos; efc_margin = r.efc_margin;
+    efc_frictionloss = r.efc_frictionloss; efc_D = r.efc_D; efc_R = r.efc_R; efc_aref = r.efc_aref; efc_force = r.efc_force;
+    efc_KBI = r.efc_KBI; sv_Jaref = r.sv_Jaref; sv_Jv = r.sv_Jv;
+  }
+  double time;
+  double qpos[T::NQ], qvel[T::NV], act[T::NA], ctrl[T::NU], qacc[T::NV], qacc_warmstart[T::NV], act_dot[T::NA];
+  double mocap_pos[3 * T::NMOCAP], mocap_quat[4 * T::NMOCAP];
+  double xpos[3 * T::NBODY], xquat[4 * T::NBODY], xmat[9 * T::NBODY], xipos[3 * T::NBODY], ximat[9 * T::NBODY];
+  double xanchor[3 * T::NJNT], xaxis[3 * T::NJNT];
+  double geom_xpos[3 * T::NGEOM], geom_xmat[9 * T::NGEOM];
+  double site_xpos[3 * T::NSITE], site_xmat[9 * T::NSITE];
+  double subtree_com[3 * T::NBODY], cinert[10 * T::NBODY], crb[10 * T::NBODY], cdof[6 * T::NV];
+  double qM[T::NV * T::NV], qLD[T::NV * T::NV], qLDiagInv[T::NV];
+  double actuator_length[T::NU], actuator_velocity[T::NU], actuator_force[T::NU];
+  double cvel[6 * T::NBODY], cdof_dot[6 * T::NV];
+  double qfrc_bias[T::NV], qfrc_passive[T::NV], qfrc_actuator[T::NV], qfrc_smooth[T::NV], qacc_smooth[T::NV],
+      qfrc_constraint[T::NV];
+  double subtree_linvel[3 * T::NBODY], subtree_angmom[3 * T::NBODY];
+  int ncon, nefc, solver_iter, warning;
+  Contact contact[1];
+  double coneH[1];
+  int *efc_type, *efc_id, *efc_state;
+  double *efc_J, *efc_pos, *efc_margin, *efc_frictionloss, *efc_D, *efc_R, *efc_aref, *efc_force, *efc_KBI;
+  double sv_Ma[T::NV], sv_grad[T::NV], sv_search[T::NV], sv_Mv[T::NV], sv_H[T::NV * T::NV];
+  double *sv_Jaref, *sv_Jv;
 };
 
 enum { WARN_BADQPOS = 1, WARN_BADQVEL = 2, WARN_BADQACC = 4, WARN_BADCTRL = 8, WARN_CAPACITY = 16 };

@@ -109,6 +109,7 @@ struct Variant {
   int (*plan)(void*, const double*, int, const double*, int, double, const double*, int, int, int);
   int (*launch)(cudaStream_t, const void*, const double*, int, int, int, long long, double*, unsigned char*, MinLoc*, Writeback, bool, int*);
   int (*robust)(cudaStream_t, const void*, const double*, int, int, double*, unsigned char*, Writeback, XfrcNoise);   // null: no force perturbations
+  int (*task_ok)(const DevTask&, int) = nullptr;   // model-specialised instantiations: was the kernel compiled for this cost specification?
 };
 // the force-perturbed kernels live in their own translation unit (ps_variant_robust.cu), so that the code
 // generated for the planning kernels of a variant's unit does not depend on them
@@ -126,6 +127,17 @@ template <class T, int WARPS>
 inline Variant make_coop_variant(const char* name, RobustFn robust = nullptr) {
   return Variant{name, sizeof(Constants<T>), offsetof(Constants<T>, p), sizeof(DevPlan<T>), WARPS * 32, true, true, fill_model<T>, set_options<T>, set_debug<T>, set_task<T>, set_plan<T>, launch_coop<T, WARPS>, robust};
 }
+// model-specialised lean instantiation (SpecTraits<Spec>, ps_types.cuh): compile-time topology and cost layout
+template <class T, int BLOCK>
+inline Variant make_spec_variant(const char* name) {
+  Variant v{name, sizeof(Constants<T>), offsetof(Constants<T>, p), sizeof(DevPlan<T>), BLOCK, false, true, fill_model_spec<T>, set_options_spec<T>,
+            set_debug_spec<T>, set_task_spec<T>, set_plan<T>, launch_rollout<T, BLOCK>, nullptr};
+  v.task_ok = task_matches_spec<T>;
+  return v;
+}
+#define PS_DECL_SPEC_VARIANT(N) const Variant* variant_spec_##N();
+PS_SPEC_LIST(PS_DECL_SPEC_VARIANT)
+#undef PS_DECL_SPEC_VARIANT
 const Variant* variant_tiny();
 const Variant* variant_planar();
 const Variant* variant_legged();

@@ -50,6 +50,7 @@ int mmo_get(void* hp, const char* f, double* out, int cap) {
   if (!std::strcmp(f, "nefc")) { out[0] = h->d.nefc; return 1; }
   if (!std::strcmp(f, "ncon")) { out[0] = h->d.ncon; return 1; }
   if (!std::strcmp(f, "solver_iter")) { out[0] = h->d.solver_iter; return 1; }
+  if (!std::strcmp(f, "dbg_line_evals")) { out[0] = (double)mm::g_dbg_line_evals; return 1; }
   if (!std::strcmp(f, "warnings")) { double s = 0; for (int i = 0; i < N_WARN; i++) s += h->d.warning[i]; out[0] = s; return 1; }
   if (!std::strcmp(f, "contact")) {  // [dist, pos3, frame9, dim, geom1, geom2] per contact
     int n = 0; for (auto& c : h->d.contact) { if (n + 16 > cap) break; out[n] = c.dist; copy(out + n + 1, c.pos, 3); copy(out + n + 4, c.frame, 9); out[n + 13] = c.dim; out[n + 14] = c.geom1; out[n + 15] = c.geom2; n += 16; }

@@ -77,5 +77,6 @@ double ray(const Model* m, const Data* d, const double pnt[3], const double vec[
            const unsigned char* geomgroup, int flg_static, int bodyexclude, int* geomid);
 int name2id(const Model* m, int objtype, const char* name);
 
+extern long long g_dbg_line_evals;
 }  // namespace mm
 #endif

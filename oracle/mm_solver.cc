@@ -119,8 +119,11 @@ static void gradientAndDirection(const Model* m, Data* d, Ctx& c) {
 }
 
 // cost and its first two derivatives along the search direction at step alpha
+// diagnostics (tools/solver_work_survey.py): line-search evaluations since process start; not thread-safe, single-thread use only
+long long g_dbg_line_evals = 0;
 static void evalLine(const Model* m, const Data* d, const Ctx& c, const double quadGauss[3], double alpha,
                      double* cost, double* d1, double* d2) {
+  g_dbg_line_evals++;
   double f = quadGauss[0] + alpha * quadGauss[1] + alpha * alpha * quadGauss[2];
   double g = quadGauss[1] + 2 * alpha * quadGauss[2];
   double h = 2 * quadGauss[2];

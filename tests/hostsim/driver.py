@@ -25,6 +25,34 @@ def build(force=False):
     return _LIB
 
 
+def build_spec(force=False):
+    """libhostsim_spec.so: the model-specialised lean instantiations under the defines of csrc/ps_variant_tiny_spec.cu"""
+    src = os.path.join(_HERE, "hostsim_spec.cc"); out = os.path.join(_HERE, "libhostsim_spec.so")
+    deps = [src] + [os.path.join(_CSRC, f) for f in os.listdir(_CSRC) if f.endswith((".cuh", ".h"))]
+    if not force and os.path.exists(out) and all(os.path.getmtime(out) >= os.path.getmtime(d) for d in deps):
+        return out
+    subprocess.run(["g++", "-std=c++17", "-O2", "-ffp-contract=off", "-fPIC", "-shared", "-x", "c++", src, "-o", out], check=True)
+    return out
+
+
+def rollout_spec(model, task, state, time, times, knots, interp, H, timestep, mocap=None):
+    """One rollout on a model-specialised instantiation (raises when no specialisation matches the model / task)."""
+    L = ctypes.CDLL(build_spec())
+    ns, nu, nr = model.nq + model.nv + model.na, model.nu, task.num_residual
+    state = np.ascontiguousarray(state, dtype=np.float64); times = np.ascontiguousarray(times, dtype=np.float64)
+    knots = np.ascontiguousarray(knots, dtype=np.float64).reshape(len(times), nu)
+    states = np.zeros((H, ns)); actions = np.zeros((H, nu)); residual = np.zeros((H, nr)); costs = np.zeros(H)
+    total = ctypes.c_double(0); flags = ctypes.c_int(0); variant = ctypes.create_string_buffer(1024)
+    mo = None if mocap is None else np.ascontiguousarray(mocap, dtype=np.float64)
+    rc = L.hs_rollout_spec(ctypes.byref(model.c_struct()), ctypes.byref(task), _p(state), _p(mo) if mo is not None else None,
+                           ctypes.c_double(time), _p(times), _p(knots), len(times), int(interp), int(H), ctypes.c_double(timestep),
+                           _p(states), _p(actions), _p(residual), _p(costs), ctypes.byref(total), ctypes.byref(flags), variant, 1024)
+    if rc != 0:
+        raise RuntimeError(f"hs_rollout_spec failed ({rc}): {variant.value.decode()}")
+    return dict(states=states, actions=actions, residual=residual, costs=costs, total=total.value, flags=flags.value,
+                variant=variant.value.decode())
+
+
 def build_planner_host(force=False):
     """libps_planner_host.so: the product's host planner classes (mujoco_mpc_b200/host/*.cc, unchanged) linked
     against hostengine.cc, the host-compiled stand-in of the engine ABI.  -Bsymbolic keeps its ps_* references

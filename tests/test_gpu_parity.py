@@ -125,7 +125,8 @@ def test_parity_quadruped_one_second_horizon(oracle_lib):
 
 
 @pytest.mark.parametrize("name,engine,expect", [
-    ("Cartpole", "warp", "tiny_coop"), ("Cartpole", "thread", "tiny"), ("Acrobot", "warp", "tiny_coop"),
+    ("Cartpole", "warp", "tiny_coop"), ("Cartpole", "thread", "tiny_Cartpole"), ("Cartpole", "dense", "tiny"), ("Acrobot", "warp", "tiny_coop"),
+    ("Acrobot", "thread", "tiny_Acrobot"), ("Acrobot", "dense", "tiny"), ("Particle", "thread", "tiny_Particle"), ("Particle", "dense", "tiny"),
     ("Walker", "warp", "planar_coop"), ("Walker", "thread", "planar"),
     ("Quadruped Flat", "warp", "legged_coop"), ("Quadruped Flat", "thread", "legged_sparse"), ("Quadruped Flat", "dense", "legged")])
 def test_parity_every_kernel_flavour(oracle_lib, name, engine, expect):
@@ -133,6 +134,23 @@ def test_parity_every_kernel_flavour(oracle_lib, name, engine, expect):
     from mujoco_mpc_b200 import task as T
     prep = (lambda m, t: T.quadruped_snapshot(m, t, mode="Quadruped", gait="Trot", time=0.37)) if name.startswith("Quadruped") else None
     run_case(name, N=160, interp=2, H=41, prep=prep, engine=engine, expect=expect)
+
+
+def test_model_specialised_kernel_falls_back_on_any_integer_difference(oracle_lib):
+    # the model-specialised lean kernels (csrc/ps_variant_tiny_spec.cu) are compiled for the registered tasks' integers;
+    # a cost specification or a model that differs in any of them must run on the generic lean kernel, same results
+    def other_norm(m, t):
+        t.norm[2] = 2; t.num_norm_parameter[2] = 1                      # velocity term: quadratic -> L2 with one parameter
+        npar = sum(int(t.num_norm_parameter[k]) for k in range(2))
+        for k in range(31, npar, -1):
+            t.norm_parameter[k] = t.norm_parameter[k - 1]
+        t.norm_parameter[npar] = 0.1
+    run_case("Cartpole", N=96, interp=2, H=41, prep=other_norm, expect="tiny")
+
+    def limited_pole(m, t):
+        m.v["jnt_limited"] = np.array([1, 1], dtype=np.int32); m.v["jnt_range"] = np.array([[-1.8, 1.8], [-0.3, 0.3]]); m._c = None
+    run_case("Cartpole", N=96, interp=2, H=41, prep=limited_pole, expect="tiny")
+    run_case("Cartpole", N=96, interp=2, H=41, expect="tiny_Cartpole")
 
 
 def test_first_iteration_zero_nominal(oracle_lib):

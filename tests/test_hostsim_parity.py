@@ -15,7 +15,7 @@ def hostsim_lib(oracle_lib):
     return driver.build()
 
 
-def check(name, H, prep=None, N=3, sigma=0.2, time=0.3, seed=0, coop=False):
+def check(name, H, prep=None, N=3, sigma=0.2, time=0.3, seed=0, coop=False, spec=None):
     m, t, s = registry.load(name)
     if prep:
         prep(m, t)
@@ -28,7 +28,11 @@ def check(name, H, prep=None, N=3, sigma=0.2, time=0.3, seed=0, coop=False):
     for i in range(N):
         ot = o.trajectory(i)
         _, kn = o.policy(2 + i)
-        h = driver.rollout(m, t, st, time, nt, kn, interp, H, s["timestep"], s["integrator"], coop=coop)
+        if spec:
+            h = driver.rollout_spec(m, t, st, time, nt, kn, interp, H, s["timestep"])
+            assert h["variant"] == spec
+        else:
+            h = driver.rollout(m, t, st, time, nt, kn, interp, H, s["timestep"], s["integrator"], coop=coop)
         assert h["flags"] == (1 if ot["failure"] else 0)
         if ot["failure"]:
             continue
@@ -40,6 +44,31 @@ def check(name, H, prep=None, N=3, sigma=0.2, time=0.3, seed=0, coop=False):
 @pytest.mark.parametrize("name,H", [("Particle", 51), ("Cartpole", 101), ("Acrobot", 101), ("Swimmer", 40), ("Walker", 60)])
 def test_kernel_source_matches_oracle(hostsim_lib, name, H):
     check(name, H)
+
+
+@pytest.mark.parametrize("name,H,sigma", [("Particle", 51, 0.2), ("Cartpole", 101, 0.2), ("Cartpole", 201, 1.0), ("Acrobot", 101, 0.2),
+                                          ("Particle", 101, 1.0)])
+def test_model_specialised_source_matches_oracle(hostsim_lib, name, H, sigma):
+    # csrc/ps_variant_tiny_spec.cu's instantiations (compile-time tables, bounded tree walks, split row storage);
+    # sigma = 1 drives the cart / the particle into their joint limits, i.e. through the constraint rows
+    check(name, H, N=4, sigma=sigma, spec="tiny_" + name)
+
+
+def test_model_specialisation_rejects_other_models(hostsim_lib):
+    m, t, s = registry.load("Cartpole")
+    m.v["jnt_limited"] = np.array([1, 1], dtype=np.int32); m._c = None
+    with pytest.raises(RuntimeError, match="differs from the Cartpole specialisation"):
+        driver.rollout_spec(m, t, registry.synthetic_state(m), 0.0, np.zeros(1), np.zeros((1, m.nu)), 0, 5, s["timestep"])
+    m, t, s = registry.load("Walker")
+    with pytest.raises(RuntimeError, match="sizes differ"):
+        driver.rollout_spec(m, t, registry.synthetic_state(m), 0.0, np.zeros(1), np.zeros((1, m.nu)), 0, 5, s["timestep"])
+
+
+def test_generated_spec_header_is_current():
+    import os, subprocess, sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    assert subprocess.run([sys.executable, os.path.join(root, "tools", "gen_spec_header.py"), "--check"]).returncode == 0, \
+        "csrc/ps_spec_generated.h is stale: run python tools/gen_spec_header.py"
 
 
 @pytest.mark.parametrize("mode,gait,angvel", [("Quadruped", "Trot", 0.0), ("Biped", "Trot", 0.0), ("Walk", "Canter", 0.5),
