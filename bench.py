@@ -132,39 +132,69 @@ def make_cases(workload, rank, world, weak=False):
     return cases
 
 
+def _cpu_planners(cases, cores):
+    """One CPU planner per task: the reference's OWN SamplingPlanner build (oracle/_ref/libmjpc_ref.so: mjpc/planners/sampling,
+    trajectory.cc, task.cc, tasks/*.cc compiled unmodified; kind "reference") where it travelled with the snapshot, else the
+    oracle's restatement of it (kind "port").  Both run the restated MuJoCo step below mj_step.  Returns (kind, [run(n)])."""
+    from oracle import pyoracle
+    pyoracle.build()
+    L = pyoracle.ref_lib()
+    have_ref = L is not None and hasattr(L, "refp_create") and os.environ.get("PS_CPU_ARM", "") != "port"
+    runs = []
+    for c in cases:
+        if have_ref:
+            from mujoco_mpc_b200 import registry, task as _task
+            from tests.common import model_mocap
+            r = pyoracle.RefPlanner(c["model"], registry._TASK_ID_NAME.get(c["name"], c["name"]))
+            mocap = model_mocap(c["model"])
+            if c["name"] == "Quadruped Flat":       # a trotting robot, as the GPU arm's snapshot
+                par = r.task_spec()["parameters"].copy()
+                par[_task.parameter_index(c["model"], "select_Gait")] = _task._as_double(_task.QUAD_GAITS["Trot"])
+                r.task_set(mode=0, parameters=par)
+                _, mocap = r.task_transition(c["state"], mocap, 0.0)
+            cap = int(L.refp_max_trajectory())      # kMaxTrajectory: the reference rolls at most 128 samples per OptimizePolicy
+
+            def run(n, r=r, c=c, mocap=mocap, cap=cap):
+                done = 0
+                while done < n:                     # a batch beyond kMaxTrajectory takes several planning iterations
+                    k = min(cap, n - done)
+                    r.configure(c["P"], c["interp"], c["sigma"], 0.0, k)
+                    r.set_state(c["state"], 0.0, mocap=mocap); r.set_policy(c["times"], c["knots"], c["interp"])
+                    r.optimize(k, c["H"], None, nthread=cores); done += k
+            runs.append((run, r))
+        else:
+            o = pyoracle.Oracle(c["model"], c["task"]); o.configure(c["P"], c["interp"], c["sigma"])
+
+            def run(n, o=o, c=c):
+                z = np.random.default_rng(1).standard_normal((n, c["P"], c["model"].nu))
+                o.set_state(c["state"], 0.0); o.set_policy(c["times"], c["knots"], c["interp"]); o.optimize(n, c["H"], z, nthread=cores)
+            runs.append((run, o))
+    return ("reference" if have_ref else "port"), runs
+
+
 def cpu_arm(cases, cores, budget_s, steps=None, warmup=0):
     """The CPU planner on `cores` host threads over the SAME fraction f of every task's samples (so the tasks weigh in
     as on the GPU), f sized so that one step is about `budget_s` of wall time.  Returns (sample-steps/s, s per step,
-    description, per-task rates)."""
-    from oracle import pyoracle
-    pyoracle.build()
-    runs = []
-    for c in cases:
-        o = pyoracle.Oracle(c["model"], c["task"]); o.configure(c["P"], c["interp"], c["sigma"])
-        runs.append([o, c, 0, None, 0.0])
-
-    def one(o, c, n, z):
-        o.set_state(c["state"], 0.0); o.set_policy(c["times"], c["knots"], c["interp"]); o.optimize(n, c["H"], z, nthread=cores)
-
+    description, per-task rates, kind)."""
+    kind, planners = _cpu_planners(cases, cores)
+    runs = [[planners[i][0], c, 0, None, 0.0] for i, c in enumerate(cases)]
     # calibration: per-task rate on 8 rollouts per thread
     full_s = 0.0
     for r in runs:
-        o, c = r[0], r[1]
+        c = r[1]
         n0 = min(c["N_total"], max(8 * cores, 128))
-        z = np.random.default_rng(1).standard_normal((n0, c["P"], c["model"].nu))
-        one(o, c, n0, z)
-        t0 = time.perf_counter(); one(o, c, n0, z); dt = time.perf_counter() - t0
+        r[0](n0)
+        t0 = time.perf_counter(); r[0](n0); dt = time.perf_counter() - t0
         full_s += c["N_total"] / n0 * dt
     f = min(1.0, budget_s / max(full_s, 1e-9))
     f = max(f, max(min(1.0, max(8 * cores, 128) / c["N_total"]) for c in cases))     # >= 8 rollouts per thread on every task
     for r in runs:
         c = r[1]
         r[2] = max(1, min(c["N_total"], int(round(f * c["N_total"]))))
-        r[3] = np.random.default_rng(1).standard_normal((r[2], c["P"], c["model"].nu))
 
     def step():
         for r in runs:
-            t0 = time.perf_counter(); one(r[0], r[1], r[2], r[3]); r[4] += time.perf_counter() - t0
+            t0 = time.perf_counter(); r[0](r[2]); r[4] += time.perf_counter() - t0
     for _ in range(warmup):
         step()
     for r in runs:
@@ -175,9 +205,16 @@ def cpu_arm(cases, cores, budget_s, steps=None, warmup=0):
     dt = (time.perf_counter() - t0) / n_steps
     units = sum(r[2] * (r[1]["H"] - 1) for r in runs)
     per_task = {r[1]["name"]: r[2] * (r[1]["H"] - 1) * n_steps / r[4] for r in runs}
+    how = "the reference's own SamplingPlanner + ThreadPool, kMaxTrajectory = 128 samples per OptimizePolicy" if kind == "reference" else \
+        "persistent thread pool, dynamic scheduling"
     sample = f"{n_steps} steps of " + "; ".join(f"{r[1]['name']} {r[2]} of {r[1]['N_total']} samples x {r[1]['H'] - 1} steps" for r in runs) + \
-        f" (fraction {f:.4g} of every task, persistent {cores}-thread pool, dynamic scheduling)"
-    return units / dt, dt, sample, per_task
+        f" (fraction {f:.4g} of every task, {cores} threads, {how})"
+    return units / dt, dt, sample, per_task, kind
+
+
+CPU_NOTE = {"reference": "the reference's own planner / rollout / cost / residual code (compiled unmodified into oracle/_ref) over the restated "
+                         "MuJoCo 3.1.4 step: MuJoCo itself is absent, so the physics below mj_step is the oracle's (unpinned)",
+            "port": "reference planner logic restated over the restated MuJoCo 3.1.4 step (physics unpinned); not the reference binary"}
 
 
 def run_reference(args, rank, world):
@@ -186,13 +223,12 @@ def run_reference(args, rank, world):
         return
     cases = make_cases(args.workload, 0, 1)
     cores = len(os.sched_getaffinity(0))
-    v, dt, sample, per_task = cpu_arm(cases, cores, budget_s=1.5, steps=args.steps, warmup=args.warmup)
+    v, dt, sample, per_task, kind = cpu_arm(cases, cores, budget_s=1.5, steps=args.steps, warmup=args.warmup)
     line = {"impl": "reference", "metric": METRIC, "value": v, "unit": "sample-steps/s", "n_gpus": args.gpus, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": dt * 1e3, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
             "dtype": "f64", "data": "synthetic", "config": {"workload": args.workload},
             "tasks": [{"name": k, "value": x, "unit": "sample-steps/s"} for k, x in per_task.items()],
-            "cpu_baseline": {"value": v, "unit": "sample-steps/s", "cores": cores, "kind": "port", "sample": sample,
-                             "note": "reference planner logic over the restated MuJoCo 3.1.4 step (physics unpinned); not the reference binary"},
+            "cpu_baseline": {"value": v, "unit": "sample-steps/s", "cores": cores, "kind": kind, "sample": sample, "note": CPU_NOTE[kind]},
             "e2e": {"value": v, "unit": "sample-steps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
     print(json.dumps(line))
 
@@ -377,9 +413,14 @@ def main():
                              "traffic_gbs": (traffic / (kern_ms[dom][1] * 1e-3) / 1e9) if traffic else None}}
         if not args.no_cpu_baseline and world == 1:
             cores = len(os.sched_getaffinity(0))
-            v, dt, sample, per_task = cpu_arm(make_cases(args.workload, 0, 1), cores, budget_s=2.0)
-            line["cpu_baseline"] = {"value": v, "unit": "sample-steps/s", "cores": cores, "kind": "port", "sample": sample,
-                                    "per_task": per_task}
+            v, dt, sample, per_task, kind = cpu_arm(make_cases(args.workload, 0, 1), cores, budget_s=2.0)
+            line["cpu_baseline"] = {"value": v, "unit": "sample-steps/s", "cores": cores, "kind": kind, "sample": sample,
+                                    "per_task": per_task, "note": CPU_NOTE[kind]}
+            if kind == "reference":      # the restated planner (one batch, dynamic scheduling, no 128-sample cap) beside it, for scale
+                os.environ["PS_CPU_ARM"] = "port"
+                v2, _, sample2, per_task2, _ = cpu_arm(make_cases(args.workload, 0, 1), cores, budget_s=1.0)
+                os.environ.pop("PS_CPU_ARM", None)
+                line["cpu_baseline"]["port"] = {"value": v2, "per_task": per_task2, "sample": sample2, "note": CPU_NOTE["port"]}
         print(json.dumps(line))
     for e in engines:
         e.close()

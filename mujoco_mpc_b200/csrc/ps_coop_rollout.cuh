@@ -276,8 +276,11 @@ coop_robust_kernel(const Constants<T>* __restrict__ gconst, const double* __rest
 // the cooperative engine, SIMD across rollouts.  Its working set sits in local memory, so it needs
 // tens of thousands of rollouts in flight to hide that latency -- the large-batch engine, where the
 // warp-per-rollout kernel above is the small-batch (latency) engine.
+#ifndef PS_SPARSE_RESIDENT
+#define PS_SPARSE_RESIDENT 512          // threads the register cap keeps resident per SM
+#endif
 template <class T, int BLOCK, bool WB>
-__global__ void __launch_bounds__(BLOCK, 512 / BLOCK)
+__global__ void __launch_bounds__(BLOCK, PS_SPARSE_RESIDENT / BLOCK)
 sparse_rollout_kernel(const Constants<T>* __restrict__ gconst, const double* __restrict__ knots, int stride, int first, int n,
                       long long sample_offset, double* __restrict__ returns, unsigned char* __restrict__ failure,
                       MinLoc* __restrict__ block_min, Writeback wb) {

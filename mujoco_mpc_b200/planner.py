@@ -151,6 +151,11 @@ class CudaSamplingPlanner:
     def improvement(self):
         return self.L.psp_improvement(self.h)
 
+    def engine_ptr(self):
+        """PsEngine* behind the host class (returns of the whole batch, kernel timers ...)"""
+        self.L.psp_engine.restype = ctypes.c_void_p
+        return self.L.psp_engine(self.h)
+
     def NumParameters(self):
         return self.L.psp_num_parameters(self.h)
 

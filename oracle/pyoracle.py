@@ -189,3 +189,131 @@ class Oracle:
         ret = ctypes.c_double(); fail = ctypes.c_int()
         self.L.mmo_get_trajectory(self.h, i, _p(st), _p(ac), _p(tm), _p(rs), _p(cs), _p(tr), ctypes.byref(ret), ctypes.byref(fail))
         return dict(states=st, actions=ac, times=tm, residual=rs, costs=cs, trace=tr, total_return=ret.value, failure=bool(fail.value))
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+# The reference's OWN planner / rollout / cost / residual code (oracle/_ref/libmjpc_ref.so: mjpc/planners/sampling/*.cc,
+# trajectory.cc, task.cc, utilities.cc, states/state.cc, threadpool.cc and the six tasks/*/*.cc compiled unmodified; the
+# physics below mj_step is the restated step above).  Present only where /root/reference was available at build time.
+class RefPlanner:
+    def __init__(self, model, task_name):
+        L = ref_lib()
+        if L is None or not hasattr(L, "refp_create"):
+            raise RuntimeError("oracle/_ref/libmjpc_ref.so with the reference planner is not built (needs /root/reference)")
+        L.refp_create.restype = ctypes.c_void_p
+        L.refp_improvement.restype = ctypes.c_double
+        L.refp_task_residual.restype = ctypes.c_double
+        self.L, self.model = L, model
+        self._keep = model.c_struct()                      # the PsModel must outlive the mjModel view
+        self.h = ctypes.c_void_p(L.refp_create(ctypes.byref(self._keep), task_name.encode()))
+        if not self.h:
+            raise RuntimeError(f"reference task {task_name!r} unknown")
+        self.ns = model.nq + model.nv + model.na
+        nr, nt, ntr, npar = ctypes.c_int(), ctypes.c_int(), ctypes.c_int(), ctypes.c_int()
+        L.refp_task_dims(self.h, ctypes.byref(nr), ctypes.byref(nt), ctypes.byref(ntr), ctypes.byref(npar))
+        self.num_residual, self.num_term, self.num_trace, self.num_parameters = nr.value, nt.value, ntr.value, npar.value
+
+    def __del__(self):
+        try:
+            self.L.refp_destroy(self.h)
+        except Exception:
+            pass
+
+    @staticmethod
+    def zero_warmstart_per_rollout(on):
+        """test-harness switch (ref_glue.cc): clear qacc_warmstart at the first step of every rollout, i.e. the engine's
+        semantics; off = the reference's (the worker's mjData keeps the previous rollout's)"""
+        ref_lib().ref_set_zero_warmstart_on_rewind(int(bool(on)))
+
+    def task_spec(self):
+        nt = self.num_term
+        dims = (ctypes.c_int * nt)(); norm = (ctypes.c_int * nt)(); npar = (ctypes.c_int * nt)()
+        w = np.zeros(nt); prm = np.zeros(4 * nt + 4); risk = ctypes.c_double(); par = np.zeros(max(self.num_parameters, 1))
+        self.L.refp_task_spec(self.h, dims, norm, npar, _p(w), _p(prm), ctypes.byref(risk), _p(par))
+        return dict(dim_norm_residual=list(dims), norm=list(norm), num_norm_parameter=list(npar), weight=w, norm_parameter=prm[:sum(npar)],
+                    risk=risk.value, parameters=par[:self.num_parameters])
+
+    def task_set(self, mode=-1, parameters=None, weight=None):
+        p = _arr(parameters) if parameters is not None else None; w = _arr(weight) if weight is not None else None
+        self.L.refp_task_set(self.h, int(mode), _p(p), 0 if p is None else p.size, _p(w), 0 if w is None else w.size)
+
+    def task_transition(self, state, mocap, time):
+        s = _arr(state); mo = _arr(mocap).copy() if mocap is not None else None
+        mode = self.L.refp_task_transition(self.h, _p(s), _p(mo), ctypes.c_double(time))
+        return mode, mo
+
+    def residual(self, state, ctrl, mocap, time):
+        s = _arr(state); c = _arr(ctrl); mo = _arr(mocap) if mocap is not None else None
+        r = np.zeros(self.num_residual); t = np.zeros(self.num_term)
+        cost = self.L.refp_task_residual(self.h, _p(s), _p(c), _p(mo), ctypes.c_double(time), _p(r), _p(t))
+        return r, t, cost
+
+    def configure(self, num_spline_points, interpolation, sigma0, sigma1=0.0, num_trajectory=10, sliding_plan=0):
+        self.P = num_spline_points
+        self.L.refp_configure(self.h, int(num_spline_points), int(interpolation), ctypes.c_double(sigma0), ctypes.c_double(sigma1),
+                              int(num_trajectory), int(sliding_plan))
+
+    def set_state(self, state, time, mocap=None, userdata=None):
+        s = _arr(state); mo = _arr(mocap) if mocap is not None else None; ud = _arr(userdata) if userdata is not None else None
+        self.L.refp_set_state(self.h, _p(s), _p(mo), _p(ud), ctypes.c_double(time))
+
+    def set_policy(self, times, knots, interp):
+        t = _arr(times); k = _arr(knots)
+        self.L.refp_set_policy(self.h, _p(t), _p(k), len(t), int(interp))
+
+    def optimize(self, N, H, z=None, use_std2=None, nthread=1):
+        zz = _arr(z) if z is not None else None
+        u = np.ascontiguousarray(use_std2, dtype=np.uint8) if use_std2 is not None else None
+        self.N, self.H = N, H
+        w = self.L.refp_optimize(self.h, int(N), int(H), _p(zz), u.ctypes.data_as(ctypes.c_char_p) if u is not None else None, int(nthread))
+        if w < 0 and N > self.L.refp_max_trajectory():
+            raise ValueError(f"the reference planner rolls at most kMaxTrajectory = {self.L.refp_max_trajectory()} samples")
+        return w
+
+    def returns(self):
+        r = np.zeros(self.N); f = np.zeros(self.N, dtype=np.uint8)
+        self.L.refp_get_returns(self.h, self.N, _p(r), f.ctypes.data_as(ctypes.c_char_p)); return r, f
+
+    def trajectory(self, i):
+        H, m = self.H, self.model
+        st = np.zeros((H, self.ns)); ac = np.zeros((H, m.nu)); tm = np.zeros(H)
+        rs = np.zeros((H, self.num_residual)); cs = np.zeros(H); tr = np.zeros((H, max(3 * self.num_trace, 1)))
+        ret = ctypes.c_double(); fail = ctypes.c_int()
+        self.L.refp_get_trajectory(self.h, int(i), _p(st), _p(ac), _p(tm), _p(rs), _p(cs), _p(tr), ctypes.byref(ret), ctypes.byref(fail))
+        return dict(states=st, actions=ac, times=tm, residual=rs, costs=cs, trace=tr[:, :3 * self.num_trace], total_return=ret.value,
+                    failure=bool(fail.value))
+
+    def policy(self, which=0):
+        nu = self.model.nu
+        t = np.zeros(600); k = np.zeros(600 * max(nu, 1))
+        P = self.L.refp_get_policy(self.h, int(which), _p(t), _p(k))
+        return t[:P].copy(), k[:P * nu].reshape(P, nu).copy()
+
+    def action(self, t, use_previous=False):
+        out = np.zeros(max(self.model.nu, 1))
+        self.L.refp_action(self.h, ctypes.c_double(t), int(use_previous), _p(out)); return out[:self.model.nu]
+
+    def improvement(self):
+        return self.L.refp_improvement(self.h)
+
+    def quadruped_state(self):
+        """QuadrupedFlat::ResidualFn's Transition-managed state in the PsTask.aux layout (task.py A_MODE .. A_ORIENTATION + 4)"""
+        aux = np.zeros(17)
+        if self.L.refp_quadruped_state(self.h, _p(aux)) != 0:
+            raise RuntimeError("not the quadruped task")
+        return aux
+
+    def export_task_state(self, task):
+        """copy the reference task's current parameters / weights (and the quadruped's residual state) into a PsTask"""
+        spec = self.task_spec()
+        for k, v in enumerate(spec["parameters"]):
+            task.parameters[k] = float(v)
+        for k, v in enumerate(spec["weight"]):
+            task.weight[k] = float(v)
+        try:
+            aux = self.quadruped_state()
+            for k in range(17):
+                task.aux[k] = float(aux[k])
+        except RuntimeError:
+            pass
+        return task
