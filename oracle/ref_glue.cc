@@ -18,7 +18,7 @@ mjfGeneric mjcb_control = nullptr;
 
 namespace {
 struct DataBox { mjData view; mm::Data d; const mjModel* m; };
-struct ModelBox { mjModel view; std::vector<double> key_mpos, key_mquat; };
+struct ModelBox { mjModel view; std::vector<double> key_mpos, key_mquat; std::vector<std::vector<mjtByte>> bytes; };
 
 // Test-harness switch: the reference's worker mjData keeps qacc_warmstart from whatever rollout it ran last
 // (planners/sampling/planner.cc:374), the engine under test starts every rollout from a zero warm start (DESIGN.md,
@@ -58,22 +58,8 @@ extern "C" void ref_set_zero_warmstart_on_rewind(int on) { g_zero_warmstart_on_r
 extern "C" mjModel* ref_make_model(const PsModel* p) {
   ModelBox* b = new ModelBox();
   mjModel& m = b->view; std::memset(&m, 0, sizeof(m));
-#define C(f) m.f = const_cast<std::remove_const_t<std::remove_pointer_t<decltype(p->f)>>*>(p->f);
-#define CI(f) m.f = p->f;
-  CI(nq) CI(nv) CI(nu) CI(na) CI(nbody) CI(njnt) CI(ngeom) CI(nsite) CI(nmocap) CI(nsensor) CI(nsensordata) CI(nuser_sensor) CI(nnumeric)
-  CI(nnumericdata) CI(ntext) CI(ntextdata) CI(nkey) CI(nuserdata) CI(nnames)
-  C(body_mocapid) C(jnt_type) C(jnt_qposadr) C(jnt_dofadr) C(sensor_type) C(sensor_objtype) C(sensor_objid) C(sensor_dim) C(sensor_adr)
-  C(numeric_adr) C(numeric_size) C(text_adr) C(text_size) C(name_bodyadr) C(name_jntadr) C(name_geomadr) C(name_siteadr)
-  C(name_actuatoradr) C(name_sensoradr) C(name_numericadr) C(name_textadr) C(name_keyadr)
-  C(actuator_ctrlrange) C(sensor_user) C(numeric_data) C(key_qpos) C(key_qvel) C(key_act) C(key_ctrl) C(qpos0) C(text_data) C(names)
-#undef C
-#undef CI
-  m.opt.timestep = p->opt_timestep; m.opt.impratio = p->opt_impratio; m.opt.tolerance = p->opt_tolerance; m.opt.ls_tolerance = p->opt_ls_tolerance;
-  m.opt.density = p->opt_density; m.opt.viscosity = p->opt_viscosity; m.opt.integrator = p->opt_integrator; m.opt.cone = p->opt_cone;
-  m.opt.solver = p->opt_solver; m.opt.iterations = p->opt_iterations; m.opt.ls_iterations = p->opt_ls_iterations;
-  m.opt.disableflags = p->opt_disableflags; m.opt.enableflags = p->opt_enableflags;
-  for (int k = 0; k < 3; k++) { m.opt.gravity[k] = p->opt_gravity[k]; m.opt.wind[k] = p->opt_wind[k]; }
-  m.stat.meaninertia = p->stat_meaninertia;
+  auto bytes = [b](const int* v, size_t n) { b->bytes.emplace_back(n ? n : 1); for (size_t i = 0; i < n; i++) b->bytes.back()[i] = (mjtByte)v[i]; return b->bytes.back().data(); };
+#include "ref_model_fill.inc"
   // keyframe mocap poses are not part of PsModel: the model's own body poses (what the compiler stores by default)
   b->key_mpos.assign((size_t)3 * p->nmocap * (p->nkey > 0 ? p->nkey : 1), 0.0); b->key_mquat.assign((size_t)4 * p->nmocap * (p->nkey > 0 ? p->nkey : 1), 0.0);
   for (int k = 0; k < (p->nkey > 0 ? p->nkey : 1); k++)

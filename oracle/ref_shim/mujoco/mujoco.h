@@ -71,15 +71,9 @@ struct mjStatistic { mjtNum meaninertia; };
 struct mjWarningStat { int lastinfo, number; };
 struct PsModel_;
 struct mjModel_ {
-  int nq, nv, nu, na, nbody, njnt, ngeom, nsite, nmocap, nsensor, nsensordata, nuser_sensor, nnumeric, nnumericdata, ntext,
-      ntextdata, nkey, nuserdata, nnames;
   mjOption opt; mjStatistic stat;
-  int *body_mocapid, *jnt_type, *jnt_qposadr, *jnt_dofadr, *sensor_type, *sensor_objtype, *sensor_objid, *sensor_dim,
-      *sensor_adr, *numeric_adr, *numeric_size, *text_adr, *text_size, *name_bodyadr, *name_jntadr, *name_geomadr, *name_siteadr,
-      *name_actuatoradr, *name_sensoradr, *name_numericadr, *name_textadr, *name_keyadr;
-  mjtNum *actuator_ctrlrange, *sensor_user, *numeric_data, *key_qpos, *key_qvel, *key_act, *key_ctrl, *key_mpos, *key_mquat,
-      *qpos0;
-  char *text_data, *names;
+#include "mjmodel_fields.inc"          // every array / size PsModel mirrors, under mjModel's names and types
+  mjtNum *key_mpos, *key_mquat;
   const PsModel_* ps;          // shim: the flat model this view was filled from (what the oracle physics reads)
 };
 typedef struct mjModel_ mjModel;
