@@ -292,6 +292,8 @@ def main():
 
     # end-to-end arm: the drop-in host planner (CudaSamplingPlanner), host buffers in and out
     from mujoco_mpc_b200.planner import CudaSamplingPlanner
+    from mujoco_mpc_b200 import engine as _eng
+    elib = _eng.lib()
     planners = []
     for c in cases:
         pl = CudaSamplingPlanner(c["model"], c["task"], device=local)
@@ -301,13 +303,18 @@ def main():
             pl.SetShardingNative(rank, world, dist)       # ncclAllGather inside the engine, no host bounce
         planners.append(pl)
     e2e_time = [0.0]
+    e2e_dev_ms = [0.0]                 # device time of the K1 + K2 + K3 launches inside the end-to-end steps
 
     def e2e_step():
         """public API: SetState (host state) -> OptimizePolicy (resample, H2D, K1-K3, D2H winner) -> ActionFromPolicy"""
+        import ctypes
         for pl, c in zip(planners, cases):
             pl.SetState(c["state"], e2e_time[0])
             pl.OptimizePolicy(c["H"])
             pl.ActionFromPolicy(e2e_time[0])
+            a, b, d = ctypes.c_float(), ctypes.c_float(), ctypes.c_float()
+            if elib.ps_last_kernel_ms(ctypes.c_void_p(pl.engine_ptr()), ctypes.byref(a), ctypes.byref(b), ctypes.byref(d)) == 0:
+                e2e_dev_ms[0] += a.value + b.value + d.value
         e2e_time[0] += 0.01
 
     def barrier():
@@ -342,10 +349,12 @@ def main():
     # end-to-end through the host-buffer API
     for _ in range(3):
         e2e_step()
+    e2e_dev_ms[0] = 0.0
     barrier(); t0 = time.perf_counter()
     for _ in range(args.steps):
         e2e_step()
     barrier(); e2e_s = (time.perf_counter() - t0) / args.steps
+    e2e_device_ms = e2e_dev_ms[0] / args.steps
     # the clocks sampler spans both timed regions (device-timed and end-to-end); if they were shorter than ~20
     # nvidia-smi queries, keep stepping until it has seen the GPU under this load (every rank runs the same number
     # of extra steps: each sharded step holds a collective)
@@ -402,7 +411,10 @@ def main():
                 "tasks": tasks,
                 "planning_iteration_latency_ms": {"mean": ms_step, "p50": float(np.percentile(lat, 50)), "p95": float(np.percentile(lat, 95))},
                 "e2e": {"value": e2e_value, "unit": "sample-steps/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
-                        "latency_ms": e2e_s * 1e3},
+                        "latency_ms": e2e_s * 1e3, "device_ms": e2e_device_ms, "host_overhead_ms": e2e_s * 1e3 - e2e_device_ms,
+                        "note": "closed loop: every step re-plans from the previous winner, so its rollouts (and the contact load of the quadruped's) "
+                                "differ from the fixed nominal of the device-timed steps; device_ms is the K1+K2+K3 time of THESE steps, "
+                                "host_overhead_ms what the host-buffer API adds on top"},
                 "gpu_launches": int(launches), "clocks": clocks,
                 "roofline": {"bound": "fp64", "kernel": f"{engines[dom].variant()} rollout kernel ({dc['name']})", "achieved": achieved, "peak": peak, "unit": "TFLOP/s",
                              "frac": (achieved / peak) if achieved else None,
