@@ -10,7 +10,7 @@ CSRC = os.path.join(HERE, "csrc")
 OUT = os.path.join(HERE, "libps_engine.so")
 UNITS = ["ps_engine.cu", "ps_variant_tiny.cu", "ps_variant_planar.cu", "ps_variant_legged.cu",
          "ps_variant_tiny_coop.cu", "ps_variant_planar_coop.cu", "ps_variant_legged_coop.cu", "ps_variant_planar_sparse.cu",
-         "ps_variant_legged_sparse.cu", "ps_variant_robust.cu", "ps_noalloc.cu", "ps_variant_tiny_spec.cu"]
+         "ps_variant_legged_sparse.cu", "ps_variant_robust.cu", "ps_noalloc.cu", "ps_variant_tiny_spec.cu", "ps_variant_legged_xl.cu"]
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 # -fmad=false: FP64 multiply-adds are NOT contracted, so the device arithmetic is operation-for-operation
 # the IEEE sequence the oracle executes (-ffp-contract=off).  Contact-rich rollouts amplify rounding

@@ -56,9 +56,23 @@ typedef Lanes1 Lanes;
 #endif
 
 // parallel-for over [0, n): item i is handled by lane i mod width
-#define CO_FOR(i, n) for (int i = L.lane; i < (n); i += L.width)
+// PS_COMPACT_LOOPS (thread-per-rollout instantiation, ps_variant_legged_sparse.cu): the phase loops are NOT unrolled.  That
+// kernel is bound by instruction delivery (ncu: GPC instruction-cache requests at 57 % of peak, `no_instruction` 8 cycles per
+// issue -- its ~500 KB of code streams through the SMs' instruction caches), so a smaller loop body beats the ILP of an unrolled one.
+#ifdef PS_COMPACT_LOOPS
+#define PS_LOOP_PRAGMA _Pragma("unroll 1")
+#else
+#define PS_LOOP_PRAGMA
+#endif
+// PS_LOOP2: the plain loops inside the phases (row / dof / contact loops); compacted only at PS_COMPACT_LOOPS >= 2
+#if defined(PS_COMPACT_LOOPS) && PS_COMPACT_LOOPS >= 2
+#define PS_LOOP2 _Pragma("unroll 1")
+#else
+#define PS_LOOP2
+#endif
+#define CO_FOR(i, n) PS_LOOP_PRAGMA for (int i = L.lane; i < (n); i += L.width)
 // all lanes walk [0, n) in rounds of `width`; lanes past the end still take part in collectives
-#define CO_ROUNDS(base, n) for (int base = 0; base < (n); base += L.width)
+#define CO_ROUNDS(base, n) PS_LOOP_PRAGMA for (int base = 0; base < (n); base += L.width)
 
 // ---------------------------------------------------------------- working set of one rollout
 struct CoopContact {

@@ -17,7 +17,7 @@ PS_HD double co_row_dot(const DevModel<T>& m, const CoopData<T>& d, int r, const
   const double* J = d.jpool + d.efc_jrow[r] * T::NCH; const signed char* dof = d.con_dof + id * T::NCH;
   const int n = d.contact[id].ndof;
   double s = 0;
-  for (int k = 0; k < n; k++) s += J[k] * vec[dof[k]];
+  PS_LOOP2 for (int k = 0; k < n; k++) s += J[k] * vec[dof[k]];
   return s;
 }
 
@@ -54,7 +54,7 @@ PS_NI void co_detect_contacts(const LT& L, const DevModel<T>& m, CoopData<T>& d)
         }
       }
       int total; const int off = L.scan(n, &total);
-      for (int k = 0; k < n; k++) {
+      PS_LOOP2 for (int k = 0; k < n; k++) {
         const int idx = ncon + off + k;
         if (idx >= T::MAXCON) break;
         CoopContact& con = d.contact[idx];
@@ -110,12 +110,12 @@ PS_NI void co_contact_rows(const DevModel<T>& m, CoopData<T>& d, int ci) { PS_AS
       if (i2 == i) i2 = m.dof_parentid[i2];
     }
     if (n > NCH) { d.warning |= WARN_CAPACITY; n = NCH; }       // cannot happen when NCH covers two chains
-    for (int i = 0; i < m.nv; i++) slot[i] = -1;
-    for (int k = 0; k < n; k++) { dof[k] = tmp[n - 1 - k]; slot[dof[k]] = (signed char)k; }
+    PS_LOOP2 for (int i = 0; i < m.nv; i++) slot[i] = -1;
+    PS_LOOP2 for (int k = 0; k < n; k++) { dof[k] = tmp[n - 1 - k]; slot[dof[k]] = (signed char)k; }
   }
   con.ndof = (short)n;
   double off1[3], off2[3];
-  for (int k = 0; k < 3; k++) {
+  PS_LOOP2 for (int k = 0; k < 3; k++) {
     off1[k] = w1 > 0 ? con.pos[k] - d.subtree_com[3 * m.body_rootid[w1] + k] : 0.0;
     off2[k] = w2 > 0 ? con.pos[k] - d.subtree_com[3 * m.body_rootid[w2] + k] : 0.0;
   }
@@ -124,12 +124,12 @@ PS_NI void co_contact_rows(const DevModel<T>& m, CoopData<T>& d, int ci) { PS_AS
   {
     int i1 = w1 > 0 ? m.body_dofadr[w1] + m.body_dofnum[w1] - 1 : -1;
     int i2 = w2 > 0 ? m.body_dofadr[w2] + m.body_dofnum[w2] - 1 : -1;
-    for (int k = n - 1; k >= 0; k--) {
+    PS_LOOP2 for (int k = n - 1; k >= 0; k--) {
       const int i = dof[k]; const double* c = d.cdof + 6 * i;
       double a[3] = {0, 0, 0}, b[3] = {0, 0, 0}, ar[3] = {0, 0, 0}, br[3] = {0, 0, 0};
-      if (i1 == i) { double t[3]; cross3(t, c, off1); for (int x = 0; x < 3; x++) { a[x] = c[3 + x] + t[x]; ar[x] = c[x]; } i1 = m.dof_parentid[i1]; }
-      if (i2 == i) { double t[3]; cross3(t, c, off2); for (int x = 0; x < 3; x++) { b[x] = c[3 + x] + t[x]; br[x] = c[x]; } i2 = m.dof_parentid[i2]; }
-      for (int r = 0; r < dim; r++) {
+      if (i1 == i) { double t[3]; cross3(t, c, off1); PS_LOOP2 for (int x = 0; x < 3; x++) { a[x] = c[3 + x] + t[x]; ar[x] = c[x]; } i1 = m.dof_parentid[i1]; }
+      if (i2 == i) { double t[3]; cross3(t, c, off2); PS_LOOP2 for (int x = 0; x < 3; x++) { b[x] = c[3 + x] + t[x]; br[x] = c[x]; } i2 = m.dof_parentid[i2]; }
+      PS_LOOP2 for (int r = 0; r < dim; r++) {
         const double* f = con.frame + 3 * (r % 3);
         Jc[r * NCH + k] = r < 3 ? f[0] * (b[0] - a[0]) + f[1] * (b[1] - a[1]) + f[2] * (b[2] - a[2])
                                 : f[0] * (br[0] - ar[0]) + f[1] * (br[1] - ar[1]) + f[2] * (br[2] - ar[2]);
@@ -140,20 +140,20 @@ PS_NI void co_contact_rows(const DevModel<T>& m, CoopData<T>& d, int ci) { PS_AS
   const double rot = m.body_invweight0[2 * b1 + 1] + m.body_invweight0[2 * b2 + 1];
   double* R = d.efc_R + adr;
   const int nrow = con.nrow;
-  for (int q = 0; q < nrow; q++) {
+  PS_LOOP2 for (int q = 0; q < nrow; q++) {
     const int row = adr + q;
     double* J = d.jpool + (con.jadr + q) * NCH;
     double pos = con.dist, margin = con.includemargin, diag; bool zk = false; int type;
-    if (dim == 1) { type = EFC_CONTACT_FRICTIONLESS; diag = tran; for (int k = 0; k < n; k++) J[k] = Jc[k]; }
+    if (dim == 1) { type = EFC_CONTACT_FRICTIONLESS; diag = tran; PS_LOOP2 for (int k = 0; k < n; k++) J[k] = Jc[k]; }
     else if (m.cone == CONE_ELLIPTIC) {
       type = EFC_CONTACT_ELLIPTIC; diag = q < 3 ? tran : rot;
       if (q > 0) { pos = 0; margin = 0; zk = true; }
-      for (int k = 0; k < n; k++) J[k] = Jc[q * NCH + k];
+      PS_LOOP2 for (int k = 0; k < n; k++) J[k] = Jc[q * NCH + k];
     } else {
       type = EFC_CONTACT_PYRAMIDAL;
       const int r = 1 + q / 2; const double sg = (q & 1) ? -1.0 : 1.0, mu = con.friction[r - 1];
       diag = tran + mu * mu * (r - 1 < 2 ? tran : rot);
-      for (int k = 0; k < n; k++) J[k] = Jc[k] + sg * mu * Jc[r * NCH + k];
+      PS_LOOP2 for (int k = 0; k < n; k++) J[k] = Jc[k] + sg * mu * Jc[r * NCH + k];
     }
     d.efc_type[row] = (unsigned char)type; d.efc_id[row] = (short)ci; d.efc_jrow[row] = (short)(con.jadr + q); d.efc_state[row] = 0;
     co_row_params(m.timestep, m.disableflags, con.solref, con.solimp, pos, margin, diag, zk, R + q, d.efc_force + row, d.efc_aref + row);
@@ -162,15 +162,15 @@ PS_NI void co_contact_rows(const DevModel<T>& m, CoopData<T>& d, int ci) { PS_AS
     if (m.cone == CONE_ELLIPTIC) {
       R[1] = R[0] / fmax(kMinVal, m.impratio);
       con.mu = con.friction[0] * sqrt(R[1] / R[0]);
-      for (int j = 1; j < dim - 1; j++) R[j + 1] = R[1] * con.friction[0] * con.friction[0] / (con.friction[j] * con.friction[j]);
+      PS_LOOP2 for (int j = 1; j < dim - 1; j++) R[j + 1] = R[1] * con.friction[0] * con.friction[0] / (con.friction[j] * con.friction[j]);
     } else {
       const double R1 = R[0] / fmax(kMinVal, m.impratio);
       con.mu = con.friction[0] * sqrt(R1 / R[0]);
       const double Rpy = 2 * con.mu * con.mu * R[0];
-      for (int j = 0; j < 2 * (dim - 1); j++) R[j] = Rpy;
+      PS_LOOP2 for (int j = 0; j < 2 * (dim - 1); j++) R[j] = Rpy;
     }
   }
-  for (int q = 0; q < nrow; q++) d.efc_D[adr + q] = 1 / R[q];
+  PS_LOOP2 for (int q = 0; q < nrow; q++) d.efc_D[adr + q] = 1 / R[q];
 }
 
 template <class T, class LT>
@@ -195,13 +195,13 @@ PS_NI void co_make_constraints(const LT& L, const DevModel<T>& m, CoopData<T>& d
       const int j = base + L.lane; int cnt = 0; double dist[2]; int sgn[2];
       if (j < m.njnt && m.jnt_limited[j] && (m.jnt_type[j] == JNT_HINGE || m.jnt_type[j] == JNT_SLIDE)) {
         const double value = d.qpos[m.jnt_qposadr[j]], margin = m.jnt_margin[j];
-        for (int side = -1; side <= 1; side += 2) {
+        PS_LOOP2 for (int side = -1; side <= 1; side += 2) {
           const double ds = side * (m.jnt_range[2 * j + (side + 1) / 2] - value);
           if (ds < margin) { dist[cnt] = ds; sgn[cnt] = -side; cnt++; }
         }
       }
       int total; const int off = L.scan(cnt, &total);
-      for (int c = 0; c < cnt; c++) {
+      PS_LOOP2 for (int c = 0; c < cnt; c++) {
         const int row = nefc + off + c;
         if (row >= T::MAXEFC) break;
         d.efc_type[row] = EFC_LIMIT_JOINT; d.efc_id[row] = (short)j; d.efc_jrow[row] = (short)sgn[c]; d.efc_state[row] = 0;

@@ -99,7 +99,7 @@ PS_FN void co_integrate(const LT& L, const DevModel<T>& m, CoopData<T>& d) {
   CO_FOR(j, m.njnt) {
     const int qa = m.jnt_qposadr[j], da = m.jnt_dofadr[j], jt = m.jnt_type[j];
     if (jt == JNT_FREE) {
-      for (int k = 0; k < 3; k++) d.qpos[qa + k] += dt * d.qvel[da + k];
+      PS_LOOP2 for (int k = 0; k < 3; k++) d.qpos[qa + k] += dt * d.qvel[da + k];
       quat_integrate(d.qpos + qa + 3, d.qvel + da + 3, dt);
     } else if (jt == JNT_BALL) quat_integrate(d.qpos + qa, d.qvel + da, dt);
     else d.qpos[qa] += dt * d.qvel[da];
@@ -126,7 +126,7 @@ PS_FN double co_rollout(const LT& L, const DevModel<T>& m, const DevTask& task, 
   const double* kcol = knots + i;
   double sum = 0; bool failed = false;
 
-  for (int t = 0; t < H; t++) {
+  PS_LOOP2 for (int t = 0; t < H; t++) {
     const bool terminal = t == H - 1;
     if (!terminal) {
       // policy: spline sample + clamp, one lane per actuator
@@ -155,9 +155,9 @@ PS_FN double co_rollout(const LT& L, const DevModel<T>& m, const DevTask& task, 
       CO_FOR(k, nr) wb.residual[((size_t)t * nr + k) * stride + i] = d.residual[k];
       if (L.lane == 0) {
         wb.costs[(size_t)t * stride + i] = c;
-        for (int k = 0; k < task.num_trace; k++) {
+        PS_LOOP2 for (int k = 0; k < task.num_trace; k++) {
           double tr[3]; read_sensor(m, d, task.trace_sensor[k], tr);
-          for (int x = 0; x < 3; x++) wb.trace[((size_t)t * ntr + 3 * k + x) * stride + i] = tr[x];
+          PS_LOOP2 for (int x = 0; x < 3; x++) wb.trace[((size_t)t * ntr + 3 * k + x) * stride + i] = tr[x];
         }
       }
     }
@@ -204,7 +204,7 @@ coop_rollout_kernel(const Constants<T>* __restrict__ gconst, const double* __res
     constexpr uint32_t total = (uint32_t)sizeof(Constants<T>);
     mbar_expect_tx(&bar, total);
     const char* src = reinterpret_cast<const char*>(gconst); char* dst = reinterpret_cast<char*>(&sc);
-    for (uint32_t off = 0; off < total; off += 32768u) {
+    PS_LOOP2 for (uint32_t off = 0; off < total; off += 32768u) {
       const uint32_t sz = total - off < 32768u ? total - off : 32768u;
       tma_bulk_g2s(dst + off, src + off, sz, &bar);
     }
@@ -215,7 +215,7 @@ coop_rollout_kernel(const Constants<T>* __restrict__ gconst, const double* __res
   Lanes L; L.lane = threadIdx.x & 31; L.width = 32;
   CoopData<T>& d = *reinterpret_cast<CoopData<T>*>(smem + kConst + warp * kData);
   double best = 1.0e300; long long best_i = 0x7fffffffffffffffLL;
-  for (;;) {
+  PS_LOOP2 for (;;) {
     int k = 0;
     if (L.lane == 0) k = atomicAdd(counter, 1);
     k = __shfl_sync(0xffffffffu, k, 0);
@@ -230,7 +230,7 @@ coop_rollout_kernel(const Constants<T>* __restrict__ gconst, const double* __res
   if (L.lane == 0) { warp_min[warp].cost = best; warp_min[warp].index = best_i; }
   __syncthreads();
   if (threadIdx.x == 0) {
-    for (int w = 1; w < WARPS; w++) if (better(warp_min[w].cost, warp_min[w].index, best, best_i)) { best = warp_min[w].cost; best_i = warp_min[w].index; }
+    PS_LOOP2 for (int w = 1; w < WARPS; w++) if (better(warp_min[w].cost, warp_min[w].index, best, best_i)) { best = warp_min[w].cost; best_i = warp_min[w].index; }
     block_min[blockIdx.x].cost = best; block_min[blockIdx.x].index = best_i;
   }
 }
@@ -254,7 +254,7 @@ coop_robust_kernel(const Constants<T>* __restrict__ gconst, const double* __rest
     constexpr uint32_t total = (uint32_t)sizeof(Constants<T>);
     mbar_expect_tx(&bar, total);
     const char* src = reinterpret_cast<const char*>(gconst); char* dst = reinterpret_cast<char*>(&sc);
-    for (uint32_t off = 0; off < total; off += 32768u) {
+    PS_LOOP2 for (uint32_t off = 0; off < total; off += 32768u) {
       const uint32_t sz = total - off < 32768u ? total - off : 32768u;
       tma_bulk_g2s(dst + off, src + off, sz, &bar);
     }
@@ -293,27 +293,30 @@ sparse_rollout_kernel(const Constants<T>* __restrict__ gconst, const double* __r
     constexpr uint32_t total = (uint32_t)sizeof(Constants<T>);
     mbar_expect_tx(&bar, total);
     const char* src = reinterpret_cast<const char*>(gconst); char* dst = reinterpret_cast<char*>(&sc);
-    for (uint32_t off = 0; off < total; off += 32768u) {
+    PS_LOOP2 for (uint32_t off = 0; off < total; off += 32768u) {
       const uint32_t sz = total - off < 32768u ? total - off : 32768u;
       tma_bulk_g2s(dst + off, src + off, sz, &bar);
     }
   }
   mbar_wait(&bar, 0);
-  const int i = first + blockIdx.x * blockDim.x + threadIdx.x;
-  const bool active = i < first + n;
-  double total = 1.0e300;
-  if (active) {
-    int flags = 0;
-    CoopData<T> d;
-    Lanes1 L;
-    total = co_rollout<T, WB>(L, sc.m, sc.t, sc.p, knots, stride, i, wb, d, &flags);
-    returns[i] = total;
-    failure[i] = (unsigned char)flags;
+  // grid-stride over the batch: the launch may use fewer blocks than the batch needs (launch_sparse: a bounded number of
+  // resident rollouts per SM keeps their thread-private working sets inside L1 / L2), each block then rolls several groups
+  double c = 1.0e300; long long gi = 0x7fffffffffffffffLL;
+  PS_LOOP2 for (int base = blockIdx.x * blockDim.x; base < n; base += gridDim.x * blockDim.x) {
+    const int i = first + base + threadIdx.x;
+    if (i < first + n) {
+      int flags = 0;
+      CoopData<T> d;
+      Lanes1 L;
+      double total = co_rollout<T, WB>(L, sc.m, sc.t, sc.p, knots, stride, i, wb, d, &flags);
+      returns[i] = total;
+      failure[i] = (unsigned char)flags;
+      if (!(total == total)) total = 1.0e300;
+      if (better(total, sample_offset + i, c, gi)) { c = total; gi = sample_offset + i; }
+    }
   }
-  double c = active ? total : 1.0e300; long long gi = active ? sample_offset + i : 0x7fffffffffffffffLL;
-  if (!(c == c)) c = 1.0e300;
 #pragma unroll
-  for (int o = 16; o > 0; o >>= 1) {
+  PS_LOOP2 for (int o = 16; o > 0; o >>= 1) {
     const double oc = __shfl_down_sync(0xffffffffu, c, o);
     const long long oi = __shfl_down_sync(0xffffffffu, gi, o);
     if (better(oc, oi, c, gi)) { c = oc; gi = oi; }
@@ -321,8 +324,46 @@ sparse_rollout_kernel(const Constants<T>* __restrict__ gconst, const double* __r
   if ((threadIdx.x & 31) == 0) { warp_min[threadIdx.x >> 5].cost = c; warp_min[threadIdx.x >> 5].index = gi; }
   __syncthreads();
   if (threadIdx.x == 0) {
-    for (int w = 1; w < (int)(blockDim.x >> 5); w++) if (better(warp_min[w].cost, warp_min[w].index, c, gi)) { c = warp_min[w].cost; gi = warp_min[w].index; }
+    PS_LOOP2 for (int w = 1; w < (int)(blockDim.x >> 5); w++) if (better(warp_min[w].cost, warp_min[w].index, c, gi)) { c = warp_min[w].cost; gi = warp_min[w].index; }
     block_min[blockIdx.x].cost = c; block_min[blockIdx.x].index = gi;
+  }
+}
+
+// ---------------------------------------------------------------- capacity-overflow fix-up
+// A rollout that ran out of the scoring kernel's contact / constraint-row capacity carries flag bit 1 and was scored with the
+// rows that fit.  The reference never truncates (mjpc/trajectory.cc:169-173: a rollout is valid or 1e6), so every flagged
+// sample is rolled again here -- thread per rollout over the same phases, instantiated at capacities (TXL) large enough for
+// a fallen robot, working set in local memory -- and its return / flags / trajectory replace the truncated ones before
+// the argmin.  `list` / `count` come from collect_flagged_kernel; with count == 0 (the usual case) the blocks exit at once.
+template <class TXL, int BLOCK, bool WB>
+__global__ void __launch_bounds__(BLOCK)
+sparse_fixup_kernel(const Constants<TXL>* __restrict__ gconst, const double* __restrict__ knots, int stride,
+                    double* __restrict__ returns, unsigned char* __restrict__ failure, const int* __restrict__ list,
+                    const int* __restrict__ count, Writeback wb) {
+  const int n = *count;
+  if ((int)(blockIdx.x * blockDim.x) >= n) return;            // whole block has nothing to do (uniform: before any barrier)
+  __shared__ Constants<TXL> sc;
+  __shared__ alignas(8) uint64_t bar;
+  if (threadIdx.x == 0) { mbar_init(&bar, 1); asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    constexpr uint32_t total = (uint32_t)sizeof(Constants<TXL>);
+    mbar_expect_tx(&bar, total);
+    const char* src = reinterpret_cast<const char*>(gconst); char* dst = reinterpret_cast<char*>(&sc);
+    PS_LOOP2 for (uint32_t off = 0; off < total; off += 32768u) {
+      const uint32_t sz = total - off < 32768u ? total - off : 32768u;
+      tma_bulk_g2s(dst + off, src + off, sz, &bar);
+    }
+  }
+  mbar_wait(&bar, 0);
+  PS_LOOP2 for (int j = blockIdx.x * blockDim.x + threadIdx.x; j < n; j += gridDim.x * blockDim.x) {
+    const int i = list[j];
+    int flags = 0;
+    CoopData<TXL> d;
+    Lanes1 L;
+    const double total = co_rollout<TXL, WB>(L, sc.m, sc.t, sc.p, knots, stride, i, wb, d, &flags);
+    returns[i] = total;
+    failure[i] = (unsigned char)flags;
   }
 }
 #endif

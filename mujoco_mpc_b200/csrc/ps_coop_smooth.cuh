@@ -20,25 +20,25 @@ PS_NI void co_body_frame(const DevModel<T>& m, CoopData<T>& d, int b) { PS_ASSUM
     vcopy(d.xanchor + 3 * ja, pos, 3); vcopy(d.xaxis + 3 * ja, m.jnt_axis + 3 * ja, 3);
   } else {
     double t[3]; mat_vec3(t, d.xmat + 9 * par, m.body_pos + 3 * b);
-    for (int k = 0; k < 3; k++) pos[k] = d.xpos[3 * par + k] + t[k];
+    PS_LOOP2 for (int k = 0; k < 3; k++) pos[k] = d.xpos[3 * par + k] + t[k];
     quat_mul(quat, d.xquat + 4 * par, m.body_quat + 4 * b);
-    for (int j = ja; j < ja + jn; j++) {
+    PS_LOOP2 for (int j = ja; j < ja + jn; j++) {
       const int qa = m.jnt_qposadr[j];
       double* anchor = d.xanchor + 3 * j; double* axis = d.xaxis + 3 * j;
       double v[3]; quat_rotate(v, m.jnt_pos + 3 * j, quat);
-      for (int k = 0; k < 3; k++) anchor[k] = v[k] + pos[k];
+      PS_LOOP2 for (int k = 0; k < 3; k++) anchor[k] = v[k] + pos[k];
       quat_rotate(axis, m.jnt_axis + 3 * j, quat);
       const int jt = m.jnt_type[j];
       if (jt == JNT_SLIDE) {
         const double dq = d.qpos[qa] - m.qpos0[qa];
-        for (int k = 0; k < 3; k++) pos[k] += axis[k] * dq;
+        PS_LOOP2 for (int k = 0; k < 3; k++) pos[k] += axis[k] * dq;
       } else if (jt == JNT_HINGE || jt == JNT_BALL) {
         double ql[4];
         if (jt == JNT_BALL) vcopy(ql, d.qpos + qa, 4);
         else axis_angle_quat(ql, m.jnt_axis + 3 * j, d.qpos[qa] - m.qpos0[qa]);
         quat_mul(quat, quat, ql);
         quat_rotate(v, m.jnt_pos + 3 * j, quat);
-        for (int k = 0; k < 3; k++) pos[k] = anchor[k] - v[k];
+        PS_LOOP2 for (int k = 0; k < 3; k++) pos[k] = anchor[k] - v[k];
       }
     }
   }
@@ -46,7 +46,7 @@ PS_NI void co_body_frame(const DevModel<T>& m, CoopData<T>& d, int b) { PS_ASSUM
   vcopy(d.xquat + 4 * b, quat, 4); vcopy(d.xpos + 3 * b, pos, 3);
   quat_to_mat(d.xmat + 9 * b, quat);
   double t[3]; mat_vec3(t, d.xmat + 9 * b, m.body_ipos + 3 * b);
-  for (int k = 0; k < 3; k++) d.xipos[3 * b + k] = pos[k] + t[k];
+  PS_LOOP2 for (int k = 0; k < 3; k++) d.xipos[3 * b + k] = pos[k] + t[k];
   double qi[4]; quat_mul(qi, quat, m.body_iquat + 4 * b); quat_to_mat(d.ximat + 9 * b, qi);
 }
 
@@ -64,7 +64,7 @@ PS_NI void co_kinematics(const LT& L, const DevModel<T>& m, CoopData<T>& d) { PS
     vzero(d.xipos, 3); vzero(d.ximat, 9); d.ximat[0] = d.ximat[4] = d.ximat[8] = 1;
   }
   L.sync();
-  for (int l = 1; l < m.nlevel; l++) {
+  PS_LOOP2 for (int l = 1; l < m.nlevel; l++) {
     const int a = m.level_adr[l], n = m.level_adr[l + 1] - a;
     CO_FOR(k, n) co_body_frame<T, LT>(m, d, m.level_body[a + k]);
     L.sync();
@@ -72,7 +72,7 @@ PS_NI void co_kinematics(const LT& L, const DevModel<T>& m, CoopData<T>& d) { PS
   CO_FOR(s, m.nsite) {
     const int b = m.site_bodyid[s]; double t[3], q[4];
     mat_vec3(t, d.xmat + 9 * b, m.site_pos + 3 * s);
-    for (int k = 0; k < 3; k++) d.site_xpos[3 * s + k] = d.xpos[3 * b + k] + t[k];
+    PS_LOOP2 for (int k = 0; k < 3; k++) d.site_xpos[3 * s + k] = d.xpos[3 * b + k] + t[k];
     quat_mul(q, d.xquat + 4 * b, m.site_quat + 4 * s); quat_to_mat(d.site_xmat + 9 * s, q);
   }
   CO_FOR(k, m.ntrack) geom_pose(m, d, m.track_geom[k], d.track_xpos + 3 * k, d.track_xmat + 9 * k);
@@ -82,12 +82,12 @@ PS_NI void co_kinematics(const LT& L, const DevModel<T>& m, CoopData<T>& d) { PS
 // `n` values per body.  include_world: whether body 0 accumulates too.
 template <class T, class LT>
 PS_NI void co_fold_children(const LT& L, const DevModel<T>& m, double* x, int n, bool include_world) { PS_ASSUME_SHARED(&m);
-  for (int l = m.nlevel - 2; l >= (include_world ? 0 : 1); l--) {
+  PS_LOOP2 for (int l = m.nlevel - 2; l >= (include_world ? 0 : 1); l--) {
     const int a = m.level_adr[l], nb = m.level_adr[l + 1] - a;
     CO_FOR(w, nb * n) {
       const int p = m.level_body[a + w / n], k = w % n;
       double s = x[n * p + k];
-      for (int c = m.child_adr[p]; c < m.child_adr[p + 1]; c++) s += x[n * m.child_list[c] + k];
+      PS_LOOP2 for (int c = m.child_adr[p]; c < m.child_adr[p + 1]; c++) s += x[n * m.child_list[c] + k];
       x[n * p + k] = s;
     }
     L.sync();
@@ -104,14 +104,14 @@ PS_NI void co_com_position(const LT& L, const DevModel<T>& m, CoopData<T>& d) { 
   co_fold_children(L, m, sc, 3, true);
   CO_FOR(i, nb) {
     if (m.body_subtreemass[i] < kMinVal) vcopy(sc + 3 * i, d.xipos + 3 * i, 3);
-    else for (int k = 0; k < 3; k++) sc[3 * i + k] /= m.body_subtreemass[i];
+    else PS_LOOP2 for (int k = 0; k < 3; k++) sc[3 * i + k] /= m.body_subtreemass[i];
   }
   L.sync();
   CO_FOR(i, nb) {
     double* c = d.cinert + 10 * i;
     if (i == 0) { vzero(c, 10); continue; }
     double off[3]; const double* root = sc + 3 * m.body_rootid[i];
-    for (int k = 0; k < 3; k++) off[k] = d.xipos[3 * i + k] - root[k];
+    PS_LOOP2 for (int k = 0; k < 3; k++) off[k] = d.xipos[3 * i + k] - root[k];
     const double* R = d.ximat + 9 * i; const double* I = m.body_inertia + 3 * i; const double mass = m.body_mass[i];
     const double w00 = R[0] * I[0] * R[0] + R[1] * I[1] * R[1] + R[2] * I[2] * R[2];
     const double w11 = R[3] * I[0] * R[3] + R[4] * I[1] * R[4] + R[5] * I[2] * R[5];
@@ -130,14 +130,14 @@ PS_NI void co_com_position(const LT& L, const DevModel<T>& m, CoopData<T>& d) { 
   CO_FOR(j, m.njnt) {
     const int b = m.jnt_bodyid[j]; int da = m.jnt_dofadr[j];
     double off[3]; const double* root = sc + 3 * m.body_rootid[b];
-    for (int k = 0; k < 3; k++) off[k] = root[k] - d.xanchor[3 * j + k];
+    PS_LOOP2 for (int k = 0; k < 3; k++) off[k] = root[k] - d.xanchor[3 * j + k];
     const int jt = m.jnt_type[j];
     if (jt == JNT_FREE) {
-      for (int k = 0; k < 3; k++) { double ax[3] = {0, 0, 0}; ax[k] = 1; dof_motion(d.cdof + 6 * (da + k), ax, nullptr); }
+      PS_LOOP2 for (int k = 0; k < 3; k++) { double ax[3] = {0, 0, 0}; ax[k] = 1; dof_motion(d.cdof + 6 * (da + k), ax, nullptr); }
       da += 3;
     }
     if (jt == JNT_FREE || jt == JNT_BALL) {
-      for (int k = 0; k < 3; k++) {
+      PS_LOOP2 for (int k = 0; k < 3; k++) {
         double ax[3] = {d.xmat[9 * b + k], d.xmat[9 * b + 3 + k], d.xmat[9 * b + 6 + k]};
         dof_motion(d.cdof + 6 * (da + k), ax, off);
       }
@@ -152,7 +152,7 @@ PS_NI void co_com_position(const LT& L, const DevModel<T>& m, CoopData<T>& d) { 
 template <class T, class LT>
 PS_NI void co_factor_tree(const LT& L, const DevModel<T>& m, double* A, double* dinv) { PS_ASSUME_SHARED(&m);
   constexpr int S = T::NV; const int nv = m.nv;
-  for (int k = nv - 1; k >= 0; k--) {
+  PS_LOOP2 for (int k = nv - 1; k >= 0; k--) {
     double dk = A[k * S + k];
     if (dk < kMinVal) { dk = kMinVal; if (L.lane == 0) A[k * S + k] = kMinVal; }
     const int pa = m.fpair_adr[k], np = m.fpair_adr[k + 1] - pa;
@@ -177,12 +177,12 @@ template <class T, class LT>
 PS_NI void co_solve_tree(const LT& L, const DevModel<T>& m, double* x, const double* A, const double* dinv) { PS_ASSUME_SHARED(&m);
   constexpr int S = T::NV; const int nv = m.nv;
   // x <- L^-T x : a dof collects from its descendants (deepest first, decreasing index)
-  for (int l = m.ndoflevel - 2; l >= 0; l--) {
+  PS_LOOP2 for (int l = m.ndoflevel - 2; l >= 0; l--) {
     const int a = m.doflevel_adr[l], n = m.doflevel_adr[l + 1] - a;
     CO_FOR(w, n) {
       const int j = m.doflevel_dof[a + w];
       double s = x[j];
-      for (int c = m.dofdesc_adr[j]; c < m.dofdesc_adr[j + 1]; c++) { const int i = m.dofdesc[c]; s -= A[i * S + j] * x[i]; }
+      PS_LOOP2 for (int c = m.dofdesc_adr[j]; c < m.dofdesc_adr[j + 1]; c++) { const int i = m.dofdesc[c]; s -= A[i * S + j] * x[i]; }
       x[j] = s;
     }
     L.sync();
@@ -190,12 +190,12 @@ PS_NI void co_solve_tree(const LT& L, const DevModel<T>& m, double* x, const dou
   CO_FOR(i, nv) x[i] *= dinv[i];
   L.sync();
   // x <- L^-1 x : a dof subtracts its ancestors (shallowest first)
-  for (int l = 1; l < m.ndoflevel; l++) {
+  PS_LOOP2 for (int l = 1; l < m.ndoflevel; l++) {
     const int a = m.doflevel_adr[l], n = m.doflevel_adr[l + 1] - a;
     CO_FOR(w, n) {
       const int i = m.doflevel_dof[a + w];
       double s = x[i];
-      for (int c = m.dofanc_adr[i]; c < m.dofanc_adr[i + 1]; c++) { const int j = m.dofanc[c]; s -= A[i * S + j] * x[j]; }
+      PS_LOOP2 for (int c = m.dofanc_adr[i]; c < m.dofanc_adr[i + 1]; c++) { const int j = m.dofanc[c]; s -= A[i * S + j] * x[j]; }
       x[i] = s;
     }
     L.sync();
@@ -245,21 +245,21 @@ template <class T, class LT>
 PS_NI void co_body_velocity(const DevModel<T>& m, const CoopData<T>& d, const double* qvel, double* cvel, double* cdof_dot, int i) { PS_ASSUME_SHARED(&m); if (LT::kSharedData) PS_ASSUME_SHARED(&d);
   double v[6]; vcopy(v, cvel + 6 * m.body_parentid[i], 6);
   const int ja = m.body_jntadr[i];
-  for (int j = ja; j < ja + m.body_jntnum[i]; j++) {
+  PS_LOOP2 for (int j = ja; j < ja + m.body_jntnum[i]; j++) {
     int da = m.jnt_dofadr[j]; const int jt = m.jnt_type[j];
     if (jt == JNT_FREE) {
-      for (int k = 0; k < 3; k++) {
+      PS_LOOP2 for (int k = 0; k < 3; k++) {
         vzero(cdof_dot + 6 * (da + k), 6);
-        for (int r = 0; r < 6; r++) v[r] += d.cdof[6 * (da + k) + r] * qvel[da + k];
+        PS_LOOP2 for (int r = 0; r < 6; r++) v[r] += d.cdof[6 * (da + k) + r] * qvel[da + k];
       }
       da += 3;
     }
     if (jt == JNT_FREE || jt == JNT_BALL) {
-      for (int k = 0; k < 3; k++) cross_motion(cdof_dot + 6 * (da + k), v, d.cdof + 6 * (da + k));
-      for (int k = 0; k < 3; k++) for (int r = 0; r < 6; r++) v[r] += d.cdof[6 * (da + k) + r] * qvel[da + k];
+      PS_LOOP2 for (int k = 0; k < 3; k++) cross_motion(cdof_dot + 6 * (da + k), v, d.cdof + 6 * (da + k));
+      PS_LOOP2 for (int k = 0; k < 3; k++) PS_LOOP2 for (int r = 0; r < 6; r++) v[r] += d.cdof[6 * (da + k) + r] * qvel[da + k];
     } else {
       cross_motion(cdof_dot + 6 * da, v, d.cdof + 6 * da);
-      for (int r = 0; r < 6; r++) v[r] += d.cdof[6 * da + r] * qvel[da];
+      PS_LOOP2 for (int r = 0; r < 6; r++) v[r] += d.cdof[6 * da + r] * qvel[da];
     }
   }
   vcopy(cvel + 6 * i, v, 6);
@@ -272,7 +272,7 @@ PS_NI void co_velocity_stage(const LT& L, const DevModel<T>& m, CoopData<T>& d) 
   CO_FOR(i, m.nu) d.actuator_velocity[i] = m.act_gear[i] * d.qvel[m.jnt_dofadr[m.act_jntid[i]]];
   if (L.lane == 0) vzero(cvel, 6);
   L.sync();
-  for (int l = 1; l < m.nlevel; l++) {
+  PS_LOOP2 for (int l = 1; l < m.nlevel; l++) {
     const int a = m.level_adr[l], n = m.level_adr[l + 1] - a;
     CO_FOR(k, n) co_body_velocity<T, LT>(m, d, d.qvel, cvel, cdd, m.level_body[a + k]);
     L.sync();
@@ -290,23 +290,23 @@ PS_NI void co_velocity_stage(const LT& L, const DevModel<T>& m, CoopData<T>& d) 
   double* cacc = d.scratch; double* cfrc = d.scratch + 6 * nb;
   if (L.lane == 0) {
     const bool grav = !(m.disableflags & DSBL_GRAVITY);
-    for (int k = 0; k < 3; k++) { cacc[k] = 0; cacc[3 + k] = grav ? -m.gravity[k] : 0.0; }
+    PS_LOOP2 for (int k = 0; k < 3; k++) { cacc[k] = 0; cacc[3 + k] = grav ? -m.gravity[k] : 0.0; }
     vzero(cfrc, 6);
   }
   L.sync();
-  for (int l = 1; l < m.nlevel; l++) {
+  PS_LOOP2 for (int l = 1; l < m.nlevel; l++) {
     const int a = m.level_adr[l], n = m.level_adr[l + 1] - a;
     CO_FOR(k, n) {
       const int i = m.level_body[a + k], bda = m.body_dofadr[i];
       double ca[6]; vcopy(ca, cacc + 6 * m.body_parentid[i], 6);
-      for (int j = 0; j < m.body_dofnum[i]; j++)
-        for (int r = 0; r < 6; r++) ca[r] += cdd[6 * (bda + j) + r] * d.qvel[bda + j];
+      PS_LOOP2 for (int j = 0; j < m.body_dofnum[i]; j++)
+        PS_LOOP2 for (int r = 0; r < 6; r++) ca[r] += cdd[6 * (bda + j) + r] * d.qvel[bda + j];
       vcopy(cacc + 6 * i, ca, 6);
       double t1[6], t2[6], t3[6];
       inert_vec(t1, d.cinert + 10 * i, ca);
       inert_vec(t2, d.cinert + 10 * i, cvel + 6 * i);
       cross_force(t3, cvel + 6 * i, t2);
-      for (int r = 0; r < 6; r++) cfrc[6 * i + r] = t1[r] + t3[r];
+      PS_LOOP2 for (int r = 0; r < 6; r++) cfrc[6 * i + r] = t1[r] + t3[r];
     }
     L.sync();
   }
@@ -322,34 +322,34 @@ PS_NI void co_subtree_velocity(const LT& L, const DevModel<T>& m, CoopData<T>& d
   double* bodyvel = d.scratch; double* lv = d.subtree_linvel; double* am = d.subtree_angmom;
   CO_FOR(i, nb) {
     frame_velocity(m, d, i, d.xipos + 3 * i, bodyvel + 6 * i);
-    for (int k = 0; k < 3; k++) lv[3 * i + k] = m.body_mass[i] * bodyvel[6 * i + 3 + k];
+    PS_LOOP2 for (int k = 0; k < 3; k++) lv[3 * i + k] = m.body_mass[i] * bodyvel[6 * i + 3 + k];
     double t[3], t2[3]; matT_vec3(t, d.ximat + 9 * i, bodyvel + 6 * i);
-    for (int k = 0; k < 3; k++) t[k] *= m.body_inertia[3 * i + k];
+    PS_LOOP2 for (int k = 0; k < 3; k++) t[k] *= m.body_inertia[3 * i + k];
     mat_vec3(t2, d.ximat + 9 * i, t); vcopy(am + 3 * i, t2, 3);
   }
   L.sync();
   co_fold_children(L, m, lv, 3, true);
-  CO_FOR(i, nb) for (int k = 0; k < 3; k++) lv[3 * i + k] /= fmax(kMinVal, m.body_subtreemass[i]);
+  CO_FOR(i, nb) PS_LOOP2 for (int k = 0; k < 3; k++) lv[3 * i + k] /= fmax(kMinVal, m.body_subtreemass[i]);
   L.sync();
   // angular momentum: own offset term of a body, then fold it (and its transport term) into the parent
-  for (int l = m.nlevel - 1; l >= 1; l--) {
+  PS_LOOP2 for (int l = m.nlevel - 1; l >= 1; l--) {
     const int a = m.level_adr[l], n = m.level_adr[l + 1] - a;
     CO_FOR(k, n) {
       const int i = m.level_body[a + k]; double dx[3], dv[3], dL[3];
-      for (int c = 0; c < 3; c++) { dx[c] = d.xipos[3 * i + c] - d.subtree_com[3 * i + c]; dv[c] = (bodyvel[6 * i + 3 + c] - lv[3 * i + c]) * m.body_mass[i]; }
+      PS_LOOP2 for (int c = 0; c < 3; c++) { dx[c] = d.xipos[3 * i + c] - d.subtree_com[3 * i + c]; dv[c] = (bodyvel[6 * i + 3 + c] - lv[3 * i + c]) * m.body_mass[i]; }
       cross3(dL, dx, dv);
-      for (int c = 0; c < 3; c++) am[3 * i + c] += dL[c];
+      PS_LOOP2 for (int c = 0; c < 3; c++) am[3 * i + c] += dL[c];
     }
     L.sync();
     const int pa = m.level_adr[l - 1], pn = m.level_adr[l] - pa;
     CO_FOR(k, pn) {
       const int p = m.level_body[pa + k];
-      for (int cc = m.child_adr[p]; cc < m.child_adr[p + 1]; cc++) {
+      PS_LOOP2 for (int cc = m.child_adr[p]; cc < m.child_adr[p + 1]; cc++) {
         const int i = m.child_list[cc]; double dx[3], dv[3], dL[3];
-        for (int c = 0; c < 3; c++) am[3 * p + c] += am[3 * i + c];
-        for (int c = 0; c < 3; c++) { dx[c] = d.subtree_com[3 * i + c] - d.subtree_com[3 * p + c]; dv[c] = (lv[3 * i + c] - lv[3 * p + c]) * m.body_subtreemass[i]; }
+        PS_LOOP2 for (int c = 0; c < 3; c++) am[3 * p + c] += am[3 * i + c];
+        PS_LOOP2 for (int c = 0; c < 3; c++) { dx[c] = d.subtree_com[3 * i + c] - d.subtree_com[3 * p + c]; dv[c] = (lv[3 * i + c] - lv[3 * p + c]) * m.body_subtreemass[i]; }
         cross3(dL, dx, dv);
-        for (int c = 0; c < 3; c++) am[3 * p + c] += dL[c];
+        PS_LOOP2 for (int c = 0; c < 3; c++) am[3 * p + c] += dL[c];
       }
     }
     L.sync();
@@ -393,7 +393,7 @@ PS_NI void co_actuation_stage(const LT& L, const DevModel<T>& m, CoopData<T>& d)
   // several actuators may drive one dof: accumulate in actuator order, one lane per dof
   if (nu && !(m.disableflags & DSBL_ACTUATION)) CO_FOR(i, nv) {
     double s = 0;
-    for (int a = 0; a < nu; a++) if (m.jnt_dofadr[m.act_jntid[a]] == i) s += m.act_gear[a] * d.actuator_force[a];
+    PS_LOOP2 for (int a = 0; a < nu; a++) if (m.jnt_dofadr[m.act_jntid[a]] == i) s += m.act_gear[a] * d.actuator_force[a];
     d.qfrc_actuator[i] = s;
   }
   L.sync();
@@ -418,7 +418,7 @@ PS_NI void co_acceleration_stage_xfrc(const LT& L, const DevModel<T>& m, CoopDat
   CO_FOR(c, m.nv) {
     double acc = d.qfrc_passive[c] - d.qfrc_bias[c] + d.qfrc_actuator[c];
     const double* cd = d.cdof + 6 * c;
-    for (int b = 1; b < m.nbody; b++) {
+    PS_LOOP2 for (int b = 1; b < m.nbody; b++) {
       const double* x = xfrc_applied + 6 * b;
       if (x[0] == 0 && x[1] == 0 && x[2] == 0 && x[3] == 0 && x[4] == 0 && x[5] == 0) continue;
       const int w = m.body_weldid[b];
@@ -428,9 +428,9 @@ PS_NI void co_acceleration_stage_xfrc(const LT& L, const DevModel<T>& m, CoopDat
       if (i != c) continue;                         // dof c does not move body b
       double off[3], t[3];
       const double* root = d.subtree_com + 3 * m.body_rootid[w];
-      for (int k = 0; k < 3; k++) off[k] = d.xipos[3 * b + k] - root[k];
+      PS_LOOP2 for (int k = 0; k < 3; k++) off[k] = d.xipos[3 * b + k] - root[k];
       cross3(t, cd, off);
-      for (int k = 0; k < 3; k++) acc += (cd[3 + k] + t[k]) * x[k] + cd[k] * x[3 + k];
+      PS_LOOP2 for (int k = 0; k < 3; k++) acc += (cd[3 + k] + t[k]) * x[k] + cd[k] * x[3 + k];
     }
     d.qfrc_smooth[c] = acc;
     d.qacc_smooth[c] = acc;

@@ -27,30 +27,30 @@ PS_NI double co_update_rows(const LT& L, const DevModel<T>& m, CoopData<T>& d, c
       if (i != con.efc_address) continue;              // the contact's first row does the whole cone
       const int dim = con.dim; const double mu = con.mu; const double* fr = con.friction;
       double U[6]; U[0] = jar[i] * mu;
-      for (int j = 1; j < dim; j++) U[j] = jar[i + j] * fr[j - 1];
+      PS_LOOP2 for (int j = 1; j < dim; j++) U[j] = jar[i + j] * fr[j - 1];
       const double N = U[0]; double TT = 0;
-      for (int j = 1; j < dim; j++) TT += U[j] * U[j];
+      PS_LOOP2 for (int j = 1; j < dim; j++) TT += U[j] * U[j];
       const double Tn = sqrt(TT);
       int st;
       if (N >= mu * Tn || (Tn <= 0 && N >= 0)) {
-        st = ST_SATISFIED; for (int j = 0; j < dim; j++) { d.efc_force[i + j] = 0; d.sv_tmp[i + j] = 0; }
+        st = ST_SATISFIED; PS_LOOP2 for (int j = 0; j < dim; j++) { d.efc_force[i + j] = 0; d.sv_tmp[i + j] = 0; }
       } else if (mu * N + Tn <= 0 || (Tn <= 0 && N < 0)) {
         st = ST_QUADRATIC;
-        for (int j = 0; j < dim; j++) { d.efc_force[i + j] = -d.efc_D[i + j] * jar[i + j]; d.sv_tmp[i + j] = 0.5 * d.efc_D[i + j] * jar[i + j] * jar[i + j]; }
+        PS_LOOP2 for (int j = 0; j < dim; j++) { d.efc_force[i + j] = -d.efc_D[i + j] * jar[i + j]; d.sv_tmp[i + j] = 0.5 * d.efc_D[i + j] * jar[i + j] * jar[i + j]; }
       } else {
         st = ST_CONE;
         const double Dm = d.efc_D[i] / (mu * mu * (1 + mu * mu));
         const double NT = N - mu * Tn;
         d.sv_tmp[i] = 0.5 * Dm * NT * NT;
         d.efc_force[i] = -Dm * NT * mu;
-        for (int j = 1; j < dim; j++) { d.efc_force[i + j] = -d.efc_force[i] / Tn * U[j] * fr[j - 1]; d.sv_tmp[i + j] = 0; }
+        PS_LOOP2 for (int j = 1; j < dim; j++) { d.efc_force[i + j] = -d.efc_force[i] / Tn * U[j] * fr[j - 1]; d.sv_tmp[i + j] = 0; }
       }
-      for (int j = 0; j < dim; j++) d.efc_state[i + j] = (unsigned char)st;
+      PS_LOOP2 for (int j = 0; j < dim; j++) d.efc_state[i + j] = (unsigned char)st;
     }
   }
   L.sync();
   double cost = 0;
-  for (int i = 0; i < nefc; i++) cost += d.sv_tmp[i];
+  PS_LOOP2 for (int i = 0; i < nefc; i++) cost += d.sv_tmp[i];
   return cost;
 }
 
@@ -61,7 +61,7 @@ PS_NI void co_update_cost(const LT& L, const DevModel<T>& m, CoopData<T>& d, CoS
   const int nv = m.nv;
   const double cc = co_update_rows(L, m, d, d.sv_Jaref);
   double g = 0;
-  for (int i = 0; i < nv; i++) g += 0.5 * (d.sv_Ma[i] - d.qfrc_smooth[i]) * (d.qacc[i] - d.qacc_smooth[i]);
+  PS_LOOP2 for (int i = 0; i < nv; i++) g += 0.5 * (d.sv_Ma[i] - d.qfrc_smooth[i]) * (d.qacc[i] - d.qacc_smooth[i]);
   c.gauss = g; c.prev_cost = c.cost; c.cost = g + cc;
   // qfrc_constraint = J' f, one lane per dof, rows in order
   const int nf = (m.disableflags & DSBL_FRICTIONLOSS) ? 0 : m.nfrictionrow;
@@ -70,15 +70,15 @@ PS_NI void co_update_cost(const LT& L, const DevModel<T>& m, CoopData<T>& d, CoS
     double s = 0;
     const int fr = nf ? m.dof_frictionrow[i] : -1;
     if (fr >= 0) { const double f = d.efc_force[fr]; if (f != 0) s += f; }
-    for (int r = nf; r < nf + nl; r++) {
+    PS_LOOP2 for (int r = nf; r < nf + nl; r++) {
       const double f = d.efc_force[r];
       if (f != 0 && m.jnt_dofadr[d.efc_id[r]] == i) s += (double)d.efc_jrow[r] * f;
     }
-    for (int ci = 0; ci < ncon; ci++) {
+    PS_LOOP2 for (int ci = 0; ci < ncon; ci++) {
       const CoopContact& con = d.contact[ci];
       const int k = d.con_slot[ci * T::NV + i];
       if (con.efc_address < 0 || k < 0) continue;
-      for (int q = 0; q < con.nrow; q++) {
+      PS_LOOP2 for (int q = 0; q < con.nrow; q++) {
         const double f = d.efc_force[con.efc_address + q];
         if (f != 0) s += d.jpool[(con.jadr + q) * T::NCH + k] * f;
       }
@@ -101,10 +101,10 @@ PS_NI void co_newton_direction(const LT& L, const DevModel<T>& m, CoopData<T>& d
   CO_FOR(k, nf) if (d.efc_state[k] == ST_QUADRATIC) { const int i = d.efc_id[k]; H[i * S + i] += d.efc_D[k]; }
   L.sync();
   if (L.lane == 0)
-    for (int r = nf; r < nf + d.nlimit; r++) if (d.efc_state[r] == ST_QUADRATIC) { const int i = m.jnt_dofadr[d.efc_id[r]]; H[i * S + i] += d.efc_D[r]; }
+    PS_LOOP2 for (int r = nf; r < nf + d.nlimit; r++) if (d.efc_state[r] == ST_QUADRATIC) { const int i = m.jnt_dofadr[d.efc_id[r]]; H[i * S + i] += d.efc_D[r]; }
   L.sync();
   // contacts one after the other; lanes own (dof slot, dof slot) pairs of the contact's block
-  for (int ci = 0; ci < d.ncon; ci++) {
+  PS_LOOP2 for (int ci = 0; ci < d.ncon; ci++) {
     const CoopContact& con = d.contact[ci];
     const int adr = con.efc_address;
     if (adr < 0) continue;
@@ -116,9 +116,9 @@ PS_NI void co_newton_direction(const LT& L, const DevModel<T>& m, CoopData<T>& d
       const int dim = con.dim; const double mu = con.mu; const double* fr = con.friction;
       // local cone Hessian (dim x dim), recomputed from the row residuals
       double U[6]; U[0] = d.sv_Jaref[adr] * mu;
-      for (int j = 1; j < dim; j++) U[j] = d.sv_Jaref[adr + j] * fr[j - 1];
+      PS_LOOP2 for (int j = 1; j < dim; j++) U[j] = d.sv_Jaref[adr + j] * fr[j - 1];
       const double N = U[0]; double TT = 0;
-      for (int j = 1; j < dim; j++) TT += U[j] * U[j];
+      PS_LOOP2 for (int j = 1; j < dim; j++) TT += U[j] * U[j];
       const double Tn = sqrt(TT);
       const double Dm = d.efc_D[adr] / (mu * mu * (1 + mu * mu));
       const double s1 = mu * N / (Tn * Tn * Tn), s2 = mu * mu - mu * N / Tn;
@@ -134,7 +134,7 @@ PS_NI void co_newton_direction(const LT& L, const DevModel<T>& m, CoopData<T>& d
       CO_FOR(w, dim * n) {
         const int a = w / n, k = w % n;
         double t = 0;
-        for (int b = 0; b < dim; b++) t += d.sv_coneH[a * dim + b] * J[b * NCH + k];
+        PS_LOOP2 for (int b = 0; b < dim; b++) t += d.sv_coneH[a * dim + b] * J[b * NCH + k];
         d.sv_T[a * NCH + k] = t;
       }
       L.sync();
@@ -143,8 +143,8 @@ PS_NI void co_newton_direction(const LT& L, const DevModel<T>& m, CoopData<T>& d
       const int ki = m.tri_a[w], kj = m.tri_b[w];     // ki >= kj
       double* h = H + dof[ki] * S + dof[kj];
       double acc = *h;
-      if (cone) { for (int a = 0; a < con.dim; a++) acc += J[a * NCH + ki] * d.sv_T[a * NCH + kj]; }
-      else for (int q = 0; q < nrow; q++) if (d.efc_state[adr + q] == ST_QUADRATIC) acc += d.efc_D[adr + q] * J[q * NCH + ki] * J[q * NCH + kj];
+      if (cone) { PS_LOOP2 for (int a = 0; a < con.dim; a++) acc += J[a * NCH + ki] * d.sv_T[a * NCH + kj]; }
+      else PS_LOOP2 for (int q = 0; q < nrow; q++) if (d.efc_state[adr + q] == ST_QUADRATIC) acc += d.efc_D[adr + q] * J[q * NCH + ki] * J[q * NCH + kj];
       *h = acc;
     }
     L.sync();
@@ -152,10 +152,10 @@ PS_NI void co_newton_direction(const LT& L, const DevModel<T>& m, CoopData<T>& d
   // right-looking Cholesky: scale column j, then subtract its outer product from the trailing
   // triangle.  Entry (i, k) receives the products of columns 0 .. k-1 in that order, which is the
   // summation order of the row-by-row formulation (s -= L_ik' L_kk', k' ascending).
-  for (int j = 0; j < nv; j++) {
+  PS_LOOP2 for (int j = 0; j < nv; j++) {
     const double dg = sqrt(fmax(H[j * S + j], kMinVal));
     L.sync();
-    for (int base = j; base < nv; base += L.width) {
+    PS_LOOP2 for (int base = j; base < nv; base += L.width) {
       const int i = base + L.lane;
       if (i == j) H[j * S + j] = dg; else if (i < nv) H[i * S + j] = H[i * S + j] / dg;
     }
@@ -171,14 +171,14 @@ PS_NI void co_newton_direction(const LT& L, const DevModel<T>& m, CoopData<T>& d
   double* x = d.sv_x;
   CO_FOR(i, nv) x[i] = d.sv_grad[i];
   L.sync();
-  for (int k = 0; k < nv; k++) {
+  PS_LOOP2 for (int k = 0; k < nv; k++) {
     const double xk = x[k] / H[k * S + k];
     L.sync();
     if (L.lane == 0) x[k] = xk;
-    for (int base = k + 1; base < nv; base += L.width) { const int i = base + L.lane; if (i < nv) x[i] -= H[i * S + k] * xk; }
+    PS_LOOP2 for (int base = k + 1; base < nv; base += L.width) { const int i = base + L.lane; if (i < nv) x[i] -= H[i * S + k] * xk; }
     L.sync();
   }
-  for (int k = nv - 1; k >= 0; k--) {
+  PS_LOOP2 for (int k = nv - 1; k >= 0; k--) {
     const double xk = x[k] / H[k * S + k];
     L.sync();
     if (L.lane == 0) x[k] = xk;
@@ -212,15 +212,15 @@ PS_NI void co_line_eval(const LT& L, const DevModel<T>& m, CoopData<T>& d, const
       if (i != con.efc_address) continue;
       const int dim = con.dim; const double mu = con.mu; const double* fr = con.friction;
       const double N = x * mu, Np = v * mu; double TT = 0, UV = 0, VV = 0;
-      for (int j = 1; j < dim; j++) {
+      PS_LOOP2 for (int j = 1; j < dim; j++) {
         const double u = (d.sv_Jaref[i + j] + alpha * d.sv_Jv[i + j]) * fr[j - 1], w = d.sv_Jv[i + j] * fr[j - 1];
         TT += u * u; UV += u * w; VV += w * w;
       }
       const double Tn = sqrt(TT);
-      for (int j = 0; j < dim; j++) { tf[i + j] = 0; tg[i + j] = 0; th[i + j] = 0; }
+      PS_LOOP2 for (int j = 0; j < dim; j++) { tf[i + j] = 0; tg[i + j] = 0; th[i + j] = 0; }
       if (N >= mu * Tn || (Tn <= 0 && N >= 0)) {
       } else if (mu * N + Tn <= 0 || (Tn <= 0 && N < 0)) {
-        for (int j = 0; j < dim; j++) {
+        PS_LOOP2 for (int j = 0; j < dim; j++) {
           const double xj = d.sv_Jaref[i + j] + alpha * d.sv_Jv[i + j], vj = d.sv_Jv[i + j], Dj = d.efc_D[i + j];
           tf[i + j] = 0.5 * Dj * xj * xj; tg[i + j] = Dj * xj * vj; th[i + j] = Dj * vj * vj;
         }
@@ -236,11 +236,11 @@ PS_NI void co_line_eval(const LT& L, const DevModel<T>& m, CoopData<T>& d, const
   double f, g, h;
   if (LT::single || L.width == 1) {       // one working lane: plain sequential sums
     f = qg[0] + alpha * qg[1] + alpha * alpha * qg[2]; g = qg[1] + 2 * alpha * qg[2]; h = 2 * qg[2];
-    for (int i = 0; i < nefc; i++) { f += tf[i]; g += tg[i]; h += th[i]; }
+    PS_LOOP2 for (int i = 0; i < nefc; i++) { f += tf[i]; g += tg[i]; h += th[i]; }
   } else {                                   // three lanes add up one quantity each, in row order, then broadcast
     double acc = L.lane == 0 ? qg[0] + alpha * qg[1] + alpha * alpha * qg[2] : (L.lane == 1 ? qg[1] + 2 * alpha * qg[2] : 2 * qg[2]);
     const double* src = L.lane == 0 ? tf : (L.lane == 1 ? tg : th);
-    if (L.lane < 3) for (int i = 0; i < nefc; i++) acc += src[i];
+    if (L.lane < 3) PS_LOOP2 for (int i = 0; i < nefc; i++) acc += src[i];
     f = L.bcast(acc, 0); g = L.bcast(acc, 1); h = L.bcast(acc, 2);
   }
   L.sync();
@@ -258,13 +258,13 @@ PS_NI double co_line_search(const LT& L, const DevModel<T>& m, CoopData<T>& d, c
   CO_FOR(r, nefc) d.sv_Jv[r] = co_row_dot(m, d, r, d.sv_search);
   L.sync();
   double qg[3] = {c.gauss, 0, 0};
-  for (int i = 0; i < nv; i++) { qg[1] += d.sv_search[i] * (d.sv_Ma[i] - d.qfrc_smooth[i]); qg[2] += 0.5 * d.sv_search[i] * d.sv_Mv[i]; }
+  PS_LOOP2 for (int i = 0; i < nv; i++) { qg[1] += d.sv_search[i] * (d.sv_Ma[i] - d.qfrc_smooth[i]); qg[2] += 0.5 * d.sv_search[i] * d.sv_Mv[i]; }
   double c0, d0, h0; co_line_eval(L, m, d, qg, 0, &c0, &d0, &h0);
   if (!(h0 > 0) || d0 >= 0) return 0;
   double lo = 0, hi = -1;
   double alpha = -d0 / h0, cc, dd, hh;
   co_line_eval(L, m, d, qg, alpha, &cc, &dd, &hh);
-  for (int it = 0; it < m.ls_iterations && fabs(dd) >= gtol; it++) {
+  PS_LOOP2 for (int it = 0; it < m.ls_iterations && fabs(dd) >= gtol; it++) {
     if (dd < 0) lo = alpha; else hi = alpha;
     double an = hh > 0 ? alpha - dd / hh : -1;
     if (hi < 0) { if (!(an > lo)) an = 2 * alpha; }
@@ -294,7 +294,7 @@ PS_NI void co_constraint_stage(const LT& L, const DevModel<T>& m, CoopData<T>& d
     CO_FOR(r, nefc) d.sv_Jaref[r] = co_row_dot(m, d, r, d.qacc) - d.efc_aref[r];
     L.sync();
     double cw = co_update_rows(L, m, d, d.sv_Jaref);
-    for (int i = 0; i < nv; i++) cw += 0.5 * (d.sv_Ma[i] - d.qfrc_smooth[i]) * (d.qacc[i] - d.qacc_smooth[i]);
+    PS_LOOP2 for (int i = 0; i < nv; i++) cw += 0.5 * (d.sv_Ma[i] - d.qfrc_smooth[i]) * (d.qacc[i] - d.qacc_smooth[i]);
     L.sync();
     CO_FOR(r, nefc) d.sv_Jv[r] = co_row_dot(m, d, r, d.qacc_smooth) - d.efc_aref[r];
     L.sync();

@@ -67,6 +67,7 @@ struct PsEngine_ {
   long long offset = 0;
   double *d_nominal = nullptr, *d_ctrlrange = nullptr, *d_knots = nullptr, *d_returns = nullptr, *d_record = nullptr, *d_z = nullptr;
   unsigned char *d_failure = nullptr, *d_std2 = nullptr; MinLoc* d_blockmin = nullptr;
+  int* d_fix = nullptr;                                           // [0] = count, [1 ..] = flagged samples (capacity-overflow fix-up)
   double* h_record = nullptr;                                     // pinned
   size_t knots_cap = 0, z_cap = 0; bool have_noise = false;
   unsigned long long seed = 1234, iteration = 0;
@@ -169,7 +170,7 @@ void ps_destroy(PsEngine* e) {
   cudaStreamSynchronize(e->stream);
   void* bufs[] = {e->d_const, e->d_nominal, e->d_ctrlrange, e->d_knots, e->d_returns, e->d_record, e->d_z, e->d_failure, e->d_std2,
                   e->d_blockmin, e->d_counter, e->d_const2, e->wb.states, e->wb.actions, e->wb.residual, e->wb.costs, e->wb.times, e->wb.trace, e->d_scratch,
-                  e->d_xfrc, e->d_param_std, e->d_elite, e->d_ce_out};
+                  e->d_xfrc, e->d_param_std, e->d_elite, e->d_ce_out, e->d_fix};
   for (void* b : bufs) if (b) cudaFree(b);
   if (e->comm && nccl_api().ok) nccl_api().CommDestroy(e->comm);
   if (e->d_gather) cudaFree(e->d_gather);
@@ -365,7 +366,9 @@ static int alloc_samples(PsEngine* e, int N) {
   const int stride = (N + 31) & ~31;
   if (stride > e->cap) {
     if (e->d_returns) cudaFree(e->d_returns); if (e->d_failure) cudaFree(e->d_failure); if (e->d_blockmin) cudaFree(e->d_blockmin);
-    e->d_returns = nullptr; e->d_failure = nullptr; e->d_blockmin = nullptr; e->cap = 0;
+    if (e->d_fix) cudaFree(e->d_fix);
+    e->d_returns = nullptr; e->d_failure = nullptr; e->d_blockmin = nullptr; e->d_fix = nullptr; e->cap = 0;
+    CU(cudaMalloc(&e->d_fix, sizeof(int) * (stride + 1)));
     CU(cudaMalloc(&e->d_returns, sizeof(double) * stride));
     CU(cudaMalloc(&e->d_failure, stride));
     CU(cudaMalloc(&e->d_blockmin, sizeof(MinLoc) * (stride + 1)));   // one entry per block (a block is >= 1 rollout) + a spare
@@ -414,6 +417,16 @@ static int run_iteration(PsEngine* e, int N, int H, double sigma0, double sigma1
                                             e->have_noise ? e->d_std2 : nullptr, e->d_knots, stride, e->have_param_std ? e->d_param_std : nullptr);
   CU(cudaEventRecord(e->ev[1], e->stream));
   e->nblocks = run->launch(e->stream, dc, e->d_knots, stride, 0, N, (long long)sample_offset, e->d_returns, e->d_failure, e->d_blockmin, e->wb, writeback, e->d_counter);
+  if (run->fixup) {
+    // capacity overflow never changes the answer: flagged rollouts are rolled again at the large capacities, then the
+    // block minima are rebuilt from the (possibly rewritten) returns
+    CU(cudaMemsetAsync(e->d_fix, 0, sizeof(int), e->stream));
+    collect_flagged_kernel<<<(N + 255) / 256, 256, 0, e->stream>>>(e->d_failure, 0, N, e->d_fix + 1, e->d_fix);
+    run->fixup(e->stream, dc, e->d_knots, stride, e->d_returns, e->d_failure, e->d_fix + 1, e->d_fix, e->wb, writeback);
+    e->nblocks = (N + 1023) / 1024;
+    minloc_returns_kernel<<<e->nblocks, 256, 0, e->stream>>>(e->d_returns, N, (long long)sample_offset, e->d_blockmin);
+    e->launches += 3;
+  }
   CU(cudaEventRecord(e->ev[2], e->stream));
   argmin_kernel<<<1, 256, 0, e->stream>>>(e->d_blockmin, e->nblocks, e->d_returns, e->d_knots, stride, nelem, (long long)sample_offset, e->d_record);
   CU(cudaEventRecord(e->ev[3], e->stream));
@@ -599,6 +612,12 @@ int ps_get_trajectory(PsEngine* e, int sample, double* states, double* actions, 
     // single re-roll: whichever kernel scored the batch (its constants are still resident)
     e->last->launch(e->stream, e->last_dconst, e->d_knots, stride, sample, 1, e->offset, e->d_returns, e->d_failure, tmp, e->wb, true, e->d_counter);
     e->launches++;
+    if (e->last->fixup) {      // the scoring kernel's capacity overflows for this sample again: take the large-capacity trajectory
+      CU(cudaMemsetAsync(e->d_fix, 0, sizeof(int), e->stream));
+      collect_flagged_kernel<<<1, 32, 0, e->stream>>>(e->d_failure, sample, 1, e->d_fix + 1, e->d_fix);
+      e->last->fixup(e->stream, e->last_dconst, e->d_knots, stride, e->d_returns, e->d_failure, e->d_fix + 1, e->d_fix, e->wb, true);
+      e->launches += 2;
+    }
     CU(cudaGetLastError());
   }
   const int ns = e->ns, nr = e->task.num_residual, nt = 3 * e->task.num_trace;

@@ -73,6 +73,35 @@ __global__ void normal_fill_kernel(double* __restrict__ out, size_t n, unsigned 
   out[i] = sqrt(-2.0 * log(u01_open(c[0], c[1]))) * cospi(2.0 * u01_open(c[2], c[3]));
 }
 
+// ---------------------------------------------------------------- capacity-overflow fix-up support
+// compact list of the samples whose rollout overflowed the scoring kernel's contact / row capacity (flag bit 1)
+__global__ void collect_flagged_kernel(const unsigned char* __restrict__ failure, int first, int n, int* __restrict__ list, int* __restrict__ count) {
+  const int i = first + blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < first + n && (failure[i] & 2)) list[atomicAdd(count, 1)] = i;
+}
+// block-level (return, global index) min straight from the per-sample returns: the input of K3 whenever returns may have
+// been rewritten after K2 (fix-up pass).  One entry per 1024 samples.
+__global__ void __launch_bounds__(256)
+minloc_returns_kernel(const double* __restrict__ returns, int n, long long sample_offset, MinLoc* __restrict__ block_min) {
+  __shared__ MinLoc wm[8];
+  double c = 1.0e300; long long gi = 0x7fffffffffffffffLL;
+  for (int k = 0; k < 4; k++) {
+    const int i = blockIdx.x * 1024 + k * 256 + threadIdx.x;
+    if (i < n) { double v = returns[i]; if (!(v == v)) v = 1.0e300; if (better(v, sample_offset + i, c, gi)) { c = v; gi = sample_offset + i; } }
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    const double oc = __shfl_down_sync(0xffffffffu, c, o); const long long oi = __shfl_down_sync(0xffffffffu, gi, o);
+    if (better(oc, oi, c, gi)) { c = oc; gi = oi; }
+  }
+  if ((threadIdx.x & 31) == 0) { wm[threadIdx.x >> 5].cost = c; wm[threadIdx.x >> 5].index = gi; }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    for (int w = 1; w < 8; w++) if (better(wm[w].cost, wm[w].index, c, gi)) { c = wm[w].cost; gi = wm[w].index; }
+    block_min[blockIdx.x].cost = c; block_min[blockIdx.x].index = gi;
+  }
+}
+
 // ---------------------------------------------------------------- K3
 // record = [winner_cost, winner_global_index, nominal_cost (local sample 0), knots[nelem]...]
 __global__ void argmin_kernel(const MinLoc* __restrict__ block_min, int nblocks, const double* __restrict__ returns,

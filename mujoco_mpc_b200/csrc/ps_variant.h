@@ -4,6 +4,7 @@
 #include "ps_kernels.cuh"
 #include "ps_coop_rollout.cuh"
 #include <cstddef>
+#include <cstdlib>
 #include "ps_host_model.h"
 
 namespace ps {
@@ -87,13 +88,23 @@ inline int launch_coop(cudaStream_t st, const void* dconst, const double* knots,
   return grid;
 }
 
+#ifndef PS_SPARSE_BLOCKS_PER_SM_DEFAULT
+#define PS_SPARSE_BLOCKS_PER_SM_DEFAULT 0       // 0: one block per group of rollouts (no cap)
+#endif
 // thread-per-rollout launch of the compressed-Jacobian phases (sparse_rollout_kernel)
 template <class T, int BLOCK>
 inline int launch_sparse(cudaStream_t st, const void* dconst, const double* knots, int stride, int first, int n,
                          long long offset, double* returns, unsigned char* failure, MinLoc* block_min, Writeback wb, bool writeback,
                          int* counter) {
   (void)counter;
-  const int block = pick_block(n, BLOCK), grid = (n + block - 1) / block;
+  const int block = pick_block(n, BLOCK); int grid = (n + block - 1) / block;
+  // PS_SPARSE_BLOCKS_PER_SM (diagnostics / tuning): cap the grid at that many blocks per SM; the kernel strides over the batch
+  static const int per_sm = std::getenv("PS_SPARSE_BLOCKS_PER_SM") ? std::atoi(std::getenv("PS_SPARSE_BLOCKS_PER_SM")) : PS_SPARSE_BLOCKS_PER_SM_DEFAULT;
+  if (per_sm > 0) {
+    static int sms = 0;
+    if (!sms) { int dev = 0; cudaGetDevice(&dev); cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev); if (sms <= 0) sms = 148; }
+    if (grid > sms * per_sm) grid = sms * per_sm;
+  }
   const Constants<T>* c = reinterpret_cast<const Constants<T>*>(dconst);
   if (writeback) sparse_rollout_kernel<T, BLOCK, true><<<grid, block, 0, st>>>(c, knots, stride, first, n, offset, returns, failure, block_min, wb);
   else sparse_rollout_kernel<T, BLOCK, false><<<grid, block, 0, st>>>(c, knots, stride, first, n, offset, returns, failure, block_min, wb);
@@ -109,7 +120,9 @@ struct Variant {
   int (*plan)(void*, const double*, int, const double*, int, double, const double*, int, int, int);
   int (*launch)(cudaStream_t, const void*, const double*, int, int, int, long long, double*, unsigned char*, MinLoc*, Writeback, bool, int*);
   int (*robust)(cudaStream_t, const void*, const double*, int, int, double*, unsigned char*, Writeback, XfrcNoise);   // null: no force perturbations
-  int (*task_ok)(const DevTask&, int) = nullptr;   // model-specialised instantiations: was the kernel compiled for this cost specification?
+  int (*task_ok)(const DevTask&, int) = nullptr;
+  // re-roll of the samples that overflowed this kernel's contact / row capacity (null: the class has no contacts or no larger class)
+  void (*fixup)(cudaStream_t, const void*, const double*, int, double*, unsigned char*, const int*, const int*, Writeback, bool) = nullptr;   // model-specialised instantiations: was the kernel compiled for this cost specification?
 };
 // the force-perturbed kernels live in their own translation unit (ps_variant_robust.cu), so that the code
 // generated for the planning kernels of a variant's unit does not depend on them
@@ -145,6 +158,8 @@ template <class T, int BLOCK>
 inline Variant make_sparse_variant(const char* name) {
   return Variant{name, sizeof(Constants<T>), offsetof(Constants<T>, p), sizeof(DevPlan<T>), BLOCK, true, true, fill_model<T>, set_options<T>, set_debug<T>, set_task<T>, set_plan<T>, launch_sparse<T, BLOCK>, nullptr};
 }
+// capacity-overflow re-rolls of the legged class (ps_variant_legged_xl.cu)
+void launch_fixup_legged(cudaStream_t, const void*, const double*, int, double*, unsigned char*, const int*, const int*, Writeback, bool);
 const Variant* variant_planar_sparse();
 const Variant* variant_legged_sparse();
 const Variant* variant_tiny_coop();

@@ -4,5 +4,5 @@
 #define PS_SPARSE_BLOCK 128
 #endif
 namespace ps {
-const Variant* variant_legged_sparse() { static const Variant v = make_sparse_variant<LeggedCoopT, PS_SPARSE_BLOCK>("legged_sparse"); return &v; }
+const Variant* variant_legged_sparse() { static const Variant v = [] { Variant x = make_sparse_variant<LeggedCoopT, PS_SPARSE_BLOCK>("legged_sparse"); x.fixup = launch_fixup_legged; return x; }(); return &v; }
 }  // namespace ps

@@ -132,3 +132,12 @@ void mmo_get_trajectory(void* hp, int i, double* states, double* actions, double
 }
 
 }  // extern "C"
+
+#ifdef MM_COUNT_FLOPS
+// libmm_oracle_flops.so only (oracle/flopcount.h): the tally of FP64 operations since the last reset
+FlopCounter g_flops;
+extern "C" void mmo_flops_reset(void) { g_flops = FlopCounter(); }
+extern "C" void mmo_flops(long long* out /*[5]: add, mul, div, sqrt, special*/) {
+  out[0] = g_flops.add; out[1] = g_flops.mul; out[2] = g_flops.div; out[3] = g_flops.sqrt_; out[4] = g_flops.special;
+}
+#endif

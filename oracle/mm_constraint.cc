@@ -98,7 +98,7 @@ void makeConstraint(const Model* m, Data* d) {
       addRow(d, nv, Jc.data(), con.dist, con.includemargin, 0, CNSTR_CONTACT_FRICTIONLESS, ci);
     } else if (m->opt_cone == PS_CONE_ELLIPTIC) {
       for (int r = 0; r < dim; r++)
-        addRow(d, nv, Jc.data() + r * nv, r == 0 ? con.dist : 0, r == 0 ? con.includemargin : 0, 0, CNSTR_CONTACT_ELLIPTIC, ci);
+        addRow(d, nv, Jc.data() + r * nv, r == 0 ? con.dist : double(0), r == 0 ? con.includemargin : double(0), 0, CNSTR_CONTACT_ELLIPTIC, ci);
     } else {
       for (int r = 1; r < dim; r++)
         for (int s = 0; s < 2; s++) {

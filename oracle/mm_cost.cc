@@ -38,7 +38,7 @@ void splineSample(const double* times, const double* knots, int P, int dim, int 
 }
 
 double normValue(const double* x, const double* params, int n, int type) {
-  double y = 0, p = params ? params[0] : 0, q = params ? params[1] : 0;
+  double y = 0, p = params ? params[0] : double(0), q = params ? params[1] : double(0);
   switch (type) {
     case -1: y = x[0]; break;
     case 0: for (int i = 0; i < n; i++) y += x[i] * x[i]; y *= 0.5; break;
@@ -49,7 +49,7 @@ double normValue(const double* x, const double* params, int n, int type) {
     case 5: for (int i = 0; i < n; i++) y += std::pow(std::fabs(x[i]), p); break;
     case 6: for (int i = 0; i < n; i++) y += std::sqrt(x[i] * x[i] + p * p) - p; break;
     case 7: for (int i = 0; i < n; i++) { double e = std::pow(std::fabs(x[i]), q) + std::pow(p, q); y += std::pow(e, 1 / q) - p; } break;
-    case 8: for (int i = 0; i < n; i++) { if (p > 0) y += p * std::log(1 + std::exp(x[i] / p)); else y += x[i] > 0 ? x[i] : 0; } break;
+    case 8: for (int i = 0; i < n; i++) { if (p > 0) y += p * std::log(1 + std::exp(x[i] / p)); else y += x[i] > 0 ? x[i] : double(0); } break;
     default: break;
   }
   return y;
@@ -58,7 +58,7 @@ double normValue(const double* x, const double* params, int n, int type) {
 void costTerms(const PsTask* t, const double* residual, double* terms, bool weighted) {
   int fs = 0, ps = 0;
   for (int k = 0; k < t->num_term; k++) {
-    terms[k] = (weighted ? t->weight[k] : 1) * normValue(residual + fs, t->norm_parameter + ps, t->dim_norm_residual[k], t->norm[k]);
+    terms[k] = (weighted ? t->weight[k] : double(1)) * normValue(residual + fs, t->norm_parameter + ps, t->dim_norm_residual[k], t->norm[k]);
     fs += t->dim_norm_residual[k]; ps += t->num_norm_parameter[k];
   }
 }

@@ -158,7 +158,7 @@ double stepHeight(double time, double footphase, double duty_ratio) {
     angle *= 0.5 / (1 - duty_ratio);
     value = cosDet(clip(angle, -kPi / 2, kPi / 2));
   }
-  return std::fabs(value) < 1e-6 ? 0.0 : value;
+  return std::fabs(value) < 1e-6 ? double(0.0) : value;
 }
 
 // quadruped.cc:681-697
@@ -243,7 +243,7 @@ void quadrupedResidual(const Model* m, const Data* d, const PsTask* t, double* r
   else { target[0] = goal_pos[0]; target[1] = goal_pos[1]; target[2] = goal_pos[2]; }
   residual[counter++] = head[0] - target[0];
   residual[counter++] = head[1] - target[1];
-  residual[counter++] = s.mode == kModeScramble ? 2 * (head[2] - target[2]) : 0;
+  residual[counter++] = s.mode == kModeScramble ? 2 * (head[2] - target[2]) : double(0);
 
   // ---------- Gait ----------
   const int gait = s.mode == kModeBiped ? kGaitTrot : s.gait;
@@ -271,8 +271,8 @@ void quadrupedResidual(const Model* m, const Data* d, const PsTask* t, double* r
     const double ground_height = ground(m, d, query);
     const double height_target = ground_height + kFootRadius + step[f];
     double diff = foot_pos[f][2] - height_target;
-    if (s.mode == kModeScramble) diff = diff < 0 ? diff : 0;      // mju_min(0, diff)
-    residual[counter++] = step[f] ? diff : 0;
+    if (s.mode == kModeScramble) diff = diff < 0 ? diff : double(0);      // mju_min(0, diff)
+    residual[counter++] = step[f] ? diff : double(0);
   }
 
   // ---------- Balance ----------

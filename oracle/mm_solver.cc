@@ -51,7 +51,7 @@ static double constraintUpdate(const Model* m, Data* d, const double* jar, bool 
           H[0] = 1;
           for (int j = 1; j < dim; j++) H[j] = H[j * dim] = -mu * U[j] / T;
           double s1 = mu * N / (T * T * T), s2 = mu * mu - mu * N / T;
-          for (int k = 1; k < dim; k++) for (int j = 1; j < dim; j++) H[k * dim + j] = s1 * U[j] * U[k] + (k == j ? s2 : 0.0);
+          for (int k = 1; k < dim; k++) for (int j = 1; j < dim; j++) H[k * dim + j] = s1 * U[j] * U[k] + (k == j ? s2 : double(0.0));
           for (int k = 0; k < dim; k++) for (int j = 0; j < dim; j++)
             H[k * dim + j] *= Dm * (k == 0 ? mu : fr[k - 1]) * (j == 0 ? mu : fr[j - 1]);
         }
@@ -183,7 +183,7 @@ static double lineSearch(const Model* m, Data* d, Ctx& c) {
   evalLine(m, d, c, qg, alpha, &cc, &dd, &hh);
   for (int it = 0; it < m->opt_ls_iterations && std::fabs(dd) >= gtol; it++) {
     if (dd < 0) lo = alpha; else hi = alpha;
-    double an = hh > 0 ? alpha - dd / hh : -1;
+    double an = hh > 0 ? alpha - dd / hh : double(-1);
     if (hi < 0) { if (!(an > lo)) an = 2 * alpha; }
     else if (!(an > lo && an < hi)) an = 0.5 * (lo + hi);
     alpha = an;

@@ -47,7 +47,7 @@ void rne(const Model* m, Data* d, const double* qvel, double* result) {
   }
   std::vector<double> cacc(6 * nb, 0.0), cfrc(6 * nb, 0.0);
   bool grav = !(m->opt_disableflags & PS_DSBL_GRAVITY);
-  for (int k = 0; k < 3; k++) cacc[3 + k] = grav ? -m->opt_gravity[k] : 0.0;
+  for (int k = 0; k < 3; k++) cacc[3 + k] = grav ? -m->opt_gravity[k] : double(0.0);
   for (int i = 1; i < nb; i++) {
     int bda = m->body_dofadr[i];
     double* ca = &cacc[6 * i]; copy(ca, &cacc[6 * m->body_parentid[i]], 6);

@@ -54,6 +54,33 @@ def test_model_specialised_source_matches_oracle(hostsim_lib, name, H, sigma):
     check(name, H, N=4, sigma=sigma, spec="tiny_" + name)
 
 
+def test_capacity_overflow_is_rolled_again_at_large_capacity(hostsim_lib):
+    """A quadruped lying on its side has 28 contacts / 102 rows -- beyond the scoring kernels' 24 contacts.  The engine's
+    fix-up pass re-rolls such samples at the LeggedXLT capacities (64 / 256); that instantiation must equal the oracle
+    (which has no capacity at all) bit for bit, like every other one."""
+    m, t, s = registry.load("Quadruped Flat")
+    T.quadruped_snapshot(m, t, mode="Quadruped", gait="Trot", time=0.0)
+    st = fallen_quadruped_state(m)
+    P, interp, H = min(s["num_spline_points"], 36), 2, 31
+    rng = np.random.default_rng(4)
+    for trial in range(2):
+        kn = rng.normal(0, 0.3, (P, m.nu)); nt = np.linspace(0.0, 0.3, P)
+        o = pyoracle.Oracle(m, t); o.configure(P, interp, 0.0); o.set_state(st, 0.0); o.set_policy(nt, kn, interp)
+        o.optimize(1, H, np.zeros((1, P, m.nu)))
+        ot = o.trajectory(0)
+        _, knots_used = o.policy(2)
+        h = driver.rollout(m, t, st, 0.0, o.policy(1)[0], knots_used, interp, H, s["timestep"], s["integrator"], coop=True)
+        assert "legged_xl" in h["variant"], h["variant"]
+        assert h["flags"] == 0
+        assert np.array_equal(h["states"], ot["states"]) and np.array_equal(h["residual"], ot["residual"]) and h["total"] == ot["total_return"]
+
+
+def fallen_quadruped_state(m):
+    st = registry.home_state(m)
+    st[2] = 0.12; st[3:7] = [np.cos(np.pi / 4), np.sin(np.pi / 4), 0.0, 0.0]       # on its side, just above the floor
+    return st
+
+
 def test_model_specialisation_rejects_other_models(hostsim_lib):
     m, t, s = registry.load("Cartpole")
     m.v["jnt_limited"] = np.array([1, 1], dtype=np.int32); m._c = None
