@@ -48,7 +48,7 @@ def main():
     print(f"{a.task}: N={N} H={H} variant={e.variant()}  writeback record {per_step} doubles / sample-step, {total / 1e6:.1f} MB per launch")
     print(f"  rollout kernel {out[False]:.3f} ms cost-only, {out[True]:.3f} ms with writeback (+ the memset of the buffers is outside the kernel)")
     print(f"  writeback alone would need {total / 6.5e12 * 1e3:.3f} ms at the measured copy bandwidth (6.5 TB/s); it costs {extra:.3f} ms "
-          f"= {total / max(extra, 1e-6) / 1e9:.0f} GB/s effective, {total / out[True] / 1e6:.0f} GB/s averaged over the whole kernel")
+          f"= {total / max(extra * 1e-3, 1e-9) / 1e9:.0f} GB/s marginal, {total / (out[True] * 1e-3) / 1e9:.0f} GB/s averaged over the whole kernel")
     e.close()
 
 
