@@ -26,6 +26,10 @@ struct Lanes1 {
   PS_HD bool any(bool p) const { return p; }
   PS_HD int scan(int v, int* total) const { *total = v; return 0; }
   PS_HD int min(int v) const { return v; }
+  // block-level lockstep hooks (Lanes1Block below): trivial for every other lane type
+  static constexpr bool kBlock = false;
+  PS_HD bool block_any(bool p) const { return p; }
+  PS_HD void block_sync() const {}
 };
 
 #ifdef __CUDACC__
@@ -50,6 +54,19 @@ struct Lanes {
     for (int o = 16; o > 0; o >>= 1) { const int t = __shfl_xor_sync(0xffffffffu, v, o); v = t < v ? t : v; }
     return v;
   }
+  static constexpr bool kBlock = false;
+  __device__ __forceinline__ bool block_any(bool p) const { return p; }
+  __device__ __forceinline__ void block_sync() const {}
+};
+// One working lane per rollout (thread-per-rollout kernel) whose BLOCK walks the time steps, the stages of a step and the
+// Newton iterations of the constraint solver in lockstep.  That kernel is bound by instruction delivery (ncu: GPC
+// instruction-cache requests at 57 % of peak with 16 warps per SM each somewhere else in ~370 KB of code per step); warps
+// that execute the same stage at the same time share the SM's instruction cache lines.  Only control flow changes: a
+// rollout whose solver has converged idles at the barrier until the block's slowest one has, arithmetic is untouched.
+struct Lanes1Block : Lanes1 {
+  static constexpr bool kBlock = true;
+  __device__ __forceinline__ bool block_any(bool p) const { return __syncthreads_or(p) != 0; }
+  __device__ __forceinline__ void block_sync() const { __syncthreads(); }
 };
 #else
 typedef Lanes1 Lanes;
@@ -71,6 +88,11 @@ typedef Lanes1 Lanes;
 #define PS_LOOP2
 #endif
 #define CO_FOR(i, n) PS_LOOP_PRAGMA for (int i = L.lane; i < (n); i += L.width)
+// parallel-for over the pairs (a, k) of [0, A) x [0, K), row-major (w = a K + k).  A single working lane walks them with
+// counters -- no integer division per item (the thread-per-rollout kernel spent a visible share of its XU pipe on w / K, w % K)
+#define CO_FOR2(w, A, a, K, k)                                                                                     \
+  PS_LOOP_PRAGMA for (int w = L.lane, a = LT::single ? 0 : w / (K), k = LT::single ? 0 : w % (K); w < (A) * (K);           \
+                      w += L.width, LT::single ? (++k == (K) ? (k = 0, ++a) : 0) : (a = w / (K), k = w % (K)))
 // all lanes walk [0, n) in rounds of `width`; lanes past the end still take part in collectives
 #define CO_ROUNDS(base, n) PS_LOOP_PRAGMA for (int base = 0; base < (n); base += L.width)
 

@@ -14,23 +14,32 @@ namespace ps {
 // lanes a stage runs on: all of them, or (diagnostics) a single working lane
 PS_HD Lanes1 stage_lanes(const Lanes1& L, int, int) { return L; }
 #ifdef __CUDACC__
+__device__ __forceinline__ Lanes1Block stage_lanes(const Lanes1Block& L, int, int) { return L; }
 __device__ __forceinline__ Lanes stage_lanes(const Lanes& L, int debug_serial, int stage) {
   if ((debug_serial >> stage) & 1) { Lanes S; S.lane = L.lane == 0 ? 0 : (1 << 28); S.width = 1; return S; }
   return L;
 }
 #endif
 
+// `active` = the rollout is still alive.  Under block lockstep (LT::kBlock) a dead rollout keeps walking the stage
+// sequence -- doing nothing -- so that the block's barriers stay matched; for every other lane type the caller only gets
+// here with active == true or skips the stages altogether.
 template <class T, class LT>
-PS_FN void co_forward_pass(const LT& L, const DevModel<T>& m, CoopData<T>& d) {
+PS_FN void co_forward_pass(const LT& L, const DevModel<T>& m, CoopData<T>& d, bool active = true) {
   const int dbg = m.debug_serial;
-  co_position_smooth(stage_lanes(L, dbg, 0), m, d);
-  co_make_constraints(stage_lanes(L, dbg, 1), m, d);
-  co_velocity_stage(stage_lanes(L, dbg, 2), m, d);
-  co_reference_acceleration(stage_lanes(L, dbg, 3), m, d);
-  if (m.need_subtreevel) co_subtree_velocity(stage_lanes(L, dbg, 4), m, d);
-  co_actuation_stage(stage_lanes(L, dbg, 5), m, d);
-  co_acceleration_stage(stage_lanes(L, dbg, 6), m, d);
-  co_constraint_stage(stage_lanes(L, dbg, 7), m, d);
+  if (active) co_position_smooth(stage_lanes(L, dbg, 0), m, d);
+  L.block_sync();
+  if (active) co_make_constraints(stage_lanes(L, dbg, 1), m, d);
+  L.block_sync();
+  if (active) {
+    co_velocity_stage(stage_lanes(L, dbg, 2), m, d);
+    co_reference_acceleration(stage_lanes(L, dbg, 3), m, d);
+    if (m.need_subtreevel) co_subtree_velocity(stage_lanes(L, dbg, 4), m, d);
+    co_actuation_stage(stage_lanes(L, dbg, 5), m, d);
+    co_acceleration_stage(stage_lanes(L, dbg, 6), m, d);
+  }
+  L.block_sync();
+  co_constraint_stage(stage_lanes(L, dbg, 7), m, d, active);
 }
 
 // forward pass under Cartesian perturbation forces (robust re-rolls only)
@@ -111,24 +120,30 @@ PS_FN void co_integrate(const LT& L, const DevModel<T>& m, CoopData<T>& d) {
 // knots: SoA [P*nu][stride]; i = this rollout's column.  flags: bit0 failure, bit1 capacity overflow
 template <class T, bool WB, class LT, class PT = CoPerturbation<T, false>>
 PS_FN double co_rollout(const LT& L, const DevModel<T>& m, const DevTask& task, const DevPlan<T>& plan, const double* knots,
-                        int stride, int i, const Writeback& wb, CoopData<T>& d, int* flags, const PT pert = PT()) {
+                        int stride, int i, const Writeback& wb, CoopData<T>& d, int* flags, const PT pert = PT(), bool live = true) {
+  // `live` = false: a padding thread of a block that walks in lockstep (LT::kBlock) -- it takes part in the block's
+  // barriers and touches nothing else.  A rollout that fails stops working but, under lockstep, keeps pace the same way;
+  // for every other lane type the remaining time steps of a dead rollout are an empty loop.
   const int nq = m.nq, nv = m.nv, na = m.na, nu = m.nu, ns = nq + nv + na, nr = task.num_residual;
   const int H = plan.horizon, P = plan.num_spline_points, ntr = 3 * task.num_trace;
-  CO_FOR(k, nq) d.qpos[k] = plan.state[k];
-  CO_FOR(k, nv) { d.qvel[k] = plan.state[nq + k]; d.qacc_warmstart[k] = 0; d.qacc[k] = 0; }
-  CO_FOR(k, na) d.act[k] = plan.state[nq + nv + k];
-  CO_FOR(k, nu) d.ctrl[k] = 0;
-  CO_FOR(k, m.nmocap) { vcopy(d.mocap_pos + 3 * k, plan.mocap + 7 * k, 3); vcopy(d.mocap_quat + 4 * k, plan.mocap + 7 * k + 3, 4); }
-  if (L.lane == 0) { d.time = plan.time; d.warning = 0; d.ncon = 0; d.nefc = 0; d.nlimit = 0; d.solver_iter = 0; }
-  if (WB) { CO_FOR(k, ns) wb.states[(size_t)k * stride + i] = plan.state[k]; if (L.lane == 0) wb.times[i] = plan.time; }
-  L.sync();
-  if constexpr (PT::kActive) pert.reset(L, m);
+  if (live) {
+    CO_FOR(k, nq) d.qpos[k] = plan.state[k];
+    CO_FOR(k, nv) { d.qvel[k] = plan.state[nq + k]; d.qacc_warmstart[k] = 0; d.qacc[k] = 0; }
+    CO_FOR(k, na) d.act[k] = plan.state[nq + nv + k];
+    CO_FOR(k, nu) d.ctrl[k] = 0;
+    CO_FOR(k, m.nmocap) { vcopy(d.mocap_pos + 3 * k, plan.mocap + 7 * k, 3); vcopy(d.mocap_quat + 4 * k, plan.mocap + 7 * k + 3, 4); }
+    if (L.lane == 0) { d.time = plan.time; d.warning = 0; d.ncon = 0; d.nefc = 0; d.nlimit = 0; d.solver_iter = 0; }
+    if (WB) { CO_FOR(k, ns) wb.states[(size_t)k * stride + i] = plan.state[k]; if (L.lane == 0) wb.times[i] = plan.time; }
+    L.sync();
+    if constexpr (PT::kActive) pert.reset(L, m);
+  }
   const double* kcol = knots + i;
-  double sum = 0; bool failed = false;
+  double sum = 0; bool failed = false, dead = !live;
 
   PS_LOOP2 for (int t = 0; t < H; t++) {
     const bool terminal = t == H - 1;
-    if (!terminal) {
+    L.block_sync();
+    if (!terminal && !dead) {
       // policy: spline sample + clamp, one lane per actuator
       const double time = d.time;
       CO_FOR(a, nu) {
@@ -141,42 +156,50 @@ PS_FN double co_rollout(const LT& L, const DevModel<T>& m, const DevTask& task, 
       CO_FOR(k, nq) bad = bad || bad_number(d.qpos[k]);
       CO_FOR(k, nv) bad = bad || bad_number(d.qvel[k]);
       L.sync();
-      if (L.any(bad)) { failed = true; if (WB) { CO_FOR(a, nu) wb.actions[((size_t)t * nu + a) * stride + i] = d.ctrl[a]; } break; }
+      if (L.any(bad)) { failed = true; dead = true; if (WB) { CO_FOR(a, nu) wb.actions[((size_t)t * nu + a) * stride + i] = d.ctrl[a]; } }
     }
-    if (WB && (!terminal || H > 1)) CO_FOR(a, nu) wb.actions[((size_t)t * nu + a) * stride + i] = d.ctrl[a];
-    if constexpr (PT::kActive) pert.forward(L, m, d); else co_forward_pass(L, m, d);
-    if (L.lane == 0) {
-      task_residual(m, d, task, d.residual);
-      d.sc_cost = cost_value(task, d.residual);
-    }
-    L.sync();
-    const double c = d.sc_cost;
-    if (WB) {
-      CO_FOR(k, nr) wb.residual[((size_t)t * nr + k) * stride + i] = d.residual[k];
+    if (!LT::kBlock && dead) break;
+    if (WB && !dead && (!terminal || H > 1)) CO_FOR(a, nu) wb.actions[((size_t)t * nu + a) * stride + i] = d.ctrl[a];
+    if constexpr (PT::kActive) { if (!dead) pert.forward(L, m, d); } else co_forward_pass(L, m, d, !dead);
+    if (!dead) {
       if (L.lane == 0) {
-        wb.costs[(size_t)t * stride + i] = c;
-        PS_LOOP2 for (int k = 0; k < task.num_trace; k++) {
-          double tr[3]; read_sensor(m, d, task.trace_sensor[k], tr);
-          PS_LOOP2 for (int x = 0; x < 3; x++) wb.trace[((size_t)t * ntr + 3 * k + x) * stride + i] = tr[x];
+        task_residual(m, d, task, d.residual);
+        d.sc_cost = cost_value(task, d.residual);
+      }
+      L.sync();
+      const double c = d.sc_cost;
+      if (WB) {
+        CO_FOR(k, nr) wb.residual[((size_t)t * nr + k) * stride + i] = d.residual[k];
+        if (L.lane == 0) {
+          wb.costs[(size_t)t * stride + i] = c;
+          PS_LOOP2 for (int k = 0; k < task.num_trace; k++) {
+            double tr[3]; read_sensor(m, d, task.trace_sensor[k], tr);
+            PS_LOOP2 for (int x = 0; x < 3; x++) wb.trace[((size_t)t * ntr + 3 * k + x) * stride + i] = tr[x];
+          }
+        }
+      }
+      if (terminal) sum += c;
+      else {
+        bool badacc = false;
+        CO_FOR(k, nv) badacc = badacc || bad_number(d.qacc[k]);
+        if (L.any(badacc) || (d.warning & (WARN_BADQPOS | WARN_BADQVEL | WARN_BADQACC | WARN_BADCTRL))) { failed = true; dead = true; }
+        else {
+          sum += c;
+          co_integrate(stage_lanes(L, m.debug_serial, 8), m, d);
+          if (WB) {
+            double* s = wb.states + ((size_t)(t + 1) * ns) * stride + i;
+            CO_FOR(k, nq) s[(size_t)k * stride] = d.qpos[k];
+            CO_FOR(k, nv) s[(size_t)(nq + k) * stride] = d.qvel[k];
+            CO_FOR(k, na) s[(size_t)(nq + nv + k) * stride] = d.act[k];
+            if (L.lane == 0) wb.times[(size_t)(t + 1) * stride + i] = d.time;
+          }
         }
       }
     }
-    if (terminal) { sum += c; break; }
-    bool badacc = false;
-    CO_FOR(k, nv) badacc = badacc || bad_number(d.qacc[k]);
-    if (L.any(badacc) || (d.warning & (WARN_BADQPOS | WARN_BADQVEL | WARN_BADQACC | WARN_BADCTRL))) { failed = true; break; }
-    sum += c;
-    co_integrate(stage_lanes(L, m.debug_serial, 8), m, d);
-    if (WB) {
-      double* s = wb.states + ((size_t)(t + 1) * ns) * stride + i;
-      CO_FOR(k, nq) s[(size_t)k * stride] = d.qpos[k];
-      CO_FOR(k, nv) s[(size_t)(nq + k) * stride] = d.qvel[k];
-      CO_FOR(k, na) s[(size_t)(nq + nv + k) * stride] = d.act[k];
-      if (L.lane == 0) wb.times[(size_t)(t + 1) * stride + i] = d.time;
-    }
+    if (!LT::kBlock && dead) break;
   }
   const double total = failed ? 1.0e6 : sum / (H > 1 ? H : 1);
-  *flags = (failed ? 1 : 0) | ((d.warning & WARN_CAPACITY) ? 2 : 0);
+  *flags = !live ? 0 : ((failed ? 1 : 0) | ((d.warning & WARN_CAPACITY) ? 2 : 0));
   L.sync();
   return total;
 }
@@ -204,7 +227,7 @@ coop_rollout_kernel(const Constants<T>* __restrict__ gconst, const double* __res
     constexpr uint32_t total = (uint32_t)sizeof(Constants<T>);
     mbar_expect_tx(&bar, total);
     const char* src = reinterpret_cast<const char*>(gconst); char* dst = reinterpret_cast<char*>(&sc);
-    PS_LOOP2 for (uint32_t off = 0; off < total; off += 32768u) {
+    for (uint32_t off = 0; off < total; off += 32768u) {
       const uint32_t sz = total - off < 32768u ? total - off : 32768u;
       tma_bulk_g2s(dst + off, src + off, sz, &bar);
     }
@@ -254,7 +277,7 @@ coop_robust_kernel(const Constants<T>* __restrict__ gconst, const double* __rest
     constexpr uint32_t total = (uint32_t)sizeof(Constants<T>);
     mbar_expect_tx(&bar, total);
     const char* src = reinterpret_cast<const char*>(gconst); char* dst = reinterpret_cast<char*>(&sc);
-    PS_LOOP2 for (uint32_t off = 0; off < total; off += 32768u) {
+    for (uint32_t off = 0; off < total; off += 32768u) {
       const uint32_t sz = total - off < 32768u ? total - off : 32768u;
       tma_bulk_g2s(dst + off, src + off, sz, &bar);
     }
@@ -276,6 +299,9 @@ coop_robust_kernel(const Constants<T>* __restrict__ gconst, const double* __rest
 // the cooperative engine, SIMD across rollouts.  Its working set sits in local memory, so it needs
 // tens of thousands of rollouts in flight to hide that latency -- the large-batch engine, where the
 // warp-per-rollout kernel above is the small-batch (latency) engine.
+#ifndef PS_SPARSE_LOCKSTEP
+#define PS_SPARSE_LOCKSTEP 1
+#endif
 #ifndef PS_SPARSE_RESIDENT
 #define PS_SPARSE_RESIDENT 512          // threads the register cap keeps resident per SM
 #endif
@@ -293,7 +319,7 @@ sparse_rollout_kernel(const Constants<T>* __restrict__ gconst, const double* __r
     constexpr uint32_t total = (uint32_t)sizeof(Constants<T>);
     mbar_expect_tx(&bar, total);
     const char* src = reinterpret_cast<const char*>(gconst); char* dst = reinterpret_cast<char*>(&sc);
-    PS_LOOP2 for (uint32_t off = 0; off < total; off += 32768u) {
+    for (uint32_t off = 0; off < total; off += 32768u) {
       const uint32_t sz = total - off < 32768u ? total - off : 32768u;
       tma_bulk_g2s(dst + off, src + off, sz, &bar);
     }
@@ -302,13 +328,19 @@ sparse_rollout_kernel(const Constants<T>* __restrict__ gconst, const double* __r
   // grid-stride over the batch: the launch may use fewer blocks than the batch needs (launch_sparse: a bounded number of
   // resident rollouts per SM keeps their thread-private working sets inside L1 / L2), each block then rolls several groups
   double c = 1.0e300; long long gi = 0x7fffffffffffffffLL;
-  PS_LOOP2 for (int base = blockIdx.x * blockDim.x; base < n; base += gridDim.x * blockDim.x) {
+  for (int base = blockIdx.x * blockDim.x; base < n; base += gridDim.x * blockDim.x) {      // block-uniform trip count
     const int i = first + base + threadIdx.x;
-    if (i < first + n) {
-      int flags = 0;
-      CoopData<T> d;
-      Lanes1 L;
-      double total = co_rollout<T, WB>(L, sc.m, sc.t, sc.p, knots, stride, i, wb, d, &flags);
+    const bool live = i < first + n;
+    int flags = 0;
+    CoopData<T> d;
+#if PS_SPARSE_LOCKSTEP
+    Lanes1Block L;         // the block walks steps / stages / Newton iterations together (ps_coop.cuh); padding threads idle along
+    double total = co_rollout<T, WB, Lanes1Block>(L, sc.m, sc.t, sc.p, knots, stride, live ? i : first, wb, d, &flags, CoPerturbation<T, false>(), live);
+#else
+    Lanes1 L;
+    double total = live ? co_rollout<T, WB>(L, sc.m, sc.t, sc.p, knots, stride, i, wb, d, &flags) : 0.0;
+#endif
+    if (live) {
       returns[i] = total;
       failure[i] = (unsigned char)flags;
       if (!(total == total)) total = 1.0e300;
@@ -316,7 +348,7 @@ sparse_rollout_kernel(const Constants<T>* __restrict__ gconst, const double* __r
     }
   }
 #pragma unroll
-  PS_LOOP2 for (int o = 16; o > 0; o >>= 1) {
+  for (int o = 16; o > 0; o >>= 1) {
     const double oc = __shfl_down_sync(0xffffffffu, c, o);
     const long long oi = __shfl_down_sync(0xffffffffu, gi, o);
     if (better(oc, oi, c, gi)) { c = oc; gi = oi; }
@@ -324,7 +356,7 @@ sparse_rollout_kernel(const Constants<T>* __restrict__ gconst, const double* __r
   if ((threadIdx.x & 31) == 0) { warp_min[threadIdx.x >> 5].cost = c; warp_min[threadIdx.x >> 5].index = gi; }
   __syncthreads();
   if (threadIdx.x == 0) {
-    PS_LOOP2 for (int w = 1; w < (int)(blockDim.x >> 5); w++) if (better(warp_min[w].cost, warp_min[w].index, c, gi)) { c = warp_min[w].cost; gi = warp_min[w].index; }
+    for (int w = 1; w < (int)(blockDim.x >> 5); w++) if (better(warp_min[w].cost, warp_min[w].index, c, gi)) { c = warp_min[w].cost; gi = warp_min[w].index; }
     block_min[blockIdx.x].cost = c; block_min[blockIdx.x].index = gi;
   }
 }
@@ -332,17 +364,22 @@ sparse_rollout_kernel(const Constants<T>* __restrict__ gconst, const double* __r
 // ---------------------------------------------------------------- capacity-overflow fix-up
 // A rollout that ran out of the scoring kernel's contact / constraint-row capacity carries flag bit 1 and was scored with the
 // rows that fit.  The reference never truncates (mjpc/trajectory.cc:169-173: a rollout is valid or 1e6), so every flagged
-// sample is rolled again here -- thread per rollout over the same phases, instantiated at capacities (TXL) large enough for
-// a fallen robot, working set in local memory -- and its return / flags / trajectory replace the truncated ones before
-// the argmin.  `list` / `count` come from collect_flagged_kernel; with count == 0 (the usual case) the blocks exit at once.
-template <class TXL, int BLOCK, bool WB>
-__global__ void __launch_bounds__(BLOCK)
-sparse_fixup_kernel(const Constants<TXL>* __restrict__ gconst, const double* __restrict__ knots, int stride,
-                    double* __restrict__ returns, unsigned char* __restrict__ failure, const int* __restrict__ list,
-                    const int* __restrict__ count, Writeback wb) {
+// sample is rolled again here at capacities (TXL) large enough for a fallen robot, and its return / flags / trajectory
+// replace the truncated ones before the argmin.  Flagged samples are few and each one is latency bound, so this is the
+// warp-per-rollout coding (working set in shared memory, ~0.8 ms per step instead of the ~25 ms a lone thread needs):
+// persistent blocks pull entries of `list` (collect_flagged_kernel) through `counter` until `*count` are done; with
+// count == 0 -- the usual case -- every block exits before touching shared memory.
+template <class TXL, int WARPS, bool WB>
+__global__ void __launch_bounds__(WARPS * 32)
+coop_fixup_kernel(const Constants<TXL>* __restrict__ gconst, const double* __restrict__ knots, int stride,
+                  double* __restrict__ returns, unsigned char* __restrict__ failure, const int* __restrict__ list,
+                  const int* __restrict__ count, int* __restrict__ counter, Writeback wb) {
   const int n = *count;
-  if ((int)(blockIdx.x * blockDim.x) >= n) return;            // whole block has nothing to do (uniform: before any barrier)
-  __shared__ Constants<TXL> sc;
+  if ((int)(blockIdx.x * WARPS) >= n) return;                // nothing for this block (uniform: before any barrier)
+  extern __shared__ __align__(128) unsigned char smem[];
+  Constants<TXL>& sc = *reinterpret_cast<Constants<TXL>*>(smem);
+  constexpr size_t kConst = (sizeof(Constants<TXL>) + 127) / 128 * 128;
+  constexpr size_t kData = (sizeof(CoopData<TXL>) + 127) / 128 * 128;
   __shared__ alignas(8) uint64_t bar;
   if (threadIdx.x == 0) { mbar_init(&bar, 1); asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
   __syncthreads();
@@ -350,20 +387,24 @@ sparse_fixup_kernel(const Constants<TXL>* __restrict__ gconst, const double* __r
     constexpr uint32_t total = (uint32_t)sizeof(Constants<TXL>);
     mbar_expect_tx(&bar, total);
     const char* src = reinterpret_cast<const char*>(gconst); char* dst = reinterpret_cast<char*>(&sc);
-    PS_LOOP2 for (uint32_t off = 0; off < total; off += 32768u) {
+    for (uint32_t off = 0; off < total; off += 32768u) {
       const uint32_t sz = total - off < 32768u ? total - off : 32768u;
       tma_bulk_g2s(dst + off, src + off, sz, &bar);
     }
   }
   mbar_wait(&bar, 0);
-  PS_LOOP2 for (int j = blockIdx.x * blockDim.x + threadIdx.x; j < n; j += gridDim.x * blockDim.x) {
-    const int i = list[j];
+  const int warp = threadIdx.x >> 5;
+  Lanes L; L.lane = threadIdx.x & 31; L.width = 32;
+  CoopData<TXL>& d = *reinterpret_cast<CoopData<TXL>*>(smem + kConst + warp * kData);
+  for (;;) {
+    int k = 0;
+    if (L.lane == 0) k = atomicAdd(counter, 1);
+    k = __shfl_sync(0xffffffffu, k, 0);
+    if (k >= n) break;
+    const int i = list[k];
     int flags = 0;
-    CoopData<TXL> d;
-    Lanes1 L;
     const double total = co_rollout<TXL, WB>(L, sc.m, sc.t, sc.p, knots, stride, i, wb, d, &flags);
-    returns[i] = total;
-    failure[i] = (unsigned char)flags;
+    if (L.lane == 0) { returns[i] = total; failure[i] = (unsigned char)flags; }
   }
 }
 #endif

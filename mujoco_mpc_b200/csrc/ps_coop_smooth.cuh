@@ -84,8 +84,8 @@ template <class T, class LT>
 PS_NI void co_fold_children(const LT& L, const DevModel<T>& m, double* x, int n, bool include_world) { PS_ASSUME_SHARED(&m);
   PS_LOOP2 for (int l = m.nlevel - 2; l >= (include_world ? 0 : 1); l--) {
     const int a = m.level_adr[l], nb = m.level_adr[l + 1] - a;
-    CO_FOR(w, nb * n) {
-      const int p = m.level_body[a + w / n], k = w % n;
+    CO_FOR2(w, nb, bi, n, k) {
+      const int p = m.level_body[a + bi];
       double s = x[n * p + k];
       PS_LOOP2 for (int c = m.child_adr[p]; c < m.child_adr[p + 1]; c++) s += x[n * m.child_list[c] + k];
       x[n * p + k] = s;

@@ -122,8 +122,7 @@ PS_NI void co_newton_direction(const LT& L, const DevModel<T>& m, CoopData<T>& d
       const double Tn = sqrt(TT);
       const double Dm = d.efc_D[adr] / (mu * mu * (1 + mu * mu));
       const double s1 = mu * N / (Tn * Tn * Tn), s2 = mu * mu - mu * N / Tn;
-      CO_FOR(w, dim * dim) {
-        const int k = w / dim, j = w % dim;
+      CO_FOR2(w, dim, k, dim, j) {
         double h;
         if (k == 0 && j == 0) h = 1;
         else if (k == 0 || j == 0) h = -mu * U[k + j] / Tn;
@@ -131,8 +130,7 @@ PS_NI void co_newton_direction(const LT& L, const DevModel<T>& m, CoopData<T>& d
         d.sv_coneH[w] = h * (Dm * (k == 0 ? mu : fr[k - 1]) * (j == 0 ? mu : fr[j - 1]));
       }
       L.sync();
-      CO_FOR(w, dim * n) {
-        const int a = w / n, k = w % n;
+      CO_FOR2(w, dim, a, n, k) {
         double t = 0;
         PS_LOOP2 for (int b = 0; b < dim; b++) t += d.sv_coneH[a * dim + b] * J[b * NCH + k];
         d.sv_T[a * NCH + k] = t;
@@ -247,85 +245,113 @@ PS_NI void co_line_eval(const LT& L, const DevModel<T>& m, CoopData<T>& d, const
   *cost = f; *d1 = g; *d2 = h;
 }
 
+// `active` / block_any: see co_constraint_stage.  With block_any(p) == p this is mj_solNewton's exact line search as before:
+// Newton steps on the 1-D cost, bracketed, until |slope| < gtol or ls_iterations.
 template <class T, class LT>
-PS_NI double co_line_search(const LT& L, const DevModel<T>& m, CoopData<T>& d, const CoSolverScalars& c) { PS_ASSUME_SHARED(&m); if (LT::kSharedData) PS_ASSUME_SHARED(&d);
-  const int nv = m.nv, nefc = d.nefc;
-  const double snorm = sqrt(vdot(d.sv_search, d.sv_search, nv));
-  if (snorm < kMinVal) return 0;
-  const double scale = 1.0 / (m.meaninertia * (nv > 1 ? nv : 1));
-  const double gtol = m.tolerance * m.ls_tolerance * snorm / scale;
-  co_mul_M(L, m, d, d.sv_Mv, d.sv_search);
-  CO_FOR(r, nefc) d.sv_Jv[r] = co_row_dot(m, d, r, d.sv_search);
-  L.sync();
+PS_NI double co_line_search(const LT& L, const DevModel<T>& m, CoopData<T>& d, const CoSolverScalars& c, bool active = true) { PS_ASSUME_SHARED(&m); if (LT::kSharedData) PS_ASSUME_SHARED(&d);
+  const int nv = m.nv, nefc = active ? d.nefc : 0;
   double qg[3] = {c.gauss, 0, 0};
-  PS_LOOP2 for (int i = 0; i < nv; i++) { qg[1] += d.sv_search[i] * (d.sv_Ma[i] - d.qfrc_smooth[i]); qg[2] += 0.5 * d.sv_search[i] * d.sv_Mv[i]; }
-  double c0, d0, h0; co_line_eval(L, m, d, qg, 0, &c0, &d0, &h0);
-  if (!(h0 > 0) || d0 >= 0) return 0;
-  double lo = 0, hi = -1;
-  double alpha = -d0 / h0, cc, dd, hh;
-  co_line_eval(L, m, d, qg, alpha, &cc, &dd, &hh);
-  PS_LOOP2 for (int it = 0; it < m.ls_iterations && fabs(dd) >= gtol; it++) {
-    if (dd < 0) lo = alpha; else hi = alpha;
-    double an = hh > 0 ? alpha - dd / hh : -1;
-    if (hi < 0) { if (!(an > lo)) an = 2 * alpha; }
-    else if (!(an > lo && an < hi)) an = 0.5 * (lo + hi);
-    alpha = an;
-    co_line_eval(L, m, d, qg, alpha, &cc, &dd, &hh);
+  double gtol = 0, c0 = 0, lo = 0, hi = -1, alpha = 0, cc = 0, dd = 0, hh = 0;
+  bool go = false;
+  if (active) {
+    const double snorm = sqrt(vdot(d.sv_search, d.sv_search, nv));
+    if (snorm < kMinVal) active = false;
+    else {
+      const double scale = 1.0 / (m.meaninertia * (nv > 1 ? nv : 1));
+      gtol = m.tolerance * m.ls_tolerance * snorm / scale;
+      co_mul_M(L, m, d, d.sv_Mv, d.sv_search);
+      CO_FOR(r, nefc) d.sv_Jv[r] = co_row_dot(m, d, r, d.sv_search);
+      L.sync();
+      PS_LOOP2 for (int i = 0; i < nv; i++) { qg[1] += d.sv_search[i] * (d.sv_Ma[i] - d.qfrc_smooth[i]); qg[2] += 0.5 * d.sv_search[i] * d.sv_Mv[i]; }
+      double d0, h0; co_line_eval(L, m, d, qg, 0, &c0, &d0, &h0);
+      if (!(h0 > 0) || d0 >= 0) active = false;
+      else {
+        alpha = -d0 / h0;
+        co_line_eval(L, m, d, qg, alpha, &cc, &dd, &hh);
+        go = 0 < m.ls_iterations && fabs(dd) >= gtol;
+      }
+    }
   }
-  if (!(cc < c0)) return 0;
+  int it = 0;
+  while (L.block_any(go)) {
+    if (go) {
+      if (dd < 0) lo = alpha; else hi = alpha;
+      double an = hh > 0 ? alpha - dd / hh : -1;
+      if (hi < 0) { if (!(an > lo)) an = 2 * alpha; }
+      else if (!(an > lo && an < hi)) an = 0.5 * (lo + hi);
+      alpha = an;
+      co_line_eval(L, m, d, qg, alpha, &cc, &dd, &hh);
+      it++;
+      go = it < m.ls_iterations && fabs(dd) >= gtol;
+    }
+  }
+  if (!active || !(cc < c0)) return 0;
   return alpha;
 }
 
 template <class T, class LT>
-PS_NI void co_constraint_stage(const LT& L, const DevModel<T>& m, CoopData<T>& d) { PS_ASSUME_SHARED(&m); if (LT::kSharedData) PS_ASSUME_SHARED(&d);
-  const int nv = m.nv, nefc = d.nefc;
-  if (!nefc) {
+PS_NI void co_constraint_stage(const LT& L, const DevModel<T>& m, CoopData<T>& d, bool active = true) { PS_ASSUME_SHARED(&m); if (LT::kSharedData) PS_ASSUME_SHARED(&d);
+  // `active`: this rollout is still alive.  Under block lockstep (LT::kBlock) every thread of the block walks the Newton
+  // loop together -- block_any() is a block-wide OR -- and a thread without work idles; for every other lane type
+  // block_any(p) == p and the loop below is the plain `while (iter < iterations) { ... break ... }` of mj_solNewton.
+  const int nv = m.nv, nefc = active ? d.nefc : 0;
+  const bool run = active && nefc > 0;
+  if (active && !nefc) {
     CO_FOR(i, nv) { d.qacc[i] = d.qacc_smooth[i]; d.qacc_warmstart[i] = d.qacc_smooth[i]; d.qfrc_constraint[i] = 0; }
     if (L.lane == 0) d.solver_iter = 0;
     L.sync();
-    return;
   }
   CoSolverScalars c; c.cost = 0; c.prev_cost = 0; c.gauss = 0;
-  if (!(m.disableflags & DSBL_WARMSTART)) {
-    // keep the warm start only if it beats the unconstrained acceleration
-    CO_FOR(i, nv) d.qacc[i] = d.qacc_warmstart[i];
-    L.sync();
+  if (run) {
+    if (!(m.disableflags & DSBL_WARMSTART)) {
+      // keep the warm start only if it beats the unconstrained acceleration
+      CO_FOR(i, nv) d.qacc[i] = d.qacc_warmstart[i];
+      L.sync();
+      co_mul_M(L, m, d, d.sv_Ma, d.qacc);
+      CO_FOR(r, nefc) d.sv_Jaref[r] = co_row_dot(m, d, r, d.qacc) - d.efc_aref[r];
+      L.sync();
+      double cw = co_update_rows(L, m, d, d.sv_Jaref);
+      PS_LOOP2 for (int i = 0; i < nv; i++) cw += 0.5 * (d.sv_Ma[i] - d.qfrc_smooth[i]) * (d.qacc[i] - d.qacc_smooth[i]);
+      L.sync();
+      CO_FOR(r, nefc) d.sv_Jv[r] = co_row_dot(m, d, r, d.qacc_smooth) - d.efc_aref[r];
+      L.sync();
+      const double cs = co_update_rows(L, m, d, d.sv_Jv);
+      L.sync();
+      if (cw > cs) { CO_FOR(i, nv) d.qacc[i] = d.qacc_smooth[i]; }
+      L.sync();
+    } else { CO_FOR(i, nv) d.qacc[i] = d.qacc_smooth[i]; L.sync(); }
     co_mul_M(L, m, d, d.sv_Ma, d.qacc);
     CO_FOR(r, nefc) d.sv_Jaref[r] = co_row_dot(m, d, r, d.qacc) - d.efc_aref[r];
     L.sync();
-    double cw = co_update_rows(L, m, d, d.sv_Jaref);
-    PS_LOOP2 for (int i = 0; i < nv; i++) cw += 0.5 * (d.sv_Ma[i] - d.qfrc_smooth[i]) * (d.qacc[i] - d.qacc_smooth[i]);
-    L.sync();
-    CO_FOR(r, nefc) d.sv_Jv[r] = co_row_dot(m, d, r, d.qacc_smooth) - d.efc_aref[r];
-    L.sync();
-    const double cs = co_update_rows(L, m, d, d.sv_Jv);
-    L.sync();
-    if (cw > cs) { CO_FOR(i, nv) d.qacc[i] = d.qacc_smooth[i]; }
-    L.sync();
-  } else { CO_FOR(i, nv) d.qacc[i] = d.qacc_smooth[i]; L.sync(); }
-  co_mul_M(L, m, d, d.sv_Ma, d.qacc);
-  CO_FOR(r, nefc) d.sv_Jaref[r] = co_row_dot(m, d, r, d.qacc) - d.efc_aref[r];
-  L.sync();
-  co_update_cost(L, m, d, c);
-  co_newton_direction(L, m, d);
-  const double scale = 1.0 / (m.meaninertia * (nv > 1 ? nv : 1));
-  int iter = 0;
-  while (iter < m.iterations) {
-    const double alpha = co_line_search(L, m, d, c);
-    if (alpha == 0) break;
-    CO_FOR(i, nv) { d.qacc[i] += alpha * d.sv_search[i]; d.sv_Ma[i] += alpha * d.sv_Mv[i]; }
-    CO_FOR(r, nefc) d.sv_Jaref[r] += alpha * d.sv_Jv[r];
-    L.sync();
     co_update_cost(L, m, d, c);
     co_newton_direction(L, m, d);
-    iter++;
-    const double improvement = scale * (c.prev_cost - c.cost);
-    const double gradient = scale * sqrt(vdot(d.sv_grad, d.sv_grad, nv));
-    if (improvement < m.tolerance || gradient < m.tolerance) break;
   }
-  CO_FOR(i, nv) d.qacc_warmstart[i] = d.qacc[i];
-  if (L.lane == 0) d.solver_iter = iter;
-  L.sync();
+  const double scale = 1.0 / (m.meaninertia * (nv > 1 ? nv : 1));
+  int iter = 0;
+  bool more = run && iter < m.iterations;
+  while (L.block_any(more)) {
+    const double alpha = co_line_search(L, m, d, c, more);
+    if (more && alpha == 0) more = false;
+    if (more) {
+      CO_FOR(i, nv) { d.qacc[i] += alpha * d.sv_search[i]; d.sv_Ma[i] += alpha * d.sv_Mv[i]; }
+      CO_FOR(r, nefc) d.sv_Jaref[r] += alpha * d.sv_Jv[r];
+      L.sync();
+      co_update_cost(L, m, d, c);
+    }
+    L.block_sync();
+    if (more) {
+      co_newton_direction(L, m, d);
+      iter++;
+      const double improvement = scale * (c.prev_cost - c.cost);
+      const double gradient = scale * sqrt(vdot(d.sv_grad, d.sv_grad, nv));
+      if (improvement < m.tolerance || gradient < m.tolerance || iter >= m.iterations) more = false;
+    }
+  }
+  if (run) {
+    CO_FOR(i, nv) d.qacc_warmstart[i] = d.qacc[i];
+    if (L.lane == 0) d.solver_iter = iter;
+    L.sync();
+  }
 }
 
 }  // namespace ps

@@ -422,7 +422,7 @@ static int run_iteration(PsEngine* e, int N, int H, double sigma0, double sigma1
     // block minima are rebuilt from the (possibly rewritten) returns
     CU(cudaMemsetAsync(e->d_fix, 0, sizeof(int), e->stream));
     collect_flagged_kernel<<<(N + 255) / 256, 256, 0, e->stream>>>(e->d_failure, 0, N, e->d_fix + 1, e->d_fix);
-    run->fixup(e->stream, dc, e->d_knots, stride, e->d_returns, e->d_failure, e->d_fix + 1, e->d_fix, e->wb, writeback);
+    run->fixup(e->stream, dc, e->d_knots, stride, e->d_returns, e->d_failure, e->d_fix + 1, e->d_fix, e->d_counter, e->wb, writeback);
     e->nblocks = (N + 1023) / 1024;
     minloc_returns_kernel<<<e->nblocks, 256, 0, e->stream>>>(e->d_returns, N, (long long)sample_offset, e->d_blockmin);
     e->launches += 3;
@@ -615,7 +615,7 @@ int ps_get_trajectory(PsEngine* e, int sample, double* states, double* actions, 
     if (e->last->fixup) {      // the scoring kernel's capacity overflows for this sample again: take the large-capacity trajectory
       CU(cudaMemsetAsync(e->d_fix, 0, sizeof(int), e->stream));
       collect_flagged_kernel<<<1, 32, 0, e->stream>>>(e->d_failure, sample, 1, e->d_fix + 1, e->d_fix);
-      e->last->fixup(e->stream, e->last_dconst, e->d_knots, stride, e->d_returns, e->d_failure, e->d_fix + 1, e->d_fix, e->wb, true);
+      e->last->fixup(e->stream, e->last_dconst, e->d_knots, stride, e->d_returns, e->d_failure, e->d_fix + 1, e->d_fix, e->d_counter, e->wb, true);
       e->launches += 2;
     }
     CU(cudaGetLastError());

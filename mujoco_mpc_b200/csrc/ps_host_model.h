@@ -26,7 +26,7 @@ typedef Traits<19, 18, 12, 0, 16, 13, 44, 8, 2, 40, 16, 96, 16, true> LeggedT;  
 typedef Traits<2, 2, 2, 0, 4, 2, 8, 2, 1, 0, 0, 4, 12, false, 2, 4> TinyCoopT;
 typedef Traits<9, 9, 6, 5, 9, 9, 18, 6, 1, 8, 14, 64, 20, false, 9, 52> PlanarCoopT;
 typedef Traits<19, 18, 12, 0, 16, 13, 44, 8, 2, 40, 24, 120, 16, true, 12, 84> LeggedCoopT;
-// capacity-overflow re-rolls (csrc/ps_coop_rollout.cuh: sparse_fixup_kernel): the same model capacities -- so the same
+// capacity-overflow re-rolls (csrc/ps_coop_rollout.cuh: coop_fixup_kernel): the same model capacities -- so the same
 // Constants layout -- with room for 64 contacts / 256 constraint rows (a fallen robot: 39 / 141 in the capacity survey)
 typedef Traits<19, 18, 12, 0, 16, 13, 44, 8, 2, 40, 64, 256, 16, true, 12, 192> LeggedXLT;
 static_assert(sizeof(Constants<LeggedXLT>) == sizeof(Constants<LeggedCoopT>) && sizeof(Constants<LeggedXLT>) == sizeof(Constants<LeggedT>),

@@ -97,7 +97,7 @@ extern "C" int hs_rollout_coop(const PsModel* m, const PsTask* t, const double* 
   if (r == 0) { std::snprintf(variant, cap, "%s (sizeof CoopData %zu, Constants %zu)", name, sizeof(CoopData<T>), sizeof(Constants<T>)); return 0; } if (r == -2) { std::snprintf(variant, cap, "%s", why.c_str()); return -2; }
   TRYC(PlanarCoopT, "planar_coop")
   // legged class: as the engine does, a rollout that overflows the scoring capacities (flag bit 1) is rolled again at the
-  // large-capacity instantiation of the fix-up pass (sparse_fixup_kernel<LeggedXLT>)
+  // large-capacity instantiation of the fix-up pass (coop_fixup_kernel<LeggedXLT>)
   r = run_coop<LeggedCoopT>(m, t, pl, state, mocap, time, times, knots, P, interp, H, timestep, integrator, states, actions, residual, costs, total, flags, &why);
   if (r == 0 && (*flags & 2)) {
     r = run_coop<LeggedXLT>(m, t, pl, state, mocap, time, times, knots, P, interp, H, timestep, integrator, states, actions, residual, costs, total, flags, &why);

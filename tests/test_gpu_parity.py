@@ -49,7 +49,7 @@ def run_case(name, N, interp, H=None, seed=2024, sigma=None, time=0.37, warm=Tru
     gret, gfail = e.returns()
     assert np.array_equal(ofail.astype(bool), (gfail & 1).astype(bool))
     # bit 1 = the rollout ran out of contact / constraint-row capacity.  The engine rolls such samples again at the large
-    # capacities of its fix-up pass (sparse_fixup_kernel), so no sample may still carry it: every sample is in the parity set
+    # capacities of its fix-up pass (coop_fixup_kernel), so no sample may still carry it: every sample is in the parity set
     # (a rollout that DIVERGED -- bit 0, scored 1e6 on both sides -- may still carry it: its contact set exploded on the way)
     capped = ((gfail & 2) != 0) & ((gfail & 1) == 0)
     assert not capped.any(), (name, int(capped.sum()))

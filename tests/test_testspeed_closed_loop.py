@@ -11,8 +11,9 @@ pytestmark = pytest.mark.gpu
 from tests.common import oracle_closed_loop  # noqa: E402
 
 
-@pytest.mark.parametrize("task_name,interp,N", [("Cartpole", 0, 10), ("Acrobot", 2, 16), ("Particle", 2, 16)])
-def test_testspeed_closed_loop_matches_oracle(oracle_lib, task_name, interp, N):
+@pytest.mark.parametrize("task_name,interp,N,steps", [("Cartpole", 0, 10, 120), ("Acrobot", 2, 16, 120), ("Particle", 2, 16, 120),
+                                                    ("Swimmer", 2, 16, 60), ("Walker", 2, 16, 60), ("Quadruped Flat", 2, 12, 40)])
+def test_testspeed_closed_loop_matches_oracle(oracle_lib, task_name, interp, N, steps):
     from mujoco_mpc_b200.testspeed import synchronous_planning_cost
     cache = {}
 
@@ -21,10 +22,10 @@ def test_testspeed_closed_loop_matches_oracle(oracle_lib, task_name, interp, N):
             cache[k] = np.random.default_rng(1000 + k).standard_normal((n, P, nu))
         return cache[k]
     from mujoco_mpc_b200.testspeed import plant_model
-    total_time = 120 * plant_model(task_name).opt_timestep          # 120 plant steps, a plan after every 4th
+    total_time = steps * plant_model(task_name).opt_timestep        # a plan after every 4th plant step
     g = synchronous_planning_cost(task_name, steps_per_planning_iteration=4, total_time=total_time, num_trajectory=N, interpolation=interp, noise=noise)
     o = oracle_closed_loop(task_name, 4, total_time, N, interp, noise)
-    assert g["plans"] == o["plans"] == 30
+    assert g["plans"] == o["plans"] == steps // 4
     assert abs(g["time"] - o["time"]) < 1e-12
     assert np.abs(g["state"] - o["state"]).max() <= 1e-9 * max(1.0, np.abs(o["state"]).max())
     assert abs(g["total_cost"] - o["total_cost"]) <= 1e-8 * max(1.0, abs(o["total_cost"]))
