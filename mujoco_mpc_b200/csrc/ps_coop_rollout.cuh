@@ -117,15 +117,19 @@ PS_FN void co_integrate(const LT& L, const DevModel<T>& m, CoopData<T>& d) {
   L.sync();
 }
 
-// knots: SoA [P*nu][stride]; i = this rollout's column.  flags: bit0 failure, bit1 capacity overflow
+// What a rollout carries from one time step to the next besides its CoopData state: the running cost sum and its fate.
+struct CoCarry { double sum; bool failed, dead; };
+
+// co_rollout = co_rollout_begin + co_rollout_steps(0, H) + co_rollout_end.  The split exists for the step-wise launches of
+// the thread-per-rollout kernel (sparse_step_kernel), which save / restore the state between launches so that rollouts
+// can be re-binned by workload; the arithmetic of a rollout does not depend on how its steps are grouped.
 template <class T, bool WB, class LT, class PT = CoPerturbation<T, false>>
-PS_FN double co_rollout(const LT& L, const DevModel<T>& m, const DevTask& task, const DevPlan<T>& plan, const double* knots,
-                        int stride, int i, const Writeback& wb, CoopData<T>& d, int* flags, const PT pert = PT(), bool live = true) {
+PS_FN CoCarry co_rollout_begin(const LT& L, const DevModel<T>& m, const DevPlan<T>& plan, int stride, int i, const Writeback& wb,
+                               CoopData<T>& d, const PT pert = PT(), bool live = true) {
   // `live` = false: a padding thread of a block that walks in lockstep (LT::kBlock) -- it takes part in the block's
   // barriers and touches nothing else.  A rollout that fails stops working but, under lockstep, keeps pace the same way;
   // for every other lane type the remaining time steps of a dead rollout are an empty loop.
-  const int nq = m.nq, nv = m.nv, na = m.na, nu = m.nu, ns = nq + nv + na, nr = task.num_residual;
-  const int H = plan.horizon, P = plan.num_spline_points, ntr = 3 * task.num_trace;
+  const int nq = m.nq, nv = m.nv, na = m.na, nu = m.nu, ns = nq + nv + na;
   if (live) {
     CO_FOR(k, nq) d.qpos[k] = plan.state[k];
     CO_FOR(k, nv) { d.qvel[k] = plan.state[nq + k]; d.qacc_warmstart[k] = 0; d.qacc[k] = 0; }
@@ -137,10 +141,20 @@ PS_FN double co_rollout(const LT& L, const DevModel<T>& m, const DevTask& task, 
     L.sync();
     if constexpr (PT::kActive) pert.reset(L, m);
   }
-  const double* kcol = knots + i;
-  double sum = 0; bool failed = false, dead = !live;
+  CoCarry c; c.sum = 0; c.failed = false; c.dead = !live;
+  return c;
+}
 
-  PS_LOOP2 for (int t = 0; t < H; t++) {
+// time steps [t_begin, t_end) of the recursion (t = H - 1 is the terminal forward pass)
+template <class T, bool WB, class LT, class PT = CoPerturbation<T, false>>
+PS_FN void co_rollout_steps(const LT& L, const DevModel<T>& m, const DevTask& task, const DevPlan<T>& plan, const double* knots,
+                            int stride, int i, const Writeback& wb, CoopData<T>& d, CoCarry& carry, int t_begin, int t_end,
+                            const PT pert = PT()) {
+  const int nq = m.nq, nv = m.nv, na = m.na, nu = m.nu, ns = nq + nv + na, nr = task.num_residual;
+  const int H = plan.horizon, P = plan.num_spline_points, ntr = 3 * task.num_trace;
+  const double* kcol = knots + i;
+  double sum = carry.sum; bool failed = carry.failed, dead = carry.dead;
+  PS_LOOP2 for (int t = t_begin; t < t_end; t++) {
     const bool terminal = t == H - 1;
     L.block_sync();
     if (!terminal && !dead) {
@@ -198,10 +212,25 @@ PS_FN double co_rollout(const LT& L, const DevModel<T>& m, const DevTask& task, 
     }
     if (!LT::kBlock && dead) break;
   }
-  const double total = failed ? 1.0e6 : sum / (H > 1 ? H : 1);
-  *flags = !live ? 0 : ((failed ? 1 : 0) | ((d.warning & WARN_CAPACITY) ? 2 : 0));
+  carry.sum = sum; carry.failed = failed; carry.dead = dead;
+}
+
+template <class T, class LT>
+PS_FN double co_rollout_end(const LT& L, const DevPlan<T>& plan, const CoopData<T>& d, const CoCarry& carry, bool live, int* flags) {
+  const int H = plan.horizon;
+  const double total = carry.failed ? 1.0e6 : carry.sum / (H > 1 ? H : 1);
+  *flags = !live ? 0 : ((carry.failed ? 1 : 0) | ((d.warning & WARN_CAPACITY) ? 2 : 0));
   L.sync();
   return total;
+}
+
+// knots: SoA [P*nu][stride]; i = this rollout's column.  flags: bit0 failure, bit1 capacity overflow
+template <class T, bool WB, class LT, class PT = CoPerturbation<T, false>>
+PS_FN double co_rollout(const LT& L, const DevModel<T>& m, const DevTask& task, const DevPlan<T>& plan, const double* knots,
+                        int stride, int i, const Writeback& wb, CoopData<T>& d, int* flags, const PT pert = PT(), bool live = true) {
+  CoCarry carry = co_rollout_begin<T, WB>(L, m, plan, stride, i, wb, d, pert, live);
+  co_rollout_steps<T, WB>(L, m, task, plan, knots, stride, i, wb, d, carry, 0, plan.horizon, pert);
+  return co_rollout_end(L, plan, d, carry, live, flags);
 }
 
 #ifdef __CUDACC__

@@ -94,7 +94,8 @@ PS_NI void co_newton_direction(const LT& L, const DevModel<T>& m, CoopData<T>& d
   constexpr int S = T::NV, NCH = T::NCH; const int nv = m.nv;
   double* H = d.qH;
   CO_FOR(i, nv) d.sv_grad[i] = d.sv_Ma[i] - d.qfrc_smooth[i] - d.qfrc_constraint[i];
-  CO_FOR(w, nv * S) H[w] = d.qM[w];
+  if constexpr (LT::single) { PS_LOOP2 for (int i = 0; i < nv; i++) PS_LOOP2 for (int k = 0; k <= i; k++) H[i * S + k] = d.qM[i * S + k]; }   // nothing reads the upper triangle
+  else CO_FOR(w, nv * S) H[w] = d.qM[w];
   L.sync();
   // unit rows: friction rows hit distinct diagonal entries; limit rows go through one lane, in order
   const int nf = (m.disableflags & DSBL_FRICTIONLOSS) ? 0 : m.nfrictionrow;
@@ -146,6 +147,56 @@ PS_NI void co_newton_direction(const LT& L, const DevModel<T>& m, CoopData<T>& d
       *h = acc;
     }
     L.sync();
+  }
+  if constexpr (LT::single) {
+    // ONE working lane (thread-per-rollout kernel, host build): row-by-row Cholesky with the current row in registers.
+    // Entry (i, k) = (H_ik - sum_{j<k} L_ij L_kj) / L_kk with j ascending -- the very operation sequence of the column
+    // formulation below -- but row i is loaded once (up to 18 independent loads in flight), the finished rows are only
+    // read, and nothing is stored until the row is complete: a third of the loads, a sixth of the stores, and no
+    // load-after-store serialisation.  That kernel is bound by the latency of its thread-private memory (ncu:
+    // long_scoreboard 21 cycles per issue, the trailing update of the column formulation alone 25 % of the stall samples).
+    double r[S];
+    PS_LOOP2 for (int i = 0; i < nv; i++) {
+      const double* Hi = H + i * S;
+#pragma unroll
+      for (int k = 0; k < S; k++) if (k <= i) r[k] = Hi[k];
+#pragma unroll
+      for (int k = 0; k < S; k++) {
+        if (k <= i) {
+          const double* Lk = H + k * S;
+          double acc = r[k];
+#pragma unroll
+          for (int j = 0; j < k; j++) acc -= r[j] * (k == i ? r[j] : Lk[j]);
+          r[k] = (k == i) ? sqrt(fmax(acc, kMinVal)) : acc / Lk[k];
+        }
+      }
+#pragma unroll
+      for (int k = 0; k < S; k++) if (k <= i) H[i * S + k] = r[k];
+    }
+    // forward / backward substitution by columns, the vector in registers
+#pragma unroll
+    for (int i = 0; i < S; i++) r[i] = i < nv ? d.sv_grad[i] : 0.0;
+#pragma unroll
+    for (int k = 0; k < S; k++) {
+      if (k < nv) {
+        const double xk = r[k] / H[k * S + k];
+        r[k] = xk;
+#pragma unroll
+        for (int i = k + 1; i < S; i++) if (i < nv) r[i] -= H[i * S + k] * xk;
+      }
+    }
+#pragma unroll
+    for (int k = S - 1; k >= 0; k--) {
+      if (k < nv) {
+        const double xk = r[k] / H[k * S + k];
+        r[k] = xk;
+#pragma unroll
+        for (int i = 0; i < k; i++) r[i] -= H[k * S + i] * xk;
+      }
+    }
+#pragma unroll
+    for (int i = 0; i < S; i++) if (i < nv) d.sv_search[i] = -r[i];
+    return;
   }
   // right-looking Cholesky: scale column j, then subtract its outer product from the trailing
   // triangle.  Entry (i, k) receives the products of columns 0 .. k-1 in that order, which is the
