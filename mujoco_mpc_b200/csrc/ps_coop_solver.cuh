@@ -66,6 +66,51 @@ PS_NI void co_update_cost(const LT& L, const DevModel<T>& m, CoopData<T>& d, CoS
   // qfrc_constraint = J' f, one lane per dof, rows in order
   const int nf = (m.disableflags & DSBL_FRICTIONLOSS) ? 0 : m.nfrictionrow;
   const int nl = d.nlimit, ncon = d.ncon;
+  if constexpr (LT::single) {
+    // ONE working lane: unit rows dof by dof, then the contacts one after the other, each scattering into the dofs it touches.
+    // A dof's sum still receives its friction row, the limit rows and the contacts' rows in that order (contacts and their
+    // rows ascending), so it is the sum of the dof-major form below; a contact without force is skipped after nrow loads.
+    PS_LOOP2 for (int i = 0; i < nv; i++) {
+      double s = 0;
+      const int fr = nf ? m.dof_frictionrow[i] : -1;
+      if (fr >= 0) { const double f = d.efc_force[fr]; if (f != 0) s += f; }
+      PS_LOOP2 for (int r = nf; r < nf + nl; r++) {
+        const double f = d.efc_force[r];
+        if (f != 0 && m.jnt_dofadr[d.efc_id[r]] == i) s += (double)d.efc_jrow[r] * f;
+      }
+      d.qfrc_constraint[i] = s;
+    }
+    constexpr int MR = 6;
+    PS_LOOP2 for (int ci = 0; ci < ncon; ci++) {
+      const CoopContact& con = d.contact[ci];
+      const int adr = con.efc_address, nrow = con.nrow;
+      if (adr < 0) continue;
+      const double* J = d.jpool + con.jadr * T::NCH;
+      const signed char* dof = d.con_dof + ci * T::NCH;
+      const int n = con.ndof;
+      if (nrow <= MR) {
+        double fq[MR]; unsigned nz = 0;
+#pragma unroll
+        for (int q = 0; q < MR; q++) if (q < nrow) { fq[q] = d.efc_force[adr + q]; if (fq[q] != 0) nz |= 1u << q; }
+        if (!nz) continue;
+        PS_LOOP2 for (int k = 0; k < n; k++) {
+          double* dst = d.qfrc_constraint + dof[k];
+          double s = *dst;
+#pragma unroll
+          for (int q = 0; q < MR; q++) if (nz >> q & 1u) s += J[q * T::NCH + k] * fq[q];
+          *dst = s;
+        }
+      } else {
+        PS_LOOP2 for (int k = 0; k < n; k++) {
+          double* dst = d.qfrc_constraint + dof[k];
+          double s = *dst;
+          PS_LOOP2 for (int q = 0; q < nrow; q++) { const double f = d.efc_force[adr + q]; if (f != 0) s += J[q * T::NCH + k] * f; }
+          *dst = s;
+        }
+      }
+    }
+    return;
+  }
   CO_FOR(i, nv) {
     double s = 0;
     const int fr = nf ? m.dof_frictionrow[i] : -1;
@@ -113,6 +158,69 @@ PS_NI void co_newton_direction(const LT& L, const DevModel<T>& m, CoopData<T>& d
     const signed char* dof = d.con_dof + ci * NCH;
     const double* J = d.jpool + con.jadr * NCH;
     const bool cone = d.efc_type[adr] == EFC_CONTACT_ELLIPTIC && d.efc_state[adr] == ST_CONE;
+    if constexpr (LT::single) {
+      // ONE working lane: the contact's block is accumulated dof-slot row by dof-slot row with that row's Jacobian column
+      // (times D, or the cone's T column) in registers.  Every H entry receives the very products of the pair loop below in
+      // the same order -- (D J_ki) J_kj for q ascending, J_a,ki T_a,kj for a ascending -- so the sums are bit-identical; what
+      // changes is the traffic to thread-private memory (ncu: this block was 40 % of the kernel's executed instructions,
+      // 4 loads per row and pair): 1 load per row and pair, nothing at all for a contact with no active row.
+      constexpr int MR = 6;                                  // rows kept in registers (elliptic: dim <= 6; pyramidal condim 3: 4)
+      if (cone && con.dim == 3) {
+        const double mu = con.mu; const double* fr = con.friction;
+        double U[3]; U[0] = d.sv_Jaref[adr] * mu; U[1] = d.sv_Jaref[adr + 1] * fr[0]; U[2] = d.sv_Jaref[adr + 2] * fr[1];
+        const double N = U[0]; double TT = 0; TT += U[1] * U[1]; TT += U[2] * U[2];
+        const double Tn = sqrt(TT);
+        const double Dm = d.efc_D[adr] / (mu * mu * (1 + mu * mu));
+        const double s1 = mu * N / (Tn * Tn * Tn), s2 = mu * mu - mu * N / Tn;
+        double hC[9];
+#pragma unroll
+        for (int k = 0; k < 3; k++)
+#pragma unroll
+          for (int j = 0; j < 3; j++) {
+            double h;
+            if (k == 0 && j == 0) h = 1;
+            else if (k == 0 || j == 0) h = -mu * U[k + j] / Tn;
+            else h = s1 * U[j] * U[k] + (k == j ? s2 : 0.0);
+            hC[k * 3 + j] = h * (Dm * (k == 0 ? mu : fr[k - 1]) * (j == 0 ? mu : fr[j - 1]));
+          }
+        PS_LOOP2 for (int k = 0; k < n; k++) {
+          const double j0 = J[k], j1 = J[NCH + k], j2 = J[2 * NCH + k];
+#pragma unroll
+          for (int a = 0; a < 3; a++) { double t = 0; t += hC[a * 3] * j0; t += hC[a * 3 + 1] * j1; t += hC[a * 3 + 2] * j2; d.sv_T[a * NCH + k] = t; }
+        }
+        PS_LOOP2 for (int ki = 0; ki < n; ki++) {
+          const double j0 = J[ki], j1 = J[NCH + ki], j2 = J[2 * NCH + ki];
+          double* Hrow = H + dof[ki] * S;
+          PS_LOOP2 for (int kj = 0; kj <= ki; kj++) {
+            double* h = Hrow + dof[kj];
+            double acc = *h;
+            acc += j0 * d.sv_T[kj]; acc += j1 * d.sv_T[NCH + kj]; acc += j2 * d.sv_T[2 * NCH + kj];
+            *h = acc;
+          }
+        }
+        continue;
+      }
+      if (!cone && nrow <= MR) {
+        double Dq[MR]; unsigned quad = 0;
+#pragma unroll
+        for (int q = 0; q < MR; q++) if (q < nrow && d.efc_state[adr + q] == ST_QUADRATIC) { quad |= 1u << q; Dq[q] = d.efc_D[adr + q]; }
+        if (!quad) continue;                                  // no active row: the block adds nothing
+        PS_LOOP2 for (int ki = 0; ki < n; ki++) {
+          double DJ[MR];
+#pragma unroll
+          for (int q = 0; q < MR; q++) if (quad >> q & 1u) DJ[q] = Dq[q] * J[q * NCH + ki];
+          double* Hrow = H + dof[ki] * S;
+          PS_LOOP2 for (int kj = 0; kj <= ki; kj++) {
+            double* h = Hrow + dof[kj];
+            double acc = *h;
+#pragma unroll
+            for (int q = 0; q < MR; q++) if (quad >> q & 1u) acc += DJ[q] * J[q * NCH + kj];
+            *h = acc;
+          }
+        }
+        continue;
+      }
+    }
     if (cone) {
       const int dim = con.dim; const double mu = con.mu; const double* fr = con.friction;
       // local cone Hessian (dim x dim), recomputed from the row residuals
@@ -243,6 +351,52 @@ template <class T, class LT>
 PS_NI void co_line_eval(const LT& L, const DevModel<T>& m, CoopData<T>& d, const double* qg, double alpha,
                         double* cost, double* d1, double* d2) { PS_ASSUME_SHARED(&m); if (LT::kSharedData) PS_ASSUME_SHARED(&d);
   const int nefc = d.nefc;
+  if constexpr (LT::single) {
+    // ONE working lane: the rows' terms go straight into the three sums, in row order (a cone's trailing rows add their
+    // zeros like the two-pass form below does) -- no per-row stores and no second pass over them
+    double f = qg[0] + alpha * qg[1] + alpha * alpha * qg[2], g = qg[1] + 2 * alpha * qg[2], h = 2 * qg[2];
+    PS_LOOP2 for (int i = 0; i < nefc; i++) {
+      const int tp = d.efc_type[i];
+      const double D = d.efc_D[i];
+      const double v = d.sv_Jv[i], x = d.sv_Jaref[i] + alpha * v;
+      if (tp == EFC_FRICTION_DOF) {
+        const double R = d.efc_R[i], fl = m.dof_frictionloss[d.efc_id[i]];
+        if (x <= -R * fl) { f += -0.5 * R * fl * fl - fl * x; g += -fl * v; h += 0.0; }
+        else if (x >= R * fl) { f += -0.5 * R * fl * fl + fl * x; g += fl * v; h += 0.0; }
+        else { f += 0.5 * D * x * x; g += D * x * v; h += D * v * v; }
+      } else if (tp != EFC_CONTACT_ELLIPTIC) {
+        if (x < 0) { f += 0.5 * D * x * x; g += D * x * v; h += D * v * v; }
+        else { f += 0.0; g += 0.0; h += 0.0; }
+      } else {
+        const CoopContact& con = d.contact[d.efc_id[i]];
+        if (i != con.efc_address) continue;
+        const int dim = con.dim; const double mu = con.mu; const double* fr = con.friction;
+        const double N = x * mu, Np = v * mu; double TT = 0, UV = 0, VV = 0;
+        PS_LOOP2 for (int j = 1; j < dim; j++) {
+          const double u = (d.sv_Jaref[i + j] + alpha * d.sv_Jv[i + j]) * fr[j - 1], w = d.sv_Jv[i + j] * fr[j - 1];
+          TT += u * u; UV += u * w; VV += w * w;
+        }
+        const double Tn = sqrt(TT);
+        if (N >= mu * Tn || (Tn <= 0 && N >= 0)) {
+          PS_LOOP2 for (int j = 0; j < dim; j++) { f += 0.0; g += 0.0; h += 0.0; }
+        } else if (mu * N + Tn <= 0 || (Tn <= 0 && N < 0)) {
+          PS_LOOP2 for (int j = 0; j < dim; j++) {
+            const double xj = d.sv_Jaref[i + j] + alpha * d.sv_Jv[i + j], vj = d.sv_Jv[i + j], Dj = d.efc_D[i + j];
+            f += 0.5 * Dj * xj * xj; g += Dj * xj * vj; h += Dj * vj * vj;
+          }
+        } else {
+          const double Dm = D / (mu * mu * (1 + mu * mu));
+          const double Tp = UV / Tn, Tpp = VV / Tn - UV * UV / (Tn * Tn * Tn);
+          const double NT = N - mu * Tn, NTp = Np - mu * Tp;
+          f += 0.5 * Dm * NT * NT; g += Dm * NT * NTp; h += Dm * (NTp * NTp + NT * (-mu * Tpp));
+          PS_LOOP2 for (int j = 1; j < dim; j++) { f += 0.0; g += 0.0; h += 0.0; }
+        }
+        i += dim - 1;
+      }
+    }
+    *cost = f; *d1 = g; *d2 = h;
+    return;
+  }
   double* tf = d.sv_tmp; double* tg = d.efc_force; double* th = d.efc_aref;     // both dead during the line search
   CO_FOR(i, nefc) {
     const int tp = d.efc_type[i];

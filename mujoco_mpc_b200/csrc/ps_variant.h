@@ -103,6 +103,8 @@ inline int launch_sparse(cudaStream_t st, const void* dconst, const double* knot
   if (!sms_) { int dev = 0; cudaGetDevice(&dev); cudaDeviceGetAttribute(&sms_, cudaDevAttrMultiProcessorCount, dev); if (sms_ <= 0) sms_ = 148; }
   int block = pick_block(n, BLOCK);
   if (n >= sms_ * 64) { block = ((n + sms_ - 1) / sms_ + 31) & ~31; if (block > BLOCK) block = BLOCK; }
+  static const int block_rt = std::getenv("PS_SPARSE_BLOCK_RT") ? std::atoi(std::getenv("PS_SPARSE_BLOCK_RT")) : 0;   // diagnostics / tuning
+  if (block_rt >= 32 && block_rt <= BLOCK && block > block_rt) block = block_rt & ~31;
   int grid = (n + block - 1) / block;
   // PS_SPARSE_BLOCKS_PER_SM (diagnostics / tuning): cap the grid at that many blocks per SM; the kernel strides over the batch
   static const int per_sm = std::getenv("PS_SPARSE_BLOCKS_PER_SM") ? std::atoi(std::getenv("PS_SPARSE_BLOCKS_PER_SM")) : PS_SPARSE_BLOCKS_PER_SM_DEFAULT;
