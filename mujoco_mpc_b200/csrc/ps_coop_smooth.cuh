@@ -228,6 +228,26 @@ PS_NI void co_mass_matrix(const LT& L, const DevModel<T>& m, CoopData<T>& d) { P
 
 template <class T, class LT>
 PS_NI void co_mul_M(const LT& L, const DevModel<T>& m, const CoopData<T>& d, double* res, const double* vec) { PS_ASSUME_SHARED(&m); if (LT::kSharedData) PS_ASSUME_SHARED(&d);
+  if constexpr (LT::single) {
+    // one working lane: the vector is loaded once and stays in registers (the dots are those of vdot, j ascending)
+    constexpr int S = T::NV; const int nv = m.nv;
+    if (nv == S) {          // (a model below the class capacity takes the plain loop)
+      double v[S];
+#pragma unroll
+      for (int j = 0; j < S; j++) v[j] = vec[j];
+      PS_LOOP2 for (int i = 0; i < S; i++) {
+        const double* row = d.qM + i * S;
+        double r[S];          // the row's loads are independent of each other: all in flight before the first product
+#pragma unroll
+        for (int j = 0; j < S; j++) r[j] = row[j];
+        double s = 0;
+#pragma unroll
+        for (int j = 0; j < S; j++) s += r[j] * v[j];
+        res[i] = s;
+      }
+      return;
+    }
+  }
   CO_FOR(i, m.nv) res[i] = vdot(d.qM + i * T::NV, vec, m.nv);
 }
 

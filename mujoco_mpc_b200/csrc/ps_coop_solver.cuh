@@ -133,12 +133,75 @@ PS_NI void co_update_cost(const LT& L, const DevModel<T>& m, CoopData<T>& d, CoS
   L.sync();
 }
 
-// H = M + J' D_active J (+ cone blocks) -> Cholesky -> search = -H^-1 grad
+// grad = M a - qfrc_smooth - J' f
+template <class T, class LT>
+PS_NI void co_newton_gradient(const LT& L, const DevModel<T>& m, CoopData<T>& d) { PS_ASSUME_SHARED(&m); if (LT::kSharedData) PS_ASSUME_SHARED(&d);
+  CO_FOR(i, m.nv) d.sv_grad[i] = d.sv_Ma[i] - d.qfrc_smooth[i] - d.qfrc_constraint[i];
+  L.sync();
+}
+
+// One contact in the cone state, ONE working lane (see co_newton_direction): local cone Hessian C (DIM x DIM) in registers,
+// T = C J column by column, then the contact's block of H dof-slot row by row.  Products and summation orders are those of the
+// cooperative form in co_newton_direction (b, a ascending), entry by entry.
+template <int DIM, class T>
+PS_FN void co_cone_block_single(CoopData<T>& d, const CoopContact& con, int adr, int n, const double* J, const signed char* dof, double* H) {
+  constexpr int S = T::NV, NCH = T::NCH;
+  const double mu = con.mu; const double* fr = con.friction;
+  double U[DIM]; U[0] = d.sv_Jaref[adr] * mu;
+#pragma unroll
+  for (int j = 1; j < DIM; j++) U[j] = d.sv_Jaref[adr + j] * fr[j - 1];
+  const double N = U[0]; double TT = 0;
+#pragma unroll
+  for (int j = 1; j < DIM; j++) TT += U[j] * U[j];
+  const double Tn = sqrt(TT);
+  const double Dm = d.efc_D[adr] / (mu * mu * (1 + mu * mu));
+  const double s1 = mu * N / (Tn * Tn * Tn), s2 = mu * mu - mu * N / Tn;
+  double hC[DIM * DIM];
+#pragma unroll
+  for (int k = 0; k < DIM; k++)
+#pragma unroll
+    for (int j = 0; j < DIM; j++) {
+      double h;
+      if (k == 0 && j == 0) h = 1;
+      else if (k == 0 || j == 0) h = -mu * U[k + j] / Tn;
+      else h = s1 * U[j] * U[k] + (k == j ? s2 : 0.0);
+      hC[k * DIM + j] = h * (Dm * (k == 0 ? mu : fr[k - 1]) * (j == 0 ? mu : fr[j - 1]));
+    }
+  PS_LOOP2 for (int k = 0; k < n; k++) {
+    double jc[DIM];
+#pragma unroll
+    for (int b = 0; b < DIM; b++) jc[b] = J[b * NCH + k];
+#pragma unroll
+    for (int a = 0; a < DIM; a++) {
+      double t = 0;
+#pragma unroll
+      for (int b = 0; b < DIM; b++) t += hC[a * DIM + b] * jc[b];
+      d.sv_T[a * NCH + k] = t;
+    }
+  }
+  PS_LOOP2 for (int ki = 0; ki < n; ki++) {
+    double jc[DIM];
+#pragma unroll
+    for (int a = 0; a < DIM; a++) jc[a] = J[a * NCH + ki];
+    double* Hrow = H + dof[ki] * S;
+    PS_LOOP2 for (int kj = 0; kj <= ki; kj++) {
+      double tc[DIM];
+#pragma unroll
+      for (int a = 0; a < DIM; a++) tc[a] = d.sv_T[a * NCH + kj];
+      double* h = Hrow + dof[kj];
+      double acc = *h;
+#pragma unroll
+      for (int a = 0; a < DIM; a++) acc += jc[a] * tc[a];
+      *h = acc;
+    }
+  }
+}
+
+// H = M + J' D_active J (+ cone blocks) -> Cholesky -> search = -H^-1 grad (grad: co_newton_gradient)
 template <class T, class LT>
 PS_NI void co_newton_direction(const LT& L, const DevModel<T>& m, CoopData<T>& d) { PS_ASSUME_SHARED(&m); if (LT::kSharedData) PS_ASSUME_SHARED(&d);
   constexpr int S = T::NV, NCH = T::NCH; const int nv = m.nv;
   double* H = d.qH;
-  CO_FOR(i, nv) d.sv_grad[i] = d.sv_Ma[i] - d.qfrc_smooth[i] - d.qfrc_constraint[i];
   if constexpr (LT::single) { PS_LOOP2 for (int i = 0; i < nv; i++) PS_LOOP2 for (int k = 0; k <= i; k++) H[i * S + k] = d.qM[i * S + k]; }   // nothing reads the upper triangle
   else CO_FOR(w, nv * S) H[w] = d.qM[w];
   L.sync();
@@ -165,41 +228,8 @@ PS_NI void co_newton_direction(const LT& L, const DevModel<T>& m, CoopData<T>& d
       // changes is the traffic to thread-private memory (ncu: this block was 40 % of the kernel's executed instructions,
       // 4 loads per row and pair): 1 load per row and pair, nothing at all for a contact with no active row.
       constexpr int MR = 6;                                  // rows kept in registers (elliptic: dim <= 6; pyramidal condim 3: 4)
-      if (cone && con.dim == 3) {
-        const double mu = con.mu; const double* fr = con.friction;
-        double U[3]; U[0] = d.sv_Jaref[adr] * mu; U[1] = d.sv_Jaref[adr + 1] * fr[0]; U[2] = d.sv_Jaref[adr + 2] * fr[1];
-        const double N = U[0]; double TT = 0; TT += U[1] * U[1]; TT += U[2] * U[2];
-        const double Tn = sqrt(TT);
-        const double Dm = d.efc_D[adr] / (mu * mu * (1 + mu * mu));
-        const double s1 = mu * N / (Tn * Tn * Tn), s2 = mu * mu - mu * N / Tn;
-        double hC[9];
-#pragma unroll
-        for (int k = 0; k < 3; k++)
-#pragma unroll
-          for (int j = 0; j < 3; j++) {
-            double h;
-            if (k == 0 && j == 0) h = 1;
-            else if (k == 0 || j == 0) h = -mu * U[k + j] / Tn;
-            else h = s1 * U[j] * U[k] + (k == j ? s2 : 0.0);
-            hC[k * 3 + j] = h * (Dm * (k == 0 ? mu : fr[k - 1]) * (j == 0 ? mu : fr[j - 1]));
-          }
-        PS_LOOP2 for (int k = 0; k < n; k++) {
-          const double j0 = J[k], j1 = J[NCH + k], j2 = J[2 * NCH + k];
-#pragma unroll
-          for (int a = 0; a < 3; a++) { double t = 0; t += hC[a * 3] * j0; t += hC[a * 3 + 1] * j1; t += hC[a * 3 + 2] * j2; d.sv_T[a * NCH + k] = t; }
-        }
-        PS_LOOP2 for (int ki = 0; ki < n; ki++) {
-          const double j0 = J[ki], j1 = J[NCH + ki], j2 = J[2 * NCH + ki];
-          double* Hrow = H + dof[ki] * S;
-          PS_LOOP2 for (int kj = 0; kj <= ki; kj++) {
-            double* h = Hrow + dof[kj];
-            double acc = *h;
-            acc += j0 * d.sv_T[kj]; acc += j1 * d.sv_T[NCH + kj]; acc += j2 * d.sv_T[2 * NCH + kj];
-            *h = acc;
-          }
-        }
-        continue;
-      }
+      if (cone && con.dim == 3) { co_cone_block_single<3>(d, con, adr, n, J, dof, H); continue; }
+      if (cone && con.dim == 6) { co_cone_block_single<6>(d, con, adr, n, J, dof, H); continue; }
       if (!cone && nrow <= MR) {
         double Dq[MR]; unsigned quad = 0;
 #pragma unroll
@@ -529,6 +559,7 @@ PS_NI void co_constraint_stage(const LT& L, const DevModel<T>& m, CoopData<T>& d
     CO_FOR(r, nefc) d.sv_Jaref[r] = co_row_dot(m, d, r, d.qacc) - d.efc_aref[r];
     L.sync();
     co_update_cost(L, m, d, c);
+    co_newton_gradient(L, m, d);
     co_newton_direction(L, m, d);
   }
   const double scale = 1.0 / (m.meaninertia * (nv > 1 ? nv : 1));
@@ -545,12 +576,15 @@ PS_NI void co_constraint_stage(const LT& L, const DevModel<T>& m, CoopData<T>& d
     }
     L.block_sync();
     if (more) {
-      co_newton_direction(L, m, d);
+      // mj_solNewton factorises the Hessian and solves for the next direction before it tests for convergence; the
+      // direction of the last iteration is never used, so the test comes first here and the last factorisation is skipped
+      co_newton_gradient(L, m, d);
       iter++;
       const double improvement = scale * (c.prev_cost - c.cost);
       const double gradient = scale * sqrt(vdot(d.sv_grad, d.sv_grad, nv));
       if (improvement < m.tolerance || gradient < m.tolerance || iter >= m.iterations) more = false;
     }
+    if (more) co_newton_direction(L, m, d);
   }
   if (run) {
     CO_FOR(i, nv) d.qacc_warmstart[i] = d.qacc[i];
