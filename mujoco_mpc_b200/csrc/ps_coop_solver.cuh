@@ -202,7 +202,15 @@ template <class T, class LT>
 PS_NI void co_newton_direction(const LT& L, const DevModel<T>& m, CoopData<T>& d) { PS_ASSUME_SHARED(&m); if (LT::kSharedData) PS_ASSUME_SHARED(&d);
   constexpr int S = T::NV, NCH = T::NCH; const int nv = m.nv;
   double* H = d.qH;
-  if constexpr (LT::single) { PS_LOOP2 for (int i = 0; i < nv; i++) PS_LOOP2 for (int k = 0; k <= i; k++) H[i * S + k] = d.qM[i * S + k]; }   // nothing reads the upper triangle
+  if constexpr (LT::single) {                  // nothing reads the upper triangle; a row's loads are in flight together
+    PS_LOOP2 for (int i = 0; i < nv; i++) {
+      double r[S];
+#pragma unroll
+      for (int k = 0; k < S; k++) if (k <= i) r[k] = d.qM[i * S + k];
+#pragma unroll
+      for (int k = 0; k < S; k++) if (k <= i) H[i * S + k] = r[k];
+    }
+  }
   else CO_FOR(w, nv * S) H[w] = d.qM[w];
   L.sync();
   // unit rows: friction rows hit distinct diagonal entries; limit rows go through one lane, in order
@@ -480,7 +488,7 @@ PS_NI void co_line_eval(const LT& L, const DevModel<T>& m, CoopData<T>& d, const
   *cost = f; *d1 = g; *d2 = h;
 }
 
-// `active` / block_any: see co_constraint_stage.  With block_any(p) == p this is mj_solNewton's exact line search as before:
+// `active`: see co_constraint_stage (a thread without work passes through).  mj_solNewton's exact line search:
 // Newton steps on the 1-D cost, bracketed, until |slope| < gtol or ls_iterations.
 template <class T, class LT>
 PS_NI double co_line_search(const LT& L, const DevModel<T>& m, CoopData<T>& d, const CoSolverScalars& c, bool active = true) { PS_ASSUME_SHARED(&m); if (LT::kSharedData) PS_ASSUME_SHARED(&d);
@@ -508,7 +516,8 @@ PS_NI double co_line_search(const LT& L, const DevModel<T>& m, CoopData<T>& d, c
     }
   }
   int it = 0;
-  while (L.block_any(go)) {
+  // (under block lockstep the line search runs free: its code is small, and a barrier per line-search iteration cost 4.5 %)
+  while (go) {
     if (go) {
       if (dd < 0) lo = alpha; else hi = alpha;
       double an = hh > 0 ? alpha - dd / hh : -1;

@@ -239,7 +239,10 @@ int ps_set_model(PsEngine* e, const PsModel* m) {
   std::vector<double> st(e->ns, 0.0); for (int i = 0; i < m->nq; i++) st[i] = m->qpos0[i];
   chosen->plan(e->h_const, st.data(), e->ns, mocap.data(), m->nmocap, 0.0, nullptr, 0, 0, 0);
   if (e->var_large) e->var_large->plan(e->h_const2, st.data(), e->ns, mocap.data(), m->nmocap, 0.0, nullptr, 0, 0, 0);
-  if (const char* dbg = std::getenv("PS_COOP_SERIAL")) chosen->debug(e->h_const, std::atoi(dbg));
+  if (const char* dbg = std::getenv("PS_COOP_SERIAL")) {
+    chosen->debug(e->h_const, std::atoi(dbg));
+    if (e->var_large && e->var_large->debug) e->var_large->debug(e->h_const2, std::atoi(dbg));
+  }
   e->have_model = true; e->have_task = false; e->wb_valid = false; e->large_ok = true;
   return 0;
 }
