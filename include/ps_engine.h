@@ -64,6 +64,15 @@ int ps_set_options(PsEngine* e, double timestep, int integrator);
 int ps_set_task(PsEngine* e, const PsTask* t);
 /* SamplingPlanner::SetState, planner.cc:146-149 */
 int ps_set_state(PsEngine* e, const double* state, const double* mocap, const double* userdata, double time);
+/* mjData::qacc_warmstart.  The reference's plant is ONE mjData stepped by mj_step (testspeed.cc:95-113, agent.cc
+ * plant step), so its constraint solver starts every step from the previous step's solution.  A closed-loop plant
+ * run as one launch per planning period reproduces that by handing the value across launches:
+ * ps_get_warmstart reads what rollout `sample` of the last writeback batch carried out of its last integrated
+ * step (nv doubles), ps_set_warmstart makes the rollouts of the following launches start from it
+ * (qacc_warmstart = NULL: back to zeros).  Planning rollouts start from zeros -- the pinned reading of
+ * Trajectory::Rollout (trajectory.cc:100-130), whose per-thread mjData holds whatever that thread rolled last. */
+int ps_set_warmstart(PsEngine* e, const double* qacc_warmstart, int nv);
+int ps_get_warmstart(PsEngine* e, int sample, double* qacc_warmstart);
 /* nominal plan (policy.plan): P knot times, knots[P][nu] */
 int ps_set_nominal(PsEngine* e, const double* times, const double* knots, int P, int interpolation);
 /* optional injected standard-normal noise z[N][P][nu] and per-sample second-std flags (parity

@@ -93,6 +93,7 @@ class Agent:
         self.mocap = mo.reshape(-1, 7).copy() if mo is not None else np.zeros((0, 7))
         self.userdata = np.zeros(pm.nuserdata)
         self.ctrl = np.zeros(pm.nu)
+        self._warmstart = np.zeros(pm.nv)              # mjData::qacc_warmstart of the agent-side plant (mj_resetData: zeros)
         for i, w in enumerate(self._default_weights):
             self.task.weight[i] = w; self.plant_task.weight[i] = w
         for i, v in enumerate(self._default_parameters):           # Task::Reset re-reads the residual_* numerics
@@ -185,6 +186,7 @@ class Agent:
         interp = self.settings["interpolation"]
         self.plant.set_state(self._state_vector(), self.time, mocap=self._mocap_flat())
         self.plant.set_nominal(times, knots, interp)
+        self.plant.set_warmstart(self._warmstart)
         self.plant.rollouts(1, steps + 1, 0.0, writeback=True)
         return self.plant.trajectory(0)
 
@@ -193,6 +195,7 @@ class Agent:
         if mo is not None and self.task_id == "Particle":
             self.mocap = mo.reshape(-1, 7).copy()
         tr = self._forward_record(1)
+        self._warmstart = self.plant.warmstart(0)      # mj_step leaves its solution in qacc_warmstart for the next step
         pm = self.plant_model
         self.ctrl = tr["actions"][0].copy()
         st = tr["states"][1]

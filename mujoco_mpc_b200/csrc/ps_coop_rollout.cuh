@@ -132,7 +132,7 @@ PS_FN CoCarry co_rollout_begin(const LT& L, const DevModel<T>& m, const DevPlan<
   const int nq = m.nq, nv = m.nv, na = m.na, nu = m.nu, ns = nq + nv + na;
   if (live) {
     CO_FOR(k, nq) d.qpos[k] = plan.state[k];
-    CO_FOR(k, nv) { d.qvel[k] = plan.state[nq + k]; d.qacc_warmstart[k] = 0; d.qacc[k] = 0; }
+    CO_FOR(k, nv) { d.qvel[k] = plan.state[nq + k]; d.qacc_warmstart[k] = plan.warmstart[k]; d.qacc[k] = 0; }
     CO_FOR(k, na) d.act[k] = plan.state[nq + nv + k];
     CO_FOR(k, nu) d.ctrl[k] = 0;
     CO_FOR(k, m.nmocap) { vcopy(d.mocap_pos + 3 * k, plan.mocap + 7 * k, 3); vcopy(d.mocap_quat + 4 * k, plan.mocap + 7 * k + 3, 4); }
@@ -174,6 +174,8 @@ PS_FN void co_rollout_steps(const LT& L, const DevModel<T>& m, const DevTask& ta
     }
     if (!LT::kBlock && dead) break;
     if (WB && !dead && (!terminal || H > 1)) CO_FOR(a, nu) wb.actions[((size_t)t * nu + a) * stride + i] = d.ctrl[a];
+    // what an mjData stepped H - 1 times carries into its next mj_step (the terminal forward pass below is the planner's, not the plant's)
+    if (WB && terminal && !dead) CO_FOR(k, nv) wb.warmstart[(size_t)k * stride + i] = d.qacc_warmstart[k];
     if constexpr (PT::kActive) { if (!dead) pert.forward(L, m, d); } else co_forward_pass(L, m, d, !dead);
     if (!dead) {
       if (L.lane == 0) {

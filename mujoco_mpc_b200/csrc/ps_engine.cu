@@ -72,7 +72,7 @@ struct PsEngine_ {
   size_t knots_cap = 0, z_cap = 0; bool have_noise = false;
   unsigned long long seed = 1234, iteration = 0;
   // writeback buffers (parity / BestTrajectory), sized on demand
-  Writeback wb{}; size_t wb_cap[6] = {0, 0, 0, 0, 0, 0}; int wb_N = 0, wb_H = 0; bool wb_valid = false;
+  Writeback wb{}; size_t wb_cap[7] = {0, 0, 0, 0, 0, 0, 0}; int wb_N = 0, wb_H = 0; bool wb_valid = false;
   double sigma0 = 0, sigma1 = 0;
   cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
   long long launches = 0;
@@ -169,7 +169,7 @@ void ps_destroy(PsEngine* e) {
   cudaSetDevice(e->device);
   cudaStreamSynchronize(e->stream);
   void* bufs[] = {e->d_const, e->d_nominal, e->d_ctrlrange, e->d_knots, e->d_returns, e->d_record, e->d_z, e->d_failure, e->d_std2,
-                  e->d_blockmin, e->d_counter, e->d_const2, e->wb.states, e->wb.actions, e->wb.residual, e->wb.costs, e->wb.times, e->wb.trace, e->d_scratch,
+                  e->d_blockmin, e->d_counter, e->d_const2, e->wb.states, e->wb.actions, e->wb.residual, e->wb.costs, e->wb.times, e->wb.trace, e->wb.warmstart, e->d_scratch,
                   e->d_xfrc, e->d_param_std, e->d_elite, e->d_ce_out, e->d_fix};
   for (void* b : bufs) if (b) cudaFree(b);
   if (e->comm && nccl_api().ok) nccl_api().CommDestroy(e->comm);
@@ -384,9 +384,10 @@ static int alloc_samples(PsEngine* e, int N) {
 
 static int prepare_writeback(PsEngine* e, int H, int stride) {
   const size_t ns = e->ns, nr = e->task.num_residual, nt = 3 * (size_t)e->task.num_trace;
-  double** ptr[6] = {&e->wb.states, &e->wb.actions, &e->wb.residual, &e->wb.costs, &e->wb.times, &e->wb.trace};
-  const size_t need[6] = {H * ns * stride, (size_t)H * e->nu * stride, H * nr * stride, (size_t)H * stride, (size_t)H * stride, H * (nt ? nt : 1) * stride};
-  for (int k = 0; k < 6; k++) { if (ensure(ptr[k], &e->wb_cap[k], need[k])) return -1; CU(cudaMemsetAsync(*ptr[k], 0, need[k] * sizeof(double), e->stream)); }
+  double** ptr[7] = {&e->wb.states, &e->wb.actions, &e->wb.residual, &e->wb.costs, &e->wb.times, &e->wb.trace, &e->wb.warmstart};
+  const size_t need[7] = {H * ns * stride, (size_t)H * e->nu * stride, H * nr * stride, (size_t)H * stride, (size_t)H * stride, H * (nt ? nt : 1) * stride,
+                          (size_t)(e->nv > 0 ? e->nv : 1) * stride};
+  for (int k = 0; k < 7; k++) { if (ensure(ptr[k], &e->wb_cap[k], need[k])) return -1; CU(cudaMemsetAsync(*ptr[k], 0, need[k] * sizeof(double), e->stream)); }
   return 0;
 }
 
@@ -606,11 +607,12 @@ int ps_get_trajectory(PsEngine* e, int sample, double* states, double* actions, 
   if (!e->wb_valid) {
     // re-roll just this sample with writeback (candidate knots are still resident)
     const size_t ns = e->ns, nr = e->task.num_residual, nt = 3 * (size_t)e->task.num_trace;
-    double** ptr[6] = {&e->wb.states, &e->wb.actions, &e->wb.residual, &e->wb.costs, &e->wb.times, &e->wb.trace};
-    const size_t need[6] = {H * ns * stride, (size_t)H * e->nu * stride, H * nr * stride, (size_t)H * stride, (size_t)H * stride, H * (nt ? nt : 1) * stride};
-    for (int k = 0; k < 6; k++) if (ensure(ptr[k], &e->wb_cap[k], need[k])) return -1;
+    double** ptr[7] = {&e->wb.states, &e->wb.actions, &e->wb.residual, &e->wb.costs, &e->wb.times, &e->wb.trace, &e->wb.warmstart};
+    const size_t need[7] = {H * ns * stride, (size_t)H * e->nu * stride, H * nr * stride, (size_t)H * stride, (size_t)H * stride, H * (nt ? nt : 1) * stride,
+                            (size_t)(e->nv > 0 ? e->nv : 1) * stride};
+    for (int k = 0; k < 7; k++) if (ensure(ptr[k], &e->wb_cap[k], need[k])) return -1;
     // zero this sample's column lazily: a failed rollout leaves later steps untouched, so clear all
-    for (int k = 0; k < 6; k++) CU(cudaMemsetAsync(*ptr[k], 0, need[k] * sizeof(double), e->stream));
+    for (int k = 0; k < 7; k++) CU(cudaMemsetAsync(*ptr[k], 0, need[k] * sizeof(double), e->stream));
     MinLoc* tmp = e->d_blockmin + e->cap;   // spare slot
     // single re-roll: whichever kernel scored the batch (its constants are still resident)
     e->last->launch(e->stream, e->last_dconst, e->d_knots, stride, sample, 1, e->offset, e->d_returns, e->d_failure, tmp, e->wb, true, e->d_counter);
@@ -633,6 +635,26 @@ int ps_get_trajectory(PsEngine* e, int sample, double* states, double* actions, 
   CU(cudaStreamSynchronize(e->stream));
   if (total_return) CU(cudaMemcpy(total_return, e->d_returns + sample, sizeof(double), cudaMemcpyDeviceToHost));
   if (failure) { unsigned char f = 0; CU(cudaMemcpy(&f, e->d_failure + sample, 1, cudaMemcpyDeviceToHost)); *failure = f & 1; }
+  return 0;
+}
+
+// qacc_warmstart of the following launches' rollouts (DevPlan::warmstart); null: back to zeros
+int ps_set_warmstart(PsEngine* e, const double* qacc_warmstart, int nv) {
+  if (!e || !e->have_model) return fail("ps_set_warmstart: no model");
+  if (qacc_warmstart && nv != e->nv) return fail("ps_set_warmstart: nv does not match the model");
+  if (!e->var->warmstart) return fail("ps_set_warmstart: not supported by this kernel");
+  e->var->warmstart(e->h_const, qacc_warmstart, e->nv);
+  if (e->var_large && e->var_large->warmstart) e->var_large->warmstart(e->h_const2, qacc_warmstart, e->nv);
+  return 0;
+}
+
+// qacc_warmstart rollout `sample` of the last writeback batch carried out of its last integrated step
+int ps_get_warmstart(PsEngine* e, int sample, double* qacc_warmstart) {
+  if (!e || !e->wb_valid || !e->wb.warmstart) return fail("ps_get_warmstart: call ps_rollouts_writeback first");
+  if (sample < 0 || sample >= e->wb_N || !qacc_warmstart) return fail("ps_get_warmstart: bad sample");
+  CU(cudaSetDevice(e->device));
+  if (gather_column(e, e->wb.warmstart, e->nv, sample, qacc_warmstart)) return -1;
+  CU(cudaStreamSynchronize(e->stream));
   return 0;
 }
 

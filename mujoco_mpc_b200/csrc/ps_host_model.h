@@ -323,6 +323,13 @@ inline int set_plan(void* c, const double* state, int ns, const double* mocap, i
   return 0;
 }
 
+// DevPlan::warmstart: w (nv entries) or zeros
+template <class T>
+inline void set_warmstart(void* c, const double* w, int nv) {
+  DevPlan<T>& p = reinterpret_cast<Constants<T>*>(c)->p;
+  for (int i = 0; i < T::NV; i++) p.warmstart[i] = (w && i < nv) ? w[i] : 0.0;
+}
+
 
 // PsTask (C ABI) -> DevTask; also reports whether the task reads subtree-velocity sensors
 inline int convert_task(const PsTask* t, const int* sensor_type, int nsensor, DevTask* out, int* need_subtreevel, std::string* why) {

@@ -14,6 +14,7 @@ struct alignas(128) Constants { DevModel<T> m; DevTask t; DevPlan<T> p; };
 // optional full-trajectory outputs, SoA [t][field][stride] with the sample index fastest
 struct Writeback {
   double* states; double* actions; double* residual; double* costs; double* times; double* trace;
+  double* warmstart;      // [nv][stride]: qacc_warmstart after the last integrated step (before the terminal forward pass)
 };
 
 // Force perturbation of the robust re-rolls: standard-normal tensor [(t * 6 nbody + k)][stride] and the discrete
@@ -55,7 +56,7 @@ PS_FN double rollout_sample(const DevModel<T>& m, const TK& task, const DevPlan<
   PS_SPEC_UNROLL
   for (int k = 0; k < nq; k++) d.qpos[k] = plan.state[k];
   PS_SPEC_UNROLL
-  for (int k = 0; k < nv; k++) { d.qvel[k] = plan.state[nq + k]; d.qacc_warmstart[k] = 0; d.qacc[k] = 0; }
+  for (int k = 0; k < nv; k++) { d.qvel[k] = plan.state[nq + k]; d.qacc_warmstart[k] = plan.warmstart[k]; d.qacc[k] = 0; }
   PS_SPEC_UNROLL
   for (int k = 0; k < na; k++) d.act[k] = plan.state[nq + nv + k];
   PS_SPEC_UNROLL
@@ -86,6 +87,8 @@ PS_FN double rollout_sample(const DevModel<T>& m, const TK& task, const DevPlan<
     // terminal: ctrl is NOT rewritten before the final forward pass (trajectory.cc:190-198)
     if (WB && (!terminal || H > 1)) PS_SPEC_UNROLL for (int a = 0; a < nu; a++) wb.actions[((size_t)t * nu + a) * stride + i] = d.ctrl[a];
     if (!terminal && state_is_bad(m, d)) { failed = true; break; }
+    // what an mjData stepped H - 1 times carries into its next mj_step (the terminal forward pass below is the planner's, not the plant's)
+    if (WB && terminal) { PS_SPEC_UNROLL for (int k = 0; k < nv; k++) wb.warmstart[(size_t)k * stride + i] = d.qacc_warmstart[k]; }
     pert.forward(m, d);
     task_residual(m, d, task, residual);
     const double c = cost_value(task, residual);
@@ -154,6 +157,8 @@ PS_FN double rollout_sample(const DevModel<T>& m, const TK& task, const DevPlan<
   if (!failed) {
     // terminal: ctrl is NOT rewritten before the final forward pass (trajectory.cc:190-198)
     if (WB && H > 1) PS_SPEC_UNROLL for (int a = 0; a < nu; a++) wb.actions[((size_t)(H - 1) * nu + a) * stride + i] = d.ctrl[a];
+    // what an mjData stepped H - 1 times carries into its next mj_step (the terminal forward pass below is the planner's, not the plant's)
+    if (WB) { PS_SPEC_UNROLL for (int k = 0; k < nv; k++) wb.warmstart[(size_t)k * stride + i] = d.qacc_warmstart[k]; }
     pert.forward(m, d);
     task_residual(m, d, task, residual);
     const double c = cost_value(task, residual);

@@ -252,6 +252,10 @@ struct alignas(16) DevPlan {
   double time;
   double spline_times[36];   // kMaxSplinePoints-ish cap of the reference GUI (sampling/planner.h:36)
   int num_spline_points, interpolation, horizon, pad_;
+  // qacc_warmstart a rollout's first constraint solve starts from.  Zero for planning rollouts (the pinned reading of
+  // Trajectory::Rollout, whose per-thread mjData carries whatever that thread rolled last); the closed-loop plant sets it
+  // to the value its previous launch ended with (ps_set_warmstart), as one mjData stepped by mj_step carries it over.
+  double warmstart[T::NV];
 };
 
 // dof counts: compile-time in a LEAN instantiation (loops over dofs unroll, small arrays stay in registers)

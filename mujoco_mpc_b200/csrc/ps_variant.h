@@ -131,6 +131,8 @@ struct Variant {
   int (*task_ok)(const DevTask&, int) = nullptr;
   // re-roll of the samples that overflowed this kernel's contact / row capacity (null: the class has no contacts or no larger class)
   void (*fixup)(cudaStream_t, const void*, const double*, int, double*, unsigned char*, const int*, const int*, int*, Writeback, bool) = nullptr;   // model-specialised instantiations: was the kernel compiled for this cost specification?
+  // qacc_warmstart of the next launches' rollouts (null pointer: zeros) -- DevPlan::warmstart, ps_set_warmstart
+  void (*warmstart)(void*, const double*, int) = nullptr;
 };
 // the force-perturbed kernels live in their own translation unit (ps_variant_robust.cu), so that the code
 // generated for the planning kernels of a variant's unit does not depend on them
@@ -142,11 +144,15 @@ int launch_robust_planar_coop(cudaStream_t, const void*, const double*, int, int
 int launch_robust_legged_coop(cudaStream_t, const void*, const double*, int, int, double*, unsigned char*, Writeback, XfrcNoise);
 template <class T, int BLOCK>
 inline Variant make_variant(const char* name, RobustFn robust) {
-  return Variant{name, sizeof(Constants<T>), offsetof(Constants<T>, p), sizeof(DevPlan<T>), BLOCK, false, T::LEAN, fill_model<T>, set_options<T>, set_debug<T>, set_task<T>, set_plan<T>, launch_rollout<T, BLOCK>, robust};
+  Variant v{name, sizeof(Constants<T>), offsetof(Constants<T>, p), sizeof(DevPlan<T>), BLOCK, false, T::LEAN, fill_model<T>, set_options<T>, set_debug<T>, set_task<T>, set_plan<T>, launch_rollout<T, BLOCK>, robust};
+  v.warmstart = set_warmstart<T>;
+  return v;
 }
 template <class T, int WARPS>
 inline Variant make_coop_variant(const char* name, RobustFn robust = nullptr) {
-  return Variant{name, sizeof(Constants<T>), offsetof(Constants<T>, p), sizeof(DevPlan<T>), WARPS * 32, true, true, fill_model<T>, set_options<T>, set_debug<T>, set_task<T>, set_plan<T>, launch_coop<T, WARPS>, robust};
+  Variant v{name, sizeof(Constants<T>), offsetof(Constants<T>, p), sizeof(DevPlan<T>), WARPS * 32, true, true, fill_model<T>, set_options<T>, set_debug<T>, set_task<T>, set_plan<T>, launch_coop<T, WARPS>, robust};
+  v.warmstart = set_warmstart<T>;
+  return v;
 }
 // model-specialised lean instantiation (SpecTraits<Spec>, ps_types.cuh): compile-time topology and cost layout
 template <class T, int BLOCK>
@@ -154,6 +160,7 @@ inline Variant make_spec_variant(const char* name) {
   Variant v{name, sizeof(Constants<T>), offsetof(Constants<T>, p), sizeof(DevPlan<T>), BLOCK, false, true, fill_model_spec<T>, set_options_spec<T>,
             set_debug_spec<T>, set_task_spec<T>, set_plan<T>, launch_rollout<T, BLOCK>, nullptr};
   v.task_ok = task_matches_spec<T>;
+  v.warmstart = set_warmstart<T>;
   return v;
 }
 #define PS_DECL_SPEC_VARIANT(N) const Variant* variant_spec_##N();
@@ -164,7 +171,9 @@ const Variant* variant_planar();
 const Variant* variant_legged();
 template <class T, int BLOCK>
 inline Variant make_sparse_variant(const char* name) {
-  return Variant{name, sizeof(Constants<T>), offsetof(Constants<T>, p), sizeof(DevPlan<T>), BLOCK, true, true, fill_model<T>, set_options<T>, set_debug<T>, set_task<T>, set_plan<T>, launch_sparse<T, BLOCK>, nullptr};
+  Variant v{name, sizeof(Constants<T>), offsetof(Constants<T>, p), sizeof(DevPlan<T>), BLOCK, true, true, fill_model<T>, set_options<T>, set_debug<T>, set_task<T>, set_plan<T>, launch_sparse<T, BLOCK>, nullptr};
+  v.warmstart = set_warmstart<T>;
+  return v;
 }
 // capacity-overflow re-rolls of the legged class (ps_variant_legged_xl.cu)
 void launch_fixup_legged(cudaStream_t, const void*, const double*, int, double*, unsigned char*, const int*, const int*, int*, Writeback, bool);

@@ -18,7 +18,8 @@ EXPORTS = ["ps_last_error", "ps_create", "ps_destroy", "ps_set_model", "ps_set_o
            "ps_kernel_launch_count", "ps_winner_record_device", "ps_stream", "ps_name", "ps_variant", "ps_fp64_peak", "ps_constants_bytes",
            "ps_set_param_std", "ps_elite_update", "ps_elite_update_ms", "ps_get_all_traces",
            "ps_set_engine_flavour", "ps_rollout_candidates", "ps_comm_unique_id", "ps_comm_init", "ps_comm_info",
-           "ps_last_exchange_ms", "ps_sync_record", "ps_last_upload_bytes", "ps_argmin_noalloc", "ps_noalloc_scratch_bytes"]
+           "ps_last_exchange_ms", "ps_sync_record", "ps_last_upload_bytes", "ps_argmin_noalloc", "ps_noalloc_scratch_bytes",
+           "ps_set_warmstart", "ps_get_warmstart"]
 
 
 class EngineError(RuntimeError):
@@ -122,6 +123,17 @@ class Engine:
         s = _arr(state)
         mo = _arr(mocap) if mocap is not None else None
         self._ck(self.L.ps_set_state(self.h, _p(s), _p(mo), None, ctypes.c_double(time)))
+
+    def set_warmstart(self, qacc_warmstart=None):
+        """mjData::qacc_warmstart of the following launches' rollouts (None: zeros, the planning default)"""
+        w = _arr(qacc_warmstart) if qacc_warmstart is not None else None
+        self._ck(self.L.ps_set_warmstart(self.h, _p(w), int(w.size) if w is not None else 0))
+
+    def warmstart(self, sample=0):
+        """qacc_warmstart rollout `sample` of the last writeback batch carried out of its last integrated step"""
+        out = np.zeros(self.model.nv)
+        self._ck(self.L.ps_get_warmstart(self.h, int(sample), _p(out)))
+        return out
 
     def set_nominal(self, times, knots, interp):
         t = _arr(times)

@@ -9,9 +9,10 @@ action = ActionFromPolicy(state, time); mj_step; cost = CostValue(sensordata); a
 `steps_per_planning_iteration`-th step PlanIteration (agent.cc:270-315: planner.SetState(agent.state) -- still
 the pre-step state --, steps = clamp(horizon / agent_timestep + 1, 1, 512), OptimizePolicy).  Covered: the tasks
 whose Transition() is the base no-op (cartpole, acrobot, swimmer, walker) and Particle (Transition moves the goal
-mocap along a Lissajous curve, particle.cc:58-65).  One deviation: the plant runs as one launch per planning
-period, and a launch starts its constraint solver from a zero warm start where the reference's mjData carries
-qacc_warmstart over -- the same solution to solver tolerance (last-bit differences on the contact tasks).
+mocap along a Lissajous curve, particle.cc:58-65).  The plant runs as one launch per planning period; the
+constraint solver's warm start is handed from one launch to the next (ps_get_warmstart / ps_set_warmstart), as the
+reference's one mjData carries qacc_warmstart from step to step.  Quadruped Flat runs with the mode / gait of its
+reset state; its Transition (gait switching, quadruped.cc) is not in this loop.
 
     python -m mujoco_mpc_b200.testspeed --task Cartpole --steps_per_planning_iteration 4 --total_time 10
 """
@@ -85,6 +86,7 @@ def synchronous_planning_cost(task_name, steps_per_planning_iteration=4, total_t
         plant.set_nominal(times, knots, interp)
         plant.rollouts(1, k + 1, 0.0, writeback=True)
         tr = plant.trajectory(0)
+        plant.set_warmstart(plant.warmstart(0))        # one mjData stepped by mj_step carries qacc_warmstart over
         total_cost += float(np.sum(tr["costs"][:k]))
         # agent.state was captured BEFORE the last step (testspeed.cc:97 precedes mj_step): that is what plans
         plan_state = tr["states"][k - 1].copy(); plan_time = float(tr["times"][k - 1])

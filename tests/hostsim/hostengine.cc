@@ -30,6 +30,7 @@ struct Runner {
   virtual void plan(const double* state, int ns, const double* mocap, int nmocap, double time, const double* times, int P, int interp, int H) = 0;
   virtual double roll(const double* knots, const Writeback& wb, int* flags, const XfrcNoise* xf) = 0;
   virtual double timestep() const = 0;
+  virtual void warmstart(const double* w, int nv) = 0;
 };
 template <class T>
 struct RunnerT : Runner {
@@ -49,15 +50,17 @@ struct RunnerT : Runner {
     return rollout_sample<T, true>(c->m, c->t, c->p, knots, 1, 0, wb, flags);
   }
   double timestep() const override { return c->m.timestep; }
+  void warmstart(const double* w, int nv) override { set_warmstart<T>(c, w, nv); }
 };
 
 struct Sample {
-  std::vector<double> states, actions, times, residual, costs, trace;
+  std::vector<double> states, actions, times, residual, costs, trace, warm;
   void size(int H, int ns, int nu, int nr, int nt) {
+    warm.assign(64, 0);       // >= nv of every capacity class
     states.assign((size_t)H * ns, 0); actions.assign((size_t)H * (nu ? nu : 1), 0); times.assign(H, 0);
     residual.assign((size_t)H * (nr ? nr : 1), 0); costs.assign(H, 0); trace.assign((size_t)H * (nt ? nt : 1), 0);
   }
-  Writeback wb() { return Writeback{states.data(), actions.data(), residual.data(), costs.data(), times.data(), trace.data()}; }
+  Writeback wb() { return Writeback{states.data(), actions.data(), residual.data(), costs.data(), times.data(), trace.data(), warm.data()}; }
 };
 }  // namespace
 
@@ -117,6 +120,15 @@ int ps_set_state(PsEngine* e, const double* state, const double* mocap, const do
   std::copy(state, state + e->state.size(), e->state.begin());
   if (mocap && e->m->nmocap) std::copy(mocap, mocap + 7 * e->m->nmocap, e->mocap.begin());
   e->time = time; return 0;
+}
+int ps_set_warmstart(PsEngine* e, const double* w, int nv) {
+  if (!e->run) return fail("ps_set_warmstart: no model");
+  if (w && nv != e->m->nv) return fail("ps_set_warmstart: nv does not match the model");
+  e->run->warmstart(w, e->m->nv); return 0;
+}
+int ps_get_warmstart(PsEngine* e, int sample, double* w) {
+  if (sample < 0 || sample >= (int)e->samples.size() || !w) return fail("ps_get_warmstart: bad sample");
+  std::copy(e->samples[sample].warm.begin(), e->samples[sample].warm.begin() + e->m->nv, w); return 0;
 }
 int ps_set_nominal(PsEngine* e, const double* times, const double* knots, int P, int interp) {
   if (!e->run) return fail("ps_set_nominal: no model");

@@ -31,7 +31,8 @@ static int run(const PsModel* m, const PsTask* t, const PairList& pl, const doub
   Constants<T>* k = (Constants<T>*)c;
   const int ns = m->nq + m->nv + m->na, nr = t->num_residual, nu = m->nu;
   std::vector<double> tm(H), tr((size_t)H * 3 * (t->num_trace ? t->num_trace : 1));
-  Writeback wb{states, actions, residual, costs, tm.data(), tr.data()};
+  std::vector<double> warm(64, 0.0);
+  Writeback wb{states, actions, residual, costs, tm.data(), tr.data(), warm.data()};
   (void)ns; (void)nr; (void)nu;
   if (g_xfrc_z && g_xfrc_std > 0) {      // the instantiation robust_rollout_kernel runs
     XfrcNoise xf{g_xfrc_z, std::exp(-k->m.timestep / g_xfrc_rate), 0.0};
@@ -60,7 +61,8 @@ static int run_coop(const PsModel* m, const PsTask* t, const PairList& pl, const
   set_plan<T>(c, state, m->nq + m->nv + m->na, mocap, m->nmocap, time, times, P, interp, H);
   Constants<T>* k = (Constants<T>*)c;
   std::vector<double> tm(H), tr((size_t)H * 3 * (t->num_trace ? t->num_trace : 1));
-  Writeback wb{states, actions, residual, costs, tm.data(), tr.data()};
+  std::vector<double> warm(64, 0.0);
+  Writeback wb{states, actions, residual, costs, tm.data(), tr.data(), warm.data()};
   std::vector<char> dbuf(sizeof(CoopData<T>) + 256);
   CoopData<T>* d = (CoopData<T>*)(((uintptr_t)dbuf.data() + 127) & ~(uintptr_t)127);
   std::memset((void*)d, 0xFF, sizeof(CoopData<T>));   // poison: a read-before-write shows up as NaN

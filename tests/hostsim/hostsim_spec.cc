@@ -27,7 +27,8 @@ static int run_spec(const PsModel* m, const PsTask* t, const PairList& pl, const
   set_plan<T>(c, state, m->nq + m->nv + m->na, mocap, m->nmocap, time, times, P, interp, H);
   Constants<T>* k = (Constants<T>*)c;
   std::vector<double> tm(H), tr((size_t)H * 3 * (t->num_trace ? t->num_trace : 1));
-  Writeback wb{states, actions, residual, costs, tm.data(), tr.data()};
+  std::vector<double> warm(64, 0.0);
+  Writeback wb{states, actions, residual, costs, tm.data(), tr.data(), warm.data()};
   const SpecTaskView<typename T::Topo> tv(k->t);
   *total = rollout_sample<T, true, false, SpecTaskView<typename T::Topo>>(k->m, tv, k->p, knots, 1, 0, wb, flags);
   return 0;
