@@ -225,6 +225,20 @@ class RefPlanner:
         semantics; off = the reference's (the worker's mjData keeps the previous rollout's)"""
         ref_lib().ref_set_zero_warmstart_on_rewind(int(bool(on)))
 
+    @staticmethod
+    def tolerate_errors(on):
+        """bench-harness switch (ref_planner_wrap.cc): count mju_error calls raised inside the reference's code and go on
+        instead of aborting; off (default) = abort.  Returns nothing; see error_count()."""
+        ref_lib().refp_tolerate_errors(int(bool(on)))
+
+    @staticmethod
+    def error_count(reset=False):
+        L = ref_lib(); L.refp_error_count.restype = ctypes.c_long
+        n = int(L.refp_error_count())
+        if reset:
+            L.refp_error_reset()
+        return n
+
     def task_spec(self):
         nt = self.num_term
         dims = (ctypes.c_int * nt)(); norm = (ctypes.c_int * nt)(); npar = (ctypes.c_int * nt)()

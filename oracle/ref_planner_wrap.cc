@@ -5,6 +5,7 @@
 // (ref_glue.cc).  tools/gen_golden_planner.py drives this to write tests/golden/planner_reference_*.npz, against which
 // the restatement (mm_planner.cc / mm_cost.cc / mm_quadruped.cc) and the CUDA engine are checked; bench.py's CPU arms
 // time it (cpu_baseline.kind = "reference").
+#include <atomic>
 #include <cstring>
 #include <memory>
 #include <string>
@@ -88,6 +89,15 @@ void refp_destroy(void* hp) {
   mj_deleteData(h->scratch); h->planner.reset(); h->pool.reset(); mj_deleteModel(h->model); delete h;
 }
 int refp_max_trajectory(void) { return mjpc::kMaxTrajectory; }
+
+/* mju_error handling of the timed reference arm (ref_shim/mujoco/mujoco.h: mju_shim_error_hook).  on = 1: an error raised
+ * inside the reference's code is counted and execution continues, as MuJoCo does when mju_user_error is installed;
+ * on = 0 (default, every test): abort.  The count is reported next to the timing so that the reader sees it. */
+static std::atomic<long> g_mju_errors{0};
+static void count_mju_error(const char*) { g_mju_errors.fetch_add(1, std::memory_order_relaxed); }
+void refp_tolerate_errors(int on) { mju_shim_error_hook() = on ? count_mju_error : nullptr; }
+long refp_error_count(void) { return g_mju_errors.load(); }
+void refp_error_reset(void) { g_mju_errors.store(0); }
 
 /* planner settings the GUI / numerics expose (public members of SamplingPlanner) */
 void refp_configure(void* hp, int num_spline_points, int interpolation, double sigma0, double sigma1, int num_trajectory, int sliding_plan) {

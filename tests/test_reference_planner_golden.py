@@ -162,3 +162,35 @@ def test_impact_of_the_zero_warm_start_deviation():
         assert res[0][0] == res[1][0], name
         d = np.abs(res[0][1] - res[1][1]).max() / max(1.0, np.abs(res[0][1]).max())
         assert d <= bound, (name, d)
+
+
+@pytest.mark.skipif(not _have_reference(), reason="oracle/_ref with the reference planner is built only where /root/reference exists")
+def test_reference_mju_error_is_counted_when_tolerated(oracle_lib):
+    """Ground() (mjpc/utilities.cc:538-556) calls mju_error when nothing lies under a foot -- a robot more than 0.5 m below the
+    floor.  The reference process would end there; the timed reference arm of bench.py installs a counting handler instead
+    (RefPlanner.tolerate_errors), after which the ray's -1 is used as the distance.  That is the arithmetic of the oracle port
+    (and of the device code), so the residuals agree; without the handler the shim aborts, which is what every other test runs with."""
+    from tests.common import model_mocap
+    model, task, s = registry.load("Quadruped Flat")
+    r = pyoracle.RefPlanner(model, "Quadruped Flat")
+    state = registry.home_state(model).copy()
+    state[2] -= 2.0                                     # trunk (free joint z) two metres under the floor
+    mocap = model_mocap(model)
+    pyoracle.RefPlanner.tolerate_errors(True); pyoracle.RefPlanner.error_count(reset=True)
+    try:
+        res, _, cost = r.residual(state, np.zeros(model.nu), mocap, 0.0)
+        n = pyoracle.RefPlanner.error_count(reset=True)
+    finally:
+        pyoracle.RefPlanner.tolerate_errors(False)
+    assert n >= 1 and np.all(np.isfinite(res)) and np.isfinite(cost)
+    r.export_task_state(task)
+    o = pyoracle.Oracle(model, task)
+    o.reset_data()
+    o.set("qpos", state[:model.nq]); o.set("qvel", state[model.nq:model.nq + model.nv]); o.set("time", [0.0])
+    if model.nmocap:
+        mo = np.asarray(mocap, dtype=np.float64).reshape(-1, 7)
+        o.set("mocap_pos", mo[:, :3].reshape(-1)); o.set("mocap_quat", mo[:, 3:].reshape(-1))
+    o.set("ctrl", np.zeros(model.nu))
+    o.forward()
+    ores = o.get("sensordata")[:task.num_residual]
+    assert np.abs(ores - res).max() <= 1e-9 * max(1.0, np.abs(res).max())

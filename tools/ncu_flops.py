@@ -12,6 +12,6 @@ flops = cnt["dadd"] + cnt["dmul"] + 2 * cnt["dfma"]
 inst = g("smsp__inst_executed.sum")
 print({"flops_per_step": flops / steps, "dadd": cnt["dadd"] / steps, "dmul": cnt["dmul"] / steps, "dfma": cnt["dfma"] / steps,
        "warp_inst_per_step": inst / steps, "thread_inst_per_step": inst * g("smsp__thread_inst_executed_per_inst_executed.ratio") / steps,
-       "dram_bytes_per_step": (g("dram__bytes_read.sum") * {"Gbyte": 1e9, "Mbyte": 1e6, "Kbyte": 1e3, "byte": 1}[rows[1][hdr.index("dram__bytes_read.sum")]]
-                               + g("dram__bytes_write.sum") * {"Gbyte": 1e9, "Mbyte": 1e6, "Kbyte": 1e3, "byte": 1}[rows[1][hdr.index("dram__bytes_write.sum")]]) / steps,
+       "dram_bytes_per_step": (g("dram__bytes_read.sum") * {"Tbyte": 1e12, "Gbyte": 1e9, "Mbyte": 1e6, "Kbyte": 1e3, "byte": 1}[rows[1][hdr.index("dram__bytes_read.sum")]]
+                               + g("dram__bytes_write.sum") * {"Tbyte": 1e12, "Gbyte": 1e9, "Mbyte": 1e6, "Kbyte": 1e3, "byte": 1}[rows[1][hdr.index("dram__bytes_write.sum")]]) / steps,
        "duration_ms": g("gpu__time_duration.sum") * {"s": 1e3, "ms": 1, "us": 1e-3, "ns": 1e-6}.get(rows[1][hdr.index("gpu__time_duration.sum")], 1)})
