@@ -39,7 +39,8 @@ static const Family kFamilies[] = {
     {variant_tiny(), nullptr, 0},
     {variant_planar_coop(), variant_planar(), 2560},         // nv ~ 9: dense thread-per-rollout wins the big batches
     {variant_planar(), nullptr, 0},
-    {variant_legged_coop(), variant_legged_sparse(), 8192},  // nv ~ 18: compressed-Jacobian thread-per-rollout
+    {variant_legged_coop(), variant_legged_sparse(), 6144},  // nv ~ 18: compressed-Jacobian thread-per-rollout (quadruped, 1 s horizon: warp kernel
+                                                             // 617 / 1193 ms at 4096 / 8192 rollouts, thread kernel 816 / 1042 ms: profiles/r02_crossover_legged.txt)
     {variant_legged(), nullptr, 0},
 };
 
