@@ -468,11 +468,17 @@ PS_NT void update_cost(const DevModel<T>& m, RolloutData<T>& d, SolverScalars& c
   }
 }
 
-// H = M + J' D_active J (+ cone blocks), dense Cholesky, search = -H^-1 grad
+// grad = M a - qfrc_smooth - J' f
+template <class T>
+PS_FN void newton_gradient(const DevModel<T>& m, RolloutData<T>& d) {
+  const int nv = nv_of(m);
+  PS_SPEC_UNROLL for (int i = 0; i < nv; i++) d.sv_grad[i] = d.sv_Ma[i] - d.qfrc_smooth[i] - d.qfrc_constraint[i];
+}
+
+// H = M + J' D_active J (+ cone blocks), dense Cholesky, search = -H^-1 grad (grad: newton_gradient)
 template <class T>
 PS_NT void newton_direction(const DevModel<T>& m, RolloutData<T>& d) {
   constexpr int S = T::NV; const int nv = nv_of(m), nefc = d.nefc;
-  PS_SPEC_UNROLL for (int i = 0; i < nv; i++) d.sv_grad[i] = d.sv_Ma[i] - d.qfrc_smooth[i] - d.qfrc_constraint[i];
   double* H = d.sv_H;
   PS_SPEC_UNROLL for (int i = 0; i < nv; i++) PS_SPEC_UNROLL for (int j = 0; j < nv; j++) H[i * S + j] = d.qM[i * S + j];
   for (int r = 0; r < nefc; r++) {
@@ -603,6 +609,7 @@ PS_NT void constraint_stage(const DevModel<T>& m, RolloutData<T>& d) {
   mul_M(m, d, d.sv_Ma, d.qacc);
   for (int r = 0; r < nefc; r++) d.sv_Jaref[r] = vdot(d.efc_J + r * S, d.qacc, nv) - d.efc_aref[r];
   update_cost(m, d, c, coneH);
+  newton_gradient(m, d);
   newton_direction(m, d);
   const double scale = 1.0 / (m.meaninertia * (nv > 1 ? nv : 1));
   int iter = 0;
@@ -612,11 +619,14 @@ PS_NT void constraint_stage(const DevModel<T>& m, RolloutData<T>& d) {
     PS_SPEC_UNROLL for (int i = 0; i < nv; i++) { d.qacc[i] += alpha * d.sv_search[i]; d.sv_Ma[i] += alpha * d.sv_Mv[i]; }
     for (int r = 0; r < nefc; r++) d.sv_Jaref[r] += alpha * d.sv_Jv[r];
     update_cost(m, d, c, coneH);
-    newton_direction(m, d);
+    // mj_solNewton factorises the Hessian and solves for the next direction before it tests for convergence; the direction
+    // of the last iteration is never used, so the test comes first here and the last factorisation is skipped
+    newton_gradient(m, d);
     iter++;
     const double improvement = scale * (c.prev_cost - c.cost);
     const double gradient = scale * sqrt(vdot(d.sv_grad, d.sv_grad, nv));
-    if (improvement < m.tolerance || gradient < m.tolerance) break;
+    if (improvement < m.tolerance || gradient < m.tolerance || iter >= m.iterations) break;
+    newton_direction(m, d);
   }
   d.solver_iter = iter;
   vcopy(d.qacc_warmstart, d.qacc, nv);

@@ -217,9 +217,13 @@ int ps_set_model(PsEngine* e, const PsModel* m) {
   e->h_const2 = nullptr; e->d_const2 = nullptr;
   e->var = chosen; e->h_const = host; e->var_large = nullptr; e->crossover = fam->crossover; e->last = chosen;
   CU(cudaMalloc(&e->d_const, chosen->const_bytes));
-  if (fam->large) {
-    void* h2 = nullptr; CU(cudaMallocHost(&h2, fam->large->const_bytes)); std::memset(h2, 0, fam->large->const_bytes);
-    if (fam->large->fill(m, pl, h2, &why) == 0) { e->var_large = fam->large; e->h_const2 = h2; CU(cudaMalloc(&e->d_const2, fam->large->const_bytes)); }
+  const Variant* large = fam->large;
+  // diagnostics / tuning: PS_PLANAR_LARGE=sparse serves the planar class's big batches with the single-lane phase-parallel
+  // coding (the quadruped's large-batch kernel at planar capacities) instead of the dense thread-per-rollout kernel
+  if (large == variant_planar() && std::getenv("PS_PLANAR_LARGE") && std::string(std::getenv("PS_PLANAR_LARGE")) == "sparse") large = variant_planar_sparse();
+  if (large) {
+    void* h2 = nullptr; CU(cudaMallocHost(&h2, large->const_bytes)); std::memset(h2, 0, large->const_bytes);
+    if (large->fill(m, pl, h2, &why) == 0) { e->var_large = large; e->h_const2 = h2; CU(cudaMalloc(&e->d_const2, large->const_bytes)); }
     else cudaFreeHost(h2);     // the model fits only the small-batch kernel's capacities: it serves every batch size
   }
   e->nbody = m->nbody; e->timestep = m->opt_timestep; e->integrator = m->opt_integrator;
