@@ -74,11 +74,11 @@ PS_NI void co_update_cost(const LT& L, const DevModel<T>& m, CoopData<T>& d, CoS
       double s = 0;
       const int fr = nf ? m.dof_frictionrow[i] : -1;
       if (fr >= 0) { const double f = d.efc_force[fr]; if (f != 0) s += f; }
-      PS_LOOP2 for (int r = nf; r < nf + nl; r++) {
-        const double f = d.efc_force[r];
-        if (f != 0 && m.jnt_dofadr[d.efc_id[r]] == i) s += (double)d.efc_jrow[r] * f;
-      }
       d.qfrc_constraint[i] = s;
+    }
+    PS_LOOP2 for (int r = nf; r < nf + nl; r++) {        // limit rows in order, each into the dof of its joint
+      const double f = d.efc_force[r];
+      if (f != 0) d.qfrc_constraint[m.jnt_dofadr[d.efc_id[r]]] += (double)d.efc_jrow[r] * f;
     }
     constexpr int MR = 6;
     PS_LOOP2 for (int ci = 0; ci < ncon; ci++) {
