@@ -11,6 +11,61 @@ namespace ps {
 template <class T, class LT>
 PS_NI double co_update_rows(const LT& L, const DevModel<T>& m, CoopData<T>& d, const double* jar) { PS_ASSUME_SHARED(&m); if (LT::kSharedData) PS_ASSUME_SHARED(&d);
   const int nefc = d.nefc;
+  if constexpr (LT::single) {
+    // ONE working lane: three homogeneous loops in row order (friction-loss rows, limit rows, contacts -- see co_line_eval),
+    // the cost summed as the rows go by: the same terms in the same order as the loop over row indices below
+    double cost = 0;
+    const int nf = (m.disableflags & DSBL_FRICTIONLOSS) ? 0 : m.nfrictionrow;
+    const int nl = d.nlimit, ncon = d.ncon;
+    PS_LOOP2 for (int i = 0; i < nf; i++) {
+      const double D = d.efc_D[i], R = d.efc_R[i], x = jar[i];
+      const double f = m.dof_frictionloss[d.efc_id[i]];
+      if (x <= -R * f) { d.efc_state[i] = ST_LINEARNEG; d.efc_force[i] = f; cost += -0.5 * R * f * f - f * x; }
+      else if (x >= R * f) { d.efc_state[i] = ST_LINEARPOS; d.efc_force[i] = -f; cost += -0.5 * R * f * f + f * x; }
+      else { d.efc_state[i] = ST_QUADRATIC; d.efc_force[i] = -D * x; cost += 0.5 * D * x * x; }
+    }
+    PS_LOOP2 for (int i = nf; i < nf + nl; i++) {
+      const double D = d.efc_D[i], x = jar[i];
+      if (x < 0) { d.efc_state[i] = ST_QUADRATIC; d.efc_force[i] = -D * x; cost += 0.5 * D * x * x; }
+      else { d.efc_state[i] = ST_SATISFIED; d.efc_force[i] = 0; cost += 0.0; }
+    }
+    PS_LOOP2 for (int ci = 0; ci < ncon; ci++) {
+      const CoopContact& con = d.contact[ci];
+      const int i = con.efc_address;
+      if (i < 0) continue;
+      if (d.efc_type[i] != EFC_CONTACT_ELLIPTIC) {
+        const int nrow = con.nrow;
+        PS_LOOP2 for (int q = 0; q < nrow; q++) {
+          const double D = d.efc_D[i + q], x = jar[i + q];
+          if (x < 0) { d.efc_state[i + q] = ST_QUADRATIC; d.efc_force[i + q] = -D * x; cost += 0.5 * D * x * x; }
+          else { d.efc_state[i + q] = ST_SATISFIED; d.efc_force[i + q] = 0; cost += 0.0; }
+        }
+        continue;
+      }
+      const int dim = con.dim; const double mu = con.mu; const double* fr = con.friction;
+      double U[6]; U[0] = jar[i] * mu;
+      PS_LOOP2 for (int j = 1; j < dim; j++) U[j] = jar[i + j] * fr[j - 1];
+      const double N = U[0]; double TT = 0;
+      PS_LOOP2 for (int j = 1; j < dim; j++) TT += U[j] * U[j];
+      const double Tn = sqrt(TT);
+      int st;
+      if (N >= mu * Tn || (Tn <= 0 && N >= 0)) {
+        st = ST_SATISFIED; PS_LOOP2 for (int j = 0; j < dim; j++) { d.efc_force[i + j] = 0; cost += 0.0; }
+      } else if (mu * N + Tn <= 0 || (Tn <= 0 && N < 0)) {
+        st = ST_QUADRATIC;
+        PS_LOOP2 for (int j = 0; j < dim; j++) { d.efc_force[i + j] = -d.efc_D[i + j] * jar[i + j]; cost += 0.5 * d.efc_D[i + j] * jar[i + j] * jar[i + j]; }
+      } else {
+        st = ST_CONE;
+        const double Dm = d.efc_D[i] / (mu * mu * (1 + mu * mu));
+        const double NT = N - mu * Tn;
+        cost += 0.5 * Dm * NT * NT;
+        d.efc_force[i] = -Dm * NT * mu;
+        PS_LOOP2 for (int j = 1; j < dim; j++) { d.efc_force[i + j] = -d.efc_force[i] / Tn * U[j] * fr[j - 1]; cost += 0.0; }
+      }
+      PS_LOOP2 for (int j = 0; j < dim; j++) d.efc_state[i + j] = (unsigned char)st;
+    }
+    return cost;
+  }
   CO_FOR(i, nefc) {
     const int tp = d.efc_type[i];
     const double D = d.efc_D[i], R = d.efc_R[i], x = jar[i];
@@ -391,45 +446,59 @@ PS_NI void co_line_eval(const LT& L, const DevModel<T>& m, CoopData<T>& d, const
   const int nefc = d.nefc;
   if constexpr (LT::single) {
     // ONE working lane: the rows' terms go straight into the three sums, in row order (a cone's trailing rows add their
-    // zeros like the two-pass form below does) -- no per-row stores and no second pass over them
+    // zeros like the two-pass form below does) -- no per-row stores and no second pass over them.  The rows are walked
+    // as three homogeneous loops -- friction-loss rows, limit rows, contacts: that IS the row order (co_make_constraint) --
+    // so that the threads of a warp run the same code at the same time; one loop over row indices with a branch on the row
+    // type had them at 5 of 32 lanes (ncu), because rollouts with different limit counts hold different row types at one index.
     double f = qg[0] + alpha * qg[1] + alpha * alpha * qg[2], g = qg[1] + 2 * alpha * qg[2], h = 2 * qg[2];
-    PS_LOOP2 for (int i = 0; i < nefc; i++) {
-      const int tp = d.efc_type[i];
-      const double D = d.efc_D[i];
-      const double v = d.sv_Jv[i], x = d.sv_Jaref[i] + alpha * v;
-      if (tp == EFC_FRICTION_DOF) {
-        const double R = d.efc_R[i], fl = m.dof_frictionloss[d.efc_id[i]];
-        if (x <= -R * fl) { f += -0.5 * R * fl * fl - fl * x; g += -fl * v; h += 0.0; }
-        else if (x >= R * fl) { f += -0.5 * R * fl * fl + fl * x; g += fl * v; h += 0.0; }
-        else { f += 0.5 * D * x * x; g += D * x * v; h += D * v * v; }
-      } else if (tp != EFC_CONTACT_ELLIPTIC) {
-        if (x < 0) { f += 0.5 * D * x * x; g += D * x * v; h += D * v * v; }
-        else { f += 0.0; g += 0.0; h += 0.0; }
+    const int nf = (m.disableflags & DSBL_FRICTIONLOSS) ? 0 : m.nfrictionrow;
+    const int nl = d.nlimit, ncon = d.ncon;
+    PS_LOOP2 for (int i = 0; i < nf; i++) {
+      const double D = d.efc_D[i], v = d.sv_Jv[i], x = d.sv_Jaref[i] + alpha * v;
+      const double R = d.efc_R[i], fl = m.dof_frictionloss[d.efc_id[i]];
+      if (x <= -R * fl) { f += -0.5 * R * fl * fl - fl * x; g += -fl * v; h += 0.0; }
+      else if (x >= R * fl) { f += -0.5 * R * fl * fl + fl * x; g += fl * v; h += 0.0; }
+      else { f += 0.5 * D * x * x; g += D * x * v; h += D * v * v; }
+    }
+    PS_LOOP2 for (int i = nf; i < nf + nl; i++) {
+      const double D = d.efc_D[i], v = d.sv_Jv[i], x = d.sv_Jaref[i] + alpha * v;
+      if (x < 0) { f += 0.5 * D * x * x; g += D * x * v; h += D * v * v; }
+      else { f += 0.0; g += 0.0; h += 0.0; }
+    }
+    PS_LOOP2 for (int ci = 0; ci < ncon; ci++) {
+      const CoopContact& con = d.contact[ci];
+      const int i = con.efc_address;
+      if (i < 0) continue;
+      if (d.efc_type[i] != EFC_CONTACT_ELLIPTIC) {          // frictionless / pyramidal rows: plain inequalities
+        const int nrow = con.nrow;
+        PS_LOOP2 for (int q = 0; q < nrow; q++) {
+          const double D = d.efc_D[i + q], v = d.sv_Jv[i + q], x = d.sv_Jaref[i + q] + alpha * v;
+          if (x < 0) { f += 0.5 * D * x * x; g += D * x * v; h += D * v * v; }
+          else { f += 0.0; g += 0.0; h += 0.0; }
+        }
+        continue;
+      }
+      const double D = d.efc_D[i], v = d.sv_Jv[i], x = d.sv_Jaref[i] + alpha * v;
+      const int dim = con.dim; const double mu = con.mu; const double* fr = con.friction;
+      const double N = x * mu, Np = v * mu; double TT = 0, UV = 0, VV = 0;
+      PS_LOOP2 for (int j = 1; j < dim; j++) {
+        const double u = (d.sv_Jaref[i + j] + alpha * d.sv_Jv[i + j]) * fr[j - 1], w = d.sv_Jv[i + j] * fr[j - 1];
+        TT += u * u; UV += u * w; VV += w * w;
+      }
+      const double Tn = sqrt(TT);
+      if (N >= mu * Tn || (Tn <= 0 && N >= 0)) {
+        PS_LOOP2 for (int j = 0; j < dim; j++) { f += 0.0; g += 0.0; h += 0.0; }
+      } else if (mu * N + Tn <= 0 || (Tn <= 0 && N < 0)) {
+        PS_LOOP2 for (int j = 0; j < dim; j++) {
+          const double xj = d.sv_Jaref[i + j] + alpha * d.sv_Jv[i + j], vj = d.sv_Jv[i + j], Dj = d.efc_D[i + j];
+          f += 0.5 * Dj * xj * xj; g += Dj * xj * vj; h += Dj * vj * vj;
+        }
       } else {
-        const CoopContact& con = d.contact[d.efc_id[i]];
-        if (i != con.efc_address) continue;
-        const int dim = con.dim; const double mu = con.mu; const double* fr = con.friction;
-        const double N = x * mu, Np = v * mu; double TT = 0, UV = 0, VV = 0;
-        PS_LOOP2 for (int j = 1; j < dim; j++) {
-          const double u = (d.sv_Jaref[i + j] + alpha * d.sv_Jv[i + j]) * fr[j - 1], w = d.sv_Jv[i + j] * fr[j - 1];
-          TT += u * u; UV += u * w; VV += w * w;
-        }
-        const double Tn = sqrt(TT);
-        if (N >= mu * Tn || (Tn <= 0 && N >= 0)) {
-          PS_LOOP2 for (int j = 0; j < dim; j++) { f += 0.0; g += 0.0; h += 0.0; }
-        } else if (mu * N + Tn <= 0 || (Tn <= 0 && N < 0)) {
-          PS_LOOP2 for (int j = 0; j < dim; j++) {
-            const double xj = d.sv_Jaref[i + j] + alpha * d.sv_Jv[i + j], vj = d.sv_Jv[i + j], Dj = d.efc_D[i + j];
-            f += 0.5 * Dj * xj * xj; g += Dj * xj * vj; h += Dj * vj * vj;
-          }
-        } else {
-          const double Dm = D / (mu * mu * (1 + mu * mu));
-          const double Tp = UV / Tn, Tpp = VV / Tn - UV * UV / (Tn * Tn * Tn);
-          const double NT = N - mu * Tn, NTp = Np - mu * Tp;
-          f += 0.5 * Dm * NT * NT; g += Dm * NT * NTp; h += Dm * (NTp * NTp + NT * (-mu * Tpp));
-          PS_LOOP2 for (int j = 1; j < dim; j++) { f += 0.0; g += 0.0; h += 0.0; }
-        }
-        i += dim - 1;
+        const double Dm = D / (mu * mu * (1 + mu * mu));
+        const double Tp = UV / Tn, Tpp = VV / Tn - UV * UV / (Tn * Tn * Tn);
+        const double NT = N - mu * Tn, NTp = Np - mu * Tp;
+        f += 0.5 * Dm * NT * NT; g += Dm * NT * NTp; h += Dm * (NTp * NTp + NT * (-mu * Tpp));
+        PS_LOOP2 for (int j = 1; j < dim; j++) { f += 0.0; g += 0.0; h += 0.0; }
       }
     }
     *cost = f; *d1 = g; *d2 = h;
