@@ -226,8 +226,13 @@ PS_NI void co_mass_matrix(const LT& L, const DevModel<T>& m, CoopData<T>& d) { P
   co_factor_tree(L, m, d.qH, d.qLDiagInv);
 }
 
+// One working lane at the class capacity: co_mul_M can leave a copy of M's lower triangle in `Hcopy` while the rows are in
+// registers, so that the Newton direction that follows does not load M again (co_newton_direction; every direction is
+// preceded by an M v whose H is dead: the product before the solver's loop, or the line search's)
+template <class T, class LT> PS_HD bool co_H_prefilled(const DevModel<T>& m) { return LT::single && m.nv == T::NV; }
+
 template <class T, class LT>
-PS_NI void co_mul_M(const LT& L, const DevModel<T>& m, const CoopData<T>& d, double* res, const double* vec) { PS_ASSUME_SHARED(&m); if (LT::kSharedData) PS_ASSUME_SHARED(&d);
+PS_NI void co_mul_M(const LT& L, const DevModel<T>& m, const CoopData<T>& d, double* res, const double* vec, double* Hcopy = nullptr) { PS_ASSUME_SHARED(&m); if (LT::kSharedData) PS_ASSUME_SHARED(&d);
   if constexpr (LT::single) {
     // one working lane: the vector is loaded once and stays in registers (the dots are those of vdot, j ascending)
     constexpr int S = T::NV; const int nv = m.nv;
@@ -242,6 +247,10 @@ PS_NI void co_mul_M(const LT& L, const DevModel<T>& m, const CoopData<T>& d, dou
         double r0[S], r1[S];
 #pragma unroll
         for (int j = 0; j < S; j++) { r0[j] = row[j]; r1[j] = row[S + j]; }
+        if (Hcopy) {
+#pragma unroll
+          for (int j = 0; j < S; j++) { if (j <= i) Hcopy[i * S + j] = r0[j]; if (j <= i + 1) Hcopy[(i + 1) * S + j] = r1[j]; }
+        }
         double s0 = 0, s1 = 0;
 #pragma unroll
         for (int j = 0; j < S; j++) { s0 += r0[j] * v[j]; s1 += r1[j] * v[j]; }
@@ -251,7 +260,7 @@ PS_NI void co_mul_M(const LT& L, const DevModel<T>& m, const CoopData<T>& d, dou
         const double* row = d.qM + (S - 1) * S;
         double s = 0;
 #pragma unroll
-        for (int j = 0; j < S; j++) s += row[j] * v[j];
+        for (int j = 0; j < S; j++) { const double x = row[j]; if (Hcopy) Hcopy[(S - 1) * S + j] = x; s += x * v[j]; }
         res[S - 1] = s;
       }
       return;

@@ -258,7 +258,9 @@ PS_NI void co_newton_direction(const LT& L, const DevModel<T>& m, CoopData<T>& d
   constexpr int S = T::NV, NCH = T::NCH; const int nv = m.nv;
   double* H = d.qH;
   if constexpr (LT::single) {                  // nothing reads the upper triangle; a row's loads are in flight together
-    PS_LOOP2 for (int i = 0; i < nv; i++) {
+    // at the class capacity H already holds M: the M v that precedes every direction stored it (co_mul_M, co_H_prefilled) --
+    // ncu had 8.7 % of the kernel's stall samples on this copy's loads, M having been evicted since the product read it
+    if (!co_H_prefilled<T, LT>(m)) PS_LOOP2 for (int i = 0; i < nv; i++) {
       double r[S];
 #pragma unroll
       for (int k = 0; k < S; k++) if (k <= i) r[k] = d.qM[i * S + k];
@@ -571,7 +573,7 @@ PS_NI double co_line_search(const LT& L, const DevModel<T>& m, CoopData<T>& d, c
     else {
       const double scale = 1.0 / (m.meaninertia * (nv > 1 ? nv : 1));
       gtol = m.tolerance * m.ls_tolerance * snorm / scale;
-      co_mul_M(L, m, d, d.sv_Mv, d.sv_search);
+      co_mul_M(L, m, d, d.sv_Mv, d.sv_search, co_H_prefilled<T, LT>(m) ? d.qH : nullptr);     // + H := M for the direction that follows
       CO_FOR(r, nefc) d.sv_Jv[r] = co_row_dot(m, d, r, d.sv_search);
       L.sync();
       PS_LOOP2 for (int i = 0; i < nv; i++) { qg[1] += d.sv_search[i] * (d.sv_Ma[i] - d.qfrc_smooth[i]); qg[2] += 0.5 * d.sv_search[i] * d.sv_Mv[i]; }
@@ -633,7 +635,7 @@ PS_NI void co_constraint_stage(const LT& L, const DevModel<T>& m, CoopData<T>& d
       if (cw > cs) { CO_FOR(i, nv) d.qacc[i] = d.qacc_smooth[i]; }
       L.sync();
     } else { CO_FOR(i, nv) d.qacc[i] = d.qacc_smooth[i]; L.sync(); }
-    co_mul_M(L, m, d, d.sv_Ma, d.qacc);
+    co_mul_M(L, m, d, d.sv_Ma, d.qacc, co_H_prefilled<T, LT>(m) ? d.qH : nullptr);             // + H := M for the first direction
     CO_FOR(r, nefc) d.sv_Jaref[r] = co_row_dot(m, d, r, d.qacc) - d.efc_aref[r];
     L.sync();
     co_update_cost(L, m, d, c);
