@@ -80,8 +80,40 @@ PS_NI void co_kinematics(const LT& L, const DevModel<T>& m, CoopData<T>& d) { PS
 
 // fold children into parents, deepest level first: x[p] += x[c] for c in children(p), decreasing c,
 // `n` values per body.  include_world: whether body 0 accumulates too.
+// the same for ONE working lane and N values per body known at compile time: a parent's N sums sit in registers while its
+// children go by (each element still receives its children in list order), a child's N loads are independent of each other
+template <int N, class T>
+PS_FN void co_fold_children_single(const DevModel<T>& m, double* x, bool include_world) {
+  PS_LOOP2 for (int l = m.nlevel - 2; l >= (include_world ? 0 : 1); l--) {
+    const int a = m.level_adr[l], nb = m.level_adr[l + 1] - a;
+    PS_LOOP2 for (int bi = 0; bi < nb; bi++) {
+      const int p = m.level_body[a + bi];
+      const int c0 = m.child_adr[p], c1 = m.child_adr[p + 1];
+      if (c0 == c1) continue;                        // a leaf keeps its values
+      double acc[N];
+#pragma unroll
+      for (int k = 0; k < N; k++) acc[k] = x[N * p + k];
+      PS_LOOP2 for (int c = c0; c < c1; c++) {
+        const double* xc = x + N * m.child_list[c];
+        double v[N];
+#pragma unroll
+        for (int k = 0; k < N; k++) v[k] = xc[k];
+#pragma unroll
+        for (int k = 0; k < N; k++) acc[k] += v[k];
+      }
+#pragma unroll
+      for (int k = 0; k < N; k++) x[N * p + k] = acc[k];
+    }
+  }
+}
+
 template <class T, class LT>
 PS_NI void co_fold_children(const LT& L, const DevModel<T>& m, double* x, int n, bool include_world) { PS_ASSUME_SHARED(&m);
+  if constexpr (LT::single) {
+    if (n == 3) { co_fold_children_single<3>(m, x, include_world); return; }
+    if (n == 6) { co_fold_children_single<6>(m, x, include_world); return; }
+    if (n == 10) { co_fold_children_single<10>(m, x, include_world); return; }
+  }
   PS_LOOP2 for (int l = m.nlevel - 2; l >= (include_world ? 0 : 1); l--) {
     const int a = m.level_adr[l], nb = m.level_adr[l + 1] - a;
     CO_FOR2(w, nb, bi, n, k) {
@@ -157,6 +189,20 @@ PS_NI void co_factor_tree(const LT& L, const DevModel<T>& m, double* A, double* 
     if (dk < kMinVal) { dk = kMinVal; if (L.lane == 0) A[k * S + k] = kMinVal; }
     const int pa = m.fpair_adr[k], np = m.fpair_adr[k + 1] - pa;
     if (np == 0) continue;                    // dof without ancestors: nothing to eliminate
+    if constexpr (LT::single) {
+      // ONE working lane: the quotient A[k][i] / dk depends on i alone and the pair list is grouped by i (ps_host_model.h),
+      // so it is formed once per ancestor instead of once per pair, and it IS the normalised entry the second loop below
+      // would divide out again (row k is not touched by the pair updates): 99 FP64 divisions per factorisation of the
+      // quadruped's tree instead of 474, the same values in the same places
+      int last = -1; double tmp = 0;
+      PS_LOOP2 for (int w = 0; w < np; w++) {
+        const int i = m.fpair_i[pa + w], j = m.fpair_j[pa + w];
+        if (i != last) { if (last >= 0) A[k * S + last] = tmp; tmp = A[k * S + i] / dk; last = i; }
+        A[i * S + j] -= A[k * S + j] * tmp;
+      }
+      if (last >= 0) A[k * S + last] = tmp;
+      continue;
+    }
     CO_FOR(w, np) {
       const int i = m.fpair_i[pa + w], j = m.fpair_j[pa + w];
       const double tmp = A[k * S + i] / dk;
