@@ -16,12 +16,12 @@ def rel_err(a, b):
     return np.abs(a - b).max() / max(1.0, np.abs(b).max())
 
 
-def run_case(name, N, interp, H=None, seed=2024, sigma=None, time=0.37, warm=True, prep=None, engine=None, expect=None, state=None):
+def run_case(name, N, interp, H=None, seed=2024, sigma=None, time=0.37, warm=True, prep=None, engine=None, expect=None, state=None, P=None):
     model, task, s = registry.load(name)
     if prep is not None:
         prep(model, task)
     H = H or s["steps"]
-    P = min(s["num_spline_points"], 36)
+    P = min(s["num_spline_points"], 36) if P is None else P
     sigma = s["exploration"] if sigma is None else sigma
     rng = np.random.default_rng(seed)
     z = rng.standard_normal((N, P, model.nu))
@@ -79,6 +79,38 @@ def run_case(name, N, interp, H=None, seed=2024, sigma=None, time=0.37, warm=Tru
     assert np.allclose(e.knots(gw), pk, rtol=0, atol=1e-14)
     e.close()
     return worst_s, worst_r
+
+
+# The edges of the domain, through the C ABI: one sample, the terminal forward pass alone (H = 1), one integrated step, a batch
+# that is not a multiple of a warp, kMaxTrajectoryHorizon = 512 (mjpc/trajectory.h:27), one knot, the 36-knot maximum of the
+# reference's GUI (planners/sampling/planner.h:36) -- on every capacity class.  (tests/test_hostsim_parity.py runs the same edges
+# on the host-compiled kernel source at bit equality.)
+@pytest.mark.parametrize("name,N,H,interp,P,warm", [
+    ("Cartpole", 1, 1, 0, None, False), ("Cartpole", 1, 2, 2, None, True), ("Cartpole", 33, 7, 1, None, True),
+    ("Cartpole", 7, 512, 2, None, True), ("Particle", 129, 51, 0, 1, False), ("Acrobot", 5, 40, 2, 36, True),
+    ("Walker", 3, 1, 2, None, False), ("Walker", 3, 2, 2, None, True), ("Quadruped Flat", 3, 1, 2, None, False),
+    ("Quadruped Flat", 3, 2, 2, None, True), ("Quadruped Flat", 37, 6, 1, 36, True)])
+def test_parity_at_the_size_limits(oracle_lib, name, N, H, interp, P, warm):
+    from mujoco_mpc_b200 import task as T
+    prep = (lambda m, t: T.quadruped_snapshot(m, t, mode="Quadruped", gait="Trot", time=0.0)) if name.startswith("Quadruped") else None
+    run_case(name, N, interp, H=H, P=P, warm=warm, prep=prep)
+
+
+def test_sizes_beyond_the_limits_are_rejected():
+    """kMaxTrajectoryHorizon = 512 steps and 36 knots are hard limits of the reference's arrays; the engine refuses anything
+    beyond them (and empty batches / horizons) with an error instead of truncating."""
+    from mujoco_mpc_b200.engine import EngineError
+    model, task, s = registry.load("Cartpole")
+    e = Engine(model, task)
+    e.set_state(synthetic_state(model), 0.0)
+    with pytest.raises(EngineError):
+        e.set_nominal(np.linspace(0, 1, 37), np.zeros((37, model.nu)), 2)
+    e.set_nominal(np.linspace(0, 1, 5), np.zeros((5, model.nu)), 2)
+    for N, H in ((4, 513), (0, 10), (4, 0)):
+        with pytest.raises(EngineError):
+            e.rollouts(N, H, 0.1)
+    e.rollouts(4, 512, 0.1)                   # the limit itself is fine
+    e.close()
 
 
 @pytest.mark.parametrize("name", ["Particle", "Cartpole", "Acrobot"])

@@ -15,11 +15,12 @@ def hostsim_lib(oracle_lib):
     return driver.build()
 
 
-def check(name, H, prep=None, N=3, sigma=0.2, time=0.3, seed=0, coop=False, spec=None):
+def check(name, H, prep=None, N=3, sigma=0.2, time=0.3, seed=0, coop=False, spec=None, P=None, interp=None):
     m, t, s = registry.load(name)
     if prep:
         prep(m, t)
-    P, interp = min(s["num_spline_points"], 36), s["interpolation"]
+    P = min(s["num_spline_points"], 36) if P is None else P
+    interp = s["interpolation"] if interp is None else interp
     st = registry.synthetic_state(m, seed=3)
     z = np.random.default_rng(seed).standard_normal((N, P * m.nu))
     o = pyoracle.Oracle(m, t); o.configure(P, interp, sigma); o.set_state(st, time)
@@ -44,6 +45,20 @@ def check(name, H, prep=None, N=3, sigma=0.2, time=0.3, seed=0, coop=False, spec
 @pytest.mark.parametrize("name,H", [("Particle", 51), ("Cartpole", 101), ("Acrobot", 101), ("Swimmer", 40), ("Walker", 60)])
 def test_kernel_source_matches_oracle(hostsim_lib, name, H):
     check(name, H)
+
+
+# The edges of the domain: the terminal forward pass alone (H = 1), one integrated step, kMaxTrajectoryHorizon = 512
+# (mjpc/trajectory.h:27), one knot, the 36-knot maximum of the reference's GUI (planners/sampling/planner.h:36), on every capacity
+# class and both codings of the step.
+@pytest.mark.parametrize("name,H,P,interp,coop", [
+    ("Cartpole", 1, None, None, False), ("Cartpole", 2, None, None, False), ("Cartpole", 512, None, None, False),
+    ("Particle", 51, 1, 0, False), ("Particle", 51, 2, 1, False), ("Acrobot", 40, 36, 2, False),
+    ("Walker", 1, None, None, False), ("Walker", 2, None, None, True), ("Walker", 30, 36, 2, True),
+    ("Quadruped Flat", 1, None, None, True), ("Quadruped Flat", 2, None, None, False), ("Quadruped Flat", 6, 36, 1, True),
+    ("Quadruped Flat", 6, 1, 0, True)])
+def test_kernel_source_matches_oracle_at_the_size_limits(hostsim_lib, name, H, P, interp, coop):
+    prep = (lambda m, t: T.quadruped_snapshot(m, t, mode="Quadruped", gait="Trot", time=0.0)) if name.startswith("Quadruped") else None
+    check(name, H, prep=prep, P=P, interp=interp, coop=coop)
 
 
 @pytest.mark.parametrize("name,H,sigma", [("Particle", 51, 0.2), ("Cartpole", 101, 0.2), ("Cartpole", 201, 1.0), ("Acrobot", 101, 0.2),
