@@ -618,11 +618,12 @@ PS_NI void co_constraint_stage(const LT& L, const DevModel<T>& m, CoopData<T>& d
   }
   CoSolverScalars c; c.cost = 0; c.prev_cost = 0; c.gauss = 0;
   if (run) {
+    double* const Hcopy = co_H_prefilled<T, LT>(m) ? d.qH : nullptr;                 // + H := M for the first direction (co_mul_M)
     if (!(m.disableflags & DSBL_WARMSTART)) {
       // keep the warm start only if it beats the unconstrained acceleration
       CO_FOR(i, nv) d.qacc[i] = d.qacc_warmstart[i];
       L.sync();
-      co_mul_M(L, m, d, d.sv_Ma, d.qacc);
+      co_mul_M(L, m, d, d.sv_Ma, d.qacc, Hcopy);
       CO_FOR(r, nefc) d.sv_Jaref[r] = co_row_dot(m, d, r, d.qacc) - d.efc_aref[r];
       L.sync();
       double cw = co_update_rows(L, m, d, d.sv_Jaref);
@@ -632,12 +633,23 @@ PS_NI void co_constraint_stage(const LT& L, const DevModel<T>& m, CoopData<T>& d
       L.sync();
       const double cs = co_update_rows(L, m, d, d.sv_Jv);
       L.sync();
-      if (cw > cs) { CO_FOR(i, nv) d.qacc[i] = d.qacc_smooth[i]; }
+      // M qacc and J qacc - aref of the chosen start: the warm start's are in sv_Ma / sv_Jaref already (computed above, not
+      // touched since); the unconstrained acceleration's J a - aref is sv_Jv.  mj_solNewton computes both again -- the same
+      // operations on the same operands, so the same bits -- at the price of one more pass over M and over every Jacobian row.
+      if (cw > cs) {
+        CO_FOR(i, nv) d.qacc[i] = d.qacc_smooth[i];
+        CO_FOR(r, nefc) d.sv_Jaref[r] = d.sv_Jv[r];
+        L.sync();
+        co_mul_M(L, m, d, d.sv_Ma, d.qacc);
+      }
       L.sync();
-    } else { CO_FOR(i, nv) d.qacc[i] = d.qacc_smooth[i]; L.sync(); }
-    co_mul_M(L, m, d, d.sv_Ma, d.qacc, co_H_prefilled<T, LT>(m) ? d.qH : nullptr);             // + H := M for the first direction
-    CO_FOR(r, nefc) d.sv_Jaref[r] = co_row_dot(m, d, r, d.qacc) - d.efc_aref[r];
-    L.sync();
+    } else {
+      CO_FOR(i, nv) d.qacc[i] = d.qacc_smooth[i];
+      L.sync();
+      co_mul_M(L, m, d, d.sv_Ma, d.qacc, Hcopy);
+      CO_FOR(r, nefc) d.sv_Jaref[r] = co_row_dot(m, d, r, d.qacc) - d.efc_aref[r];
+      L.sync();
+    }
     co_update_cost(L, m, d, c);
     co_newton_gradient(L, m, d);
     co_newton_direction(L, m, d);
