@@ -244,7 +244,11 @@ template <class T, int WARPS, bool WB>
 __global__ void __launch_bounds__(WARPS * 32)
 coop_rollout_kernel(const Constants<T>* __restrict__ gconst, const double* __restrict__ knots, int stride, int first, int n,
                     long long sample_offset, double* __restrict__ returns, unsigned char* __restrict__ failure,
-                    MinLoc* __restrict__ block_min, Writeback wb, int* __restrict__ counter) {
+                    MinLoc* __restrict__ block_min, Writeback wb, int* __restrict__ counter, int active_warps) {
+  // active_warps: how many of the block's WARPS pull rollouts (launch_coop).  A batch smaller than WARPS x the SM count is
+  // spread over the SMs instead of packed WARPS to an SM: a rollout alone on its SM runs about twice as fast as one that
+  // shares the SM's instruction cache and issue slots with three others at other places in the code (ncu, N = 128:
+  // `no_instruction` 1.8 cycles per issue on 32 of 148 SMs).  The other warps go straight to the closing barrier.
   extern __shared__ __align__(128) unsigned char smem[];
   Constants<T>& sc = *reinterpret_cast<Constants<T>*>(smem);
   constexpr size_t kConst = (sizeof(Constants<T>) + 127) / 128 * 128;
@@ -269,7 +273,7 @@ coop_rollout_kernel(const Constants<T>* __restrict__ gconst, const double* __res
   Lanes L; L.lane = threadIdx.x & 31; L.width = 32;
   CoopData<T>& d = *reinterpret_cast<CoopData<T>*>(smem + kConst + warp * kData);
   double best = 1.0e300; long long best_i = 0x7fffffffffffffffLL;
-  PS_LOOP2 for (;;) {
+  if (warp < active_warps) PS_LOOP2 for (;;) {
     int k = 0;
     if (L.lane == 0) k = atomicAdd(counter, 1);
     k = __shfl_sync(0xffffffffu, k, 0);

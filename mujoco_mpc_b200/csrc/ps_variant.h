@@ -66,10 +66,12 @@ inline int launch_coop(cudaStream_t st, const void* dconst, const double* knots,
   constexpr size_t kConst = (sizeof(Constants<T>) + 127) / 128 * 128, kData = (sizeof(CoopData<T>) + 127) / 128 * 128;
   constexpr size_t smem = kConst + WARPS * kData;
   static int resident[2] = {0, 0};                 // blocks the device keeps resident, per kernel flavour
+  static int sm_count = 0;
   const int f = writeback ? 1 : 0;
   if (!resident[f]) {
     int dev = 0, sms = 0, per_sm = 0;
     cudaGetDevice(&dev); cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    sm_count = sms > 0 ? sms : 148;
     if (writeback) {
       cudaFuncSetAttribute(coop_rollout_kernel<T, WARPS, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
       cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, coop_rollout_kernel<T, WARPS, true>, WARPS * 32, smem);
@@ -79,12 +81,16 @@ inline int launch_coop(cudaStream_t st, const void* dconst, const double* knots,
     }
     resident[f] = sms * (per_sm > 0 ? per_sm : 1);
   }
-  int grid = (n + WARPS - 1) / WARPS;
+  // small batches are spread over the SMs: only as many warps per block pull rollouts as the batch needs (coop_rollout_kernel)
+  int active = (n + sm_count - 1) / sm_count;
+  if (active < 1) active = 1;
+  if (active > WARPS) active = WARPS;
+  int grid = (n + active - 1) / active;
   if (grid > resident[f]) grid = resident[f];
   const Constants<T>* c = reinterpret_cast<const Constants<T>*>(dconst);
   cudaMemsetAsync(counter, 0, sizeof(int), st);
-  if (writeback) coop_rollout_kernel<T, WARPS, true><<<grid, WARPS * 32, smem, st>>>(c, knots, stride, first, n, offset, returns, failure, block_min, wb, counter);
-  else coop_rollout_kernel<T, WARPS, false><<<grid, WARPS * 32, smem, st>>>(c, knots, stride, first, n, offset, returns, failure, block_min, wb, counter);
+  if (writeback) coop_rollout_kernel<T, WARPS, true><<<grid, WARPS * 32, smem, st>>>(c, knots, stride, first, n, offset, returns, failure, block_min, wb, counter, active);
+  else coop_rollout_kernel<T, WARPS, false><<<grid, WARPS * 32, smem, st>>>(c, knots, stride, first, n, offset, returns, failure, block_min, wb, counter, active);
   return grid;
 }
 
